@@ -1,0 +1,172 @@
+/* libvaeclust.so -- C-ABI of the B200 (sm_100a) kernels behind the VAE-training and latent-clustering hot path
+ * of NawrozHaseen/VAE-for-Hybrid-Music-Clustering.
+ *
+ * The reference ships no native code and no FFI; every entry point below therefore cites the
+ * reference *call site* (file:line under /root/reference/scripts, or sklearn:<path> for the un-vendored
+ * scikit-learn arithmetic those scripts reach) that it replaces.  INTEGRATION.md shows the ctypes stubs a
+ * maintainer of the reference would add.
+ *
+ * Conventions
+ *   - every function returns VC_OK (0) or a negative VC_ERR_*; vc_last_error_string() describes the last failure
+ *     of the calling thread;
+ *   - all data pointers are DEVICE pointers owned by the caller unless the comment says "host"; nothing is
+ *     allocated, freed or synchronised inside the library; `stream` is a cudaStream_t passed as void*;
+ *   - dense tensors are contiguous, row-major, fp32 unless stated; activations at the boundary are NCHW and
+ *     weights use torch's state_dict layouts (Linear [out,in], Conv2d [Cout,Cin,kh,kw], ConvTranspose2d
+ *     [Cin,Cout,kh,kw]) so checkpoints interchange with the reference;
+ *   - workspace sizes come from the matching vc_*_workspace_bytes().
+ */
+#ifndef VAECLUST_H_
+#define VAECLUST_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define VC_OK 0
+#define VC_ERR_BAD_ARG (-1)
+#define VC_ERR_UNSUPPORTED (-2)
+#define VC_ERR_CUDA (-3)
+#define VC_ERR_WORKSPACE (-4)
+
+/* loss reduction conventions */
+#define VC_LOSS_MEAN_MEAN 0 /* scripts 06/12: mean over all elements for both terms (12:262-264, 06:182-188) */
+#define VC_LOSS_SUM_MEAN 1  /* script 19: feature-sum then batch-mean (19:226-228, 19:124-126)            */
+
+const char* vc_last_error_string(void);
+int vc_version(void);
+int vc_sm_count(void);
+
+/* ------------------------------------------------------------------------------------------------ VAE loss
+ * reparameterisation + KL (12:168-172,189-190; 19:105-108,124-126; 06:164-168,186):
+ *   z = mu + eps*exp(0.5*lv);  kl_rows[i] = -0.5 * sum_j (1 + lv - mu^2 - exp(lv))
+ * eps is supplied by the caller (torch.randn on the host side keeps the reference's RNG stream). */
+int vc_reparam_kl_fwd(const float* mu, const float* lv, const float* eps, int B, int z, float* z_out,
+                      float* kl_rows, void* stream);
+/* dmu = dz + dkl_rows[i]*mu ; dlv = dz*eps*0.5*exp(0.5 lv) + dkl_rows[i]*0.5*(exp(lv)-1).
+ * dz or dkl_rows may be NULL (treated as zero). */
+int vc_reparam_kl_bwd(const float* dz, const float* dkl_rows, const float* mu, const float* lv, const float* eps,
+                      int B, int z, float* dmu, float* dlv, void* stream);
+
+/* Reconstruction term with the crop of 12:260 folded in: xhat is [outer, Hh, Wh], x is [outer, H, W] with
+ * H<=Hh, W<=Wh; one pass computes sq_sum = sum (xhat-x)^2 over the cropped window (double, deterministic
+ * two-stage reduction) AND dxhat = grad_scale * 2 (xhat-x) (zero outside the window).  For 2-d inputs
+ * (scripts 06/19) pass outer=B, Hh=H=1, Wh=W=features.  dxhat may be NULL (forward only). */
+size_t vc_recon_loss_workspace_bytes(void);
+int vc_recon_loss_fwd_bwd(const float* xhat, const float* x, int64_t outer, int Hh, int Wh, int H, int W,
+                          float grad_scale, float* dxhat, double* sq_sum, void* workspace, size_t workspace_bytes,
+                          void* stream);
+/* out3 = {loss, recon, kl} (device floats) from sq_sum and kl_rows under `mode` (VC_LOSS_*). */
+int vc_loss_finalize(const double* sq_sum, const float* kl_rows, int B, int z, int64_t n_recon_elems, float beta,
+                     int mode, float* out3, void* stream);
+
+/* ------------------------------------------------------------------------------------------ dense layers
+ * nn.Linear (+ReLU) of 12:98-103,114-117,129-132,159-164; 19:79-95; 06:149-157.
+ * y[M,N] = act(x[M,K] W[N,K]^T + b[N]). */
+int vc_linear_fwd(const float* x, const float* W, const float* b, float* y, int M, int N, int K, int relu,
+                  void* stream);
+int vc_linear_dgrad(const float* dy, const float* W, float* dx, int M, int N, int K, void* stream);
+int vc_linear_wgrad(const float* dy, const float* x, float* dW, int M, int N, int K, int accumulate,
+                    void* stream);
+/* db[c] (+)= sum over outer,inner of dy[outer, C, inner]  (bias gradient of Linear: inner=1; Conv: inner=H*W) */
+int vc_bias_grad(const float* dy, int64_t outer, int C, int64_t inner, float* db, int accumulate, void* stream);
+/* dx = dy * (y > 0) */
+int vc_relu_bwd(const float* dy, const float* y, float* dx, int64_t n, void* stream);
+/* out[b,:] = [a[b,0:na], l[b,0:nl]*gate[b], gate[b] if append_gate]  -- `l*m` and torch.cat of 12:178-180 and
+ * the cat([x,c]) / cat([z,c]) of 19:97-115 (gate=NULL, append_gate=0). */
+int vc_cat_gate_fwd(const float* a, int na, const float* l, int nl, const float* gate, int append_gate, int B,
+                    float* out, void* stream);
+int vc_cat_gate_bwd(const float* dout, int na, int nl, const float* gate, int append_gate, int B, float* da,
+                    float* dl, void* stream);
+
+/* nn.Conv2d(Cin,Cout,3,stride=2,padding=1) (+ReLU) of 12:87-89.  x [B,Cin,H,W] -> y [B,Cout,OH,OW],
+ * OH=(H-1)/2+1, OW=(W-1)/2+1. */
+size_t vc_conv_wgrad_workspace_bytes(int Cout, int Cin, int ksize);
+int vc_conv2d_s2k3_fwd(const float* x, const float* W, const float* b, float* y, int B, int Cin, int H, int Wd,
+                       int Cout, int relu, void* stream);
+int vc_conv2d_s2k3_dgrad(const float* dy, const float* W, float* dx, int B, int Cin, int H, int Wd, int Cout,
+                         void* stream);
+int vc_conv2d_s2k3_wgrad(const float* dy, const float* x, float* dW, int B, int Cin, int H, int Wd, int Cout,
+                         void* workspace, size_t workspace_bytes, void* stream);
+/* nn.ConvTranspose2d(Cin,Cout,4,stride=2,padding=1) (+ReLU) of 12:135-137.  x [B,Cin,H,W] -> y [B,Cout,2H,2W]. */
+int vc_convT2d_s2k4_fwd(const float* x, const float* W, const float* b, float* y, int B, int Cin, int H, int Wd,
+                        int Cout, int relu, void* stream);
+int vc_convT2d_s2k4_dgrad(const float* dy, const float* W, float* dx, int B, int Cin, int H, int Wd, int Cout,
+                          void* stream);
+int vc_convT2d_s2k4_wgrad(const float* dy, const float* x, float* dW, int B, int Cin, int H, int Wd, int Cout,
+                          void* workspace, size_t workspace_bytes, void* stream);
+
+/* ------------------------------------------------------------------------------------------------- Adam
+ * torch.optim.Adam defaults (12:233, 19:202, 06:310): one launch over a device-resident table of chunks. */
+typedef struct VcAdamChunk {
+  float* p;
+  const float* g;
+  float* m;
+  float* v;
+  int64_t n;
+} VcAdamChunk;
+int vc_adam_multi(const VcAdamChunk* table, int n_chunks, float lr, float beta1, float beta2, float eps,
+                  float bias_corr1, float bias_corr2, void* stream);
+
+/* --------------------------------------------------------------------------------------------- KMeans
+ * One Lloyd iteration of sklearn:cluster/_k_means_lloyd.pyx:23-218 reached from 07:70-71, 13:120-121, 16:183,
+ * 20:68-69: labels[i] = first argmin_j (||c_j||^2 - 2 x_i.c_j); per-cluster sums/counts of the points.
+ * X [N,d] fp32 row-major (d % 4 == 0, d <= 256), C [k,d] (k <= 256).  `labels` holds the previous labels on
+ * entry (any value on the first iteration) and the new ones on exit; *n_changed counts differences.
+ * sums [k,d] and counts [k] are doubles reduced in a fixed order (deterministic).  update=0 skips the
+ * M-step accumulation (final E-step, _kmeans.py:742-754). */
+size_t vc_kmeans_workspace_bytes(int k, int d);
+int vc_kmeans_assign_update(const float* X, int64_t N, int d, const float* C, int k, int32_t* labels,
+                            double* sums, double* counts, int64_t* n_changed, int update, void* workspace,
+                            size_t workspace_bytes, void* stream);
+/* centers_new = sums/counts (count==0 keeps the old centre, _k_means_common.pyx:274-295);
+ * *shift_sq = sum_j ||c_new_j - c_old_j||^2 (:298-311). */
+int vc_kmeans_finalize(const double* sums, const double* counts, const float* C_old, int k, int d, float* C_new,
+                       double* shift_sq, void* stream);
+/* inertia = sum_i ||x_i - c_label(i)||^2 by direct differences (_k_means_common.pyx:94-124); optionally writes
+ * per-point squared distances (used by the empty-cluster relocation, :167-211). */
+int vc_kmeans_inertia(const float* X, int64_t N, int d, const float* C, int k, const int32_t* labels,
+                      double* inertia, float* point_sqdist, void* workspace, size_t workspace_bytes, void* stream);
+/* per-cluster sums/counts for given labels (M-step only; also first pass of Davies-Bouldin). */
+int vc_cluster_sums(const float* X, int64_t N, int d, const int32_t* labels, int k, double* sums, double* counts,
+                    void* workspace, size_t workspace_bytes, void* stream);
+/* column mean and (population) variance in double: KMeans centering + tol (_kmeans.py:285-293,1487-1490),
+ * StandardScaler (06:291-292, 07:67-68, 13:194, 16:178). */
+size_t vc_col_stats_workspace_bytes(int d);
+int vc_col_stats(const float* X, int64_t N, int d, double* mean, double* var, void* workspace,
+                 size_t workspace_bytes, void* stream);
+/* out = (X - shift) * scale  per column (shift/scale double [d]; scale may be NULL) */
+int vc_col_affine(const float* X, int64_t N, int d, const double* shift, const double* scale, float* out,
+                  void* stream);
+/* squared distances from m query rows Q [m,d] to every row of X -> out [m,N] (k-means++ potentials,
+ * _kmeans.py:180-278) */
+int vc_sqdist_rows(const float* X, int64_t N, int d, const float* Q, int m, float* out, void* stream);
+
+/* ----------------------------------------------------------------------------------------- silhouette
+ * sklearn:metrics/cluster/_unsupervised.py:149-200,211-323 reached from 13:74,78, 16:68,73, 20:45, 22:61.
+ * Xs is X permuted so that rows are grouped by cluster (cluster c occupies rows [off[c], off[c+1])); sqn are
+ * the squared row norms.  For rows [row_begin,row_end) computes cluster_sums[i-row_begin, c] =
+ * sum_{j in cluster c} ||x_i - x_j|| (self-distance forced to 0, pairwise.py:2285). */
+int vc_silhouette_gather(const float* X, int64_t N, int d, const int64_t* order, const double* shift, float* Xs,
+                         float* sqn, void* stream);
+int vc_silhouette_rows(const float* Xs, const float* sqn, int64_t N, int d, const int64_t* off_host, int k,
+                       int64_t row_begin, int64_t row_end, float* cluster_sums, void* stream);
+/* s_i = (b-a)/max(a,b) from cluster_sums (:191-200,315-323); writes s per row and *s_sum (double). */
+size_t vc_silhouette_finalize_workspace_bytes(void);
+int vc_silhouette_finalize(const float* cluster_sums, const int32_t* labels_sorted, const int64_t* counts_dev,
+                           int k, int64_t nrows, float* s_rows, double* s_sum, void* workspace,
+                           size_t workspace_bytes, void* stream);
+
+/* ------------------------------------------------------------------------------------- Davies-Bouldin
+ * sklearn:metrics/cluster/_unsupervised.py:457-487 reached from 13:94,98, 16:89,94.
+ * intra_sum[c] = sum_{i in c} ||x_i - centroid_c|| (double). */
+int vc_dbi_intra(const float* X, int64_t N, int d, const int32_t* labels, const double* centroids, int k,
+                 double* intra_sum, void* workspace, size_t workspace_bytes, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* VAECLUST_H_ */

@@ -1,0 +1,72 @@
+// Shared helpers for libvaeclust.so (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <cuda_bf16.h>
+#include <stdint.h>
+#include <stdio.h>
+#include "../../include/vaeclust.h"
+
+namespace vc {
+
+void set_error(const char* fmt, ...);
+
+#define VC_REQUIRE(cond, code, ...)                 \
+  do {                                              \
+    if (!(cond)) {                                  \
+      ::vc::set_error(__VA_ARGS__);                 \
+      return (code);                                \
+    }                                               \
+  } while (0)
+
+#define VC_LAUNCH_CHECK()                                                        \
+  do {                                                                           \
+    cudaError_t e__ = cudaGetLastError();                                        \
+    if (e__ != cudaSuccess) {                                                    \
+      ::vc::set_error("%s:%d CUDA launch failed: %s", __FILE__, __LINE__,        \
+                      cudaGetErrorString(e__));                                  \
+      return VC_ERR_CUDA;                                                        \
+    }                                                                            \
+  } while (0)
+
+#define VC_CUDA(call)                                                            \
+  do {                                                                           \
+    cudaError_t e__ = (call);                                                    \
+    if (e__ != cudaSuccess) {                                                    \
+      ::vc::set_error("%s:%d %s: %s", __FILE__, __LINE__, #call,                 \
+                      cudaGetErrorString(e__));                                  \
+      return VC_ERR_CUDA;                                                        \
+    }                                                                            \
+  } while (0)
+
+int sm_count();
+
+static inline cudaStream_t as_stream(void* s) { return reinterpret_cast<cudaStream_t>(s); }
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ double warp_sum(double v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+// Block-wide sum, result valid in thread 0. `scratch` holds >= 32 elements.
+template <typename T>
+__device__ __forceinline__ T block_sum(T v, T* scratch) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  v = warp_sum(v);
+  __syncthreads();
+  if (lane == 0) scratch[warp] = v;
+  __syncthreads();
+  const int nw = (blockDim.x + 31) >> 5;
+  if (warp == 0) {
+    v = lane < nw ? scratch[lane] : T(0);
+    v = warp_sum(v);
+  }
+  return v;
+}
+
+}  // namespace vc

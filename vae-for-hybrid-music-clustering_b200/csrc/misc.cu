@@ -1,0 +1,314 @@
+// Library core (error string, device info) and the small HBM-bound helpers: ReLU backward, bias gradient,
+// gate+concat, multi-tensor Adam, column statistics / affine (KMeans centering, StandardScaler).
+#include <stdarg.h>
+#include "common.cuh"
+
+namespace vc {
+
+static thread_local char g_err[512] = "";
+
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+
+int sm_count() {
+  static int cached = 0;
+  if (cached) return cached;
+  int dev = 0, n = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) return 148;
+  if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) return 148;
+  cached = n;
+  return n;
+}
+
+__global__ void relu_bwd_kernel(const float* __restrict__ dy, const float* __restrict__ y, float* __restrict__ dx,
+                                int64_t n) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride)
+    dx[i] = y[i] > 0.f ? dy[i] : 0.f;
+}
+
+__global__ void relu_bwd_vec_kernel(const float4* __restrict__ dy, const float4* __restrict__ y,
+                                    float4* __restrict__ dx, int64_t n4) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += stride) {
+    const float4 g = dy[i], v = y[i];
+    dx[i] = make_float4(v.x > 0.f ? g.x : 0.f, v.y > 0.f ? g.y : 0.f, v.z > 0.f ? g.z : 0.f,
+                        v.w > 0.f ? g.w : 0.f);
+  }
+}
+
+// db[c] = sum_{o,i} dy[o,C,inner]; one block per channel, fixed-order (deterministic) reduction.
+__global__ void bias_grad_kernel(const float* __restrict__ dy, int64_t outer, int C, int64_t inner,
+                                 float* __restrict__ db, int accumulate) {
+  __shared__ double scratch[32];
+  const int c = blockIdx.x;
+  double acc = 0.0;
+  if (inner == 1) {
+    for (int64_t o = threadIdx.x; o < outer; o += blockDim.x) acc += (double)dy[o * C + c];
+  } else {
+    for (int64_t o = 0; o < outer; ++o) {
+      const float* p = dy + (o * C + c) * inner;
+      float part = 0.f;
+      for (int64_t i = threadIdx.x; i < inner; i += blockDim.x) part += p[i];
+      acc += (double)part;
+    }
+  }
+  acc = block_sum<double>(acc, scratch);
+  if (threadIdx.x == 0) db[c] = (accumulate ? db[c] : 0.f) + (float)acc;
+}
+
+__global__ void cat_gate_fwd_kernel(const float* __restrict__ a, int na, const float* __restrict__ l, int nl,
+                                    const float* __restrict__ gate, int append_gate, int B,
+                                    float* __restrict__ out) {
+  const int wout = na + nl + (append_gate ? 1 : 0);
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= B * wout) return;
+  const int r = i / wout, c = i % wout;
+  const float g = gate ? gate[r] : 1.f;
+  float v;
+  if (c < na) v = a[r * na + c];
+  else if (c < na + nl) v = l[r * nl + (c - na)] * g;
+  else v = g;
+  out[i] = v;
+}
+
+__global__ void cat_gate_bwd_kernel(const float* __restrict__ dout, int na, int nl, const float* __restrict__ gate,
+                                    int append_gate, int B, float* __restrict__ da, float* __restrict__ dl) {
+  const int wout = na + nl + (append_gate ? 1 : 0);
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= B * (na + nl)) return;
+  const int r = i / (na + nl), c = i % (na + nl);
+  const float g = gate ? gate[r] : 1.f;
+  const float v = dout[r * wout + c];
+  if (c < na) {
+    if (da) da[r * na + c] = v;
+  } else {
+    if (dl) dl[r * nl + (c - na)] = v * g;
+  }
+}
+
+constexpr int kAdamThreads = 256;
+
+__global__ void __launch_bounds__(kAdamThreads)
+adam_multi_kernel(const VcAdamChunk* __restrict__ table, float lr, float b1, float b2, float eps, float bc1,
+                  float bc2) {
+  const VcAdamChunk ch = table[blockIdx.x];
+  // torch.optim.Adam (single-tensor, non-capturable) arithmetic order:
+  //   m = b1*m + (1-b1)*g ; v = b2*v + (1-b2)*g*g ; p -= (lr/bc1) * m / (sqrt(v)/sqrt(bc2) + eps)
+  const float step_size = lr / bc1;
+  const float inv_sqrt_bc2 = 1.f / sqrtf(bc2);
+  const bool vec = ((reinterpret_cast<uintptr_t>(ch.p) | reinterpret_cast<uintptr_t>(ch.g) |
+                     reinterpret_cast<uintptr_t>(ch.m) | reinterpret_cast<uintptr_t>(ch.v)) & 15) == 0;
+  const int64_t n = ch.n;
+  if (vec) {
+    const int64_t n4 = n >> 2;
+    float4* p4 = reinterpret_cast<float4*>(ch.p);
+    const float4* g4 = reinterpret_cast<const float4*>(ch.g);
+    float4* m4 = reinterpret_cast<float4*>(ch.m);
+    float4* v4 = reinterpret_cast<float4*>(ch.v);
+    for (int64_t i = threadIdx.x; i < n4; i += kAdamThreads) {
+      float4 p = p4[i], m = m4[i], v = v4[i];
+      const float4 g = __ldcs(g4 + i);
+#define VC_ADAM1(c)                                           \
+  m.c = b1 * m.c + (1.f - b1) * g.c;                          \
+  v.c = b2 * v.c + (1.f - b2) * g.c * g.c;                    \
+  p.c -= step_size * (m.c / (sqrtf(v.c) * inv_sqrt_bc2 + eps));
+      VC_ADAM1(x) VC_ADAM1(y) VC_ADAM1(z) VC_ADAM1(w)
+#undef VC_ADAM1
+      p4[i] = p;
+      m4[i] = m;
+      v4[i] = v;
+    }
+    for (int64_t i = (n4 << 2) + threadIdx.x; i < n; i += kAdamThreads) {
+      const float g = ch.g[i];
+      const float m = b1 * ch.m[i] + (1.f - b1) * g;
+      const float v = b2 * ch.v[i] + (1.f - b2) * g * g;
+      ch.m[i] = m;
+      ch.v[i] = v;
+      ch.p[i] -= step_size * (m / (sqrtf(v) * inv_sqrt_bc2 + eps));
+    }
+  } else {
+    for (int64_t i = threadIdx.x; i < n; i += kAdamThreads) {
+      const float g = ch.g[i];
+      const float m = b1 * ch.m[i] + (1.f - b1) * g;
+      const float v = b2 * ch.v[i] + (1.f - b2) * g * g;
+      ch.m[i] = m;
+      ch.v[i] = v;
+      ch.p[i] -= step_size * (m / (sqrtf(v) * inv_sqrt_bc2 + eps));
+    }
+  }
+}
+
+// ---- column statistics: two-stage, fixed order.  Stage 1: each block owns a contiguous row range and writes
+// per-column (sum, sumsq about a pivot row) in double.  d <= 1024.
+constexpr int kColBlocks = 148 * 4;
+
+__global__ void col_stats_stage1(const float* __restrict__ X, int64_t N, int d, double* __restrict__ part) {
+  // threads: x = column (<= d rounded), y = row lane
+  extern __shared__ double sh[];
+  const int tx = threadIdx.x, ty = threadIdx.y;
+  const int64_t rows_per = (N + gridDim.x - 1) / gridDim.x;
+  const int64_t r0 = (int64_t)blockIdx.x * rows_per;
+  const int64_t r1 = r0 + rows_per < N ? r0 + rows_per : N;
+  for (int c = tx; c < d; c += blockDim.x) {
+    const double pivot = (double)X[c];  // row 0 as pivot keeps sumsq well conditioned
+    double s = 0.0, q = 0.0;
+    for (int64_t r = r0 + ty; r < r1; r += blockDim.y) {
+      const double v = (double)X[r * d + c] - pivot;
+      s += v;
+      q += v * v;
+    }
+    sh[(ty * d + c) * 2 + 0] = s;
+    sh[(ty * d + c) * 2 + 1] = q;
+  }
+  __syncthreads();
+  if (ty == 0) {
+    for (int c = tx; c < d; c += blockDim.x) {
+      double s = 0.0, q = 0.0;
+      for (int y = 0; y < blockDim.y; ++y) {
+        s += sh[(y * d + c) * 2 + 0];
+        q += sh[(y * d + c) * 2 + 1];
+      }
+      part[((int64_t)blockIdx.x * d + c) * 2 + 0] = s;
+      part[((int64_t)blockIdx.x * d + c) * 2 + 1] = q;
+    }
+  }
+}
+
+__global__ void col_stats_stage2(const float* __restrict__ X, const double* __restrict__ part, int nblocks,
+                                 int64_t N, int d, double* __restrict__ mean, double* __restrict__ var) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= d) return;
+  double s = 0.0, q = 0.0;
+  for (int b = 0; b < nblocks; ++b) {
+    s += part[((int64_t)b * d + c) * 2 + 0];
+    q += part[((int64_t)b * d + c) * 2 + 1];
+  }
+  const double pivot = (double)X[c];
+  const double ms = s / (double)N;
+  mean[c] = pivot + ms;
+  if (var) {
+    double v = q / (double)N - ms * ms;
+    var[c] = v > 0.0 ? v : 0.0;
+  }
+}
+
+__global__ void col_affine_kernel(const float* __restrict__ X, int64_t n, int d, const double* __restrict__ shift,
+                                  const double* __restrict__ scale, float* __restrict__ out) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+    const int c = (int)(i % d);
+    // numpy's in-place `X -= mean; X /= scale` on a float32 array with float64 operands: each op is
+    // evaluated in double and rounded back to float32.
+    float v = (float)((double)X[i] - shift[c]);
+    if (scale) v = (float)((double)v / scale[c]);
+    out[i] = v;
+  }
+}
+
+}  // namespace vc
+
+using namespace vc;
+
+extern "C" const char* vc_last_error_string(void) { return g_err; }
+extern "C" int vc_version(void) { return 100; }
+extern "C" int vc_sm_count(void) { return sm_count(); }
+
+static inline int grid_for(int64_t n, int threads, int per_thread) {
+  int64_t b = (n + (int64_t)threads * per_thread - 1) / ((int64_t)threads * per_thread);
+  const int64_t cap = (int64_t)sm_count() * 16;
+  if (b > cap) b = cap;
+  if (b < 1) b = 1;
+  return (int)b;
+}
+
+extern "C" int vc_relu_bwd(const float* dy, const float* y, float* dx, int64_t n, void* stream) {
+  VC_REQUIRE(dy && y && dx && n >= 0, VC_ERR_BAD_ARG, "vc_relu_bwd: bad arguments");
+  if (n == 0) return VC_OK;
+  const bool vec = n % 4 == 0 && ((reinterpret_cast<uintptr_t>(dy) | reinterpret_cast<uintptr_t>(y) |
+                                   reinterpret_cast<uintptr_t>(dx)) & 15) == 0;
+  if (vec)
+    relu_bwd_vec_kernel<<<grid_for(n / 4, 256, 2), 256, 0, as_stream(stream)>>>(
+        reinterpret_cast<const float4*>(dy), reinterpret_cast<const float4*>(y), reinterpret_cast<float4*>(dx),
+        n / 4);
+  else
+    relu_bwd_kernel<<<grid_for(n, 256, 4), 256, 0, as_stream(stream)>>>(dy, y, dx, n);
+  VC_LAUNCH_CHECK();
+  return VC_OK;
+}
+
+extern "C" int vc_bias_grad(const float* dy, int64_t outer, int C, int64_t inner, float* db, int accumulate,
+                            void* stream) {
+  VC_REQUIRE(dy && db && outer > 0 && C > 0 && inner > 0, VC_ERR_BAD_ARG, "vc_bias_grad: bad arguments");
+  bias_grad_kernel<<<C, 256, 0, as_stream(stream)>>>(dy, outer, C, inner, db, accumulate);
+  VC_LAUNCH_CHECK();
+  return VC_OK;
+}
+
+extern "C" int vc_cat_gate_fwd(const float* a, int na, const float* l, int nl, const float* gate, int append_gate,
+                               int B, float* out, void* stream) {
+  VC_REQUIRE(out && B > 0 && na >= 0 && nl >= 0 && (na == 0 || a) && (nl == 0 || l), VC_ERR_BAD_ARG,
+             "vc_cat_gate_fwd: bad arguments");
+  VC_REQUIRE(!append_gate || gate, VC_ERR_BAD_ARG, "vc_cat_gate_fwd: append_gate without gate");
+  const int n = B * (na + nl + (append_gate ? 1 : 0));
+  cat_gate_fwd_kernel<<<(n + 255) / 256, 256, 0, as_stream(stream)>>>(a, na, l, nl, gate, append_gate, B, out);
+  VC_LAUNCH_CHECK();
+  return VC_OK;
+}
+
+extern "C" int vc_cat_gate_bwd(const float* dout, int na, int nl, const float* gate, int append_gate, int B,
+                               float* da, float* dl, void* stream) {
+  VC_REQUIRE(dout && B > 0 && na >= 0 && nl >= 0, VC_ERR_BAD_ARG, "vc_cat_gate_bwd: bad arguments");
+  const int n = B * (na + nl);
+  if (n == 0) return VC_OK;
+  cat_gate_bwd_kernel<<<(n + 255) / 256, 256, 0, as_stream(stream)>>>(dout, na, nl, gate, append_gate, B, da, dl);
+  VC_LAUNCH_CHECK();
+  return VC_OK;
+}
+
+extern "C" int vc_adam_multi(const VcAdamChunk* table, int n_chunks, float lr, float beta1, float beta2, float eps,
+                             float bias_corr1, float bias_corr2, void* stream) {
+  VC_REQUIRE(table && n_chunks >= 0, VC_ERR_BAD_ARG, "vc_adam_multi: bad arguments");
+  if (n_chunks == 0) return VC_OK;
+  adam_multi_kernel<<<n_chunks, kAdamThreads, 0, as_stream(stream)>>>(table, lr, beta1, beta2, eps, bias_corr1,
+                                                                     bias_corr2);
+  VC_LAUNCH_CHECK();
+  return VC_OK;
+}
+
+extern "C" size_t vc_col_stats_workspace_bytes(int d) { return sizeof(double) * 2 * (size_t)kColBlocks * d; }
+
+extern "C" int vc_col_stats(const float* X, int64_t N, int d, double* mean, double* var, void* workspace,
+                            size_t workspace_bytes, void* stream) {
+  VC_REQUIRE(X && mean && N > 0 && d > 0 && d <= 1024, VC_ERR_BAD_ARG, "vc_col_stats: bad arguments (N=%lld d=%d)",
+             (long long)N, d);
+  VC_REQUIRE(workspace && workspace_bytes >= vc_col_stats_workspace_bytes(d), VC_ERR_WORKSPACE,
+             "vc_col_stats: workspace too small");
+  int tx = 32;
+  while (tx < d && tx < 256) tx <<= 1;
+  int ty = 512 / tx;
+  // shared memory: ty*d*2 doubles
+  while ((size_t)ty * d * 2 * sizeof(double) > 40000 && ty > 1) ty >>= 1;
+  int blocks = kColBlocks;
+  if ((int64_t)blocks * ty > N) blocks = (int)((N + ty - 1) / ty);
+  if (blocks < 1) blocks = 1;
+  double* part = static_cast<double*>(workspace);
+  col_stats_stage1<<<blocks, dim3(tx, ty), (size_t)ty * d * 2 * sizeof(double), as_stream(stream)>>>(X, N, d, part);
+  VC_LAUNCH_CHECK();
+  col_stats_stage2<<<(d + 127) / 128, 128, 0, as_stream(stream)>>>(X, part, blocks, N, d, mean, var);
+  VC_LAUNCH_CHECK();
+  return VC_OK;
+}
+
+extern "C" int vc_col_affine(const float* X, int64_t N, int d, const double* shift, const double* scale, float* out,
+                             void* stream) {
+  VC_REQUIRE(X && out && shift && N > 0 && d > 0, VC_ERR_BAD_ARG, "vc_col_affine: bad arguments");
+  const int64_t n = N * d;
+  col_affine_kernel<<<grid_for(n, 256, 4), 256, 0, as_stream(stream)>>>(X, n, d, shift, scale, out);
+  VC_LAUNCH_CHECK();
+  return VC_OK;
+}
