@@ -148,17 +148,20 @@ int vc_sqdist_rows(const float* X, int64_t N, int d, const float* Q, int m, floa
 /* ----------------------------------------------------------------------------------------- silhouette
  * sklearn:metrics/cluster/_unsupervised.py:149-200,211-323 reached from 13:74,78, 16:68,73, 20:45, 22:61.
  * Xs is X permuted so that rows are grouped by cluster (cluster c occupies rows [off[c], off[c+1])); sqn are
- * the squared row norms.  For rows [row_begin,row_end) computes cluster_sums[i-row_begin, c] =
- * sum_{j in cluster c} ||x_i - x_j|| (self-distance forced to 0, pairwise.py:2285). */
+ * the squared row norms; off_dev is a DEVICE array of k+1 int64 offsets.  For rows [row_begin,row_end) computes
+ * cluster_sums[s, i-row_begin, c] = sum over the column tiles of cluster c owned by split s (s < nsplit; splits
+ * only add parallelism for small N) of ||x_i - x_j|| (self-distance forced to 0, pairwise.py:2285).
+ * cluster_sums is [nsplit, row_end-row_begin, k]. */
 int vc_silhouette_gather(const float* X, int64_t N, int d, const int64_t* order, const double* shift, float* Xs,
                          float* sqn, void* stream);
-int vc_silhouette_rows(const float* Xs, const float* sqn, int64_t N, int d, const int64_t* off_host, int k,
-                       int64_t row_begin, int64_t row_end, float* cluster_sums, void* stream);
-/* s_i = (b-a)/max(a,b) from cluster_sums (:191-200,315-323); writes s per row and *s_sum (double). */
+int vc_silhouette_rows(const float* Xs, const float* sqn, int64_t N, int d, const int64_t* off_dev, int k,
+                       int64_t row_begin, int64_t row_end, int nsplit, float* cluster_sums, void* stream);
+/* s_i = (b-a)/max(a,b) from cluster_sums (:191-200,315-323); writes s per row and *s_sum (double).
+ * labels_sorted points at the label of row_begin. */
 size_t vc_silhouette_finalize_workspace_bytes(void);
-int vc_silhouette_finalize(const float* cluster_sums, const int32_t* labels_sorted, const int64_t* counts_dev,
-                           int k, int64_t nrows, float* s_rows, double* s_sum, void* workspace,
-                           size_t workspace_bytes, void* stream);
+int vc_silhouette_finalize(const float* cluster_sums, int nsplit, const int32_t* labels_sorted,
+                           const int64_t* counts_dev, int k, int64_t nrows, float* s_rows, double* s_sum,
+                           void* workspace, size_t workspace_bytes, void* stream);
 
 /* ------------------------------------------------------------------------------------- Davies-Bouldin
  * sklearn:metrics/cluster/_unsupervised.py:457-487 reached from 13:94,98, 16:89,94.

@@ -1,0 +1,501 @@
+// KMeans Lloyd iteration, fused assign + update in ONE pass over X (132 B/point of HBM traffic at d=32).
+//
+// Persistent CTAs (2 per SM).  Each CTA streams tiles of TP points: the tile is one contiguous slab of X, moved
+// global->shared by a single 1-D bulk async copy (cp.async.bulk, the TMA engine) into a 2-deep mbarrier ring, so
+// the copy of tile t+2 overlaps the arithmetic of tile t+1.
+//   phase A (thread = point): x row in registers, centroids broadcast from shared memory,
+//            pd_j = ||c_j||^2 - 2 x.c_j, first-minimum argmin with strict '<' (sklearn:_k_means_lloyd.pyx:196-213);
+//   phase B (warp = the 32 points it just labelled, lane = dimension): labels exchanged by shuffle, the row is
+//            added to a warp-private shared-memory accumulator [k,d] with plain (conflict-free, race-free) RMW.
+// Warp accumulators are folded into a per-CTA double accumulator every kFlush tiles, CTAs write double partials,
+// and a second kernel reduces them in a fixed order: bit-reproducible run to run, no floating-point atomics.
+#include "common.cuh"
+
+namespace vc {
+
+constexpr int kKmThreads = 256;
+constexpr int kKmWarps = kKmThreads / 32;
+constexpr int kFlush = 16;
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "WAIT_%=:\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+      "@p bra DONE_%=;\n\t"
+      "bra WAIT_%=;\n\t"
+      "DONE_%=:\n\t}" ::"r"(smem_u32(bar)),
+      "r"(parity)
+      : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                   smem_u32(dst)),
+               "l"(src), "r"(bytes), "r"(smem_u32(bar))
+               : "memory");
+}
+
+struct KmSmem {
+  int tp;             // points per tile
+  int ncopies;        // accumulator copies (warps * groups)
+  size_t off_acc, off_dsum, off_c, off_c2, off_cnt, off_bar, total;
+};
+
+static KmSmem km_layout(int k, int d, int update) {
+  KmSmem L;
+  int tp = 256;
+  while (tp > 32 && (size_t)2 * tp * d * 4 > 128 * 1024) tp >>= 1;
+  L.tp = tp;
+  const int groups = (d <= 16 && 32 % d == 0) ? 32 / d : 1;
+  L.ncopies = update ? kKmWarps * groups : 0;
+  size_t o = (size_t)2 * tp * d * 4;
+  L.off_acc = o;  o += (size_t)L.ncopies * k * d * 4;
+  o = (o + 7) & ~(size_t)7;
+  L.off_dsum = o; o += update ? (size_t)k * d * 8 : 0;
+  L.off_c = o;    o += (size_t)k * d * 4;
+  L.off_c2 = o;   o += (size_t)k * 4;
+  L.off_cnt = o;  o += (size_t)k * 4;
+  o = (o + 7) & ~(size_t)7;
+  L.off_bar = o;  o += 16;
+  L.total = o;
+  return L;
+}
+
+// D4 = d/4 when compile-time (register-resident row), 0 = generic d read from shared memory.
+template <int D4>
+__global__ void __launch_bounds__(kKmThreads)
+kmeans_assign_update_kernel(const float* __restrict__ X, int64_t N, int d, const float* __restrict__ C, int k,
+                            int32_t* __restrict__ labels, double* __restrict__ part_sums,
+                            long long* __restrict__ part_counts, unsigned long long* __restrict__ n_changed,
+                            int update, int assign, int tp, int ncopies, size_t off_acc, size_t off_dsum, size_t off_c,
+                            size_t off_c2, size_t off_cnt, size_t off_bar) {
+  extern __shared__ __align__(128) unsigned char smem[];
+  float* tile[2] = {reinterpret_cast<float*>(smem), reinterpret_cast<float*>(smem) + (size_t)tp * d};
+  float* acc = reinterpret_cast<float*>(smem + off_acc);
+  double* dsum = reinterpret_cast<double*>(smem + off_dsum);
+  float* cs = reinterpret_cast<float*>(smem + off_c);
+  float* c2 = reinterpret_cast<float*>(smem + off_c2);
+  int* cnt = reinterpret_cast<int*>(smem + off_cnt);
+  uint64_t* bar = reinterpret_cast<uint64_t*>(smem + off_bar);
+
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int kd = k * d;
+  const int64_t ntiles = (N + tp - 1) / tp;
+
+  if (tid == 0) {
+    mbar_init(&bar[0], 1);
+    mbar_init(&bar[1], 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  for (int i = tid; i < kd; i += kKmThreads) cs[i] = C[i];
+  for (int i = tid; i < k; i += kKmThreads) cnt[i] = 0;
+  if (update) {
+    for (int i = tid; i < ncopies * kd; i += kKmThreads) acc[i] = 0.f;
+    for (int i = tid; i < kd; i += kKmThreads) dsum[i] = 0.0;
+  }
+  __syncthreads();
+  for (int c = warp; c < k; c += kKmWarps) {  // ||c||^2 in the same dimension order as the dot products
+    float s = 0.f;
+    for (int j = lane; j < d; j += 32) s += cs[c * d + j] * cs[c * d + j];
+    s = warp_sum(s);
+    if (lane == 0) c2[c] = s;
+  }
+  // prologue: first two tiles of this CTA
+  if (tid == 0) {
+#pragma unroll
+    for (int b = 0; b < 2; ++b) {
+      const int64_t t = (int64_t)blockIdx.x + (int64_t)b * gridDim.x;
+      if (t < ntiles) {
+        const int64_t p0 = t * tp;
+        const uint32_t bytes = (uint32_t)((N - p0 < tp ? N - p0 : tp) * d * 4);
+        mbar_expect_tx(&bar[b], bytes);
+        bulk_g2s(tile[b], X + p0 * d, bytes, &bar[b]);
+      }
+    }
+  }
+  __syncthreads();
+
+  unsigned long long my_changed = 0;
+  int it = 0;
+  for (int64_t t = blockIdx.x; t < ntiles; t += gridDim.x, ++it) {
+    const int b = it & 1;
+    const uint32_t parity = (it >> 1) & 1;
+    mbar_wait(&bar[b], parity);
+    const float* xt = tile[b];
+    const int64_t p0 = t * tp;
+    const int npts = (int)(N - p0 < tp ? N - p0 : tp);
+
+    // ---------------- phase A: distances + argmin, thread = point
+    int label = -1;
+    if (tid < npts && !assign) {
+      label = labels[p0 + tid];
+      if ((unsigned)label >= (unsigned)k) label = -1;
+      else atomicAdd(&cnt[label], 1);
+    } else if (tid < npts) {
+      float best = 0.f;
+      if (D4 > 0) {
+        float4 xr[D4 > 0 ? D4 : 1];
+        const float4* row = reinterpret_cast<const float4*>(xt + (size_t)tid * d);
+#pragma unroll
+        for (int j = 0; j < D4; ++j) xr[j] = row[j];
+        for (int c = 0; c < k; ++c) {
+          const float4* cr = reinterpret_cast<const float4*>(cs + c * d);
+          float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+#pragma unroll
+          for (int j = 0; j < D4; ++j) {
+            const float4 cv = cr[j];
+            s0 = fmaf(xr[j].x, cv.x, s0);
+            s1 = fmaf(xr[j].y, cv.y, s1);
+            s2 = fmaf(xr[j].z, cv.z, s2);
+            s3 = fmaf(xr[j].w, cv.w, s3);
+          }
+          const float pd = fmaf(-2.f, (s0 + s1) + (s2 + s3), c2[c]);
+          if (c == 0 || pd < best) { best = pd; label = c; }
+        }
+      } else {
+        const float4* row = reinterpret_cast<const float4*>(xt + (size_t)tid * d);
+        const int d4 = d >> 2;
+        for (int c = 0; c < k; ++c) {
+          const float4* cr = reinterpret_cast<const float4*>(cs + c * d);
+          float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+          for (int j = 0; j < d4; ++j) {
+            const float4 xv = row[j], cv = cr[j];
+            s0 = fmaf(xv.x, cv.x, s0);
+            s1 = fmaf(xv.y, cv.y, s1);
+            s2 = fmaf(xv.z, cv.z, s2);
+            s3 = fmaf(xv.w, cv.w, s3);
+          }
+          const float pd = fmaf(-2.f, (s0 + s1) + (s2 + s3), c2[c]);
+          if (c == 0 || pd < best) { best = pd; label = c; }
+        }
+      }
+      const int32_t old = labels[p0 + tid];
+      labels[p0 + tid] = label;
+      my_changed += (old != label);
+      if (update) atomicAdd(&cnt[label], 1);
+    }
+
+    // ---------------- phase B: centroid-sum update, warp = its own 32 points, lane = dimension
+    if (update) {
+      const int wp0 = warp * 32;  // first point (within the tile) of this warp
+      if (d <= 16 && 32 % d == 0) {
+        const int groups = 32 / d, g = lane / d, dim = lane % d;
+        float* my = acc + (size_t)(warp * groups + g) * kd;
+        for (int q = g; q < 32; q += groups) {
+          const int lab = __shfl_sync(0xffffffffu, label, q);
+          if (lab >= 0) my[lab * d + dim] += xt[(size_t)(wp0 + q) * d + dim];
+        }
+      } else {
+        float* my = acc + (size_t)warp * kd;
+        for (int q = 0; q < 32; ++q) {
+          const int lab = __shfl_sync(0xffffffffu, label, q);
+          if (lab >= 0) {
+            for (int dim = lane; dim < d; dim += 32) my[lab * d + dim] += xt[(size_t)(wp0 + q) * d + dim];
+          }
+        }
+      }
+    }
+    __syncthreads();  // every warp is done with tile[b]
+    if (update && ((it + 1) % kFlush == 0)) {
+      for (int e = tid; e < kd; e += kKmThreads) {
+        double s = 0.0;
+        for (int cpy = 0; cpy < ncopies; ++cpy) {
+          s += (double)acc[(size_t)cpy * kd + e];
+          acc[(size_t)cpy * kd + e] = 0.f;
+        }
+        dsum[e] += s;
+      }
+      __syncthreads();
+    }
+    if (tid == 0) {
+      const int64_t tn = t + 2 * (int64_t)gridDim.x;
+      if (tn < ntiles) {
+        const int64_t pn = tn * tp;
+        const uint32_t bytes = (uint32_t)((N - pn < tp ? N - pn : tp) * d * 4);
+        // order the generic-proxy reads of tile[b] before the async-proxy overwrite
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        mbar_expect_tx(&bar[b], bytes);
+        bulk_g2s(tile[b], X + pn * d, bytes, &bar[b]);
+      }
+    }
+  }
+
+  // ---------------- epilogue: per-CTA partials in double, fixed order
+  __syncthreads();
+  if (update) {
+    for (int e = tid; e < kd; e += kKmThreads) {
+      double s = dsum[e];
+      for (int cpy = 0; cpy < ncopies; ++cpy) s += (double)acc[(size_t)cpy * kd + e];
+      part_sums[(size_t)blockIdx.x * kd + e] = s;
+    }
+    for (int c = tid; c < k; c += kKmThreads) part_counts[(size_t)blockIdx.x * k + c] = cnt[c];
+  }
+  my_changed = (unsigned long long)__reduce_add_sync(0xffffffffu, (unsigned)my_changed);
+  if (lane == 0 && my_changed) atomicAdd(n_changed, my_changed);
+}
+
+__global__ void kmeans_reduce_partials_kernel(const double* __restrict__ part_sums,
+                                              const long long* __restrict__ part_counts, int nblocks, int k, int d,
+                                              double* __restrict__ sums, double* __restrict__ counts) {
+  const int e = blockIdx.x * blockDim.x + threadIdx.x;
+  const int kd = k * d;
+  if (e < kd) {
+    double s = 0.0;
+    for (int b = 0; b < nblocks; ++b) s += part_sums[(size_t)b * kd + e];
+    sums[e] = s;
+  }
+  if (e < k) {
+    long long c = 0;
+    for (int b = 0; b < nblocks; ++b) c += part_counts[(size_t)b * k + e];
+    counts[e] = (double)c;
+  }
+}
+
+
+__global__ void kmeans_finalize_kernel(const double* __restrict__ sums, const double* __restrict__ counts,
+                                       const float* __restrict__ C_old, int k, int d, float* __restrict__ C_new,
+                                       double* __restrict__ shift_sq) {
+  __shared__ double scratch[32];
+  double acc = 0.0;
+  for (int e = threadIdx.x; e < k * d; e += blockDim.x) {
+    const int c = e / d;
+    const double n = counts[c];
+    const float old = C_old[e];
+    const float nw = n > 0.0 ? (float)(sums[e] / n) : old;
+    C_new[e] = nw;
+    const double df = (double)nw - (double)old;
+    acc += df * df;
+  }
+  acc = block_sum<double>(acc, scratch);
+  if (threadIdx.x == 0 && shift_sq) *shift_sq = acc;
+}
+
+// Per-point distance to the centre of its label.  MODE 0: squared distance in fp32 (direct differences), summed
+// into acc[0]; MODE 1: Euclidean distance against double centroids, summed per cluster (Davies-Bouldin intra).
+template <int MODE>
+__global__ void __launch_bounds__(256)
+point_dist_kernel(const float* __restrict__ X, int64_t N, int d, const float* __restrict__ Cf,
+                  const double* __restrict__ Cd, int k, const int32_t* __restrict__ labels,
+                  float* __restrict__ point_out, double* __restrict__ part, int nacc) {
+  extern __shared__ double wacc[];  // [warps][nacc]
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
+  for (int i = threadIdx.x; i < nwarps * nacc; i += blockDim.x) wacc[i] = 0.0;
+  __syncthreads();
+  double* mine = wacc + warp * nacc;
+  const int64_t gw = (int64_t)blockIdx.x * nwarps + warp, nw = (int64_t)gridDim.x * nwarps;
+  for (int64_t i = gw; i < N; i += nw) {
+    const int lab = labels[i];
+    if ((unsigned)lab >= (unsigned)k) continue;
+    double v;
+    if (MODE == 0) {
+      float s = 0.f;
+      for (int j = lane; j < d; j += 32) {
+        const float df = X[i * d + j] - Cf[lab * d + j];
+        s = fmaf(df, df, s);
+      }
+      s = warp_sum(s);
+      if (point_out && lane == 0) point_out[i] = s;
+      v = (double)s;
+    } else {
+      double s = 0.0;
+      for (int j = lane; j < d; j += 32) {
+        const double df = (double)X[i * d + j] - Cd[lab * d + j];
+        s += df * df;
+      }
+      s = warp_sum(s);
+      v = sqrt(s);
+    }
+    if (lane == 0) mine[MODE == 0 ? 0 : lab] += v;
+  }
+  __syncthreads();
+  for (int a = threadIdx.x; a < nacc; a += blockDim.x) {
+    double s = 0.0;
+    for (int w = 0; w < nwarps; ++w) s += wacc[w * nacc + a];
+    part[(size_t)blockIdx.x * nacc + a] = s;
+  }
+}
+
+__global__ void reduce_blocks_kernel(const double* __restrict__ part, int nblocks, int nacc,
+                                     double* __restrict__ out) {
+  const int a = blockIdx.x * blockDim.x + threadIdx.x;
+  if (a >= nacc) return;
+  double s = 0.0;
+  for (int b = 0; b < nblocks; ++b) s += part[(size_t)b * nacc + a];
+  out[a] = s;
+}
+
+// out[q, i] = ||X_i - Q_q||^2, evaluated in double from fp32 inputs and rounded to fp32 (what sklearn's
+// float32 euclidean_distances upcast path stores, pairwise.py:567-638).
+__global__ void sqdist_rows_kernel(const float* __restrict__ X, int64_t N, int d, const float* __restrict__ Q, int m,
+                                   float* __restrict__ out) {
+  extern __shared__ float qs[];
+  for (int i = threadIdx.x; i < m * d; i += blockDim.x) qs[i] = Q[i];
+  __syncthreads();
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < N; i += stride) {
+    for (int q = 0; q < m; ++q) {
+      double s = 0.0;
+      for (int j = 0; j < d; ++j) {
+        const double df = (double)X[i * d + j] - (double)qs[q * d + j];
+        s += df * df;
+      }
+      out[(int64_t)q * N + i] = (float)s;
+    }
+  }
+}
+
+}  // namespace vc
+
+using namespace vc;
+
+static const int kKmMaxSmem = 220 * 1024;
+
+static int km_grid(const KmSmem& L, int64_t N) {
+  int per_sm = (int)(kKmMaxSmem / (L.total + 1024));
+  if (per_sm < 1) per_sm = 1;
+  if (per_sm > 2) per_sm = 2;
+  int64_t g = (int64_t)sm_count() * per_sm;
+  const int64_t ntiles = (N + L.tp - 1) / L.tp;
+  if (g > ntiles) g = ntiles;
+  if (g < 1) g = 1;
+  return (int)g;
+}
+
+extern "C" size_t vc_kmeans_workspace_bytes(int k, int d) {
+  // per-CTA partial sums (double) + counts (int64) for up to 2 CTAs per SM, + one 8-byte counter
+  const size_t blocks = (size_t)sm_count() * 2;
+  size_t pd = blocks * (size_t)(k > 0 ? k : 1) * (size_t)(d > 0 ? d : 1) * 8;
+  size_t pc = blocks * (size_t)(k > 0 ? k : 1) * 8;
+  return pd + pc + 64;
+}
+
+template <int D4>
+static cudaError_t km_launch(int grid, const KmSmem& L, cudaStream_t s, const float* X, int64_t N, int d,
+                             const float* C, int k, int32_t* labels, double* ps, long long* pc,
+                             unsigned long long* nchg, int update, int assign) {
+  auto kern = kmeans_assign_update_kernel<D4>;
+  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L.total);
+  if (e != cudaSuccess) return e;
+  kern<<<grid, kKmThreads, L.total, s>>>(X, N, d, C, k, labels, ps, pc, nchg, update, assign, L.tp, L.ncopies,
+                                         L.off_acc, L.off_dsum, L.off_c, L.off_c2, L.off_cnt, L.off_bar);
+  return cudaGetLastError();
+}
+
+static int km_run(const float* X, int64_t N, int d, const float* C, int k, int32_t* labels, double* sums,
+                  double* counts, int64_t* n_changed, int update, int assign, void* workspace, size_t workspace_bytes,
+                  void* stream, const char* who) {
+  VC_REQUIRE(X && labels && N > 0 && d > 0 && k > 0, VC_ERR_BAD_ARG, "%s: bad arguments (N=%lld d=%d k=%d)", who,
+             (long long)N, d, k);
+  VC_REQUIRE(d % 4 == 0 && d <= 256 && k <= 256, VC_ERR_UNSUPPORTED,
+             "%s: need d %% 4 == 0, d <= 256, k <= 256 (got d=%d k=%d)", who, d, k);
+  VC_REQUIRE((reinterpret_cast<uintptr_t>(X) & 15) == 0, VC_ERR_BAD_ARG, "%s: X must be 16-byte aligned", who);
+  VC_REQUIRE(!update || (sums && counts), VC_ERR_BAD_ARG, "%s: update requested without sums/counts", who);
+  VC_REQUIRE(workspace && workspace_bytes >= vc_kmeans_workspace_bytes(k, d), VC_ERR_WORKSPACE,
+             "%s: workspace too small", who);
+  const KmSmem L = km_layout(k, d, update);
+  VC_REQUIRE(L.total <= (size_t)kKmMaxSmem, VC_ERR_UNSUPPORTED,
+             "%s: k*d=%d needs %zu bytes of shared memory (> %d)", who, k * d, L.total, kKmMaxSmem);
+  const int grid = km_grid(L, N);
+  cudaStream_t s = as_stream(stream);
+  const size_t blocks = (size_t)sm_count() * 2;
+  double* ps = static_cast<double*>(workspace);
+  long long* pc = reinterpret_cast<long long*>(ps + blocks * (size_t)k * d);
+  unsigned long long* nchg = reinterpret_cast<unsigned long long*>(pc + blocks * (size_t)k);
+  VC_CUDA(cudaMemsetAsync(nchg, 0, 8, s));
+  cudaError_t e;
+  switch (d) {
+    case 8:  e = km_launch<2>(grid, L, s, X, N, d, C, k, labels, ps, pc, nchg, update, assign); break;
+    case 16: e = km_launch<4>(grid, L, s, X, N, d, C, k, labels, ps, pc, nchg, update, assign); break;
+    case 32: e = km_launch<8>(grid, L, s, X, N, d, C, k, labels, ps, pc, nchg, update, assign); break;
+    case 64: e = km_launch<16>(grid, L, s, X, N, d, C, k, labels, ps, pc, nchg, update, assign); break;
+    default: e = km_launch<0>(grid, L, s, X, N, d, C, k, labels, ps, pc, nchg, update, assign); break;
+  }
+  VC_REQUIRE(e == cudaSuccess, VC_ERR_CUDA, "%s: launch failed: %s", who, cudaGetErrorString(e));
+  if (update) {
+    const int n = k * d;
+    kmeans_reduce_partials_kernel<<<(n + 127) / 128, 128, 0, s>>>(ps, pc, grid, k, d, sums, counts);
+    VC_LAUNCH_CHECK();
+  }
+  if (n_changed) VC_CUDA(cudaMemcpyAsync(n_changed, nchg, 8, cudaMemcpyDeviceToDevice, s));
+  return VC_OK;
+}
+
+extern "C" int vc_kmeans_assign_update(const float* X, int64_t N, int d, const float* C, int k, int32_t* labels,
+                                       double* sums, double* counts, int64_t* n_changed, int update, void* workspace,
+                                       size_t workspace_bytes, void* stream) {
+  VC_REQUIRE(C, VC_ERR_BAD_ARG, "vc_kmeans_assign_update: C is NULL");
+  return km_run(X, N, d, C, k, labels, sums, counts, n_changed, update, 1, workspace, workspace_bytes, stream,
+                "vc_kmeans_assign_update");
+}
+
+extern "C" int vc_cluster_sums(const float* X, int64_t N, int d, const int32_t* labels, int k, double* sums,
+                               double* counts, void* workspace, size_t workspace_bytes, void* stream) {
+  // centroids are not needed when labels are given; X doubles as a harmless C source for the smem preload
+  VC_REQUIRE(N >= k || N > 0, VC_ERR_BAD_ARG, "vc_cluster_sums: bad N");
+  VC_REQUIRE(sums && counts, VC_ERR_BAD_ARG, "vc_cluster_sums: sums/counts NULL");
+  VC_REQUIRE((int64_t)k <= N, VC_ERR_BAD_ARG, "vc_cluster_sums: k=%d > N=%lld", k, (long long)N);
+  return km_run(X, N, d, X, k, const_cast<int32_t*>(labels), sums, counts, nullptr, 1, 0, workspace, workspace_bytes,
+                stream, "vc_cluster_sums");
+}
+
+extern "C" int vc_kmeans_finalize(const double* sums, const double* counts, const float* C_old, int k, int d,
+                                  float* C_new, double* shift_sq, void* stream) {
+  VC_REQUIRE(sums && counts && C_old && C_new && k > 0 && d > 0, VC_ERR_BAD_ARG, "vc_kmeans_finalize: bad arguments");
+  kmeans_finalize_kernel<<<1, 256, 0, as_stream(stream)>>>(sums, counts, C_old, k, d, C_new, shift_sq);
+  VC_LAUNCH_CHECK();
+  return VC_OK;
+}
+
+static int point_dist_run(int mode, const float* X, int64_t N, int d, const float* Cf, const double* Cd, int k,
+                          const int32_t* labels, float* point_out, double* out, void* workspace,
+                          size_t workspace_bytes, void* stream) {
+  const int nacc = mode == 0 ? 1 : k;
+  int grid = sm_count() * 2;
+  if ((int64_t)grid * 8 > N) grid = (int)((N + 7) / 8);
+  VC_REQUIRE(workspace && workspace_bytes >= (size_t)grid * nacc * 8, VC_ERR_WORKSPACE,
+             "point_dist: workspace too small");
+  double* part = static_cast<double*>(workspace);
+  const size_t sh = (size_t)8 * nacc * 8;
+  if (mode == 0)
+    point_dist_kernel<0><<<grid, 256, sh, as_stream(stream)>>>(X, N, d, Cf, Cd, k, labels, point_out, part, nacc);
+  else
+    point_dist_kernel<1><<<grid, 256, sh, as_stream(stream)>>>(X, N, d, Cf, Cd, k, labels, point_out, part, nacc);
+  VC_LAUNCH_CHECK();
+  reduce_blocks_kernel<<<(nacc + 127) / 128, 128, 0, as_stream(stream)>>>(part, grid, nacc, out);
+  VC_LAUNCH_CHECK();
+  return VC_OK;
+}
+
+extern "C" int vc_kmeans_inertia(const float* X, int64_t N, int d, const float* C, int k, const int32_t* labels,
+                                 double* inertia, float* point_sqdist, void* workspace, size_t workspace_bytes,
+                                 void* stream) {
+  VC_REQUIRE(X && C && labels && inertia && N > 0 && d > 0 && k > 0, VC_ERR_BAD_ARG,
+             "vc_kmeans_inertia: bad arguments");
+  return point_dist_run(0, X, N, d, C, nullptr, k, labels, point_sqdist, inertia, workspace, workspace_bytes, stream);
+}
+
+extern "C" int vc_dbi_intra(const float* X, int64_t N, int d, const int32_t* labels, const double* centroids, int k,
+                            double* intra_sum, void* workspace, size_t workspace_bytes, void* stream) {
+  VC_REQUIRE(X && labels && centroids && intra_sum && N > 0 && d > 0 && k > 0 && k <= 1024, VC_ERR_BAD_ARG,
+             "vc_dbi_intra: bad arguments");
+  return point_dist_run(1, X, N, d, nullptr, centroids, k, labels, nullptr, intra_sum, workspace, workspace_bytes,
+                        stream);
+}
+
+extern "C" int vc_sqdist_rows(const float* X, int64_t N, int d, const float* Q, int m, float* out, void* stream) {
+  VC_REQUIRE(X && Q && out && N > 0 && d > 0 && m > 0, VC_ERR_BAD_ARG, "vc_sqdist_rows: bad arguments");
+  VC_REQUIRE((size_t)m * d * 4 <= 48 * 1024, VC_ERR_UNSUPPORTED, "vc_sqdist_rows: m*d too large (%d x %d)", m, d);
+  int64_t blocks = (N + 255) / 256;
+  if (blocks > (int64_t)sm_count() * 8) blocks = (int64_t)sm_count() * 8;
+  sqdist_rows_kernel<<<(int)blocks, 256, (size_t)m * d * 4, as_stream(stream)>>>(X, N, d, Q, m, out);
+  VC_LAUNCH_CHECK();
+  return VC_OK;
+}

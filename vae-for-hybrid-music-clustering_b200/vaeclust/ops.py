@@ -1,0 +1,317 @@
+"""torch.autograd.Functions over the C-ABI of libvaeclust.so.
+
+Every op takes/returns fp32 CUDA tensors in torch's own layouts (NCHW activations, state_dict weight layouts) and
+launches on torch's current stream.  CPU tensors are rejected: there is no fallback path.
+"""
+from __future__ import annotations
+
+from typing import Optional
+
+import torch
+
+from ._lib import VC_LOSS_MEAN_MEAN, VC_LOSS_SUM_MEAN, VaeclustError, lib, ptr, stream_ptr
+
+_ws_cache: dict = {}
+
+
+def _workspace(nbytes: int, device) -> torch.Tensor:
+    """Grow-only per-device scratch buffer (the library never allocates)."""
+    key = (device.type, device.index)
+    buf = _ws_cache.get(key)
+    if buf is None or buf.numel() < nbytes:
+        buf = torch.empty(max(int(nbytes), 1 << 20), dtype=torch.uint8, device=device)
+        _ws_cache[key] = buf
+    return buf
+
+
+def _f32(t: torch.Tensor, name: str) -> torch.Tensor:
+    if not isinstance(t, torch.Tensor) or not t.is_cuda:
+        raise VaeclustError(f"{name}: expected a CUDA tensor (vaeclust has no CPU path)")
+    if t.dtype != torch.float32:
+        raise VaeclustError(f"{name}: expected float32, got {t.dtype}")
+    return t.contiguous()
+
+
+# ----------------------------------------------------------------------------------------------- dense layers
+class LinearFn(torch.autograd.Function):
+    """y = act(x W^T + b): nn.Linear(+ReLU) of 12:98-103,114-117,129-132,159-164; 19:79-95; 06:149-157."""
+
+    @staticmethod
+    def forward(ctx, x, weight, bias, relu: bool):
+        x, weight = _f32(x, "linear.x"), _f32(weight, "linear.weight")
+        bias = _f32(bias, "linear.bias") if bias is not None else None
+        M, K = x.shape
+        N = weight.shape[0]
+        if weight.shape[1] != K:
+            raise VaeclustError(f"linear: x is [*, {K}] but weight is {tuple(weight.shape)}")
+        y = torch.empty((M, N), dtype=torch.float32, device=x.device)
+        lib().call("vc_linear_fwd", ptr(x), ptr(weight), ptr(bias), ptr(y), M, N, K, int(relu), stream_ptr())
+        ctx.relu, ctx.has_bias = bool(relu), bias is not None
+        ctx.save_for_backward(x, weight, y if relu else None)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, weight, y = ctx.saved_tensors
+        dy = _f32(dy, "linear.dy")
+        M, K = x.shape
+        N = weight.shape[0]
+        s = stream_ptr()
+        if ctx.relu:
+            g = torch.empty_like(dy)
+            lib().call("vc_relu_bwd", ptr(dy), ptr(y), ptr(g), dy.numel(), s)
+        else:
+            g = dy
+        dx = dw = db = None
+        if ctx.needs_input_grad[0]:
+            dx = torch.empty_like(x)
+            lib().call("vc_linear_dgrad", ptr(g), ptr(weight), ptr(dx), M, N, K, s)
+        if ctx.needs_input_grad[1]:
+            dw = torch.empty_like(weight)
+            lib().call("vc_linear_wgrad", ptr(g), ptr(x), ptr(dw), M, N, K, 0, s)
+        if ctx.has_bias and ctx.needs_input_grad[2]:
+            db = torch.empty(N, dtype=torch.float32, device=x.device)
+            lib().call("vc_bias_grad", ptr(g), M, N, 1, ptr(db), 0, s)
+        return dx, dw, db, None
+
+
+def linear(x, weight, bias=None, relu: bool = False):
+    return LinearFn.apply(x, weight, bias, relu)
+
+
+class Conv2dS2K3Fn(torch.autograd.Function):
+    """nn.Conv2d(Cin, Cout, 3, stride=2, padding=1) (+ReLU), 12:87-89."""
+
+    @staticmethod
+    def forward(ctx, x, weight, bias, relu: bool):
+        x, weight = _f32(x, "conv.x"), _f32(weight, "conv.weight")
+        bias = _f32(bias, "conv.bias") if bias is not None else None
+        B, Cin, H, W = x.shape
+        Cout = weight.shape[0]
+        if tuple(weight.shape[1:]) != (Cin, 3, 3):
+            raise VaeclustError(f"conv2d_s2k3: weight {tuple(weight.shape)} does not match Cin={Cin}, k=3")
+        OH, OW = (H - 1) // 2 + 1, (W - 1) // 2 + 1
+        y = torch.empty((B, Cout, OH, OW), dtype=torch.float32, device=x.device)
+        lib().call("vc_conv2d_s2k3_fwd", ptr(x), ptr(weight), ptr(bias), ptr(y), B, Cin, H, W, Cout, int(relu),
+                   stream_ptr())
+        ctx.relu, ctx.has_bias = bool(relu), bias is not None
+        ctx.save_for_backward(x, weight, y if relu else None)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, weight, y = ctx.saved_tensors
+        dy = _f32(dy, "conv.dy")
+        B, Cin, H, W = x.shape
+        Cout = weight.shape[0]
+        s = stream_ptr()
+        if ctx.relu:
+            g = torch.empty_like(dy)
+            lib().call("vc_relu_bwd", ptr(dy), ptr(y), ptr(g), dy.numel(), s)
+        else:
+            g = dy
+        dx = dw = db = None
+        if ctx.needs_input_grad[0]:
+            dx = torch.empty_like(x)
+            lib().call("vc_conv2d_s2k3_dgrad", ptr(g), ptr(weight), ptr(dx), B, Cin, H, W, Cout, s)
+        if ctx.needs_input_grad[1]:
+            dw = torch.empty_like(weight)
+            nb = lib().size("vc_conv_wgrad_workspace_bytes", Cout, Cin, 3)
+            ws = _workspace(nb, x.device)
+            lib().call("vc_conv2d_s2k3_wgrad", ptr(g), ptr(x), ptr(dw), B, Cin, H, W, Cout, ptr(ws), ws.numel(), s)
+        if ctx.has_bias and ctx.needs_input_grad[2]:
+            db = torch.empty(Cout, dtype=torch.float32, device=x.device)
+            lib().call("vc_bias_grad", ptr(g), B, Cout, g.shape[2] * g.shape[3], ptr(db), 0, s)
+        return dx, dw, db, None
+
+
+def conv2d_s2k3(x, weight, bias=None, relu: bool = False):
+    return Conv2dS2K3Fn.apply(x, weight, bias, relu)
+
+
+class ConvT2dS2K4Fn(torch.autograd.Function):
+    """nn.ConvTranspose2d(Cin, Cout, 4, stride=2, padding=1) (+ReLU), 12:135-137.  weight is [Cin, Cout, 4, 4]."""
+
+    @staticmethod
+    def forward(ctx, x, weight, bias, relu: bool):
+        x, weight = _f32(x, "convT.x"), _f32(weight, "convT.weight")
+        bias = _f32(bias, "convT.bias") if bias is not None else None
+        B, Cin, H, W = x.shape
+        Cout = weight.shape[1]
+        if weight.shape[0] != Cin or tuple(weight.shape[2:]) != (4, 4):
+            raise VaeclustError(f"convT2d_s2k4: weight {tuple(weight.shape)} does not match Cin={Cin}, k=4")
+        y = torch.empty((B, Cout, 2 * H, 2 * W), dtype=torch.float32, device=x.device)
+        lib().call("vc_convT2d_s2k4_fwd", ptr(x), ptr(weight), ptr(bias), ptr(y), B, Cin, H, W, Cout, int(relu),
+                   stream_ptr())
+        ctx.relu, ctx.has_bias = bool(relu), bias is not None
+        ctx.save_for_backward(x, weight, y if relu else None)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, weight, y = ctx.saved_tensors
+        dy = _f32(dy, "convT.dy")
+        B, Cin, H, W = x.shape
+        Cout = weight.shape[1]
+        s = stream_ptr()
+        if ctx.relu:
+            g = torch.empty_like(dy)
+            lib().call("vc_relu_bwd", ptr(dy), ptr(y), ptr(g), dy.numel(), s)
+        else:
+            g = dy
+        dx = dw = db = None
+        if ctx.needs_input_grad[0]:
+            dx = torch.empty_like(x)
+            lib().call("vc_convT2d_s2k4_dgrad", ptr(g), ptr(weight), ptr(dx), B, Cin, H, W, Cout, s)
+        if ctx.needs_input_grad[1]:
+            dw = torch.empty_like(weight)
+            nb = lib().size("vc_conv_wgrad_workspace_bytes", Cout, Cin, 4)
+            ws = _workspace(nb, x.device)
+            lib().call("vc_convT2d_s2k4_wgrad", ptr(g), ptr(x), ptr(dw), B, Cin, H, W, Cout, ptr(ws), ws.numel(), s)
+        if ctx.has_bias and ctx.needs_input_grad[2]:
+            db = torch.empty(Cout, dtype=torch.float32, device=x.device)
+            lib().call("vc_bias_grad", ptr(g), B, Cout, g.shape[2] * g.shape[3], ptr(db), 0, s)
+        return dx, dw, db, None
+
+
+def convT2d_s2k4(x, weight, bias=None, relu: bool = False):
+    return ConvT2dS2K4Fn.apply(x, weight, bias, relu)
+
+
+class CatGateFn(torch.autograd.Function):
+    """[a, l*gate, gate] (12:178-180) or [a, l] (19:97-115) along dim 1."""
+
+    @staticmethod
+    def forward(ctx, a, l, gate, append_gate: bool):
+        a, l = _f32(a, "cat.a"), _f32(l, "cat.l")
+        gate = _f32(gate, "cat.gate") if gate is not None else None
+        B, na, nl = a.shape[0], a.shape[1], l.shape[1]
+        if l.shape[0] != B or (gate is not None and gate.numel() != B):
+            raise VaeclustError("cat_gate: batch sizes differ")
+        out = torch.empty((B, na + nl + (1 if append_gate else 0)), dtype=torch.float32, device=a.device)
+        lib().call("vc_cat_gate_fwd", ptr(a), na, ptr(l), nl, ptr(gate), int(append_gate), B, ptr(out), stream_ptr())
+        ctx.dims = (B, na, nl, bool(append_gate))
+        ctx.save_for_backward(gate)
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        (gate,) = ctx.saved_tensors
+        B, na, nl, app = ctx.dims
+        dout = _f32(dout, "cat.dout")
+        da = torch.empty((B, na), dtype=torch.float32, device=dout.device) if ctx.needs_input_grad[0] else None
+        dl = torch.empty((B, nl), dtype=torch.float32, device=dout.device) if ctx.needs_input_grad[1] else None
+        lib().call("vc_cat_gate_bwd", ptr(dout), na, nl, ptr(gate), int(app), B, ptr(da), ptr(dl), stream_ptr())
+        return da, dl, None, None
+
+
+def cat_gate(a, l, gate=None, append_gate: bool = False):
+    return CatGateFn.apply(a, l, gate, append_gate)
+
+
+# --------------------------------------------------------------------------------------------------- VAE loss
+class ReparamKLFn(torch.autograd.Function):
+    """(z, kl_rows) = (mu + eps*exp(lv/2), -0.5*sum_j(1+lv-mu^2-e^lv)); backward fused into one launch."""
+
+    @staticmethod
+    def forward(ctx, mu, lv, eps):
+        mu, lv, eps = _f32(mu, "reparam.mu"), _f32(lv, "reparam.logvar"), _f32(eps, "reparam.eps")
+        B, z = mu.shape
+        zo = torch.empty_like(mu)
+        kl = torch.empty(B, dtype=torch.float32, device=mu.device)
+        lib().call("vc_reparam_kl_fwd", ptr(mu), ptr(lv), ptr(eps), B, z, ptr(zo), ptr(kl), stream_ptr())
+        ctx.save_for_backward(mu, lv, eps)
+        return zo, kl
+
+    @staticmethod
+    def backward(ctx, dz, dkl):
+        mu, lv, eps = ctx.saved_tensors
+        B, z = mu.shape
+        dz = _f32(dz, "reparam.dz") if dz is not None else None
+        dkl = _f32(dkl, "reparam.dkl") if dkl is not None else None
+        dmu, dlv = torch.empty_like(mu), torch.empty_like(lv)
+        lib().call("vc_reparam_kl_bwd", ptr(dz), ptr(dkl), ptr(mu), ptr(lv), ptr(eps), B, z, ptr(dmu), ptr(dlv),
+                   stream_ptr())
+        return dmu, dlv, None
+
+
+def reparam_kl(mu, lv, eps):
+    return ReparamKLFn.apply(mu, lv, eps)
+
+
+class KLRowsFn(torch.autograd.Function):
+    """kl_rows only (the reference's stand-alone kl_div / kl_divergence, 12:189-190, 19:124-126)."""
+
+    @staticmethod
+    def forward(ctx, mu, lv):
+        mu, lv = _f32(mu, "kl.mu"), _f32(lv, "kl.logvar")
+        B, z = mu.shape
+        kl = torch.empty(B, dtype=torch.float32, device=mu.device)
+        lib().call("vc_reparam_kl_fwd", ptr(mu), ptr(lv), None, B, z, None, ptr(kl), stream_ptr())
+        ctx.save_for_backward(mu, lv)
+        return kl
+
+    @staticmethod
+    def backward(ctx, dkl):
+        mu, lv = ctx.saved_tensors
+        B, z = mu.shape
+        dkl = _f32(dkl, "kl.dkl")
+        dmu, dlv = torch.empty_like(mu), torch.empty_like(lv)
+        lib().call("vc_reparam_kl_bwd", None, ptr(dkl), ptr(mu), ptr(lv), None, B, z, ptr(dmu), ptr(dlv),
+                   stream_ptr())
+        return dmu, dlv
+
+
+def kl_rows(mu, lv):
+    return KLRowsFn.apply(mu, lv)
+
+
+class SqErrSumFn(torch.autograd.Function):
+    """sum (xhat[..., :H, :W] - x)^2 as a 0-d fp32 tensor; d/dxhat is produced in the same pass (crop of 12:260)."""
+
+    @staticmethod
+    def forward(ctx, xhat, x):
+        xhat, x = _f32(xhat, "mse.xhat"), _f32(x, "mse.x")
+        if xhat.dim() == 2:
+            outer, Hh, Wh, H, W = xhat.shape[0], 1, xhat.shape[1], 1, x.shape[1]
+            if x.shape[0] != outer:
+                raise VaeclustError("sq_err_sum: batch sizes differ")
+        else:
+            if xhat.shape[:-2] != x.shape[:-2]:
+                raise VaeclustError(f"sq_err_sum: leading dims differ {tuple(xhat.shape)} vs {tuple(x.shape)}")
+            outer = 1
+            for s_ in xhat.shape[:-2]:
+                outer *= s_
+            Hh, Wh, H, W = xhat.shape[-2], xhat.shape[-1], x.shape[-2], x.shape[-1]
+        need_grad = ctx.needs_input_grad[0]
+        dx = torch.empty_like(xhat) if need_grad else None
+        sq = torch.empty((), dtype=torch.float64, device=xhat.device)
+        nb = lib().size("vc_recon_loss_workspace_bytes")
+        ws = _workspace(nb, xhat.device)
+        lib().call("vc_recon_loss_fwd_bwd", ptr(xhat), ptr(x), outer, Hh, Wh, H, W, 1.0, ptr(dx), ptr(sq), ptr(ws),
+                   ws.numel(), stream_ptr())
+        ctx.save_for_backward(dx)
+        return sq.to(torch.float32)
+
+    @staticmethod
+    def backward(ctx, g):
+        (dx,) = ctx.saved_tensors
+        return dx * g, None
+
+
+def sq_err_sum(xhat, x):
+    return SqErrSumFn.apply(xhat, x)
+
+
+def mse_loss(xhat, x, reduction: str = "mean"):
+    """Drop-in for nn.MSELoss()/F.mse_loss as used at 12:234,262 and 06:184 (crop-aware)."""
+    s = sq_err_sum(xhat, x)
+    if reduction == "mean":
+        return s / x.numel()
+    if reduction == "sum":
+        return s
+    raise VaeclustError("mse_loss: reduction must be 'mean' or 'sum'")
+
+
+__all__ = ["linear", "conv2d_s2k3", "convT2d_s2k4", "cat_gate", "reparam_kl", "kl_rows", "sq_err_sum", "mse_loss",
+           "VC_LOSS_MEAN_MEAN", "VC_LOSS_SUM_MEAN"]
