@@ -58,8 +58,8 @@ def lloyd_mstep(X, labels, centers_old):
     centers_new = sums.copy()
     nz = w > 0
     centers_new[nz] *= (1.0 / w[nz]).astype(X.dtype)[:, None]
-    if (~nz).any():  # :286-295 empty cluster keeps old centre
-        centers_new[~nz] = centers_old[~nz]
+    if (~nz).any():  # :286-295 an empty cluster is placed on the biggest cluster's centre
+        centers_new[~nz] = centers_new[int(np.argmax(w))]
     shift = np.sqrt(((centers_new - centers_old) ** 2).sum(axis=1))
     return centers_new, w, shift
 

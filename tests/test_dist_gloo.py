@@ -1,0 +1,96 @@
+"""CPU, world_size=2 over gloo: the sharded KMeans / silhouette / Davies-Bouldin / moments / gradient-bucket logic
+gives the single-process answer.  The CUDA entry points are replaced by oracle-backed stand-ins (tests/_cpu_stubs)."""
+import os
+import socket
+import sys
+from pathlib import Path
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as td
+import torch.multiprocessing as mp
+
+ROOT = Path(__file__).resolve().parents[1]
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _data():
+    rng = np.random.default_rng(11)
+    cent = rng.normal(0, 4, size=(4, 8))
+    X = (cent[rng.integers(0, 4, 901)] + rng.normal(size=(901, 8))).astype(np.float32)
+    init = X[rng.permutation(901)[:4]].copy()
+    return X, init
+
+
+def _worker(rank, world, port, out_dir):
+    for p in (str(ROOT), str(ROOT / "vae-for-hybrid-music-clustering_b200"), str(ROOT / "tests")):
+        sys.path.insert(0, p)
+    td.init_process_group("gloo", init_method=f"tcp://127.0.0.1:{port}", rank=rank, world_size=world)
+    import _cpu_stubs
+    from vaeclust import cluster, dist
+
+    _cpu_stubs.install(None, cluster)
+    X, init = _data()
+    lo, hi = dist.shard_bounds(X.shape[0], rank, world)
+    res = {}
+    km = cluster.KMeans(4, init=init, n_init=1, group=td.group.WORLD).fit(X[lo:hi])
+    res["labels"], res["centers"], res["inertia"], res["n_iter"] = km.labels_, km.cluster_centers_, km.inertia_, km.n_iter_
+    full = np.zeros(X.shape[0], dtype=np.int64)
+    full[lo:hi] = km.labels_
+    t = torch.from_numpy(full)
+    td.all_reduce(t)
+    res["sil"] = cluster.silhouette_score(X, t.numpy(), group=td.group.WORLD)
+    res["sil_samples"] = cluster.silhouette_samples(X, t.numpy(), group=td.group.WORLD)
+    res["dbi"] = cluster.davies_bouldin_score(X[lo:hi], km.labels_, group=td.group.WORLD)
+    sc = cluster.StandardScaler().fit(X[lo:hi], group=td.group.WORLD)
+    res["mean"], res["var"] = sc.mean_, sc.var_
+    # gradient bucket: uneven local batches 5 and 3 of a global batch of 8
+    p = torch.nn.Parameter(torch.zeros(6))
+    bucket = dist.GradBucket([p], td.group.WORLD)
+    nloc = 5 if rank == 0 else 3
+    bucket.flat.copy_(torch.full((6,), float(rank + 1)))  # local batch-mean gradient
+    bucket.all_reduce_mean(nloc, 8)
+    res["grad"] = p.grad.numpy().copy()
+    # empty-cluster relocation across ranks
+    init2 = init.copy()
+    init2[3] = 1000.0
+    km2 = cluster.KMeans(4, init=init2, n_init=1, group=td.group.WORLD).fit(X[lo:hi])
+    res["labels2"], res["inertia2"] = km2.labels_, km2.inertia_
+    np.savez(os.path.join(out_dir, f"r{rank}.npz"), **res)
+    td.destroy_process_group()
+
+
+@pytest.mark.timeout(300)
+def test_world2_matches_single_process(tmp_path):
+    from oracle import cluster_ref as cr
+    from vaeclust import dist
+
+    port = _free_port()
+    mp.spawn(_worker, args=(2, port, str(tmp_path)), nprocs=2, join=True)
+    X, init = _data()
+    labels, inertia, centers, n_iter = cr.kmeans_lloyd(X, init)
+    r = [np.load(tmp_path / f"r{i}.npz") for i in range(2)]
+    got = np.concatenate([r[0]["labels"], r[1]["labels"]])
+    assert np.array_equal(got, labels)
+    for i in range(2):
+        assert int(r[i]["n_iter"]) == n_iter
+        assert float(r[i]["inertia"]) == pytest.approx(inertia, rel=1e-6)
+        np.testing.assert_allclose(r[i]["centers"], centers, rtol=1e-5, atol=1e-6)
+        assert float(r[i]["sil"]) == pytest.approx(cr.silhouette_score(X, labels), rel=1e-5)
+        np.testing.assert_allclose(r[i]["sil_samples"], cr.silhouette_samples(X, labels), rtol=1e-4, atol=1e-5)
+        assert float(r[i]["dbi"]) == pytest.approx(cr.davies_bouldin_score(X, labels), rel=1e-6)
+        np.testing.assert_allclose(r[i]["mean"], X.astype(np.float64).mean(0), rtol=1e-9, atol=1e-12)
+        np.testing.assert_allclose(r[i]["var"], X.astype(np.float64).var(0), rtol=1e-9)
+        np.testing.assert_allclose(r[i]["grad"], np.full(6, (5 * 1.0 + 3 * 2.0) / 8))
+    np.testing.assert_array_equal(r[0]["centers"], r[1]["centers"])  # bit-identical replicas
+    init2 = init.copy()
+    init2[3] = 1000.0
+    labels2, inertia2, _, _ = cr.kmeans_lloyd(X, init2)
+    assert np.array_equal(np.concatenate([r[0]["labels2"], r[1]["labels2"]]), labels2)
+    assert float(r[0]["inertia2"]) == pytest.approx(inertia2, rel=1e-6)

@@ -264,14 +264,23 @@ __global__ void kmeans_finalize_kernel(const double* __restrict__ sums, const do
                                        const float* __restrict__ C_old, int k, int d, float* __restrict__ C_new,
                                        double* __restrict__ shift_sq) {
   __shared__ double scratch[32];
+  __shared__ int big;
+  if (threadIdx.x == 0) {  // first maximum, like np.argmax (_k_means_common.pyx:283)
+    int b = 0;
+    for (int c = 1; c < k; ++c)
+      if (counts[c] > counts[b]) b = c;
+    big = b;
+  }
+  __syncthreads();
   double acc = 0.0;
   for (int e = threadIdx.x; e < k * d; e += blockDim.x) {
-    const int c = e / d;
+    const int c = e / d, j = e % d;
     const double n = counts[c];
-    const float old = C_old[e];
-    const float nw = n > 0.0 ? (float)(sums[e] / n) : old;
+    // empty clusters are placed on the biggest cluster's centre (_k_means_common.pyx:286-295)
+    const float nw = n > 0.0 ? (float)(sums[e] / n)
+                             : (counts[big] > 0.0 ? (float)(sums[big * d + j] / counts[big]) : C_old[e]);
     C_new[e] = nw;
-    const double df = (double)nw - (double)old;
+    const double df = (double)nw - (double)C_old[e];
     acc += df * df;
   }
   acc = block_sum<double>(acc, scratch);

@@ -1,0 +1,558 @@
+"""Latent-space clustering evaluation on B200: KMeans (Lloyd), silhouette, Davies-Bouldin, StandardScaler.
+
+sklearn-shaped call signatures as the reference uses them (07:67-71, 13:62-121, 16:57-96,183, 20:40-69, 22:55-99), so
+`from vaeclust.cluster import KMeans, silhouette_score, davies_bouldin_score, StandardScaler` replaces the sklearn
+imports of those scripts.  Inputs may be numpy arrays (copied to the GPU once) or CUDA tensors (zero-copy).
+All O(N) / O(N^2) arithmetic runs in libvaeclust.so; the host only drives the Lloyd loop, draws the k-means++ random
+numbers with numpy's RandomState exactly as sklearn does, and finishes O(k^2 d) scalars.  No CPU fallback.
+
+Multi-GPU: pass `group=<torch.distributed process group>`; X is then this rank's row shard (KMeans, DBI) or the
+replicated matrix of which this rank evaluates its row block (silhouette).  See DESIGN.md (e).
+"""
+from __future__ import annotations
+
+import warnings
+from typing import Optional, Tuple
+
+import numpy as np
+import torch
+
+from . import dist as vdist
+from ._lib import VaeclustError, lib, ptr, stream_ptr
+from .ops import _workspace
+
+
+def _device() -> torch.device:
+    if not torch.cuda.is_available():
+        raise VaeclustError("vaeclust.cluster needs a CUDA device (there is no CPU path)")
+    return torch.device("cuda", torch.cuda.current_device())
+
+
+def _as_dev_f32(X) -> torch.Tensor:
+    """[N,d] float32 contiguous CUDA tensor from numpy / torch input."""
+    if isinstance(X, torch.Tensor):
+        t = X if X.is_cuda else X.to(_device())
+    else:
+        t = torch.from_numpy(np.ascontiguousarray(np.asarray(X, dtype=np.float32))).to(_device())
+    if t.dim() != 2:
+        raise ValueError(f"Expected 2D array, got {t.dim()}D array instead")
+    return t.to(torch.float32).contiguous()
+
+
+def _pad_cols(t: torch.Tensor) -> torch.Tensor:
+    """Kernels need d % 4 == 0 (16-byte rows); zero columns change no distance."""
+    d = t.shape[1]
+    if d % 4 == 0:
+        return t
+    out = torch.zeros((t.shape[0], (d + 3) // 4 * 4), dtype=t.dtype, device=t.device)
+    out[:, :d] = t
+    return out
+
+
+def _col_stats(X: torch.Tensor, group=None) -> Tuple[torch.Tensor, torch.Tensor, int]:
+    """(mean, population variance) per column in float64 on device, and the global row count."""
+    N, d = X.shape
+    mean = torch.empty(d, dtype=torch.float64, device=X.device)
+    var = torch.empty(d, dtype=torch.float64, device=X.device)
+    ws = _workspace(lib().size("vc_col_stats_workspace_bytes", d), X.device)
+    lib().call("vc_col_stats", ptr(X), N, d, ptr(mean), ptr(var), ptr(ws), ws.numel(), stream_ptr())
+    if group is not None and vdist.world_size(group) > 1:
+        mean, var, N = vdist.merge_moments(mean, var, N, group)
+    return mean, var, N
+
+
+def _col_affine(X: torch.Tensor, shift: torch.Tensor, scale: Optional[torch.Tensor]) -> torch.Tensor:
+    out = torch.empty_like(X)
+    lib().call("vc_col_affine", ptr(X), X.shape[0], X.shape[1], ptr(shift), ptr(scale), ptr(out), stream_ptr())
+    return out
+
+
+class StandardScaler:
+    """sklearn.preprocessing.StandardScaler as used at 06:291-292, 07:67-68, 13:194, 16:178 (with_mean, with_std)."""
+
+    def fit(self, X, group=None):
+        Xd = _as_dev_f32(X)
+        mean, var, n = _col_stats(Xd, group)
+        scale = torch.sqrt(var)
+        # sklearn's _handle_zeros_in_scale: (near-)constant columns are not scaled
+        eps = 10 * torch.finfo(torch.float64).eps
+        scale = torch.where(scale < eps * torch.abs(mean).clamp_min(1.0), torch.ones_like(scale), scale)
+        self._mean_d, self._scale_d = mean, scale
+        self.mean_, self.var_, self.scale_ = mean.cpu().numpy(), var.cpu().numpy(), scale.cpu().numpy()
+        self.n_samples_seen_ = int(n)
+        return self
+
+    def transform(self, X):
+        is_np = not isinstance(X, torch.Tensor)
+        out = _col_affine(_as_dev_f32(X), self._mean_d, self._scale_d)
+        return out.cpu().numpy() if is_np else out
+
+    def fit_transform(self, X, y=None, group=None):
+        return self.fit(X, group).transform(X)
+
+
+# ------------------------------------------------------------------------------------------------- KMeans
+def _is_same_clustering(a: np.ndarray, b: np.ndarray, k: int) -> bool:
+    """sklearn:cluster/_k_means_common.pyx:_is_same_clustering -- equal up to a permutation of labels."""
+    mapping = np.full(k, -1, dtype=np.int64)
+    for x, y in zip(a.tolist(), b.tolist()):
+        if mapping[x] == -1:
+            mapping[x] = y
+        elif mapping[x] != y:
+            return False
+    return True
+
+
+class _LloydState:
+    """Device buffers of one Lloyd run (allocated once per fit, reused across n_init restarts)."""
+
+    def __init__(self, N: int, d: int, k: int, device):
+        self.labels = torch.empty(N, dtype=torch.int32, device=device)
+        # stats = [sums k*d | counts k | shift_sq 1]  (float64) ; nchg int64
+        self.stats = torch.zeros(k * d + k + 1, dtype=torch.float64, device=device)
+        self.nchg = torch.zeros(1, dtype=torch.int64, device=device)
+        self.centers_new = torch.empty((k, d), dtype=torch.float32, device=device)
+        self.ws = _workspace(lib().size("vc_kmeans_workspace_bytes", k, d), device)
+        self.k, self.d = k, d
+
+    @property
+    def sums(self):
+        return self.stats[: self.k * self.d]
+
+    @property
+    def counts(self):
+        return self.stats[self.k * self.d: self.k * self.d + self.k]
+
+    @property
+    def shift(self):
+        return self.stats[self.k * self.d + self.k:]
+
+
+def _estep(X, centers, st: _LloydState, update: bool):
+    lib().call("vc_kmeans_assign_update", ptr(X), X.shape[0], X.shape[1], ptr(centers), st.k, ptr(st.labels),
+               ptr(st.sums), ptr(st.counts), ptr(st.nchg), int(update), ptr(st.ws), st.ws.numel(), stream_ptr())
+
+
+def _finalize(centers, st: _LloydState):
+    lib().call("vc_kmeans_finalize", ptr(st.sums), ptr(st.counts), ptr(centers), st.k, st.d, ptr(st.centers_new),
+               ptr(st.shift), stream_ptr())
+
+
+def _point_sqdist(X, centers, st: _LloydState) -> Tuple[torch.Tensor, torch.Tensor]:
+    out = torch.empty(X.shape[0], dtype=torch.float32, device=X.device)
+    inertia = torch.empty(1, dtype=torch.float64, device=X.device)
+    lib().call("vc_kmeans_inertia", ptr(X), X.shape[0], X.shape[1], ptr(centers), st.k, ptr(st.labels), ptr(inertia),
+               ptr(out), ptr(st.ws), st.ws.numel(), stream_ptr())
+    return inertia, out
+
+
+def _relocate_empty(X, centers, st: _LloydState, counts_host: np.ndarray, group) -> None:
+    """sklearn:cluster/_k_means_common.pyx:167-211 on the (all-reduced) sums/counts."""
+    empty = np.where(counts_host == 0)[0]
+    _, dist = _point_sqdist(X, centers, st)
+    n_e = int(min(empty.size, dist.numel()))
+    top_d, top_i = torch.topk(dist, n_e)
+    rows = X[top_i]
+    labs = st.labels[top_i].to(torch.int64)
+    if group is not None and vdist.world_size(group) > 1:
+        top_d, rows, labs = vdist.gather_top(top_d, rows, labs, n_e, group)
+    if float(top_d.max()) == 0.0:
+        return
+    sums = st.sums.view(st.k, st.d)
+    for idx in range(n_e):
+        new_id, old_id = int(empty[idx]), int(labs[idx])
+        x = rows[idx].to(torch.float64)
+        sums[old_id] -= x
+        sums[new_id] = x
+        st.counts[new_id] = 1.0
+        st.counts[old_id] -= 1.0
+
+
+def lloyd(X: torch.Tensor, centers_init: torch.Tensor, max_iter: int = 300, tol: float = 0.0, group=None,
+          state: Optional[_LloydState] = None):
+    """_kmeans_single_lloyd (sklearn:cluster/_kmeans.py:630-758) on device.  X is this rank's (centred) shard.
+    Returns (labels int32 [N_local], inertia float, centers float32 [k,d], n_iter)."""
+    N, d = X.shape
+    k = centers_init.shape[0]
+    st = state or _LloydState(N, d, k, X.device)
+    st.labels.fill_(-1)
+    centers = centers_init.to(torch.float32).contiguous().clone()
+    multi = group is not None and vdist.world_size(group) > 1
+    strict = False
+    n_iter = 0
+    for i in range(max_iter):
+        _estep(X, centers, st, update=True)
+        if multi:
+            vdist.all_reduce_sum(st.stats[: k * d + k], group)
+            vdist.all_reduce_sum(st.nchg, group)
+        _finalize(centers, st)
+        host = torch.cat([st.counts, st.shift, st.nchg.to(torch.float64)]).cpu().numpy()  # the one sync per iteration
+        counts_h, shift_sq, n_changed = host[:k], float(host[k]), int(host[k + 1])
+        if (counts_h == 0).any():
+            _relocate_empty(X, centers, st, counts_h, group)
+            _finalize(centers, st)
+            shift_sq = float(st.shift.item())
+        centers, st.centers_new = st.centers_new, centers
+        n_iter = i + 1
+        if n_changed == 0:
+            strict = True
+            break
+        if shift_sq <= tol:
+            break
+    if not strict:
+        _estep(X, centers, st, update=False)
+    inertia, _ = _point_sqdist(X, centers, st)
+    if multi:
+        vdist.all_reduce_sum(inertia, group)
+    return st.labels, float(inertia.item()), centers, n_iter
+
+
+_HOST_CUMSUM_MAX = 1 << 21  # below this, the k-means++ prefix sum replays numpy's sequential float32 cumsum
+
+
+def _sqdist_rows(X: torch.Tensor, Q: torch.Tensor) -> torch.Tensor:
+    out = torch.empty((Q.shape[0], X.shape[0]), dtype=torch.float32, device=X.device)
+    lib().call("vc_sqdist_rows", ptr(X), X.shape[0], X.shape[1], ptr(Q.contiguous()), Q.shape[0], ptr(out),
+               stream_ptr())
+    return out
+
+
+def kmeans_plusplus(X: torch.Tensor, k: int, random_state: np.random.RandomState):
+    """_kmeans_plusplus (sklearn:cluster/_kmeans.py:180-278): greedy k-means++ with 2+floor(ln k) local trials.
+    The RandomState draws happen on the host in sklearn's order; the distance scans run on the GPU."""
+    N, d = X.shape
+    n_trials = 2 + int(np.log(k))
+    centers = torch.empty((k, d), dtype=torch.float32, device=X.device)
+    indices = np.full(k, -1, dtype=np.int64)
+    if N <= _HOST_CUMSUM_MAX:  # same call, same float32 weights as sklearn (sample_weight / sample_weight.sum())
+        w = np.ones(N, dtype=np.float32)
+        center_id = int(random_state.choice(N, p=w / w.sum()))
+    else:
+        center_id = int(random_state.randint(N))
+    centers[0] = X[center_id]
+    indices[0] = center_id
+    closest = _sqdist_rows(X, centers[0:1])[0]
+    pot = float(closest.sum(dtype=torch.float64)) if N > _HOST_CUMSUM_MAX else float(
+        np.float32(closest.cpu().numpy() @ np.ones(N, dtype=np.float32)))
+    for c in range(1, k):
+        rand_vals = random_state.uniform(size=n_trials) * pot
+        if N <= _HOST_CUMSUM_MAX:
+            cs = np.cumsum(closest.cpu().numpy())  # float32 sequential, like np.cumsum(sample_weight*closest)
+            cand = np.searchsorted(cs, rand_vals)
+        else:
+            cs = torch.cumsum(closest.to(torch.float64), 0)
+            cand = torch.searchsorted(cs, torch.from_numpy(rand_vals).to(X.device)).cpu().numpy()
+        np.clip(cand, None, N - 1, out=cand)
+        cand_t = torch.from_numpy(cand.astype(np.int64)).to(X.device)
+        dist = _sqdist_rows(X, X[cand_t])
+        torch.minimum(dist, closest.unsqueeze(0), out=dist)
+        if N <= _HOST_CUMSUM_MAX:
+            pots = dist.cpu().numpy() @ np.ones(N, dtype=np.float32)
+        else:
+            pots = dist.sum(dim=1, dtype=torch.float64).cpu().numpy()
+        best = int(np.argmin(pots))
+        pot = float(pots[best])
+        closest = dist[best].clone()
+        centers[c] = X[int(cand[best])]
+        indices[c] = int(cand[best])
+    return centers, indices
+
+
+class KMeans:
+    """sklearn.cluster.KMeans as the reference uses it: KMeans(n_clusters, n_init, random_state[, init, max_iter,
+    tol]).fit / fit_predict; attributes labels_ (int32), cluster_centers_ (float32), inertia_, n_iter_.
+    Lloyd only (sklearn's default algorithm).  `init` may be "k-means++" (default), "random" or an ndarray."""
+
+    def __init__(self, n_clusters: int = 8, *, init="k-means++", n_init="auto", max_iter: int = 300,
+                 tol: float = 1e-4, verbose: int = 0, random_state=None, copy_x: bool = True, algorithm: str = "lloyd",
+                 group=None):
+        if algorithm not in ("lloyd", "auto", "full"):
+            raise VaeclustError("vaeclust KMeans implements Lloyd only")
+        self.n_clusters, self.init, self.n_init = int(n_clusters), init, n_init
+        self.max_iter, self.tol, self.verbose = int(max_iter), float(tol), verbose
+        self.random_state, self.copy_x, self.algorithm, self.group = random_state, copy_x, algorithm, group
+
+    def _check_rs(self):
+        rs = self.random_state
+        if rs is None or isinstance(rs, (int, np.integer)):
+            return np.random.RandomState(rs)
+        return rs
+
+    def fit(self, X, y=None, sample_weight=None):
+        if sample_weight is not None:
+            raise VaeclustError("vaeclust KMeans: sample_weight is not used by the reference and not supported")
+        return_numpy = not isinstance(X, torch.Tensor)
+        Xd = _as_dev_f32(X)
+        N, d_true = Xd.shape
+        k = self.n_clusters
+        multi = self.group is not None and vdist.world_size(self.group) > 1
+        n_total = N if not multi else int(vdist.all_reduce_sum(torch.tensor([N], dtype=torch.int64, device=Xd.device),
+                                                               self.group).item())
+        if n_total < k:
+            raise ValueError(f"n_samples={n_total} should be >= n_clusters={k}.")
+        init = self.init
+        init_is_array = not isinstance(init, str)
+        if init_is_array:
+            init_t = _as_dev_f32(init)
+            if tuple(init_t.shape) != (k, d_true):
+                raise ValueError(f"The shape of the initial centers {tuple(init_t.shape)} does not match "
+                                 f"(n_clusters, n_features) = ({k}, {d_true}).")
+        n_init = self.n_init
+        if n_init == "auto":
+            n_init = 1 if (init_is_array or init == "k-means++") else 10
+        if init_is_array and n_init != 1:
+            warnings.warn("Explicit initial center position passed: performing only one init in KMeans instead of "
+                          f"n_init={n_init}.", RuntimeWarning, stacklevel=2)
+            n_init = 1
+        # tolerance and centring (_kmeans.py:285-293, 1487-1490)
+        mean64, var64, _ = _col_stats(Xd, self.group)
+        tol_abs = float(var64.mean().item()) * self.tol if self.tol != 0 else 0.0
+        mean32 = mean64.to(torch.float32)
+        Xc = _pad_cols(_col_affine(Xd, mean32.to(torch.float64), None))
+        d = Xc.shape[1]
+        rs = self._check_rs()
+        st = _LloydState(N, d, k, Xc.device)
+        best = None
+        for _ in range(int(n_init)):
+            if init_is_array:
+                c0 = init_t - mean32
+            elif init == "k-means++":
+                if multi:
+                    raise VaeclustError("k-means++ over a sharded X is not implemented: pass init=<array>")
+                c0, _idx = kmeans_plusplus(Xc, k, rs)
+            elif init == "random":
+                if multi:
+                    raise VaeclustError("init='random' over a sharded X is not implemented: pass init=<array>")
+                seeds = rs.choice(N, size=k, replace=False)
+                c0 = Xc[torch.from_numpy(seeds).to(Xc.device)][:, :d_true]
+            else:
+                raise ValueError(f"init should be 'k-means++', 'random' or an array, got {init!r}")
+            c0 = _pad_cols(c0.contiguous())
+            labels, inertia, centers, n_iter = lloyd(Xc, c0, self.max_iter, tol_abs, self.group, st)
+            take = best is None
+            if not take and inertia < best[1]:
+                take = multi or not _is_same_clustering(labels.cpu().numpy(), best[0].cpu().numpy(), k)
+            if take:
+                best = (labels.clone(), inertia, centers.clone(), n_iter)
+        labels, inertia, centers, n_iter = best
+        centers = centers[:, :d_true] + mean32
+        self._labels_d, self._centers_d = labels, centers
+        self.labels_ = labels.cpu().numpy() if return_numpy else labels
+        self.cluster_centers_ = centers.cpu().numpy() if return_numpy else centers
+        self.inertia_, self.n_iter_ = inertia, n_iter
+        self.n_features_in_ = d_true
+        if not multi:
+            distinct = int(torch.unique(labels).numel())
+            if distinct < k:
+                warnings.warn(f"Number of distinct clusters ({distinct}) found smaller than n_clusters ({k}). "
+                              "Possibly due to duplicate points in X.", RuntimeWarning, stacklevel=2)
+        return self
+
+    def fit_predict(self, X, y=None, sample_weight=None):
+        return self.fit(X, sample_weight=sample_weight).labels_
+
+    def predict(self, X):
+        return_numpy = not isinstance(X, torch.Tensor)
+        Xd = _pad_cols(_as_dev_f32(X))
+        C = _pad_cols(self._centers_d.contiguous())
+        st = _LloydState(Xd.shape[0], Xd.shape[1], self.n_clusters, Xd.device)
+        _estep(Xd, C, st, update=False)
+        return st.labels.cpu().numpy() if return_numpy else st.labels
+
+
+# --------------------------------------------------------------------------------------------- silhouette
+def _encode_labels(labels, device) -> Tuple[torch.Tensor, int]:
+    """LabelEncoder (sklearn:_unsupervised.py:300-303): labels -> 0..k-1 (int64 on device)."""
+    lt = labels if isinstance(labels, torch.Tensor) else torch.from_numpy(np.asarray(labels))
+    lt = lt.to(device).reshape(-1).to(torch.int64)
+    uniq, inv = torch.unique(lt, return_inverse=True)
+    return inv, int(uniq.numel())
+
+
+def _check_number_of_labels(k: int, n: int) -> None:
+    if not 1 < k < n:
+        raise ValueError(f"Number of labels is {k}. Valid values are 2 to n_samples - 1 (inclusive)")
+
+
+def _sil_prepare(Xd: torch.Tensor, order: torch.Tensor, mean64: torch.Tensor):
+    """Rows permuted into cluster order and centred, plus their squared norms."""
+    N, d = Xd.shape
+    Xs = torch.empty_like(Xd)
+    sqn = torch.empty(N, dtype=torch.float32, device=Xd.device)
+    lib().call("vc_silhouette_gather", ptr(Xd), N, d, ptr(order), ptr(mean64), ptr(Xs), ptr(sqn), stream_ptr())
+    return Xs, sqn
+
+
+def _sil_block(Xs, sqn, off, k: int, r0: int, r1: int, lab_sorted, counts, s_sorted, s_sum) -> None:
+    """Rows [r0, r1) against all columns: per-row silhouette into s_sorted[r0:r1] and their sum into s_sum."""
+    N, d = Xs.shape
+    nrows = r1 - r0
+    tiles = (nrows + 127) // 128
+    sms = lib().size("vc_sm_count")
+    nsplit = int(max(1, min(32, (2 * sms) // max(tiles, 1))))
+    sums = torch.empty((nsplit, nrows, k), dtype=torch.float32, device=Xs.device)
+    lib().call("vc_silhouette_rows", ptr(Xs), ptr(sqn), N, d, ptr(off), k, r0, r1, nsplit, ptr(sums), stream_ptr())
+    ws = _workspace(lib().size("vc_silhouette_finalize_workspace_bytes"), Xs.device)
+    lib().call("vc_silhouette_finalize", ptr(sums), nsplit, ptr(lab_sorted[r0:]), ptr(counts), k, nrows,
+               ptr(s_sorted[r0:]), ptr(s_sum), ptr(ws), ws.numel(), stream_ptr())
+
+
+def silhouette_samples(X, labels, *, metric: str = "euclidean", group=None, _return_sum: bool = False):
+    """sklearn.metrics.silhouette_samples (euclidean only).  With `group`, every rank holds the full X and
+    evaluates rows [r*N/G, (r+1)*N/G); per-row values are all-gathered."""
+    if metric != "euclidean":
+        raise VaeclustError("vaeclust silhouette supports metric='euclidean' only (what the reference uses)")
+    return_numpy = not isinstance(X, torch.Tensor)
+    Xd = _pad_cols(_as_dev_f32(X))
+    N, d = Xd.shape
+    lab, k = _encode_labels(labels, Xd.device)
+    if lab.numel() != N:
+        raise ValueError(f"Found input variables with inconsistent numbers of samples: [{N}, {lab.numel()}]")
+    _check_number_of_labels(k, N)
+    # group rows by cluster (stable), centre for conditioning (distances are translation invariant)
+    order = torch.argsort(lab, stable=True)
+    lab_sorted = lab[order].to(torch.int32).contiguous()
+    counts = torch.bincount(lab, minlength=k).to(torch.int64)
+    off = torch.zeros(k + 1, dtype=torch.int64, device=Xd.device)
+    off[1:] = torch.cumsum(counts, 0)
+    mean64, _, _ = _col_stats(Xd)
+    Xs, sqn = _sil_prepare(Xd, order, mean64)
+    world, rank = (vdist.world_size(group), vdist.rank(group)) if group is not None else (1, 0)
+    r0, r1 = vdist.shard_bounds(N, rank, world)
+    s_sorted = torch.zeros(N, dtype=torch.float32, device=Xd.device)
+    s_sum = torch.zeros(1, dtype=torch.float64, device=Xd.device)
+    if r1 > r0:
+        _sil_block(Xs, sqn, off, k, r0, r1, lab_sorted, counts, s_sorted, s_sum)
+    if world > 1:
+        vdist.all_reduce_sum(s_sum, group)
+        if not _return_sum:
+            vdist.all_reduce_sum(s_sorted, group)  # disjoint row blocks, zeros elsewhere
+    if _return_sum:
+        return float(s_sum.item()), N
+    s = torch.empty_like(s_sorted)
+    s[order] = s_sorted
+    return s.cpu().numpy() if return_numpy else s
+
+
+def silhouette_score(X, labels, *, metric: str = "euclidean", sample_size=None, random_state=None, group=None):
+    """sklearn.metrics.silhouette_score -> python float (13:74,78; 16:68,73; 20:45; 22:61)."""
+    if sample_size is not None:
+        raise VaeclustError("vaeclust silhouette_score: sample_size is not used by the reference and not supported")
+    total, n = silhouette_samples(X, labels, metric=metric, group=group, _return_sum=True)
+    return float(np.float32(total / n)) if not isinstance(X, torch.Tensor) or X.dtype == torch.float32 else total / n
+
+
+# ----------------------------------------------------------------------------------------- Davies-Bouldin
+def _cluster_sums(Xd: torch.Tensor, lab32: torch.Tensor, k: int) -> torch.Tensor:
+    """[k*d sums | k counts] in float64 for the local rows."""
+    N, d = Xd.shape
+    stats = torch.zeros(k * d + k, dtype=torch.float64, device=Xd.device)
+    ws = _workspace(lib().size("vc_kmeans_workspace_bytes", k, d), Xd.device)
+    lib().call("vc_cluster_sums", ptr(Xd), N, d, ptr(lab32), k, ptr(stats), ptr(stats[k * d:]), ptr(ws), ws.numel(),
+               stream_ptr())
+    return stats
+
+
+def _dbi_intra(Xd: torch.Tensor, lab32: torch.Tensor, centroids: torch.Tensor, k: int) -> torch.Tensor:
+    """sum over local rows of ||x - centroid(label)|| per cluster (float64)."""
+    N, d = Xd.shape
+    intra = torch.zeros(k, dtype=torch.float64, device=Xd.device)
+    ws = _workspace(lib().size("vc_kmeans_workspace_bytes", k, d), Xd.device)
+    lib().call("vc_dbi_intra", ptr(Xd), N, d, ptr(lab32), ptr(centroids), k, ptr(intra), ptr(ws), ws.numel(),
+               stream_ptr())
+    return intra
+
+
+def davies_bouldin_score(X, labels, *, group=None) -> float:
+    """sklearn.metrics.davies_bouldin_score (sklearn:_unsupervised.py:413-487; 13:94,98; 16:89,94).
+    With `group`, X/labels are this rank's row shard; two tiny all-reduces (C5 of SURVEY.md 2.1)."""
+    Xd = _pad_cols(_as_dev_f32(X))
+    N, d = Xd.shape
+    multi = group is not None and vdist.world_size(group) > 1
+    if multi:
+        lt = labels if isinstance(labels, torch.Tensor) else torch.from_numpy(np.asarray(labels))
+        lab = lt.to(Xd.device).reshape(-1).to(torch.int64)
+        kk = torch.tensor([int(lab.max().item()) + 1], dtype=torch.int64, device=Xd.device)
+        k = int(vdist.all_reduce_max(kk, group).item())  # sharded callers pass labels already in 0..k-1
+        n_total = int(vdist.all_reduce_sum(torch.tensor([N], dtype=torch.int64, device=Xd.device), group).item())
+    else:
+        lab, k = _encode_labels(labels, Xd.device)
+        n_total = N
+    _check_number_of_labels(k, n_total)
+    lab32 = lab.to(torch.int32).contiguous()
+    stats = _cluster_sums(Xd, lab32, k)
+    if multi:
+        vdist.all_reduce_sum(stats, group)
+    counts = stats[k * d:]
+    centroids = (stats[: k * d].view(k, d) / counts.clamp_min(1.0).unsqueeze(1)).contiguous()
+    intra = _dbi_intra(Xd, lab32, centroids, k)
+    if multi:
+        vdist.all_reduce_sum(intra, group)
+    # O(k^2 d) tail on the host in float64, as sklearn does
+    intra_h = (intra / counts.clamp_min(1.0)).cpu().numpy()
+    cent_h = centroids.cpu().numpy()
+    diff = cent_h[:, None, :] - cent_h[None, :, :]
+    M = np.sqrt(np.maximum((diff * diff).sum(-1), 0.0))
+    if np.allclose(intra_h, 0) or np.allclose(M, 0):
+        return 0.0
+    M[M == 0] = np.inf
+    comb = intra_h[:, None] + intra_h[None, :]
+    return float(np.mean(np.max(comb / M, axis=1)))
+
+
+# -------------------------------------------------------------------- the reference's own wrapper helpers
+def safe_silhouette(X, labels):
+    """13:62-80 / 16:57-75: None if < 2 clusters; DBSCAN noise (-1) dropped, needs >= 3 points; errors -> None."""
+    labels = np.asarray(labels.cpu() if isinstance(labels, torch.Tensor) else labels)
+    uniq = set(labels.tolist())
+    if len(uniq) < 2:
+        return None
+    try:
+        if -1 in uniq:
+            mask = labels != -1
+            if mask.sum() < 3 or len(set(labels[mask].tolist())) < 2:
+                return None
+            Xm = X[torch.from_numpy(mask).to(X.device)] if isinstance(X, torch.Tensor) else X[mask]
+            return float(silhouette_score(Xm, labels[mask]))
+        return float(silhouette_score(X, labels))
+    except Exception:
+        return None
+
+
+def safe_db_index(X, labels):
+    """13:83-100 / 16:78-96 (`safe_dbi`): same guards as safe_silhouette."""
+    labels = np.asarray(labels.cpu() if isinstance(labels, torch.Tensor) else labels)
+    uniq = set(labels.tolist())
+    if len(uniq) < 2:
+        return None
+    try:
+        if -1 in uniq:
+            mask = labels != -1
+            if mask.sum() < 3 or len(set(labels[mask].tolist())) < 2:
+                return None
+            Xm = X[torch.from_numpy(mask).to(X.device)] if isinstance(X, torch.Tensor) else X[mask]
+            return float(davies_bouldin_score(Xm, labels[mask]))
+        return float(davies_bouldin_score(X, labels))
+    except Exception:
+        return None
+
+
+safe_dbi = safe_db_index
+
+
+def safe_silhouette_nan(X, labels) -> float:
+    """20:40-47 / 22:55-63 flavour: nan instead of None."""
+    v = safe_silhouette(X, labels)
+    return float("nan") if v is None else v
+
+
+def eval_kmeans(X, k: int, seed: int, n_init: int = 20):
+    """22:90-99: KMeans(k, random_state=seed, n_init=20) labels + silhouette."""
+    km = KMeans(n_clusters=k, random_state=seed, n_init=n_init)
+    labels = km.fit_predict(X)
+    return labels, safe_silhouette_nan(X, labels)
+
+
+__all__ = ["KMeans", "StandardScaler", "silhouette_score", "silhouette_samples", "davies_bouldin_score",
+           "safe_silhouette", "safe_db_index", "safe_dbi", "safe_silhouette_nan", "eval_kmeans", "lloyd",
+           "kmeans_plusplus"]

@@ -313,5 +313,52 @@ def mse_loss(xhat, x, reduction: str = "mean"):
     raise VaeclustError("mse_loss: reduction must be 'mean' or 'sum'")
 
 
-__all__ = ["linear", "conv2d_s2k3", "convT2d_s2k4", "cat_gate", "reparam_kl", "kl_rows", "sq_err_sum", "mse_loss",
+class VAELossFn(torch.autograd.Function):
+    """Fused training loss: crop (12:260) + squared error + its gradient in ONE pass over xhat/x, then
+    loss = recon + beta*kl under the script's reduction convention (VC_LOSS_MEAN_MEAN: 12:262-264, 06:182-188;
+    VC_LOSS_SUM_MEAN: 19:226-228).  Returns (loss 0-d, stats [3] = loss, recon, kl); stats carries no gradient.
+    `unit_grad=True` is the caller's promise that it will call loss.backward() directly (upstream gradient 1), which
+    lets backward hand out the pre-scaled dxhat without another pass over it."""
+
+    @staticmethod
+    def forward(ctx, xhat, x, kl_rows_t, beta: float, mode: int, z_dim: int, unit_grad: bool):
+        xhat, x, kl_rows_t = _f32(xhat, "vae_loss.xhat"), _f32(x, "vae_loss.x"), _f32(kl_rows_t, "vae_loss.kl_rows")
+        B = kl_rows_t.numel()
+        if xhat.dim() == 2:
+            outer, Hh, Wh, H, W = xhat.shape[0], 1, xhat.shape[1], 1, x.shape[1]
+        else:
+            outer = 1
+            for s_ in xhat.shape[:-2]:
+                outer *= s_
+            Hh, Wh, H, W = xhat.shape[-2], xhat.shape[-1], x.shape[-2], x.shape[-1]
+        n = x.numel()
+        gscale = 1.0 / n if mode == VC_LOSS_MEAN_MEAN else 1.0 / B
+        dx = torch.empty_like(xhat)
+        sq = torch.empty((), dtype=torch.float64, device=xhat.device)
+        ws = _workspace(lib().size("vc_recon_loss_workspace_bytes"), xhat.device)
+        s = stream_ptr()
+        lib().call("vc_recon_loss_fwd_bwd", ptr(xhat), ptr(x), outer, Hh, Wh, H, W, gscale, ptr(dx), ptr(sq), ptr(ws),
+                   ws.numel(), s)
+        stats = torch.empty(3, dtype=torch.float32, device=xhat.device)
+        lib().call("vc_loss_finalize", ptr(sq), ptr(kl_rows_t), B, z_dim, n, float(beta), mode, ptr(stats), s)
+        ctx.save_for_backward(dx)
+        ctx.kl_scale = float(beta) * (1.0 / (B * z_dim) if mode == VC_LOSS_MEAN_MEAN else 1.0 / B)
+        ctx.B, ctx.unit_grad = B, bool(unit_grad)
+        ctx.mark_non_differentiable(stats)
+        return stats[0].clone(), stats
+
+    @staticmethod
+    def backward(ctx, g, _gstats):
+        (dx,) = ctx.saved_tensors
+        if ctx.unit_grad:
+            dkl = torch.full((ctx.B,), ctx.kl_scale, dtype=torch.float32, device=dx.device)
+            return dx, None, dkl, None, None, None, None
+        return dx * g, None, (g * ctx.kl_scale).expand(ctx.B).contiguous(), None, None, None, None
+
+
+def vae_loss(xhat, x, kl_rows_t, beta: float, mode: int, z_dim: int, unit_grad: bool = False):
+    return VAELossFn.apply(xhat, x, kl_rows_t, beta, mode, z_dim, unit_grad)
+
+
+__all__ = ["linear", "conv2d_s2k3", "convT2d_s2k4", "cat_gate", "reparam_kl", "kl_rows", "sq_err_sum", "mse_loss", "vae_loss",
            "VC_LOSS_MEAN_MEAN", "VC_LOSS_SUM_MEAN"]

@@ -1,0 +1,144 @@
+"""Training steps and loops of the reference's VAE scripts on the CUDA ops (12:246-309, 19:209-287, 06:314-360).
+
+What is kept from the reference: batch order (the DataLoader's RandomSampler recipe is replayed, so one seed gives
+the same batches), `drop_last=False`, the two different epoch-average conventions, the log/checkpoint formats and
+the latent export.  What changes: the dataset lives in HBM and batches are gathered on the device; the loss,
+its gradient and the three logged scalars come from one fused kernel; scalars are read back once per epoch
+instead of 3 `.item()` syncs per step; the latent export skips the decoder (the reference runs it for nothing).
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass, field
+from typing import Callable, List, Optional
+
+import numpy as np
+import torch
+
+from . import dist as vdist
+from . import ops
+from ._lib import VC_LOSS_MEAN_MEAN, VC_LOSS_SUM_MEAN
+from .optim import Adam
+
+
+def epoch_permutation(n: int) -> torch.Tensor:
+    """The index order DataLoader(shuffle=True, num_workers=0) would produce for one epoch: the loader iterator
+    draws its _base_seed from the global CPU generator, RandomSampler then draws its own seed from the same
+    generator and calls torch.randperm(n, generator=fresh generator)."""
+    torch.empty((), dtype=torch.int64).random_()  # the DataLoader iterator's _base_seed draw comes first
+    seed = int(torch.empty((), dtype=torch.int64).random_().item())
+    g = torch.Generator()
+    g.manual_seed(seed)
+    return torch.randperm(n, generator=g)
+
+
+def batches(n: int, batch_size: int, shuffle: bool = True):
+    order = epoch_permutation(n) if shuffle else torch.arange(n)
+    for s in range(0, n, batch_size):  # drop_last=False (12:227, 19:192)
+        yield order[s: s + batch_size]
+
+
+class VAEStep:
+    """One optimisation step for any of the three models.  kind: "conv12" | "mlp19" | "mlp06".
+    Under a process group each rank passes ITS slice of the global batch; gradients are combined with weights
+    B_local/B_global so the result equals the reference's single-process batch mean."""
+
+    def __init__(self, model, kind: str, lr: float, beta: float, group=None):
+        self.model, self.kind, self.beta, self.group = model, kind, float(beta), group
+        self.mode = VC_LOSS_SUM_MEAN if kind == "mlp19" else VC_LOSS_MEAN_MEAN
+        self.multi = group is not None and vdist.world_size(group) > 1
+        self.opt = Adam(model.parameters(), lr=lr)
+        self.bucket = vdist.GradBucket(model.parameters(), group) if self.multi else None
+
+    def __call__(self, x, *extra, eps: Optional[torch.Tensor] = None, global_batch: Optional[int] = None):
+        m = self.model
+        if self.bucket is not None:
+            self.bucket.zero()
+        else:
+            self.opt.zero_grad()
+        if self.kind == "conv12":
+            lyr, mask = extra
+            mu, lv = m.encode(x, lyr, mask)
+        elif self.kind == "mlp19":
+            c = extra[0] if extra else None
+            mu, lv = m.encode(x, c)
+        else:
+            mu, lv = m.encode(x)
+        if eps is None:
+            eps = torch.randn_like(mu)
+        z, klr = ops.reparam_kl(mu, lv, eps)
+        if self.kind == "conv12":
+            xhat = m.audio_dec(z)
+        elif self.kind == "mlp19":
+            xhat = m.decode(z, extra[0] if extra else None)
+        else:
+            xhat = m.decode(z)
+        loss, stats = ops.vae_loss(xhat, x, klr, self.beta, self.mode, mu.shape[1], unit_grad=True)
+        loss.backward()
+        if self.multi:
+            self.bucket.all_reduce_mean(x.shape[0], global_batch or x.shape[0] * vdist.world_size(self.group))
+        self.opt.step()
+        return stats  # device tensor [loss, recon, kl] of the local batch
+
+
+@dataclass
+class TrainLog:
+    loss: List[float] = field(default_factory=list)
+    recon: List[float] = field(default_factory=list)
+    kl: List[float] = field(default_factory=list)
+
+
+def _to_dev(a, device):
+    t = a if isinstance(a, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(a))
+    return t.to(device=device, dtype=torch.float32).contiguous()
+
+
+def fit(model, kind: str, arrays, epochs: int, batch_size: int, lr: float, beta: float, device=None,
+        on_epoch: Optional[Callable] = None, group=None) -> TrainLog:
+    """The hot loop of 12:246-287 / 19:209-245 / 06:314-344 with a device-resident dataset.
+    arrays: (X, lyr, mask) for conv12; (X,) or (X, cond) for mlp19; (X,) for mlp06.
+    Epoch averages follow the scripts: unweighted mean of batch means for 06/12 (12:274-276), sample-weighted
+    for 19 (19:234-242)."""
+    device = device or torch.device("cuda", torch.cuda.current_device())
+    data = [_to_dev(a, device) for a in arrays]
+    n = data[0].shape[0]
+    model.to(device).train()
+    step = VAEStep(model, kind, lr, beta, group)
+    world, rank = (vdist.world_size(group), vdist.rank(group)) if group is not None else (1, 0)
+    log = TrainLog()
+    for epoch in range(1, epochs + 1):
+        acc = torch.zeros(3, dtype=torch.float64, device=device)
+        denom = 0.0
+        for idx in batches(n, batch_size):  # every rank draws the same permutation (same seed)
+            gb = idx.numel()
+            lo, hi = vdist.shard_bounds(gb, rank, world)
+            if hi <= lo:
+                continue
+            sel = idx[lo:hi].to(device)
+            stats = step(*[t.index_select(0, sel) for t in data], global_batch=gb)
+            w = float(hi - lo) if kind == "mlp19" else 1.0
+            acc += stats.to(torch.float64) * w
+            denom += w
+        tot = acc.cpu().numpy() / max(denom, 1.0)  # the one host sync of the epoch
+        log.loss.append(float(tot[0])); log.recon.append(float(tot[1])); log.kl.append(float(tot[2]))
+        if on_epoch is not None:
+            on_epoch(epoch, log, model)
+    return log
+
+
+@torch.no_grad()
+def export_latents(model, kind: str, arrays, batch_size: int = 512, device=None) -> np.ndarray:
+    """mu for every sample in the original order, float32 (12:289-309, 19:269-287, 06:354-360)."""
+    device = device or torch.device("cuda", torch.cuda.current_device())
+    data = [_to_dev(a, device) for a in arrays]
+    model.to(device).eval()
+    outs = []
+    for s in range(0, data[0].shape[0], batch_size):
+        part = [t[s: s + batch_size] for t in data]
+        if kind == "conv12":
+            mu, _ = model.encode(*part)
+        elif kind == "mlp19":
+            mu, _ = model.encode(part[0], part[1] if len(part) > 1 else None)
+        else:
+            mu, _ = model.encode(part[0])
+        outs.append(mu)
+    return torch.cat(outs, 0).cpu().numpy().astype(np.float32)
