@@ -208,4 +208,4 @@ def train_step(p: Dict[str, Tensor], opt: AdamRef, kind: str, batch: dict, beta:
     grads = dict(zip(names, gs))
     opt.last_grads = grads
     opt.step(grads)
-    return float(loss), float(rec), float(kl)
+    return float(loss.detach()), float(rec.detach()), float(kl.detach())

@@ -1,0 +1,137 @@
+"""GPU: every CUDA op against the plain torch fp32 op it replaces (forward values and all gradients), on the
+reference's layer shapes scaled down, including odd spatial sizes (T=646 -> 323 -> 162 -> 81 path of script 12)."""
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+RTOL, ATOL = 2e-4, 2e-5  # fp32 FFMA in a different summation order than cuDNN/cuBLAS
+
+
+def _dev():
+    return torch.device("cuda")
+
+
+def _rand(*shape, seed=0, scale=1.0):
+    g = torch.Generator().manual_seed(seed)
+    return (torch.randn(*shape, generator=g) * scale).to(_dev())
+
+
+def _check(fn_ours, fn_ref, inputs, names):
+    ins_a = [t.clone().requires_grad_(t.dtype.is_floating_point and r) for t, r in inputs]
+    ins_b = [t.clone().requires_grad_(t.dtype.is_floating_point and r) for t, r in inputs]
+    ya, yb = fn_ours(*ins_a), fn_ref(*ins_b)
+    torch.testing.assert_close(ya, yb, rtol=RTOL, atol=ATOL)
+    g = torch.randn_like(yb)
+    ya.backward(g)
+    yb.backward(g)
+    for a, b, n, (_, r) in zip(ins_a, ins_b, names, inputs):
+        if r:
+            scale = float(b.grad.abs().max().clamp_min(1e-6))
+            torch.testing.assert_close(a.grad, b.grad, rtol=RTOL, atol=ATOL * max(1.0, scale), msg=lambda m: f"{n}: {m}")
+
+
+@pytest.mark.parametrize("M,N,K,relu", [(64, 256, 470, True), (17, 16, 256, False), (3, 700, 33, True),
+                                        (256, 464, 256, False), (5, 256, 4100, True)])
+def test_linear(M, N, K, relu):
+    from vaeclust import ops
+    x, w, b = _rand(M, K, seed=1), _rand(N, K, seed=2, scale=K ** -0.5), _rand(N, seed=3)
+    ref = lambda x, w, b: F.relu(F.linear(x, w, b)) if relu else F.linear(x, w, b)
+    _check(lambda x, w, b: ops.linear(x, w, b, relu), ref, [(x, True), (w, True), (b, True)], ["x", "w", "b"])
+
+
+@pytest.mark.parametrize("B,Cin,H,W,Cout,relu", [(2, 1, 16, 22, 32, True), (3, 32, 8, 11, 64, True),
+                                                 (2, 64, 5, 7, 128, False), (1, 3, 9, 323, 8, True)])
+def test_conv2d_s2k3(B, Cin, H, W, Cout, relu):
+    from vaeclust import ops
+    x, w, b = _rand(B, Cin, H, W, seed=1), _rand(Cout, Cin, 3, 3, seed=2, scale=(Cin * 9) ** -0.5), _rand(Cout, seed=3)
+    def ref(x, w, b):
+        y = F.conv2d(x, w, b, stride=2, padding=1)
+        return F.relu(y) if relu else y
+    _check(lambda x, w, b: ops.conv2d_s2k3(x, w, b, relu), ref, [(x, True), (w, True), (b, True)], ["x", "w", "b"])
+
+
+@pytest.mark.parametrize("B,Cin,H,W,Cout,relu", [(2, 128, 2, 3, 64, True), (3, 64, 4, 6, 32, True),
+                                                 (2, 32, 8, 12, 1, False), (1, 5, 3, 81, 7, True)])
+def test_convT2d_s2k4(B, Cin, H, W, Cout, relu):
+    from vaeclust import ops
+    x, w, b = _rand(B, Cin, H, W, seed=1), _rand(Cin, Cout, 4, 4, seed=2, scale=(Cin * 4) ** -0.5), _rand(Cout, seed=3)
+    def ref(x, w, b):
+        y = F.conv_transpose2d(x, w, b, stride=2, padding=1)
+        return F.relu(y) if relu else y
+    _check(lambda x, w, b: ops.convT2d_s2k4(x, w, b, relu), ref, [(x, True), (w, True), (b, True)], ["x", "w", "b"])
+
+
+def test_cat_gate():
+    from vaeclust import ops
+    a, l = _rand(9, 32, seed=1), _rand(9, 128, seed=2)
+    m = (torch.rand(9, generator=torch.Generator().manual_seed(3)) < 0.6).float().to(_dev())
+    _check(lambda a, l: ops.cat_gate(a, l, m, True), lambda a, l: torch.cat([a, l * m[:, None], m[:, None]], 1),
+           [(a, True), (l, True)], ["a", "l"])
+    _check(lambda a, l: ops.cat_gate(a, l), lambda a, l: torch.cat([a, l], 1), [(a, True), (l, True)], ["a", "l"])
+
+
+@pytest.mark.parametrize("B,z", [(64, 32), (7, 16), (256, 16)])
+def test_reparam_kl(B, z):
+    from vaeclust import ops
+    mu, lv, eps = _rand(B, z, seed=1), _rand(B, z, seed=2, scale=0.5), _rand(B, z, seed=3)
+    def ours(mu, lv):
+        zz, kl = ops.reparam_kl(mu, lv, eps)
+        return torch.cat([zz, kl[:, None]], 1)
+    def ref(mu, lv):
+        zz = mu + eps * torch.exp(0.5 * lv)
+        kl = -0.5 * torch.sum(1 + lv - mu.pow(2) - lv.exp(), dim=1)
+        return torch.cat([zz, kl[:, None]], 1)
+    _check(ours, ref, [(mu, True), (lv, True)], ["mu", "lv"])
+    _check(lambda mu, lv: ops.kl_rows(mu, lv), lambda mu, lv: -0.5 * torch.sum(1 + lv - mu.pow(2) - lv.exp(), dim=1),
+           [(mu, True), (lv, True)], ["mu", "lv"])
+
+
+@pytest.mark.parametrize("shape_hat,shape_x", [((4, 1, 16, 24), (4, 1, 16, 22)), ((3, 1, 128, 1024), (3, 1, 128, 1024)),
+                                               ((32, 464), (32, 464)), ((5, 1, 7, 9), (5, 1, 7, 9))])
+def test_mse_and_fused_vae_loss(shape_hat, shape_x):
+    from vaeclust import ops
+    from vaeclust._lib import VC_LOSS_MEAN_MEAN, VC_LOSS_SUM_MEAN
+    xhat, x = _rand(*shape_hat, seed=1), _rand(*shape_x, seed=2)
+    crop = (lambda t: t[..., : shape_x[-2], : shape_x[-1]]) if len(shape_x) == 4 else (lambda t: t)
+    _check(lambda xh: ops.mse_loss(xh, x), lambda xh: F.mse_loss(crop(xh), x), [(xhat, True)], ["xhat"])
+    B, z = shape_x[0], 16
+    mu, lv, eps = _rand(B, z, seed=3), _rand(B, z, seed=4, scale=0.3), _rand(B, z, seed=5)
+    for mode, beta in ((VC_LOSS_MEAN_MEAN, 1.0), (VC_LOSS_SUM_MEAN, 4.0)):
+        a = [t.clone().requires_grad_(True) for t in (xhat, mu, lv)]
+        b = [t.clone().requires_grad_(True) for t in (xhat, mu, lv)]
+        _, klr = ops.reparam_kl(a[1], a[2], eps)
+        loss, stats = ops.vae_loss(a[0], x, klr, beta, mode, z, unit_grad=True)
+        loss.backward()
+        d = crop(b[0]) - x
+        klt = 1 + b[2] - b[1].pow(2) - b[2].exp()
+        if mode == VC_LOSS_MEAN_MEAN:
+            rec, kl = d.pow(2).mean(), -0.5 * klt.mean()
+        else:
+            rec, kl = d.pow(2).flatten(1).sum(1).mean(), (-0.5 * klt.sum(1)).mean()
+        ref = rec + beta * kl
+        ref.backward()
+        torch.testing.assert_close(stats, torch.stack([ref, rec, kl]).detach(), rtol=1e-5, atol=1e-6)
+        for p, q in zip(a, b):
+            torch.testing.assert_close(p.grad, q.grad, rtol=1e-4, atol=1e-7)
+
+
+def test_adam_matches_torch():
+    from vaeclust.optim import Adam
+    torch.manual_seed(0)
+    shapes = [(300, 70), (5,), (65536 + 3,), (128, 64, 4, 4)]
+    pa = [torch.nn.Parameter(torch.randn(*s, device=_dev())) for s in shapes]
+    pb = [torch.nn.Parameter(p.detach().clone()) for p in pa]
+    oa, ob = Adam(pa, lr=2e-3), torch.optim.Adam(pb, lr=2e-3)
+    for step in range(4):
+        for i, (p, q) in enumerate(zip(pa, pb)):
+            if i == 1 and step < 2:   # a parameter without gradient is skipped and its step does not advance
+                p.grad = q.grad = None
+                continue
+            g = torch.randn_like(p) * (10.0 ** (step - 2))
+            p.grad, q.grad = g.clone(), g.clone()
+        oa.step()
+        ob.step()
+    for p, q in zip(pa, pb):
+        torch.testing.assert_close(p, q, rtol=2e-6, atol=1e-7)

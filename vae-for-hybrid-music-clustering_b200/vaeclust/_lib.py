@@ -56,6 +56,40 @@ class VaeclustError(RuntimeError):
     pass
 
 
+# kernels launched per entry point (for bench.py's gpu_launches claim); anything absent launches one kernel
+_LAUNCHES = {
+    "vc_recon_loss_fwd_bwd": 2, "vc_conv2d_s2k3_wgrad": 2, "vc_convT2d_s2k4_wgrad": 2, "vc_convT2d_s2k4_fwd": 4,
+    "vc_kmeans_assign_update": 2, "vc_cluster_sums": 2, "vc_kmeans_inertia": 2, "vc_dbi_intra": 2, "vc_col_stats": 2,
+    "vc_silhouette_finalize": 2,
+}
+
+
+class Profiler:
+    """Brackets every C-ABI call with CUDA events on the launching stream (bench.py's per-kernel durations)."""
+
+    def __init__(self):
+        self.records = []  # (name, int-args signature, start event, end event)
+
+    def run(self, name, args, fn):
+        import torch
+
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        rc = fn(*args)
+        b.record()
+        self.records.append((name, tuple(x for x in args[:-1] if isinstance(x, int) and not isinstance(x, bool)
+                                         and abs(x) < (1 << 31)), a, b))
+        return rc
+
+    def summary(self):
+        """{(name, signature): (count, total_ms)} -- call after torch.cuda.synchronize()."""
+        out = {}
+        for name, sig, a, b in self.records:
+            c, t = out.get((name, sig), (0, 0.0))
+            out[(name, sig)] = (c + 1, t + a.elapsed_time(b))
+        return out
+
+
 class _Lib:
     def __init__(self) -> None:
         if not LIB_PATH.is_file():
@@ -64,6 +98,9 @@ class _Lib:
                 f"__graft_entry__ as g; g.build()'); vaeclust has no CPU or PyTorch fallback."
             )
         self.cdll = ctypes.CDLL(str(LIB_PATH))
+        self.profiler = None      # set to a Profiler to time every entry point with CUDA events
+        self.n_calls = 0          # C-ABI calls made
+        self.n_launches = 0       # kernels those calls launched (table below)
         self.protos = parse_header()
         for name, (restype, argtypes) in self.protos.items():
             fn = getattr(self.cdll, name)
@@ -74,7 +111,13 @@ class _Lib:
         return (self.cdll.vc_last_error_string() or b"").decode()
 
     def call(self, name: str, *args):
-        rc = getattr(self.cdll, name)(*args)
+        prof = self.profiler
+        if prof is None:
+            rc = getattr(self.cdll, name)(*args)
+        else:
+            rc = prof.run(name, args, getattr(self.cdll, name))
+        self.n_calls += 1
+        self.n_launches += _LAUNCHES.get(name, 1)
         if rc != VC_OK:
             raise VaeclustError(f"{name} failed ({rc}): {self.last_error()}")
 
