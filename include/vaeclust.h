@@ -65,10 +65,13 @@ int vc_loss_finalize(const double* sq_sum, const float* kl_rows, int B, int z, i
 
 /* ------------------------------------------------------------------------------------------ dense layers
  * nn.Linear (+ReLU) of 12:98-103,114-117,129-132,159-164; 19:79-95; 06:149-157.
- * y[M,N] = act(x[M,K] W[N,K]^T + b[N]). */
+ * y[M,N] = act(x[M,K] W[N,K]^T + b[N]).  Skinny shapes with a huge reduction (the 262144-wide FC layers of script 12
+ * at batch 64) are split over the reduction into the workspace and reduced in a fixed order. */
+size_t vc_linear_workspace_bytes(int M, int N, int K);
 int vc_linear_fwd(const float* x, const float* W, const float* b, float* y, int M, int N, int K, int relu,
-                  void* stream);
-int vc_linear_dgrad(const float* dy, const float* W, float* dx, int M, int N, int K, void* stream);
+                  void* workspace, size_t workspace_bytes, void* stream);
+int vc_linear_dgrad(const float* dy, const float* W, float* dx, int M, int N, int K, void* workspace,
+                    size_t workspace_bytes, void* stream);
 int vc_linear_wgrad(const float* dy, const float* x, float* dW, int M, int N, int K, int accumulate,
                     void* stream);
 /* db[c] (+)= sum over outer,inner of dy[outer, C, inner]  (bias gradient of Linear: inner=1; Conv: inner=H*W) */

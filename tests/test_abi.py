@@ -38,7 +38,7 @@ def test_version_and_error_string():
 def test_bad_arguments_fail_loudly_without_gpu():
     L = lib()
     with pytest.raises(VaeclustError, match="vc_linear_fwd"):
-        L.call("vc_linear_fwd", None, None, None, None, 0, 0, 0, 0, None)
+        L.call("vc_linear_fwd", None, None, None, None, 0, 0, 0, 0, None, 0, None)
     with pytest.raises(VaeclustError, match="d % 4"):
         L.call("vc_kmeans_assign_update", 16, 10, 3, 16, 2, 16, 16, 16, None, 1, 16, 1 << 30, None)
     with pytest.raises(VaeclustError, match="bad mode"):

@@ -267,6 +267,16 @@ __global__ void splitk_reduce_kernel(const float* __restrict__ part, int nsplit,
   out[i] = acc;
 }
 
+template <class EP>
+__global__ void splitk_reduce_ep_kernel(const float* __restrict__ part, int nsplit, int M, int N, const EP ep) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int64_t MN = (int64_t)M * N;
+  if (i >= MN) return;
+  float acc = 0.f;
+  for (int z = 0; z < nsplit; ++z) acc += part[(int64_t)z * MN + i];
+  ep((int)(i / N), (int)(i % N), acc, 0);
+}
+
 template <class AL, class BL, class EP>
 static int launch_gemm(const AL& al, const BL& bl, const EP& ep, int M, int N, int K, int nsplit, cudaStream_t s) {
   if (M <= 0 || N <= 0 || K <= 0) return VC_OK;
@@ -278,6 +288,34 @@ static int launch_gemm(const AL& al, const BL& bl, const EP& ep, int M, int N, i
     dim3 grid((M + 127) / 128, (N + 63) / 64, nsplit);
     gemm_simt_kernel<16, 16, AL, BL, EP><<<grid, 256, 0, s>>>(al, bl, ep, M, N, K, kchunk);
   }
+  VC_LAUNCH_CHECK();
+  return VC_OK;
+}
+
+// Skinny GEMMs with a huge reduction (the script-12 FC layers: M=64, K or N = 262144): split the reduction over
+// enough CTAs to fill the GPU, partials to the workspace, fixed-order reduce fused with the epilogue.
+static int linear_splits(int M, int N, int K) {
+  const int tiles = ((M + 127) / 128) * ((N + 63) / 64);
+  if (tiles >= 148 || K < 4096) return 1;
+  int s = (2 * 148 + tiles - 1) / tiles;
+  while (s > 1 && K / s < 512) --s;
+  return s;
+}
+
+template <class AL, class BL, class EP>
+static int launch_gemm_auto(const AL& al, const BL& bl, const EP& ep, int M, int N, int K, void* ws, size_t ws_bytes,
+                            cudaStream_t s) {
+  const int ns = linear_splits(M, N, K);
+  if (ns <= 1) return launch_gemm(al, bl, ep, M, N, K, 1, s);
+  const int64_t MN = (int64_t)M * N;
+  if (!ws || ws_bytes < sizeof(float) * (size_t)ns * MN) {
+    set_error("linear: workspace too small for split-K (%d splits of %lld floats)", ns, (long long)MN);
+    return VC_ERR_WORKSPACE;
+  }
+  EpSplitK eps{static_cast<float*>(ws), MN, N};
+  int rc = launch_gemm(al, bl, eps, M, N, K, ns, s);
+  if (rc != VC_OK) return rc;
+  splitk_reduce_ep_kernel<EP><<<(int)((MN + 255) / 256), 256, 0, s>>>(static_cast<float*>(ws), ns, M, N, ep);
   VC_LAUNCH_CHECK();
   return VC_OK;
 }
@@ -302,22 +340,31 @@ static inline ConvGeom convT_geom(int B, int Cin, int H, int W, int Cout) {
 }
 static inline bool fits_int(int64_t v) { return v > 0 && v < (int64_t)2147483647; }
 
+extern "C" size_t vc_linear_workspace_bytes(int M, int N, int K) {
+  // worst case over fwd (reduce over K) and dgrad (reduce over N)
+  size_t a = (size_t)linear_splits(M, N, K) * M * N, b = (size_t)linear_splits(M, K, N) * M * K;
+  if (linear_splits(M, N, K) <= 1) a = 0;
+  if (linear_splits(M, K, N) <= 1) b = 0;
+  return sizeof(float) * (a > b ? a : b);
+}
+
 extern "C" int vc_linear_fwd(const float* x, const float* W, const float* b, float* y, int M, int N, int K, int relu,
-                             void* stream) {
+                             void* workspace, size_t workspace_bytes, void* stream) {
   VC_REQUIRE(x && W && y && M > 0 && N > 0 && K > 0, VC_ERR_BAD_ARG, "vc_linear_fwd: bad arguments M=%d N=%d K=%d", M,
              N, K);
   ARowK a; a.p = x; a.ld = K;
   BRowK bb; bb.p = W; bb.ld = K;
   EpRowMajor ep{y, N, b, relu, 0};
-  return launch_gemm(a, bb, ep, M, N, K, 1, as_stream(stream));
+  return launch_gemm_auto(a, bb, ep, M, N, K, workspace, workspace_bytes, as_stream(stream));
 }
 
-extern "C" int vc_linear_dgrad(const float* dy, const float* W, float* dx, int M, int N, int K, void* stream) {
+extern "C" int vc_linear_dgrad(const float* dy, const float* W, float* dx, int M, int N, int K, void* workspace,
+                               size_t workspace_bytes, void* stream) {
   VC_REQUIRE(dy && W && dx && M > 0 && N > 0 && K > 0, VC_ERR_BAD_ARG, "vc_linear_dgrad: bad arguments");
   ARowK a; a.p = dy; a.ld = N;           // A(m, n') over reduction index n' = out feature
   BColK bb{W, K};                         // B(n', k) = W[n'*K + k]
   EpRowMajor ep{dx, K, nullptr, 0, 0};
-  return launch_gemm(a, bb, ep, M, K, N, 1, as_stream(stream));
+  return launch_gemm_auto(a, bb, ep, M, K, N, workspace, workspace_bytes, as_stream(stream));
 }
 
 extern "C" int vc_linear_wgrad(const float* dy, const float* x, float* dW, int M, int N, int K, int accumulate,

@@ -146,18 +146,43 @@ kmeans_assign_update_kernel(const float* __restrict__ X, int64_t N, int d, const
         const float4* row = reinterpret_cast<const float4*>(xt + (size_t)tid * d);
 #pragma unroll
         for (int j = 0; j < D4; ++j) xr[j] = row[j];
-        for (int c = 0; c < k; ++c) {
-          const float4* cr = reinterpret_cast<const float4*>(cs + c * d);
+        // One sequential FMA chain per centroid over dimensions 0..d-1 -- the accumulation order of a BLAS sgemm
+        // micro-kernel (each output element is a running rank-1 update), which is what sklearn's chunked
+        // `-2 X C^T + ||c||^2` evaluates (_k_means_lloyd.pyx:196-203).  Four centroids are interleaved for ILP.
+        int c = 0;
+        for (; c + 4 <= k; c += 4) {
+          const float4* c0 = reinterpret_cast<const float4*>(cs + (c + 0) * d);
+          const float4* c1 = reinterpret_cast<const float4*>(cs + (c + 1) * d);
+          const float4* c2p = reinterpret_cast<const float4*>(cs + (c + 2) * d);
+          const float4* c3 = reinterpret_cast<const float4*>(cs + (c + 3) * d);
           float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+#pragma unroll
+          for (int j = 0; j < D4; ++j) {
+            const float4 v0 = c0[j], v1 = c1[j], v2 = c2p[j], v3 = c3[j];
+            s0 = fmaf(xr[j].x, v0.x, s0); s1 = fmaf(xr[j].x, v1.x, s1); s2 = fmaf(xr[j].x, v2.x, s2); s3 = fmaf(xr[j].x, v3.x, s3);
+            s0 = fmaf(xr[j].y, v0.y, s0); s1 = fmaf(xr[j].y, v1.y, s1); s2 = fmaf(xr[j].y, v2.y, s2); s3 = fmaf(xr[j].y, v3.y, s3);
+            s0 = fmaf(xr[j].z, v0.z, s0); s1 = fmaf(xr[j].z, v1.z, s1); s2 = fmaf(xr[j].z, v2.z, s2); s3 = fmaf(xr[j].z, v3.z, s3);
+            s0 = fmaf(xr[j].w, v0.w, s0); s1 = fmaf(xr[j].w, v1.w, s1); s2 = fmaf(xr[j].w, v2.w, s2); s3 = fmaf(xr[j].w, v3.w, s3);
+          }
+          const float p0_ = fmaf(-2.f, s0, c2[c]), p1_ = fmaf(-2.f, s1, c2[c + 1]);
+          const float p2_ = fmaf(-2.f, s2, c2[c + 2]), p3_ = fmaf(-2.f, s3, c2[c + 3]);
+          if (c == 0 || p0_ < best) { best = p0_; label = c; }
+          if (p1_ < best) { best = p1_; label = c + 1; }
+          if (p2_ < best) { best = p2_; label = c + 2; }
+          if (p3_ < best) { best = p3_; label = c + 3; }
+        }
+        for (; c < k; ++c) {
+          const float4* cr = reinterpret_cast<const float4*>(cs + c * d);
+          float s0 = 0.f;
 #pragma unroll
           for (int j = 0; j < D4; ++j) {
             const float4 cv = cr[j];
             s0 = fmaf(xr[j].x, cv.x, s0);
-            s1 = fmaf(xr[j].y, cv.y, s1);
-            s2 = fmaf(xr[j].z, cv.z, s2);
-            s3 = fmaf(xr[j].w, cv.w, s3);
+            s0 = fmaf(xr[j].y, cv.y, s0);
+            s0 = fmaf(xr[j].z, cv.z, s0);
+            s0 = fmaf(xr[j].w, cv.w, s0);
           }
-          const float pd = fmaf(-2.f, (s0 + s1) + (s2 + s3), c2[c]);
+          const float pd = fmaf(-2.f, s0, c2[c]);
           if (c == 0 || pd < best) { best = pd; label = c; }
         }
       } else {
@@ -165,15 +190,15 @@ kmeans_assign_update_kernel(const float* __restrict__ X, int64_t N, int d, const
         const int d4 = d >> 2;
         for (int c = 0; c < k; ++c) {
           const float4* cr = reinterpret_cast<const float4*>(cs + c * d);
-          float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+          float s0 = 0.f;
           for (int j = 0; j < d4; ++j) {
             const float4 xv = row[j], cv = cr[j];
             s0 = fmaf(xv.x, cv.x, s0);
-            s1 = fmaf(xv.y, cv.y, s1);
-            s2 = fmaf(xv.z, cv.z, s2);
-            s3 = fmaf(xv.w, cv.w, s3);
+            s0 = fmaf(xv.y, cv.y, s0);
+            s0 = fmaf(xv.z, cv.z, s0);
+            s0 = fmaf(xv.w, cv.w, s0);
           }
-          const float pd = fmaf(-2.f, (s0 + s1) + (s2 + s3), c2[c]);
+          const float pd = fmaf(-2.f, s0, c2[c]);
           if (c == 0 || pd < best) { best = pd; label = c; }
         }
       }

@@ -45,7 +45,9 @@ class LinearFn(torch.autograd.Function):
         if weight.shape[1] != K:
             raise VaeclustError(f"linear: x is [*, {K}] but weight is {tuple(weight.shape)}")
         y = torch.empty((M, N), dtype=torch.float32, device=x.device)
-        lib().call("vc_linear_fwd", ptr(x), ptr(weight), ptr(bias), ptr(y), M, N, K, int(relu), stream_ptr())
+        ws = _workspace(lib().size("vc_linear_workspace_bytes", M, N, K), x.device)
+        lib().call("vc_linear_fwd", ptr(x), ptr(weight), ptr(bias), ptr(y), M, N, K, int(relu), ptr(ws), ws.numel(),
+                   stream_ptr())
         ctx.relu, ctx.has_bias = bool(relu), bias is not None
         ctx.save_for_backward(x, weight, y if relu else None)
         return y
@@ -65,7 +67,8 @@ class LinearFn(torch.autograd.Function):
         dx = dw = db = None
         if ctx.needs_input_grad[0]:
             dx = torch.empty_like(x)
-            lib().call("vc_linear_dgrad", ptr(g), ptr(weight), ptr(dx), M, N, K, s)
+            ws = _workspace(lib().size("vc_linear_workspace_bytes", M, N, K), x.device)
+            lib().call("vc_linear_dgrad", ptr(g), ptr(weight), ptr(dx), M, N, K, ptr(ws), ws.numel(), s)
         if ctx.needs_input_grad[1]:
             dw = torch.empty_like(weight)
             lib().call("vc_linear_wgrad", ptr(g), ptr(x), ptr(dw), M, N, K, 0, s)
