@@ -5,8 +5,9 @@
 // the copy of tile t+2 overlaps the arithmetic of tile t+1.
 //   phase A (thread = point): x row in registers, centroids broadcast from shared memory,
 //            pd_j = ||c_j||^2 - 2 x.c_j, first-minimum argmin with strict '<' (sklearn:_k_means_lloyd.pyx:196-213);
-//   phase B (warp = the 32 points it just labelled, lane = dimension): labels exchanged by shuffle, the row is
-//            added to a warp-private shared-memory accumulator [k,d] with plain (conflict-free, race-free) RMW.
+//   phase B (warp = the 32 points it just labelled, lane = its own point, walking the dimensions diagonally): the
+//            row is added to a warp-private shared-memory accumulator [k,d] with plain, bank-conflict-free,
+//            race-free read-modify-writes (32 points per instruction).
 // Warp accumulators are folded into a per-CTA double accumulator every kFlush tiles, CTAs write double partials,
 // and a second kernel reduces them in a fixed order: bit-reproducible run to run, no floating-point atomics.
 #include "common.cuh"
@@ -46,7 +47,7 @@ __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t by
 struct KmSmem {
   int tp;             // points per tile
   int ncopies;        // accumulator copies (warps * groups)
-  size_t off_acc, off_dsum, off_c, off_c2, off_cnt, off_bar, total;
+  size_t off_acc, off_dsum, off_c, off_c2, off_cnt, off_wl, off_bar, total;
 };
 
 static KmSmem km_layout(int k, int d, int update) {
@@ -54,7 +55,7 @@ static KmSmem km_layout(int k, int d, int update) {
   int tp = 256;
   while (tp > 32 && (size_t)2 * tp * d * 4 > 128 * 1024) tp >>= 1;
   L.tp = tp;
-  const int groups = (d <= 16 && 32 % d == 0) ? 32 / d : 1;
+  const int groups = d < 32 ? (31 / d + 1) : 1;  // accumulator copies per warp (see the diagonal update)
   L.ncopies = update ? kKmWarps * groups : 0;
   size_t o = (size_t)2 * tp * d * 4;
   L.off_acc = o;  o += (size_t)L.ncopies * k * d * 4;
@@ -63,6 +64,7 @@ static KmSmem km_layout(int k, int d, int update) {
   L.off_c = o;    o += (size_t)k * d * 4;
   L.off_c2 = o;   o += (size_t)k * 4;
   L.off_cnt = o;  o += (size_t)k * 4;
+  L.off_wl = o;   o += (size_t)kKmThreads * 4;
   o = (o + 7) & ~(size_t)7;
   L.off_bar = o;  o += 16;
   L.total = o;
@@ -76,14 +78,16 @@ kmeans_assign_update_kernel(const float* __restrict__ X, int64_t N, int d, const
                             int32_t* __restrict__ labels, double* __restrict__ part_sums,
                             long long* __restrict__ part_counts, unsigned long long* __restrict__ n_changed,
                             int update, int assign, int tp, int ncopies, size_t off_acc, size_t off_dsum, size_t off_c,
-                            size_t off_c2, size_t off_cnt, size_t off_bar) {
+                            size_t off_c2, size_t off_cnt, size_t off_wl, size_t off_bar) {
   extern __shared__ __align__(128) unsigned char smem[];
-  float* tile[2] = {reinterpret_cast<float*>(smem), reinterpret_cast<float*>(smem) + (size_t)tp * d};
+  float* tile0 = reinterpret_cast<float*>(smem);
+  const int tile_elems = tp * d;
   float* acc = reinterpret_cast<float*>(smem + off_acc);
   double* dsum = reinterpret_cast<double*>(smem + off_dsum);
   float* cs = reinterpret_cast<float*>(smem + off_c);
   float* c2 = reinterpret_cast<float*>(smem + off_c2);
   int* cnt = reinterpret_cast<int*>(smem + off_cnt);
+  int* wl = reinterpret_cast<int*>(smem + off_wl) + (threadIdx.x & ~31);  // this warp's 32 labels
   uint64_t* bar = reinterpret_cast<uint64_t*>(smem + off_bar);
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -117,7 +121,7 @@ kmeans_assign_update_kernel(const float* __restrict__ X, int64_t N, int d, const
         const int64_t p0 = t * tp;
         const uint32_t bytes = (uint32_t)((N - p0 < tp ? N - p0 : tp) * d * 4);
         mbar_expect_tx(&bar[b], bytes);
-        bulk_g2s(tile[b], X + p0 * d, bytes, &bar[b]);
+        bulk_g2s(tile0 + b * tile_elems, X + p0 * d, bytes, &bar[b]);
       }
     }
   }
@@ -128,15 +132,17 @@ kmeans_assign_update_kernel(const float* __restrict__ X, int64_t N, int d, const
   for (int64_t t = blockIdx.x; t < ntiles; t += gridDim.x, ++it) {
     const int b = it & 1;
     const uint32_t parity = (it >> 1) & 1;
-    mbar_wait(&bar[b], parity);
-    const float* xt = tile[b];
     const int64_t p0 = t * tp;
     const int npts = (int)(N - p0 < tp ? N - p0 : tp);
+    // previous label of my point: issued before the wait so its latency hides behind the tile copy / phase A
+    const int32_t old = (tid < npts) ? labels[p0 + tid] : -1;
+    mbar_wait(&bar[b], parity);
+    const float* xt = tile0 + b * tile_elems;
 
     // ---------------- phase A: distances + argmin, thread = point
     int label = -1;
     if (tid < npts && !assign) {
-      label = labels[p0 + tid];
+      label = old;
       if ((unsigned)label >= (unsigned)k) label = -1;
       else atomicAdd(&cnt[label], 1);
     } else if (tid < npts) {
@@ -202,7 +208,6 @@ kmeans_assign_update_kernel(const float* __restrict__ X, int64_t N, int d, const
           if (c == 0 || pd < best) { best = pd; label = c; }
         }
       }
-      const int32_t old = labels[p0 + tid];
       labels[p0 + tid] = label;
       my_changed += (old != label);
       if (update) atomicAdd(&cnt[label], 1);
@@ -210,22 +215,19 @@ kmeans_assign_update_kernel(const float* __restrict__ X, int64_t N, int d, const
 
     // ---------------- phase B: centroid-sum update, warp = its own 32 points, lane = dimension
     if (update) {
-      const int wp0 = warp * 32;  // first point (within the tile) of this warp
-      if (d <= 16 && 32 % d == 0) {
-        const int groups = 32 / d, g = lane / d, dim = lane % d;
-        float* my = acc + (size_t)(warp * groups + g) * kd;
-        for (int q = g; q < 32; q += groups) {
-          const int lab = __shfl_sync(0xffffffffu, label, q);
-          if (lab >= 0) my[lab * d + dim] += xt[(size_t)(wp0 + q) * d + dim];
-        }
-      } else {
-        float* my = acc + (size_t)warp * kd;
-        for (int q = 0; q < 32; ++q) {
-          const int lab = __shfl_sync(0xffffffffu, label, q);
-          if (lab >= 0) {
-            for (int dim = lane; dim < d; dim += 32) my[lab * d + dim] += xt[(size_t)(wp0 + q) * d + dim];
-          }
-        }
+      // "diagonal" update: lane = its own point; at step j it handles dimension (j + lane) % d of that point, so the
+      // 32 lanes of one LDS/STS touch 32 different dimensions -> different banks and, even when labels coincide,
+      // different accumulator words (a plain read-modify-write is race free).  For d < 32 lanes that are d apart
+      // would meet on one dimension, so they use separate accumulator copies (copy = lane / d).
+      const int cpy = d < 32 ? lane / d : 0;
+      const int ncp = d < 32 ? (31 / d + 1) : 1;
+      float* my = acc + (size_t)(warp * ncp + cpy) * kd + (label >= 0 ? label * d : 0);
+      const float* xrow = xt + (size_t)(warp * 32 + lane) * d;
+      int dim = lane % d;
+      for (int j = 0; j < d; ++j) {
+        if (label >= 0) my[dim] += xrow[dim];
+        dim = dim + 1 == d ? 0 : dim + 1;
+        __syncwarp();
       }
     }
     __syncthreads();  // every warp is done with tile[b]
@@ -248,7 +250,7 @@ kmeans_assign_update_kernel(const float* __restrict__ X, int64_t N, int d, const
         // order the generic-proxy reads of tile[b] before the async-proxy overwrite
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
         mbar_expect_tx(&bar[b], bytes);
-        bulk_g2s(tile[b], X + pn * d, bytes, &bar[b]);
+        bulk_g2s(tile0 + b * tile_elems, X + pn * d, bytes, &bar[b]);
       }
     }
   }
@@ -419,7 +421,7 @@ static cudaError_t km_launch(int grid, const KmSmem& L, cudaStream_t s, const fl
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L.total);
   if (e != cudaSuccess) return e;
   kern<<<grid, kKmThreads, L.total, s>>>(X, N, d, C, k, labels, ps, pc, nchg, update, assign, L.tp, L.ncopies,
-                                         L.off_acc, L.off_dsum, L.off_c, L.off_c2, L.off_cnt, L.off_bar);
+                                         L.off_acc, L.off_dsum, L.off_c, L.off_c2, L.off_cnt, L.off_wl, L.off_bar);
   return cudaGetLastError();
 }
 
