@@ -10,7 +10,9 @@
 //            race-free read-modify-writes (32 points per instruction).
 // Warp accumulators are folded into a per-CTA double accumulator every kFlush tiles, CTAs write double partials,
 // and a second kernel reduces them in a fixed order: bit-reproducible run to run, no floating-point atomics.
+#include <string.h>
 #include "common.cuh"
+#include "tma.cuh"
 
 namespace vc {
 
@@ -18,36 +20,22 @@ constexpr int kKmThreads = 256;
 constexpr int kKmWarps = kKmThreads / 32;
 constexpr int kFlush = 16;
 
-__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+using tma::mbar_init;
+using tma::mbar_expect_tx;
+using tma::mbar_wait;
 
-__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
-  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
-}
-__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
-  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
-  asm volatile(
-      "{\n\t.reg .pred p;\n\t"
-      "WAIT_%=:\n\t"
-      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
-      "@p bra DONE_%=;\n\t"
-      "bra WAIT_%=;\n\t"
-      "DONE_%=:\n\t}" ::"r"(smem_u32(bar)),
-      "r"(parity)
-      : "memory");
-}
 __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
   asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
-                   smem_u32(dst)),
-               "l"(src), "r"(bytes), "r"(smem_u32(bar))
+                   tma::s32(dst)),
+               "l"(src), "r"(bytes), "r"(tma::s32(bar))
                : "memory");
 }
 
 struct KmSmem {
   int tp;             // points per tile
-  int ncopies;        // accumulator copies (warps * groups)
-  size_t off_acc, off_dsum, off_c, off_c2, off_cnt, off_wl, off_bar, total;
+  int ncopies;        // accumulator copies (warps * copies per warp)
+  int swz;            // 1: tiles arrive through a 2-D tensor map with the 128-byte swizzle (d % 32 == 0)
+  size_t off_acc, off_dsum, off_c, off_c2, off_cnt, off_bar, total;
 };
 
 static KmSmem km_layout(int k, int d, int update) {
@@ -55,6 +43,7 @@ static KmSmem km_layout(int k, int d, int update) {
   int tp = 256;
   while (tp > 32 && (size_t)2 * tp * d * 4 > 128 * 1024) tp >>= 1;
   L.tp = tp;
+  L.swz = (d % 32 == 0) ? 1 : 0;
   const int groups = d < 32 ? (31 / d + 1) : 1;  // accumulator copies per warp (see the diagonal update)
   L.ncopies = update ? kKmWarps * groups : 0;
   size_t o = (size_t)2 * tp * d * 4;
@@ -64,65 +53,82 @@ static KmSmem km_layout(int k, int d, int update) {
   L.off_c = o;    o += (size_t)k * d * 4;
   L.off_c2 = o;   o += (size_t)k * 4;
   L.off_cnt = o;  o += (size_t)k * 4;
-  L.off_wl = o;   o += (size_t)kKmThreads * 4;
   o = (o + 7) & ~(size_t)7;
   L.off_bar = o;  o += 16;
-  L.total = o;
+  L.total = o + 1024;  // slack: the tile ring is aligned to 1024 B by hand (swizzle atoms)
   return L;
 }
 
-// D4 = d/4 when compile-time (register-resident row), 0 = generic d read from shared memory.
-template <int D4>
+struct KmArgs {
+  const float* X; int64_t N; int d; const float* C; int k; int32_t* labels; double* part_sums;
+  long long* part_counts; unsigned long long* n_changed; int update, assign, tp, ncopies;
+  size_t off_acc, off_dsum, off_c, off_c2, off_cnt, off_bar;
+};
+
+// 16-byte chunk j of row r of a tile.  SW: panel j/8 of [tp][128 B] rows, chunk index XORed with r%8 (what TMA wrote);
+// otherwise rows are contiguous.
+template <bool SW>
+__device__ __forceinline__ float4 row_chunk(const unsigned char* tileb, int tp, int d, int r, int j) {
+  if (SW) return *reinterpret_cast<const float4*>(tileb + (size_t)(j >> 3) * tp * 128 + tma::sw128(r, j & 7));
+  return *reinterpret_cast<const float4*>(tileb + ((size_t)r * d + 4 * j) * 4);
+}
+
+// D4 = d/4 when compile-time (register-resident row), 0 = generic d.
+template <int D4, bool SW>
 __global__ void __launch_bounds__(kKmThreads)
-kmeans_assign_update_kernel(const float* __restrict__ X, int64_t N, int d, const float* __restrict__ C, int k,
-                            int32_t* __restrict__ labels, double* __restrict__ part_sums,
-                            long long* __restrict__ part_counts, unsigned long long* __restrict__ n_changed,
-                            int update, int assign, int tp, int ncopies, size_t off_acc, size_t off_dsum, size_t off_c,
-                            size_t off_c2, size_t off_cnt, size_t off_wl, size_t off_bar) {
-  extern __shared__ __align__(128) unsigned char smem[];
-  float* tile0 = reinterpret_cast<float*>(smem);
-  const int tile_elems = tp * d;
-  float* acc = reinterpret_cast<float*>(smem + off_acc);
-  double* dsum = reinterpret_cast<double*>(smem + off_dsum);
-  float* cs = reinterpret_cast<float*>(smem + off_c);
-  float* c2 = reinterpret_cast<float*>(smem + off_c2);
-  int* cnt = reinterpret_cast<int*>(smem + off_cnt);
-  int* wl = reinterpret_cast<int*>(smem + off_wl) + (threadIdx.x & ~31);  // this warp's 32 labels
-  uint64_t* bar = reinterpret_cast<uint64_t*>(smem + off_bar);
+kmeans_assign_update_kernel(const KmArgs a, const __grid_constant__ CUtensorMap tmap) {
+  extern __shared__ unsigned char smem_raw[];
+  unsigned char* smem = smem_raw + ((1024u - (tma::s32(smem_raw) & 1023u)) & 1023u);
+  const int d = a.d, k = a.k, tp = a.tp, update = a.update;
+  const int64_t N = a.N;
+  const size_t tile_bytes = (size_t)tp * d * 4;
+  float* acc = reinterpret_cast<float*>(smem + a.off_acc);
+  double* dsum = reinterpret_cast<double*>(smem + a.off_dsum);
+  float* cs = reinterpret_cast<float*>(smem + a.off_c);
+  float* c2 = reinterpret_cast<float*>(smem + a.off_c2);
+  int* cnt = reinterpret_cast<int*>(smem + a.off_cnt);
+  uint64_t* bar = reinterpret_cast<uint64_t*>(smem + a.off_bar);
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int kd = k * d;
   const int64_t ntiles = (N + tp - 1) / tp;
 
+  auto issue = [&](int b, int64_t t) {  // one thread: arm the barrier and start the copy of tile t into slot b
+    const int64_t p0 = t * tp;
+    unsigned char* dst = smem + (size_t)b * tile_bytes;
+    if (SW) {
+      mbar_expect_tx(&bar[b], (uint32_t)tile_bytes);  // out-of-range rows are zero-filled and still counted
+      for (int p = 0; p < d / 32; ++p) tma::load_2d(dst + (size_t)p * tp * 128, &tmap, &bar[b], p * 32, (int)p0);
+    } else {
+      const uint32_t bytes = (uint32_t)((N - p0 < tp ? N - p0 : tp) * d * 4);
+      mbar_expect_tx(&bar[b], bytes);
+      bulk_g2s(dst, a.X + p0 * d, bytes, &bar[b]);
+    }
+  };
+
   if (tid == 0) {
+    if (SW) tma::prefetch_map(&tmap);
     mbar_init(&bar[0], 1);
     mbar_init(&bar[1], 1);
-    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    tma::mbar_fence_init();
   }
-  for (int i = tid; i < kd; i += kKmThreads) cs[i] = C[i];
+  for (int i = tid; i < kd; i += kKmThreads) cs[i] = a.C[i];
   for (int i = tid; i < k; i += kKmThreads) cnt[i] = 0;
   if (update) {
-    for (int i = tid; i < ncopies * kd; i += kKmThreads) acc[i] = 0.f;
+    for (int i = tid; i < a.ncopies * kd; i += kKmThreads) acc[i] = 0.f;
     for (int i = tid; i < kd; i += kKmThreads) dsum[i] = 0.0;
   }
   __syncthreads();
-  for (int c = warp; c < k; c += kKmWarps) {  // ||c||^2 in the same dimension order as the dot products
+  for (int c = warp; c < k; c += kKmWarps) {
     float s = 0.f;
     for (int j = lane; j < d; j += 32) s += cs[c * d + j] * cs[c * d + j];
     s = warp_sum(s);
     if (lane == 0) c2[c] = s;
   }
-  // prologue: first two tiles of this CTA
   if (tid == 0) {
-#pragma unroll
     for (int b = 0; b < 2; ++b) {
       const int64_t t = (int64_t)blockIdx.x + (int64_t)b * gridDim.x;
-      if (t < ntiles) {
-        const int64_t p0 = t * tp;
-        const uint32_t bytes = (uint32_t)((N - p0 < tp ? N - p0 : tp) * d * 4);
-        mbar_expect_tx(&bar[b], bytes);
-        bulk_g2s(tile0 + b * tile_elems, X + p0 * d, bytes, &bar[b]);
-      }
+      if (t < ntiles) issue(b, t);
     }
   }
   __syncthreads();
@@ -135,26 +141,25 @@ kmeans_assign_update_kernel(const float* __restrict__ X, int64_t N, int d, const
     const int64_t p0 = t * tp;
     const int npts = (int)(N - p0 < tp ? N - p0 : tp);
     // previous label of my point: issued before the wait so its latency hides behind the tile copy / phase A
-    const int32_t old = (tid < npts) ? labels[p0 + tid] : -1;
+    const int32_t old = (tid < npts) ? a.labels[p0 + tid] : -1;
     mbar_wait(&bar[b], parity);
-    const float* xt = tile0 + b * tile_elems;
+    const unsigned char* tileb = smem + (size_t)b * tile_bytes;
 
     // ---------------- phase A: distances + argmin, thread = point
     int label = -1;
-    if (tid < npts && !assign) {
+    if (tid < npts && !a.assign) {
       label = old;
       if ((unsigned)label >= (unsigned)k) label = -1;
       else atomicAdd(&cnt[label], 1);
     } else if (tid < npts) {
       float best = 0.f;
+      // One sequential FMA chain per centroid over dimensions 0..d-1 -- the accumulation order of a BLAS sgemm
+      // micro-kernel (each output element is a running rank-1 update), which is what sklearn's chunked
+      // `-2 X C^T + ||c||^2` evaluates (_k_means_lloyd.pyx:196-203).  Four centroids are interleaved for ILP.
       if (D4 > 0) {
         float4 xr[D4 > 0 ? D4 : 1];
-        const float4* row = reinterpret_cast<const float4*>(xt + (size_t)tid * d);
 #pragma unroll
-        for (int j = 0; j < D4; ++j) xr[j] = row[j];
-        // One sequential FMA chain per centroid over dimensions 0..d-1 -- the accumulation order of a BLAS sgemm
-        // micro-kernel (each output element is a running rank-1 update), which is what sklearn's chunked
-        // `-2 X C^T + ||c||^2` evaluates (_k_means_lloyd.pyx:196-203).  Four centroids are interleaved for ILP.
+        for (int j = 0; j < D4; ++j) xr[j] = row_chunk<SW>(tileb, tp, d, tid, j);
         int c = 0;
         for (; c + 4 <= k; c += 4) {
           const float4* c0 = reinterpret_cast<const float4*>(cs + (c + 0) * d);
@@ -192,13 +197,12 @@ kmeans_assign_update_kernel(const float* __restrict__ X, int64_t N, int d, const
           if (c == 0 || pd < best) { best = pd; label = c; }
         }
       } else {
-        const float4* row = reinterpret_cast<const float4*>(xt + (size_t)tid * d);
         const int d4 = d >> 2;
         for (int c = 0; c < k; ++c) {
           const float4* cr = reinterpret_cast<const float4*>(cs + c * d);
           float s0 = 0.f;
           for (int j = 0; j < d4; ++j) {
-            const float4 xv = row[j], cv = cr[j];
+            const float4 xv = row_chunk<SW>(tileb, tp, d, tid, j), cv = cr[j];
             s0 = fmaf(xv.x, cv.x, s0);
             s0 = fmaf(xv.y, cv.y, s0);
             s0 = fmaf(xv.z, cv.z, s0);
@@ -208,33 +212,52 @@ kmeans_assign_update_kernel(const float* __restrict__ X, int64_t N, int d, const
           if (c == 0 || pd < best) { best = pd; label = c; }
         }
       }
-      labels[p0 + tid] = label;
+      a.labels[p0 + tid] = label;
       my_changed += (old != label);
       if (update) atomicAdd(&cnt[label], 1);
     }
 
-    // ---------------- phase B: centroid-sum update, warp = its own 32 points, lane = dimension
+    // ---------------- phase B: centroid-sum update
     if (update) {
-      // "diagonal" update: lane = its own point; at step j it handles dimension (j + lane) % d of that point, so the
-      // 32 lanes of one LDS/STS touch 32 different dimensions -> different banks and, even when labels coincide,
-      // different accumulator words (a plain read-modify-write is race free).  For d < 32 lanes that are d apart
-      // would meet on one dimension, so they use separate accumulator copies (copy = lane / d).
-      const int cpy = d < 32 ? lane / d : 0;
-      const int ncp = d < 32 ? (31 / d + 1) : 1;
-      float* my = acc + (size_t)(warp * ncp + cpy) * kd + (label >= 0 ? label * d : 0);
-      const float* xrow = xt + (size_t)(warp * 32 + lane) * d;
-      int dim = lane % d;
-      for (int j = 0; j < d; ++j) {
-        if (label >= 0) my[dim] += xrow[dim];
-        dim = dim + 1 == d ? 0 : dim + 1;
-        __syncwarp();
+      // "diagonal" update: lane = its own point; at step j it handles one dimension of that point chosen so that
+      // the 32 lanes of each LDS/STS touch 32 different banks and, even when labels coincide, 32 different
+      // accumulator words (a plain read-modify-write is race free; one instruction serves 32 points).
+      if (SW) {
+        // physical word w = (j + lane) % 32 of the row's 128-byte panel slice holds logical dimension
+        // ((w/4) ^ (row%8))*4 + w%4 ; for a fixed j this map is injective over the lanes.
+        float* my = acc + (size_t)warp * kd + (label >= 0 ? label * d : 0);
+        const int r = warp * 32 + lane;
+        for (int p = 0; p < d / 32; ++p) {
+          const float* xrow = reinterpret_cast<const float*>(tileb + (size_t)p * tp * 128 + (size_t)r * 128);
+          float* myp = my + p * 32;
+          int w = lane;
+#pragma unroll 4
+          for (int j = 0; j < 32; ++j) {
+            const int dim = ((((w >> 2) ^ (lane & 7)) << 2) | (w & 3));
+            if (label >= 0) myp[dim] += xrow[w];
+            w = (w + 1) & 31;
+            __syncwarp();
+          }
+        }
+      } else {
+        // rows are contiguous: dimension (j + lane) % d; lanes d apart would meet, so they use separate copies
+        const int cpy = d < 32 ? lane / d : 0;
+        const int ncp = d < 32 ? (31 / d + 1) : 1;
+        float* my = acc + (size_t)(warp * ncp + cpy) * kd + (label >= 0 ? label * d : 0);
+        const float* xrow = reinterpret_cast<const float*>(tileb) + (size_t)(warp * 32 + lane) * d;
+        int dim = lane % d;
+        for (int j = 0; j < d; ++j) {
+          if (label >= 0) my[dim] += xrow[dim];
+          dim = dim + 1 == d ? 0 : dim + 1;
+          __syncwarp();
+        }
       }
     }
-    __syncthreads();  // every warp is done with tile[b]
+    __syncthreads();  // every warp is done with this slot
     if (update && ((it + 1) % kFlush == 0)) {
       for (int e = tid; e < kd; e += kKmThreads) {
         double s = 0.0;
-        for (int cpy = 0; cpy < ncopies; ++cpy) {
+        for (int cpy = 0; cpy < a.ncopies; ++cpy) {
           s += (double)acc[(size_t)cpy * kd + e];
           acc[(size_t)cpy * kd + e] = 0.f;
         }
@@ -245,12 +268,8 @@ kmeans_assign_update_kernel(const float* __restrict__ X, int64_t N, int d, const
     if (tid == 0) {
       const int64_t tn = t + 2 * (int64_t)gridDim.x;
       if (tn < ntiles) {
-        const int64_t pn = tn * tp;
-        const uint32_t bytes = (uint32_t)((N - pn < tp ? N - pn : tp) * d * 4);
-        // order the generic-proxy reads of tile[b] before the async-proxy overwrite
-        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-        mbar_expect_tx(&bar[b], bytes);
-        bulk_g2s(tile0 + b * tile_elems, X + pn * d, bytes, &bar[b]);
+        tma::fence_proxy_async();  // order the generic-proxy reads of the slot before the async-proxy overwrite
+        issue(b, tn);
       }
     }
   }
@@ -260,13 +279,13 @@ kmeans_assign_update_kernel(const float* __restrict__ X, int64_t N, int d, const
   if (update) {
     for (int e = tid; e < kd; e += kKmThreads) {
       double s = dsum[e];
-      for (int cpy = 0; cpy < ncopies; ++cpy) s += (double)acc[(size_t)cpy * kd + e];
-      part_sums[(size_t)blockIdx.x * kd + e] = s;
+      for (int cpy = 0; cpy < a.ncopies; ++cpy) s += (double)acc[(size_t)cpy * kd + e];
+      a.part_sums[(size_t)blockIdx.x * kd + e] = s;
     }
-    for (int c = tid; c < k; c += kKmThreads) part_counts[(size_t)blockIdx.x * k + c] = cnt[c];
+    for (int c = tid; c < k; c += kKmThreads) a.part_counts[(size_t)blockIdx.x * k + c] = cnt[c];
   }
   my_changed = (unsigned long long)__reduce_add_sync(0xffffffffu, (unsigned)my_changed);
-  if (lane == 0 && my_changed) atomicAdd(n_changed, my_changed);
+  if (lane == 0 && my_changed) atomicAdd(a.n_changed, my_changed);
 }
 
 __global__ void kmeans_reduce_partials_kernel(const double* __restrict__ part_sums,
@@ -413,15 +432,12 @@ extern "C" size_t vc_kmeans_workspace_bytes(int k, int d) {
   return pd + pc + 64;
 }
 
-template <int D4>
-static cudaError_t km_launch(int grid, const KmSmem& L, cudaStream_t s, const float* X, int64_t N, int d,
-                             const float* C, int k, int32_t* labels, double* ps, long long* pc,
-                             unsigned long long* nchg, int update, int assign) {
-  auto kern = kmeans_assign_update_kernel<D4>;
+template <int D4, bool SW>
+static cudaError_t km_launch(int grid, const KmSmem& L, cudaStream_t s, const KmArgs& a, const CUtensorMap& tm) {
+  auto kern = kmeans_assign_update_kernel<D4, SW>;
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L.total);
   if (e != cudaSuccess) return e;
-  kern<<<grid, kKmThreads, L.total, s>>>(X, N, d, C, k, labels, ps, pc, nchg, update, assign, L.tp, L.ncopies,
-                                         L.off_acc, L.off_dsum, L.off_c, L.off_c2, L.off_cnt, L.off_wl, L.off_bar);
+  kern<<<grid, kKmThreads, L.total, s>>>(a, tm);
   return cudaGetLastError();
 }
 
@@ -446,13 +462,30 @@ static int km_run(const float* X, int64_t N, int d, const float* C, int k, int32
   long long* pc = reinterpret_cast<long long*>(ps + blocks * (size_t)k * d);
   unsigned long long* nchg = reinterpret_cast<unsigned long long*>(pc + blocks * (size_t)k);
   VC_CUDA(cudaMemsetAsync(nchg, 0, 8, s));
+  KmArgs a{X, N, d, C, k, labels, ps, pc, nchg, update, assign, L.tp, L.ncopies,
+           L.off_acc, L.off_dsum, L.off_c, L.off_c2, L.off_cnt, L.off_bar};
+  CUtensorMap tm;
+  memset(&tm, 0, sizeof(tm));
+  if (L.swz) {
+    const uint64_t dims[2] = {(uint64_t)d, (uint64_t)N};
+    const uint64_t strides[1] = {(uint64_t)d * 4};
+    const uint32_t box[2] = {32u, (uint32_t)L.tp};
+    int rc = tma::make_map(&tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, X, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B);
+    if (rc != VC_OK) return rc;
+  }
   cudaError_t e;
-  switch (d) {
-    case 8:  e = km_launch<2>(grid, L, s, X, N, d, C, k, labels, ps, pc, nchg, update, assign); break;
-    case 16: e = km_launch<4>(grid, L, s, X, N, d, C, k, labels, ps, pc, nchg, update, assign); break;
-    case 32: e = km_launch<8>(grid, L, s, X, N, d, C, k, labels, ps, pc, nchg, update, assign); break;
-    case 64: e = km_launch<16>(grid, L, s, X, N, d, C, k, labels, ps, pc, nchg, update, assign); break;
-    default: e = km_launch<0>(grid, L, s, X, N, d, C, k, labels, ps, pc, nchg, update, assign); break;
+  if (L.swz) {
+    switch (d) {
+      case 32: e = km_launch<8, true>(grid, L, s, a, tm); break;
+      case 64: e = km_launch<16, true>(grid, L, s, a, tm); break;
+      default: e = km_launch<0, true>(grid, L, s, a, tm); break;
+    }
+  } else {
+    switch (d) {
+      case 8:  e = km_launch<2, false>(grid, L, s, a, tm); break;
+      case 16: e = km_launch<4, false>(grid, L, s, a, tm); break;
+      default: e = km_launch<0, false>(grid, L, s, a, tm); break;
+    }
   }
   VC_REQUIRE(e == cudaSuccess, VC_ERR_CUDA, "%s: launch failed: %s", who, cudaGetErrorString(e));
   if (update) {
