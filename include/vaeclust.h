@@ -159,6 +159,12 @@ int vc_silhouette_gather(const float* X, int64_t N, int d, const int64_t* order,
                          float* sqn, void* stream);
 int vc_silhouette_rows(const float* Xs, const float* sqn, int64_t N, int d, const int64_t* off_dev, int k,
                        int64_t row_begin, int64_t row_end, int nsplit, float* cluster_sums, void* stream);
+/* Tensor-core variant (tcgen05, bf16 hi/lo split with fp32 accumulation in TMEM; d <= 128).  First split the sorted,
+ * centred rows into two bf16 matrices H, L of shape [N, dp] (dp = d rounded up to a multiple of 64, caller-owned,
+ * 128-byte aligned), then run row blocks exactly like vc_silhouette_rows. */
+int vc_silhouette_split_bf16(const float* Xs, int64_t N, int d, int dp, void* H, void* L, void* stream);
+int vc_silhouette_rows_tc(const void* H, const void* L, const float* sqn, int64_t N, int dp, const int64_t* off_dev,
+                          int k, int64_t row_begin, int64_t row_end, int nsplit, float* cluster_sums, void* stream);
 /* s_i = (b-a)/max(a,b) from cluster_sums (:191-200,315-323); writes s per row and *s_sum (double).
  * labels_sorted points at the label of row_begin. */
 size_t vc_silhouette_finalize_workspace_bytes(void);

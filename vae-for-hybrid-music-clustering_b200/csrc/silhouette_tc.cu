@@ -1,0 +1,263 @@
+// Silhouette on the 5th-generation tensor cores (tcgen05 + TMEM + TMA), sm_100a.
+//
+// The N^2 d contraction x_i . x_j runs as bf16 MMAs with fp32 accumulation in tensor memory.  Plain bf16 inputs
+// are not accurate enough for the 1e-5 target, so each fp32 coordinate is split x = hi + lo (two bf16) and
+//   x.y ~= hi.hi + hi.lo + lo.hi           (the dropped lo.lo term is 2^-16 relative)
+// is accumulated by three MMAs per 16-wide k step into the same TMEM tile.  Norms stay fp32.
+//
+// One CTA owns a 128-row block.  Its hi/lo row operands are loaded once; 128-column tiles of the (cluster-sorted)
+// matrix stream through a TMA ring.  Warp roles: warp 0 = TMA producer, warp 1 = MMA issuer (one elected lane),
+// warps 2..5 = epilogue.  Each epilogue thread owns one accumulator lane = one row i: it pulls the 128 dot products
+// of the tile out of TMEM (tcgen05.ld), forms d = sqrt(max(0, |x_i|^2 + |x_j|^2 - 2 x_i.x_j)) and keeps the running
+// sum for the current cluster in a register -- rows are sorted by cluster, so no bucketing is needed
+// (sklearn:metrics/cluster/_unsupervised.py:184-189 does np.bincount per row instead).  Two TMEM accumulator stages
+// let the MMAs of tile t+1 overlap the epilogue of tile t.
+#include "common.cuh"
+#include "tc05.cuh"
+
+namespace vc {
+
+constexpr int ST_ROWS = 128;      // rows per CTA (UMMA M)
+constexpr int ST_COLS = 128;      // columns per tile (UMMA N)
+constexpr int ST_THREADS = 192;   // 6 warps
+
+// fp32 -> (hi, lo) bf16 split, zero-padded to dp columns (dp % 64 == 0)
+__global__ void split_bf16_kernel(const float* __restrict__ X, int64_t N, int d, int dp, __nv_bfloat16* __restrict__ H,
+                                  __nv_bfloat16* __restrict__ L) {
+  const int64_t n = N * dp;
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+    const int c = (int)(i % dp);
+    const int64_t r = i / dp;
+    const float v = c < d ? X[r * d + c] : 0.f;
+    const __nv_bfloat16 h = __float2bfloat16_rn(v);
+    H[i] = h;
+    L[i] = __float2bfloat16_rn(v - __bfloat162float(h));
+  }
+}
+
+struct SilTcArgs {
+  const float* sqn; const int64_t* off; int k; int64_t N, row_begin, row_end; int nsplit; float* out;
+  int panels;   // dp / 64
+  int stages;   // depth of the column-tile ring
+};
+
+__device__ __forceinline__ float fast_sqrt(float x) {
+  float y;
+  asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
+__global__ void __launch_bounds__(ST_THREADS, 1)
+silhouette_tc_kernel(const SilTcArgs a, const __grid_constant__ CUtensorMap mapH, const __grid_constant__ CUtensorMap mapL) {
+  extern __shared__ unsigned char smem_raw[];
+  unsigned char* smem = smem_raw + ((1024u - (tma::s32(smem_raw) & 1023u)) & 1023u);
+  const int P = a.panels, S = a.stages;
+  const uint32_t panel_bytes = ST_ROWS * 128;             // [128 rows][64 bf16]
+  const uint32_t op_bytes = panel_bytes * P;              // one operand (hi or lo) of one tile
+  unsigned char* sA = smem;                               // A_hi | A_lo
+  unsigned char* sB = smem + 2 * op_bytes;                // S x (B_hi | B_lo)
+  float* cns = reinterpret_cast<float*>(sB + (size_t)S * 2 * op_bytes);  // 2 x 128 column norms
+  uint64_t* bars = reinterpret_cast<uint64_t*>(cns + 2 * ST_COLS);
+  uint64_t* a_full = bars;                // 1
+  uint64_t* b_full = bars + 1;            // S
+  uint64_t* b_empty = b_full + S;         // S
+  uint64_t* t_full = b_empty + S;         // 2
+  uint64_t* t_empty = t_full + 2;         // 2
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(t_empty + 2);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int64_t r0 = a.row_begin + (int64_t)blockIdx.x * ST_ROWS;
+  const int split = blockIdx.y;
+
+  if (threadIdx.x == 0) {
+    tma::prefetch_map(&mapH);
+    tma::prefetch_map(&mapL);
+    tma::mbar_init(a_full, 1);
+    for (int s = 0; s < S; ++s) { tma::mbar_init(&b_full[s], 1); tma::mbar_init(&b_empty[s], 1); }
+    for (int s = 0; s < 2; ++s) { tma::mbar_init(&t_full[s], 1); tma::mbar_init(&t_empty[s], 128); }
+    tma::mbar_fence_init();
+  }
+  if (warp == 1) tc05::tmem_alloc(tmem_slot, 256);
+  tc05::fence_before();
+  __syncthreads();
+  tc05::fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ===================== TMA producer =====================
+    if (lane == 0) {
+      tma::mbar_expect_tx(a_full, 2 * op_bytes);
+      for (int p = 0; p < P; ++p) {
+        tma::load_2d(sA + p * panel_bytes, &mapH, a_full, p * 64, (int)r0);
+        tma::load_2d(sA + op_bytes + p * panel_bytes, &mapL, a_full, p * 64, (int)r0);
+      }
+      int64_t counter = 0;
+      uint32_t it = 0;
+      for (int c = 0; c < a.k; ++c) {
+        const int64_t c0 = a.off[c], c1 = a.off[c + 1];
+        for (int64_t j0 = c0; j0 < c1; j0 += ST_COLS, ++counter) {
+          if (counter % a.nsplit != split) continue;
+          const int s = it % S;
+          const uint32_t ph = (it / S) & 1;
+          tma::mbar_wait(&b_empty[s], ph ^ 1);
+          unsigned char* dst = sB + (size_t)s * 2 * op_bytes;
+          tma::mbar_expect_tx(&b_full[s], 2 * op_bytes);
+          for (int p = 0; p < P; ++p) {
+            tma::load_2d(dst + p * panel_bytes, &mapH, &b_full[s], p * 64, (int)j0);
+            tma::load_2d(dst + op_bytes + p * panel_bytes, &mapL, &b_full[s], p * 64, (int)j0);
+          }
+          ++it;
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer =====================
+    if (lane == 0) {
+      constexpr uint32_t kIdesc = tc05::idesc(tc05::kFmtBF16, ST_ROWS, ST_COLS, 0, 0);
+      tma::mbar_wait(a_full, 0);
+      tc05::fence_after();
+      const uint32_t aH = tma::s32(sA), aL = aH + op_bytes;
+      int64_t counter = 0;
+      uint32_t it = 0;
+      for (int c = 0; c < a.k; ++c) {
+        const int64_t c0 = a.off[c], c1 = a.off[c + 1];
+        for (int64_t j0 = c0; j0 < c1; j0 += ST_COLS, ++counter) {
+          if (counter % a.nsplit != split) continue;
+          const int s = it % S;
+          const uint32_t ph = (it / S) & 1;
+          const int as = it & 1;
+          const uint32_t aph = (it >> 1) & 1;
+          tma::mbar_wait(&t_empty[as], aph ^ 1);   // epilogue has drained this accumulator stage
+          tma::mbar_wait(&b_full[s], ph);          // column operands have landed
+          tc05::fence_after();
+          const uint32_t bH = tma::s32(sB + (size_t)s * 2 * op_bytes), bL = bH + op_bytes;
+          const uint32_t tacc = tmem_base + as * ST_COLS;
+          uint32_t accum = 0;
+          for (int p = 0; p < P; ++p) {
+#pragma unroll
+            for (int kk = 0; kk < 4; ++kk) {  // 64 bf16 per panel / UMMA_K 16
+              const uint32_t o = p * panel_bytes + kk * 32;
+              const uint64_t dAH = tc05::desc_k_sw128(aH + o), dAL = tc05::desc_k_sw128(aL + o);
+              const uint64_t dBH = tc05::desc_k_sw128(bH + o), dBL = tc05::desc_k_sw128(bL + o);
+              tc05::mma_bf16(tacc, dAH, dBH, kIdesc, accum);
+              tc05::mma_bf16(tacc, dAH, dBL, kIdesc, 1);
+              tc05::mma_bf16(tacc, dAL, dBH, kIdesc, 1);
+              accum = 1;
+            }
+          }
+          tc05::commit(&b_empty[s]);   // ring slot reusable once these MMAs have read it
+          tc05::commit(&t_full[as]);   // accumulator ready for the epilogue
+          ++it;
+        }
+      }
+    }
+  } else {
+    // ===================== epilogue: warps 2..5, thread = one row =====================
+    const int q = warp & 3;                      // TMEM lane quarter this warp may access
+    const int rl = q * 32 + lane;                // row within the tile
+    const int64_t row = r0 + rl;
+    const bool row_ok = row < a.row_end;
+    const float rn = row_ok ? a.sqn[row] : 0.f;
+    const int e = threadIdx.x - 64;              // 0..127: which column norm this thread stages
+    const int64_t nrows = a.row_end - a.row_begin;
+    float* o = a.out + (int64_t)split * nrows * a.k;
+    int64_t counter = 0;
+    uint32_t it = 0;
+    for (int c = 0; c < a.k; ++c) {
+      const int64_t c0 = a.off[c], c1 = a.off[c + 1];
+      float rsum = 0.f;
+      for (int64_t j0 = c0; j0 < c1; j0 += ST_COLS, ++counter) {
+        if (counter % a.nsplit != split) continue;
+        const int as = it & 1;
+        const uint32_t aph = (it >> 1) & 1;
+        float* cn = cns + as * ST_COLS;
+        cn[e] = (j0 + e < c1) ? a.sqn[j0 + e] : 0.f;
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+        tma::mbar_wait(&t_full[as], aph);
+        tc05::fence_after();
+        const bool masked = (j0 + ST_COLS > c1) || (j0 < r0 + ST_ROWS && r0 < j0 + ST_COLS);
+        const uint32_t tacc = tmem_base + ((uint32_t)(q * 32) << 16) + as * ST_COLS;
+#pragma unroll 1
+        for (int cb = 0; cb < ST_COLS; cb += 32) {
+          float v[32];
+          tc05::ld_32x32(tacc + cb, v);
+          tc05::ld_wait();
+          if (!masked) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+              const float d2 = fmaxf(fmaf(-2.f, v[j], rn + cn[cb + j]), 0.f);
+              rsum += fast_sqrt(d2);
+            }
+          } else {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+              const int64_t col = j0 + cb + j;
+              const float d2 = fmaxf(fmaf(-2.f, v[j], rn + cn[cb + j]), 0.f);
+              rsum += (col < c1 && col != row) ? fast_sqrt(d2) : 0.f;
+            }
+          }
+        }
+        tc05::fence_before();
+        tma::mbar_arrive(&t_empty[as]);
+        ++it;
+      }
+      if (row_ok) o[(row - a.row_begin) * a.k + c] = rsum;
+    }
+  }
+
+  tc05::fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc05::fence_after();
+    tc05::tmem_dealloc(tmem_base, 256);
+  }
+}
+
+}  // namespace vc
+
+using namespace vc;
+
+extern "C" int vc_silhouette_split_bf16(const float* Xs, int64_t N, int d, int dp, void* H, void* L, void* stream) {
+  VC_REQUIRE(Xs && H && L && N > 0 && d > 0 && dp >= d && dp % 64 == 0, VC_ERR_BAD_ARG,
+             "vc_silhouette_split_bf16: bad arguments (d=%d dp=%d)", d, dp);
+  int64_t blocks = (N * dp + 255) / 256;
+  if (blocks > (int64_t)sm_count() * 16) blocks = (int64_t)sm_count() * 16;
+  split_bf16_kernel<<<(int)blocks, 256, 0, as_stream(stream)>>>(Xs, N, d, dp, static_cast<__nv_bfloat16*>(H),
+                                                               static_cast<__nv_bfloat16*>(L));
+  VC_LAUNCH_CHECK();
+  return VC_OK;
+}
+
+extern "C" int vc_silhouette_rows_tc(const void* H, const void* L, const float* sqn, int64_t N, int dp,
+                                     const int64_t* off_dev, int k, int64_t row_begin, int64_t row_end, int nsplit,
+                                     float* cluster_sums, void* stream) {
+  VC_REQUIRE(H && L && sqn && off_dev && cluster_sums && N > 0 && k > 0, VC_ERR_BAD_ARG,
+             "vc_silhouette_rows_tc: bad arguments");
+  VC_REQUIRE(dp % 64 == 0 && dp >= 64 && dp <= 128, VC_ERR_UNSUPPORTED,
+             "vc_silhouette_rows_tc: padded width %d not in {64, 128} (use the fp32 kernel)", dp);
+  VC_REQUIRE(row_begin >= 0 && row_end <= N && row_begin < row_end, VC_ERR_BAD_ARG,
+             "vc_silhouette_rows_tc: bad row range");
+  VC_REQUIRE(nsplit >= 1 && nsplit <= 65535 && N < 2147483647LL, VC_ERR_BAD_ARG, "vc_silhouette_rows_tc: bad nsplit/N");
+  VC_REQUIRE(((reinterpret_cast<uintptr_t>(H) | reinterpret_cast<uintptr_t>(L)) & 127) == 0, VC_ERR_BAD_ARG,
+             "vc_silhouette_rows_tc: operand buffers must be 128-byte aligned");
+  CUtensorMap mH, mL;
+  const uint64_t dims[2] = {(uint64_t)dp, (uint64_t)N};
+  const uint64_t strides[1] = {(uint64_t)dp * 2};
+  const uint32_t box[2] = {64u, (uint32_t)ST_ROWS};
+  int rc = tma::make_map(&mH, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, H, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B);
+  if (rc != VC_OK) return rc;
+  rc = tma::make_map(&mL, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, L, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B);
+  if (rc != VC_OK) return rc;
+  SilTcArgs a;
+  a.sqn = sqn; a.off = off_dev; a.k = k; a.N = N; a.row_begin = row_begin; a.row_end = row_end; a.nsplit = nsplit;
+  a.out = cluster_sums; a.panels = dp / 64; a.stages = dp == 64 ? 4 : 2;
+  const size_t op = (size_t)ST_ROWS * 128 * a.panels;
+  const size_t smem = 2 * op + (size_t)a.stages * 2 * op + 2 * ST_COLS * 4 + (1 + 2 * a.stages + 4) * 8 + 16 + 1024;
+  VC_CUDA(cudaFuncSetAttribute(silhouette_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  const int64_t tiles = (row_end - row_begin + ST_ROWS - 1) / ST_ROWS;
+  dim3 grid((unsigned)tiles, (unsigned)nsplit);
+  silhouette_tc_kernel<<<grid, ST_THREADS, smem, as_stream(stream)>>>(a, mH, mL);
+  VC_LAUNCH_CHECK();
+  return VC_OK;
+}

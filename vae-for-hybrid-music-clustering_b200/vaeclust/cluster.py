@@ -383,6 +383,9 @@ def _sil_prepare(Xd: torch.Tensor, order: torch.Tensor, mean64: torch.Tensor):
     return Xs, sqn
 
 
+SILHOUETTE_PRECISION = "tc"  # "tc": tcgen05 bf16 hi/lo split (d <= 128); "fp32": FFMA tile kernel
+
+
 def _sil_block(Xs, sqn, off, k: int, r0: int, r1: int, lab_sorted, counts, s_sorted, s_sum) -> None:
     """Rows [r0, r1) against all columns: per-row silhouette into s_sorted[r0:r1] and their sum into s_sum."""
     N, d = Xs.shape
@@ -391,7 +394,16 @@ def _sil_block(Xs, sqn, off, k: int, r0: int, r1: int, lab_sorted, counts, s_sor
     sms = lib().size("vc_sm_count")
     nsplit = int(max(1, min(32, (2 * sms) // max(tiles, 1))))
     sums = torch.empty((nsplit, nrows, k), dtype=torch.float32, device=Xs.device)
-    lib().call("vc_silhouette_rows", ptr(Xs), ptr(sqn), N, d, ptr(off), k, r0, r1, nsplit, ptr(sums), stream_ptr())
+    dp = (d + 63) // 64 * 64
+    if SILHOUETTE_PRECISION == "tc" and dp <= 128:
+        H = torch.empty((N, dp), dtype=torch.bfloat16, device=Xs.device)
+        L = torch.empty((N, dp), dtype=torch.bfloat16, device=Xs.device)
+        lib().call("vc_silhouette_split_bf16", ptr(Xs), N, d, dp, ptr(H), ptr(L), stream_ptr())
+        lib().call("vc_silhouette_rows_tc", ptr(H), ptr(L), ptr(sqn), N, dp, ptr(off), k, r0, r1, nsplit, ptr(sums),
+                   stream_ptr())
+    else:
+        lib().call("vc_silhouette_rows", ptr(Xs), ptr(sqn), N, d, ptr(off), k, r0, r1, nsplit, ptr(sums),
+                   stream_ptr())
     ws = _workspace(lib().size("vc_silhouette_finalize_workspace_bytes"), Xs.device)
     lib().call("vc_silhouette_finalize", ptr(sums), nsplit, ptr(lab_sorted[r0:]), ptr(counts), k, nrows,
                ptr(s_sorted[r0:]), ptr(s_sum), ptr(ws), ws.numel(), stream_ptr())
