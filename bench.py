@@ -103,6 +103,13 @@ def synth_vae_data(n, device, seed=0):
 def flops_of(name: str, sig) -> float:
     """Algorithmic FLOPs of one C-ABI call from its integer arguments ('algorithmic work')."""
     try:
+        if name == "vc_dense_op":
+            op, _prec, B, Cin, H, W, Cout = sig[:7]
+            if op <= 2:
+                return 2.0 * B * Cin * Cout
+            if op <= 5:
+                return 2.0 * B * ((H - 1) // 2 + 1) * ((W - 1) // 2 + 1) * Cout * Cin * 9
+            return 2.0 * B * (4 * H * W) * Cout * Cin * 4
         if name.startswith("vc_linear_"):
             M, N, K = sig[:3]
             return 2.0 * M * N * K
@@ -156,6 +163,8 @@ def bench_vae(args, rank, world, device, group):
     from vaeclust.train import VAEStep
 
     L = vaeclust.lib()
+    from vaeclust import ops as vops
+    vops.set_precision(args.precision)
     X, lyr, m = synth_vae_data(N_CLIPS, device, seed=0)
     torch.manual_seed(42)
     model = nn.ConvMultiModalVAE(1, (F_MEL, T_MEL), ZDIM, LYR).to(device).train()
@@ -353,6 +362,8 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--precision", default="bf16", choices=["bf16", "fp32"],
+                    help="dense-layer arithmetic: bf16 = tcgen05 tensor cores (fp32 accumulate), fp32 = FFMA parity mode")
     ap.add_argument("--skip-extra", action="store_true", help="VAE step only (no KMeans / silhouette sub-benchmarks)")
     ap.add_argument("--skip-cpu", action="store_true", help="do not time the CPU baseline")
     args = ap.parse_args()
@@ -393,7 +404,7 @@ def main():
         roof = roofline_from_summary(vae["summ"], args.steps, vae["n_params"], pk)
         line = {"metric": METRIC, "value": clips / (vae["ms"] * 1e-3), "unit": UNIT, "n_gpus": world,
                 "steps": args.steps, "warmup": args.warmup, "ms_per_step": vae["ms"] / args.steps,
-                "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+                "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16" if args.precision == "bf16" else "f32", "data": "synthetic",
                 "config": {"workload": f"script-12 conv multimodal VAE train step (fwd+bwd+Adam), batch {BATCH}/GPU "
                                        f"(global {vae['gb']}), 1x{F_MEL}x{T_MEL} log-mel + {LYR}-d lyrics, z={ZDIM}, "
                                        f"{vae['n_params']} params, dp{world}",

@@ -102,6 +102,31 @@ int vc_convT2d_s2k4_dgrad(const float* dy, const float* W, float* dx, int B, int
 int vc_convT2d_s2k4_wgrad(const float* dy, const float* x, float* dW, int B, int Cin, int H, int Wd, int Cout,
                           void* workspace, size_t workspace_bytes, void* stream);
 
+/* One entry point for every dense-layer op in either precision.  VC_PREC_FP32: the fp32 FFMA kernels above
+ * (reference-precision path).  VC_PREC_BF16_TC: operands rounded to bf16, tcgen05 tensor-core MMAs with fp32
+ * accumulation in tensor memory, fp32 outputs.  Argument meaning per op (in0, in1 -> out):
+ *   LINEAR_FWD  x[B,Cin],  W[Cout,Cin]        -> y[B,Cout]          (H = W = 1; bias, relu used)
+ *   LINEAR_DGRAD dy[B,Cout], W                -> dx[B,Cin]
+ *   LINEAR_WGRAD dy[B,Cout], x[B,Cin]         -> dW[Cout,Cin]
+ *   CONV_FWD    x[B,Cin,H,W], W[Cout,Cin,3,3] -> y[B,Cout,OH,OW]    (bias, relu used)
+ *   CONV_DGRAD  dy, W -> dx[B,Cin,H,W]          CONV_WGRAD  dy, x -> dW[Cout,Cin,3,3]
+ *   CONVT_FWD   x[B,Cin,H,W], W[Cin,Cout,4,4] -> y[B,Cout,2H,2W]    (bias, relu used)
+ *   CONVT_DGRAD dy, W -> dx[B,Cin,H,W]          CONVT_WGRAD dy, x -> dW[Cin,Cout,4,4] */
+#define VC_PREC_FP32 0
+#define VC_PREC_BF16_TC 1
+#define VC_OP_LINEAR_FWD 0
+#define VC_OP_LINEAR_DGRAD 1
+#define VC_OP_LINEAR_WGRAD 2
+#define VC_OP_CONV_FWD 3
+#define VC_OP_CONV_DGRAD 4
+#define VC_OP_CONV_WGRAD 5
+#define VC_OP_CONVT_FWD 6
+#define VC_OP_CONVT_DGRAD 7
+#define VC_OP_CONVT_WGRAD 8
+size_t vc_dense_op_workspace_bytes(int op, int precision, int B, int Cin, int H, int W, int Cout);
+int vc_dense_op(int op, int precision, const float* in0, const float* in1, const float* bias, float* out, int B,
+                int Cin, int H, int W, int Cout, int relu, void* workspace, size_t workspace_bytes, void* stream);
+
 /* ------------------------------------------------------------------------------------------------- Adam
  * torch.optim.Adam defaults (12:233, 19:202, 06:310): one launch over a device-resident table of chunks. */
 typedef struct VcAdamChunk {
@@ -161,7 +186,8 @@ int vc_silhouette_rows(const float* Xs, const float* sqn, int64_t N, int d, cons
                        int64_t row_begin, int64_t row_end, int nsplit, float* cluster_sums, void* stream);
 /* Tensor-core variant (tcgen05, bf16 hi/lo split with fp32 accumulation in TMEM; d <= 128).  First split the sorted,
  * centred rows into two bf16 matrices H, L of shape [N, dp] (dp = d rounded up to a multiple of 64, caller-owned,
- * 128-byte aligned), then run row blocks exactly like vc_silhouette_rows. */
+ * 128-byte aligned), then run row blocks like vc_silhouette_rows, except that cluster_sums holds TWO partial
+ * planes per split: [2*nsplit, row_end-row_begin, k] (pass 2*nsplit to vc_silhouette_finalize). */
 int vc_silhouette_split_bf16(const float* Xs, int64_t N, int d, int dp, void* H, void* L, void* stream);
 int vc_silhouette_rows_tc(const void* H, const void* L, const float* sqn, int64_t N, int dp, const int64_t* off_dev,
                           int k, int64_t row_begin, int64_t row_end, int nsplit, float* cluster_sums, void* stream);

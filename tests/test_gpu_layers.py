@@ -135,3 +135,65 @@ def test_adam_matches_torch():
         ob.step()
     for p, q in zip(pa, pb):
         torch.testing.assert_close(p, q, rtol=2e-6, atol=1e-7)
+
+
+# ------------------------------------------------------------------------------------ bf16 tensor-core path
+@pytest.fixture
+def bf16_mode():
+    from vaeclust import ops
+    ops.set_precision("bf16")
+    yield
+    ops.set_precision("fp32")
+
+
+def _r(t):  # what the tensor-core path sees: operands rounded to bf16
+    return t.bfloat16().float()
+
+
+def _check_bf16(fn_ours, fn_ref, x, w, b):
+    """Forward against the fp32 op evaluated on bf16-rounded operands (tight: only the summation order differs);
+    gradients against fp32 autograd with a bf16-sized tolerance (dy is rounded once more in the backward GEMMs)."""
+    xa, wa, ba = (t.clone().requires_grad_(True) for t in (x, w, b))
+    xb, wb, bb = (t.clone().requires_grad_(True) for t in (x, w, b))
+    ya = fn_ours(xa, wa, ba)
+    with torch.no_grad():
+        yr = fn_ref(_r(x), _r(w), b)
+    torch.testing.assert_close(ya, yr, rtol=2e-4, atol=2e-4)
+    yb = fn_ref(xb, wb, bb)
+    g = torch.randn_like(yb)
+    ya.backward(g)
+    yb.backward(g)
+    for p, q, n in ((xa, xb, "x"), (wa, wb, "w"), (ba, bb, "b")):
+        scale = float(q.grad.abs().max().clamp_min(1e-6))
+        torch.testing.assert_close(p.grad, q.grad, rtol=3e-2, atol=2e-2 * scale, msg=lambda m: f"{n}: {m}")
+
+
+@pytest.mark.parametrize("M,N,K,relu", [(64, 256, 470, True), (17, 16, 256, False), (3, 700, 33, True),
+                                        (64, 256, 8200, True), (64, 4100, 256, True)])
+def test_linear_bf16(M, N, K, relu, bf16_mode):
+    from vaeclust import ops
+    x, w, b = _rand(M, K, seed=1), _rand(N, K, seed=2, scale=K ** -0.5), _rand(N, seed=3)
+    ref = lambda x, w, b: F.relu(F.linear(x, w, b)) if relu else F.linear(x, w, b)
+    _check_bf16(lambda x, w, b: ops.linear(x, w, b, relu), ref, x, w, b)
+
+
+@pytest.mark.parametrize("B,Cin,H,W,Cout,relu", [(2, 1, 16, 22, 32, True), (3, 32, 8, 11, 64, True),
+                                                 (2, 64, 5, 7, 128, False), (1, 3, 9, 323, 8, True)])
+def test_conv2d_s2k3_bf16(B, Cin, H, W, Cout, relu, bf16_mode):
+    from vaeclust import ops
+    x, w, b = _rand(B, Cin, H, W, seed=1), _rand(Cout, Cin, 3, 3, seed=2, scale=(Cin * 9) ** -0.5), _rand(Cout, seed=3)
+    def ref(x, w, b):
+        y = F.conv2d(x, w, b, stride=2, padding=1)
+        return F.relu(y) if relu else y
+    _check_bf16(lambda x, w, b: ops.conv2d_s2k3(x, w, b, relu), ref, x, w, b)
+
+
+@pytest.mark.parametrize("B,Cin,H,W,Cout,relu", [(2, 128, 2, 3, 64, True), (3, 64, 4, 6, 32, True),
+                                                 (2, 32, 8, 12, 1, False), (1, 5, 3, 81, 7, True)])
+def test_convT2d_s2k4_bf16(B, Cin, H, W, Cout, relu, bf16_mode):
+    from vaeclust import ops
+    x, w, b = _rand(B, Cin, H, W, seed=1), _rand(Cin, Cout, 4, 4, seed=2, scale=(Cin * 4) ** -0.5), _rand(Cout, seed=3)
+    def ref(x, w, b):
+        y = F.conv_transpose2d(x, w, b, stride=2, padding=1)
+        return F.relu(y) if relu else y
+    _check_bf16(lambda x, w, b: ops.convT2d_s2k4(x, w, b, relu), ref, x, w, b)

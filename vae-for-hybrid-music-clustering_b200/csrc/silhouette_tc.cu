@@ -2,13 +2,13 @@
 //
 // The N^2 d contraction x_i . x_j runs as bf16 MMAs with fp32 accumulation in tensor memory.  Plain bf16 inputs
 // are not accurate enough for the 1e-5 target, so each fp32 coordinate is split x = hi + lo (two bf16) and
-//   x.y ~= hi.hi + hi.lo + lo.hi           (the dropped lo.lo term is 2^-16 relative)
-// is accumulated by three MMAs per 16-wide k step into the same TMEM tile.  Norms stay fp32.
+//   x.y = hi.hi + hi.lo + lo.hi + lo.lo     (hi + lo carries 16 mantissa bits; every product is exact in fp32)
+// is accumulated by four MMAs per 16-wide k step into the same TMEM tile.  Norms stay fp32.
 //
 // One CTA owns a 128-row block.  Its hi/lo row operands are loaded once; 128-column tiles of the (cluster-sorted)
 // matrix stream through a TMA ring.  Warp roles: warp 0 = TMA producer, warp 1 = MMA issuer (one elected lane),
-// warps 2..5 = epilogue.  Each epilogue thread owns one accumulator lane = one row i: it pulls the 128 dot products
-// of the tile out of TMEM (tcgen05.ld), forms d = sqrt(max(0, |x_i|^2 + |x_j|^2 - 2 x_i.x_j)) and keeps the running
+// warps 2..9 = epilogue.  Each epilogue thread owns one accumulator lane = one row i and half of the tile's
+// columns: it pulls its 64 dot products out of TMEM (tcgen05.ld), forms d = sqrt(max(0, |x_i|^2 + |x_j|^2 - 2 x_i.x_j)) and keeps the running
 // sum for the current cluster in a register -- rows are sorted by cluster, so no bucketing is needed
 // (sklearn:metrics/cluster/_unsupervised.py:184-189 does np.bincount per row instead).  Two TMEM accumulator stages
 // let the MMAs of tile t+1 overlap the epilogue of tile t.
@@ -19,7 +19,8 @@ namespace vc {
 
 constexpr int ST_ROWS = 128;      // rows per CTA (UMMA M)
 constexpr int ST_COLS = 128;      // columns per tile (UMMA N)
-constexpr int ST_THREADS = 192;   // 6 warps
+constexpr int ST_THREADS = 320;   // 10 warps: TMA, MMA, 8 epilogue
+constexpr int ST_EPI = 256;       // epilogue threads (two per accumulator lane, 64 columns each)
 
 // fp32 -> (hi, lo) bf16 split, zero-padded to dp columns (dp % 64 == 0)
 __global__ void split_bf16_kernel(const float* __restrict__ X, int64_t N, int d, int dp, __nv_bfloat16* __restrict__ H,
@@ -75,7 +76,7 @@ silhouette_tc_kernel(const SilTcArgs a, const __grid_constant__ CUtensorMap mapH
     tma::prefetch_map(&mapL);
     tma::mbar_init(a_full, 1);
     for (int s = 0; s < S; ++s) { tma::mbar_init(&b_full[s], 1); tma::mbar_init(&b_empty[s], 1); }
-    for (int s = 0; s < 2; ++s) { tma::mbar_init(&t_full[s], 1); tma::mbar_init(&t_empty[s], 128); }
+    for (int s = 0; s < 2; ++s) { tma::mbar_init(&t_full[s], 1); tma::mbar_init(&t_empty[s], ST_EPI); }
     tma::mbar_fence_init();
   }
   if (warp == 1) tc05::tmem_alloc(tmem_slot, 256);
@@ -143,6 +144,7 @@ silhouette_tc_kernel(const SilTcArgs a, const __grid_constant__ CUtensorMap mapH
               tc05::mma_bf16(tacc, dAH, dBH, kIdesc, accum);
               tc05::mma_bf16(tacc, dAH, dBL, kIdesc, 1);
               tc05::mma_bf16(tacc, dAL, dBH, kIdesc, 1);
+              tc05::mma_bf16(tacc, dAL, dBL, kIdesc, 1);
               accum = 1;
             }
           }
@@ -153,15 +155,16 @@ silhouette_tc_kernel(const SilTcArgs a, const __grid_constant__ CUtensorMap mapH
       }
     }
   } else {
-    // ===================== epilogue: warps 2..5, thread = one row =====================
+    // ===================== epilogue: warps 2..9; thread = one row x one 64-column half of the tile ==========
     const int q = warp & 3;                      // TMEM lane quarter this warp may access
+    const int half = (warp - 2) >> 2;            // which 64 columns of each tile
     const int rl = q * 32 + lane;                // row within the tile
     const int64_t row = r0 + rl;
     const bool row_ok = row < a.row_end;
     const float rn = row_ok ? a.sqn[row] : 0.f;
-    const int e = threadIdx.x - 64;              // 0..127: which column norm this thread stages
+    const int e = threadIdx.x - 64;              // 0..255; the first 128 stage the column norms
     const int64_t nrows = a.row_end - a.row_begin;
-    float* o = a.out + (int64_t)split * nrows * a.k;
+    float* o = a.out + ((int64_t)split * 2 + half) * nrows * a.k;   // the two halves are separate partial planes
     int64_t counter = 0;
     uint32_t it = 0;
     for (int c = 0; c < a.k; ++c) {
@@ -172,34 +175,37 @@ silhouette_tc_kernel(const SilTcArgs a, const __grid_constant__ CUtensorMap mapH
         const int as = it & 1;
         const uint32_t aph = (it >> 1) & 1;
         float* cn = cns + as * ST_COLS;
-        cn[e] = (j0 + e < c1) ? a.sqn[j0 + e] : 0.f;
-        asm volatile("bar.sync 1, 128;" ::: "memory");
+        if (e < ST_COLS) cn[e] = (j0 + e < c1) ? a.sqn[j0 + e] : 0.f;
+        asm volatile("bar.sync 1, 256;" ::: "memory");
         tma::mbar_wait(&t_full[as], aph);
         tc05::fence_after();
         const bool masked = (j0 + ST_COLS > c1) || (j0 < r0 + ST_ROWS && r0 < j0 + ST_COLS);
-        const uint32_t tacc = tmem_base + ((uint32_t)(q * 32) << 16) + as * ST_COLS;
-#pragma unroll 1
-        for (int cb = 0; cb < ST_COLS; cb += 32) {
-          float v[32];
-          tc05::ld_32x32(tacc + cb, v);
-          tc05::ld_wait();
-          if (!masked) {
+        const int cb0 = half * 64;
+        const uint32_t tacc = tmem_base + ((uint32_t)(q * 32) << 16) + as * ST_COLS + cb0;
+        float v[64];
+        tc05::ld_32x32(tacc, v);          // both 32-column chunks in flight before the wait
+        tc05::ld_32x32(tacc + 32, v + 32);
+        tc05::ld_wait();
+        tc05::fence_before();
+        tma::mbar_arrive(&t_empty[as]);   // accumulator stage is free as soon as it sits in registers
+        const float4* cn4 = reinterpret_cast<const float4*>(cn + cb0);
+        if (!masked) {
 #pragma unroll
-            for (int j = 0; j < 32; ++j) {
-              const float d2 = fmaxf(fmaf(-2.f, v[j], rn + cn[cb + j]), 0.f);
-              rsum += fast_sqrt(d2);
-            }
-          } else {
+          for (int j = 0; j < 16; ++j) {
+            const float4 cc = cn4[j];
+            rsum += fast_sqrt(fmaxf(fmaf(-2.f, v[4 * j + 0], rn + cc.x), 0.f));
+            rsum += fast_sqrt(fmaxf(fmaf(-2.f, v[4 * j + 1], rn + cc.y), 0.f));
+            rsum += fast_sqrt(fmaxf(fmaf(-2.f, v[4 * j + 2], rn + cc.z), 0.f));
+            rsum += fast_sqrt(fmaxf(fmaf(-2.f, v[4 * j + 3], rn + cc.w), 0.f));
+          }
+        } else {
 #pragma unroll
-            for (int j = 0; j < 32; ++j) {
-              const int64_t col = j0 + cb + j;
-              const float d2 = fmaxf(fmaf(-2.f, v[j], rn + cn[cb + j]), 0.f);
-              rsum += (col < c1 && col != row) ? fast_sqrt(d2) : 0.f;
-            }
+          for (int j = 0; j < 64; ++j) {
+            const int64_t col = j0 + cb0 + j;
+            const float d2 = fmaxf(fmaf(-2.f, v[j], rn + cn[cb0 + j]), 0.f);
+            rsum += (col < c1 && col != row) ? fast_sqrt(d2) : 0.f;
           }
         }
-        tc05::fence_before();
-        tma::mbar_arrive(&t_empty[as]);
         ++it;
       }
       if (row_ok) o[(row - a.row_begin) * a.k + c] = rsum;

@@ -393,15 +393,18 @@ def _sil_block(Xs, sqn, off, k: int, r0: int, r1: int, lab_sorted, counts, s_sor
     tiles = (nrows + 127) // 128
     sms = lib().size("vc_sm_count")
     nsplit = int(max(1, min(32, (2 * sms) // max(tiles, 1))))
-    sums = torch.empty((nsplit, nrows, k), dtype=torch.float32, device=Xs.device)
     dp = (d + 63) // 64 * 64
     if SILHOUETTE_PRECISION == "tc" and dp <= 128:
+        # the tensor-core kernel writes two partial planes per split (one per 64-column half of a tile)
+        sums = torch.empty((2 * nsplit, nrows, k), dtype=torch.float32, device=Xs.device)
         H = torch.empty((N, dp), dtype=torch.bfloat16, device=Xs.device)
         L = torch.empty((N, dp), dtype=torch.bfloat16, device=Xs.device)
         lib().call("vc_silhouette_split_bf16", ptr(Xs), N, d, dp, ptr(H), ptr(L), stream_ptr())
         lib().call("vc_silhouette_rows_tc", ptr(H), ptr(L), ptr(sqn), N, dp, ptr(off), k, r0, r1, nsplit, ptr(sums),
                    stream_ptr())
+        nsplit *= 2
     else:
+        sums = torch.empty((nsplit, nrows, k), dtype=torch.float32, device=Xs.device)
         lib().call("vc_silhouette_rows", ptr(Xs), ptr(sqn), N, d, ptr(off), k, r0, r1, nsplit, ptr(sums),
                    stream_ptr())
     ws = _workspace(lib().size("vc_silhouette_finalize_workspace_bytes"), Xs.device)

@@ -33,31 +33,66 @@ def _f32(t: torch.Tensor, name: str) -> torch.Tensor:
 
 
 # ----------------------------------------------------------------------------------------------- dense layers
-class LinearFn(torch.autograd.Function):
-    """y = act(x W^T + b): nn.Linear(+ReLU) of 12:98-103,114-117,129-132,159-164; 19:79-95; 06:149-157."""
+PRECISION = "fp32"  # "fp32": FFMA reference-precision kernels; "bf16": tcgen05 tensor cores (bf16 in, fp32 accumulate)
+_PREC = {"fp32": 0, "bf16": 1}
+_OPS = {"linear": (0, 1, 2), "conv": (3, 4, 5), "convT": (6, 7, 8)}  # (fwd, dgrad, wgrad) ids of vc_dense_op
+
+
+def set_precision(p: str) -> None:
+    """Select the arithmetic of the dense layers for ops created from now on."""
+    global PRECISION
+    if p not in _PREC:
+        raise VaeclustError(f"precision must be one of {sorted(_PREC)}")
+    PRECISION = p
+
+
+def _dense(op: int, prec: int, in0, in1, bias, out, B, Cin, H, W, Cout, relu) -> None:
+    nb = lib().size("vc_dense_op_workspace_bytes", op, prec, B, Cin, H, W, Cout)
+    ws = _workspace(nb, out.device)
+    lib().call("vc_dense_op", op, prec, ptr(in0), ptr(in1), ptr(bias), ptr(out), B, Cin, H, W, Cout, int(relu), ptr(ws),
+               ws.numel(), stream_ptr())
+
+
+class _DenseFn(torch.autograd.Function):
+    """Shared forward/backward of Linear, Conv2d(k3,s2,p1) and ConvTranspose2d(k4,s2,p1) (+bias, +ReLU)."""
 
     @staticmethod
-    def forward(ctx, x, weight, bias, relu: bool):
-        x, weight = _f32(x, "linear.x"), _f32(weight, "linear.weight")
-        bias = _f32(bias, "linear.bias") if bias is not None else None
-        M, K = x.shape
-        N = weight.shape[0]
-        if weight.shape[1] != K:
-            raise VaeclustError(f"linear: x is [*, {K}] but weight is {tuple(weight.shape)}")
-        y = torch.empty((M, N), dtype=torch.float32, device=x.device)
-        ws = _workspace(lib().size("vc_linear_workspace_bytes", M, N, K), x.device)
-        lib().call("vc_linear_fwd", ptr(x), ptr(weight), ptr(bias), ptr(y), M, N, K, int(relu), ptr(ws), ws.numel(),
-                   stream_ptr())
-        ctx.relu, ctx.has_bias = bool(relu), bias is not None
+    def forward(ctx, kind: str, x, weight, bias, relu: bool):
+        x, weight = _f32(x, kind + ".x"), _f32(weight, kind + ".weight")
+        bias = _f32(bias, kind + ".bias") if bias is not None else None
+        prec = _PREC[PRECISION]
+        if kind == "linear":
+            B, Cin = x.shape
+            H = W = 1
+            Cout = weight.shape[0]
+            if weight.shape[1] != Cin:
+                raise VaeclustError(f"linear: x is [*, {Cin}] but weight is {tuple(weight.shape)}")
+            yshape = (B, Cout)
+        elif kind == "conv":
+            B, Cin, H, W = x.shape
+            Cout = weight.shape[0]
+            if tuple(weight.shape[1:]) != (Cin, 3, 3):
+                raise VaeclustError(f"conv2d_s2k3: weight {tuple(weight.shape)} does not match Cin={Cin}, k=3")
+            yshape = (B, Cout, (H - 1) // 2 + 1, (W - 1) // 2 + 1)
+        else:
+            B, Cin, H, W = x.shape
+            Cout = weight.shape[1]
+            if weight.shape[0] != Cin or tuple(weight.shape[2:]) != (4, 4):
+                raise VaeclustError(f"convT2d_s2k4: weight {tuple(weight.shape)} does not match Cin={Cin}, k=4")
+            yshape = (B, Cout, 2 * H, 2 * W)
+        y = torch.empty(yshape, dtype=torch.float32, device=x.device)
+        _dense(_OPS[kind][0], prec, x, weight, bias, y, B, Cin, H, W, Cout, relu)
+        ctx.kind, ctx.prec, ctx.relu, ctx.has_bias = kind, prec, bool(relu), bias is not None
+        ctx.dims = (B, Cin, H, W, Cout)
         ctx.save_for_backward(x, weight, y if relu else None)
         return y
 
     @staticmethod
     def backward(ctx, dy):
         x, weight, y = ctx.saved_tensors
-        dy = _f32(dy, "linear.dy")
-        M, K = x.shape
-        N = weight.shape[0]
+        dy = _f32(dy, ctx.kind + ".dy")
+        B, Cin, H, W, Cout = ctx.dims
+        _, op_d, op_w = _OPS[ctx.kind]
         s = stream_ptr()
         if ctx.relu:
             g = torch.empty_like(dy)
@@ -65,120 +100,32 @@ class LinearFn(torch.autograd.Function):
         else:
             g = dy
         dx = dw = db = None
-        if ctx.needs_input_grad[0]:
-            dx = torch.empty_like(x)
-            ws = _workspace(lib().size("vc_linear_workspace_bytes", M, N, K), x.device)
-            lib().call("vc_linear_dgrad", ptr(g), ptr(weight), ptr(dx), M, N, K, ptr(ws), ws.numel(), s)
         if ctx.needs_input_grad[1]:
+            dx = torch.empty_like(x)
+            _dense(op_d, ctx.prec, g, weight, None, dx, B, Cin, H, W, Cout, False)
+        if ctx.needs_input_grad[2]:
             dw = torch.empty_like(weight)
-            lib().call("vc_linear_wgrad", ptr(g), ptr(x), ptr(dw), M, N, K, 0, s)
-        if ctx.has_bias and ctx.needs_input_grad[2]:
-            db = torch.empty(N, dtype=torch.float32, device=x.device)
-            lib().call("vc_bias_grad", ptr(g), M, N, 1, ptr(db), 0, s)
-        return dx, dw, db, None
+            _dense(op_w, ctx.prec, g, x, None, dw, B, Cin, H, W, Cout, False)
+        if ctx.has_bias and ctx.needs_input_grad[3]:
+            db = torch.empty(Cout, dtype=torch.float32, device=x.device)
+            inner = 1 if ctx.kind == "linear" else g.shape[2] * g.shape[3]
+            lib().call("vc_bias_grad", ptr(g), B, Cout, inner, ptr(db), 0, s)
+        return None, dx, dw, db, None
 
 
 def linear(x, weight, bias=None, relu: bool = False):
-    return LinearFn.apply(x, weight, bias, relu)
-
-
-class Conv2dS2K3Fn(torch.autograd.Function):
-    """nn.Conv2d(Cin, Cout, 3, stride=2, padding=1) (+ReLU), 12:87-89."""
-
-    @staticmethod
-    def forward(ctx, x, weight, bias, relu: bool):
-        x, weight = _f32(x, "conv.x"), _f32(weight, "conv.weight")
-        bias = _f32(bias, "conv.bias") if bias is not None else None
-        B, Cin, H, W = x.shape
-        Cout = weight.shape[0]
-        if tuple(weight.shape[1:]) != (Cin, 3, 3):
-            raise VaeclustError(f"conv2d_s2k3: weight {tuple(weight.shape)} does not match Cin={Cin}, k=3")
-        OH, OW = (H - 1) // 2 + 1, (W - 1) // 2 + 1
-        y = torch.empty((B, Cout, OH, OW), dtype=torch.float32, device=x.device)
-        lib().call("vc_conv2d_s2k3_fwd", ptr(x), ptr(weight), ptr(bias), ptr(y), B, Cin, H, W, Cout, int(relu),
-                   stream_ptr())
-        ctx.relu, ctx.has_bias = bool(relu), bias is not None
-        ctx.save_for_backward(x, weight, y if relu else None)
-        return y
-
-    @staticmethod
-    def backward(ctx, dy):
-        x, weight, y = ctx.saved_tensors
-        dy = _f32(dy, "conv.dy")
-        B, Cin, H, W = x.shape
-        Cout = weight.shape[0]
-        s = stream_ptr()
-        if ctx.relu:
-            g = torch.empty_like(dy)
-            lib().call("vc_relu_bwd", ptr(dy), ptr(y), ptr(g), dy.numel(), s)
-        else:
-            g = dy
-        dx = dw = db = None
-        if ctx.needs_input_grad[0]:
-            dx = torch.empty_like(x)
-            lib().call("vc_conv2d_s2k3_dgrad", ptr(g), ptr(weight), ptr(dx), B, Cin, H, W, Cout, s)
-        if ctx.needs_input_grad[1]:
-            dw = torch.empty_like(weight)
-            nb = lib().size("vc_conv_wgrad_workspace_bytes", Cout, Cin, 3)
-            ws = _workspace(nb, x.device)
-            lib().call("vc_conv2d_s2k3_wgrad", ptr(g), ptr(x), ptr(dw), B, Cin, H, W, Cout, ptr(ws), ws.numel(), s)
-        if ctx.has_bias and ctx.needs_input_grad[2]:
-            db = torch.empty(Cout, dtype=torch.float32, device=x.device)
-            lib().call("vc_bias_grad", ptr(g), B, Cout, g.shape[2] * g.shape[3], ptr(db), 0, s)
-        return dx, dw, db, None
+    """y = act(x W^T + b): nn.Linear(+ReLU) of 12:98-103,114-117,129-132,159-164; 19:79-95; 06:149-157."""
+    return _DenseFn.apply("linear", x, weight, bias, relu)
 
 
 def conv2d_s2k3(x, weight, bias=None, relu: bool = False):
-    return Conv2dS2K3Fn.apply(x, weight, bias, relu)
-
-
-class ConvT2dS2K4Fn(torch.autograd.Function):
-    """nn.ConvTranspose2d(Cin, Cout, 4, stride=2, padding=1) (+ReLU), 12:135-137.  weight is [Cin, Cout, 4, 4]."""
-
-    @staticmethod
-    def forward(ctx, x, weight, bias, relu: bool):
-        x, weight = _f32(x, "convT.x"), _f32(weight, "convT.weight")
-        bias = _f32(bias, "convT.bias") if bias is not None else None
-        B, Cin, H, W = x.shape
-        Cout = weight.shape[1]
-        if weight.shape[0] != Cin or tuple(weight.shape[2:]) != (4, 4):
-            raise VaeclustError(f"convT2d_s2k4: weight {tuple(weight.shape)} does not match Cin={Cin}, k=4")
-        y = torch.empty((B, Cout, 2 * H, 2 * W), dtype=torch.float32, device=x.device)
-        lib().call("vc_convT2d_s2k4_fwd", ptr(x), ptr(weight), ptr(bias), ptr(y), B, Cin, H, W, Cout, int(relu),
-                   stream_ptr())
-        ctx.relu, ctx.has_bias = bool(relu), bias is not None
-        ctx.save_for_backward(x, weight, y if relu else None)
-        return y
-
-    @staticmethod
-    def backward(ctx, dy):
-        x, weight, y = ctx.saved_tensors
-        dy = _f32(dy, "convT.dy")
-        B, Cin, H, W = x.shape
-        Cout = weight.shape[1]
-        s = stream_ptr()
-        if ctx.relu:
-            g = torch.empty_like(dy)
-            lib().call("vc_relu_bwd", ptr(dy), ptr(y), ptr(g), dy.numel(), s)
-        else:
-            g = dy
-        dx = dw = db = None
-        if ctx.needs_input_grad[0]:
-            dx = torch.empty_like(x)
-            lib().call("vc_convT2d_s2k4_dgrad", ptr(g), ptr(weight), ptr(dx), B, Cin, H, W, Cout, s)
-        if ctx.needs_input_grad[1]:
-            dw = torch.empty_like(weight)
-            nb = lib().size("vc_conv_wgrad_workspace_bytes", Cout, Cin, 4)
-            ws = _workspace(nb, x.device)
-            lib().call("vc_convT2d_s2k4_wgrad", ptr(g), ptr(x), ptr(dw), B, Cin, H, W, Cout, ptr(ws), ws.numel(), s)
-        if ctx.has_bias and ctx.needs_input_grad[2]:
-            db = torch.empty(Cout, dtype=torch.float32, device=x.device)
-            lib().call("vc_bias_grad", ptr(g), B, Cout, g.shape[2] * g.shape[3], ptr(db), 0, s)
-        return dx, dw, db, None
+    """nn.Conv2d(Cin, Cout, 3, stride=2, padding=1) (+ReLU), 12:87-89."""
+    return _DenseFn.apply("conv", x, weight, bias, relu)
 
 
 def convT2d_s2k4(x, weight, bias=None, relu: bool = False):
-    return ConvT2dS2K4Fn.apply(x, weight, bias, relu)
+    """nn.ConvTranspose2d(Cin, Cout, 4, stride=2, padding=1) (+ReLU), 12:135-137.  weight is [Cin, Cout, 4, 4]."""
+    return _DenseFn.apply("convT", x, weight, bias, relu)
 
 
 class CatGateFn(torch.autograd.Function):
@@ -363,5 +310,5 @@ def vae_loss(xhat, x, kl_rows_t, beta: float, mode: int, z_dim: int, unit_grad: 
     return VAELossFn.apply(xhat, x, kl_rows_t, beta, mode, z_dim, unit_grad)
 
 
-__all__ = ["linear", "conv2d_s2k3", "convT2d_s2k4", "cat_gate", "reparam_kl", "kl_rows", "sq_err_sum", "mse_loss", "vae_loss",
+__all__ = ["set_precision", "linear", "conv2d_s2k3", "convT2d_s2k4", "cat_gate", "reparam_kl", "kl_rows", "sq_err_sum", "mse_loss", "vae_loss",
            "VC_LOSS_MEAN_MEAN", "VC_LOSS_SUM_MEAN"]
