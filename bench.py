@@ -364,6 +364,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--precision", default="bf16", choices=["bf16", "fp32"],
                     help="dense-layer arithmetic: bf16 = tcgen05 tensor cores (fp32 accumulate), fp32 = FFMA parity mode")
+    ap.add_argument("--dump-ops", default=None, help="write the per-entry-point event timings of the timed region here")
     ap.add_argument("--skip-extra", action="store_true", help="VAE step only (no KMeans / silhouette sub-benchmarks)")
     ap.add_argument("--skip-cpu", action="store_true", help="do not time the CPU baseline")
     args = ap.parse_args()
@@ -402,6 +403,13 @@ def main():
     if rank == 0:
         clips = vae["gb"] * args.steps
         roof = roofline_from_summary(vae["summ"], args.steps, vae["n_params"], pk)
+        if args.dump_ops:
+            rows = sorted(((t / args.steps, c / args.steps, n_, list(sig)) for (n_, sig), (c, t) in vae["summ"].items()),
+                          reverse=True)
+            with open(args.dump_ops, "w") as f:
+                for t, c, n_, sig in rows:
+                    fl = flops_of(n_, sig)
+                    f.write(f"{t:9.4f} ms/step  x{c:4.1f}  {n_:28s} {sig}  {fl * c / (t * 1e-3) / 1e12 if t > 0 else 0:8.2f} TFLOP/s\n")
         line = {"metric": METRIC, "value": clips / (vae["ms"] * 1e-3), "unit": UNIT, "n_gpus": world,
                 "steps": args.steps, "warmup": args.warmup, "ms_per_step": vae["ms"] / args.steps,
                 "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16" if args.precision == "bf16" else "f32", "data": "synthetic",

@@ -75,7 +75,9 @@ int vc_linear_dgrad(const float* dy, const float* W, float* dx, int M, int N, in
 int vc_linear_wgrad(const float* dy, const float* x, float* dW, int M, int N, int K, int accumulate,
                     void* stream);
 /* db[c] (+)= sum over outer,inner of dy[outer, C, inner]  (bias gradient of Linear: inner=1; Conv: inner=H*W) */
-int vc_bias_grad(const float* dy, int64_t outer, int C, int64_t inner, float* db, int accumulate, void* stream);
+size_t vc_bias_grad_workspace_bytes(int C);
+int vc_bias_grad(const float* dy, int64_t outer, int C, int64_t inner, float* db, int accumulate, void* workspace,
+                 size_t workspace_bytes, void* stream);
 /* dx = dy * (y > 0) */
 int vc_relu_bwd(const float* dy, const float* y, float* dx, int64_t n, void* stream);
 /* out[b,:] = [a[b,0:na], l[b,0:nl]*gate[b], gate[b] if append_gate]  -- `l*m` and torch.cat of 12:178-180 and

@@ -159,7 +159,7 @@ def _check_bf16(fn_ours, fn_ref, x, w, b):
     with torch.no_grad():
         yr = fn_ref(_r(x), _r(w), b)
     torch.testing.assert_close(ya, yr, rtol=2e-4, atol=2e-4)
-    yb = fn_ref(xb, wb, bb)
+    yb = fn_ref(_r(xb), _r(wb), bb)   # same rounded operands -> same ReLU mask (rounding is straight-through)
     g = torch.randn_like(yb)
     ya.backward(g)
     yb.backward(g)

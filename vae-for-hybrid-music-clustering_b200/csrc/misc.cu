@@ -41,24 +41,45 @@ __global__ void relu_bwd_vec_kernel(const float4* __restrict__ dy, const float4*
   }
 }
 
-// db[c] = sum_{o,i} dy[o,C,inner]; one block per channel, fixed-order (deterministic) reduction.
-__global__ void bias_grad_kernel(const float* __restrict__ dy, int64_t outer, int C, int64_t inner,
-                                 float* __restrict__ db, int accumulate) {
+// db[c] = sum_{o,i} dy[o,C,inner].  Two deterministic stages: block (c, s) sums slice s of the (outer x inner) range of
+// channel c into part[c*S + s] (double), then one thread per channel folds the S partials in order.
+constexpr int kBiasSplits = 64;
+
+__global__ void __launch_bounds__(256)
+bias_grad_stage1(const float* __restrict__ dy, int64_t outer, int C, int64_t inner, int S, double* __restrict__ part) {
   __shared__ double scratch[32];
-  const int c = blockIdx.x;
+  const int c = blockIdx.x, sp = blockIdx.y;
   double acc = 0.0;
   if (inner == 1) {
-    for (int64_t o = threadIdx.x; o < outer; o += blockDim.x) acc += (double)dy[o * C + c];
+    for (int64_t o = sp * blockDim.x + threadIdx.x; o < outer; o += (int64_t)S * blockDim.x) acc += (double)dy[o * C + c];
   } else {
-    for (int64_t o = 0; o < outer; ++o) {
-      const float* p = dy + (o * C + c) * inner;
-      float part = 0.f;
-      for (int64_t i = threadIdx.x; i < inner; i += blockDim.x) part += p[i];
-      acc += (double)part;
+    // slices of the flattened (outer, inner/4) index space, float4 loads when rows are 16-byte aligned
+    const bool vec = (inner % 4 == 0) && ((reinterpret_cast<uintptr_t>(dy) & 15) == 0);
+    if (vec) {
+      const int64_t i4 = inner / 4, total = outer * i4;
+      for (int64_t e = sp * (int64_t)blockDim.x + threadIdx.x; e < total; e += (int64_t)S * blockDim.x) {
+        const int64_t o = e / i4, i = e % i4;
+        const float4 v = *reinterpret_cast<const float4*>(dy + (o * C + c) * inner + 4 * i);
+        acc += (double)((v.x + v.y) + (v.z + v.w));
+      }
+    } else {
+      const int64_t total = outer * inner;
+      for (int64_t e = sp * (int64_t)blockDim.x + threadIdx.x; e < total; e += (int64_t)S * blockDim.x) {
+        const int64_t o = e / inner, i = e % inner;
+        acc += (double)dy[(o * C + c) * inner + i];
+      }
     }
   }
   acc = block_sum<double>(acc, scratch);
-  if (threadIdx.x == 0) db[c] = (accumulate ? db[c] : 0.f) + (float)acc;
+  if (threadIdx.x == 0) part[(int64_t)c * S + sp] = acc;
+}
+
+__global__ void bias_grad_stage2(const double* __restrict__ part, int C, int S, float* __restrict__ db, int accumulate) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  double acc = 0.0;
+  for (int s = 0; s < S; ++s) acc += part[(int64_t)c * S + s];
+  db[c] = (accumulate ? db[c] : 0.f) + (float)acc;
 }
 
 __global__ void cat_gate_fwd_kernel(const float* __restrict__ a, int na, const float* __restrict__ l, int nl,
@@ -241,10 +262,19 @@ extern "C" int vc_relu_bwd(const float* dy, const float* y, float* dx, int64_t n
   return VC_OK;
 }
 
+extern "C" size_t vc_bias_grad_workspace_bytes(int C) { return sizeof(double) * (size_t)kBiasSplits * (C > 0 ? C : 1); }
+
 extern "C" int vc_bias_grad(const float* dy, int64_t outer, int C, int64_t inner, float* db, int accumulate,
-                            void* stream) {
+                            void* workspace, size_t workspace_bytes, void* stream) {
   VC_REQUIRE(dy && db && outer > 0 && C > 0 && inner > 0, VC_ERR_BAD_ARG, "vc_bias_grad: bad arguments");
-  bias_grad_kernel<<<C, 256, 0, as_stream(stream)>>>(dy, outer, C, inner, db, accumulate);
+  VC_REQUIRE(workspace && workspace_bytes >= vc_bias_grad_workspace_bytes(C), VC_ERR_WORKSPACE,
+             "vc_bias_grad: workspace too small");
+  int S = kBiasSplits;
+  while (S > 1 && outer * inner / S < 1024) S >>= 1;
+  double* part = static_cast<double*>(workspace);
+  bias_grad_stage1<<<dim3(C, S), 256, 0, as_stream(stream)>>>(dy, outer, C, inner, S, part);
+  VC_LAUNCH_CHECK();
+  bias_grad_stage2<<<(C + 127) / 128, 128, 0, as_stream(stream)>>>(part, C, S, db, accumulate);
   VC_LAUNCH_CHECK();
   return VC_OK;
 }

@@ -109,7 +109,8 @@ class _DenseFn(torch.autograd.Function):
         if ctx.has_bias and ctx.needs_input_grad[3]:
             db = torch.empty(Cout, dtype=torch.float32, device=x.device)
             inner = 1 if ctx.kind == "linear" else g.shape[2] * g.shape[3]
-            lib().call("vc_bias_grad", ptr(g), B, Cout, inner, ptr(db), 0, s)
+            ws = _workspace(lib().size("vc_bias_grad_workspace_bytes", Cout), x.device)
+            lib().call("vc_bias_grad", ptr(g), B, Cout, inner, ptr(db), 0, ptr(ws), ws.numel(), s)
         return None, dx, dw, db, None
 
 
