@@ -31,6 +31,21 @@ __global__ void silhouette_gather_kernel(const float* __restrict__ X, int64_t N,
   }
 }
 
+// Same close-pair rule as the tensor-core kernel (silhouette_tc.cu): below 1/256 of |x|^2 + |y|^2 the norm formula
+// has cancelled most of its bits, so the pair is recomputed as sum (x_k - y_k)^2 (duplicates come out exactly 0).
+constexpr float kCloseRatioF = 1.f / 256.f;
+__device__ __noinline__ float exact_dist_f32(const float* __restrict__ Xs, int d, int64_t i, int64_t j) {
+  const float4* a = reinterpret_cast<const float4*>(Xs + i * d);
+  const float4* b = reinterpret_cast<const float4*>(Xs + j * d);
+  float acc = 0.f;
+  for (int t = 0; t < (d >> 2); ++t) {
+    const float4 x = a[t], y = b[t];
+    const float d0 = x.x - y.x, d1 = x.y - y.y, d2 = x.z - y.z, d3 = x.w - y.w;
+    acc = fmaf(d0, d0, acc); acc = fmaf(d1, d1, acc); acc = fmaf(d2, d2, acc); acc = fmaf(d3, d3, acc);
+  }
+  return sqrtf(acc);
+}
+
 __global__ void __launch_bounds__(256)
 silhouette_rows_kernel(const float* __restrict__ Xs, const float* __restrict__ sqn, int64_t N, int d,
                        const int64_t* __restrict__ off, int k, int64_t row_begin, int64_t row_end, int nsplit,
@@ -108,10 +123,13 @@ silhouette_rows_kernel(const float* __restrict__ Xs, const float* __restrict__ s
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
           const int64_t col = j0 + tx + 16 * j;
-          float d2 = fmaf(-2.f, acc[i][j], rn[i] + cn[j]);
+          const float sn = rn[i] + cn[j];
+          float d2 = fmaf(-2.f, acc[i][j], sn);
+          const bool close = d2 < kCloseRatioF * sn;
           d2 = fmaxf(d2, 0.f);
           float dist = d2 > 0.f ? d2 * rsqrtf(d2) : 0.f;
-          if (!cvalid[j] || col == r) dist = 0.f;
+          if (!cvalid[j] || col == r || r >= row_end) dist = 0.f;
+          else if (close) dist = exact_dist_f32(Xs, d, r, col);
           rsum[i] += dist;
         }
       }

@@ -22,26 +22,53 @@ constexpr int ST_COLS = 128;      // columns per tile (UMMA N)
 constexpr int ST_THREADS = 320;   // 10 warps: TMA, MMA, 8 epilogue
 constexpr int ST_EPI = 256;       // epilogue threads (two per accumulator lane, 64 columns each)
 
-// fp32 -> (hi, lo) bf16 split, zero-padded to dp columns (dp % 64 == 0)
+// fp32 -> (hi, lo) bf16 split, zero-padded to dp columns (dp % 64 == 0); one warp per row.  Also emits the squared
+// norm of the SPLIT row (hi + lo, 16 mantissa bits), so |x|^2 + |y|^2 - 2 x.y is formed from one consistent
+// representation and the cancellation error for close pairs is fp32 rounding only.
 __global__ void split_bf16_kernel(const float* __restrict__ X, int64_t N, int d, int dp, __nv_bfloat16* __restrict__ H,
-                                  __nv_bfloat16* __restrict__ L) {
-  const int64_t n = N * dp;
-  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
-    const int c = (int)(i % dp);
-    const int64_t r = i / dp;
-    const float v = c < d ? X[r * d + c] : 0.f;
-    const __nv_bfloat16 h = __float2bfloat16_rn(v);
-    H[i] = h;
-    L[i] = __float2bfloat16_rn(v - __bfloat162float(h));
+                                  __nv_bfloat16* __restrict__ L, float* __restrict__ sqn) {
+  const int lane = threadIdx.x & 31;
+  const int64_t w = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int64_t nw = ((int64_t)gridDim.x * blockDim.x) >> 5;
+  for (int64_t r = w; r < N; r += nw) {
+    float s = 0.f;
+    for (int c = lane; c < dp; c += 32) {
+      const float v = c < d ? X[r * d + c] : 0.f;
+      const __nv_bfloat16 h = __float2bfloat16_rn(v);
+      const __nv_bfloat16 l = __float2bfloat16_rn(v - __bfloat162float(h));
+      H[r * dp + c] = h;
+      L[r * dp + c] = l;
+      const float vs = __bfloat162float(h) + __bfloat162float(l);
+      s = fmaf(vs, vs, s);
+    }
+    s = warp_sum(s);
+    if (sqn && lane == 0) sqn[r] = s;
   }
 }
 
 struct SilTcArgs {
   const float* sqn; const int64_t* off; int k; int64_t N, row_begin, row_end; int nsplit; float* out;
+  const float* Xs; int d;   // fp32 rows for the exact recomputation of close pairs
   int panels;   // dp / 64
   int stages;   // depth of the column-tile ring
 };
+
+// Pairs whose squared distance is below kCloseRatio * (|x|^2 + |y|^2) have lost most of their bits to cancellation in
+// the norm formula (duplicates and near-duplicates): they are recomputed as sum (x_k - y_k)^2 from the fp32 rows,
+// which is what sklearn's float64 upcast achieves (sklearn:metrics/pairwise.py:567-638).
+constexpr float kCloseRatio = 1.f / 256.f;
+
+__device__ __noinline__ float exact_dist(const float* __restrict__ Xs, int d, int64_t i, int64_t j) {
+  const float4* a = reinterpret_cast<const float4*>(Xs + i * d);
+  const float4* b = reinterpret_cast<const float4*>(Xs + j * d);
+  float acc = 0.f;
+  for (int t = 0; t < (d >> 2); ++t) {
+    const float4 x = a[t], y = b[t];
+    const float d0 = x.x - y.x, d1 = x.y - y.y, d2 = x.z - y.z, d3 = x.w - y.w;
+    acc = fmaf(d0, d0, acc); acc = fmaf(d1, d1, acc); acc = fmaf(d2, d2, acc); acc = fmaf(d3, d3, acc);
+  }
+  return sqrtf(acc);
+}
 
 __device__ __forceinline__ float fast_sqrt(float x) {
   float y;
@@ -190,20 +217,39 @@ silhouette_tc_kernel(const SilTcArgs a, const __grid_constant__ CUtensorMap mapH
         tma::mbar_arrive(&t_empty[as]);   // accumulator stage is free as soon as it sits in registers
         const float4* cn4 = reinterpret_cast<const float4*>(cn + cb0);
         if (!masked) {
+          float tmin = 1.f;
 #pragma unroll
           for (int j = 0; j < 16; ++j) {
             const float4 cc = cn4[j];
-            rsum += fast_sqrt(fmaxf(fmaf(-2.f, v[4 * j + 0], rn + cc.x), 0.f));
-            rsum += fast_sqrt(fmaxf(fmaf(-2.f, v[4 * j + 1], rn + cc.y), 0.f));
-            rsum += fast_sqrt(fmaxf(fmaf(-2.f, v[4 * j + 2], rn + cc.z), 0.f));
-            rsum += fast_sqrt(fmaxf(fmaf(-2.f, v[4 * j + 3], rn + cc.w), 0.f));
+            const float s0 = rn + cc.x, s1 = rn + cc.y, s2 = rn + cc.z, s3 = rn + cc.w;
+            const float e0 = fmaf(-2.f, v[4 * j + 0], s0), e1 = fmaf(-2.f, v[4 * j + 1], s1);
+            const float e2 = fmaf(-2.f, v[4 * j + 2], s2), e3 = fmaf(-2.f, v[4 * j + 3], s3);
+            tmin = fminf(tmin, fminf(fminf(fmaf(-kCloseRatio, s0, e0), fmaf(-kCloseRatio, s1, e1)),
+                                     fminf(fmaf(-kCloseRatio, s2, e2), fmaf(-kCloseRatio, s3, e3))));
+            rsum += fast_sqrt(fmaxf(e0, 0.f));
+            rsum += fast_sqrt(fmaxf(e1, 0.f));
+            rsum += fast_sqrt(fmaxf(e2, 0.f));
+            rsum += fast_sqrt(fmaxf(e3, 0.f));
+          }
+          if (tmin < 0.f && row_ok) {  // rare: some pair of this chunk is close -> replace its term by the exact one
+#pragma unroll
+            for (int j = 0; j < 64; ++j) {
+              const float s = rn + cn[cb0 + j];
+              const float d2 = fmaf(-2.f, v[j], s);
+              if (d2 < kCloseRatio * s)
+                rsum += exact_dist(a.Xs, a.d, row, j0 + cb0 + j) - fast_sqrt(fmaxf(d2, 0.f));
+            }
           }
         } else {
 #pragma unroll
           for (int j = 0; j < 64; ++j) {
             const int64_t col = j0 + cb0 + j;
-            const float d2 = fmaxf(fmaf(-2.f, v[j], rn + cn[cb0 + j]), 0.f);
-            rsum += (col < c1 && col != row) ? fast_sqrt(d2) : 0.f;
+            const float s = rn + cn[cb0 + j];
+            const float d2 = fmaf(-2.f, v[j], s);
+            float dist = fast_sqrt(fmaxf(d2, 0.f));
+            const bool live = col < c1 && col != row && row_ok;
+            if (live && d2 < kCloseRatio * s) dist = exact_dist(a.Xs, a.d, row, col);
+            rsum += live ? dist : 0.f;
           }
         }
         ++it;
@@ -224,22 +270,25 @@ silhouette_tc_kernel(const SilTcArgs a, const __grid_constant__ CUtensorMap mapH
 
 using namespace vc;
 
-extern "C" int vc_silhouette_split_bf16(const float* Xs, int64_t N, int d, int dp, void* H, void* L, void* stream) {
+extern "C" int vc_silhouette_split_bf16(const float* Xs, int64_t N, int d, int dp, void* H, void* L, float* sqn_split,
+                                        void* stream) {
   VC_REQUIRE(Xs && H && L && N > 0 && d > 0 && dp >= d && dp % 64 == 0, VC_ERR_BAD_ARG,
              "vc_silhouette_split_bf16: bad arguments (d=%d dp=%d)", d, dp);
-  int64_t blocks = (N * dp + 255) / 256;
+  int64_t blocks = (N + 7) / 8;
   if (blocks > (int64_t)sm_count() * 16) blocks = (int64_t)sm_count() * 16;
   split_bf16_kernel<<<(int)blocks, 256, 0, as_stream(stream)>>>(Xs, N, d, dp, static_cast<__nv_bfloat16*>(H),
-                                                               static_cast<__nv_bfloat16*>(L));
+                                                               static_cast<__nv_bfloat16*>(L), sqn_split);
   VC_LAUNCH_CHECK();
   return VC_OK;
 }
 
-extern "C" int vc_silhouette_rows_tc(const void* H, const void* L, const float* sqn, int64_t N, int dp,
+extern "C" int vc_silhouette_rows_tc(const void* H, const void* L, const float* Xs, int d, const float* sqn, int64_t N, int dp,
                                      const int64_t* off_dev, int k, int64_t row_begin, int64_t row_end, int nsplit,
                                      float* cluster_sums, void* stream) {
-  VC_REQUIRE(H && L && sqn && off_dev && cluster_sums && N > 0 && k > 0, VC_ERR_BAD_ARG,
+  VC_REQUIRE(H && L && Xs && sqn && off_dev && cluster_sums && N > 0 && k > 0, VC_ERR_BAD_ARG,
              "vc_silhouette_rows_tc: bad arguments");
+  VC_REQUIRE(d > 0 && d <= dp && d % 4 == 0 && (reinterpret_cast<uintptr_t>(Xs) & 15) == 0, VC_ERR_UNSUPPORTED,
+             "vc_silhouette_rows_tc: fp32 rows need d %% 4 == 0 and 16-byte alignment (d=%d)", d);
   VC_REQUIRE(dp % 64 == 0 && dp >= 64 && dp <= 128, VC_ERR_UNSUPPORTED,
              "vc_silhouette_rows_tc: padded width %d not in {64, 128} (use the fp32 kernel)", dp);
   VC_REQUIRE(row_begin >= 0 && row_end <= N && row_begin < row_end, VC_ERR_BAD_ARG,
@@ -257,6 +306,7 @@ extern "C" int vc_silhouette_rows_tc(const void* H, const void* L, const float* 
   if (rc != VC_OK) return rc;
   SilTcArgs a;
   a.sqn = sqn; a.off = off_dev; a.k = k; a.N = N; a.row_begin = row_begin; a.row_end = row_end; a.nsplit = nsplit;
+  a.Xs = Xs; a.d = d;
   a.out = cluster_sums; a.panels = dp / 64; a.stages = dp == 64 ? 4 : 2;
   const size_t op = (size_t)ST_ROWS * 128 * a.panels;
   const size_t smem = 2 * op + (size_t)a.stages * 2 * op + 2 * ST_COLS * 4 + (1 + 2 * a.stages + 4) * 8 + 16 + 1024;

@@ -399,9 +399,10 @@ def _sil_block(Xs, sqn, off, k: int, r0: int, r1: int, lab_sorted, counts, s_sor
         sums = torch.empty((2 * nsplit, nrows, k), dtype=torch.float32, device=Xs.device)
         H = torch.empty((N, dp), dtype=torch.bfloat16, device=Xs.device)
         L = torch.empty((N, dp), dtype=torch.bfloat16, device=Xs.device)
-        lib().call("vc_silhouette_split_bf16", ptr(Xs), N, d, dp, ptr(H), ptr(L), stream_ptr())
-        lib().call("vc_silhouette_rows_tc", ptr(H), ptr(L), ptr(sqn), N, dp, ptr(off), k, r0, r1, nsplit, ptr(sums),
-                   stream_ptr())
+        sqn_hl = torch.empty_like(sqn)  # norms of the split rows: the formula must cancel against the same operands
+        lib().call("vc_silhouette_split_bf16", ptr(Xs), N, d, dp, ptr(H), ptr(L), ptr(sqn_hl), stream_ptr())
+        lib().call("vc_silhouette_rows_tc", ptr(H), ptr(L), ptr(Xs), d, ptr(sqn_hl), N, dp, ptr(off), k, r0, r1, nsplit,
+                   ptr(sums), stream_ptr())
         nsplit *= 2
     else:
         sums = torch.empty((nsplit, nrows, k), dtype=torch.float32, device=Xs.device)
