@@ -178,7 +178,9 @@ def test_linear_bf16(M, N, K, relu, bf16_mode):
 
 
 @pytest.mark.parametrize("B,Cin,H,W,Cout,relu", [(2, 1, 16, 22, 32, True), (3, 32, 8, 11, 64, True),
-                                                 (2, 64, 5, 7, 128, False), (1, 3, 9, 323, 8, True)])
+                                                 (2, 64, 5, 7, 128, False), (1, 3, 9, 323, 8, True),
+                                                 (4, 32, 128, 256, 32, True),    # 256 row tiles: persistent loop
+                                                 (2, 1, 128, 646, 32, True)])    # script-12 first layer at T=646
 def test_conv2d_s2k3_bf16(B, Cin, H, W, Cout, relu, bf16_mode):
     from vaeclust import ops
     x, w, b = _rand(B, Cin, H, W, seed=1), _rand(Cout, Cin, 3, 3, seed=2, scale=(Cin * 9) ** -0.5), _rand(Cout, seed=3)
@@ -189,7 +191,9 @@ def test_conv2d_s2k3_bf16(B, Cin, H, W, Cout, relu, bf16_mode):
 
 
 @pytest.mark.parametrize("B,Cin,H,W,Cout,relu", [(2, 128, 2, 3, 64, True), (3, 64, 4, 6, 32, True),
-                                                 (2, 32, 8, 12, 1, False), (1, 5, 3, 81, 7, True)])
+                                                 (2, 32, 8, 12, 1, False), (1, 5, 3, 81, 7, True),
+                                                 (2, 32, 64, 160, 32, True),     # 160 row tiles: persistent loop
+                                                 (2, 128, 16, 81, 64, True)])    # script-12 first deconv at T=646
 def test_convT2d_s2k4_bf16(B, Cin, H, W, Cout, relu, bf16_mode):
     from vaeclust import ops
     x, w, b = _rand(B, Cin, H, W, seed=1), _rand(Cin, Cout, 4, 4, seed=2, scale=(Cin * 4) ** -0.5), _rand(Cout, seed=3)
