@@ -1,0 +1,350 @@
+// Implicit-GEMM weight gradients of Conv2d(k3,s2,p1) and ConvTranspose2d(k4,s2,p1) on tcgen05 (sm_100a).
+//
+// Both are   dW[cp, cq, th, tw] = sum_{b,i,j} P[b,cp,i,j] * Q[b,cq, 2i+th-1, 2j+tw-1]
+//   Conv2d  (12:87-89):   P = dy [B,Cout,OH,OW], Q = x  [B,Cin,H,W],    taps 3x3 -> dW [Cout,Cin,3,3]
+//   ConvT2d (12:135-137): P = x  [B,Cin,H,W],    Q = dy [B,Cout,2H,2W], taps 4x4 -> dW [Cin,Cout,4,4]
+// i.e. the GEMM  C[M = cp, N = (cq,tap)] = A[M, K] * Bq[N, K]^T  whose contraction index K runs over the B*GH*GW pixels.
+// Neither operand is materialised: per 64-pixel k-block the eight producer warps build both K-major, 128-byte-swizzled
+// tiles in shared memory (lane = pixel pair, so loads are coalesced along W and a warp's stores cover one 128-byte row
+// without bank conflicts); one elected thread issues tcgen05.mma into a 128 x BN fp32 accumulator in tensor memory.
+// The pixel range is split over the grid (deterministic split-K): CTA (z, nt) reduces k-blocks [z*kbs, (z+1)*kbs) for
+// column tile nt and writes its partial; a second kernel folds the partials in a fixed order into the weight layout.
+#include <string.h>
+#include "common.cuh"
+#include "tc05.cuh"
+
+namespace vc {
+
+constexpr int WG_THREADS = 288;               // 8 producer/epilogue warps + 1 MMA warp
+constexpr uint32_t WG_A_BYTES = 128 * 128;    // [128 rows][64 bf16]
+
+struct WgArgs {
+  const float* P; const float* Q; float* part;
+  int B, Cp, GH, GW;       // P [B, Cp, GH, GW]
+  int Cq, SH, SW;          // Q [B, Cq, SH, SW]
+  int T, taps;             // taps = T*T, source pixel (2i + th - 1, 2j + tw - 1)
+  int N, BN;               // N = Cq*taps; BN = columns per tile (multiple of 32)
+  int K, nkb, kbs;         // pixels, 64-pixel k-blocks, k-blocks per split
+  int stages;
+  int gsize;               // producer warps that share one k-block (1, 2, 4 or 8); 8/gsize k-blocks are built at once
+  uint32_t idesc;
+};
+
+__device__ __forceinline__ uint32_t wg_pack(float a, float b) {
+  __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
+  return *reinterpret_cast<uint32_t*>(&h);
+}
+
+// predicated read-only load without a branch region: 0 when !pred (the address is then never dereferenced)
+__device__ __forceinline__ float wg_ldg(const float* p, uint32_t pred) {
+  float v;
+  asm("{\n\t.reg .pred q;\n\tsetp.ne.b32 q, %2, 0;\n\tmov.f32 %0, 0f00000000;\n\t@q ld.global.nc.f32 %0, [%1];\n\t}"
+      : "=f"(v)
+      : "l"(p), "r"(pred));
+  return v;
+}
+
+// One real row of the B tile, (cq, tap) of Q: element offset relative to the lane's pixel, the validity bit to test in
+// the lane's tap mask, and the row's byte offset in a stage with the row's swizzle phase folded in (bits 4-6), so a
+// lane's store address is  soffx ^ ((chunk << 4) | 4*(lane & 3)).
+struct __align__(16) WgRow { int off; uint32_t bit; uint32_t soffx; int pad; };
+
+__global__ void __launch_bounds__(WG_THREADS, 1) conv_wgrad_igemm_kernel(const WgArgs a) {
+  extern __shared__ unsigned char smem_raw[];
+  unsigned char* smem = smem_raw + ((1024u - (tma::s32(smem_raw) & 1023u)) & 1023u);
+  const int S = a.stages;
+  const uint32_t st_bytes = WG_A_BYTES + (uint32_t)a.BN * 128u;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + (size_t)S * st_bytes);
+  uint64_t* full = bars;            // S: 256 producer arrivals
+  uint64_t* empty = bars + S;       // S: tcgen05.commit
+  uint64_t* t_full = empty + S;     // 1
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(t_full + 1);
+  WgRow* rowtab = reinterpret_cast<WgRow*>(tmem_slot + 2);  // [Cp + columns of this tile]: one entry per REAL tile row
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int z = blockIdx.x, nt = blockIdx.y;
+  const int kb0 = z * a.kbs, kb1 = min(a.nkb, kb0 + a.kbs);
+  const int nkb = max(kb1 - kb0, 0);
+  const int n_base = nt * a.BN;
+  const uint32_t tmem_cols = a.BN <= 32 ? 32u : (a.BN <= 64 ? 64u : (a.BN <= 128 ? 128u : 256u));
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < S; ++s) { tma::mbar_init(&full[s], 32 * a.gsize); tma::mbar_init(&empty[s], 1); }
+    tma::mbar_init(t_full, 1);
+    tma::mbar_fence_init();
+  }
+  if (warp == 8) tc05::tmem_alloc(tmem_slot, tmem_cols);
+  const int ncols = min(a.BN, a.N - n_base);   // real columns of this tile
+  for (int nl = threadIdx.x; nl < ncols; nl += WG_THREADS) {
+    const int n = n_base + nl;
+    const int cq = n / a.taps, tap = n - cq * a.taps, th = tap / a.T, tw = tap - th * a.T;
+    WgRow t;
+    t.off = cq * a.SH * a.SW + th * a.SW + tw; t.bit = 1u << tap;
+    t.soffx = WG_A_BYTES + (uint32_t)nl * 128u + (((uint32_t)nl & 7u) << 4); t.pad = 0;
+    rowtab[nl] = t;
+  }
+  // padding rows of both tiles are never written by the producers: zero every stage once
+  for (uint32_t o = threadIdx.x * 16u; o < (uint32_t)S * st_bytes; o += WG_THREADS * 16u)
+    *reinterpret_cast<uint4*>(smem + o) = make_uint4(0u, 0u, 0u, 0u);
+  tma::fence_proxy_async();
+  tc05::fence_before();
+  __syncthreads();
+  tc05::fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp < 8) {
+    // ===================== producers =====================
+    // The eight warps form 8/gsize groups; group q builds k-blocks q, q + ngroups, ... on its own, so several ring
+    // slots fill concurrently.  Inside a group the real rows of both tiles are dealt round-robin to its warps and
+    // processed in "units" of 16 rows x 2 pixels = 32 independent loads per lane; the loads of the next unit are issued
+    // before the current one is packed and stored (two register buffers), across k-block boundaries too.
+    const int G = a.GH * a.GW;
+    const int gsize = a.gsize, ngroups = 8 / gsize;
+    const int group = warp / gsize, wig = warp - group * gsize;
+    const int unitsA = ((a.Cp + gsize - 1) / gsize + 15) / 16;
+    const int units = unitsA + ((ncols + gsize - 1) / gsize + 15) / 16;
+    const int nmine = nkb > group ? (nkb - group + ngroups - 1) / ngroups : 0;
+    const uint32_t lane_x = (((uint32_t)lane >> 2) << 4) | ((uint32_t)(lane & 3) * 4u);
+
+    // state of the k-block being LOADED: the lane's two pixels (b,i,j), advanced by 64 pixels per k-block
+    int pb[2], pi[2], pj[2];
+#pragma unroll
+    for (int e = 0; e < 2; ++e) {
+      const int64_t m = (int64_t)(kb0 + group) * 64 + 2 * lane + e;
+      pb[e] = (int)(m / G);
+      const int r = (int)(m - (int64_t)pb[e] * G);
+      pi[e] = r / a.GW;
+      pj[e] = r - pi[e] * a.GW;
+    }
+    int l_it = 0;
+    const float* pp[2];
+    const float* qq[2];
+    uint32_t tapmask[2];
+    auto pixel_state = [&]() {
+#pragma unroll
+      for (int e = 0; e < 2; ++e) {
+        const int i = pi[e], j = pj[e];
+        pp[e] = a.P + ((int64_t)pb[e] * a.Cp * G + i * a.GW + j);
+        qq[e] = a.Q + (((int64_t)pb[e] * a.Cq * a.SH + 2 * i - 1) * a.SW + 2 * j - 1);
+        const uint32_t fullT = (1u << a.T) - 1u;
+        uint32_t mh = fullT, mw = fullT;
+        if (i == 0) mh &= ~1u;
+        if (j == 0) mw &= ~1u;
+        const int lh = a.SH + 1 - 2 * i, lw = a.SW + 1 - 2 * j;   // taps t >= lh (lw) fall off the bottom (right) edge
+        if (lh < a.T) mh &= (1u << max(lh, 0)) - 1u;
+        if (lw < a.T) mw &= (1u << max(lw, 0)) - 1u;
+        uint32_t msk = 0;
+        for (int t = 0; t < a.T; ++t) msk |= ((mh >> t) & 1u) ? (mw << (t * a.T)) : 0u;
+        tapmask[e] = pb[e] < a.B ? (msk | (1u << 31)) : 0u;
+      }
+    };
+    pixel_state();
+
+    auto load_unit = [&](int it, int u, float (&v)[32]) {   // `it` counts this group's own k-blocks
+      if (it != l_it) {   // the load cursor entered the group's next k-block: advance both pixels
+        l_it = it;
+#pragma unroll
+        for (int e = 0; e < 2; ++e) {
+          pj[e] += 64 * ngroups;
+          while (pj[e] >= a.GW) { pj[e] -= a.GW; ++pi[e]; }
+          while (pi[e] >= a.GH) { pi[e] -= a.GH; ++pb[e]; }
+        }
+        pixel_state();
+      }
+      if (u < unitsA) {   // rows of the A tile: channel cp of P at the lane's pixels
+        const uint32_t ok0 = tapmask[0] >> 31, ok1 = tapmask[1] >> 31;
+#pragma unroll
+        for (int r = 0; r < 16; ++r) {
+          const int cp = wig + gsize * (u * 16 + r);
+          const uint32_t rok = cp < a.Cp ? 1u : 0u;
+          v[2 * r] = wg_ldg(pp[0] + cp * G, ok0 & rok);
+          v[2 * r + 1] = wg_ldg(pp[1] + cp * G, ok1 & rok);
+        }
+      } else {            // rows of the B tile: (cq, tap) of Q
+#pragma unroll
+        for (int r = 0; r < 16; ++r) {
+          const int nl = wig + gsize * ((u - unitsA) * 16 + r);
+          int2 t = make_int2(0, 0);
+          if (nl < ncols) t = *reinterpret_cast<const int2*>(&rowtab[nl]);
+          v[2 * r] = wg_ldg(qq[0] + t.x, tapmask[0] & (uint32_t)t.y);
+          v[2 * r + 1] = wg_ldg(qq[1] + t.x, tapmask[1] & (uint32_t)t.y);
+        }
+      }
+    };
+    auto store_unit = [&](int c, int u, const float (&v)[32]) {
+      const int it = group + c * ngroups;   // position in the CTA's k-block sequence
+      const int s = it % S;
+      unsigned char* tile = smem + (size_t)s * st_bytes;
+      if (u == 0) tma::mbar_wait(&empty[s], ((uint32_t)(it / S) & 1u) ^ 1u);   // first store into this ring slot
+      if (u < unitsA) {
+#pragma unroll
+        for (int r = 0; r < 16; ++r) {
+          const uint32_t cp = (uint32_t)(wig + gsize * (u * 16 + r));
+          if (cp < (uint32_t)a.Cp)
+            *reinterpret_cast<uint32_t*>(tile + ((cp * 128u + ((cp & 7u) << 4)) ^ lane_x)) = wg_pack(v[2 * r], v[2 * r + 1]);
+        }
+      } else {
+#pragma unroll
+        for (int r = 0; r < 16; ++r) {
+          const int nl = wig + gsize * ((u - unitsA) * 16 + r);
+          if (nl < ncols) *reinterpret_cast<uint32_t*>(tile + (rowtab[nl].soffx ^ lane_x)) = wg_pack(v[2 * r], v[2 * r + 1]);
+        }
+      }
+      if (u == units - 1) {
+        tma::fence_proxy_async();
+        tma::mbar_arrive(&full[s]);
+      }
+    };
+
+    {
+      float buf0[32], buf1[32];
+      const int total = nmine * units;
+      int it = 0, u = 0;          // store cursor
+      int it2 = 0, u2 = 0;        // load cursor (one unit ahead)
+      auto advance = [&](int& ii, int& uu) { if (++uu == units) { uu = 0; ++ii; } };
+      if (total > 0) { load_unit(0, 0, buf0); advance(it2, u2); }
+      for (int g = 0; g < total; g += 2) {
+        if (g + 1 < total) { load_unit(it2, u2, buf1); advance(it2, u2); }
+        store_unit(it, u, buf0); advance(it, u);
+        if (g + 1 >= total) break;
+        if (g + 2 < total) { load_unit(it2, u2, buf0); advance(it2, u2); }
+        store_unit(it, u, buf1); advance(it, u);
+      }
+    }
+    // ===================== epilogue: partial tile -> workspace =====================
+    const int q = warp & 3, hh = warp >> 2;
+    const int cp = q * 32 + lane;
+    const int nchunks = a.BN >> 5;
+    if (nkb > 0) {
+      tma::mbar_wait(t_full, 0);
+      tc05::fence_after();
+    }
+    float* o = a.part + ((int64_t)z * a.Cp + cp) * a.N;
+    for (int cc = hh; cc < nchunks; cc += 2) {
+      float v[32];
+      if (nkb > 0) {
+        tc05::ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + cc * 32, v);
+        tc05::ld_wait();
+      } else {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) v[j] = 0.f;
+      }
+      if (cp < a.Cp) {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+          const int n = n_base + cc * 32 + j;
+          if (n < a.N) o[n] = v[j];
+        }
+      }
+    }
+  } else {
+    // ===================== MMA issuer =====================
+    if (lane == 0) {
+      for (int it = 0; it < nkb; ++it) {
+        const int s = it % S;
+        const uint32_t ph = (uint32_t)(it / S) & 1u;
+        tma::mbar_wait(&full[s], ph);
+        tc05::fence_after();
+        const uint32_t sa = tma::s32(smem + (size_t)s * st_bytes), sb = sa + WG_A_BYTES;
+#pragma unroll
+        for (int kk = 0; kk < 4; ++kk)
+          tc05::mma_bf16(tmem_base, tc05::desc_k_sw128(sa + kk * 32), tc05::desc_k_sw128(sb + kk * 32), a.idesc,
+                         (uint32_t)((it | kk) != 0));
+        tc05::commit(&empty[s]);
+      }
+      if (nkb > 0) tc05::commit(t_full);
+    }
+  }
+
+  tc05::fence_before();
+  __syncthreads();
+  if (warp == 8) {
+    tc05::fence_after();
+    tc05::tmem_dealloc(tmem_base, tmem_cols);
+  }
+}
+
+__global__ void wgrad_fold_kernel(const float* __restrict__ part, int nsplit, int total, float* __restrict__ out) {
+  const int e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= total) return;
+  float acc = 0.f;
+  for (int zz = 0; zz < nsplit; ++zz) acc += part[(int64_t)zz * total + e];
+  out[e] = acc;
+}
+
+// ---- host ---------------------------------------------------------------------------------------------------------
+struct WgPlan { int Cp, Cq, T, GH, GW, SH, SW, N, ntiles, BN, K, nkb, nsplit, kbs; bool ok; };
+
+static WgPlan wg_plan(int op, int B, int Cin, int H, int W, int Cout) {
+  WgPlan p;
+  memset(&p, 0, sizeof(p));
+  if (op == VC_OP_CONV_WGRAD) {
+    p.Cp = Cout; p.Cq = Cin; p.T = 3; p.GH = (H - 1) / 2 + 1; p.GW = (W - 1) / 2 + 1; p.SH = H; p.SW = W;
+  } else if (op == VC_OP_CONVT_WGRAD) {
+    p.Cp = Cin; p.Cq = Cout; p.T = 4; p.GH = H; p.GW = W; p.SH = 2 * H; p.SW = 2 * W;
+  } else {
+    return p;
+  }
+  p.N = p.Cq * p.T * p.T;
+  p.ntiles = (p.N + 255) / 256;
+  p.BN = ((p.N + p.ntiles - 1) / p.ntiles + 31) / 32 * 32;
+  const int64_t K = (int64_t)B * p.GH * p.GW;
+  p.ok = p.Cp <= 128 && K < 2147483647LL - 64 && (int64_t)B * (Cin > Cout ? Cin : Cout) * 4 * H * W < 2147483647LL;
+  if (!p.ok) return p;
+  p.K = (int)K;
+  p.nkb = (p.K + 63) / 64;
+  int ns = sm_count() / p.ntiles;
+  if (ns < 1) ns = 1;
+  if (ns > p.nkb) ns = p.nkb;
+  p.kbs = (p.nkb + ns - 1) / ns;
+  p.nsplit = (p.nkb + p.kbs - 1) / p.kbs;
+  return p;
+}
+
+bool conv_wgrad_igemm_supported(int op, int B, int Cin, int H, int W, int Cout) {
+  return wg_plan(op, B, Cin, H, W, Cout).ok;
+}
+
+size_t conv_wgrad_igemm_workspace(int op, int B, int Cin, int H, int W, int Cout) {
+  const WgPlan p = wg_plan(op, B, Cin, H, W, Cout);
+  return p.ok ? (size_t)p.nsplit * p.Cp * p.N * 4 + 1024 : 0;
+}
+
+// in0 = dy, in1 = x (vc_dense_op convention for the weight-gradient ops)
+int conv_wgrad_igemm_run(int op, const float* dy, const float* x, float* dw, int B, int Cin, int H, int W, int Cout,
+                         void* ws, size_t wsb, cudaStream_t s) {
+  const WgPlan p = wg_plan(op, B, Cin, H, W, Cout);
+  VC_REQUIRE(p.ok, VC_ERR_UNSUPPORTED, "conv_wgrad_igemm: unsupported shape");
+  VC_REQUIRE(ws && wsb >= conv_wgrad_igemm_workspace(op, B, Cin, H, W, Cout), VC_ERR_WORKSPACE,
+             "conv_wgrad_igemm: workspace too small");
+  WgArgs a;
+  memset(&a, 0, sizeof(a));
+  a.P = op == VC_OP_CONV_WGRAD ? dy : x;
+  a.Q = op == VC_OP_CONV_WGRAD ? x : dy;
+  a.part = reinterpret_cast<float*>((reinterpret_cast<uintptr_t>(ws) + 255) & ~(uintptr_t)255);
+  a.B = B; a.Cp = p.Cp; a.GH = p.GH; a.GW = p.GW; a.Cq = p.Cq; a.SH = p.SH; a.SW = p.SW;
+  a.T = p.T; a.taps = p.T * p.T; a.N = p.N; a.BN = p.BN; a.K = p.K; a.nkb = p.nkb; a.kbs = p.kbs;
+  const size_t st_bytes = WG_A_BYTES + (size_t)p.BN * 128;
+  int stages = (int)((200 * 1024) / st_bytes);
+  if (stages > 10) stages = 10;
+  if (stages < 2) stages = 2;
+  a.stages = stages;
+  {  // smallest group that keeps a warp's share of a k-block at <= 80 rows (5 full units), if the ring is deep enough
+    const int ncols = p.N < p.BN ? p.N : p.BN;
+    int gs = 1;
+    while (gs < 8 && ((p.Cp + gs - 1) / gs + (ncols + gs - 1) / gs > 80 || 8 / gs > stages - 1)) gs *= 2;
+    a.gsize = gs;
+  }
+  a.idesc = tc05::idesc(tc05::kFmtBF16, 128, p.BN, 0, 0);
+  const size_t smem = (size_t)stages * st_bytes + (2 * stages + 1) * 8 + 16 + (size_t)p.BN * 16 + 1024;
+  VC_CUDA(cudaFuncSetAttribute(conv_wgrad_igemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  dim3 grid((unsigned)p.nsplit, (unsigned)p.ntiles);
+  conv_wgrad_igemm_kernel<<<grid, WG_THREADS, smem, s>>>(a);
+  VC_LAUNCH_CHECK();
+  const int total = p.Cp * p.N;
+  wgrad_fold_kernel<<<(total + 255) / 256, 256, 0, s>>>(a.part, p.nsplit, total, dw);
+  VC_LAUNCH_CHECK();
+  return VC_OK;
+}
+
+}  // namespace vc

@@ -267,6 +267,10 @@ bool conv_igemm_supported(int op, int B, int Cin, int H, int W, int Cout);
 size_t conv_igemm_workspace(int op, int B, int Cin, int H, int W, int Cout);
 int conv_igemm_run(int op, const float* in0, const float* in1, const float* bias, float* out, int B, int Cin, int H,
                    int W, int Cout, int relu, void* ws, size_t wsb, cudaStream_t s);
+bool conv_wgrad_igemm_supported(int op, int B, int Cin, int H, int W, int Cout);   // conv_wgrad_igemm.cu
+size_t conv_wgrad_igemm_workspace(int op, int B, int Cin, int H, int W, int Cout);
+int conv_wgrad_igemm_run(int op, const float* dy, const float* x, float* dw, int B, int Cin, int H, int W, int Cout,
+                         void* ws, size_t wsb, cudaStream_t s);
 }  // namespace vc
 
 using namespace vc;
@@ -295,6 +299,7 @@ OpDims op_dims(int op, int B, int Cin, int H, int W, int Cout) {
 extern "C" size_t vc_dense_op_workspace_bytes(int op, int precision, int B, int Cin, int H, int W, int Cout) {
   if (precision == VC_PREC_BF16_TC) {
     if (conv_igemm_supported(op, B, Cin, H, W, Cout)) return conv_igemm_workspace(op, B, Cin, H, W, Cout);
+    if (conv_wgrad_igemm_supported(op, B, Cin, H, W, Cout)) return conv_wgrad_igemm_workspace(op, B, Cin, H, W, Cout);
     const OpDims g = op_dims(op, B, Cin, H, W, Cout);
     return tc_gemm_workspace(g.M, g.N, g.K);
   }
@@ -375,6 +380,8 @@ extern "C" int vc_dense_op(int op, int precision, const float* in0, const float*
     if (conv_igemm_supported(op, B, Cin, H, W, Cout))  // implicit GEMM: no im2col matrix in HBM
       return conv_igemm_run(op, in0, in1, bias, out, B, Cin, H, W, Cout, relu, workspace, workspace_bytes,
                             as_stream(stream));
+    if (conv_wgrad_igemm_supported(op, B, Cin, H, W, Cout))
+      return conv_wgrad_igemm_run(op, in0, in1, out, B, Cin, H, W, Cout, workspace, workspace_bytes, as_stream(stream));
     return dense_op_tc(op, in0, in1, bias, out, B, Cin, H, W, Cout, relu, workspace, workspace_bytes, as_stream(stream));
   }
   switch (op) {
