@@ -169,7 +169,9 @@ def _check_bf16(fn_ours, fn_ref, x, w, b):
 
 
 @pytest.mark.parametrize("M,N,K,relu", [(64, 256, 470, True), (17, 16, 256, False), (3, 700, 33, True),
-                                        (64, 256, 8200, True), (64, 4100, 256, True)])
+                                        (64, 256, 8200, True), (64, 4100, 256, True),
+                                        # big-matrix shapes take the skinny kernels (fp32 weight read in place)
+                                        (64, 256, 16640, True), (64, 16500, 256, True), (50, 256, 16644, False)])
 def test_linear_bf16(M, N, K, relu, bf16_mode):
     from vaeclust import ops
     x, w, b = _rand(M, K, seed=1), _rand(N, K, seed=2, scale=K ** -0.5), _rand(N, seed=3)

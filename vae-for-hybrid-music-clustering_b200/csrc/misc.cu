@@ -74,6 +74,16 @@ bias_grad_stage1(const float* __restrict__ dy, int64_t outer, int C, int64_t inn
   if (threadIdx.x == 0) part[(int64_t)c * S + sp] = acc;
 }
 
+// inner == 1 (Linear layers): thread = column, so every row is read as full coalesced lines; rows sp, sp+S, ...
+__global__ void bias_grad_cols_stage1(const float* __restrict__ dy, int64_t outer, int C, int S,
+                                      double* __restrict__ part) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x, sp = blockIdx.y;
+  if (c >= C) return;
+  double acc = 0.0;
+  for (int64_t o = sp; o < outer; o += S) acc += (double)dy[o * C + c];
+  part[(int64_t)c * S + sp] = acc;
+}
+
 __global__ void bias_grad_stage2(const double* __restrict__ part, int C, int S, float* __restrict__ db, int accumulate) {
   const int c = blockIdx.x * blockDim.x + threadIdx.x;
   if (c >= C) return;
@@ -270,9 +280,14 @@ extern "C" int vc_bias_grad(const float* dy, int64_t outer, int C, int64_t inner
   VC_REQUIRE(workspace && workspace_bytes >= vc_bias_grad_workspace_bytes(C), VC_ERR_WORKSPACE,
              "vc_bias_grad: workspace too small");
   int S = kBiasSplits;
-  while (S > 1 && outer * inner / S < 1024) S >>= 1;
   double* part = static_cast<double*>(workspace);
-  bias_grad_stage1<<<dim3(C, S), 256, 0, as_stream(stream)>>>(dy, outer, C, inner, S, part);
+  if (inner == 1) {
+    while (S > 1 && (outer / S < 64 || (int64_t)C * S > 262144)) S >>= 1;
+    bias_grad_cols_stage1<<<dim3((C + 127) / 128, S), 128, 0, as_stream(stream)>>>(dy, outer, C, S, part);
+  } else {
+    while (S > 1 && outer * inner / S < 1024) S >>= 1;
+    bias_grad_stage1<<<dim3(C, S), 256, 0, as_stream(stream)>>>(dy, outer, C, inner, S, part);
+  }
   VC_LAUNCH_CHECK();
   bias_grad_stage2<<<(C + 127) / 128, 128, 0, as_stream(stream)>>>(part, C, S, db, accumulate);
   VC_LAUNCH_CHECK();

@@ -1,0 +1,379 @@
+// Skinny GEMMs of the two 67M-parameter fully connected layers of the script-12 VAE (12:98-103,129-132) on tcgen05.
+//
+// With a batch of 64 every Linear op (forward, data-gradient, weight-gradient) streams one huge fp32 matrix -- the
+// weight, or its gradient -- exactly once and is HBM-bound; the other operand is tiny.  Instead of materialising a bf16
+// copy of the big matrix, this kernel reads it in place:
+//   D[M, N] = sum_k A(m,k) * Bs[n][k]        N <= 256 (batch, or the 256-wide hidden layer)
+//   * A is the big fp32 matrix, either k-contiguous (A(m,k) = A[m*lda + k]) or m-contiguous (A(m,k) = A[k*lda + m]).
+//     Eight producer warps load it coalesced, convert to bf16 and store K-major into 128-byte-swizzled shared memory
+//     (the m-contiguous case transposes on the way: lanes run along m, two consecutive k are packed per 4-byte store).
+//   * Bs is the small operand, pre-converted to bf16 [BN][Kp] (K-major) and fetched by TMA.
+//   * one elected thread issues tcgen05.mma (128 x BN fp32 accumulator in tensor memory); the producer warps then read
+//     it back and store either D[m][n] or its transpose (lanes = consecutive m, so transposed stores are coalesced),
+//     with bias (per m) and ReLU; or write a split-K partial that sk_fold_kernel reduces in a fixed order.
+#include <string.h>
+#include "common.cuh"
+#include "tc05.cuh"
+
+namespace vc {
+
+constexpr int SK_THREADS = 288;              // 8 producer/epilogue warps + 1 MMA warp
+constexpr uint32_t SK_A_BYTES = 128 * 128;   // [128 rows][64 bf16]
+
+struct SkArgs {
+  const float* A; int64_t lda; int a_mcontig;
+  int M, N, K, BN;
+  float* out; int64_t ldo; int transposed;   // out[m*ldo + n] or out[n*ldo + m]
+  const float* bias; int relu;               // bias indexed by m
+  float* part;                               // split-K partials [nsplit][N][M] (transposed: coalesced), or null
+  int nkb, kbs, stages;
+  uint32_t idesc;
+};
+
+__device__ __forceinline__ uint32_t sk_pack(float a, float b) {
+  __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
+  return *reinterpret_cast<uint32_t*>(&h);
+}
+__device__ __forceinline__ float sk_ldg(const float* p, uint32_t pred) {
+  float v;
+  asm("{\n\t.reg .pred q;\n\tsetp.ne.b32 q, %2, 0;\n\tmov.f32 %0, 0f00000000;\n\t@q ld.global.nc.f32 %0, [%1];\n\t}"
+      : "=f"(v)
+      : "l"(p), "r"(pred));
+  return v;
+}
+__device__ __forceinline__ float4 sk_ldg4(const float* p, uint32_t pred) {
+  float4 v;
+  asm("{\n\t.reg .pred q;\n\tsetp.ne.b32 q, %5, 0;\n\tmov.f32 %0, 0f00000000;\n\tmov.f32 %1, 0f00000000;\n\t"
+      "mov.f32 %2, 0f00000000;\n\tmov.f32 %3, 0f00000000;\n\t@q ld.global.nc.v4.f32 {%0, %1, %2, %3}, [%4];\n\t}"
+      : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+      : "l"(p), "r"(pred));
+  return v;
+}
+
+// small operand -> bf16 [BN][Kp], zero padded.  colmajor == 0: B(n,k) = src[n*ld + k]; else B(n,k) = src[k*ld + n]
+__global__ void sk_small_operand_kernel(const float* __restrict__ src, int64_t ld, int colmajor, int N, int K, int BN,
+                                        int Kp, __nv_bfloat16* __restrict__ out) {
+  const int64_t total = (int64_t)BN * Kp;
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += stride) {
+    int n, k;
+    if (colmajor) { k = (int)(e / BN); n = (int)(e - (int64_t)k * BN); }   // consecutive threads -> consecutive n (coalesced reads)
+    else { n = (int)(e / Kp); k = (int)(e - (int64_t)n * Kp); }
+    float v = 0.f;
+    if (n < N && k < K) v = colmajor ? src[(int64_t)k * ld + n] : src[(int64_t)n * ld + k];
+    out[(int64_t)n * Kp + k] = __float2bfloat16_rn(v);
+  }
+}
+
+__global__ void __launch_bounds__(SK_THREADS, 2)
+skinny_gemm_kernel(const SkArgs a, const __grid_constant__ CUtensorMap mapB) {
+  extern __shared__ unsigned char smem_raw[];
+  unsigned char* smem = smem_raw + ((1024u - (tma::s32(smem_raw) & 1023u)) & 1023u);
+  const int S = a.stages;
+  const uint32_t b_bytes = (uint32_t)a.BN * 128u, st_bytes = SK_A_BYTES + b_bytes;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + (size_t)S * st_bytes);
+  uint64_t* full = bars;            // S: 256 producer arrivals + the TMA transaction
+  uint64_t* empty = bars + S;       // S: tcgen05.commit
+  uint64_t* t_full = empty + S;     // 1
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(t_full + 1);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int m0 = blockIdx.x * 128, z = blockIdx.y;
+  const int kb0 = z * a.kbs, kb1 = min(a.nkb, kb0 + a.kbs);
+  const int nkb = max(kb1 - kb0, 0);
+  const uint32_t tmem_cols = a.BN <= 32 ? 32u : (a.BN <= 64 ? 64u : (a.BN <= 128 ? 128u : 256u));
+
+  if (threadIdx.x == 0) {
+    tma::prefetch_map(&mapB);
+    for (int s = 0; s < S; ++s) { tma::mbar_init(&full[s], 256 + 1); tma::mbar_init(&empty[s], 1); }
+    tma::mbar_init(t_full, 1);
+    tma::mbar_fence_init();
+  }
+  if (warp == 8) tc05::tmem_alloc(tmem_slot, tmem_cols);
+  tc05::fence_before();
+  __syncthreads();
+  tc05::fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp < 8) {
+    // ===================== producers =====================
+    auto load_kb = [&](int it, float (&v)[32]) {
+      const int k0 = (kb0 + it) * 64;
+      if (!a.a_mcontig) {
+        // rows are k-contiguous: 16 lanes x float4 cover one 64-wide row slice; 8 passes of 16 rows
+        const int half = lane >> 4, k4 = lane & 15;
+        const int k = k0 + 4 * k4;
+        const uint32_t kok = k < a.K ? 1u : 0u;   // K % 4 == 0 is required for this mode
+        const float* p = a.A + (int64_t)(m0 + warp * 2 + half) * a.lda + k;
+#pragma unroll
+        for (int ps = 0; ps < 8; ++ps) {
+          const int r = ps * 16 + warp * 2 + half;
+          const float4 f = sk_ldg4(p + (int64_t)ps * 16 * a.lda, kok & (m0 + r < a.M ? 1u : 0u));
+          v[4 * ps] = f.x; v[4 * ps + 1] = f.y; v[4 * ps + 2] = f.z; v[4 * ps + 3] = f.w;
+        }
+      } else {
+        // rows are m-contiguous: lanes run along m (coalesced), this warp owns k-pairs 4*warp .. 4*warp+3
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const int k = k0 + 2 * (warp * 4 + i);
+          const uint32_t ok0 = k < a.K ? 1u : 0u, ok1 = k + 1 < a.K ? 1u : 0u;
+          const float* p = a.A + (int64_t)k * a.lda + m0 + lane;
+#pragma unroll
+          for (int mi = 0; mi < 4; ++mi) {
+            const uint32_t mok = m0 + lane + 32 * mi < a.M ? 1u : 0u;
+            v[8 * i + 2 * mi] = sk_ldg(p + 32 * mi, ok0 & mok);
+            v[8 * i + 2 * mi + 1] = sk_ldg(p + a.lda + 32 * mi, ok1 & mok);
+          }
+        }
+      }
+    };
+    auto store_kb = [&](int it, const float (&v)[32]) {
+      const int s = it % S;
+      tma::mbar_wait(&empty[s], ((uint32_t)(it / S) & 1u) ^ 1u);
+      unsigned char* tile = smem + (size_t)s * st_bytes;
+      if (threadIdx.x == 0) {
+        tma::mbar_expect_tx(&full[s], b_bytes);
+        tma::load_2d(tile + SK_A_BYTES, &mapB, &full[s], (kb0 + it) * 64, 0);
+      }
+      if (!a.a_mcontig) {
+        const uint32_t half = (uint32_t)lane >> 4, k4 = (uint32_t)lane & 15u;
+#pragma unroll
+        for (int ps = 0; ps < 8; ++ps) {
+          const uint32_t r = (uint32_t)(ps * 16 + warp * 2) + half;
+          const uint2 o = make_uint2(sk_pack(v[4 * ps], v[4 * ps + 1]), sk_pack(v[4 * ps + 2], v[4 * ps + 3]));
+          *reinterpret_cast<uint2*>(tile + r * 128u + ((((k4 >> 1) ^ (r & 7u)) << 4) | ((k4 & 1u) << 3))) = o;
+        }
+      } else {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const uint32_t kp = (uint32_t)(warp * 4 + i);
+#pragma unroll
+          for (int mi = 0; mi < 4; ++mi) {
+            const uint32_t r = (uint32_t)(lane + 32 * mi);
+            *reinterpret_cast<uint32_t*>(tile + r * 128u + ((((kp >> 2) ^ (r & 7u)) << 4) | ((kp & 3u) << 2))) =
+                sk_pack(v[8 * i + 2 * mi], v[8 * i + 2 * mi + 1]);
+          }
+        }
+      }
+      tma::fence_proxy_async();
+      tma::mbar_arrive(&full[s]);
+    };
+    {
+      float buf0[32], buf1[32];
+      if (nkb > 0) load_kb(0, buf0);
+      for (int it = 0; it < nkb; it += 2) {
+        if (it + 1 < nkb) load_kb(it + 1, buf1);
+        store_kb(it, buf0);
+        if (it + 1 >= nkb) break;
+        if (it + 2 < nkb) load_kb(it + 2, buf0);
+        store_kb(it + 1, buf1);
+      }
+    }
+    // ===================== epilogue =====================
+    const int q = warp & 3, hh = warp >> 2;
+    const int m = m0 + q * 32 + lane;
+    const int nchunks = a.BN >> 5;
+    if (nkb > 0) {
+      tma::mbar_wait(t_full, 0);
+      tc05::fence_after();
+    }
+    const float bm = (a.bias && !a.part && m < a.M) ? __ldg(a.bias + m) : 0.f;
+    for (int cc = hh; cc < nchunks; cc += 2) {
+      float v[32];
+      if (nkb > 0) {
+        tc05::ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + cc * 32, v);
+        tc05::ld_wait();
+      } else {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) v[j] = 0.f;
+      }
+      if (m >= a.M) continue;
+      if (a.part) {
+        float* o = a.part + ((int64_t)z * a.N + cc * 32) * a.M + m;
+#pragma unroll
+        for (int j = 0; j < 32; ++j)
+          if (cc * 32 + j < a.N) o[(int64_t)j * a.M] = v[j];
+        continue;
+      }
+#pragma unroll
+      for (int j = 0; j < 32; ++j) {
+        v[j] += bm;
+        if (a.relu) v[j] = fmaxf(v[j], 0.f);
+      }
+      if (a.transposed) {
+        float* o = a.out + (int64_t)(cc * 32) * a.ldo + m;
+#pragma unroll
+        for (int j = 0; j < 32; ++j)
+          if (cc * 32 + j < a.N) o[(int64_t)j * a.ldo] = v[j];
+      } else {
+        float* o = a.out + (int64_t)m * a.ldo + cc * 32;
+        if (cc * 32 + 32 <= a.N && (a.ldo & 3) == 0 && (reinterpret_cast<uintptr_t>(a.out) & 15) == 0) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j)
+            reinterpret_cast<float4*>(o)[j] = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+        } else {
+#pragma unroll
+          for (int j = 0; j < 32; ++j)
+            if (cc * 32 + j < a.N) o[j] = v[j];
+        }
+      }
+    }
+  } else {
+    // ===================== MMA issuer =====================
+    if (lane == 0) {
+      for (int it = 0; it < nkb; ++it) {
+        const int s = it % S;
+        tma::mbar_wait(&full[s], (uint32_t)(it / S) & 1u);
+        tc05::fence_after();
+        const uint32_t sa = tma::s32(smem + (size_t)s * st_bytes), sb = sa + SK_A_BYTES;
+#pragma unroll
+        for (int kk = 0; kk < 4; ++kk)
+          tc05::mma_bf16(tmem_base, tc05::desc_k_sw128(sa + kk * 32), tc05::desc_k_sw128(sb + kk * 32), a.idesc,
+                         (uint32_t)((it | kk) != 0));
+        tc05::commit(&empty[s]);
+      }
+      if (nkb > 0) tc05::commit(t_full);
+    }
+  }
+
+  tc05::fence_before();
+  __syncthreads();
+  if (warp == 8) {
+    tc05::fence_after();
+    tc05::tmem_dealloc(tmem_base, tmem_cols);
+  }
+}
+
+// fold split-K partials [nsplit][N][M] in a fixed order, then bias (per m) / ReLU / layout
+__global__ void sk_fold_kernel(const float* __restrict__ part, int nsplit, int M, int N, const float* __restrict__ bias,
+                               int relu, int transposed, int64_t ldo, float* __restrict__ out) {
+  const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int64_t MN = (int64_t)M * N;
+  if (e >= MN) return;
+  const int n = (int)(e / M), m = (int)(e - (int64_t)n * M);
+  float acc = 0.f;
+  for (int zz = 0; zz < nsplit; ++zz) acc += part[(int64_t)zz * MN + e];
+  if (bias) acc += bias[m];
+  if (relu) acc = fmaxf(acc, 0.f);
+  out[transposed ? (int64_t)n * ldo + m : (int64_t)m * ldo + n] = acc;
+}
+
+// ---- host ---------------------------------------------------------------------------------------------------------
+struct SkPlan {
+  bool ok;
+  int M, N, K, BN, Kp, nkb, nsplit, kbs, stages;
+  int a_mcontig, a_from;        // a_from: which input is the big operand (0 = in0, 1 = in1)
+  int64_t lda, ldo, ld_small;
+  int small_colmajor, transposed, has_bias;
+};
+
+static SkPlan sk_plan(int op, int B, int Cin, int Cout, const void* in0, const void* in1) {
+  SkPlan p;
+  memset(&p, 0, sizeof(p));
+  if (B > 256) return p;
+  switch (op) {
+    case VC_OP_LINEAR_FWD:    // y[b][n] = sum_k x[b][k] W[n][k]:  A = W (k-contiguous), Bs = x, D[n][b] -> y transposed
+      p.M = Cout; p.N = B; p.K = Cin; p.a_from = 1; p.lda = Cin; p.a_mcontig = 0;
+      p.ld_small = Cin; p.small_colmajor = 0; p.ldo = Cout; p.transposed = 1; p.has_bias = 1;
+      break;
+    case VC_OP_LINEAR_DGRAD:  // dx[b][k] = sum_n dy[b][n] W[n][k]: A(m=k, kk=n) = W[kk*Cin + m] (m-contiguous)
+      p.M = Cin; p.N = B; p.K = Cout; p.a_from = 1; p.lda = Cin; p.a_mcontig = 1;
+      p.ld_small = Cout; p.small_colmajor = 0; p.ldo = Cin; p.transposed = 1;
+      break;
+    case VC_OP_LINEAR_WGRAD:  // dW[n][k] = sum_b dy[b][n] x[b][k]   (in0 = dy, in1 = x)
+      if (Cout <= 256 && Cin >= Cout) {   // rows of D = k: A = x (m-contiguous), Bs[n][b] = dy[b][n], dW = D^T
+        p.M = Cin; p.N = Cout; p.K = B; p.a_from = 1; p.lda = Cin; p.a_mcontig = 1;
+        p.ld_small = Cout; p.small_colmajor = 1; p.ldo = Cin; p.transposed = 1;
+      } else if (Cin <= 256) {            // rows of D = n: A = dy (m-contiguous), Bs[k][b] = x[b][k], dW = D
+        p.M = Cout; p.N = Cin; p.K = B; p.a_from = 0; p.lda = Cout; p.a_mcontig = 1;
+        p.ld_small = Cin; p.small_colmajor = 1; p.ldo = Cin; p.transposed = 0;
+      } else {
+        return p;
+      }
+      break;
+    default: return p;
+  }
+  if (p.N > 256 || (int64_t)p.M * p.K < (1LL << 22)) return p;   // only worth it when the big matrix dominates
+  const void* big = p.a_from ? in1 : in0;
+  if (!p.a_mcontig && ((p.lda & 3) || (p.K & 3) || (reinterpret_cast<uintptr_t>(big) & 15))) return p;
+  p.BN = (p.N + 31) / 32 * 32;
+  p.Kp = (p.K + 63) / 64 * 64;
+  p.nkb = p.Kp / 64;
+  const int mt = (p.M + 127) / 128;
+  int ns = 1;
+  if (mt < sm_count()) {
+    ns = (2 * sm_count() + mt - 1) / mt;
+    if (ns > p.nkb / 4) ns = p.nkb / 4;
+    if (ns < 1) ns = 1;
+  }
+  p.kbs = (p.nkb + ns - 1) / ns;
+  p.nsplit = (p.nkb + p.kbs - 1) / p.kbs;
+  const int st_bytes = (int)SK_A_BYTES + p.BN * 128;
+  int stages = 98304 / st_bytes;
+  if (stages > p.kbs) stages = p.kbs;
+  if (stages < 1) stages = 1;
+  p.stages = stages;
+  p.ok = true;
+  return p;
+}
+
+static size_t sk_align(size_t v) { return (v + 1023) & ~(size_t)1023; }
+
+bool skinny_gemm_supported(int op, int B, int Cin, int Cout, const void* in0, const void* in1) {
+  return sk_plan(op, B, Cin, Cout, in0, in1).ok;
+}
+
+// the alignment test needs the pointers; sized for the worst case so the query does not
+size_t skinny_gemm_workspace(int op, int B, int Cin, int Cout) {
+  const SkPlan p = sk_plan(op, B, Cin, Cout, nullptr, nullptr);
+  if (!p.ok) return 0;
+  return sk_align((size_t)p.BN * p.Kp * 2) + (p.nsplit > 1 ? sk_align((size_t)p.nsplit * p.M * p.N * 4) : 0) + 2048;
+}
+
+int skinny_gemm_run(int op, const float* in0, const float* in1, const float* bias, float* out, int B, int Cin, int Cout,
+                    int relu, void* ws, size_t wsb, cudaStream_t s) {
+  const SkPlan p = sk_plan(op, B, Cin, Cout, in0, in1);
+  VC_REQUIRE(p.ok, VC_ERR_UNSUPPORTED, "skinny_gemm: unsupported shape");
+  VC_REQUIRE(ws && wsb >= skinny_gemm_workspace(op, B, Cin, Cout), VC_ERR_WORKSPACE, "skinny_gemm: workspace too small");
+  unsigned char* w = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(ws) + 1023) & ~(uintptr_t)1023);
+  __nv_bfloat16* Bs = reinterpret_cast<__nv_bfloat16*>(w);
+  float* part = p.nsplit > 1 ? reinterpret_cast<float*>(w + sk_align((size_t)p.BN * p.Kp * 2)) : nullptr;
+  const float* big = p.a_from ? in1 : in0;
+  const float* small = p.a_from ? in0 : in1;
+  {
+    const int64_t total = (int64_t)p.BN * p.Kp;
+    int64_t blocks = (total + 255) / 256;
+    if (blocks > (int64_t)sm_count() * 16) blocks = (int64_t)sm_count() * 16;
+    sk_small_operand_kernel<<<(int)blocks, 256, 0, s>>>(small, p.ld_small, p.small_colmajor, p.N, p.K, p.BN, p.Kp, Bs);
+    VC_LAUNCH_CHECK();
+  }
+  CUtensorMap mb;
+  {
+    const uint64_t dims[2] = {(uint64_t)p.Kp, (uint64_t)p.BN};
+    const uint64_t str[1] = {(uint64_t)p.Kp * 2};
+    const uint32_t box[2] = {64u, (uint32_t)p.BN};
+    int rc = tma::make_map(&mb, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, Bs, dims, str, box, CU_TENSOR_MAP_SWIZZLE_128B);
+    if (rc != VC_OK) return rc;
+  }
+  SkArgs a;
+  memset(&a, 0, sizeof(a));
+  a.A = big; a.lda = p.lda; a.a_mcontig = p.a_mcontig;
+  a.M = p.M; a.N = p.N; a.K = p.K; a.BN = p.BN;
+  a.out = out; a.ldo = p.ldo; a.transposed = p.transposed;
+  a.bias = p.has_bias ? bias : nullptr; a.relu = relu;
+  a.part = part; a.nkb = p.nkb; a.kbs = p.kbs; a.stages = p.stages;
+  a.idesc = tc05::idesc(tc05::kFmtBF16, 128, p.BN, 0, 0);
+  const size_t smem = (size_t)p.stages * (SK_A_BYTES + (size_t)p.BN * 128) + (2 * p.stages + 1) * 8 + 16 + 1024;
+  VC_CUDA(cudaFuncSetAttribute(skinny_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  dim3 grid((unsigned)((p.M + 127) / 128), (unsigned)p.nsplit);
+  skinny_gemm_kernel<<<grid, SK_THREADS, smem, s>>>(a, mb);
+  VC_LAUNCH_CHECK();
+  if (part) {
+    const int64_t MN = (int64_t)p.M * p.N;
+    sk_fold_kernel<<<(int)((MN + 255) / 256), 256, 0, s>>>(part, p.nsplit, p.M, p.N, a.bias, relu, p.transposed, p.ldo, out);
+    VC_LAUNCH_CHECK();
+  }
+  return VC_OK;
+}
+
+}  // namespace vc

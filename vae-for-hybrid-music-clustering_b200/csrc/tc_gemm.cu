@@ -267,6 +267,10 @@ bool conv_igemm_supported(int op, int B, int Cin, int H, int W, int Cout);
 size_t conv_igemm_workspace(int op, int B, int Cin, int H, int W, int Cout);
 int conv_igemm_run(int op, const float* in0, const float* in1, const float* bias, float* out, int B, int Cin, int H,
                    int W, int Cout, int relu, void* ws, size_t wsb, cudaStream_t s);
+bool skinny_gemm_supported(int op, int B, int Cin, int Cout, const void* in0, const void* in1);   // skinny_gemm.cu
+size_t skinny_gemm_workspace(int op, int B, int Cin, int Cout);
+int skinny_gemm_run(int op, const float* in0, const float* in1, const float* bias, float* out, int B, int Cin, int Cout,
+                    int relu, void* ws, size_t wsb, cudaStream_t s);
 bool conv_wgrad_igemm_supported(int op, int B, int Cin, int H, int W, int Cout);   // conv_wgrad_igemm.cu
 size_t conv_wgrad_igemm_workspace(int op, int B, int Cin, int H, int W, int Cout);
 int conv_wgrad_igemm_run(int op, const float* dy, const float* x, float* dw, int B, int Cin, int H, int W, int Cout,
@@ -301,7 +305,8 @@ extern "C" size_t vc_dense_op_workspace_bytes(int op, int precision, int B, int 
     if (conv_igemm_supported(op, B, Cin, H, W, Cout)) return conv_igemm_workspace(op, B, Cin, H, W, Cout);
     if (conv_wgrad_igemm_supported(op, B, Cin, H, W, Cout)) return conv_wgrad_igemm_workspace(op, B, Cin, H, W, Cout);
     const OpDims g = op_dims(op, B, Cin, H, W, Cout);
-    return tc_gemm_workspace(g.M, g.N, g.K);
+    const size_t a = tc_gemm_workspace(g.M, g.N, g.K), b = skinny_gemm_workspace(op, B, Cin, Cout);
+    return a > b ? a : b;   // the skinny path may be refused at run time for a misaligned pointer
   }
   switch (op) {
     case VC_OP_LINEAR_FWD: case VC_OP_LINEAR_DGRAD: return vc_linear_workspace_bytes(B, Cout, Cin);
@@ -380,6 +385,8 @@ extern "C" int vc_dense_op(int op, int precision, const float* in0, const float*
     if (conv_igemm_supported(op, B, Cin, H, W, Cout))  // implicit GEMM: no im2col matrix in HBM
       return conv_igemm_run(op, in0, in1, bias, out, B, Cin, H, W, Cout, relu, workspace, workspace_bytes,
                             as_stream(stream));
+    if (H == 1 && W == 1 && skinny_gemm_supported(op, B, Cin, Cout, in0, in1))  // huge fp32 matrix read in place
+      return skinny_gemm_run(op, in0, in1, bias, out, B, Cin, Cout, relu, workspace, workspace_bytes, as_stream(stream));
     if (conv_wgrad_igemm_supported(op, B, Cin, H, W, Cout))
       return conv_wgrad_igemm_run(op, in0, in1, out, B, Cin, H, W, Cout, workspace, workspace_bytes, as_stream(stream));
     return dense_op_tc(op, in0, in1, bias, out, B, Cin, H, W, Cout, relu, workspace, workspace_bytes, as_stream(stream));
