@@ -195,7 +195,9 @@ def test_conv2d_s2k3_bf16(B, Cin, H, W, Cout, relu, bf16_mode):
 @pytest.mark.parametrize("B,Cin,H,W,Cout,relu", [(2, 128, 2, 3, 64, True), (3, 64, 4, 6, 32, True),
                                                  (2, 32, 8, 12, 1, False), (1, 5, 3, 81, 7, True),
                                                  (2, 32, 64, 160, 32, True),     # 160 row tiles: persistent loop
-                                                 (2, 128, 16, 81, 64, True)])    # script-12 first deconv at T=646
+                                                 (2, 128, 16, 81, 64, True),     # script-12 first deconv at T=646
+                                                 (2, 32, 64, 162, 1, False),     # script-12 last deconv at T=646
+                                                 (3, 32, 7, 40, 1, True)])       # odd height: half-empty row pair
 def test_convT2d_s2k4_bf16(B, Cin, H, W, Cout, relu, bf16_mode):
     from vaeclust import ops
     x, w, b = _rand(B, Cin, H, W, seed=1), _rand(Cin, Cout, 4, 4, seed=2, scale=(Cin * 4) ** -0.5), _rand(Cout, seed=3)

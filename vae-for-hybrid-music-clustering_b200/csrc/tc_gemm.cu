@@ -267,6 +267,9 @@ bool conv_igemm_supported(int op, int B, int Cin, int H, int W, int Cout);
 size_t conv_igemm_workspace(int op, int B, int Cin, int H, int W, int Cout);
 int conv_igemm_run(int op, const float* in0, const float* in1, const float* bias, float* out, int B, int Cin, int H,
                    int W, int Cout, int relu, void* ws, size_t wsb, cudaStream_t s);
+bool conv_direct_supported(int op, int B, int Cin, int H, int W, int Cout);   // conv_direct.cu
+int conv_direct_run(int op, const float* in0, const float* in1, const float* bias, float* out, int B, int Cin, int H,
+                    int W, int Cout, int relu, int round_bf16, cudaStream_t s);
 bool skinny_gemm_supported(int op, int B, int Cin, int Cout, const void* in0, const void* in1);   // skinny_gemm.cu
 size_t skinny_gemm_workspace(int op, int B, int Cin, int Cout);
 int skinny_gemm_run(int op, const float* in0, const float* in1, const float* bias, float* out, int B, int Cin, int Cout,
@@ -382,6 +385,8 @@ extern "C" int vc_dense_op(int op, int precision, const float* in0, const float*
     const OpDims g = op_dims(op, B, Cin, H, W, Cout);
     VC_REQUIRE((int64_t)g.M > 0 && (int64_t)B * H * W * 4 < 2147483647LL, VC_ERR_UNSUPPORTED,
                "vc_dense_op: tensor too large for 32-bit pixel index");
+    if (conv_direct_supported(op, B, Cin, H, W, Cout))  // single-channel ends: streaming FFMA kernels
+      return conv_direct_run(op, in0, in1, bias, out, B, Cin, H, W, Cout, relu, 1, as_stream(stream));
     if (conv_igemm_supported(op, B, Cin, H, W, Cout))  // implicit GEMM: no im2col matrix in HBM
       return conv_igemm_run(op, in0, in1, bias, out, B, Cin, H, W, Cout, relu, workspace, workspace_bytes,
                             as_stream(stream));
