@@ -53,6 +53,15 @@ __device__ __forceinline__ double warp_sum(double v) {
   return v;
 }
 
+// Predicated read-only load without a branch region: 0.f when pred == 0 (the address is then never dereferenced).
+__device__ __forceinline__ float ldg_pred(const float* p, uint32_t pred) {
+  float v;
+  asm("{\n\t.reg .pred q;\n\tsetp.ne.b32 q, %2, 0;\n\tmov.f32 %0, 0f00000000;\n\t@q ld.global.nc.f32 %0, [%1];\n\t}"
+      : "=f"(v)
+      : "l"(p), "r"(pred));
+  return v;
+}
+
 // Block-wide sum, result valid in thread 0. `scratch` holds >= 32 elements.
 template <typename T>
 __device__ __forceinline__ T block_sum(T v, T* scratch) {

@@ -42,8 +42,8 @@ conv1ch_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w, con
 #pragma unroll
       for (int kw = 0; kw < 3; ++kw) {
         const int ih = 2 * oh + kh - 1, iw = 2 * ow + kw - 1;
-        const bool ok = (unsigned)ih < (unsigned)H && (unsigned)iw < (unsigned)W;
-        xin[kh * 3 + kw] = ok ? rb(__ldg(xb + (int64_t)ih * W + iw), round_bf16) : 0.f;
+        const uint32_t ok = ((unsigned)ih < (unsigned)H && (unsigned)iw < (unsigned)W) ? 1u : 0u;
+        xin[kh * 3 + kw] = rb(ldg_pred(xb + (int64_t)ih * W + iw, ok), round_bf16);
       }
     float* yo = y + (int64_t)b * Cout * plane + (int64_t)oh * OW + ow;
     for (int c0 = 0; c0 < Cout; c0 += CT) {
@@ -73,7 +73,7 @@ conv1ch_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w, con
 // ---- ConvTranspose2d(Cin -> 1) forward.  Thread = two vertically adjacent input pixels (2*i2, 2*i2+1; j): a 4x3 patch
 // of x per channel feeds the 4x2 output block y[4*i2 .. 4*i2+3, 2j .. 2j+1].  Output row 2i+ph uses input rows
 // i+ph-1 (kernel row 3-... see below) and i+ph:  y[2i+ph, 2j+pw] += x[i+dh, j+dw] * W[1+ph-2dh, 1+pw-2dw].
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, 4)
 convT_to1_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ bias,
                      float* __restrict__ y, int B, int Cin, int H, int W, int relu, int round_bf16) {
   extern __shared__ float sm[];   // [Cin][16]
@@ -89,23 +89,27 @@ convT_to1_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w, c
     const int i2 = (int)(t2 % H2), b = (int)(t2 / H2);
     const int i = 2 * i2;
     // patch rows i-1 .. i+2, columns j-1 .. j+1
-    bool rok[4], cok[3];
+    uint32_t rok[4], cok[3];
 #pragma unroll
-    for (int r = 0; r < 4; ++r) rok[r] = (unsigned)(i - 1 + r) < (unsigned)H;
+    for (int r = 0; r < 4; ++r) rok[r] = (unsigned)(i - 1 + r) < (unsigned)H ? 1u : 0u;
 #pragma unroll
-    for (int c = 0; c < 3; ++c) cok[c] = (unsigned)(j - 1 + c) < (unsigned)W;
+    for (int c = 0; c < 3; ++c) cok[c] = (unsigned)(j - 1 + c) < (unsigned)W ? 1u : 0u;
     float acc[4][2];
 #pragma unroll
     for (int r = 0; r < 4; ++r) { acc[r][0] = b0; acc[r][1] = b0; }
     const float* xb = x + (int64_t)b * Cin * plane + (int64_t)(i - 1) * W + (j - 1);
-#pragma unroll 4
+#pragma unroll 2
     for (int ci = 0; ci < Cin; ++ci) {
       float p[4][3];
+      const float* xc = xb + (int64_t)ci * plane;
 #pragma unroll
       for (int r = 0; r < 4; ++r)
 #pragma unroll
-        for (int c = 0; c < 3; ++c)
-          p[r][c] = (rok[r] && cok[c]) ? rb(__ldg(xb + (int64_t)ci * plane + r * W + c), round_bf16) : 0.f;
+        for (int c = 0; c < 3; ++c) p[r][c] = ldg_pred(xc + r * W + c, rok[r] & cok[c]);
+#pragma unroll
+      for (int r = 0; r < 4; ++r)
+#pragma unroll
+        for (int c = 0; c < 3; ++c) p[r][c] = rb(p[r][c], round_bf16);
       const float4* wq = reinterpret_cast<const float4*>(sm + ci * 16);
       const float4 w0 = wq[0], w1 = wq[1], w2 = wq[2], w3 = wq[3];   // kernel rows kh = 0..3, .x-.w = kw 0..3
       // output row 2*(i+a)+ph, a in {0,1}; patch row index of input row i+a+dh is 1+a+dh
@@ -158,8 +162,8 @@ convT_to1_dgrad_kernel(const float* __restrict__ dy, const float* __restrict__ w
 #pragma unroll
       for (int kw = 0; kw < 4; ++kw) {
         const int oh = 2 * i - 1 + kh, ow = 2 * j - 1 + kw;
-        const bool ok = (unsigned)oh < (unsigned)OH && (unsigned)ow < (unsigned)OW;
-        g[kh * 4 + kw] = ok ? rb(__ldg(db + (int64_t)oh * OW + ow), round_bf16) : 0.f;
+        const uint32_t ok = ((unsigned)oh < (unsigned)OH && (unsigned)ow < (unsigned)OW) ? 1u : 0u;
+        g[kh * 4 + kw] = rb(ldg_pred(db + (int64_t)oh * OW + ow, ok), round_bf16);
       }
     float* o = dx + (int64_t)b * Cin * plane + (int64_t)i * W + j;
 #pragma unroll 4

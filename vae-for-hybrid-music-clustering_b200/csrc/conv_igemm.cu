@@ -114,10 +114,15 @@ __device__ __forceinline__ void ig_gather(const IgArgs& a, const IgPixel& px, in
     const int th = tap / a.TW, tw = tap - th * a.TW;
     const int sh = a.S * px.i + th + a.D0, sw = a.S * px.j + tw + a.D0;
     const bool ok = px.ok && tap < ntaps && (unsigned)sh < (unsigned)a.SH && (unsigned)sw < (unsigned)a.SW;
-    const int64_t plane = (int64_t)a.SH * a.SW;
-    const float* p = a.src + ((int64_t)px.b * a.C + c0) * plane + (int64_t)(ok ? sh : 0) * a.SW + (ok ? sw : 0);
+    const int plane = a.SH * a.SW;
+    const float* p = a.src + ((int64_t)px.b * a.C + c0) * plane + (ok ? sh * a.SW + sw : 0);
+    if (ok) {
 #pragma unroll
-    for (int j = 0; j < 32; ++j) v[j] = ok ? __ldg(p + j * plane) : 0.f;
+      for (int j = 0; j < 32; ++j) { v[j] = __ldg(p); p += plane; }
+    } else {
+#pragma unroll
+      for (int j = 0; j < 32; ++j) v[j] = 0.f;
+    }
   }
 }
 
@@ -201,13 +206,13 @@ conv_igemm_kernel(const IgArgs a, const __grid_constant__ CUtensorMap mapW) {
       for (int tl = 0; tl < my_tiles; ++tl) {
         const int as = tl & 1;
         const uint32_t aph = (uint32_t)(tl >> 1) & 1u;
-        tma::mbar_wait(&t_empty[as], aph ^ 1u);
+        tma::mbar_wait_backoff(&t_empty[as], aph ^ 1u, 64);
         tc05::fence_after();
         const uint32_t tacc = tmem_base + (uint32_t)(as * a.BN);
         for (int kb = 0; kb < a.nkb; ++kb, ++it) {
           const int s = it % S;
           const uint32_t ph = (uint32_t)(it / S) & 1u;
-          tma::mbar_wait(&full[s], ph);
+          tma::mbar_wait_backoff(&full[s], ph, 32);
           tc05::fence_after();
           const uint32_t sa = tma::s32(smem + (size_t)s * st_bytes), sb = sa + IG_A_BYTES;
 #pragma unroll
@@ -232,7 +237,7 @@ conv_igemm_kernel(const IgArgs a, const __grid_constant__ CUtensorMap mapW) {
       const uint32_t aph = (uint32_t)(tl >> 1) & 1u;
       const int m = ((int)blockIdx.x + tl * (int)gridDim.x) * IG_BM + row;
       const IgPixel px = ig_pixel(a, m);
-      tma::mbar_wait(&t_full[as], aph);
+      tma::mbar_wait_backoff(&t_full[as], aph, 256);
       tc05::fence_after();
       const uint32_t tacc = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * a.BN);
       for (int cc = hh; cc < nchunks; cc += 2) {

@@ -243,7 +243,7 @@ __global__ void __launch_bounds__(WG_THREADS, 1) conv_wgrad_igemm_kernel(const W
       for (int it = 0; it < nkb; ++it) {
         const int s = it % S;
         const uint32_t ph = (uint32_t)(it / S) & 1u;
-        tma::mbar_wait(&full[s], ph);
+        tma::mbar_wait_backoff(&full[s], ph, 32);
         tc05::fence_after();
         const uint32_t sa = tma::s32(smem + (size_t)s * st_bytes), sb = sa + WG_A_BYTES;
 #pragma unroll

@@ -223,7 +223,7 @@ skinny_gemm_kernel(const SkArgs a, const __grid_constant__ CUtensorMap mapB) {
     if (lane == 0) {
       for (int it = 0; it < nkb; ++it) {
         const int s = it % S;
-        tma::mbar_wait(&full[s], (uint32_t)(it / S) & 1u);
+        tma::mbar_wait_backoff(&full[s], (uint32_t)(it / S) & 1u, 32);
         tc05::fence_after();
         const uint32_t sa = tma::s32(smem + (size_t)s * st_bytes), sb = sa + SK_A_BYTES;
 #pragma unroll
