@@ -80,6 +80,10 @@ int vc_bias_grad(const float* dy, int64_t outer, int C, int64_t inner, float* db
                  size_t workspace_bytes, void* stream);
 /* dx = dy * (y > 0) */
 int vc_relu_bwd(const float* dy, const float* y, float* dx, int64_t n, void* stream);
+/* Both of the above in one pass over dy/y ([outer, C, inner] layout): g = dy * (y > 0) and db[c] = sum g, the two
+ * things autograd computes for `ReLU(conv(x) + b)` (12:87-89,135-137).  Workspace as vc_bias_grad. */
+int vc_relu_bwd_bias(const float* dy, const float* y, int64_t outer, int C, int64_t inner, float* g, float* db,
+                     void* workspace, size_t workspace_bytes, void* stream);
 /* out[b,:] = [a[b,0:na], l[b,0:nl]*gate[b], gate[b] if append_gate]  -- `l*m` and torch.cat of 12:178-180 and
  * the cat([x,c]) / cat([z,c]) of 19:97-115 (gate=NULL, append_gate=0). */
 int vc_cat_gate_fwd(const float* a, int na, const float* l, int nl, const float* gate, int append_gate, int B,

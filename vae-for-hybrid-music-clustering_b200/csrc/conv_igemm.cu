@@ -115,10 +115,15 @@ __device__ __forceinline__ void ig_gather(const IgArgs& a, const IgPixel& px, in
     const int sh = a.S * px.i + th + a.D0, sw = a.S * px.j + tw + a.D0;
     const bool ok = px.ok && tap < ntaps && (unsigned)sh < (unsigned)a.SH && (unsigned)sw < (unsigned)a.SW;
     const int plane = a.SH * a.SW;
-    const float* p = a.src + ((int64_t)px.b * a.C + c0) * plane + (ok ? sh * a.SW + sw : 0);
+    // byte address kept as one 64-bit integer and bumped by the channel stride: two integer ops per load
+    uint64_t addr = reinterpret_cast<uint64_t>(a.src + ((int64_t)px.b * a.C + c0) * plane + (ok ? sh * a.SW + sw : 0));
+    const uint64_t step = (uint64_t)plane * 4u;
     if (ok) {
 #pragma unroll
-      for (int j = 0; j < 32; ++j) { v[j] = __ldg(p); p += plane; }
+      for (int j = 0; j < 32; ++j) {
+        asm("ld.global.nc.f32 %0, [%1];" : "=f"(v[j]) : "l"(addr));
+        addr += step;
+      }
     } else {
 #pragma unroll
       for (int j = 0; j < 32; ++j) v[j] = 0.f;
@@ -237,7 +242,9 @@ conv_igemm_kernel(const IgArgs a, const __grid_constant__ CUtensorMap mapW) {
       const uint32_t aph = (uint32_t)(tl >> 1) & 1u;
       const int m = ((int)blockIdx.x + tl * (int)gridDim.x) * IG_BM + row;
       const IgPixel px = ig_pixel(a, m);
-      tma::mbar_wait_backoff(&t_full[as], aph, 256);
+      // one warp polls the accumulator barrier; the other seven park on a hardware named barrier (no issue slots)
+      if (ew == 0) tma::mbar_wait_backoff(&t_full[as], aph, 128);
+      asm volatile("bar.sync 1, 256;" ::: "memory");
       tc05::fence_after();
       const uint32_t tacc = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * a.BN);
       for (int cc = hh; cc < nchunks; cc += 2) {

@@ -84,6 +84,57 @@ __global__ void bias_grad_cols_stage1(const float* __restrict__ dy, int64_t oute
   part[(int64_t)c * S + sp] = acc;
 }
 
+// ReLU backward and bias gradient in ONE pass: g = dy * (y > 0) is written and summed per channel while it is in
+// registers.  Block (c, sp) owns whole (o, c) planes o = sp, sp+S, ...; the plane is contiguous, so the loop is plain
+// float4 streaming with no index arithmetic.  Partials land in the layout bias_grad_stage2 folds.
+__global__ void __launch_bounds__(256)
+relu_bwd_bias_stage1(const float* __restrict__ dy, const float* __restrict__ y, float* __restrict__ g, int64_t outer,
+                     int C, int64_t inner, int S, double* __restrict__ part) {
+  __shared__ double scratch[32];
+  const int c = blockIdx.x, sp = blockIdx.y;
+  double acc = 0.0;
+  const bool vec = (inner % 4 == 0) && (((reinterpret_cast<uintptr_t>(dy) | reinterpret_cast<uintptr_t>(y) |
+                                          reinterpret_cast<uintptr_t>(g)) & 15) == 0);
+  for (int64_t o = sp; o < outer; o += S) {
+    const int64_t base = (o * C + c) * inner;
+    float a = 0.f;
+    if (vec) {
+      const float4* d4 = reinterpret_cast<const float4*>(dy + base);
+      const float4* y4 = reinterpret_cast<const float4*>(y + base);
+      float4* g4 = reinterpret_cast<float4*>(g + base);
+      for (int64_t i = threadIdx.x; i < inner / 4; i += blockDim.x) {
+        const float4 d = d4[i], v = y4[i];
+        const float4 r = make_float4(v.x > 0.f ? d.x : 0.f, v.y > 0.f ? d.y : 0.f, v.z > 0.f ? d.z : 0.f,
+                                     v.w > 0.f ? d.w : 0.f);
+        g4[i] = r;
+        a += (r.x + r.y) + (r.z + r.w);
+      }
+    } else {
+      for (int64_t i = threadIdx.x; i < inner; i += blockDim.x) {
+        const float r = y[base + i] > 0.f ? dy[base + i] : 0.f;
+        g[base + i] = r;
+        a += r;
+      }
+    }
+    acc += (double)a;
+  }
+  acc = block_sum<double>(acc, scratch);
+  if (threadIdx.x == 0) part[(int64_t)c * S + sp] = acc;
+}
+// inner == 1 (Linear): thread = column
+__global__ void relu_bwd_bias_cols_stage1(const float* __restrict__ dy, const float* __restrict__ y,
+                                          float* __restrict__ g, int64_t outer, int C, int S, double* __restrict__ part) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x, sp = blockIdx.y;
+  if (c >= C) return;
+  double acc = 0.0;
+  for (int64_t o = sp; o < outer; o += S) {
+    const float r = y[o * C + c] > 0.f ? dy[o * C + c] : 0.f;
+    g[o * C + c] = r;
+    acc += (double)r;
+  }
+  part[(int64_t)c * S + sp] = acc;
+}
+
 __global__ void bias_grad_stage2(const double* __restrict__ part, int C, int S, float* __restrict__ db, int accumulate) {
   const int c = blockIdx.x * blockDim.x + threadIdx.x;
   if (c >= C) return;
@@ -272,6 +323,26 @@ extern "C" int vc_relu_bwd(const float* dy, const float* y, float* dx, int64_t n
   return VC_OK;
 }
 
+extern "C" int vc_relu_bwd_bias(const float* dy, const float* y, int64_t outer, int C, int64_t inner, float* g, float* db,
+                                void* workspace, size_t workspace_bytes, void* stream) {
+  VC_REQUIRE(dy && y && g && db && outer > 0 && C > 0 && inner > 0, VC_ERR_BAD_ARG, "vc_relu_bwd_bias: bad arguments");
+  VC_REQUIRE(workspace && workspace_bytes >= vc_bias_grad_workspace_bytes(C), VC_ERR_WORKSPACE,
+             "vc_relu_bwd_bias: workspace too small");
+  int S = kBiasSplits;
+  double* part = static_cast<double*>(workspace);
+  if (inner == 1) {
+    while (S > 1 && (S > outer || (int64_t)C * S > 262144)) S >>= 1;
+    relu_bwd_bias_cols_stage1<<<dim3((C + 127) / 128, S), 128, 0, as_stream(stream)>>>(dy, y, g, outer, C, S, part);
+  } else {
+    while (S > 1 && S > outer) S >>= 1;
+    relu_bwd_bias_stage1<<<dim3(C, S), 256, 0, as_stream(stream)>>>(dy, y, g, outer, C, inner, S, part);
+  }
+  VC_LAUNCH_CHECK();
+  bias_grad_stage2<<<(C + 127) / 128, 128, 0, as_stream(stream)>>>(part, C, S, db, 0);
+  VC_LAUNCH_CHECK();
+  return VC_OK;
+}
+
 extern "C" size_t vc_bias_grad_workspace_bytes(int C) { return sizeof(double) * (size_t)kBiasSplits * (C > 0 ? C : 1); }
 
 extern "C" int vc_bias_grad(const float* dy, int64_t outer, int C, int64_t inner, float* db, int accumulate,
@@ -282,7 +353,7 @@ extern "C" int vc_bias_grad(const float* dy, int64_t outer, int C, int64_t inner
   int S = kBiasSplits;
   double* part = static_cast<double*>(workspace);
   if (inner == 1) {
-    while (S > 1 && (outer / S < 64 || (int64_t)C * S > 262144)) S >>= 1;
+    while (S > 1 && (S > outer || (int64_t)C * S > 262144)) S >>= 1;
     bias_grad_cols_stage1<<<dim3((C + 127) / 128, S), 128, 0, as_stream(stream)>>>(dy, outer, C, S, part);
   } else {
     while (S > 1 && outer * inner / S < 1024) S >>= 1;

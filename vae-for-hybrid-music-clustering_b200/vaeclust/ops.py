@@ -94,21 +94,28 @@ class _DenseFn(torch.autograd.Function):
         B, Cin, H, W, Cout = ctx.dims
         _, op_d, op_w = _OPS[ctx.kind]
         s = stream_ptr()
-        if ctx.relu:
+        dx = dw = db = None
+        want_db = ctx.has_bias and ctx.needs_input_grad[3]
+        inner = 1 if ctx.kind == "linear" else dy.shape[2] * dy.shape[3]
+        if ctx.relu and want_db:  # ReLU mask and bias gradient in one pass over dy / y
+            g = torch.empty_like(dy)
+            db = torch.empty(Cout, dtype=torch.float32, device=x.device)
+            ws = _workspace(lib().size("vc_bias_grad_workspace_bytes", Cout), x.device)
+            lib().call("vc_relu_bwd_bias", ptr(dy), ptr(y), B, Cout, inner, ptr(g), ptr(db), ptr(ws), ws.numel(), s)
+            want_db = False
+        elif ctx.relu:
             g = torch.empty_like(dy)
             lib().call("vc_relu_bwd", ptr(dy), ptr(y), ptr(g), dy.numel(), s)
         else:
             g = dy
-        dx = dw = db = None
         if ctx.needs_input_grad[1]:
             dx = torch.empty_like(x)
             _dense(op_d, ctx.prec, g, weight, None, dx, B, Cin, H, W, Cout, False)
         if ctx.needs_input_grad[2]:
             dw = torch.empty_like(weight)
             _dense(op_w, ctx.prec, g, x, None, dw, B, Cin, H, W, Cout, False)
-        if ctx.has_bias and ctx.needs_input_grad[3]:
+        if want_db:
             db = torch.empty(Cout, dtype=torch.float32, device=x.device)
-            inner = 1 if ctx.kind == "linear" else g.shape[2] * g.shape[3]
             ws = _workspace(lib().size("vc_bias_grad_workspace_bytes", Cout), x.device)
             lib().call("vc_bias_grad", ptr(g), B, Cout, inner, ptr(db), 0, ptr(ws), ws.numel(), s)
         return None, dx, dw, db, None

@@ -80,6 +80,58 @@ class VAEStep:
         return stats  # device tensor [loss, recon, kl] of the local batch
 
 
+class HostBatchFeeder:
+    """Feeds batches from a HOST-resident (pinned) dataset, the situation of the reference's DataLoader (12:226-227,
+    19:191-192), without stalling the step: the rows of batch s+1 are copied host->device on a side stream into the
+    other half of a double buffer while batch s trains.  Large per-sample arrays (the spectrograms) go row by row
+    straight out of the pinned dataset (no host-side gather pass); small ones are gathered on the host first."""
+
+    def __init__(self, arrays, batch_size: int, device, small_bytes: int = 1 << 16):
+        self.device = device
+        self.host = [a if a.is_pinned() else a.pin_memory() for a in (t.contiguous() for t in arrays)]
+        self.copy_stream = torch.cuda.Stream(device=device)
+        self.slots = []
+        for _ in range(2):
+            dev = [torch.empty((batch_size,) + tuple(a.shape[1:]), dtype=a.dtype, device=device) for a in self.host]
+            stage = [torch.empty((batch_size,) + tuple(a.shape[1:]), dtype=a.dtype).pin_memory()
+                     if a[0].numel() * a.element_size() <= small_bytes else None for a in self.host]
+            self.slots.append(dict(dev=dev, stage=stage, ready=torch.cuda.Event(), free=torch.cuda.Event(), n=0))
+        self.bytes_per_sample = sum(a[0].numel() * a.element_size() for a in self.host)
+        self._next = 0
+        self._queue = []
+
+    def prefetch(self, idx) -> None:
+        """Enqueue the copy of the batch with sample indices `idx` (1-D CPU int64 tensor or list)."""
+        slot = self.slots[self._next]
+        self._next ^= 1
+        idx_t = idx if isinstance(idx, torch.Tensor) else torch.as_tensor(idx)
+        ids = idx_t.tolist()
+        n = len(ids)
+        with torch.cuda.stream(self.copy_stream):
+            self.copy_stream.wait_event(slot["free"])  # the step that last used this slot has been enqueued and finished
+            for h, d, st in zip(self.host, slot["dev"], slot["stage"]):
+                if st is not None:
+                    torch.index_select(h, 0, idx_t, out=st[:n])
+                    d[:n].copy_(st[:n], non_blocking=True)
+                else:
+                    for i, j in enumerate(ids):
+                        d[i].copy_(h[j], non_blocking=True)
+            slot["ready"].record(self.copy_stream)
+        slot["n"] = n
+        self._queue.append(slot)
+
+    def get(self):
+        """Device tensors of the oldest prefetched batch; the current stream waits for its copy."""
+        slot = self._queue.pop(0)
+        torch.cuda.current_stream(self.device).wait_event(slot["ready"])
+        self._last = slot
+        return [d[: slot["n"]] for d in slot["dev"]]
+
+    def release(self) -> None:
+        """Call after the step that consumed the batch has been enqueued: its slot may be refilled once that work is done."""
+        self._last["free"].record(torch.cuda.current_stream(self.device))
+
+
 @dataclass
 class TrainLog:
     loss: List[float] = field(default_factory=list)
