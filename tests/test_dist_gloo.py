@@ -57,6 +57,17 @@ def _worker(rank, world, port, out_dir):
     bucket.flat.copy_(torch.full((6,), float(rank + 1)))  # local batch-mean gradient
     bucket.all_reduce_mean(nloc, 8)
     res["grad"] = p.grad.numpy().copy()
+    # overlapped exchange: one "big" parameter reduced from its autograd hook, two small ones through the flat buffer
+    big = torch.nn.Parameter(torch.ones(40))
+    s1, s2 = torch.nn.Parameter(torch.ones(3)), torch.nn.Parameter(torch.ones(2, 2))
+    unused = torch.nn.Parameter(torch.ones(5))
+    sync = dist.OverlappedGradSync([big, s1, s2, unused], td.group.WORLD, big_numel=16)
+    for _ in range(2):  # twice: the second step must not see stale gradients
+        sync.begin(nloc, 8)
+        ((rank + 1.0) * (big.sum() + 2.0 * s1.sum() + 3.0 * s2.sum())).backward()
+        sync.finish()
+    res["ov_big"], res["ov_s1"], res["ov_s2"] = big.grad.numpy().copy(), s1.grad.numpy().copy(), s2.grad.numpy().copy()
+    res["ov_unused_none"] = np.array(unused.grad is None)
     # empty-cluster relocation across ranks
     init2 = init.copy()
     init2[3] = 1000.0
@@ -88,6 +99,11 @@ def test_world2_matches_single_process(tmp_path):
         np.testing.assert_allclose(r[i]["mean"], X.astype(np.float64).mean(0), rtol=1e-9, atol=1e-12)
         np.testing.assert_allclose(r[i]["var"], X.astype(np.float64).var(0), rtol=1e-9)
         np.testing.assert_allclose(r[i]["grad"], np.full(6, (5 * 1.0 + 3 * 2.0) / 8))
+        w = (5 * 1.0 + 3 * 2.0) / 8
+        np.testing.assert_allclose(r[i]["ov_big"], np.full(40, w), rtol=1e-6)
+        np.testing.assert_allclose(r[i]["ov_s1"], np.full(3, 2 * w), rtol=1e-6)
+        np.testing.assert_allclose(r[i]["ov_s2"], np.full((2, 2), 3 * w), rtol=1e-6)
+        assert bool(r[i]["ov_unused_none"])
     np.testing.assert_array_equal(r[0]["centers"], r[1]["centers"])  # bit-identical replicas
     init2 = init.copy()
     init2[3] = 1000.0

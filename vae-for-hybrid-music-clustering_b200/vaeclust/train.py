@@ -47,12 +47,12 @@ class VAEStep:
         self.mode = VC_LOSS_SUM_MEAN if kind == "mlp19" else VC_LOSS_MEAN_MEAN
         self.multi = group is not None and vdist.world_size(group) > 1
         self.opt = Adam(model.parameters(), lr=lr)
-        self.bucket = vdist.GradBucket(model.parameters(), group) if self.multi else None
+        self.sync = vdist.OverlappedGradSync(model.parameters(), group) if self.multi else None
 
     def __call__(self, x, *extra, eps: Optional[torch.Tensor] = None, global_batch: Optional[int] = None):
         m = self.model
-        if self.bucket is not None:
-            self.bucket.zero()
+        if self.sync is not None:
+            self.sync.begin(x.shape[0], global_batch or x.shape[0] * vdist.world_size(self.group))
         else:
             self.opt.zero_grad()
         if self.kind == "conv12":
@@ -75,7 +75,7 @@ class VAEStep:
         loss, stats = ops.vae_loss(xhat, x, klr, self.beta, self.mode, mu.shape[1], unit_grad=True)
         loss.backward()
         if self.multi:
-            self.bucket.all_reduce_mean(x.shape[0], global_batch or x.shape[0] * vdist.world_size(self.group))
+            self.sync.finish()
         self.opt.step()
         return stats  # device tensor [loss, recon, kl] of the local batch
 
