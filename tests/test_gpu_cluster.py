@@ -33,6 +33,37 @@ def test_kmeans_explicit_init_matches_oracle(n, d, k):
     np.testing.assert_allclose(km.cluster_centers_, centers, rtol=1e-4, atol=1e-5)
 
 
+@pytest.mark.parametrize("n,k,scale", [(30001, 16, 1.0), (30001, 17, 1.0), (12345, 31, 1e3), (50000, 32, 1e-3),
+                                       (255, 24, 1.0), (400003, 32, 1.0)])
+def test_kmeans_tensor_core_estep_d32(n, k, scale, monkeypatch):
+    """d == 32, 16 <= k <= 32 runs the tcgen05 E-step (tf32 hi/lo split + exact-recompute guard).  Its labels must be
+    bit-identical to the FFMA kernel's (VAECLUST_KMEANS_TC=0) at every Lloyd iteration from the same centres -- ragged
+    tile counts, several tiles per CTA, large / small magnitudes, points on bisectors -- and the first E-step must
+    equal the oracle's up to rounding-level ties."""
+    from vaeclust import cluster
+    X, _ = blobs(n, 32, max(k // 2, 2), seed=n + k)        # fewer blobs than centres: many near-bisector points
+    X = (X * scale).astype(np.float32)
+    X -= X.mean(0)
+    C0 = X[np.random.default_rng(3).permutation(n)[:k]].copy()
+    Xt, C = torch.from_numpy(X).cuda(), torch.from_numpy(C0).cuda().contiguous()
+    for it in range(6):
+        out = {}
+        for tc in ("1", "0"):
+            monkeypatch.setenv("VAECLUST_KMEANS_TC", tc)
+            st = cluster._LloydState(n, 32, k, Xt.device)
+            st.labels.fill_(-1)
+            cluster._estep(Xt, C, st, True)
+            out[tc] = st
+        assert torch.equal(out["1"].labels, out["0"].labels), it
+        assert torch.equal(out["1"].counts, out["0"].counts)
+        torch.testing.assert_close(out["1"].sums, out["0"].sums, rtol=1e-6, atol=1e-6 * scale * n / k)
+        if it == 0 and n <= 60000:
+            # vs the BLAS-ordered oracle only rounding-level bisector ties may differ (see the near-ties test below)
+            assert (out["1"].labels.cpu().numpy() != cr.lloyd_estep(X, C0)).sum() <= 3
+        cluster._finalize(C, out["1"])
+        C = out["1"].centers_new.clone().contiguous()
+
+
 def test_kmeans_estep_on_split_blobs_differs_only_at_near_ties():
     """k larger than the number of blobs puts many points near a bisector.  From identical centres, one E-step may
     differ from the BLAS-ordered oracle only where the float64 margin between the two candidates is a rounding

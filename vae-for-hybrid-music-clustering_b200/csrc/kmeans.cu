@@ -12,7 +12,7 @@
 // and a second kernel reduces them in a fixed order: bit-reproducible run to run, no floating-point atomics.
 #include <string.h>
 #include "common.cuh"
-#include "tma.cuh"
+#include "tc05.cuh"
 
 namespace vc {
 
@@ -23,6 +23,7 @@ constexpr int kFlush = 16;
 using tma::mbar_init;
 using tma::mbar_expect_tx;
 using tma::mbar_wait;
+using tma::mbar_arrive;
 
 __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
   asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
@@ -288,6 +289,321 @@ kmeans_assign_update_kernel(const KmArgs a, const __grid_constant__ CUtensorMap 
   if (lane == 0 && my_changed) atomicAdd(a.n_changed, my_changed);
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// Tensor-core E-step for d == 32 and 16 <= k <= 32, where the FFMA version is compute-bound (2kd FLOP per point).
+// The 256 x 32 fp32 tile the TMA engine delivered is already a K-major, 128-byte-swizzled UMMA operand, so the
+// distance GEMM  dot[256, k] = X_tile * C^T  runs on tcgen05 (kind::tf32) with the accumulator in tensor memory.
+// TF32 alone (10 mantissa bits) cannot reproduce sklearn's fp32 labels, so every value is split x = hi + lo with
+// hi = x with the low 13 mantissa bits cleared (exact in tf32): dot ~= hi.chi + hi.clo + lo.chi, error <= 2^-16 |x||c|.
+// Labels stay bit-exact through a guard: every centroid whose tensor-core distance lies within 2^-13 |x| max|c| of the
+// best one is re-evaluated with the reference FMA chain (the arithmetic of kmeans_assign_update_kernel) and the argmin
+// is taken over those exact values in index order; all other centroids are provably farther.  Phase B is unchanged.
+struct KmTcArgs {
+  KmArgs a;
+  int kp;                      // k rounded up to a multiple of 16 (UMMA N)
+  size_t off_lo, off_chi, off_clo, off_mbar;
+  uint32_t idesc;
+};
+
+__device__ __forceinline__ void mma_tf32(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc_,
+                                         uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}" ::"r"(tmem_d),
+      "l"(adesc), "l"(bdesc), "r"(idesc_), "r"(accumulate)
+      : "memory");
+}
+
+__device__ __forceinline__ float tf32_hi(float v) { return __uint_as_float(__float_as_uint(v) & 0xFFFFE000u); }
+
+constexpr int kTcWorkers = 256;             // worker threads: thread = row of the 256-row tile
+constexpr int kTcThreads = kTcWorkers + 32; // + one warp whose lane 0 issues the TMA copies and the MMAs
+constexpr int kTcSlots = 3;                 // tile ring depth
+
+template <int KP>
+__global__ void __launch_bounds__(kTcThreads, 1)
+kmeans_tc_kernel(const KmTcArgs ta, const __grid_constant__ CUtensorMap tmap) {
+  extern __shared__ unsigned char smem_raw[];
+  unsigned char* smem = smem_raw + ((1024u - (tma::s32(smem_raw) & 1023u)) & 1023u);
+  const KmArgs& a = ta.a;
+  constexpr int d = 32, tp = 256;
+  const int k = a.k, update = a.update;
+  const int64_t N = a.N;
+  constexpr size_t tile_bytes = (size_t)tp * d * 4;
+  float* acc = reinterpret_cast<float*>(smem + a.off_acc);
+  double* dsum = reinterpret_cast<double*>(smem + a.off_dsum);
+  float* cs = reinterpret_cast<float*>(smem + a.off_c);
+  float* c2 = reinterpret_cast<float*>(smem + a.off_c2);   // [KP], +inf beyond k
+  int* cnt = reinterpret_cast<int*>(smem + a.off_cnt);
+  unsigned char* hi_tile = smem + ta.off_lo;               // hi | lo operand tiles of the tile being multiplied
+  unsigned char* lo_tile = hi_tile + tile_bytes;
+  unsigned char* chi = smem + ta.off_chi;
+  unsigned char* clo = smem + ta.off_clo;
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + ta.off_mbar);  // [3] TMA -> workers
+  uint64_t* free_ = full + kTcSlots;                                 // [3] workers -> TMA: ring slot consumed
+  uint64_t* ready = free_ + kTcSlots;                                // workers -> MMA: hi/lo operands written
+  uint64_t* done = ready + 1;                                        // MMA -> workers: accumulator filled
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(done + 1);
+  float* cmax_s = reinterpret_cast<float*>(tmem_slot + 1);
+  int* lbl = reinterpret_cast<int*>(smem + ta.off_mbar + 128);   // [256] labels of the current tile
+
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int kd = k * d;
+  const int64_t ntiles = (N + tp - 1) / tp;
+  const int64_t G = gridDim.x;
+
+  if (tid == 0) {
+    tma::prefetch_map(&tmap);
+    for (int s = 0; s < kTcSlots; ++s) { mbar_init(&full[s], 1); mbar_init(&free_[s], kKmWarps); }
+    mbar_init(ready, kKmWarps);
+    mbar_init(done, 1);
+    tma::mbar_fence_init();
+  }
+  if (warp == kKmWarps) tc05::tmem_alloc(tmem_slot, 64);
+  for (int i = tid; i < kd; i += kTcThreads) cs[i] = a.C[i];
+  for (int i = tid; i < k; i += kTcThreads) cnt[i] = 0;
+  // centroid operands: [KP rows][32 floats], K-major with the 128-byte swizzle, split into hi / lo; padding rows zero
+  for (int e = tid; e < KP * d; e += kTcThreads) {
+    const int r = e >> 5, c = e & 31;
+    const float v = r < k ? a.C[e] : 0.f;
+    const float h = tf32_hi(v);
+    const uint32_t o = tma::sw128((uint32_t)r, (uint32_t)(c >> 2)) + (uint32_t)(c & 3) * 4u;
+    *reinterpret_cast<float*>(chi + o) = h;
+    *reinterpret_cast<float*>(clo + o) = v - h;
+  }
+  if (update) {
+    for (int i = tid; i < a.ncopies * kd; i += kTcThreads) acc[i] = 0.f;
+    for (int i = tid; i < kd; i += kTcThreads) dsum[i] = 0.0;
+  }
+  tma::fence_proxy_async();
+  tc05::fence_before();
+  __syncthreads();
+  tc05::fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  for (int c = warp; c < KP; c += kKmWarps + 1) {
+    float s = 0.f;
+    if (c < k) {
+      for (int j = lane; j < d; j += 32) s += cs[c * d + j] * cs[c * d + j];
+      s = warp_sum(s);
+    } else {
+      s = __int_as_float(0x7f800000);   // padding centroid: infinitely far
+    }
+    if (lane == 0) c2[c] = s;
+  }
+  __syncthreads();
+  if (tid == 0) {
+    float m = 0.f;
+    for (int c = 0; c < k; ++c) m = fmaxf(m, c2[c]);
+    *cmax_s = sqrtf(m);
+  }
+  __syncthreads();
+
+  if (warp == kKmWarps) {
+    // ================= copy + MMA issuer (one thread) =================
+    if (lane == 0) {
+      auto issue = [&](int slot, int64_t t) {
+        mbar_expect_tx(&full[slot], (uint32_t)tile_bytes);
+        tma::load_2d(smem + (size_t)slot * tile_bytes, &tmap, &full[slot], 0, (int)(t * tp));
+      };
+      for (int s = 0; s < kTcSlots; ++s) {
+        const int64_t t = (int64_t)blockIdx.x + (int64_t)s * G;
+        if (t < ntiles) issue(s, t);
+      }
+      const uint32_t sH = tma::s32(hi_tile), sL = tma::s32(lo_tile), sCh = tma::s32(chi), sCl = tma::s32(clo);
+      int i = 0;
+      for (int64_t t = blockIdx.x; t < ntiles; t += G, ++i) {
+        tma::mbar_wait_backoff(ready, (uint32_t)(i & 1), 64);
+        tc05::fence_after();
+#pragma unroll
+        for (int hh = 0; hh < 2; ++hh) {
+          const uint32_t tacc = tmem_base + (uint32_t)(hh * 32);
+#pragma unroll
+          for (int kk = 0; kk < 4; ++kk) {
+            const uint32_t oa = (uint32_t)(hh * 128 * 128 + kk * 32), ob = (uint32_t)(kk * 32);
+            mma_tf32(tacc, tc05::desc_k_sw128(sH + oa), tc05::desc_k_sw128(sCh + ob), ta.idesc, kk != 0);
+            mma_tf32(tacc, tc05::desc_k_sw128(sH + oa), tc05::desc_k_sw128(sCl + ob), ta.idesc, 1);
+            mma_tf32(tacc, tc05::desc_k_sw128(sL + oa), tc05::desc_k_sw128(sCh + ob), ta.idesc, 1);
+          }
+        }
+        tc05::commit(done);
+        // refill the slot tile i-1 occupied with tile i+2 once every worker warp has finished its phase B
+        if (i >= 1) {
+          const int64_t tn = t + 2 * G;
+          if (tn < ntiles) {
+            const int j = i - 1;
+            tma::mbar_wait_backoff(&free_[j % kTcSlots], (uint32_t)((j / kTcSlots) & 1), 64);
+            tma::fence_proxy_async();
+            issue(j % kTcSlots, tn);
+          }
+        }
+      }
+    }
+  } else {
+    // ================= workers: thread = row =================
+    const float cmax = *cmax_s;
+    const float band2 = 4.76837158203125e-7f * cmax * cmax;   // 2^-21 max|c|^2: rounding of the final fmaf
+    const int q = warp & 3, hf = warp >> 2;   // row tid = hf*128 + q*32 + lane: TMEM lane quarter q of tile half hf
+    // split tile i: x -> hi (exact in tf32) + lo operand tiles; returns |x|^2 of this thread's row
+    auto split = [&](int i) -> float {
+      const int slot = i % kTcSlots;
+      mbar_wait(&full[slot], (uint32_t)((i / kTcSlots) & 1));
+      const unsigned char* tileb = smem + (size_t)slot * tile_bytes;
+      float nx = 0.f;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const uint32_t o = tma::sw128((uint32_t)tid, (uint32_t)j);
+        const float4 x = *reinterpret_cast<const float4*>(tileb + o);
+        const float4 h4 = make_float4(tf32_hi(x.x), tf32_hi(x.y), tf32_hi(x.z), tf32_hi(x.w));
+        *reinterpret_cast<float4*>(hi_tile + o) = h4;
+        *reinterpret_cast<float4*>(lo_tile + o) = make_float4(x.x - h4.x, x.y - h4.y, x.z - h4.z, x.w - h4.w);
+        nx = fmaf(x.x, x.x, nx); nx = fmaf(x.y, x.y, nx); nx = fmaf(x.z, x.z, nx); nx = fmaf(x.w, x.w, nx);
+      }
+      tma::fence_proxy_async();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(ready);
+      return nx;
+    };
+
+    unsigned long long my_changed = 0;
+    float nx_next = 0.f;
+    if ((int64_t)blockIdx.x < ntiles) nx_next = split(0);
+    int it = 0;
+    for (int64_t t = blockIdx.x; t < ntiles; t += G, ++it) {
+      const int slot = it % kTcSlots;
+      const int64_t p0 = t * tp;
+      const int npts = (int)(N - p0 < tp ? N - p0 : tp);
+      const int32_t old = (tid < npts) ? a.labels[p0 + tid] : -1;
+      const float nx = nx_next;
+      const unsigned char* tileb = smem + (size_t)slot * tile_bytes;
+
+      mbar_wait(done, (uint32_t)(it & 1));
+      tc05::fence_after();
+      float v[32];
+      tc05::ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(hf * 32), v);
+      tc05::ld_wait();
+      tc05::fence_before();
+      // the accumulator and the operand tiles are free again: split tile it+1 so its MMAs run under the work below
+      if (t + G < ntiles) nx_next = split(it + 1);
+
+      // ---- argmin with the exactness guard
+      int label = -1;
+      if (tid < npts) {
+        float best = __int_as_float(0x7f800000);
+#pragma unroll
+        for (int j4 = 0; j4 < KP / 4; ++j4) {
+          const float4 cc = reinterpret_cast<const float4*>(c2)[j4];
+          v[4 * j4 + 0] = fmaf(-2.f, v[4 * j4 + 0], cc.x);
+          v[4 * j4 + 1] = fmaf(-2.f, v[4 * j4 + 1], cc.y);
+          v[4 * j4 + 2] = fmaf(-2.f, v[4 * j4 + 2], cc.z);
+          v[4 * j4 + 3] = fmaf(-2.f, v[4 * j4 + 3], cc.w);
+          best = fminf(fminf(best, v[4 * j4 + 0]), fminf(v[4 * j4 + 1], fminf(v[4 * j4 + 2], v[4 * j4 + 3])));
+        }
+        // 2^-13 |x| max|c| covers twice the tf32x3 + fp32-chain dot error
+        const float thr = best + fmaf(1.220703125e-4f * cmax, sqrtf(nx), band2);
+        uint32_t cand = 0u;
+#pragma unroll
+        for (int j = 0; j < KP; ++j) cand |= (v[j] <= thr) ? (1u << j) : 0u;
+        label = cand ? __ffs((int)cand) - 1 : 0;   // cand == 0 only for NaN input (FFMA kernel: label 0)
+        if (cand & (cand - 1u)) {   // several centroids inside the error band: decide with the reference FMA chain
+          float4 xr[8];
+#pragma unroll
+          for (int j = 0; j < 8; ++j)
+            xr[j] = *reinterpret_cast<const float4*>(tileb + tma::sw128((uint32_t)tid, (uint32_t)j));
+          label = -1;
+          float bexact = 0.f;
+          while (cand) {
+            const int c = __ffs((int)cand) - 1;
+            cand &= cand - 1u;
+            const float4* cr = reinterpret_cast<const float4*>(cs + c * d);
+            float s0 = 0.f;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              const float4 cv = cr[j];
+              s0 = fmaf(xr[j].x, cv.x, s0);
+              s0 = fmaf(xr[j].y, cv.y, s0);
+              s0 = fmaf(xr[j].z, cv.z, s0);
+              s0 = fmaf(xr[j].w, cv.w, s0);
+            }
+            const float pd = fmaf(-2.f, s0, c2[c]);
+            if (label < 0 || pd < bexact) { bexact = pd; label = c; }
+          }
+        }
+        a.labels[p0 + tid] = label;
+        my_changed += (old != label);
+        if (update) atomicAdd(&cnt[label], 1);
+      }
+      __syncwarp();
+
+      // ---- phase B: centroid-sum update, lane = dimension.  The warp walks its 32 rows four at a time; a row's label
+      // is warp-uniform (read back from shared memory), so the accumulator row it updates is too, and the only
+      // hazards are equal labels inside a quad -- resolved in registers in row order, which keeps the summation
+      // order sequential while the four loads / stores of a quad stay independent (no 32-step dependent chain).
+      if (update) {
+        lbl[tid] = label < 0 ? 0 : label;   // rows past N are zero-filled by TMA: adding them to centroid 0 is a no-op
+        __syncwarp();
+        float* accw = acc + (size_t)warp * kd + lane;
+        const unsigned char* rows = tileb + (size_t)(warp * 32) * 128 + (lane & 3) * 4;
+        const int lc = lane >> 2;
+#pragma unroll 2
+        for (int r4 = 0; r4 < 8; ++r4) {
+          const int4 L = reinterpret_cast<const int4*>(lbl + warp * 32)[r4];
+          const int r = r4 * 4;
+          const float x0 = *reinterpret_cast<const float*>(rows + (r + 0) * 128 + ((lc ^ ((r + 0) & 7)) << 4));
+          const float x1 = *reinterpret_cast<const float*>(rows + (r + 1) * 128 + ((lc ^ ((r + 1) & 7)) << 4));
+          const float x2 = *reinterpret_cast<const float*>(rows + (r + 2) * 128 + ((lc ^ ((r + 2) & 7)) << 4));
+          const float x3 = *reinterpret_cast<const float*>(rows + (r + 3) * 128 + ((lc ^ ((r + 3) & 7)) << 4));
+          float* q0 = accw + L.x * d;
+          float* q1 = accw + L.y * d;
+          float* q2 = accw + L.z * d;
+          float* q3 = accw + L.w * d;
+          float a0 = *q0, a1 = *q1, a2 = *q2, a3 = *q3;
+          const float n0 = a0 + x0;
+          a1 = (L.y == L.x) ? n0 : a1;
+          const float n1 = a1 + x1;
+          a2 = (L.z == L.y) ? n1 : ((L.z == L.x) ? n0 : a2);
+          const float n2 = a2 + x2;
+          a3 = (L.w == L.z) ? n2 : ((L.w == L.y) ? n1 : ((L.w == L.x) ? n0 : a3));
+          const float n3 = a3 + x3;
+          *q0 = n0; *q1 = n1; *q2 = n2; *q3 = n3;
+        }
+      }
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&free_[slot]);
+      if (update && ((it + 1) % kFlush == 0)) {
+        asm volatile("bar.sync 1, 256;" ::: "memory");
+        for (int e = tid; e < kd; e += kTcWorkers) {
+          double s = 0.0;
+          for (int cpy = 0; cpy < a.ncopies; ++cpy) {
+            s += (double)acc[(size_t)cpy * kd + e];
+            acc[(size_t)cpy * kd + e] = 0.f;
+          }
+          dsum[e] += s;
+        }
+        asm volatile("bar.sync 1, 256;" ::: "memory");
+      }
+    }
+    my_changed = (unsigned long long)__reduce_add_sync(0xffffffffu, (unsigned)my_changed);
+    if (lane == 0 && my_changed) atomicAdd(a.n_changed, my_changed);
+  }
+
+  // ---------------- epilogue: per-CTA partials in double, fixed order
+  tc05::fence_before();
+  __syncthreads();
+  if (update) {
+    for (int e = tid; e < kd; e += kTcThreads) {
+      double s = dsum[e];
+      for (int cpy = 0; cpy < a.ncopies; ++cpy) s += (double)acc[(size_t)cpy * kd + e];
+      a.part_sums[(size_t)blockIdx.x * kd + e] = s;
+    }
+    for (int c = tid; c < k; c += kTcThreads) a.part_counts[(size_t)blockIdx.x * k + c] = cnt[c];
+  }
+  if (warp == kKmWarps) {
+    tc05::fence_after();
+    tc05::tmem_dealloc(tmem_base, 64);
+  }
+}
+
 __global__ void kmeans_reduce_partials_kernel(const double* __restrict__ part_sums,
                                               const long long* __restrict__ part_counts, int nblocks, int k, int d,
                                               double* __restrict__ sums, double* __restrict__ counts) {
@@ -474,6 +790,48 @@ static int km_run(const float* X, int64_t N, int d, const float* C, int k, int32
     if (rc != VC_OK) return rc;
   }
   cudaError_t e;
+  const char* tc_env = getenv("VAECLUST_KMEANS_TC");   // "0": keep the FFMA E-step (A/B checks)
+  if (d == 32 && assign && k >= 16 && k <= 32 && N < 2147483647LL - 256 && !(tc_env && tc_env[0] == '0')) {
+    // tensor-core E-step (kmeans_tc_kernel): x ring 96 KB | hi, lo operand tiles 64 KB | centroid hi / lo | accumulators
+    KmTcArgs ta;
+    memset(&ta, 0, sizeof(ta));
+    ta.kp = (k + 15) / 16 * 16;
+    size_t o = (size_t)kTcSlots * 256 * 32 * 4;
+    ta.off_lo = o;  o += 2 * (size_t)256 * 32 * 4;
+    ta.off_chi = o; o += 4096;
+    ta.off_clo = o; o += 4096;
+    KmArgs a2 = a;
+    a2.tp = 256;
+    a2.ncopies = update ? kKmWarps : 0;
+    a2.off_acc = o;  o += (size_t)a2.ncopies * k * d * 4;
+    o = (o + 7) & ~(size_t)7;
+    a2.off_dsum = o; o += update ? (size_t)k * d * 8 : 0;
+    a2.off_c = o;    o += (size_t)k * d * 4;
+    a2.off_c2 = o;   o += 32 * 4;
+    a2.off_cnt = o;  o += 32 * 4;
+    a2.off_bar = o;
+    ta.off_mbar = o; o += 128 + 256 * 4;   // barriers, tmem slot, max|c| ; labels of the tile
+    ta.a = a2;
+    ta.idesc = tc05::idesc(2 /* tf32 */, 128, ta.kp, 0, 0);
+    const size_t total = o + 1024;
+    int64_t g = sm_count();
+    const int64_t ntl = (N + 255) / 256;
+    if (g > ntl) g = ntl;
+    auto kern = ta.kp == 16 ? kmeans_tc_kernel<16> : kmeans_tc_kernel<32>;
+    e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)total);
+    if (e == cudaSuccess) {
+      kern<<<(int)g, kTcThreads, total, s>>>(ta, tm);
+      e = cudaGetLastError();
+    }
+    VC_REQUIRE(e == cudaSuccess, VC_ERR_CUDA, "%s: tensor-core launch failed: %s", who, cudaGetErrorString(e));
+    if (update) {
+      const int n = k * d;
+      kmeans_reduce_partials_kernel<<<(n + 127) / 128, 128, 0, s>>>(ps, pc, (int)g, k, d, sums, counts);
+      VC_LAUNCH_CHECK();
+    }
+    if (n_changed) VC_CUDA(cudaMemcpyAsync(n_changed, nchg, 8, cudaMemcpyDeviceToDevice, s));
+    return VC_OK;
+  }
   if (L.swz) {
     switch (d) {
       case 32: e = km_launch<8, true>(grid, L, s, a, tm); break;
