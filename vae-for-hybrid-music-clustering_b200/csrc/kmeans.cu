@@ -301,8 +301,8 @@ kmeans_assign_update_kernel(const KmArgs a, const __grid_constant__ CUtensorMap 
 struct KmTcArgs {
   KmArgs a;
   int kp;                      // k rounded up to a multiple of 16 (UMMA N)
-  size_t off_lo, off_chi, off_clo, off_mbar;
-  uint32_t idesc;
+  size_t off_lo, off_chi, off_mbar;
+  uint32_t idesc, idesc2;      // UMMA instruction descriptors for N = kp and N = 2*kp
 };
 
 __device__ __forceinline__ void mma_tf32(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc_,
@@ -319,7 +319,7 @@ __device__ __forceinline__ float tf32_hi(float v) { return __uint_as_float(__flo
 
 constexpr int kTcWorkers = 256;             // worker threads: thread = row of the 256-row tile
 constexpr int kTcThreads = kTcWorkers + 32; // + one warp whose lane 0 issues the TMA copies and the MMAs
-constexpr int kTcSlots = 3;                 // tile ring depth
+constexpr int kTcSlots = 4;                 // tile ring depth
 
 template <int KP>
 __global__ void __launch_bounds__(kTcThreads, 1)
@@ -336,10 +336,9 @@ kmeans_tc_kernel(const KmTcArgs ta, const __grid_constant__ CUtensorMap tmap) {
   float* cs = reinterpret_cast<float*>(smem + a.off_c);
   float* c2 = reinterpret_cast<float*>(smem + a.off_c2);   // [KP], +inf beyond k
   int* cnt = reinterpret_cast<int*>(smem + a.off_cnt);
-  unsigned char* hi_tile = smem + ta.off_lo;               // hi | lo operand tiles of the tile being multiplied
-  unsigned char* lo_tile = hi_tile + tile_bytes;
-  unsigned char* chi = smem + ta.off_chi;
-  unsigned char* clo = smem + ta.off_clo;
+  unsigned char* lo_tile = smem + ta.off_lo;               // lo operand of the tile being multiplied
+  unsigned char* chi = smem + ta.off_chi;                  // [chi ; clo]: 2*KP rows, one B operand of N = 2*KP
+  unsigned char* clo = chi + (size_t)KP * 128;
   uint64_t* full = reinterpret_cast<uint64_t*>(smem + ta.off_mbar);  // [3] TMA -> workers
   uint64_t* free_ = full + kTcSlots;                                 // [3] workers -> TMA: ring slot consumed
   uint64_t* ready = free_ + kTcSlots;                                // workers -> MMA: hi/lo operands written
@@ -360,7 +359,7 @@ kmeans_tc_kernel(const KmTcArgs ta, const __grid_constant__ CUtensorMap tmap) {
     mbar_init(done, 1);
     tma::mbar_fence_init();
   }
-  if (warp == kKmWarps) tc05::tmem_alloc(tmem_slot, 64);
+  if (warp == kKmWarps) tc05::tmem_alloc(tmem_slot, 4 * KP);
   for (int i = tid; i < kd; i += kTcThreads) cs[i] = a.C[i];
   for (int i = tid; i < k; i += kTcThreads) cnt[i] = 0;
   // centroid operands: [KP rows][32 floats], K-major with the 128-byte swizzle, split into hi / lo; padding rows zero
@@ -410,26 +409,28 @@ kmeans_tc_kernel(const KmTcArgs ta, const __grid_constant__ CUtensorMap tmap) {
         const int64_t t = (int64_t)blockIdx.x + (int64_t)s * G;
         if (t < ntiles) issue(s, t);
       }
-      const uint32_t sH = tma::s32(hi_tile), sL = tma::s32(lo_tile), sCh = tma::s32(chi), sCl = tma::s32(clo);
+      const uint32_t sL = tma::s32(lo_tile), sCh = tma::s32(chi);
       int i = 0;
       for (int64_t t = blockIdx.x; t < ntiles; t += G, ++i) {
         tma::mbar_wait_backoff(ready, (uint32_t)(i & 1), 64);
         tc05::fence_after();
+        // A = the raw fp32 tile: kind::tf32 reads the upper 19 bits of each word, i.e. exactly hi.  One N = 2*KP
+        // MMA gives hi.chi | hi.clo side by side (A is fetched once); lo.chi accumulates onto the first KP columns.
+        const uint32_t sX = tma::s32(smem + (size_t)(i % kTcSlots) * tile_bytes);
 #pragma unroll
         for (int hh = 0; hh < 2; ++hh) {
-          const uint32_t tacc = tmem_base + (uint32_t)(hh * 32);
+          const uint32_t tacc = tmem_base + (uint32_t)(hh * 2 * KP);
 #pragma unroll
           for (int kk = 0; kk < 4; ++kk) {
             const uint32_t oa = (uint32_t)(hh * 128 * 128 + kk * 32), ob = (uint32_t)(kk * 32);
-            mma_tf32(tacc, tc05::desc_k_sw128(sH + oa), tc05::desc_k_sw128(sCh + ob), ta.idesc, kk != 0);
-            mma_tf32(tacc, tc05::desc_k_sw128(sH + oa), tc05::desc_k_sw128(sCl + ob), ta.idesc, 1);
+            mma_tf32(tacc, tc05::desc_k_sw128(sX + oa), tc05::desc_k_sw128(sCh + ob), ta.idesc2, kk != 0);
             mma_tf32(tacc, tc05::desc_k_sw128(sL + oa), tc05::desc_k_sw128(sCh + ob), ta.idesc, 1);
           }
         }
         tc05::commit(done);
-        // refill the slot tile i-1 occupied with tile i+2 once every worker warp has finished its phase B
+        // refill the slot tile i-1 occupied (tile i-1+kTcSlots) once every worker warp has finished its phase B
         if (i >= 1) {
-          const int64_t tn = t + 2 * G;
+          const int64_t tn = t + (kTcSlots - 1) * G;
           if (tn < ntiles) {
             const int j = i - 1;
             tma::mbar_wait_backoff(&free_[j % kTcSlots], (uint32_t)((j / kTcSlots) & 1), 64);
@@ -444,7 +445,7 @@ kmeans_tc_kernel(const KmTcArgs ta, const __grid_constant__ CUtensorMap tmap) {
     const float cmax = *cmax_s;
     const float band2 = 4.76837158203125e-7f * cmax * cmax;   // 2^-21 max|c|^2: rounding of the final fmaf
     const int q = warp & 3, hf = warp >> 2;   // row tid = hf*128 + q*32 + lane: TMEM lane quarter q of tile half hf
-    // split tile i: x -> hi (exact in tf32) + lo operand tiles; returns |x|^2 of this thread's row
+    // split tile i: write the lo operand tile (x - hi); returns |x|^2 of this thread's row
     auto split = [&](int i) -> float {
       const int slot = i % kTcSlots;
       mbar_wait(&full[slot], (uint32_t)((i / kTcSlots) & 1));
@@ -454,9 +455,8 @@ kmeans_tc_kernel(const KmTcArgs ta, const __grid_constant__ CUtensorMap tmap) {
       for (int j = 0; j < 8; ++j) {
         const uint32_t o = tma::sw128((uint32_t)tid, (uint32_t)j);
         const float4 x = *reinterpret_cast<const float4*>(tileb + o);
-        const float4 h4 = make_float4(tf32_hi(x.x), tf32_hi(x.y), tf32_hi(x.z), tf32_hi(x.w));
-        *reinterpret_cast<float4*>(hi_tile + o) = h4;
-        *reinterpret_cast<float4*>(lo_tile + o) = make_float4(x.x - h4.x, x.y - h4.y, x.z - h4.z, x.w - h4.w);
+        *reinterpret_cast<float4*>(lo_tile + o) =
+            make_float4(x.x - tf32_hi(x.x), x.y - tf32_hi(x.y), x.z - tf32_hi(x.z), x.w - tf32_hi(x.w));
         nx = fmaf(x.x, x.x, nx); nx = fmaf(x.y, x.y, nx); nx = fmaf(x.z, x.z, nx); nx = fmaf(x.w, x.w, nx);
       }
       tma::fence_proxy_async();
@@ -480,8 +480,21 @@ kmeans_tc_kernel(const KmTcArgs ta, const __grid_constant__ CUtensorMap tmap) {
       mbar_wait(done, (uint32_t)(it & 1));
       tc05::fence_after();
       float v[32];
-      tc05::ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(hf * 32), v);
-      tc05::ld_wait();
+      {
+        const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(hf * 2 * KP);
+        tc05::ld_32x32(taddr, v);
+        if (KP == 32) {
+          float v2[32];
+          tc05::ld_32x32(taddr + 32, v2);
+          tc05::ld_wait();
+#pragma unroll
+          for (int j = 0; j < 32; ++j) v[j] += v2[j];
+        } else {
+          tc05::ld_wait();
+#pragma unroll
+          for (int j = 0; j < 16; ++j) v[j] += v[16 + j];
+        }
+      }
       tc05::fence_before();
       // the accumulator and the operand tiles are free again: split tile it+1 so its MMAs run under the work below
       if (t + G < ntiles) nx_next = split(it + 1);
@@ -600,7 +613,7 @@ kmeans_tc_kernel(const KmTcArgs ta, const __grid_constant__ CUtensorMap tmap) {
   }
   if (warp == kKmWarps) {
     tc05::fence_after();
-    tc05::tmem_dealloc(tmem_base, 64);
+    tc05::tmem_dealloc(tmem_base, 4 * KP);
   }
 }
 
@@ -792,14 +805,13 @@ static int km_run(const float* X, int64_t N, int d, const float* C, int k, int32
   cudaError_t e;
   const char* tc_env = getenv("VAECLUST_KMEANS_TC");   // "0": keep the FFMA E-step (A/B checks)
   if (d == 32 && assign && k >= 16 && k <= 32 && N < 2147483647LL - 256 && !(tc_env && tc_env[0] == '0')) {
-    // tensor-core E-step (kmeans_tc_kernel): x ring 96 KB | hi, lo operand tiles 64 KB | centroid hi / lo | accumulators
+    // tensor-core E-step (kmeans_tc_kernel): x ring 128 KB | lo operand tile 32 KB | centroid hi ; lo | accumulators
     KmTcArgs ta;
     memset(&ta, 0, sizeof(ta));
     ta.kp = (k + 15) / 16 * 16;
     size_t o = (size_t)kTcSlots * 256 * 32 * 4;
-    ta.off_lo = o;  o += 2 * (size_t)256 * 32 * 4;
-    ta.off_chi = o; o += 4096;
-    ta.off_clo = o; o += 4096;
+    ta.off_lo = o;  o += (size_t)256 * 32 * 4;
+    ta.off_chi = o; o += 8192;
     KmArgs a2 = a;
     a2.tp = 256;
     a2.ncopies = update ? kKmWarps : 0;
@@ -813,6 +825,7 @@ static int km_run(const float* X, int64_t N, int d, const float* C, int k, int32
     ta.off_mbar = o; o += 128 + 256 * 4;   // barriers, tmem slot, max|c| ; labels of the tile
     ta.a = a2;
     ta.idesc = tc05::idesc(2 /* tf32 */, 128, ta.kp, 0, 0);
+    ta.idesc2 = tc05::idesc(2, 128, 2 * ta.kp, 0, 0);
     const size_t total = o + 1024;
     int64_t g = sm_count();
     const int64_t ntl = (N + 255) / 256;
