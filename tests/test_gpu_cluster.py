@@ -34,9 +34,9 @@ def test_kmeans_explicit_init_matches_oracle(n, d, k):
 
 
 @pytest.mark.parametrize("n,k,scale", [(30001, 16, 1.0), (30001, 17, 1.0), (12345, 31, 1e3), (50000, 32, 1e-3),
-                                       (255, 24, 1.0), (400003, 32, 1.0)])
+                                       (255, 24, 1.0), (400003, 32, 1.0), (20000, 5, 1.0), (77777, 9, 1.0)])
 def test_kmeans_tensor_core_estep_d32(n, k, scale, monkeypatch):
-    """d == 32, 16 <= k <= 32 runs the tcgen05 E-step (tf32 hi/lo split + exact-recompute guard).  Its labels must be
+    """d == 32, 5 <= k <= 32 runs the tcgen05 E-step (tf32 hi/lo split + exact-recompute guard).  Its labels must be
     bit-identical to the FFMA kernel's (VAECLUST_KMEANS_TC=0) at every Lloyd iteration from the same centres -- ragged
     tile counts, several tiles per CTA, large / small magnitudes, points on bisectors -- and the first E-step must
     equal the oracle's up to rounding-level ties."""

@@ -54,8 +54,8 @@ static KmSmem km_layout(int k, int d, int update) {
   L.off_c = o;    o += (size_t)k * d * 4;
   L.off_c2 = o;   o += (size_t)k * 4;
   L.off_cnt = o;  o += (size_t)k * 4;
-  o = (o + 7) & ~(size_t)7;
-  L.off_bar = o;  o += 16;
+  o = (o + 15) & ~(size_t)15;
+  L.off_bar = o;  o += 16 + 256 * 4;   // two mbarriers; labels of the current tile (lane = dimension update)
   L.total = o + 1024;  // slack: the tile ring is aligned to 1024 B by hand (swizzle atoms)
   return L;
 }
@@ -75,7 +75,41 @@ __device__ __forceinline__ float4 row_chunk(const unsigned char* tileb, int tp, 
 }
 
 // D4 = d/4 when compile-time (register-resident row), 0 = generic d.
-template <int D4, bool SW>
+// Centroid-sum update of one warp's 32 rows with lane = dimension (tiles in the TMA 128-byte-swizzle layout).  A row's
+// label is warp-uniform (read back from shared memory), so the accumulator row it updates is too, and the only
+// hazards are equal labels inside a quad of rows -- resolved in registers in row order, which keeps the summation
+// order sequential while the four loads / stores of a quad stay independent (no 32-step dependent chain, no
+// __syncwarp).  accw = this warp's accumulator copy + lane, rows = the warp's first row of the panel + (lane%4)*4 bytes.
+__device__ __forceinline__ void update_rows_lane_dim(float* accw, const unsigned char* rows, const int* lblw, int lane,
+                                                     int d) {
+  const int lc = lane >> 2;
+#pragma unroll 2
+  for (int r4 = 0; r4 < 8; ++r4) {
+    const int4 L = reinterpret_cast<const int4*>(lblw)[r4];
+    const int r = r4 * 4;
+    const float x0 = *reinterpret_cast<const float*>(rows + (r + 0) * 128 + ((lc ^ ((r + 0) & 7)) << 4));
+    const float x1 = *reinterpret_cast<const float*>(rows + (r + 1) * 128 + ((lc ^ ((r + 1) & 7)) << 4));
+    const float x2 = *reinterpret_cast<const float*>(rows + (r + 2) * 128 + ((lc ^ ((r + 2) & 7)) << 4));
+    const float x3 = *reinterpret_cast<const float*>(rows + (r + 3) * 128 + ((lc ^ ((r + 3) & 7)) << 4));
+    float* q0 = accw + L.x * d;
+    float* q1 = accw + L.y * d;
+    float* q2 = accw + L.z * d;
+    float* q3 = accw + L.w * d;
+    float a0 = *q0, a1 = *q1, a2 = *q2, a3 = *q3;
+    const float n0 = a0 + x0;
+    a1 = (L.y == L.x) ? n0 : a1;
+    const float n1 = a1 + x1;
+    a2 = (L.z == L.y) ? n1 : ((L.z == L.x) ? n0 : a2);
+    const float n2 = a2 + x2;
+    a3 = (L.w == L.z) ? n2 : ((L.w == L.y) ? n1 : ((L.w == L.x) ? n0 : a3));
+    const float n3 = a3 + x3;
+    *q0 = n0; *q1 = n1; *q2 = n2; *q3 = n3;
+  }
+}
+
+
+// LD: lane = dimension centroid-sum update (update_rows_lane_dim) instead of the diagonal one.
+template <int D4, bool SW, bool LD>
 __global__ void __launch_bounds__(kKmThreads)
 kmeans_assign_update_kernel(const KmArgs a, const __grid_constant__ CUtensorMap tmap) {
   extern __shared__ unsigned char smem_raw[];
@@ -223,7 +257,16 @@ kmeans_assign_update_kernel(const KmArgs a, const __grid_constant__ CUtensorMap 
       // "diagonal" update: lane = its own point; at step j it handles one dimension of that point chosen so that
       // the 32 lanes of each LDS/STS touch 32 different banks and, even when labels coincide, 32 different
       // accumulator words (a plain read-modify-write is race free; one instruction serves 32 points).
-      if (SW) {
+      if (SW && LD) {
+        // lane = dimension of a 32-wide panel; rows past N are zero-filled by TMA, so they may add to centroid 0
+        int* lbl = reinterpret_cast<int*>(smem + a.off_bar + 16);
+        lbl[tid] = label < 0 ? 0 : label;
+        __syncwarp();
+        for (int p = 0; p < d / 32 && warp * 32 < tp; ++p)
+          update_rows_lane_dim(acc + (size_t)warp * kd + p * 32 + lane,
+                               tileb + (size_t)p * tp * 128 + (size_t)(warp * 32) * 128 + (lane & 3) * 4,
+                               lbl + warp * 32, lane, d);
+      } else if (SW) {
         // physical word w = (j + lane) % 32 of the row's 128-byte panel slice holds logical dimension
         // ((w/4) ^ (row%8))*4 + w%4 ; for a fixed j this map is injective over the lanes.
         float* my = acc + (size_t)warp * kd + (label >= 0 ? label * d : 0);
@@ -290,14 +333,21 @@ kmeans_assign_update_kernel(const KmArgs a, const __grid_constant__ CUtensorMap 
 }
 
 // ---------------------------------------------------------------------------------------------------------------
-// Tensor-core E-step for d == 32 and 16 <= k <= 32, where the FFMA version is compute-bound (2kd FLOP per point).
+// Tensor-core E-step for d == 32 and 5 <= k <= 32 (k padded to KP = 16 or 32 with infinitely distant centroids), where the
+// FFMA version is compute-bound (2kd FLOP per point).
 // The 256 x 32 fp32 tile the TMA engine delivered is already a K-major, 128-byte-swizzled UMMA operand, so the
 // distance GEMM  dot[256, k] = X_tile * C^T  runs on tcgen05 (kind::tf32) with the accumulator in tensor memory.
 // TF32 alone (10 mantissa bits) cannot reproduce sklearn's fp32 labels, so every value is split x = hi + lo with
-// hi = x with the low 13 mantissa bits cleared (exact in tf32): dot ~= hi.chi + hi.clo + lo.chi, error <= 2^-16 |x||c|.
-// Labels stay bit-exact through a guard: every centroid whose tensor-core distance lies within 2^-13 |x| max|c| of the
-// best one is re-evaluated with the reference FMA chain (the arithmetic of kmeans_assign_update_kernel) and the argmin
-// is taken over those exact values in index order; all other centroids are provably farther.  Phase B is unchanged.
+// hi = x with the low 13 mantissa bits cleared: dot ~= hi.chi + hi.clo + lo.chi, error <= 2^-16 |x||c|.
+//  * kind::tf32 ignores the low 13 bits of each operand word, so the raw tile IS the hi operand; the workers only
+//    write the lo tile (x - hi).  [chi ; clo] is one B operand of N = 2*KP, so hi.chi | hi.clo come out of a single
+//    pass over A; lo.chi accumulates onto the first KP columns and the epilogue adds the two column groups.
+//  * Labels stay bit-identical to kmeans_assign_update_kernel through a guard: every centroid whose tensor-core
+//    distance lies within 2^-13 |x| max|c| (+ 2^-21 max|c|^2) of the best one is re-evaluated with the reference FMA
+//    chain and the argmin taken over those exact values in index order; all other centroids are provably farther.
+//  * Roles: warps 0-7 = workers (thread = row: split, argmin, centroid-sum update with lane = dimension), warp 8 lane 0
+//    = TMA + MMA issuer.  mbarriers full/free_ (tile ring), ready/done (operands / accumulator); the MMAs of tile
+//    i+1 run under the argmin and update of tile i.
 struct KmTcArgs {
   KmArgs a;
   int kp;                      // k rounded up to a multiple of 16 (UMMA N)
@@ -317,17 +367,17 @@ __device__ __forceinline__ void mma_tf32(uint32_t tmem_d, uint64_t adesc, uint64
 
 __device__ __forceinline__ float tf32_hi(float v) { return __uint_as_float(__float_as_uint(v) & 0xFFFFE000u); }
 
-constexpr int kTcWorkers = 256;             // worker threads: thread = row of the 256-row tile
-constexpr int kTcThreads = kTcWorkers + 32; // + one warp whose lane 0 issues the TMA copies and the MMAs
-constexpr int kTcSlots = 4;                 // tile ring depth
+__host__ __device__ constexpr int tc_slots(int tp) { return tp == 128 ? 3 : 4; }   // tile ring depth
 
-template <int KP>
-__global__ void __launch_bounds__(kTcThreads, 1)
+// TP rows per tile (128 or 256): TP worker threads (thread = row) + one warp whose lane 0 issues the TMA copies and
+// the MMAs.  TP = 128 fits two CTAs per SM, whose pipelines drift apart and hide each other's barrier / TMEM waits.
+template <int KP, int TP>
+__global__ void __launch_bounds__(TP + 32, 256 / TP)
 kmeans_tc_kernel(const KmTcArgs ta, const __grid_constant__ CUtensorMap tmap) {
   extern __shared__ unsigned char smem_raw[];
   unsigned char* smem = smem_raw + ((1024u - (tma::s32(smem_raw) & 1023u)) & 1023u);
   const KmArgs& a = ta.a;
-  constexpr int d = 32, tp = 256;
+  constexpr int d = 32, tp = TP, NW = TP / 32, kTcWorkers = TP, kTcThreads = TP + 32, kTcSlots = tc_slots(TP);
   const int k = a.k, update = a.update;
   const int64_t N = a.N;
   constexpr size_t tile_bytes = (size_t)tp * d * 4;
@@ -354,12 +404,12 @@ kmeans_tc_kernel(const KmTcArgs ta, const __grid_constant__ CUtensorMap tmap) {
 
   if (tid == 0) {
     tma::prefetch_map(&tmap);
-    for (int s = 0; s < kTcSlots; ++s) { mbar_init(&full[s], 1); mbar_init(&free_[s], kKmWarps); }
-    mbar_init(ready, kKmWarps);
+    for (int s = 0; s < kTcSlots; ++s) { mbar_init(&full[s], 1); mbar_init(&free_[s], NW); }
+    mbar_init(ready, NW);
     mbar_init(done, 1);
     tma::mbar_fence_init();
   }
-  if (warp == kKmWarps) tc05::tmem_alloc(tmem_slot, 4 * KP);
+  if (warp == NW) tc05::tmem_alloc(tmem_slot, (TP / 128) * 2 * KP);
   for (int i = tid; i < kd; i += kTcThreads) cs[i] = a.C[i];
   for (int i = tid; i < k; i += kTcThreads) cnt[i] = 0;
   // centroid operands: [KP rows][32 floats], K-major with the 128-byte swizzle, split into hi / lo; padding rows zero
@@ -380,7 +430,7 @@ kmeans_tc_kernel(const KmTcArgs ta, const __grid_constant__ CUtensorMap tmap) {
   __syncthreads();
   tc05::fence_after();
   const uint32_t tmem_base = *tmem_slot;
-  for (int c = warp; c < KP; c += kKmWarps + 1) {
+  for (int c = warp; c < KP; c += NW + 1) {
     float s = 0.f;
     if (c < k) {
       for (int j = lane; j < d; j += 32) s += cs[c * d + j] * cs[c * d + j];
@@ -398,7 +448,7 @@ kmeans_tc_kernel(const KmTcArgs ta, const __grid_constant__ CUtensorMap tmap) {
   }
   __syncthreads();
 
-  if (warp == kKmWarps) {
+  if (warp == NW) {
     // ================= copy + MMA issuer (one thread) =================
     if (lane == 0) {
       auto issue = [&](int slot, int64_t t) {
@@ -418,7 +468,7 @@ kmeans_tc_kernel(const KmTcArgs ta, const __grid_constant__ CUtensorMap tmap) {
         // MMA gives hi.chi | hi.clo side by side (A is fetched once); lo.chi accumulates onto the first KP columns.
         const uint32_t sX = tma::s32(smem + (size_t)(i % kTcSlots) * tile_bytes);
 #pragma unroll
-        for (int hh = 0; hh < 2; ++hh) {
+        for (int hh = 0; hh < TP / 128; ++hh) {
           const uint32_t tacc = tmem_base + (uint32_t)(hh * 2 * KP);
 #pragma unroll
           for (int kk = 0; kk < 4; ++kk) {
@@ -548,43 +598,17 @@ kmeans_tc_kernel(const KmTcArgs ta, const __grid_constant__ CUtensorMap tmap) {
       }
       __syncwarp();
 
-      // ---- phase B: centroid-sum update, lane = dimension.  The warp walks its 32 rows four at a time; a row's label
-      // is warp-uniform (read back from shared memory), so the accumulator row it updates is too, and the only
-      // hazards are equal labels inside a quad -- resolved in registers in row order, which keeps the summation
-      // order sequential while the four loads / stores of a quad stay independent (no 32-step dependent chain).
+      // ---- phase B: centroid-sum update, lane = dimension (update_rows_lane_dim)
       if (update) {
         lbl[tid] = label < 0 ? 0 : label;   // rows past N are zero-filled by TMA: adding them to centroid 0 is a no-op
         __syncwarp();
-        float* accw = acc + (size_t)warp * kd + lane;
-        const unsigned char* rows = tileb + (size_t)(warp * 32) * 128 + (lane & 3) * 4;
-        const int lc = lane >> 2;
-#pragma unroll 2
-        for (int r4 = 0; r4 < 8; ++r4) {
-          const int4 L = reinterpret_cast<const int4*>(lbl + warp * 32)[r4];
-          const int r = r4 * 4;
-          const float x0 = *reinterpret_cast<const float*>(rows + (r + 0) * 128 + ((lc ^ ((r + 0) & 7)) << 4));
-          const float x1 = *reinterpret_cast<const float*>(rows + (r + 1) * 128 + ((lc ^ ((r + 1) & 7)) << 4));
-          const float x2 = *reinterpret_cast<const float*>(rows + (r + 2) * 128 + ((lc ^ ((r + 2) & 7)) << 4));
-          const float x3 = *reinterpret_cast<const float*>(rows + (r + 3) * 128 + ((lc ^ ((r + 3) & 7)) << 4));
-          float* q0 = accw + L.x * d;
-          float* q1 = accw + L.y * d;
-          float* q2 = accw + L.z * d;
-          float* q3 = accw + L.w * d;
-          float a0 = *q0, a1 = *q1, a2 = *q2, a3 = *q3;
-          const float n0 = a0 + x0;
-          a1 = (L.y == L.x) ? n0 : a1;
-          const float n1 = a1 + x1;
-          a2 = (L.z == L.y) ? n1 : ((L.z == L.x) ? n0 : a2);
-          const float n2 = a2 + x2;
-          a3 = (L.w == L.z) ? n2 : ((L.w == L.y) ? n1 : ((L.w == L.x) ? n0 : a3));
-          const float n3 = a3 + x3;
-          *q0 = n0; *q1 = n1; *q2 = n2; *q3 = n3;
-        }
+        update_rows_lane_dim(acc + (size_t)warp * kd + lane, tileb + (size_t)(warp * 32) * 128 + (lane & 3) * 4,
+                             lbl + warp * 32, lane, d);
       }
       __syncwarp();
       if (lane == 0) mbar_arrive(&free_[slot]);
       if (update && ((it + 1) % kFlush == 0)) {
-        asm volatile("bar.sync 1, 256;" ::: "memory");
+        asm volatile("bar.sync 1, %0;" ::"n"(TP) : "memory");
         for (int e = tid; e < kd; e += kTcWorkers) {
           double s = 0.0;
           for (int cpy = 0; cpy < a.ncopies; ++cpy) {
@@ -593,7 +617,7 @@ kmeans_tc_kernel(const KmTcArgs ta, const __grid_constant__ CUtensorMap tmap) {
           }
           dsum[e] += s;
         }
-        asm volatile("bar.sync 1, 256;" ::: "memory");
+        asm volatile("bar.sync 1, %0;" ::"n"(TP) : "memory");
       }
     }
     my_changed = (unsigned long long)__reduce_add_sync(0xffffffffu, (unsigned)my_changed);
@@ -611,9 +635,9 @@ kmeans_tc_kernel(const KmTcArgs ta, const __grid_constant__ CUtensorMap tmap) {
     }
     for (int c = tid; c < k; c += kTcThreads) a.part_counts[(size_t)blockIdx.x * k + c] = cnt[c];
   }
-  if (warp == kKmWarps) {
+  if (warp == NW) {
     tc05::fence_after();
-    tc05::tmem_dealloc(tmem_base, 4 * KP);
+    tc05::tmem_dealloc(tmem_base, (TP / 128) * 2 * KP);
   }
 }
 
@@ -761,9 +785,9 @@ extern "C" size_t vc_kmeans_workspace_bytes(int k, int d) {
   return pd + pc + 64;
 }
 
-template <int D4, bool SW>
+template <int D4, bool SW, bool LD = false>
 static cudaError_t km_launch(int grid, const KmSmem& L, cudaStream_t s, const KmArgs& a, const CUtensorMap& tm) {
-  auto kern = kmeans_assign_update_kernel<D4, SW>;
+  auto kern = kmeans_assign_update_kernel<D4, SW, LD>;
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L.total);
   if (e != cudaSuccess) return e;
   kern<<<grid, kKmThreads, L.total, s>>>(a, tm);
@@ -804,19 +828,21 @@ static int km_run(const float* X, int64_t N, int d, const float* C, int k, int32
   }
   cudaError_t e;
   const char* tc_env = getenv("VAECLUST_KMEANS_TC");   // "0": keep the FFMA E-step (A/B checks)
-  if (d == 32 && assign && k >= 16 && k <= 32 && N < 2147483647LL - 256 && !(tc_env && tc_env[0] == '0')) {
+  const int tc_min = 11;   // below, the FFMA kernel is faster (50M x 32: k=8 1.94 vs 2.21 ms, k=12 2.38 vs 2.23 ms)
+  if (d == 32 && assign && k >= tc_min && k <= 32 && N < 2147483647LL - 256 && !(tc_env && tc_env[0] == '0')) {
     // tensor-core E-step (kmeans_tc_kernel): x ring 128 KB | lo operand tile 32 KB | centroid hi ; lo | accumulators
     KmTcArgs ta;
     memset(&ta, 0, sizeof(ta));
-    ta.kp = (k + 15) / 16 * 16;
-    size_t o = (size_t)kTcSlots * 256 * 32 * 4;
-    ta.off_lo = o;  o += (size_t)256 * 32 * 4;
-    ta.off_chi = o; o += 8192;
+    ta.kp = k <= 16 ? 16 : 32;
+    const int TP = 256;   // rows per tile; 128 (two CTAs per SM) measured 2 % slower on 50M x 32
+    const size_t tile_b = (size_t)TP * 32 * 4;
+    size_t o = (size_t)tc_slots(TP) * tile_b;
+    ta.off_lo = o;  o += tile_b;
+    ta.off_chi = o; o += (size_t)2 * ta.kp * 128;
     KmArgs a2 = a;
-    a2.tp = 256;
-    a2.ncopies = update ? kKmWarps : 0;
+    a2.tp = TP;
+    a2.ncopies = update ? TP / 32 : 0;
     a2.off_acc = o;  o += (size_t)a2.ncopies * k * d * 4;
-    o = (o + 7) & ~(size_t)7;
     a2.off_dsum = o; o += update ? (size_t)k * d * 8 : 0;
     a2.off_c = o;    o += (size_t)k * d * 4;
     a2.off_c2 = o;   o += 32 * 4;
@@ -827,13 +853,22 @@ static int km_run(const float* X, int64_t N, int d, const float* C, int k, int32
     ta.idesc = tc05::idesc(2 /* tf32 */, 128, ta.kp, 0, 0);
     ta.idesc2 = tc05::idesc(2, 128, 2 * ta.kp, 0, 0);
     const size_t total = o + 1024;
-    int64_t g = sm_count();
-    const int64_t ntl = (N + 255) / 256;
+    CUtensorMap tmt;
+    {
+      const uint64_t dims[2] = {(uint64_t)d, (uint64_t)N};
+      const uint64_t strides[1] = {(uint64_t)d * 4};
+      const uint32_t box[2] = {32u, (uint32_t)TP};
+      int rc = tma::make_map(&tmt, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, X, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B);
+      if (rc != VC_OK) return rc;
+    }
+    int64_t g = (int64_t)sm_count() * (256 / TP);
+    const int64_t ntl = (N + TP - 1) / TP;
     if (g > ntl) g = ntl;
-    auto kern = ta.kp == 16 ? kmeans_tc_kernel<16> : kmeans_tc_kernel<32>;
+    auto kern = TP == 128 ? (ta.kp == 16 ? kmeans_tc_kernel<16, 128> : kmeans_tc_kernel<32, 128>)
+                          : (ta.kp == 16 ? kmeans_tc_kernel<16, 256> : kmeans_tc_kernel<32, 256>);
     e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)total);
     if (e == cudaSuccess) {
-      kern<<<(int)g, kTcThreads, total, s>>>(ta, tm);
+      kern<<<(int)g, TP + 32, total, s>>>(ta, tmt);
       e = cudaGetLastError();
     }
     VC_REQUIRE(e == cudaSuccess, VC_ERR_CUDA, "%s: tensor-core launch failed: %s", who, cudaGetErrorString(e));
@@ -845,7 +880,15 @@ static int km_run(const float* X, int64_t N, int d, const float* C, int k, int32
     if (n_changed) VC_CUDA(cudaMemcpyAsync(n_changed, nchg, 8, cudaMemcpyDeviceToDevice, s));
     return VC_OK;
   }
-  if (L.swz) {
+  if (L.swz && assign) {
+    // lane = dimension update; labels given by the caller (assign == 0) may be out of range, which only the diagonal
+    // form's per-lane guard skips
+    switch (d) {
+      case 32: e = km_launch<8, true, true>(grid, L, s, a, tm); break;
+      case 64: e = km_launch<16, true, true>(grid, L, s, a, tm); break;
+      default: e = km_launch<0, true, true>(grid, L, s, a, tm); break;
+    }
+  } else if (L.swz) {
     switch (d) {
       case 32: e = km_launch<8, true>(grid, L, s, a, tm); break;
       case 64: e = km_launch<16, true>(grid, L, s, a, tm); break;
