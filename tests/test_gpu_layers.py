@@ -173,6 +173,9 @@ def _check_bf16(fn_ours, fn_ref, x, w, b):
 
 @pytest.mark.parametrize("M,N,K,relu", [(64, 256, 470, True), (17, 16, 256, False), (3, 700, 33, True),
                                         (64, 256, 8200, True), (64, 4100, 256, True),
+                                        # latent-head / lyrics-branch shapes: the one-launch mma.sync kernel
+                                        (64, 256, 384, True), (64, 256, 161, True), (64, 32, 256, False),
+                                        (64, 256, 32, True), (64, 128, 256, True), (7, 33, 50, False), (200, 9, 17, True),
                                         # big-matrix shapes take the skinny kernels (fp32 weight read in place)
                                         (64, 256, 16640, True), (64, 16500, 256, True), (50, 256, 16644, False)])
 def test_linear_bf16(M, N, K, relu, bf16_mode):

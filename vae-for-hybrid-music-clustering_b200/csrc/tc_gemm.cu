@@ -274,6 +274,9 @@ bool skinny_gemm_supported(int op, int B, int Cin, int Cout, const void* in0, co
 size_t skinny_gemm_workspace(int op, int B, int Cin, int Cout);
 int skinny_gemm_run(int op, const float* in0, const float* in1, const float* bias, float* out, int B, int Cin, int Cout,
                     int relu, void* ws, size_t wsb, cudaStream_t s);
+bool small_linear_supported(int op, int B, int Cin, int Cout);   // small_linear.cu
+int small_linear_run(int op, const float* in0, const float* in1, const float* bias, float* out, int B, int Cin, int Cout,
+                     int relu, cudaStream_t s);
 bool conv_wgrad_igemm_supported(int op, int B, int Cin, int H, int W, int Cout);   // conv_wgrad_igemm.cu
 size_t conv_wgrad_igemm_workspace(int op, int B, int Cin, int H, int W, int Cout);
 int conv_wgrad_igemm_run(int op, const float* dy, const float* x, float* dw, int B, int Cin, int H, int W, int Cout,
@@ -392,6 +395,8 @@ extern "C" int vc_dense_op(int op, int precision, const float* in0, const float*
                             as_stream(stream));
     if (H == 1 && W == 1 && skinny_gemm_supported(op, B, Cin, Cout, in0, in1))  // huge fp32 matrix read in place
       return skinny_gemm_run(op, in0, in1, bias, out, B, Cin, Cout, relu, workspace, workspace_bytes, as_stream(stream));
+    if (H == 1 && W == 1 && small_linear_supported(op, B, Cin, Cout))  // latency-bound: one mma.sync launch, no staging
+      return small_linear_run(op, in0, in1, bias, out, B, Cin, Cout, relu, as_stream(stream));
     if (conv_wgrad_igemm_supported(op, B, Cin, H, W, Cout))
       return conv_wgrad_igemm_run(op, in0, in1, out, B, Cin, H, W, Cout, workspace, workspace_bytes, as_stream(stream));
     return dense_op_tc(op, in0, in1, bias, out, B, Cin, H, W, Cout, relu, workspace, workspace_bytes, as_stream(stream));
