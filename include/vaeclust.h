@@ -144,6 +144,17 @@ typedef struct VcAdamChunk {
 } VcAdamChunk;
 int vc_adam_multi(const VcAdamChunk* table, int n_chunks, float lr, float beta1, float beta2, float eps,
                   float bias_corr1, float bias_corr2, void* stream);
+/* The same update for a step captured in a CUDA graph (torch.optim.Adam(capturable=True) semantics): the step counter
+ * and the bias corrections live in device memory; each call advances `step_state->step` by one on the device and
+ * derives 1 - beta^step from it, so a replayed graph performs step t, t+1, ... without host arguments changing. */
+typedef struct VcAdamDeviceStep {
+  int32_t step;
+  float bias_corr1;
+  float bias_corr2;
+  int32_t pad;
+} VcAdamDeviceStep;
+int vc_adam_multi_graph(const VcAdamChunk* table, int n_chunks, float lr, float beta1, float beta2, float eps,
+                        VcAdamDeviceStep* step_state, void* stream);
 
 /* --------------------------------------------------------------------------------------------- KMeans
  * One Lloyd iteration of sklearn:cluster/_k_means_lloyd.pyx:23-218 reached from 07:70-71, 13:120-121, 16:183,

@@ -177,8 +177,12 @@ constexpr int kAdamThreads = 256;
 
 __global__ void __launch_bounds__(kAdamThreads)
 adam_multi_kernel(const VcAdamChunk* __restrict__ table, float lr, float b1, float b2, float eps, float bc1,
-                  float bc2) {
+                  float bc2, const VcAdamDeviceStep* __restrict__ dev_step) {
   const VcAdamChunk ch = table[blockIdx.x];
+  if (dev_step) {   // graph-capturable form: the bias corrections of this step live in device memory
+    bc1 = dev_step->bias_corr1;
+    bc2 = dev_step->bias_corr2;
+  }
   // torch.optim.Adam (single-tensor, non-capturable) arithmetic order:
   //   m = b1*m + (1-b1)*g ; v = b2*v + (1-b2)*g*g ; p -= (lr/bc1) * m / (sqrt(v)/sqrt(bc2) + eps)
   const float step_size = lr / bc1;
@@ -391,7 +395,26 @@ extern "C" int vc_adam_multi(const VcAdamChunk* table, int n_chunks, float lr, f
   VC_REQUIRE(table && n_chunks >= 0, VC_ERR_BAD_ARG, "vc_adam_multi: bad arguments");
   if (n_chunks == 0) return VC_OK;
   adam_multi_kernel<<<n_chunks, kAdamThreads, 0, as_stream(stream)>>>(table, lr, beta1, beta2, eps, bias_corr1,
-                                                                     bias_corr2);
+                                                                     bias_corr2, nullptr);
+  VC_LAUNCH_CHECK();
+  return VC_OK;
+}
+
+// step += 1 and the bias corrections of that step, in double like the host path (1.0 - beta ** t in Python)
+__global__ void adam_tick_kernel(VcAdamDeviceStep* st, float b1, float b2) {
+  const int t = st->step + 1;
+  st->step = t;
+  st->bias_corr1 = (float)(1.0 - pow((double)b1, (double)t));
+  st->bias_corr2 = (float)(1.0 - pow((double)b2, (double)t));
+}
+
+extern "C" int vc_adam_multi_graph(const VcAdamChunk* table, int n_chunks, float lr, float beta1, float beta2, float eps,
+                                   VcAdamDeviceStep* step_state, void* stream) {
+  VC_REQUIRE(table && n_chunks >= 0 && step_state, VC_ERR_BAD_ARG, "vc_adam_multi_graph: bad arguments");
+  adam_tick_kernel<<<1, 1, 0, as_stream(stream)>>>(step_state, beta1, beta2);
+  VC_LAUNCH_CHECK();
+  if (n_chunks == 0) return VC_OK;
+  adam_multi_kernel<<<n_chunks, kAdamThreads, 0, as_stream(stream)>>>(table, lr, beta1, beta2, eps, 1.f, 1.f, step_state);
   VC_LAUNCH_CHECK();
   return VC_OK;
 }

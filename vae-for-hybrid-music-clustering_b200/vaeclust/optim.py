@@ -19,7 +19,7 @@ _CHUNK = 1 << 16
 
 class Adam:
     def __init__(self, params: Iterable[torch.nn.Parameter], lr: float = 1e-3, betas=(0.9, 0.999), eps: float = 1e-8,
-                 weight_decay: float = 0.0):
+                 weight_decay: float = 0.0, capturable: bool = False):
         if weight_decay != 0.0:
             raise VaeclustError("vaeclust.optim.Adam: weight_decay is not used by the reference and not supported")
         self.params: List[torch.nn.Parameter] = [p for p in params]
@@ -32,6 +32,11 @@ class Adam:
         self.state: Dict[int, dict] = {}
         self._table = None
         self._table_key = None
+        # capturable (torch.optim.Adam(capturable=True)): step counter and bias corrections live on the device, so a
+        # step recorded in a CUDA graph advances correctly on every replay (vc_adam_multi_graph)
+        self.capturable = bool(capturable)
+        self._dev_step = None
+        self._table_pinned = None
         self.param_groups = [{"params": self.params, "lr": self.lr, "betas": self.betas, "eps": self.eps}]
 
     def zero_grad(self, set_to_none: bool = True) -> None:
@@ -83,14 +88,37 @@ class Adam:
             table = np.concatenate(rows, axis=0)
             key = table.tobytes()
             dev = items[0][0].device
+            b1, b2 = self.betas
+            if self.capturable:
+                if len(by_step) != 1:
+                    raise VaeclustError("vaeclust.optim.Adam(capturable=True): every stepped parameter must share one "
+                                        "step count")
+                if self._dev_step is None:
+                    self._dev_step = torch.zeros(4, dtype=torch.int32, device=dev)
+                    self._dev_step[0] = t - 1
+                if self._table_key != key or self._table is None or self._table.device != dev:
+                    # pinned + async so the upload is legal inside a capture (a replay re-reads the same host buffer);
+                    # both buffers are allocated by the first eager step and only rewritten afterwards
+                    if self._table_pinned is None or tuple(self._table_pinned.shape) != table.shape:
+                        self._table_pinned = torch.empty(table.shape, dtype=torch.int64).pin_memory()
+                        self._table = torch.empty(table.shape, dtype=torch.int64, device=dev)
+                    self._table_pinned.numpy()[...] = table
+                    self._table.copy_(self._table_pinned, non_blocking=True)
+                    self._table_key = key
+                lib().call("vc_adam_multi_graph", ptr(self._table), int(table.shape[0]), self.lr, b1, b2, self.eps,
+                           ptr(self._dev_step), stream_ptr())
+                continue
             if self._table_key != key or self._table is None or self._table.device != dev:
                 self._table = torch.from_numpy(table).to(dev, non_blocking=False)
                 self._table_key = key
-            b1, b2 = self.betas
             lib().call("vc_adam_multi", ptr(self._table), int(table.shape[0]), self.lr, b1, b2, self.eps,
                        1.0 - b1 ** t, 1.0 - b2 ** t, stream_ptr())
 
     def state_dict(self) -> dict:
+        if self.capturable and self._dev_step is not None:   # replays advance the device counter only
+            t = int(self._dev_step[0])
+            for st in self.state.values():
+                st["step"] = t
         return {"state": {i: {k: (v.clone() if torch.is_tensor(v) else v) for k, v in self._state(p).items()}
                           for i, p in enumerate(self.params)},
                 "param_groups": [{"lr": self.lr, "betas": self.betas, "eps": self.eps}]}

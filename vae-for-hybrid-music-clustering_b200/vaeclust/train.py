@@ -42,11 +42,11 @@ class VAEStep:
     Under a process group each rank passes ITS slice of the global batch; gradients are combined with weights
     B_local/B_global so the result equals the reference's single-process batch mean."""
 
-    def __init__(self, model, kind: str, lr: float, beta: float, group=None):
+    def __init__(self, model, kind: str, lr: float, beta: float, group=None, capturable: bool = False):
         self.model, self.kind, self.beta, self.group = model, kind, float(beta), group
         self.mode = VC_LOSS_SUM_MEAN if kind == "mlp19" else VC_LOSS_MEAN_MEAN
         self.multi = group is not None and vdist.world_size(group) > 1
-        self.opt = Adam(model.parameters(), lr=lr)
+        self.opt = Adam(model.parameters(), lr=lr, capturable=capturable)
         self.sync = vdist.OverlappedGradSync(model.parameters(), group) if self.multi else None
 
     def __call__(self, x, *extra, eps: Optional[torch.Tensor] = None, global_batch: Optional[int] = None):
@@ -78,6 +78,53 @@ class VAEStep:
             self.sync.finish()
         self.opt.step()
         return stats  # device tensor [loss, recon, kl] of the local batch
+
+
+class GraphedVAEStep:
+    """The same optimisation step recorded once into a CUDA graph and replayed (single GPU): the ~125 kernel launches
+    of a step are submitted by one cudaGraphLaunch, which removes the host launch gaps between the short kernels of
+    the latent head and of the backward pass.  The first `warmup` calls run eagerly (they allocate optimizer state and
+    warm the allocator), the next call captures; inputs are copied into static buffers, `eps` (optional) likewise, else
+    it is drawn inside the graph from torch's graph-safe generator.  Returns the static [loss, recon, kl] tensor --
+    read it before the next call.  Shapes must not change after capture (pass full batches)."""
+
+    def __init__(self, model, kind: str, lr: float, beta: float, warmup: int = 2):
+        self.step = VAEStep(model, kind, lr, beta, group=None, capturable=True)
+        self.warmup, self.calls = int(warmup), 0
+        self.graph = None
+        self.static_in = None
+        self.static_eps = None
+        self.out = None
+
+    @property
+    def opt(self):
+        return self.step.opt
+
+    def __call__(self, x, *extra, eps: Optional[torch.Tensor] = None, global_batch: Optional[int] = None):
+        self.calls += 1
+        if self.graph is None and self.calls <= self.warmup:
+            return self.step(x, *extra, eps=eps)
+        if self.graph is None:
+            self.static_in = [t.clone() if torch.is_tensor(t) else t for t in (x,) + tuple(extra)]
+            self.static_eps = eps.clone() if eps is not None else None
+            self.step.opt.zero_grad()       # gradients must be (re)allocated from the graph's private pool
+            torch.cuda.synchronize()
+            self.graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(self.graph):
+                self.out = self.step(*self.static_in, eps=self.static_eps)
+        else:
+            if (eps is None) != (self.static_eps is None):
+                raise ValueError("GraphedVAEStep: pass eps on every call or on none (fixed at capture)")
+            for s, t in zip(self.static_in, (x,) + tuple(extra)):
+                if torch.is_tensor(s):
+                    if s.shape != t.shape:
+                        raise ValueError(f"GraphedVAEStep: input shape changed after capture ({tuple(t.shape)} vs "
+                                         f"{tuple(s.shape)})")
+                    s.copy_(t, non_blocking=True)
+            if eps is not None:
+                self.static_eps.copy_(eps, non_blocking=True)
+        self.graph.replay()
+        return self.out
 
 
 class HostBatchFeeder:
