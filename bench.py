@@ -200,8 +200,8 @@ def bench_vae(args, rank, world, device, group):
     model = nn.ConvMultiModalVAE(1, (F_MEL, T_MEL), ZDIM, LYR).to(device).train()
     # one GPU: the step is recorded once into a CUDA graph and replayed (vaeclust.train.GraphedVAEStep, the public API);
     # under torchrun the eager step with overlapped gradient exchange runs
-    use_graph = world == 1 and not args.no_graph
-    step = (GraphedVAEStep(model, "conv12", lr=2e-3, beta=1.0, warmup=2) if use_graph
+    use_graph = not args.no_graph
+    step = (GraphedVAEStep(model, "conv12", lr=2e-3, beta=1.0, warmup=2, group=group if world > 1 else None) if use_graph
             else VAEStep(model, "conv12", lr=2e-3, beta=1.0, group=group if world > 1 else None))
     gperm = torch.Generator().manual_seed(1)
     perm = torch.randperm(N_CLIPS, generator=gperm)
@@ -234,12 +234,12 @@ def bench_vae(args, rank, world, device, group):
     def e2e_run(first, n):
         feeder.prefetch(batch_idx(first))
         for s in range(first, first + n):
-            if s + 1 < first + n:
-                feeder.prefetch(batch_idx(s + 1))
             xb, lb, mb = feeder.get()
             eps = torch.randn(BATCH, ZDIM, device=device, generator=eps_gen)
             st = step(xb, lb, mb, eps=eps, global_batch=gb)
             feeder.release()
+            if s + 1 < first + n:   # enqueued after this step's launch, so the host-side copy calls hide behind it
+                feeder.prefetch(batch_idx(s + 1))
             sink.append(st.cpu())  # device->host read of the step's result: one sync per step
 
     e2e_run(0, min(2, args.warmup))
@@ -434,6 +434,8 @@ def main():
     from vaeclust import dist as vdist
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device; the product path has no CPU fallback (use --impl reference)")
+    if not args.no_graph:   # NCCL collectives are captured into the step's CUDA graph (watchdog must not query events)
+        os.environ.setdefault("TORCH_NCCL_ASYNC_ERROR_HANDLING", "0")
     rank, world, local = vdist.init_from_env("nccl")
     torch.cuda.set_device(local)
     device = torch.device("cuda", local)

@@ -81,15 +81,17 @@ class VAEStep:
 
 
 class GraphedVAEStep:
-    """The same optimisation step recorded once into a CUDA graph and replayed (single GPU): the ~125 kernel launches
+    """The same optimisation step recorded once into a CUDA graph and replayed: the ~125 kernel launches
     of a step are submitted by one cudaGraphLaunch, which removes the host launch gaps between the short kernels of
     the latent head and of the backward pass.  The first `warmup` calls run eagerly (they allocate optimizer state and
     warm the allocator), the next call captures; inputs are copied into static buffers, `eps` (optional) likewise, else
     it is drawn inside the graph from torch's graph-safe generator.  Returns the static [loss, recon, kl] tensor --
-    read it before the next call.  Shapes must not change after capture (pass full batches)."""
+    read it before the next call.  Shapes must not change after capture (pass full batches).  Under a process group
+    the overlapped NCCL gradient exchange is captured with the step (set TORCH_NCCL_ASYNC_ERROR_HANDLING=0 before
+    init_process_group, as for any NCCL-in-graph capture); `global_batch` is fixed at capture."""
 
-    def __init__(self, model, kind: str, lr: float, beta: float, warmup: int = 2):
-        self.step = VAEStep(model, kind, lr, beta, group=None, capturable=True)
+    def __init__(self, model, kind: str, lr: float, beta: float, warmup: int = 2, group=None):
+        self.step = VAEStep(model, kind, lr, beta, group=group, capturable=True)
         self.warmup, self.calls = int(warmup), 0
         self.graph = None
         self.static_in = None
@@ -103,7 +105,7 @@ class GraphedVAEStep:
     def __call__(self, x, *extra, eps: Optional[torch.Tensor] = None, global_batch: Optional[int] = None):
         self.calls += 1
         if self.graph is None and self.calls <= self.warmup:
-            return self.step(x, *extra, eps=eps)
+            return self.step(x, *extra, eps=eps, global_batch=global_batch)
         if self.graph is None:
             self.static_in = [t.clone() if torch.is_tensor(t) else t for t in (x,) + tuple(extra)]
             self.static_eps = eps.clone() if eps is not None else None
@@ -111,7 +113,7 @@ class GraphedVAEStep:
             torch.cuda.synchronize()
             self.graph = torch.cuda.CUDAGraph()
             with torch.cuda.graph(self.graph):
-                self.out = self.step(*self.static_in, eps=self.static_eps)
+                self.out = self.step(*self.static_in, eps=self.static_eps, global_batch=global_batch)
         else:
             if (eps is None) != (self.static_eps is None):
                 raise ValueError("GraphedVAEStep: pass eps on every call or on none (fixed at capture)")
