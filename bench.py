@@ -292,6 +292,17 @@ def roofline_from_summary(summ, steps, n_params, pk, ms_per_step):
 
     rows = sorted((entry(n_, d) for n_, d in fam.items()), key=lambda e: -e["share_of_step"])
     roof = dict(rows[0])
+    # DRAM bytes per launch of the headline family from the committed ncu capture (same command, --no-graph), next to
+    # the algorithmic bytes per launch the `achieved` figure uses
+    try:
+        tr = json.load(open(ROOT / "profiles" / "ncu_traffic_r1.json"))
+        if roof["kernel"] in tr:
+            roof["traffic"] = tr[roof["kernel"]]["dram_bytes_per_launch"]
+            roof["traffic_source"] = tr["_source"]
+    except (OSError, ValueError):
+        pass
+    d0 = fam[roof["kernel"]]
+    roof["algorithmic_bytes_per_launch"] = d0["bytes"] / max(d0["cnt"], 1)
     roof["peak_source"] = pk["src"] + (" copy bandwidth" if roof["bound"] == "hbm" else " sustained bf16")
     roof["kernels"] = [{k: (round(v, 4) if isinstance(v, float) else v) for k, v in r.items() if k != "traffic"}
                        for r in rows[:8]]

@@ -18,7 +18,9 @@
 namespace vc {
 
 constexpr int ST_ROWS = 128;      // rows per CTA (UMMA M)
-constexpr int ST_COLS = 128;      // columns per tile (UMMA N)
+// columns per tile (UMMA N) are a template parameter: 256 when the operands are 64 wide (one barrier round trip,
+// TMEM load and loop overhead per 128 columns a thread instead of per 64, and the tensor pipe's widest N), 128 when
+// they are 128 wide (shared memory)
 constexpr int ST_THREADS = 320;   // 10 warps: TMA, MMA, 8 epilogue
 constexpr int ST_EPI = 256;       // epilogue threads (two per accumulator lane, 64 columns each)
 
@@ -76,17 +78,19 @@ __device__ __forceinline__ float fast_sqrt(float x) {
   return y;
 }
 
+template <int ST_COLS>
 __global__ void __launch_bounds__(ST_THREADS, 1)
 silhouette_tc_kernel(const SilTcArgs a, const __grid_constant__ CUtensorMap mapH, const __grid_constant__ CUtensorMap mapL) {
   extern __shared__ unsigned char smem_raw[];
   unsigned char* smem = smem_raw + ((1024u - (tma::s32(smem_raw) & 1023u)) & 1023u);
   const int P = a.panels, S = a.stages;
   const uint32_t panel_bytes = ST_ROWS * 128;             // [128 rows][64 bf16]
-  const uint32_t op_bytes = panel_bytes * P;              // one operand (hi or lo) of one tile
+  const uint32_t op_bytes = panel_bytes * P;              // one row operand (hi or lo)
+  const uint32_t bpanel_bytes = ST_COLS * 128;            // [ST_COLS rows][64 bf16] of a column tile
+  const uint32_t bop_bytes = bpanel_bytes * P;            // one column operand (hi or lo) of one tile
   unsigned char* sA = smem;                               // A_hi | A_lo
   unsigned char* sB = smem + 2 * op_bytes;                // S x (B_hi | B_lo)
-  float* cns = reinterpret_cast<float*>(sB + (size_t)S * 2 * op_bytes);  // 2 x 128 column norms
-  uint64_t* bars = reinterpret_cast<uint64_t*>(cns + 2 * ST_COLS);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sB + (size_t)S * 2 * bop_bytes);
   uint64_t* a_full = bars;                // 1
   uint64_t* b_full = bars + 1;            // S
   uint64_t* b_empty = b_full + S;         // S
@@ -106,7 +110,7 @@ silhouette_tc_kernel(const SilTcArgs a, const __grid_constant__ CUtensorMap mapH
     for (int s = 0; s < 2; ++s) { tma::mbar_init(&t_full[s], 1); tma::mbar_init(&t_empty[s], ST_EPI); }
     tma::mbar_fence_init();
   }
-  if (warp == 1) tc05::tmem_alloc(tmem_slot, 256);
+  if (warp == 1) tc05::tmem_alloc(tmem_slot, 2 * ST_COLS);
   tc05::fence_before();
   __syncthreads();
   tc05::fence_after();
@@ -124,17 +128,19 @@ silhouette_tc_kernel(const SilTcArgs a, const __grid_constant__ CUtensorMap mapH
       uint32_t it = 0;
       for (int c = 0; c < a.k; ++c) {
         const int64_t c0 = a.off[c], c1 = a.off[c + 1];
-        for (int64_t j0 = c0; j0 < c1; j0 += ST_COLS, ++counter) {
+        for (int64_t j0 = c0 & ~(int64_t)3; j0 < c1; j0 += ST_COLS, ++counter) {   // 16-byte aligned norms
           if (counter % a.nsplit != split) continue;
           const int s = it % S;
           const uint32_t ph = (it / S) & 1;
           tma::mbar_wait(&b_empty[s], ph ^ 1);
-          unsigned char* dst = sB + (size_t)s * 2 * op_bytes;
-          tma::mbar_expect_tx(&b_full[s], 2 * op_bytes);
-          for (int p = 0; p < P; ++p) {
-            tma::load_2d(dst + p * panel_bytes, &mapH, &b_full[s], p * 64, (int)j0);
-            tma::load_2d(dst + op_bytes + p * panel_bytes, &mapL, &b_full[s], p * 64, (int)j0);
-          }
+          unsigned char* dst = sB + (size_t)s * 2 * bop_bytes;
+          tma::mbar_expect_tx(&b_full[s], 2 * bop_bytes);
+          for (int p = 0; p < P; ++p)
+            for (int h = 0; h < ST_COLS / ST_ROWS; ++h) {   // the tensor-map box is 128 rows
+              const uint32_t o = p * bpanel_bytes + h * panel_bytes;
+              tma::load_2d(dst + o, &mapH, &b_full[s], p * 64, (int)j0 + h * ST_ROWS);
+              tma::load_2d(dst + bop_bytes + o, &mapL, &b_full[s], p * 64, (int)j0 + h * ST_ROWS);
+            }
           ++it;
         }
       }
@@ -150,7 +156,7 @@ silhouette_tc_kernel(const SilTcArgs a, const __grid_constant__ CUtensorMap mapH
       uint32_t it = 0;
       for (int c = 0; c < a.k; ++c) {
         const int64_t c0 = a.off[c], c1 = a.off[c + 1];
-        for (int64_t j0 = c0; j0 < c1; j0 += ST_COLS, ++counter) {
+        for (int64_t j0 = c0 & ~(int64_t)3; j0 < c1; j0 += ST_COLS, ++counter) {   // 16-byte aligned norms
           if (counter % a.nsplit != split) continue;
           const int s = it % S;
           const uint32_t ph = (it / S) & 1;
@@ -159,15 +165,15 @@ silhouette_tc_kernel(const SilTcArgs a, const __grid_constant__ CUtensorMap mapH
           tma::mbar_wait(&t_empty[as], aph ^ 1);   // epilogue has drained this accumulator stage
           tma::mbar_wait(&b_full[s], ph);          // column operands have landed
           tc05::fence_after();
-          const uint32_t bH = tma::s32(sB + (size_t)s * 2 * op_bytes), bL = bH + op_bytes;
+          const uint32_t bH = tma::s32(sB + (size_t)s * 2 * bop_bytes), bL = bH + bop_bytes;
           const uint32_t tacc = tmem_base + as * ST_COLS;
           uint32_t accum = 0;
           for (int p = 0; p < P; ++p) {
 #pragma unroll
             for (int kk = 0; kk < 4; ++kk) {  // 64 bf16 per panel / UMMA_K 16
-              const uint32_t o = p * panel_bytes + kk * 32;
+              const uint32_t o = p * panel_bytes + kk * 32, ob = p * bpanel_bytes + kk * 32;
               const uint64_t dAH = tc05::desc_k_sw128(aH + o), dAL = tc05::desc_k_sw128(aL + o);
-              const uint64_t dBH = tc05::desc_k_sw128(bH + o), dBL = tc05::desc_k_sw128(bL + o);
+              const uint64_t dBH = tc05::desc_k_sw128(bH + ob), dBL = tc05::desc_k_sw128(bL + ob);
               tc05::mma_bf16(tacc, dAH, dBH, kIdesc, accum);
               tc05::mma_bf16(tacc, dAH, dBL, kIdesc, 1);
               tc05::mma_bf16(tacc, dAL, dBH, kIdesc, 1);
@@ -189,7 +195,6 @@ silhouette_tc_kernel(const SilTcArgs a, const __grid_constant__ CUtensorMap mapH
     const int64_t row = r0 + rl;
     const bool row_ok = row < a.row_end;
     const float rn = row_ok ? a.sqn[row] : 0.f;
-    const int e = threadIdx.x - 64;              // 0..255; the first 128 stage the column norms
     const int64_t nrows = a.row_end - a.row_begin;
     float* o = a.out + ((int64_t)split * 2 + half) * nrows * a.k;   // the two halves are separate partial planes
     int64_t counter = 0;
@@ -197,59 +202,64 @@ silhouette_tc_kernel(const SilTcArgs a, const __grid_constant__ CUtensorMap mapH
     for (int c = 0; c < a.k; ++c) {
       const int64_t c0 = a.off[c], c1 = a.off[c + 1];
       float rsum = 0.f;
-      for (int64_t j0 = c0; j0 < c1; j0 += ST_COLS, ++counter) {
+      for (int64_t j0 = c0 & ~(int64_t)3; j0 < c1; j0 += ST_COLS, ++counter) {   // 16-byte aligned norms
         if (counter % a.nsplit != split) continue;
         const int as = it & 1;
         const uint32_t aph = (it >> 1) & 1;
-        float* cn = cns + as * ST_COLS;
-        if (e < ST_COLS) cn[e] = (j0 + e < c1) ? a.sqn[j0 + e] : 0.f;
-        asm volatile("bar.sync 1, 256;" ::: "memory");
         tma::mbar_wait(&t_full[as], aph);
         tc05::fence_after();
-        const bool masked = (j0 + ST_COLS > c1) || (j0 < r0 + ST_ROWS && r0 < j0 + ST_COLS);
-        const int cb0 = half * 64;
-        const uint32_t tacc = tmem_base + ((uint32_t)(q * 32) << 16) + as * ST_COLS + cb0;
-        float v[64];
-        tc05::ld_32x32(tacc, v);          // both 32-column chunks in flight before the wait
-        tc05::ld_32x32(tacc + 32, v + 32);
-        tc05::ld_wait();
-        tc05::fence_before();
-        tma::mbar_arrive(&t_empty[as]);   // accumulator stage is free as soon as it sits in registers
-        const float4* cn4 = reinterpret_cast<const float4*>(cn + cb0);
-        if (!masked) {
-          float tmin = 1.f;
-#pragma unroll
-          for (int j = 0; j < 16; ++j) {
-            const float4 cc = cn4[j];
-            const float s0 = rn + cc.x, s1 = rn + cc.y, s2 = rn + cc.z, s3 = rn + cc.w;
-            const float e0 = fmaf(-2.f, v[4 * j + 0], s0), e1 = fmaf(-2.f, v[4 * j + 1], s1);
-            const float e2 = fmaf(-2.f, v[4 * j + 2], s2), e3 = fmaf(-2.f, v[4 * j + 3], s3);
-            tmin = fminf(tmin, fminf(fminf(fmaf(-kCloseRatio, s0, e0), fmaf(-kCloseRatio, s1, e1)),
-                                     fminf(fmaf(-kCloseRatio, s2, e2), fmaf(-kCloseRatio, s3, e3))));
-            rsum += fast_sqrt(fmaxf(e0, 0.f));
-            rsum += fast_sqrt(fmaxf(e1, 0.f));
-            rsum += fast_sqrt(fmaxf(e2, 0.f));
-            rsum += fast_sqrt(fmaxf(e3, 0.f));
+        const bool masked = j0 < c0 || (j0 + ST_COLS > c1) || (j0 < r0 + ST_ROWS && r0 < j0 + ST_COLS);
+#pragma unroll 1
+        for (int ch = 0; ch < ST_COLS / 128; ++ch) {
+          const int cb0 = half * (ST_COLS / 2) + ch * 64;
+          const uint32_t tacc = tmem_base + ((uint32_t)(q * 32) << 16) + as * ST_COLS + cb0;
+          float v[64];
+          tc05::ld_32x32(tacc, v);          // both 32-column chunks in flight before the wait
+          tc05::ld_32x32(tacc + 32, v + 32);
+          tc05::ld_wait();
+          if (ch == ST_COLS / 128 - 1) {
+            tc05::fence_before();
+            tma::mbar_arrive(&t_empty[as]);   // accumulator stage is free as soon as it sits in registers
           }
-          if (tmin < 0.f && row_ok) {  // rare: some pair of this chunk is close -> replace its term by the exact one
+          // column norms straight from global memory (every row of the tile reads the same 64 floats: L1 broadcast)
+          const float* cn = a.sqn + j0 + cb0;
+          if (!masked) {
+            const float4* cn4 = reinterpret_cast<const float4*>(cn);
+            float tmin = 1.f;
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {
+              const float4 cc = __ldg(cn4 + j);
+              const float s0 = rn + cc.x, s1 = rn + cc.y, s2 = rn + cc.z, s3 = rn + cc.w;
+              const float e0 = fmaf(-2.f, v[4 * j + 0], s0), e1 = fmaf(-2.f, v[4 * j + 1], s1);
+              const float e2 = fmaf(-2.f, v[4 * j + 2], s2), e3 = fmaf(-2.f, v[4 * j + 3], s3);
+              tmin = fminf(tmin, fminf(fminf(fmaf(-kCloseRatio, s0, e0), fmaf(-kCloseRatio, s1, e1)),
+                                       fminf(fmaf(-kCloseRatio, s2, e2), fmaf(-kCloseRatio, s3, e3))));
+              rsum += fast_sqrt(fmaxf(e0, 0.f));
+              rsum += fast_sqrt(fmaxf(e1, 0.f));
+              rsum += fast_sqrt(fmaxf(e2, 0.f));
+              rsum += fast_sqrt(fmaxf(e3, 0.f));
+            }
+            if (tmin < 0.f && row_ok) {  // rare: some pair of this chunk is close -> replace its term by the exact one
+#pragma unroll
+              for (int j = 0; j < 64; ++j) {
+                const float s = rn + __ldg(cn + j);
+                const float d2 = fmaf(-2.f, v[j], s);
+                if (d2 < kCloseRatio * s)
+                  rsum += exact_dist(a.Xs, a.d, row, j0 + cb0 + j) - fast_sqrt(fmaxf(d2, 0.f));
+              }
+            }
+          } else {
 #pragma unroll
             for (int j = 0; j < 64; ++j) {
-              const float s = rn + cn[cb0 + j];
+              const int64_t col = j0 + cb0 + j;
+              const bool in_cluster = col >= c0 && col < c1;
+              const bool live = in_cluster && col != row && row_ok;
+              const float s = rn + (in_cluster ? __ldg(cn + j) : 0.f);
               const float d2 = fmaf(-2.f, v[j], s);
-              if (d2 < kCloseRatio * s)
-                rsum += exact_dist(a.Xs, a.d, row, j0 + cb0 + j) - fast_sqrt(fmaxf(d2, 0.f));
+              float dist = fast_sqrt(fmaxf(d2, 0.f));
+              if (live && d2 < kCloseRatio * s) dist = exact_dist(a.Xs, a.d, row, col);
+              rsum += live ? dist : 0.f;
             }
-          }
-        } else {
-#pragma unroll
-          for (int j = 0; j < 64; ++j) {
-            const int64_t col = j0 + cb0 + j;
-            const float s = rn + cn[cb0 + j];
-            const float d2 = fmaf(-2.f, v[j], s);
-            float dist = fast_sqrt(fmaxf(d2, 0.f));
-            const bool live = col < c1 && col != row && row_ok;
-            if (live && d2 < kCloseRatio * s) dist = exact_dist(a.Xs, a.d, row, col);
-            rsum += live ? dist : 0.f;
           }
         }
         ++it;
@@ -262,7 +272,7 @@ silhouette_tc_kernel(const SilTcArgs a, const __grid_constant__ CUtensorMap mapH
   __syncthreads();
   if (warp == 1) {
     tc05::fence_after();
-    tc05::tmem_dealloc(tmem_base, 256);
+    tc05::tmem_dealloc(tmem_base, 2 * ST_COLS);
   }
 }
 
@@ -307,13 +317,15 @@ extern "C" int vc_silhouette_rows_tc(const void* H, const void* L, const float* 
   SilTcArgs a;
   a.sqn = sqn; a.off = off_dev; a.k = k; a.N = N; a.row_begin = row_begin; a.row_end = row_end; a.nsplit = nsplit;
   a.Xs = Xs; a.d = d;
-  a.out = cluster_sums; a.panels = dp / 64; a.stages = dp == 64 ? 4 : 2;
-  const size_t op = (size_t)ST_ROWS * 128 * a.panels;
-  const size_t smem = 2 * op + (size_t)a.stages * 2 * op + 2 * ST_COLS * 4 + (1 + 2 * a.stages + 4) * 8 + 16 + 1024;
-  VC_CUDA(cudaFuncSetAttribute(silhouette_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  a.out = cluster_sums; a.panels = dp / 64; a.stages = dp == 64 ? 3 : 2;
+  const int cols = dp == 64 ? 256 : 128;
+  const size_t op = (size_t)ST_ROWS * 128 * a.panels, bop = (size_t)cols * 128 * a.panels;
+  const size_t smem = 2 * op + (size_t)a.stages * 2 * bop + (1 + 2 * a.stages + 4) * 8 + 16 + 1024;
+  auto kern = dp == 64 ? silhouette_tc_kernel<256> : silhouette_tc_kernel<128>;
+  VC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   const int64_t tiles = (row_end - row_begin + ST_ROWS - 1) / ST_ROWS;
   dim3 grid((unsigned)tiles, (unsigned)nsplit);
-  silhouette_tc_kernel<<<grid, ST_THREADS, smem, as_stream(stream)>>>(a, mH, mL);
+  kern<<<grid, ST_THREADS, smem, as_stream(stream)>>>(a, mH, mL);
   VC_LAUNCH_CHECK();
   return VC_OK;
 }
