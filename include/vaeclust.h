@@ -203,12 +203,14 @@ int vc_silhouette_rows(const float* Xs, const float* sqn, int64_t N, int d, cons
                        int64_t row_begin, int64_t row_end, int nsplit, float* cluster_sums, void* stream);
 /* Tensor-core variant (tcgen05, bf16 hi/lo split with fp32 accumulation in TMEM; d <= 128).  First split the sorted,
  * centred rows into two bf16 matrices H, L of shape [N, dp] (dp = d rounded up to a multiple of 64, caller-owned,
- * 128-byte aligned), then run row blocks like vc_silhouette_rows, except that cluster_sums holds TWO partial
- * planes per split: [2*nsplit, row_end-row_begin, k] (pass 2*nsplit to vc_silhouette_finalize).
+ * 128-byte aligned), then run row blocks like vc_silhouette_rows, except that cluster_sums holds P =
+ * vc_silhouette_tc_planes(dp) partial planes per split (one per column part of a tile an epilogue thread owns):
+ * [P*nsplit, row_end-row_begin, k] (pass P*nsplit to vc_silhouette_finalize).
  * sqn_split (may be NULL) receives the squared norms of the split rows (hi + lo); pass those as `sqn` to
  * vc_silhouette_rows_tc so the norm formula cancels consistently.  Xs/d are the fp32 rows (d % 4 == 0): pairs whose
  * squared distance falls below 1/256 of |x|^2 + |y|^2 (duplicates, near-duplicates) are recomputed from them as
  * sum (x - y)^2, the accuracy sklearn gets from its float64 upcast (pairwise.py:567-638). */
+int vc_silhouette_tc_planes(int dp);
 int vc_silhouette_split_bf16(const float* Xs, int64_t N, int d, int dp, void* H, void* L, float* sqn_split,
                              void* stream);
 int vc_silhouette_rows_tc(const void* H, const void* L, const float* Xs, int d, const float* sqn, int64_t N, int dp,

@@ -21,8 +21,7 @@ constexpr int ST_ROWS = 128;      // rows per CTA (UMMA M)
 // columns per tile (UMMA N) are a template parameter: 256 when the operands are 64 wide (one barrier round trip,
 // TMEM load and loop overhead per 128 columns a thread instead of per 64, and the tensor pipe's widest N), 128 when
 // they are 128 wide (shared memory)
-constexpr int ST_THREADS = 320;   // 10 warps: TMA, MMA, 8 epilogue
-constexpr int ST_EPI = 256;       // epilogue threads (two per accumulator lane, 64 columns each)
+// epilogue warps EW (template): EW/4 threads per accumulator lane, each owning ST_COLS/(EW/4) columns of a tile
 
 // fp32 -> (hi, lo) bf16 split, zero-padded to dp columns (dp % 64 == 0); one warp per row.  Also emits the squared
 // norm of the SPLIT row (hi + lo, 16 mantissa bits), so |x|^2 + |y|^2 - 2 x.y is formed from one consistent
@@ -78,12 +77,15 @@ __device__ __forceinline__ float fast_sqrt(float x) {
   return y;
 }
 
-template <int ST_COLS>
-__global__ void __launch_bounds__(ST_THREADS, 1)
+template <int ST_COLS, int EW>
+__global__ void __launch_bounds__(64 + 32 * EW, 1)
 silhouette_tc_kernel(const SilTcArgs a, const __grid_constant__ CUtensorMap mapH, const __grid_constant__ CUtensorMap mapL) {
   extern __shared__ unsigned char smem_raw[];
   unsigned char* smem = smem_raw + ((1024u - (tma::s32(smem_raw) & 1023u)) & 1023u);
   const int P = a.panels, S = a.stages;
+  constexpr int ST_EPI = 32 * EW, PARTS = EW / 4, PCOLS = ST_COLS / PARTS;
+  // columns per TMEM read: 18 warps put five on one scheduler, whose 16384 registers then allow 96 per thread
+  constexpr int CW = EW == 16 ? 32 : 64;
   const uint32_t panel_bytes = ST_ROWS * 128;             // [128 rows][64 bf16]
   const uint32_t op_bytes = panel_bytes * P;              // one row operand (hi or lo)
   const uint32_t bpanel_bytes = ST_COLS * 128;            // [ST_COLS rows][64 bf16] of a column tile
@@ -190,13 +192,13 @@ silhouette_tc_kernel(const SilTcArgs a, const __grid_constant__ CUtensorMap mapH
   } else {
     // ===================== epilogue: warps 2..9; thread = one row x one 64-column half of the tile ==========
     const int q = warp & 3;                      // TMEM lane quarter this warp may access
-    const int half = (warp - 2) >> 2;            // which 64 columns of each tile
+    const int half = (warp - 2) >> 2;            // which PCOLS columns of each tile
     const int rl = q * 32 + lane;                // row within the tile
     const int64_t row = r0 + rl;
     const bool row_ok = row < a.row_end;
     const float rn = row_ok ? a.sqn[row] : 0.f;
     const int64_t nrows = a.row_end - a.row_begin;
-    float* o = a.out + ((int64_t)split * 2 + half) * nrows * a.k;   // the two halves are separate partial planes
+    float* o = a.out + ((int64_t)split * PARTS + half) * nrows * a.k;   // every column part is its own partial plane
     int64_t counter = 0;
     uint32_t it = 0;
     for (int c = 0; c < a.k; ++c) {
@@ -210,14 +212,14 @@ silhouette_tc_kernel(const SilTcArgs a, const __grid_constant__ CUtensorMap mapH
         tc05::fence_after();
         const bool masked = j0 < c0 || (j0 + ST_COLS > c1) || (j0 < r0 + ST_ROWS && r0 < j0 + ST_COLS);
 #pragma unroll 1
-        for (int ch = 0; ch < ST_COLS / 128; ++ch) {
-          const int cb0 = half * (ST_COLS / 2) + ch * 64;
+        for (int ch = 0; ch < PCOLS / CW; ++ch) {
+          const int cb0 = half * PCOLS + ch * CW;
           const uint32_t tacc = tmem_base + ((uint32_t)(q * 32) << 16) + as * ST_COLS + cb0;
-          float v[64];
-          tc05::ld_32x32(tacc, v);          // both 32-column chunks in flight before the wait
-          tc05::ld_32x32(tacc + 32, v + 32);
+          float v[CW];
+          tc05::ld_32x32(tacc, v);          // all 32-column chunks in flight before the wait
+          if (CW == 64) tc05::ld_32x32(tacc + 32, v + (CW == 64 ? 32 : 0));
           tc05::ld_wait();
-          if (ch == ST_COLS / 128 - 1) {
+          if (ch == PCOLS / CW - 1) {
             tc05::fence_before();
             tma::mbar_arrive(&t_empty[as]);   // accumulator stage is free as soon as it sits in registers
           }
@@ -227,7 +229,7 @@ silhouette_tc_kernel(const SilTcArgs a, const __grid_constant__ CUtensorMap mapH
             const float4* cn4 = reinterpret_cast<const float4*>(cn);
             float tmin = 1.f;
 #pragma unroll
-            for (int j = 0; j < 16; ++j) {
+            for (int j = 0; j < CW / 4; ++j) {
               const float4 cc = __ldg(cn4 + j);
               const float s0 = rn + cc.x, s1 = rn + cc.y, s2 = rn + cc.z, s3 = rn + cc.w;
               const float e0 = fmaf(-2.f, v[4 * j + 0], s0), e1 = fmaf(-2.f, v[4 * j + 1], s1);
@@ -241,7 +243,7 @@ silhouette_tc_kernel(const SilTcArgs a, const __grid_constant__ CUtensorMap mapH
             }
             if (tmin < 0.f && row_ok) {  // rare: some pair of this chunk is close -> replace its term by the exact one
 #pragma unroll
-              for (int j = 0; j < 64; ++j) {
+              for (int j = 0; j < CW; ++j) {
                 const float s = rn + __ldg(cn + j);
                 const float d2 = fmaf(-2.f, v[j], s);
                 if (d2 < kCloseRatio * s)
@@ -250,7 +252,7 @@ silhouette_tc_kernel(const SilTcArgs a, const __grid_constant__ CUtensorMap mapH
             }
           } else {
 #pragma unroll
-            for (int j = 0; j < 64; ++j) {
+            for (int j = 0; j < CW; ++j) {
               const int64_t col = j0 + cb0 + j;
               const bool in_cluster = col >= c0 && col < c1;
               const bool live = in_cluster && col != row && row_ok;
@@ -279,6 +281,8 @@ silhouette_tc_kernel(const SilTcArgs a, const __grid_constant__ CUtensorMap mapH
 }  // namespace vc
 
 using namespace vc;
+
+extern "C" int vc_silhouette_tc_planes(int dp) { return dp == 64 ? 4 : 2; }
 
 extern "C" int vc_silhouette_split_bf16(const float* Xs, int64_t N, int d, int dp, void* H, void* L, float* sqn_split,
                                         void* stream) {
@@ -321,11 +325,12 @@ extern "C" int vc_silhouette_rows_tc(const void* H, const void* L, const float* 
   const int cols = dp == 64 ? 256 : 128;
   const size_t op = (size_t)ST_ROWS * 128 * a.panels, bop = (size_t)cols * 128 * a.panels;
   const size_t smem = 2 * op + (size_t)a.stages * 2 * bop + (1 + 2 * a.stages + 4) * 8 + 16 + 1024;
-  auto kern = dp == 64 ? silhouette_tc_kernel<256> : silhouette_tc_kernel<128>;
+  auto kern = dp == 64 ? silhouette_tc_kernel<256, 16> : silhouette_tc_kernel<128, 8>;
+  const int threads = dp == 64 ? 64 + 32 * 16 : 64 + 32 * 8;
   VC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   const int64_t tiles = (row_end - row_begin + ST_ROWS - 1) / ST_ROWS;
   dim3 grid((unsigned)tiles, (unsigned)nsplit);
-  kern<<<grid, ST_THREADS, smem, as_stream(stream)>>>(a, mH, mL);
+  kern<<<grid, threads, smem, as_stream(stream)>>>(a, mH, mL);
   VC_LAUNCH_CHECK();
   return VC_OK;
 }

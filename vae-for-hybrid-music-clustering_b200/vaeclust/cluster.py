@@ -395,15 +395,16 @@ def _sil_block(Xs, sqn, off, k: int, r0: int, r1: int, lab_sorted, counts, s_sor
     nsplit = int(max(1, min(32, (2 * sms) // max(tiles, 1))))
     dp = (d + 63) // 64 * 64
     if SILHOUETTE_PRECISION == "tc" and dp <= 128:
-        # the tensor-core kernel writes two partial planes per split (one per 64-column half of a tile)
-        sums = torch.empty((2 * nsplit, nrows, k), dtype=torch.float32, device=Xs.device)
+        # the tensor-core kernel writes several partial planes per split (one per column part of a tile)
+        planes = lib().size("vc_silhouette_tc_planes", dp)
+        sums = torch.empty((planes * nsplit, nrows, k), dtype=torch.float32, device=Xs.device)
         H = torch.empty((N, dp), dtype=torch.bfloat16, device=Xs.device)
         L = torch.empty((N, dp), dtype=torch.bfloat16, device=Xs.device)
         sqn_hl = torch.empty_like(sqn)  # norms of the split rows: the formula must cancel against the same operands
         lib().call("vc_silhouette_split_bf16", ptr(Xs), N, d, dp, ptr(H), ptr(L), ptr(sqn_hl), stream_ptr())
         lib().call("vc_silhouette_rows_tc", ptr(H), ptr(L), ptr(Xs), d, ptr(sqn_hl), N, dp, ptr(off), k, r0, r1, nsplit,
                    ptr(sums), stream_ptr())
-        nsplit *= 2
+        nsplit *= planes
     else:
         sums = torch.empty((nsplit, nrows, k), dtype=torch.float32, device=Xs.device)
         lib().call("vc_silhouette_rows", ptr(Xs), ptr(sqn), N, d, ptr(off), k, r0, r1, nsplit, ptr(sums),
