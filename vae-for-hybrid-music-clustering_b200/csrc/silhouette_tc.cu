@@ -227,27 +227,28 @@ silhouette_tc_kernel(const SilTcArgs a, const __grid_constant__ CUtensorMap mapH
           const float* cn = a.sqn + j0 + cb0;
           if (!masked) {
             const float4* cn4 = reinterpret_cast<const float4*>(cn);
-            float tmin = 1.f;
+            // five instructions per pair: s = |x|^2+|y|^2, e = s - 2 x.y, running min, sqrt(|e|), running sum.  A close
+            // pair (e < s/256) has | |x|-|y| | <= |x-y| < (|x|+|y|)/16, hence |y|^2 < 1.29 |x|^2 and e < |x|^2/112:
+            // one comparison of the chunk minimum against |x|^2/112 finds every chunk that can hold one.
+            float emin = 3.0e38f;
 #pragma unroll
             for (int j = 0; j < CW / 4; ++j) {
               const float4 cc = __ldg(cn4 + j);
-              const float s0 = rn + cc.x, s1 = rn + cc.y, s2 = rn + cc.z, s3 = rn + cc.w;
-              const float e0 = fmaf(-2.f, v[4 * j + 0], s0), e1 = fmaf(-2.f, v[4 * j + 1], s1);
-              const float e2 = fmaf(-2.f, v[4 * j + 2], s2), e3 = fmaf(-2.f, v[4 * j + 3], s3);
-              tmin = fminf(tmin, fminf(fminf(fmaf(-kCloseRatio, s0, e0), fmaf(-kCloseRatio, s1, e1)),
-                                       fminf(fmaf(-kCloseRatio, s2, e2), fmaf(-kCloseRatio, s3, e3))));
-              rsum += fast_sqrt(fmaxf(e0, 0.f));
-              rsum += fast_sqrt(fmaxf(e1, 0.f));
-              rsum += fast_sqrt(fmaxf(e2, 0.f));
-              rsum += fast_sqrt(fmaxf(e3, 0.f));
+              const float e0 = fmaf(-2.f, v[4 * j + 0], rn + cc.x), e1 = fmaf(-2.f, v[4 * j + 1], rn + cc.y);
+              const float e2 = fmaf(-2.f, v[4 * j + 2], rn + cc.z), e3 = fmaf(-2.f, v[4 * j + 3], rn + cc.w);
+              emin = fminf(emin, fminf(fminf(e0, e1), fminf(e2, e3)));
+              rsum += fast_sqrt(fabsf(e0));
+              rsum += fast_sqrt(fabsf(e1));
+              rsum += fast_sqrt(fabsf(e2));
+              rsum += fast_sqrt(fabsf(e3));
             }
-            if (tmin < 0.f && row_ok) {  // rare: some pair of this chunk is close -> replace its term by the exact one
+            if (emin < rn * (1.f / 112.f) && row_ok) {  // rare: replace the term of every close pair by the exact one
 #pragma unroll
               for (int j = 0; j < CW; ++j) {
                 const float s = rn + __ldg(cn + j);
                 const float d2 = fmaf(-2.f, v[j], s);
                 if (d2 < kCloseRatio * s)
-                  rsum += exact_dist(a.Xs, a.d, row, j0 + cb0 + j) - fast_sqrt(fmaxf(d2, 0.f));
+                  rsum += exact_dist(a.Xs, a.d, row, j0 + cb0 + j) - fast_sqrt(fabsf(d2));
               }
             }
           } else {
@@ -258,7 +259,7 @@ silhouette_tc_kernel(const SilTcArgs a, const __grid_constant__ CUtensorMap mapH
               const bool live = in_cluster && col != row && row_ok;
               const float s = rn + (in_cluster ? __ldg(cn + j) : 0.f);
               const float d2 = fmaf(-2.f, v[j], s);
-              float dist = fast_sqrt(fmaxf(d2, 0.f));
+              float dist = fast_sqrt(fabsf(d2));
               if (live && d2 < kCloseRatio * s) dist = exact_dist(a.Xs, a.d, row, col);
               rsum += live ? dist : 0.f;
             }
