@@ -55,7 +55,15 @@ bias_grad_stage1(const float* __restrict__ dy, int64_t outer, int C, int64_t inn
   } else {
     // slices of the flattened (outer, inner/4) index space, float4 loads when rows are 16-byte aligned
     const bool vec = (inner % 4 == 0) && ((reinterpret_cast<uintptr_t>(dy) & 15) == 0);
-    if (vec) {
+    if (vec && C == 1) {
+      // single channel (the reconstruction's bias): dy is one contiguous vector, no index arithmetic
+      const int64_t total = outer * (inner / 4);
+      const float4* p4 = reinterpret_cast<const float4*>(dy);
+      for (int64_t e = sp * (int64_t)blockDim.x + threadIdx.x; e < total; e += (int64_t)S * blockDim.x) {
+        const float4 v = __ldcs(p4 + e);
+        acc += (double)((v.x + v.y) + (v.z + v.w));
+      }
+    } else if (vec) {
       const int64_t i4 = inner / 4, total = outer * i4;
       for (int64_t e = sp * (int64_t)blockDim.x + threadIdx.x; e < total; e += (int64_t)S * blockDim.x) {
         const int64_t o = e / i4, i = e % i4;
@@ -347,7 +355,11 @@ extern "C" int vc_relu_bwd_bias(const float* dy, const float* y, int64_t outer, 
   return VC_OK;
 }
 
-extern "C" size_t vc_bias_grad_workspace_bytes(int C) { return sizeof(double) * (size_t)kBiasSplits * (C > 0 ? C : 1); }
+// kBiasSplits partials per channel, at least 1024 in total so that a few channels still fill the GPU
+extern "C" size_t vc_bias_grad_workspace_bytes(int C) {
+  const size_t n = (size_t)kBiasSplits * (C > 0 ? C : 1);
+  return sizeof(double) * (n > 1024 ? n : 1024);
+}
 
 extern "C" int vc_bias_grad(const float* dy, int64_t outer, int C, int64_t inner, float* db, int accumulate,
                             void* workspace, size_t workspace_bytes, void* stream) {
@@ -360,6 +372,7 @@ extern "C" int vc_bias_grad(const float* dy, int64_t outer, int C, int64_t inner
     while (S > 1 && (S > outer || (int64_t)C * S > 262144)) S >>= 1;
     bias_grad_cols_stage1<<<dim3((C + 127) / 128, S), 128, 0, as_stream(stream)>>>(dy, outer, C, S, part);
   } else {
+    while ((int64_t)C * S < 512) S <<= 1;   // few channels: split further so the grid still fills the GPU
     while (S > 1 && outer * inner / S < 1024) S >>= 1;
     bias_grad_stage1<<<dim3(C, S), 256, 0, as_stream(stream)>>>(dy, outer, C, inner, S, part);
   }
