@@ -274,7 +274,7 @@ def roofline_from_summary(summ, steps, n_params, pk, ms_per_step):
         d = fam.setdefault(family_of(name, sig), dict(ms=0.0, cnt=0, flops=0.0, bytes=0.0))
         d["ms"] += tms; d["cnt"] += cnt
         d["flops"] += cnt * flops_of(name, sig)
-        d["bytes"] += cnt * (28.0 * n_params if name == "vc_adam_multi" else bytes_of(name, sig))
+        d["bytes"] += cnt * (28.0 * n_params if name.startswith("vc_adam_multi") else bytes_of(name, sig))
     total = sum(d["ms"] for d in fam.values()) or 1.0
 
     def entry(n_, d):
@@ -471,6 +471,8 @@ def main():
     if rank == 0:
         clips = vae["gb"] * args.steps
         roof = roofline_from_summary(vae["summ"], args.steps, vae["n_params"], pk, vae["ms_prof"] / args.steps)
+        roof["step"]["measured_ms"] = vae["ms"] / args.steps          # the timed region, not the event-bracketed pass
+        roof["step"]["frac"] = roof["step"]["roofline_ms"] / roof["step"]["measured_ms"]
         roof["timing"] = (f"per-call CUDA events over {args.steps} eager steps ({vae['ms_prof'] / args.steps:.3f} ms/step with the "
                           "event pairs) run after the timed region" + ("; the timed region replays a CUDA graph of the same "
                           "launches" if vae["graph"] else ""))
