@@ -357,6 +357,47 @@ def bench_kmeans(rank, world, device, group, pk):
                         "scaling": "strong"}, per_k=out, bytes_per_point=132)
 
 
+def bench_cvae19(args, rank, world, device, group):
+    """script-19 CVAE (464 + 6 cond -> 256 -> 256 -> 16 -> ... -> 464, beta 4, lr 1e-3), 200 k
+    synthetic rows resident on the device, data-parallel and weak-scaled: 256 rows per GPU (the script's batch) and
+    8192 per GPU, in the precision of the run (bf16 operands / fp32 accumulate by default), the step replayed from a CUDA
+    graph like the headline."""
+    import torch
+    from vaeclust import nn, ops as vops
+    from vaeclust.train import GraphedVAEStep, VAEStep
+    vops.set_precision(args.precision)
+    N, D, COND = 200_000, 464, 6
+    g = torch.Generator(device=device).manual_seed(11 + rank)
+    sig = torch.logspace(2, 0, 80, device=device)
+    X = torch.cat([torch.randn(N, 80, device=device, generator=g) * sig,
+                   torch.randn(N, 384, device=device, generator=g) * 0.05], dim=1).contiguous()
+    cond = torch.nn.functional.one_hot(torch.randint(0, COND, (N,), device=device, generator=g), COND).float()
+    out = {}
+    for B in (256, 8192):
+        torch.manual_seed(42)
+        model = nn.MLPVAE(D, 16, 256, cond_dim=COND, conditional=True).to(device).train()
+        grp = group if world > 1 else None
+        step = (VAEStep(model, "mlp19", lr=1e-3, beta=4.0, group=grp) if args.no_graph
+                else GraphedVAEStep(model, "mlp19", lr=1e-3, beta=4.0, warmup=2, group=grp))
+
+        def run(s):
+            lo = (s * B) % (N - B)
+            return step(X[lo: lo + B], cond[lo: lo + B], global_batch=B * world)
+
+        for s in range(5):
+            run(s)
+        iters = 50
+        ms = timed_max_ms(lambda s: run(5 + s), iters, world, device)
+        out[f"B{B}"] = dict(ms_per_step=ms / iters, clips_per_s=B * world * iters / (ms * 1e-3),
+                            last_loss=float(run(0)[0]))
+    return dict(metric="CVAE (script 19) train clips/s", unit="clips/s", value=out["B8192"]["clips_per_s"],
+                dtype="bf16" if args.precision == "bf16" else "f32",
+                config={"workload": "script-19 CVAE 470->256->256->16->22->256->256->464, beta 4, Adam 1e-3, "
+                                    "200k x 464 resident rows, batch per GPU 256 and 8192", "scaling": "weak",
+                        "submission": "eager" if args.no_graph else "one CUDA graph replay per step"},
+                per_batch=out)
+
+
 def bench_silhouette(rank, world, device, group):
     """Silhouette row blocks on 500k x 64 (script 16 sweep shape), k=8; rows sharded over ranks."""
     import torch
@@ -462,6 +503,7 @@ def main():
         torch.cuda.empty_cache()
         extra["kmeans"] = bench_kmeans(rank, world, device, group, pk)
         extra["silhouette"] = bench_silhouette(rank, world, device, group)
+        extra["cvae19"] = bench_cvae19(args, rank, world, device, group)
     cpu = None
     if rank == 0 and world == 1 and not args.skip_cpu:
         v, spstep, cores = cpu_vae_steps(BATCH, 3, 1)
