@@ -133,6 +133,15 @@ size_t vc_dense_op_workspace_bytes(int op, int precision, int B, int Cin, int H,
 int vc_dense_op(int op, int precision, const float* in0, const float* in1, const float* bias, float* out, int B,
                 int Cin, int H, int W, int Cout, int relu, void* workspace, size_t workspace_bytes, void* stream);
 
+/* Whole backward of one SMALL Linear(+ReLU) layer (latent head / lyrics branch / script-19 and script-06 MLPs,
+ * 12:88-120,159-166; 19:79-95; 06:149-157) in one launch, bf16 operands / fp32 accumulate like VC_PREC_BF16_TC:
+ * g = dy * (y > 0) (y = the layer's saved ReLU output, or NULL for no activation); dW[Cout,Cin] = g^T x;
+ * db[Cout] = column sums of g (NULL: skip); dx[B,Cin] = g W (NULL: skip).  vc_linear_bwd_small_supported() says whether
+ * a shape qualifies (B <= 256, Cin*Cout <= 2^20); other shapes go through vc_relu_bwd_bias + vc_dense_op. */
+int vc_linear_bwd_small_supported(int B, int Cin, int Cout);
+int vc_linear_bwd_small(const float* dy, const float* y, const float* x, const float* W, float* dW, float* db,
+                        float* dx, int B, int Cin, int Cout, void* stream);
+
 /* ------------------------------------------------------------------------------------------------- Adam
  * torch.optim.Adam defaults (12:233, 19:202, 06:310): one launch over a device-resident table of chunks. */
 typedef struct VcAdamChunk {

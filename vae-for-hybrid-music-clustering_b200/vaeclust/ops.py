@@ -97,6 +97,15 @@ class _DenseFn(torch.autograd.Function):
         dx = dw = db = None
         want_db = ctx.has_bias and ctx.needs_input_grad[3]
         inner = 1 if ctx.kind == "linear" else dy.shape[2] * dy.shape[3]
+        if (ctx.kind == "linear" and ctx.prec == _PREC["bf16"] and ctx.needs_input_grad[2]
+                and lib().size("vc_linear_bwd_small_supported", B, Cin, Cout)):
+            # latency-bound layer: ReLU mask, weight / bias / data gradients in one launch
+            dw = torch.empty_like(weight)
+            db = torch.empty(Cout, dtype=torch.float32, device=x.device) if want_db else None
+            dx = torch.empty_like(x) if ctx.needs_input_grad[1] else None
+            lib().call("vc_linear_bwd_small", ptr(dy), ptr(y) if ctx.relu else None, ptr(x), ptr(weight), ptr(dw),
+                       ptr(db), ptr(dx), B, Cin, Cout, s)
+            return None, dx, dw, db, None
         if ctx.relu and want_db:  # ReLU mask and bias gradient in one pass over dy / y
             g = torch.empty_like(dy)
             db = torch.empty(Cout, dtype=torch.float32, device=x.device)
