@@ -421,6 +421,42 @@ def bench_silhouette(rank, world, device, group):
 
 
 # -------------------------------------------------------------------------- CPU baseline / reference arm
+def cpu_cluster_baselines():
+    """The reference's clustering arithmetic IS scikit-learn (un-vendored dependency): time
+    sklearn.cluster.KMeans (explicit init, n_init=1, 10 Lloyd iterations) and sklearn.metrics.silhouette_score on bounded
+    samples of the C4 / C5 workloads with all host threads.  Returns {"kmeans": {...}, "silhouette": {...}}."""
+    import numpy as np
+    import sklearn
+    from sklearn.cluster import KMeans
+    from sklearn.metrics import silhouette_score
+    cores = os.cpu_count() or 1
+    out = {}
+    rng = np.random.default_rng(1)
+    n, d, k, iters = 4_000_000, 32, 8, 10
+    cent = rng.normal(0, 3, size=(16, d)).astype(np.float32)
+    X = cent[rng.integers(0, 16, n)] + rng.standard_normal((n, d), dtype=np.float32)
+    init = X[rng.permutation(n)[:k]].copy()
+    t0 = time.perf_counter()
+    km = KMeans(k, init=init, n_init=1, max_iter=iters, tol=0.0).fit(X)
+    dt = time.perf_counter() - t0
+    out["kmeans"] = {"value": n * km.n_iter_ / dt, "unit": "point-assigns/s", "cores": cores,
+                     "kind": f"reference (scikit-learn {sklearn.__version__})",
+                     "sample": f"KMeans(k={k}, init=array, n_init=1, max_iter={iters}, tol=0).fit on {n} x {d} fp32: "
+                               f"{km.n_iter_} iterations in {dt:.2f} s"}
+    del X
+    n2, d2, k2 = 20_000, 64, 8
+    cent = rng.normal(0, 3, size=(k2, d2)).astype(np.float32)
+    lab = rng.integers(0, k2, n2)
+    X2 = cent[lab] + rng.standard_normal((n2, d2), dtype=np.float32)
+    t0 = time.perf_counter()
+    sc = silhouette_score(X2, lab)
+    dt = time.perf_counter() - t0
+    out["silhouette"] = {"value": n2 * n2 / dt, "unit": "ordered pairs/s", "cores": cores,
+                         "kind": f"reference (scikit-learn {sklearn.__version__})",
+                         "sample": f"silhouette_score on {n2} x {d2} fp32, k={k2}: {dt:.2f} s (score {sc:.4f})"}
+    return out
+
+
 def cpu_vae_steps(batch: int, steps: int, warmup: int):
     """The reference's script-12 train step on the host cores: torch-CPU restatement of ConvMultiModalVAE + MSE + KL
     + Adam (oracle/vae_ref.py, pinned against the reference classes by oracle/make_golden.py).  Returns clips/s."""
@@ -510,6 +546,13 @@ def main():
         cpu = {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
                "sample": f"3 steps (+1 warm-up) of the full batch-{BATCH} step, torch-CPU fp32 restatement of the "
                          f"reference classes, {spstep:.2f} s/step"}
+    if rank == 0 and world == 1 and not args.skip_cpu and extra:
+        try:
+            cb = cpu_cluster_baselines()
+            extra["kmeans"]["cpu_baseline"] = cb["kmeans"]
+            extra["silhouette"]["cpu_baseline"] = cb["silhouette"]
+        except Exception as e:  # scikit-learn missing on the box: say so instead of failing the headline
+            extra["kmeans"]["cpu_baseline"] = {"unavailable": repr(e)}
     if rank == 0:
         clips = vae["gb"] * args.steps
         roof = roofline_from_summary(vae["summ"], args.steps, vae["n_params"], pk, vae["ms_prof"] / args.steps)
