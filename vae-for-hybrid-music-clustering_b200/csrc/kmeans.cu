@@ -567,6 +567,7 @@ kmeans_tc_kernel(const KmTcArgs ta, const __grid_constant__ CUtensorMap tmap) {
         uint32_t cand = 0u;
 #pragma unroll
         for (int j = 0; j < KP; ++j) cand |= (v[j] <= thr) ? (1u << j) : 0u;
+        cand &= k >= 32 ? 0xffffffffu : (1u << k) - 1u;   // padding centroids can only pass if thr is inf (non-finite input)
         label = cand ? __ffs((int)cand) - 1 : 0;   // cand == 0 only for NaN input (FFMA kernel: label 0)
         if (cand & (cand - 1u)) {   // several centroids inside the error band: decide with the reference FMA chain
           float4 xr[8];
