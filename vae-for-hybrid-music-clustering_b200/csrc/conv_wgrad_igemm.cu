@@ -44,12 +44,27 @@ __device__ __forceinline__ float wg_ldg(const float* p, uint32_t pred) {
   return v;
 }
 
+// 8-byte variant (the address must be 8-byte aligned when pred != 0)
+__device__ __forceinline__ float2 wg_ldg2(const float* p, uint32_t pred) {
+  float2 v;
+  asm("{\n\t.reg .pred q;\n\tsetp.ne.b32 q, %3, 0;\n\tmov.f32 %0, 0f00000000;\n\tmov.f32 %1, 0f00000000;\n\t"
+      "@q ld.global.nc.v2.f32 {%0, %1}, [%2];\n\t}"
+      : "=f"(v.x), "=f"(v.y)
+      : "l"(p), "r"(pred));
+  return v;
+}
+
 // One real row of the B tile, (cq, tap) of Q: element offset relative to the lane's pixel, the validity bit to test in
 // the lane's tap mask, and the row's byte offset in a stage with the row's swizzle phase folded in (bits 4-6), so a
 // lane's store address is  soffx ^ ((chunk << 4) | 4*(lane & 3)).
 struct __align__(16) WgRow { int off; uint32_t bit; uint32_t soffx; int pad; };
 
+// VEC: both spatial widths are even, so a lane's pixel pair (j, j+1) sits in one row and its T+2 source columns
+// 2j-1 .. 2j+T start one float before an 8-byte boundary: a group of T tile rows (one (cq, th), tw = 0..T-1) is fed by
+// two 8-byte loads plus one or two predicated scalars instead of 2T scalar loads, and an A row by one 8-byte load.
+template <int VT>   // 0: scalar producers; 3 / 4: vector producers for T = 3 / 4
 __global__ void __launch_bounds__(WG_THREADS, 1) conv_wgrad_igemm_kernel(const WgArgs a) {
+  constexpr bool VEC = VT != 0;
   extern __shared__ unsigned char smem_raw[];
   unsigned char* smem = smem_raw + ((1024u - (tma::s32(smem_raw) & 1023u)) & 1023u);
   const int S = a.stages;
@@ -75,7 +90,16 @@ __global__ void __launch_bounds__(WG_THREADS, 1) conv_wgrad_igemm_kernel(const W
   }
   if (warp == 8) tc05::tmem_alloc(tmem_slot, tmem_cols);
   const int ncols = min(a.BN, a.N - n_base);   // real columns of this tile
-  for (int nl = threadIdx.x; nl < ncols; nl += WG_THREADS) {
+  if (VEC) {   // one entry per row group (cq, th): source offset of column 2j-1 and the th validity bit
+    for (int gi = threadIdx.x; gi < ncols / a.T; gi += WG_THREADS) {
+      const int n = n_base + gi * a.T;
+      const int cq = n / a.taps, th = (n - cq * a.taps) / a.T;
+      WgRow t;
+      t.off = cq * a.SH * a.SW + th * a.SW; t.bit = 1u << th; t.soffx = 0; t.pad = 0;
+      rowtab[gi] = t;
+    }
+  }
+  for (int nl = threadIdx.x; !VEC && nl < ncols; nl += WG_THREADS) {
     const int n = n_base + nl;
     const int cq = n / a.taps, tap = n - cq * a.taps, th = tap / a.T, tw = tap - th * a.T;
     WgRow t;
@@ -102,7 +126,11 @@ __global__ void __launch_bounds__(WG_THREADS, 1) conv_wgrad_igemm_kernel(const W
     const int gsize = a.gsize, ngroups = 8 / gsize;
     const int group = warp / gsize, wig = warp - group * gsize;
     const int unitsA = ((a.Cp + gsize - 1) / gsize + 15) / 16;
-    const int units = unitsA + ((ncols + gsize - 1) / gsize + 15) / 16;
+    // VEC: a B unit is GPU row groups of T rows (4 x 4 or 5 x 3 rows = 32 / 30 values per lane)
+    constexpr int T = VEC ? VT : 1, GPU = VT == 4 ? 4 : 5;
+    const int ngrp = ncols / T;
+    const int units = unitsA + (VEC ? ((ngrp + gsize - 1) / gsize + GPU - 1) / GPU
+                                    : ((ncols + gsize - 1) / gsize + 15) / 16);
     const int nmine = nkb > group ? (nkb - group + ngroups - 1) / ngroups : 0;
     const uint32_t lane_x = (((uint32_t)lane >> 2) << 4) | ((uint32_t)(lane & 3) * 4u);
 
@@ -120,6 +148,7 @@ __global__ void __launch_bounds__(WG_THREADS, 1) conv_wgrad_igemm_kernel(const W
     const float* pp[2];
     const float* qq[2];
     uint32_t tapmask[2];
+    uint32_t vmask = 0, ok_left = 0, ok_right = 0;   // VEC: valid th bits of the pair's row, column 2j-1 / 2j+4 in range
     auto pixel_state = [&]() {
 #pragma unroll
       for (int e = 0; e < 2; ++e) {
@@ -136,6 +165,11 @@ __global__ void __launch_bounds__(WG_THREADS, 1) conv_wgrad_igemm_kernel(const W
         uint32_t msk = 0;
         for (int t = 0; t < a.T; ++t) msk |= ((mh >> t) & 1u) ? (mw << (t * a.T)) : 0u;
         tapmask[e] = pb[e] < a.B ? (msk | (1u << 31)) : 0u;
+        if (VEC && e == 0) {
+          vmask = pb[0] < a.B ? mh : 0u;
+          ok_left = j > 0 ? 1u : 0u;
+          ok_right = 2 * j + 4 < a.SW ? 1u : 0u;
+        }
       }
     };
     pixel_state();
@@ -157,8 +191,39 @@ __global__ void __launch_bounds__(WG_THREADS, 1) conv_wgrad_igemm_kernel(const W
         for (int r = 0; r < 16; ++r) {
           const int cp = wig + gsize * (u * 16 + r);
           const uint32_t rok = cp < a.Cp ? 1u : 0u;
-          v[2 * r] = wg_ldg(pp[0] + cp * G, ok0 & rok);
-          v[2 * r + 1] = wg_ldg(pp[1] + cp * G, ok1 & rok);
+          if (VEC) {   // the pair is both in or both out (K is even), consecutive and 8-byte aligned
+            const float2 t2 = wg_ldg2(pp[0] + cp * G, ok0 & rok);
+            v[2 * r] = t2.x; v[2 * r + 1] = t2.y;
+          } else {
+            v[2 * r] = wg_ldg(pp[0] + cp * G, ok0 & rok);
+            v[2 * r + 1] = wg_ldg(pp[1] + cp * G, ok1 & rok);
+          }
+        }
+      } else if (VEC) {   // row groups of the B tile: (cq, th), all tw at once
+#pragma unroll
+        for (int r = 0; r < 5; ++r) {
+          if (r < GPU) {
+            const int gi = wig + gsize * ((u - unitsA) * GPU + r);
+            int2 t = make_int2(0, 0);
+            if (gi < ngrp) t = *reinterpret_cast<const int2*>(&rowtab[gi]);
+            const uint32_t ok = vmask & (uint32_t)t.y;          // row 2i-1+th inside the image (and a real group)
+            const float* src = qq[0] + t.x;                      // column 2j-1 of that row
+            const float fl = wg_ldg(src, ok ? ok_left : 0u);
+            const float2 m0 = wg_ldg2(src + 1, ok), m1 = wg_ldg2(src + 3, ok);
+            if (T == 4) {
+              const float fr = wg_ldg(src + 5, ok ? ok_right : 0u);
+              float* o = v + 8 * r;   // (pixel j, pixel j+1) for tw = 0..3
+              o[0] = fl;   o[1] = m0.y;
+              o[2] = m0.x; o[3] = m1.x;
+              o[4] = m0.y; o[5] = m1.y;
+              o[6] = m1.x; o[7] = fr;
+            } else {
+              float* o = v + 6 * r;   // tw = 0..2
+              o[0] = fl;   o[1] = m0.y;
+              o[2] = m0.x; o[3] = m1.x;
+              o[4] = m0.y; o[5] = m1.y;
+            }
+          }
         }
       } else {            // rows of the B tile: (cq, tap) of Q
 #pragma unroll
@@ -182,6 +247,24 @@ __global__ void __launch_bounds__(WG_THREADS, 1) conv_wgrad_igemm_kernel(const W
           const uint32_t cp = (uint32_t)(wig + gsize * (u * 16 + r));
           if (cp < (uint32_t)a.Cp)
             *reinterpret_cast<uint32_t*>(tile + ((cp * 128u + ((cp & 7u) << 4)) ^ lane_x)) = wg_pack(v[2 * r], v[2 * r + 1]);
+        }
+      } else if (VEC) {
+#pragma unroll
+        for (int r = 0; r < 5; ++r) {
+          if (r < GPU) {
+            const int gi = wig + gsize * ((u - unitsA) * GPU + r);
+            if (gi < ngrp) {
+#pragma unroll
+              for (int tw = 0; tw < 4; ++tw) {
+                if (tw < T) {
+                  const uint32_t nl = (uint32_t)(gi * T + tw);
+                  const uint32_t so = WG_A_BYTES + nl * 128u + ((nl & 7u) << 4);
+                  *reinterpret_cast<uint32_t*>(tile + (so ^ lane_x)) =
+                      wg_pack(v[2 * (T * r + tw)], v[2 * (T * r + tw) + 1]);
+                }
+              }
+            }
+          }
         }
       } else {
 #pragma unroll
@@ -288,6 +371,8 @@ static WgPlan wg_plan(int op, int B, int Cin, int H, int W, int Cout) {
   p.N = p.Cq * p.T * p.T;
   p.ntiles = (p.N + 255) / 256;
   p.BN = ((p.N + p.ntiles - 1) / p.ntiles + 31) / 32 * 32;
+  // (T = 3 tiles that hold whole row groups would need BN % 96 == 0: measured slower -- unbalanced tiles -- so the
+  // vector producers below are used for T = 4 only, where BN % 4 == 0 always holds)
   const int64_t K = (int64_t)B * p.GH * p.GW;
   p.ok = p.Cp <= 128 && K < 2147483647LL - 64 && (int64_t)B * (Cin > Cout ? Cin : Cout) * 4 * H * W < 2147483647LL;
   if (!p.ok) return p;
@@ -337,9 +422,13 @@ int conv_wgrad_igemm_run(int op, const float* dy, const float* x, float* dw, int
   }
   a.idesc = tc05::idesc(tc05::kFmtBF16, 128, p.BN, 0, 0);
   const size_t smem = (size_t)stages * st_bytes + (2 * stages + 1) * 8 + 16 + (size_t)p.BN * 16 + 1024;
-  VC_CUDA(cudaFuncSetAttribute(conv_wgrad_igemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  // vector producers: even widths (pixel pairs never straddle a row, 8-byte aligned sources), whole row groups per tile
+  const bool vec = p.T == 4 && p.GW % 2 == 0 && p.SW % 2 == 0 && p.BN % p.T == 0 && p.N % p.T == 0 &&
+                   ((reinterpret_cast<uintptr_t>(a.P) | reinterpret_cast<uintptr_t>(a.Q)) & 7) == 0;
+  auto kern = !vec ? conv_wgrad_igemm_kernel<0> : (p.T == 4 ? conv_wgrad_igemm_kernel<4> : conv_wgrad_igemm_kernel<3>);
+  VC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   dim3 grid((unsigned)p.nsplit, (unsigned)p.ntiles);
-  conv_wgrad_igemm_kernel<<<grid, WG_THREADS, smem, s>>>(a);
+  kern<<<grid, WG_THREADS, smem, s>>>(a);
   VC_LAUNCH_CHECK();
   const int total = p.Cp * p.N;
   wgrad_fold_kernel<<<(total + 255) / 256, 256, 0, s>>>(a.part, p.nsplit, total, dw);
