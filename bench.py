@@ -252,6 +252,7 @@ def bench_vae(args, rank, world, device, group):
     # stream (a graph replay cannot be bracketed per call); these durations feed `roofline`, shares are taken against
     # this pass's own step time.  Runs last: eager steps re-point the optimizer's chunk table away from the graph.
     eager = step.step if use_graph else step
+    eager.overlap = False   # per-kernel durations need serial launches: the early Adam updates go back into one launch
     resident_step(0, eager)
     prof = Profiler()
     L.profiler = prof

@@ -164,6 +164,13 @@ typedef struct VcAdamDeviceStep {
 } VcAdamDeviceStep;
 int vc_adam_multi_graph(const VcAdamChunk* table, int n_chunks, float lr, float beta1, float beta2, float eps,
                         VcAdamDeviceStep* step_state, void* stream);
+/* The two halves of vc_adam_multi_graph on their own, for a step that updates its parameters in several launches
+ * (vaeclust.optim.Adam.overlap: the 67 M-element FC weights are updated on a side stream as soon as backward has
+ * produced their gradients, under the rest of backward): vc_adam_tick advances the counter once per step,
+ * vc_adam_multi_at updates the chunks of `table` with the bias corrections of the current device step. */
+int vc_adam_tick(VcAdamDeviceStep* step_state, float beta1, float beta2, void* stream);
+int vc_adam_multi_at(const VcAdamChunk* table, int n_chunks, float lr, float beta1, float beta2, float eps,
+                     const VcAdamDeviceStep* step_state, void* stream);
 
 /* --------------------------------------------------------------------------------------------- KMeans
  * One Lloyd iteration of sklearn:cluster/_k_means_lloyd.pyx:23-218 reached from 07:70-71, 13:120-121, 16:183,

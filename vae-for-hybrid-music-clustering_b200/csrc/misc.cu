@@ -432,6 +432,25 @@ extern "C" int vc_adam_multi_graph(const VcAdamChunk* table, int n_chunks, float
   return VC_OK;
 }
 
+// The two halves of vc_adam_multi_graph as separate entry points: a step that updates its parameters in several
+// launches (large gradients as soon as backward has produced them, on a side stream, under the rest of backward)
+// advances the device step counter once, then every launch reads the bias corrections of that step.
+extern "C" int vc_adam_tick(VcAdamDeviceStep* step_state, float beta1, float beta2, void* stream) {
+  VC_REQUIRE(step_state, VC_ERR_BAD_ARG, "vc_adam_tick: bad arguments");
+  adam_tick_kernel<<<1, 1, 0, as_stream(stream)>>>(step_state, beta1, beta2);
+  VC_LAUNCH_CHECK();
+  return VC_OK;
+}
+
+extern "C" int vc_adam_multi_at(const VcAdamChunk* table, int n_chunks, float lr, float beta1, float beta2, float eps,
+                                const VcAdamDeviceStep* step_state, void* stream) {
+  VC_REQUIRE(table && n_chunks >= 0 && step_state, VC_ERR_BAD_ARG, "vc_adam_multi_at: bad arguments");
+  if (n_chunks == 0) return VC_OK;
+  adam_multi_kernel<<<n_chunks, kAdamThreads, 0, as_stream(stream)>>>(table, lr, beta1, beta2, eps, 1.f, 1.f, step_state);
+  VC_LAUNCH_CHECK();
+  return VC_OK;
+}
+
 extern "C" size_t vc_col_stats_workspace_bytes(int d) { return sizeof(double) * 2 * (size_t)kColBlocks * d; }
 
 extern "C" int vc_col_stats(const float* X, int64_t N, int d, double* mean, double* var, void* workspace,

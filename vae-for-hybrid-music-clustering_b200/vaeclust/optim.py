@@ -30,13 +30,17 @@ class Adam:
                 raise VaeclustError("vaeclust.optim.Adam: parameters must be float32 CUDA tensors (no CPU path)")
         self.lr, self.betas, self.eps = float(lr), (float(betas[0]), float(betas[1])), float(eps)
         self.state: Dict[int, dict] = {}
-        self._table = None
-        self._table_key = None
+        self._tables: Dict[tuple, dict] = {}   # chunk tables on the device, one per launch group
         # capturable (torch.optim.Adam(capturable=True)): step counter and bias corrections live on the device, so a
         # step recorded in a CUDA graph advances correctly on every replay (vc_adam_multi_graph)
         self.capturable = bool(capturable)
         self._dev_step = None
-        self._table_pinned = None
+        self._early: Dict[int, int] = {}       # id(param) -> slot of the parameters updated from a grad hook
+        self._early_stream = None
+        self._early_done = None                # ids updated early in the current step (None: not in overlap mode)
+        self._early_pending = False
+        self._ticked = False
+        self._hooks: list = []
         self.param_groups = [{"params": self.params, "lr": self.lr, "betas": self.betas, "eps": self.eps}]
 
     def zero_grad(self, set_to_none: bool = True) -> None:
@@ -56,13 +60,57 @@ class Adam:
             self.state[id(p)] = st
         return st
 
+    # ------------------------------------------------------------------ overlap of large updates with backward
+    def overlap(self, params: Iterable[torch.nn.Parameter], stream: "torch.cuda.Stream | None" = None) -> None:
+        """Update `params` EARLY: a post-accumulate-grad hook launches the Adam update of each of them on `stream`
+        (a side stream) the moment backward has written its gradient, so the 28 B/parameter sweep over a large
+        tensor runs under the remaining (instruction-bound, not HBM-bound) backward kernels instead of after them.
+        `step()` then updates only the other parameters and joins the side stream.  The caller must call
+        `begin_step()` before backward of every step.  Arithmetic is unchanged (same kernel, same step count)."""
+        params = [p for p in params]
+        known = {id(p) for p in self.params}
+        for p in params:
+            if id(p) not in known:
+                raise ValueError("Adam.overlap: parameter is not managed by this optimizer")
+        for h in self._hooks:
+            h.remove()
+        self._hooks = []
+        self._early = {id(p): i for i, p in enumerate(params)}
+        self._early_stream = stream if stream is not None else torch.cuda.Stream(device=params[0].device)
+        for p in params:
+            self._hooks.append(p.register_post_accumulate_grad_hook(self._early_hook))
+
     @torch.no_grad()
-    def step(self) -> None:
-        self.lr = float(self.param_groups[0]["lr"])
+    def begin_step(self) -> None:
+        """Start of a step in overlap mode: forget which parameters were updated early and, in capturable mode,
+        advance the device step counter once for all launches of this step."""
+        self._early_done = set()
+        self._ticked = False
+        if self._early and self.capturable:
+            if self._dev_step is None:
+                dev = self.params[0].device
+                t0 = max((st["step"] for st in self.state.values()), default=0)
+                self._dev_step = torch.zeros(4, dtype=torch.int32, device=dev)
+                self._dev_step[0] = t0
+            lib().call("vc_adam_tick", ptr(self._dev_step), self.betas[0], self.betas[1], stream_ptr())
+            self._ticked = True
+
+    def _early_hook(self, p) -> None:
+        if self._early_done is None or p.grad is None:   # begin_step() not called: step() handles p as usual
+            return
+        cur = torch.cuda.current_stream(p.device)
+        side = self._early_stream
+        side.wait_stream(cur)
+        with torch.cuda.stream(side), torch.no_grad():
+            self._update([p], slot=("early", self._early[id(p)]))
+        self._early_done.add(id(p))
+        self._early_pending = True
+
+    # ----------------------------------------------------------------------------------------------- the update
+    def _update(self, plist, slot) -> None:
+        """One launch per distinct step count over the chunk table of `plist` on the current stream."""
         by_step: Dict[int, list] = {}
-        for p in self.params:
-            if p.grad is None:
-                continue
+        for p in plist:
             g = p.grad
             if not g.is_contiguous():
                 g = g.contiguous()
@@ -89,6 +137,7 @@ class Adam:
             key = table.tobytes()
             dev = items[0][0].device
             b1, b2 = self.betas
+            c = self._tables.setdefault(slot, {"key": None, "dev": None, "pinned": None})
             if self.capturable:
                 if len(by_step) != 1:
                     raise VaeclustError("vaeclust.optim.Adam(capturable=True): every stepped parameter must share one "
@@ -96,23 +145,40 @@ class Adam:
                 if self._dev_step is None:
                     self._dev_step = torch.zeros(4, dtype=torch.int32, device=dev)
                     self._dev_step[0] = t - 1
-                if self._table_key != key or self._table is None or self._table.device != dev:
+                if c["key"] != key or c["dev"] is None or c["dev"].device != dev:
                     # pinned + async so the upload is legal inside a capture (a replay re-reads the same host buffer);
                     # both buffers are allocated by the first eager step and only rewritten afterwards
-                    if self._table_pinned is None or tuple(self._table_pinned.shape) != table.shape:
-                        self._table_pinned = torch.empty(table.shape, dtype=torch.int64).pin_memory()
-                        self._table = torch.empty(table.shape, dtype=torch.int64, device=dev)
-                    self._table_pinned.numpy()[...] = table
-                    self._table.copy_(self._table_pinned, non_blocking=True)
-                    self._table_key = key
-                lib().call("vc_adam_multi_graph", ptr(self._table), int(table.shape[0]), self.lr, b1, b2, self.eps,
-                           ptr(self._dev_step), stream_ptr())
+                    if c["pinned"] is None or tuple(c["pinned"].shape) != table.shape:
+                        c["pinned"] = torch.empty(table.shape, dtype=torch.int64).pin_memory()
+                        c["dev"] = torch.empty(table.shape, dtype=torch.int64, device=dev)
+                    c["pinned"].numpy()[...] = table
+                    c["dev"].copy_(c["pinned"], non_blocking=True)
+                    c["key"] = key
+                if self._ticked:
+                    lib().call("vc_adam_multi_at", ptr(c["dev"]), int(table.shape[0]), self.lr, b1, b2, self.eps,
+                               ptr(self._dev_step), stream_ptr())
+                else:
+                    lib().call("vc_adam_multi_graph", ptr(c["dev"]), int(table.shape[0]), self.lr, b1, b2, self.eps,
+                               ptr(self._dev_step), stream_ptr())
                 continue
-            if self._table_key != key or self._table is None or self._table.device != dev:
-                self._table = torch.from_numpy(table).to(dev, non_blocking=False)
-                self._table_key = key
-            lib().call("vc_adam_multi", ptr(self._table), int(table.shape[0]), self.lr, b1, b2, self.eps,
+            if c["key"] != key or c["dev"] is None or c["dev"].device != dev:
+                c["dev"] = torch.from_numpy(table).to(dev, non_blocking=False)
+                c["key"] = key
+            lib().call("vc_adam_multi", ptr(c["dev"]), int(table.shape[0]), self.lr, b1, b2, self.eps,
                        1.0 - b1 ** t, 1.0 - b2 ** t, stream_ptr())
+
+    @torch.no_grad()
+    def step(self) -> None:
+        self.lr = float(self.param_groups[0]["lr"])
+        done = self._early_done or ()
+        rest = [p for p in self.params if p.grad is not None and id(p) not in done]
+        if rest:
+            self._update(rest, slot=("rest",))
+        if self._early_pending:
+            torch.cuda.current_stream(self.params[0].device).wait_stream(self._early_stream)
+            self._early_pending = False
+        self._early_done = None
+        self._ticked = False
 
     def state_dict(self) -> dict:
         if self.capturable and self._dev_step is not None:   # replays advance the device counter only

@@ -8,6 +8,7 @@ instead of 3 `.item()` syncs per step; the latent export skips the decoder (the 
 """
 from __future__ import annotations
 
+import os
 from dataclasses import dataclass, field
 from typing import Callable, List, Optional
 
@@ -18,6 +19,8 @@ from . import dist as vdist
 from . import ops
 from ._lib import VC_LOSS_MEAN_MEAN, VC_LOSS_SUM_MEAN
 from .optim import Adam
+
+_OVERLAP_MIN_NUMEL = 1 << 22   # parameters at least this large are updated early, on a side stream (Adam.overlap)
 
 
 def epoch_permutation(n: int) -> torch.Tensor:
@@ -48,6 +51,15 @@ class VAEStep:
         self.multi = group is not None and vdist.world_size(group) > 1
         self.opt = Adam(model.parameters(), lr=lr, capturable=capturable)
         self.sync = vdist.OverlappedGradSync(model.parameters(), group) if self.multi else None
+        # opt-in (VAECLUST_ADAM_OVERLAP=1), one GPU: the Adam sweep over a large weight (28 B/parameter) starts on a
+        # side stream as soon as backward has produced its gradient and runs under the remaining backward kernels.
+        # Bit-identical, but measured SLOWER on script 12 (4.86 -> 4.95-5.00 ms/step, B200): the co-resident Adam CTAs
+        # take issue slots and L2 bandwidth from the instruction-bound implicit-GEMM producers, which costs more than
+        # the 0.6 ms sweep that gets hidden.  Kept off by default; DESIGN.md 5 records the experiment.
+        big = [p for p in model.parameters() if p.numel() >= _OVERLAP_MIN_NUMEL]
+        self.overlap = bool(big) and not self.multi and os.environ.get("VAECLUST_ADAM_OVERLAP", "0") == "1"
+        if self.overlap:
+            self.opt.overlap(big)
 
     def __call__(self, x, *extra, eps: Optional[torch.Tensor] = None, global_batch: Optional[int] = None):
         m = self.model
@@ -55,6 +67,8 @@ class VAEStep:
             self.sync.begin(x.shape[0], global_batch or x.shape[0] * vdist.world_size(self.group))
         else:
             self.opt.zero_grad()
+        if self.overlap:
+            self.opt.begin_step()
         if self.kind == "conv12":
             lyr, mask = extra
             mu, lv = m.encode(x, lyr, mask)
