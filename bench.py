@@ -156,10 +156,10 @@ def family_of(name: str, sig) -> str:
     op, _prec, B, Cin, H, W, Cout = sig[:7]
     if op <= 2:
         return "skinny_gemm (FC 262144<->256)" if Cin * Cout >= (1 << 22) else "small_linear (mma.sync, latent head)"
+    if (op in (3, 5) and Cin == 1) or (op in (6, 7, 8) and Cout == 1):   # incl. the tap-correlation weight gradients
+        return "conv_direct (1-channel ends)"
     if op in (5, 8):
         return "conv_wgrad_igemm"
-    if (op == 3 and Cin == 1) or (op in (6, 7) and Cout == 1):
-        return "conv_direct (1-channel ends)"
     return "conv_igemm (fwd / dgrad)"
 
 

@@ -171,6 +171,56 @@ def _check_bf16(fn_ours, fn_ref, x, w, b):
         torch.testing.assert_close(p.grad, q.grad, rtol=3e-2, atol=2e-2 * scale, msg=lambda m: f"{n}: {m}")
 
 
+@pytest.mark.parametrize("kind,B,C,H,W", [("conv", 2, 32, 16, 24), ("conv", 3, 8, 17, 32), ("conv", 2, 32, 128, 1024),
+                                          ("conv", 1, 4, 1, 8), ("convT", 2, 32, 8, 12), ("convT", 3, 32, 7, 40),
+                                          ("convT", 2, 32, 64, 512), ("convT", 1, 4, 1, 4)])
+def test_single_channel_wgrad_tap_kernel(kind, B, C, H, W, bf16_mode):
+    """Weight gradients of the single-channel ends (Conv2d(1 -> C) k3 with W % 8 == 0, ConvTranspose2d(C -> 1) k4 with
+    W % 4 == 0) take the streaming tap-correlation kernel, which multiplies the fp32 values (no bf16 rounding of dy
+    and x).  Against float64 autograd the only difference is fp32 summation: 2e-5 of the gradient's scale."""
+    from vaeclust import ops
+    if kind == "conv":
+        x, w = _rand(B, 1, H, W, seed=1), _rand(C, 1, 3, 3, seed=2, scale=1 / 3)
+        ours = lambda x, w: ops.conv2d_s2k3(x, w, None, False)
+        ref = lambda x, w: F.conv2d(x, w, None, stride=2, padding=1)
+    else:
+        x, w = _rand(B, C, H, W, seed=1), _rand(C, 1, 4, 4, seed=2, scale=(C * 4) ** -0.5)
+        ours = lambda x, w: ops.convT2d_s2k4(x, w, None, False)
+        ref = lambda x, w: F.conv_transpose2d(x, w, None, stride=2, padding=1)
+    wa = w.clone().requires_grad_(True)
+    ya = ours(x, wa)
+    g = torch.randn_like(ya)
+    ya.backward(g)
+    wb = w.double().requires_grad_(True)
+    ref(x.double(), wb).backward(g.double())
+    scale = float(wb.grad.abs().max())
+    assert float((wa.grad.double() - wb.grad).abs().max()) <= 2e-5 * scale
+    # deterministic: a second evaluation gives the same bits
+    wa2 = w.clone().requires_grad_(True)
+    ours(x, wa2).backward(g)
+    assert torch.equal(wa.grad, wa2.grad)
+
+
+@pytest.mark.parametrize("B,Cin,H,W,relu", [(2, 32, 8, 12, False), (3, 32, 7, 40, True), (2, 32, 64, 128, False),
+                                             (1, 5, 1, 4, True), (2, 8, 33, 256, True)])
+def test_convT_to1_quad_kernel_equals_scalar_kernel(B, Cin, H, W, relu, bf16_mode):
+    """ConvTranspose2d(Cin -> 1) forward: the 2 x 4-pixel-per-thread kernel (W % 4 == 0, 16-byte aligned input) keeps
+    the FMA order of the 2 x 1 kernel, so a misaligned copy of the same input (which takes the scalar kernel) must give
+    identical bits; both match torch on the bf16-rounded operands (the direct kernels belong to the bf16 mode)."""
+    from vaeclust import ops
+    x, w, b = _rand(B, Cin, H, W, seed=4), _rand(Cin, 1, 4, 4, seed=5, scale=(Cin * 4) ** -0.5), _rand(1, seed=6)
+    store = torch.empty(x.numel() + 1, device=x.device)
+    x_off = store[1:].view_as(x)
+    x_off.copy_(x)
+    assert x.data_ptr() % 16 == 0 and x_off.data_ptr() % 16 == 4
+    with torch.no_grad():
+        y_quad, y_scalar = ops.convT2d_s2k4(x, w, b, relu), ops.convT2d_s2k4(x_off, w, b, relu)
+        ref = F.conv_transpose2d(_r(x), _r(w), b, stride=2, padding=1)
+        ref = F.relu(ref) if relu else ref
+    assert torch.equal(y_quad, y_scalar)
+    torch.testing.assert_close(y_quad, ref, rtol=2e-5, atol=2e-6)
+
+
 @pytest.mark.parametrize("M,N,K,relu", [(64, 256, 470, True), (17, 16, 256, False), (3, 700, 33, True),
                                         (64, 256, 8200, True), (64, 4100, 256, True),
                                         # latent-head / lyrics-branch shapes: the one-launch mma.sync kernel

@@ -12,6 +12,16 @@ namespace vc {
 __device__ __forceinline__ float rb(float v, int round_bf16) {
   return round_bf16 ? __bfloat162float(__float2bfloat16_rn(v)) : v;
 }
+// two values through one packed conversion (F2FP.BF16.F32.PACK_AB on the ALU pipe + two bit operations) instead of
+// two scalar F2F conversions, which issue at a quarter of the rate and were 0.045 ms of the Cin -> 1 deconvolution
+__device__ __forceinline__ void rb2(float& a, float& b, int round_bf16) {
+  if (round_bf16) {
+    const __nv_bfloat162 h = __floats2bfloat162_rn(a, b);   // .x = a (low half), .y = b (high half)
+    const uint32_t u = *reinterpret_cast<const uint32_t*>(&h);
+    a = __uint_as_float(u << 16);
+    b = __uint_as_float(u & 0xffff0000u);
+  }
+}
 
 // ---- Conv2d(1 -> Cout): y[b,co,oh,ow] = act(bias[co] + sum_{kh,kw} x[b,0,2oh+kh-1,2ow+kw-1] * W[co,0,kh,kw])
 // shared weights transposed to wt[tap][co] (co padded to a multiple of 4) so four channels come from one LDS.128
@@ -141,6 +151,91 @@ convT_to1_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w, c
   }
 }
 
+// ---- the same operator, thread = 2 input rows x 4 input columns (W % 4 == 0, 16-byte aligned x): the kernel above
+// issues 12 scalar loads per channel for two input pixels and is bound by the load/store unit's one warp-load per clock
+// (50 M warp loads = 0.18 ms of its 0.21 ms at 64 x 32 x 64 x 512); here a 4 x 6 patch is one 16-byte load plus two
+// halo scalars per row, i.e. the same 12 load instructions feed four times the pixels.  The FMA order of every output
+// is the one of the kernel above, so both produce identical bits.
+__global__ void __launch_bounds__(256, 2)
+convT_to1_fwd_quad_kernel(const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ bias,
+                          float* __restrict__ y, int B, int Cin, int H, int W, int relu, int round_bf16) {
+  extern __shared__ float sm[];   // [Cin][16]
+  for (int e = threadIdx.x; e < Cin * 16; e += blockDim.x) sm[e] = rb(w[e], round_bf16);
+  __syncthreads();
+  const int H2 = (H + 1) / 2, W4 = W >> 2;
+  const int64_t total = (int64_t)B * H2 * W4;
+  const int64_t plane = (int64_t)H * W;
+  const float b0 = bias ? bias[0] : 0.f;
+  for (int64_t m = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; m < total; m += (int64_t)gridDim.x * blockDim.x) {
+    const int j = (int)(m % W4) * 4;
+    const int64_t t2 = m / W4;
+    const int i2 = (int)(t2 % H2), b = (int)(t2 / H2);
+    const int i = 2 * i2;
+    bool rok[4];
+#pragma unroll
+    for (int r = 0; r < 4; ++r) rok[r] = (unsigned)(i - 1 + r) < (unsigned)H;
+    const uint32_t lok = j > 0 ? 1u : 0u, hok = j + 4 < W ? 1u : 0u;
+    float acc[4][8];
+#pragma unroll
+    for (int r = 0; r < 4; ++r)
+#pragma unroll
+      for (int c = 0; c < 8; ++c) acc[r][c] = b0;
+    const float* xb = x + (int64_t)b * Cin * plane + (int64_t)(i - 1) * W + j;
+    // (an explicit register pipeline over channels -- loads of ci+1 under the FMAs of ci -- measured slower than letting
+    // the compiler overlap two unrolled channels: 0.127 vs 0.115 ms)
+#pragma unroll 2
+    for (int ci = 0; ci < Cin; ++ci) {
+      float p[4][6];   // input rows i-1 .. i+2, columns j-1 .. j+4
+      const float* xc = xb + (int64_t)ci * plane;
+#pragma unroll
+      for (int r = 0; r < 4; ++r) {
+        const float* xr = xc + r * W;
+        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (rok[r]) v = __ldg(reinterpret_cast<const float4*>(xr));
+        p[r][0] = ldg_pred(xr - 1, (rok[r] ? 1u : 0u) & lok);
+        p[r][1] = v.x; p[r][2] = v.y; p[r][3] = v.z; p[r][4] = v.w;
+        p[r][5] = ldg_pred(xr + 4, (rok[r] ? 1u : 0u) & hok);
+      }
+#pragma unroll
+      for (int r = 0; r < 4; ++r)
+#pragma unroll
+        for (int c = 0; c < 6; c += 2) rb2(p[r][c], p[r][c + 1], round_bf16);
+      const float4* wq = reinterpret_cast<const float4*>(sm + ci * 16);
+      const float4 w0 = wq[0], w1 = wq[1], w2 = wq[2], w3 = wq[3];   // kernel rows kh = 0..3, .x-.w = kw 0..3
+#pragma unroll
+      for (int a = 0; a < 2; ++a) {
+        const float* up = p[a];       // input row i+a-1
+        const float* md = p[a + 1];   // input row i+a
+        const float* dn = p[a + 2];   // input row i+a+1
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {   // input column j+c: patch columns c (left), c+1 (centre), c+2 (right)
+          float s00 = acc[2 * a][2 * c], s01 = acc[2 * a][2 * c + 1];
+          float s10 = acc[2 * a + 1][2 * c], s11 = acc[2 * a + 1][2 * c + 1];
+          s00 = fmaf(up[c], w3.w, s00); s00 = fmaf(up[c + 1], w3.y, s00); s00 = fmaf(md[c], w1.w, s00); s00 = fmaf(md[c + 1], w1.y, s00);
+          s01 = fmaf(up[c + 1], w3.z, s01); s01 = fmaf(up[c + 2], w3.x, s01); s01 = fmaf(md[c + 1], w1.z, s01); s01 = fmaf(md[c + 2], w1.x, s01);
+          s10 = fmaf(md[c], w2.w, s10); s10 = fmaf(md[c + 1], w2.y, s10); s10 = fmaf(dn[c], w0.w, s10); s10 = fmaf(dn[c + 1], w0.y, s10);
+          s11 = fmaf(md[c + 1], w2.z, s11); s11 = fmaf(md[c + 2], w2.x, s11); s11 = fmaf(dn[c + 1], w0.z, s11); s11 = fmaf(dn[c + 2], w0.x, s11);
+          acc[2 * a][2 * c] = s00; acc[2 * a][2 * c + 1] = s01; acc[2 * a + 1][2 * c] = s10; acc[2 * a + 1][2 * c + 1] = s11;
+        }
+      }
+    }
+    const int OW = 2 * W;
+    float* yo = y + (int64_t)b * 4 * plane + (int64_t)(2 * i) * OW + 2 * j;
+#pragma unroll
+    for (int r = 0; r < 4; ++r) {
+      if (i + (r >> 1) < H) {
+        if (relu) {
+#pragma unroll
+          for (int c = 0; c < 8; ++c) acc[r][c] = fmaxf(acc[r][c], 0.f);
+        }
+        float4* o = reinterpret_cast<float4*>(yo + (int64_t)r * OW);
+        o[0] = make_float4(acc[r][0], acc[r][1], acc[r][2], acc[r][3]);
+        o[1] = make_float4(acc[r][4], acc[r][5], acc[r][6], acc[r][7]);
+      }
+    }
+  }
+}
+
 // ---- ConvTranspose2d(Cin -> 1) data-gradient: dx[b,ci,i,j] = sum_{kh,kw} dy[b,0,2i-1+kh,2j-1+kw] * W[ci,0,kh,kw]
 __global__ void __launch_bounds__(256)
 convT_to1_dgrad_kernel(const float* __restrict__ dy, const float* __restrict__ w, float* __restrict__ dx, int B, int Cin,
@@ -181,6 +276,110 @@ convT_to1_dgrad_kernel(const float* __restrict__ dy, const float* __restrict__ w
   }
 }
 
+// ---- weight gradients of the two single-channel ends.  Both are a correlation of a C-channel tensor A [B,C,PH,PW]
+// with KS x KS strided taps of a ONE-channel tensor S [B,1,SH,SW], summed over every pixel:
+//   out[c][kh][kw] = sum_{b,ph,pw} A[b,c,ph,pw] * S[b,0,2ph-1+kh,2pw-1+kw]
+// Conv2d(1 -> C) k3:          A = dy, S = x  (KS = 3);   ConvTranspose2d(C -> 1) k4: A = x, S = dy (KS = 4).
+// As an implicit GEMM this is a 9- or 16-wide problem on a 128-wide tensor-core tile (0.13 ms each); here it is a
+// streaming reduction bound by reading A once (268 MB): thread = four horizontally adjacent pixels of CG channels,
+// A as one 16-byte load per channel, a row of S as two 16-byte loads plus halo scalars, CG*KS*KS register accumulators
+// kept across the thread's whole pixel range, then a fixed-order warp / grid reduction in double.
+template <int KS, int CG>
+__global__ void __launch_bounds__(256, 2)
+tap_wgrad_kernel(const float* __restrict__ A, const float* __restrict__ S, double* __restrict__ part, int B, int C,
+                 int PH, int PW, int SH, int SW, int round_bf16) {
+  constexpr int T = KS * KS, NS = KS + 6;
+  // warp = channel group, lane = pixel quad: the eight warps of a block walk the SAME 32 quads, so the S patch (160 of
+  // the 224 bytes a thread loads per step) comes from L2 once per block and from L1 for the other seven warps.  With
+  // the group on blockIdx.y instead, S was re-read from L2 by every group and the kernel sat at the L2 bandwidth
+  // (7.3 TB/s of L2->SM traffic for 2.3 TB/s of useful HBM traffic).
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int c0 = (blockIdx.y * 8 + warp) * CG;
+  if (c0 >= C) return;
+  const int PW4 = PW >> 2;
+  const int64_t total = (int64_t)B * PH * PW4;
+  const int64_t aplane = (int64_t)PH * PW, splane = (int64_t)SH * SW;
+  float acc[CG][T];
+#pragma unroll
+  for (int c = 0; c < CG; ++c)
+#pragma unroll
+    for (int t = 0; t < T; ++t) acc[c][t] = 0.f;
+  for (int64_t m = (int64_t)blockIdx.x * 32 + lane; m < total; m += (int64_t)gridDim.x * 32) {
+    const int pw0 = (int)(m % PW4) * 4;
+    const int64_t t2 = m / PW4;
+    const int ph = (int)(t2 % PH), b = (int)(t2 / PH);
+    // every load of the iteration is issued before the first FMA (one memory round trip per iteration, not one per
+    // tap row): A as CG 16-byte loads, each tap row of S as two 16-byte loads plus the two halo scalars
+    const float* ap = A + ((int64_t)b * C + c0) * aplane + (int64_t)ph * PW + pw0;
+    const float* sp = S + (int64_t)b * splane + 2 * pw0;
+    const uint32_t lok = pw0 > 0 ? 1u : 0u, hok = 2 * pw0 + 8 < SW ? 1u : 0u;
+    float4 av[CG], s0[KS], s1[KS];
+    float sl[KS], sh[KS];
+#pragma unroll
+    for (int c = 0; c < CG; ++c) av[c] = __ldcs(reinterpret_cast<const float4*>(ap + c * aplane));
+#pragma unroll
+    for (int r = 0; r < KS; ++r) {
+      const int sr = 2 * ph - 1 + r;
+      const bool rok = (unsigned)sr < (unsigned)SH;
+      const float* srow = sp + (int64_t)sr * SW;
+      s0[r] = make_float4(0.f, 0.f, 0.f, 0.f);
+      s1[r] = s0[r];
+      if (rok) {
+        s0[r] = __ldg(reinterpret_cast<const float4*>(srow));
+        s1[r] = __ldg(reinterpret_cast<const float4*>(srow + 4));
+      }
+      sl[r] = ldg_pred(srow - 1, (rok ? 1u : 0u) & lok);
+      sh[r] = KS == 4 ? ldg_pred(srow + 8, (rok ? 1u : 0u) & hok) : 0.f;
+    }
+    float a[CG][4];
+#pragma unroll
+    for (int c = 0; c < CG; ++c) {
+      a[c][0] = av[c].x; a[c][1] = av[c].y; a[c][2] = av[c].z; a[c][3] = av[c].w;
+      rb2(a[c][0], a[c][1], round_bf16);
+      rb2(a[c][2], a[c][3], round_bf16);
+    }
+#pragma unroll
+    for (int r = 0; r < KS; ++r) {
+      float s[NS + 1];   // S columns 2*pw0-1 .. 2*pw0+KS+4 (padded to an even count for the paired rounding)
+      s[0] = sl[r];
+      s[1] = s0[r].x; s[2] = s0[r].y; s[3] = s0[r].z; s[4] = s0[r].w;
+      s[5] = s1[r].x; s[6] = s1[r].y; s[7] = s1[r].z; s[8] = s1[r].w;
+      s[9] = sh[r];
+#pragma unroll
+      for (int q = 0; q < 10; q += 2) rb2(s[q], s[q + 1], round_bf16);
+#pragma unroll
+      for (int c = 0; c < CG; ++c)
+#pragma unroll
+        for (int kw = 0; kw < KS; ++kw) {
+          float v = acc[c][r * KS + kw];
+#pragma unroll
+          for (int px = 0; px < 4; ++px) v = fmaf(a[c][px], s[2 * px + kw], v);
+          acc[c][r * KS + kw] = v;
+        }
+    }
+  }
+  // fixed-order reduction: lanes (xor butterfly) here, blocks in order in the fold kernel, in double
+  double* pp = part + ((int64_t)blockIdx.x * C + c0) * T;
+#pragma unroll
+  for (int c = 0; c < CG; ++c)
+#pragma unroll
+    for (int t = 0; t < T; ++t) {
+      float v = acc[c][t];
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+      if (lane == 0) pp[c * T + t] = (double)v;
+    }
+}
+
+// out[e] = sum over the nblk block partials part[blk][C*T], in block order
+__global__ void tap_wgrad_fold_kernel(const double* __restrict__ part, int nblk, int n, float* __restrict__ out) {
+  const int e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= n) return;
+  double v = 0.0;
+  for (int b = 0; b < nblk; ++b) v += part[(int64_t)b * n + e];
+  out[e] = (float)v;
+}
+
 // ---- host -----------------------------------------------------------------------------------------------------------
 bool conv_direct_supported(int op, int B, int Cin, int H, int W, int Cout) {
   (void)B; (void)H;
@@ -188,6 +387,47 @@ bool conv_direct_supported(int op, int B, int Cin, int H, int W, int Cout) {
   if (op == VC_OP_CONVT_FWD) return Cout == 1 && Cin <= 512;
   if (op == VC_OP_CONVT_DGRAD) return Cout == 1 && Cin <= 512;
   return false;
+}
+
+// weight gradients of the single-channel ends (tap_wgrad_kernel): in0 = dy, in1 = x as in vc_dense_op
+constexpr int kTapBlocks = 2 * 148 * 2;   // upper bound of blockIdx.x per launch (workspace sizing: [blk][C][T])
+bool conv_direct_wgrad_supported(int op, int B, int Cin, int H, int W, int Cout) {
+  (void)B; (void)H;
+  if (op == VC_OP_CONV_WGRAD) return Cin == 1 && Cout % 4 == 0 && Cout <= 512 && W % 8 == 0;
+  if (op == VC_OP_CONVT_WGRAD) return Cout == 1 && Cin % 4 == 0 && Cin <= 512 && W % 4 == 0;
+  return false;
+}
+size_t conv_direct_wgrad_workspace(int op, int Cin, int Cout) {
+  const int C = op == VC_OP_CONV_WGRAD ? Cout : Cin, T = op == VC_OP_CONV_WGRAD ? 9 : 16;
+  return sizeof(double) * (size_t)kTapBlocks * C * T;
+}
+int conv_direct_wgrad_run(int op, const float* dy, const float* x, float* dw, int B, int Cin, int H, int W, int Cout,
+                          int round_bf16, void* ws, size_t wsb, cudaStream_t s) {
+  VC_REQUIRE(ws && wsb >= conv_direct_wgrad_workspace(op, Cin, Cout), VC_ERR_WORKSPACE,
+             "conv_direct_wgrad_run: workspace too small");
+  double* part = static_cast<double*>(ws);
+  int nblk = 2 * sm_count();   // two 256-thread blocks per SM, every block walks all channels of its blockIdx.y
+  if (nblk > kTapBlocks) nblk = kTapBlocks;
+  if (op == VC_OP_CONV_WGRAD) {   // A = dy [B,Cout,OH,OW], S = x [B,1,H,W]
+    constexpr int CG = 4, T = 9;
+    const int OH = (H - 1) / 2 + 1, OW = W / 2, groups = Cout / CG;
+    const int64_t quads = (int64_t)B * OH * (OW / 4);
+    if ((int64_t)nblk * 32 > quads) nblk = (int)((quads + 31) / 32);
+    tap_wgrad_kernel<3, CG><<<dim3(nblk, (groups + 7) / 8), 256, 0, s>>>(dy, x, part, B, Cout, OH, OW, H, W, round_bf16);
+    VC_LAUNCH_CHECK();
+    tap_wgrad_fold_kernel<<<(Cout * T + 127) / 128, 128, 0, s>>>(part, nblk, Cout * T, dw);
+  } else {                        // A = x [B,Cin,H,W], S = dy [B,1,2H,2W]
+    constexpr int CG = 4, T = 16;
+    const int groups = Cin / CG;
+    const int64_t quads = (int64_t)B * H * (W / 4);
+    if ((int64_t)nblk * 32 > quads) nblk = (int)((quads + 31) / 32);
+    tap_wgrad_kernel<4, CG><<<dim3(nblk, (groups + 7) / 8), 256, 0, s>>>(x, dy, part, B, Cin, H, W, 2 * H, 2 * W,
+                                                                          round_bf16);
+    VC_LAUNCH_CHECK();
+    tap_wgrad_fold_kernel<<<(Cin * T + 127) / 128, 128, 0, s>>>(part, nblk, Cin * T, dw);
+  }
+  VC_LAUNCH_CHECK();
+  return VC_OK;
 }
 
 static int direct_grid(int64_t total) {
@@ -208,9 +448,16 @@ int conv_direct_run(int op, const float* in0, const float* in1, const float* bia
     else
       conv1ch_fwd_kernel<16><<<grid, 256, smem, s>>>(in0, in1, bias, out, B, H, W, Cout, OH, OW, relu, round_bf16);
   } else if (op == VC_OP_CONVT_FWD) {
-    const int grid = direct_grid((int64_t)B * ((H + 1) / 2) * W);
-    convT_to1_fwd_kernel<<<grid, 256, (size_t)Cin * 16 * sizeof(float), s>>>(in0, in1, bias, out, B, Cin, H, W, relu,
-                                                                               round_bf16);
+    const bool quad = (W % 4) == 0 && ((reinterpret_cast<uintptr_t>(in0) | reinterpret_cast<uintptr_t>(out)) & 15) == 0;
+    if (quad) {
+      const int grid = direct_grid((int64_t)B * ((H + 1) / 2) * (W / 4));
+      convT_to1_fwd_quad_kernel<<<grid, 256, (size_t)Cin * 16 * sizeof(float), s>>>(in0, in1, bias, out, B, Cin, H, W,
+                                                                                      relu, round_bf16);
+    } else {
+      const int grid = direct_grid((int64_t)B * ((H + 1) / 2) * W);
+      convT_to1_fwd_kernel<<<grid, 256, (size_t)Cin * 16 * sizeof(float), s>>>(in0, in1, bias, out, B, Cin, H, W, relu,
+                                                                                 round_bf16);
+    }
   } else if (op == VC_OP_CONVT_DGRAD) {
     const int grid = direct_grid((int64_t)B * H * W);
     convT_to1_dgrad_kernel<<<grid, 256, (size_t)Cin * 16 * sizeof(float), s>>>(in0, in1, out, B, Cin, H, W, round_bf16);

@@ -93,39 +93,69 @@ __global__ void bias_grad_cols_stage1(const float* __restrict__ dy, int64_t oute
 }
 
 // ReLU backward and bias gradient in ONE pass: g = dy * (y > 0) is written and summed per channel while it is in
-// registers.  Block (c, sp) owns whole (o, c) planes o = sp, sp+S, ...; the plane is contiguous, so the loop is plain
-// float4 streaming with no index arithmetic.  Partials land in the layout bias_grad_stage2 folds.
-__global__ void __launch_bounds__(256)
-relu_bwd_bias_stage1(const float* __restrict__ dy, const float* __restrict__ y, float* __restrict__ g, int64_t outer,
-                     int C, int64_t inner, int S, double* __restrict__ part) {
-  __shared__ double scratch[32];
-  const int c = blockIdx.x, sp = blockIdx.y;
+// registers.  Channel c's elements, flattened over (o, i), are cut into S equal slices and block (c, sp) streams slice
+// sp; the host sizes S so that C*S blocks are exactly the blocks the GPU holds at once (one balanced wave: no tail of
+// half-empty SMs, which cost the plane-per-block version 13 % at 2048 or 4096 equal blocks on 1184 slots).  Inside a
+// slice the loop walks plane by plane, so there is no division per element.  Partials land in the layout
+// bias_grad_stage2 folds.
+template <typename V>   // float4 (inner % 4 == 0, 16-byte aligned) or float
+__device__ __forceinline__ double relu_bwd_slice(const float* __restrict__ dy, const float* __restrict__ y,
+                                                 float* __restrict__ g, int64_t outer, int C, int64_t inner, int S,
+                                                 int c, int sp) {
+  constexpr int W = sizeof(V) / 4;
+  const int64_t iw = inner / W, total = outer * iw;
+  const int64_t len = (total + S - 1) / S;
+  const int64_t lo = (int64_t)sp * len, hi = lo + len < total ? lo + len : total;
   double acc = 0.0;
-  const bool vec = (inner % 4 == 0) && (((reinterpret_cast<uintptr_t>(dy) | reinterpret_cast<uintptr_t>(y) |
-                                          reinterpret_cast<uintptr_t>(g)) & 15) == 0);
-  for (int64_t o = sp; o < outer; o += S) {
+  for (int64_t o = lo / iw; o * iw < hi; ++o) {
+    const int64_t first = o * iw;
+    const int64_t s0 = (lo > first ? lo : first) - first, s1 = (hi < first + iw ? hi : first + iw) - first;
     const int64_t base = (o * C + c) * inner;
+    const V* dv = reinterpret_cast<const V*>(dy + base);
+    const V* yv = reinterpret_cast<const V*>(y + base);
+    V* gv = reinterpret_cast<V*>(g + base);
     float a = 0.f;
-    if (vec) {
-      const float4* d4 = reinterpret_cast<const float4*>(dy + base);
-      const float4* y4 = reinterpret_cast<const float4*>(y + base);
-      float4* g4 = reinterpret_cast<float4*>(g + base);
-      for (int64_t i = threadIdx.x; i < inner / 4; i += blockDim.x) {
-        const float4 d = d4[i], v = y4[i];
-        const float4 r = make_float4(v.x > 0.f ? d.x : 0.f, v.y > 0.f ? d.y : 0.f, v.z > 0.f ? d.z : 0.f,
-                                     v.w > 0.f ? d.w : 0.f);
-        g4[i] = r;
-        a += (r.x + r.y) + (r.z + r.w);
+    if constexpr (W == 4) {
+      int64_t i = s0 + threadIdx.x;
+      for (; i + blockDim.x < s1; i += 2 * blockDim.x) {   // two independent 16-byte load pairs in flight per thread
+        const float4 d0 = __ldcs(dv + i), v0 = __ldcs(yv + i);
+        const float4 d1 = __ldcs(dv + i + blockDim.x), v1 = __ldcs(yv + i + blockDim.x);
+        const float4 r0 = make_float4(v0.x > 0.f ? d0.x : 0.f, v0.y > 0.f ? d0.y : 0.f, v0.z > 0.f ? d0.z : 0.f,
+                                      v0.w > 0.f ? d0.w : 0.f);
+        const float4 r1 = make_float4(v1.x > 0.f ? d1.x : 0.f, v1.y > 0.f ? d1.y : 0.f, v1.z > 0.f ? d1.z : 0.f,
+                                      v1.w > 0.f ? d1.w : 0.f);
+        gv[i] = r0;
+        gv[i + blockDim.x] = r1;
+        a += ((r0.x + r0.y) + (r0.z + r0.w)) + ((r1.x + r1.y) + (r1.z + r1.w));
+      }
+      if (i < s1) {
+        const float4 d0 = __ldcs(dv + i), v0 = __ldcs(yv + i);
+        const float4 r0 = make_float4(v0.x > 0.f ? d0.x : 0.f, v0.y > 0.f ? d0.y : 0.f, v0.z > 0.f ? d0.z : 0.f,
+                                      v0.w > 0.f ? d0.w : 0.f);
+        gv[i] = r0;
+        a += (r0.x + r0.y) + (r0.z + r0.w);
       }
     } else {
-      for (int64_t i = threadIdx.x; i < inner; i += blockDim.x) {
-        const float r = y[base + i] > 0.f ? dy[base + i] : 0.f;
-        g[base + i] = r;
+      for (int64_t i = s0 + threadIdx.x; i < s1; i += blockDim.x) {
+        const float r = yv[i] > 0.f ? dv[i] : 0.f;
+        gv[i] = r;
         a += r;
       }
     }
     acc += (double)a;
   }
+  return acc;
+}
+
+__global__ void __launch_bounds__(256)
+relu_bwd_bias_stage1(const float* __restrict__ dy, const float* __restrict__ y, float* __restrict__ g, int64_t outer,
+                     int C, int64_t inner, int S, double* __restrict__ part) {
+  __shared__ double scratch[32];
+  const int c = blockIdx.x, sp = blockIdx.y;
+  const bool vec = (inner % 4 == 0) && (((reinterpret_cast<uintptr_t>(dy) | reinterpret_cast<uintptr_t>(y) |
+                                          reinterpret_cast<uintptr_t>(g)) & 15) == 0);
+  double acc = vec ? relu_bwd_slice<float4>(dy, y, g, outer, C, inner, S, c, sp)
+                   : relu_bwd_slice<float>(dy, y, g, outer, C, inner, S, c, sp);
   acc = block_sum<double>(acc, scratch);
   if (threadIdx.x == 0) part[(int64_t)c * S + sp] = acc;
 }
@@ -141,6 +171,35 @@ __global__ void relu_bwd_bias_cols_stage1(const float* __restrict__ dy, const fl
     acc += (double)r;
   }
   part[(int64_t)c * S + sp] = acc;
+}
+
+// inner == 1, C % 4 == 0, 16-byte aligned: thread = four columns as one float4, rows sp, sp+S, ... (four row steps in
+// flight); partials in [S][C] order so that the four doubles a thread writes are contiguous.  The scalar kernel above
+// had one row split (S = 1) at C = 262144, i.e. 64 dependent 4-byte steps per thread: 2.6 TB/s.
+__global__ void __launch_bounds__(256)
+relu_bwd_bias_cols4_stage1(const float4* __restrict__ dy, const float4* __restrict__ y, float4* __restrict__ g,
+                           int64_t outer, int C4, int S, double* __restrict__ part) {
+  const int c4 = blockIdx.x * blockDim.x + threadIdx.x, sp = blockIdx.y;
+  if (c4 >= C4) return;
+  double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
+#pragma unroll 4
+  for (int64_t o = sp; o < outer; o += S) {
+    const float4 d = __ldcs(dy + o * C4 + c4), v = __ldcs(y + o * C4 + c4);
+    const float4 r = make_float4(v.x > 0.f ? d.x : 0.f, v.y > 0.f ? d.y : 0.f, v.z > 0.f ? d.z : 0.f,
+                                 v.w > 0.f ? d.w : 0.f);
+    g[o * C4 + c4] = r;
+    a0 += (double)r.x; a1 += (double)r.y; a2 += (double)r.z; a3 += (double)r.w;
+  }
+  double* p = part + ((int64_t)sp * C4 + c4) * 4;
+  reinterpret_cast<double2*>(p)[0] = make_double2(a0, a1);
+  reinterpret_cast<double2*>(p)[1] = make_double2(a2, a3);
+}
+__global__ void bias_grad_stage2_rows(const double* __restrict__ part, int C, int S, float* __restrict__ db) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  double acc = 0.0;
+  for (int s = 0; s < S; ++s) acc += part[(int64_t)s * C + c];
+  db[c] = (float)acc;
 }
 
 __global__ void bias_grad_stage2(const double* __restrict__ part, int C, int S, float* __restrict__ db, int accumulate) {
@@ -342,11 +401,35 @@ extern "C" int vc_relu_bwd_bias(const float* dy, const float* y, int64_t outer, 
              "vc_relu_bwd_bias: workspace too small");
   int S = kBiasSplits;
   double* part = static_cast<double*>(workspace);
-  if (inner == 1) {
+  if (inner == 1 && C % 4 == 0 && C >= 4096 &&
+      ((reinterpret_cast<uintptr_t>(dy) | reinterpret_cast<uintptr_t>(y) | reinterpret_cast<uintptr_t>(g)) & 15) == 0) {
+    const int C4 = C / 4;
+    S = 1;   // enough row splits for ~2 threads per resident-thread slot, at least 8 rows each
+    while (S < kBiasSplits && (int64_t)C4 * S < 2 * 2048 * (int64_t)sm_count() && outer / (2 * S) >= 8) S <<= 1;
+    relu_bwd_bias_cols4_stage1<<<dim3((C4 + 255) / 256, S), 256, 0, as_stream(stream)>>>(
+        reinterpret_cast<const float4*>(dy), reinterpret_cast<const float4*>(y), reinterpret_cast<float4*>(g), outer, C4,
+        S, part);
+    VC_LAUNCH_CHECK();
+    bias_grad_stage2_rows<<<(C + 127) / 128, 128, 0, as_stream(stream)>>>(part, C, S, db);
+    VC_LAUNCH_CHECK();
+    return VC_OK;
+  } else if (inner == 1) {
     while (S > 1 && (S > outer || (int64_t)C * S > 262144)) S >>= 1;
     relu_bwd_bias_cols_stage1<<<dim3((C + 127) / 128, S), 128, 0, as_stream(stream)>>>(dy, y, g, outer, C, S, part);
   } else {
-    while (S > 1 && S > outer) S >>= 1;
+    // one balanced wave: as many equal slices per channel as there are resident-block slots (never more than the
+    // workspace's kBiasSplits per channel, never slices shorter than ~one pass of the block)
+    static int slots = 0;
+    if (slots == 0) {
+      int per_sm = 0;
+      cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, relu_bwd_bias_stage1, 256, 0);
+      slots = (per_sm > 0 ? per_sm : 1) * sm_count();
+    }
+    S = slots / C;
+    if (S > kBiasSplits) S = kBiasSplits;
+    const int64_t units = outer * (inner % 4 == 0 ? inner / 4 : inner);
+    while (S > 1 && units / S < 256) --S;
+    if (S < 1) S = 1;
     relu_bwd_bias_stage1<<<dim3(C, S), 256, 0, as_stream(stream)>>>(dy, y, g, outer, C, inner, S, part);
   }
   VC_LAUNCH_CHECK();

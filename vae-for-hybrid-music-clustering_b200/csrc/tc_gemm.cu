@@ -270,6 +270,10 @@ int conv_igemm_run(int op, const float* in0, const float* in1, const float* bias
 bool conv_direct_supported(int op, int B, int Cin, int H, int W, int Cout);   // conv_direct.cu
 int conv_direct_run(int op, const float* in0, const float* in1, const float* bias, float* out, int B, int Cin, int H,
                     int W, int Cout, int relu, int round_bf16, cudaStream_t s);
+bool conv_direct_wgrad_supported(int op, int B, int Cin, int H, int W, int Cout);
+size_t conv_direct_wgrad_workspace(int op, int Cin, int Cout);
+int conv_direct_wgrad_run(int op, const float* dy, const float* x, float* dw, int B, int Cin, int H, int W, int Cout,
+                          int round_bf16, void* ws, size_t wsb, cudaStream_t s);
 bool skinny_gemm_supported(int op, int B, int Cin, int Cout, const void* in0, const void* in1);   // skinny_gemm.cu
 size_t skinny_gemm_workspace(int op, int B, int Cin, int Cout);
 int skinny_gemm_run(int op, const float* in0, const float* in1, const float* bias, float* out, int B, int Cin, int Cout,
@@ -309,6 +313,14 @@ OpDims op_dims(int op, int B, int Cin, int H, int W, int Cout) {
 extern "C" size_t vc_dense_op_workspace_bytes(int op, int precision, int B, int Cin, int H, int W, int Cout) {
   if (precision == VC_PREC_BF16_TC) {
     if (conv_igemm_supported(op, B, Cin, H, W, Cout)) return conv_igemm_workspace(op, B, Cin, H, W, Cout);
+    if (conv_direct_wgrad_supported(op, B, Cin, H, W, Cout)) {   // a misaligned pointer falls back to the GEMM below
+      const size_t a = conv_direct_wgrad_workspace(op, Cin, Cout);
+      const size_t b = conv_wgrad_igemm_supported(op, B, Cin, H, W, Cout)
+                           ? conv_wgrad_igemm_workspace(op, B, Cin, H, W, Cout)
+                           : tc_gemm_workspace(op_dims(op, B, Cin, H, W, Cout).M, op_dims(op, B, Cin, H, W, Cout).N,
+                                               op_dims(op, B, Cin, H, W, Cout).K);
+      return a > b ? a : b;
+    }
     if (conv_wgrad_igemm_supported(op, B, Cin, H, W, Cout)) return conv_wgrad_igemm_workspace(op, B, Cin, H, W, Cout);
     const OpDims g = op_dims(op, B, Cin, H, W, Cout);
     const size_t a = tc_gemm_workspace(g.M, g.N, g.K), b = skinny_gemm_workspace(op, B, Cin, Cout);
@@ -390,6 +402,11 @@ extern "C" int vc_dense_op(int op, int precision, const float* in0, const float*
                "vc_dense_op: tensor too large for 32-bit pixel index");
     if (conv_direct_supported(op, B, Cin, H, W, Cout))  // single-channel ends: streaming FFMA kernels
       return conv_direct_run(op, in0, in1, bias, out, B, Cin, H, W, Cout, relu, 1, as_stream(stream));
+    if (conv_direct_wgrad_supported(op, B, Cin, H, W, Cout) &&
+        ((reinterpret_cast<uintptr_t>(in0) | reinterpret_cast<uintptr_t>(in1)) & 15) == 0)  // streaming tap reduction
+      // FFMA on the fp32 values: a weight gradient gains nothing from rounding dy and x to bf16 first
+      return conv_direct_wgrad_run(op, in0, in1, out, B, Cin, H, W, Cout, 0, workspace, workspace_bytes,
+                                   as_stream(stream));
     if (conv_igemm_supported(op, B, Cin, H, W, Cout))  // implicit GEMM: no im2col matrix in HBM
       return conv_igemm_run(op, in0, in1, bias, out, B, Cin, H, W, Cout, relu, workspace, workspace_bytes,
                             as_stream(stream));
