@@ -248,6 +248,51 @@ def test_conv2d_s2k3_bf16(B, Cin, H, W, Cout, relu, bf16_mode):
     _check_bf16(lambda x, w, b: ops.conv2d_s2k3(x, w, b, relu), ref, x, w, b)
 
 
+@pytest.mark.parametrize("kind,B,Cin,H,W,Cout", [
+    ("conv", 2, 32, 16, 128, 64),     # Cp 64, N 288: two 144-column tiles, one k-block per CTA
+    ("conv", 8, 32, 64, 256, 64),     # 512 k-blocks: seven per CTA, the ring wraps
+    ("conv", 1, 64, 5, 128, 128),     # odd height (bottom row group off the image), Cp 128, three 192-column tiles
+    ("conv", 1, 64, 4, 256, 64),      # Cp 64 with 192-column tiles
+    ("conv", 1, 16, 2, 128, 128),     # Cp 128, a single 144-column tile
+    ("convT", 2, 64, 4, 64, 32),      # Cp 64, two 256-column tiles
+    ("convT", 8, 64, 32, 128, 32),    # seven k-blocks per CTA
+    ("convT", 1, 128, 3, 128, 64),    # Cp 128, four tiles
+    ("convT", 1, 64, 1, 64, 16)])     # one input row: both outer row groups off the image
+def test_wgrad_fast_producers_equal_general_kernel(kind, B, Cin, H, W, Cout, bf16_mode):
+    """Model-shaped weight gradients (64-pixel k-blocks inside one row, Cp in {64, 128}) take conv_wgrad_fast_kernel.
+    Operands that start 4 bytes off an 8-byte boundary take the general table-driven kernel: both sum the same bf16
+    products in fp32 (different split-K order only), so they agree to 1e-4 of the gradient's scale, and with float64
+    autograd on the bf16-rounded operands."""
+    from vaeclust import ops
+    if kind == "conv":
+        x, w = _rand(B, Cin, H, W, seed=1), _rand(Cout, Cin, 3, 3, seed=2, scale=(Cin * 9) ** -0.5)
+        ours = lambda x, w: ops.conv2d_s2k3(x, w, None, False)
+        ref = lambda x, w: F.conv2d(x, w, None, stride=2, padding=1)
+    else:
+        x, w = _rand(B, Cin, H, W, seed=1), _rand(Cin, Cout, 4, 4, seed=2, scale=(Cin * 4) ** -0.5)
+        ours = lambda x, w: ops.convT2d_s2k4(x, w, None, False)
+        ref = lambda x, w: F.conv_transpose2d(x, w, None, stride=2, padding=1)
+
+    def off4(t):   # same values, data pointer 4 bytes past a 16-byte boundary
+        store = torch.empty(t.numel() + 1, device=t.device)
+        v = store[1:].view_as(t)
+        v.copy_(t)
+        assert v.data_ptr() % 8 == 4
+        return v
+
+    wa = w.clone().requires_grad_(True)
+    ya = ours(x, wa)
+    g = torch.randn_like(ya)
+    ya.backward(g)
+    wb = w.clone().requires_grad_(True)
+    ours(off4(x), wb).backward(off4(g))
+    wr = _r(w).double().requires_grad_(True)
+    ref(_r(x).double(), wr).backward(_r(g).double())
+    scale = float(wr.grad.abs().max())
+    assert float((wa.grad - wb.grad).abs().max()) <= 1e-4 * scale
+    assert float((wa.grad.double() - wr.grad).abs().max()) <= 1e-4 * scale
+
+
 @pytest.mark.parametrize("B,Cin,H,W,Cout,relu", [(2, 128, 2, 3, 64, True), (3, 64, 4, 6, 32, True),
                                                  (2, 32, 8, 12, 1, False), (1, 5, 3, 81, 7, True),
                                                  (2, 32, 64, 160, 32, True),     # 160 row tiles: persistent loop

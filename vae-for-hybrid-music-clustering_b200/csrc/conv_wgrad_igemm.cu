@@ -347,7 +347,223 @@ __global__ void __launch_bounds__(WG_THREADS, 1) conv_wgrad_igemm_kernel(const W
   }
 }
 
+// ---- fast producers ------------------------------------------------------------------------------------------------
+// Same GEMM, same tiles, same MMA issuer, for the shapes of the model itself: GW % 64 == 0 (a 64-pixel k-block is one
+// run of a P row, so batch, row and the valid source rows are warp-uniform), SW == 2 GW, Cp == 8 NA, and a column tile
+// of BN = 8 NG T columns that holds whole row groups (cq, th).  All eight producer warps build the same k-block: warp w
+// owns A rows cp = w + 8r and row groups gi = w + 8g, so
+//   * a row's swizzle phase (row & 7) does not depend on r / g: every shared-memory store is base register + immediate;
+//   * a group's source offset and th class are per-warp constants held in registers (no table, no index arithmetic);
+//   * rows outside the image are read from the nearest valid row (no predicate on the wide loads) and the packed words
+//     are ANDed with a per-k-block mask; only the two scalar edge columns keep a (loop-invariant) predicate.
+// A k-block is loaded in two halves into two register buffers; the loads of the next half are in flight while the
+// current one is packed and stored.  About 5 instructions per tile row instead of ~35.
+template <int T, int NG, int NA>
+struct WgBuf { float a[NA]; float q[(NG / 2) * (T + 2)]; uint32_t mk[T == 4 ? 1 : 3]; };
+
+template <int T, int NG, int NA>
+__global__ void __launch_bounds__(WG_THREADS, 1) conv_wgrad_fast_kernel(const WgArgs a) {
+  constexpr int BN = 8 * NG * T;
+  constexpr int NC = T == 4 ? 1 : 3;   // th classes of a warp's groups: th(g) = (Gi0 + w + 8g) % T has period NC in g
+  constexpr int V = T + 2;             // source columns 2j-1 .. 2j+T of a pixel pair
+  constexpr int NGH = NG / 2, NAH = NA / 2;
+  constexpr uint32_t ST_BYTES = WG_A_BYTES + (uint32_t)BN * 128u;
+  constexpr uint32_t TMEM_COLS = BN <= 128 ? 128u : 256u;
+  static_assert(NG % 2 == 0 && NA % 2 == 0 && BN % 16 == 0 && BN <= 256, "tile shape");
+  extern __shared__ unsigned char smem_raw[];
+  unsigned char* smem = smem_raw + ((1024u - (tma::s32(smem_raw) & 1023u)) & 1023u);
+  const int S = a.stages;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + (size_t)S * ST_BYTES);
+  uint64_t* full = bars;            // S: 256 producer arrivals
+  uint64_t* empty = bars + S;       // S: tcgen05.commit
+  uint64_t* t_full = empty + S;     // 1
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(t_full + 1);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int z = blockIdx.x, nt = blockIdx.y;
+  const int kb0 = z * a.kbs, kb1 = min(a.nkb, kb0 + a.kbs);
+  const int nkb = max(kb1 - kb0, 0);
+  const int n_base = nt * BN;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < S; ++s) { tma::mbar_init(&full[s], 256); tma::mbar_init(&empty[s], 1); }
+    tma::mbar_init(t_full, 1);
+    tma::mbar_fence_init();
+  }
+  if (warp == 8) tc05::tmem_alloc(tmem_slot, TMEM_COLS);
+  // A rows >= Cp are never written by the producers: zero every stage once
+  for (uint32_t o = threadIdx.x * 16u; o < (uint32_t)S * ST_BYTES; o += WG_THREADS * 16u)
+    *reinterpret_cast<uint4*>(smem + o) = make_uint4(0u, 0u, 0u, 0u);
+  tma::fence_proxy_async();
+  tc05::fence_before();
+  __syncthreads();
+  tc05::fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp < 8) {
+    // ===================== producers =====================
+    const int w = warp;
+    const int G = a.GH * a.GW;
+    const int Gi0 = nt * (BN / T);   // first row group of this column tile
+    int off[NG];                     // source offset of group g relative to (channel 0, row 2i-1)
+#pragma unroll
+    for (int g = 0; g < NG; ++g) {
+      const int gi = Gi0 + w + 8 * g, cq = gi / T, th = gi - cq * T;
+      off[g] = (cq * a.SH + th) * a.SW;
+    }
+    int thc[NC];
+#pragma unroll
+    for (int c = 0; c < NC; ++c) thc[c] = (Gi0 + w + 8 * c) % T;
+    const uint32_t lane_x = (((uint32_t)lane >> 2) << 4) | ((uint32_t)(lane & 3) * 4u);
+    const uint32_t sA = (uint32_t)w * 128u + ((((uint32_t)w & 7u) << 4) ^ lane_x);   // row w + 8r: + r * 1024
+    uint32_t sB[T];                                                                 // row T(w + 8g) + tw: + g * 8T * 128
+#pragma unroll
+    for (int tw = 0; tw < T; ++tw) {
+      const uint32_t nl = (uint32_t)(T * w + tw);
+      sB[tw] = WG_A_BYTES + nl * 128u + (((nl & 7u) << 4) ^ lane_x);
+    }
+
+    // load cursor: k-block kb0 + c covers pixels (b, i, jb .. jb+63); this lane owns the pair jb + 2 lane, + 1
+    int b, i, jb;
+    {
+      const int64_t m = (int64_t)kb0 * 64;
+      b = (int)(m / G);
+      const int r = (int)(m - (int64_t)b * G);
+      i = r / a.GW;
+      jb = r - i * a.GW;
+    }
+    const float* pA = nullptr;
+    const float* qc[NC];
+    uint32_t mk[NC];
+    bool okl = false, okr = false;
+    auto state = [&]() {
+      const int j = jb + 2 * lane;
+      pA = a.P + (((int64_t)b * a.Cp + w) * G + i * a.GW + j);
+      const float* pQ = a.Q + (((int64_t)b * a.Cq * a.SH + (2 * i - 1)) * a.SW + 2 * j - 1);
+#pragma unroll
+      for (int c = 0; c < NC; ++c) {
+        const int row = 2 * i - 1 + thc[c];
+        const int rc = min(max(row, 0), a.SH - 1);
+        qc[c] = pQ + (rc - row) * a.SW;
+        mk[c] = rc == row ? 0xffffffffu : 0u;
+      }
+      okl = j > 0;
+      okr = j + 2 < a.GW;
+    };
+    auto advance = [&]() {
+      jb += 64;
+      if (jb >= a.GW) { jb = 0; if (++i >= a.GH) { i = 0; ++b; } }
+      state();
+    };
+
+    using Buf = WgBuf<T, NG, NA>;
+    auto load_half = [&](const int h, Buf& u) {
+#pragma unroll
+      for (int r = 0; r < NAH; ++r) {
+        const float2 t2 = __ldg(reinterpret_cast<const float2*>(pA + (int64_t)((h * NAH + r) * 8) * G));
+        u.a[2 * r] = t2.x; u.a[2 * r + 1] = t2.y;
+      }
+#pragma unroll
+      for (int gg = 0; gg < NGH; ++gg) {
+        const int g = h * NGH + gg;
+        const float* src = qc[g % NC] + off[g];          // column 2j-1 of the group's source row
+        float* o = u.q + gg * V;
+        o[0] = okl ? __ldg(src) : 0.f;
+        const float2 m0 = __ldg(reinterpret_cast<const float2*>(src + 1));
+        const float2 m1 = __ldg(reinterpret_cast<const float2*>(src + 3));
+        o[1] = m0.x; o[2] = m0.y; o[3] = m1.x; o[4] = m1.y;
+        if (T == 4) o[5] = okr ? __ldg(src + 5) : 0.f;
+      }
+#pragma unroll
+      for (int c = 0; c < NC; ++c) u.mk[c] = mk[c];
+    };
+    auto store_half = [&](const int h, const Buf& u, unsigned char* tile) {
+#pragma unroll
+      for (int r = 0; r < NAH; ++r)
+        *reinterpret_cast<uint32_t*>(tile + sA + (uint32_t)((h * NAH + r) * 1024)) = wg_pack(u.a[2 * r], u.a[2 * r + 1]);
+#pragma unroll
+      for (int gg = 0; gg < NGH; ++gg) {
+        const int g = h * NGH + gg;
+        const float* o = u.q + gg * V;
+        const uint32_t m = u.mk[g % NC];
+        unsigned char* dst = tile + (uint32_t)(g * 8 * T * 128);
+        // (pixel j, pixel j+1) of tap tw are source columns (2j-1+tw, 2j+1+tw) = o[tw], o[tw+2]
+#pragma unroll
+        for (int tw = 0; tw < T; ++tw)
+          *reinterpret_cast<uint32_t*>(dst + sB[tw]) = wg_pack(o[tw], o[tw + 2]) & m;
+      }
+    };
+
+    {
+      Buf u0, u1;
+      int s = 0;
+      uint32_t ph = 1;   // parity to wait for on empty[s]: first pass through the ring never blocks
+      if (nkb > 0) { state(); load_half(0, u0); }
+      for (int c = 0; c < nkb; ++c) {
+        load_half(1, u1);
+        unsigned char* tile = smem + (size_t)s * ST_BYTES;
+        tma::mbar_wait(&empty[s], ph);
+        store_half(0, u0, tile);
+        if (c + 1 < nkb) { advance(); load_half(0, u0); }
+        store_half(1, u1, tile);
+        tma::fence_proxy_async();
+        tma::mbar_arrive(&full[s]);
+        if (++s == S) { s = 0; ph ^= 1u; }
+      }
+    }
+    // ===================== epilogue: partial tile -> workspace =====================
+    const int q = warp & 3, hh = warp >> 2;
+    const int cp = q * 32 + lane;
+    constexpr int nchunks = (BN + 31) / 32;
+    if (nkb > 0) {
+      tma::mbar_wait(t_full, 0);
+      tc05::fence_after();
+    }
+    float* o = a.part + ((int64_t)z * a.Cp + cp) * a.N + n_base;
+    for (int cc = hh; cc < nchunks; cc += 2) {
+      float v[32];
+      if (nkb > 0) {
+        tc05::ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + cc * 32, v);
+        tc05::ld_wait();
+      } else {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) v[j] = 0.f;
+      }
+      if (cp < a.Cp) {
+#pragma unroll
+        for (int j = 0; j < 32; ++j)
+          if (cc * 32 + j < BN) o[cc * 32 + j] = v[j];
+      }
+    }
+  } else {
+    // ===================== MMA issuer =====================
+    if (lane == 0) {
+      for (int it = 0; it < nkb; ++it) {
+        const int s = it % S;
+        const uint32_t ph = (uint32_t)(it / S) & 1u;
+        tma::mbar_wait_backoff(&full[s], ph, 32);
+        tc05::fence_after();
+        const uint32_t sa = tma::s32(smem + (size_t)s * ST_BYTES), sb = sa + WG_A_BYTES;
+#pragma unroll
+        for (int kk = 0; kk < 4; ++kk)
+          tc05::mma_bf16(tmem_base, tc05::desc_k_sw128(sa + kk * 32), tc05::desc_k_sw128(sb + kk * 32), a.idesc,
+                         (uint32_t)((it | kk) != 0));
+        tc05::commit(&empty[s]);
+      }
+      if (nkb > 0) tc05::commit(t_full);
+    }
+  }
+
+  tc05::fence_before();
+  __syncthreads();
+  if (warp == 8) {
+    tc05::fence_after();
+    tc05::tmem_dealloc(tmem_base, TMEM_COLS);
+  }
+}
+
 __global__ void wgrad_fold_kernel(const float* __restrict__ part, int nsplit, int total, float* __restrict__ out) {
+
   const int e = blockIdx.x * blockDim.x + threadIdx.x;
   if (e >= total) return;
   float acc = 0.f;
@@ -356,9 +572,9 @@ __global__ void wgrad_fold_kernel(const float* __restrict__ part, int nsplit, in
 }
 
 // ---- host ---------------------------------------------------------------------------------------------------------
-struct WgPlan { int Cp, Cq, T, GH, GW, SH, SW, N, ntiles, BN, K, nkb, nsplit, kbs; bool ok; };
+struct WgPlan { int Cp, Cq, T, GH, GW, SH, SW, N, ntiles, BN, K, nkb, nsplit, kbs; bool ok, fast; };
 
-static WgPlan wg_plan(int op, int B, int Cin, int H, int W, int Cout) {
+static WgPlan wg_plan(int op, int B, int Cin, int H, int W, int Cout, bool allow_fast = true) {
   WgPlan p;
   memset(&p, 0, sizeof(p));
   if (op == VC_OP_CONV_WGRAD) {
@@ -371,6 +587,11 @@ static WgPlan wg_plan(int op, int B, int Cin, int H, int W, int Cout) {
   p.N = p.Cq * p.T * p.T;
   p.ntiles = (p.N + 255) / 256;
   p.BN = ((p.N + p.ntiles - 1) / p.ntiles + 31) / 32 * 32;
+  // fast producers (conv_wgrad_fast_kernel): k-blocks are runs of one P row, tiles of whole row groups
+  if (allow_fast && p.GW % 64 == 0 && p.SW == 2 * p.GW && (p.Cp == 64 || p.Cp == 128)) {
+    const int bn = p.T == 4 ? 256 : (p.N % 192 == 0 ? 192 : 144);
+    if (p.N % bn == 0) { p.fast = true; p.BN = bn; p.ntiles = p.N / bn; }
+  }
   // (T = 3 tiles that hold whole row groups would need BN % 96 == 0: measured slower -- unbalanced tiles -- so the
   // vector producers below are used for T = 4 only, where BN % 4 == 0 always holds)
   const int64_t K = (int64_t)B * p.GH * p.GW;
@@ -392,13 +613,19 @@ bool conv_wgrad_igemm_supported(int op, int B, int Cin, int H, int W, int Cout) 
 
 size_t conv_wgrad_igemm_workspace(int op, int B, int Cin, int H, int W, int Cout) {
   const WgPlan p = wg_plan(op, B, Cin, H, W, Cout);
-  return p.ok ? (size_t)p.nsplit * p.Cp * p.N * 4 + 1024 : 0;
+  if (!p.ok) return 0;
+  const WgPlan q = wg_plan(op, B, Cin, H, W, Cout, false);   // a misaligned operand falls back to the general kernel
+  const int ns = p.nsplit > q.nsplit ? p.nsplit : q.nsplit;
+  return (size_t)ns * p.Cp * p.N * 4 + 1024;
 }
 
 // in0 = dy, in1 = x (vc_dense_op convention for the weight-gradient ops)
 int conv_wgrad_igemm_run(int op, const float* dy, const float* x, float* dw, int B, int Cin, int H, int W, int Cout,
                          void* ws, size_t wsb, cudaStream_t s) {
-  const WgPlan p = wg_plan(op, B, Cin, H, W, Cout);
+  const float* P0 = op == VC_OP_CONV_WGRAD ? dy : x;
+  const float* Q0 = op == VC_OP_CONV_WGRAD ? x : dy;
+  const bool aligned8 = ((reinterpret_cast<uintptr_t>(P0) | reinterpret_cast<uintptr_t>(Q0)) & 7) == 0;
+  const WgPlan p = wg_plan(op, B, Cin, H, W, Cout, aligned8);
   VC_REQUIRE(p.ok, VC_ERR_UNSUPPORTED, "conv_wgrad_igemm: unsupported shape");
   VC_REQUIRE(ws && wsb >= conv_wgrad_igemm_workspace(op, B, Cin, H, W, Cout), VC_ERR_WORKSPACE,
              "conv_wgrad_igemm: workspace too small");
@@ -421,6 +648,20 @@ int conv_wgrad_igemm_run(int op, const float* dy, const float* x, float* dw, int
     a.gsize = gs;
   }
   a.idesc = tc05::idesc(tc05::kFmtBF16, 128, p.BN, 0, 0);
+  if (p.fast) {
+    void (*fk)(const WgArgs) = nullptr;
+    if (p.T == 4) fk = p.Cp == 64 ? conv_wgrad_fast_kernel<4, 8, 8> : conv_wgrad_fast_kernel<4, 8, 16>;
+    else if (p.BN == 192) fk = p.Cp == 64 ? conv_wgrad_fast_kernel<3, 8, 8> : conv_wgrad_fast_kernel<3, 8, 16>;
+    else fk = p.Cp == 64 ? conv_wgrad_fast_kernel<3, 6, 8> : conv_wgrad_fast_kernel<3, 6, 16>;
+    const size_t fsmem = (size_t)stages * st_bytes + (2 * stages + 1) * 8 + 16 + 1024;
+    VC_CUDA(cudaFuncSetAttribute(fk, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fsmem));
+    fk<<<dim3((unsigned)p.nsplit, (unsigned)p.ntiles), WG_THREADS, fsmem, s>>>(a);
+    VC_LAUNCH_CHECK();
+    const int tot = p.Cp * p.N;
+    wgrad_fold_kernel<<<(tot + 255) / 256, 256, 0, s>>>(a.part, p.nsplit, tot, dw);
+    VC_LAUNCH_CHECK();
+    return VC_OK;
+  }
   const size_t smem = (size_t)stages * st_bytes + (2 * stages + 1) * 8 + 16 + (size_t)p.BN * 16 + 1024;
   // vector producers: even widths (pixel pairs never straddle a row, 8-byte aligned sources), whole row groups per tile
   const bool vec = p.T == 4 && p.GW % 2 == 0 && p.SW % 2 == 0 && p.BN % p.T == 0 && p.N % p.T == 0 &&
