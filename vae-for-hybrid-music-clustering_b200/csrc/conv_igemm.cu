@@ -131,6 +131,40 @@ __device__ __forceinline__ void ig_gather(const IgArgs& a, const IgPixel& px, in
   }
 }
 
+// Table-driven variant of the C % 32 == 0 branch above: everything that depends only on (k-block, k half) -- tap
+// offsets and the element offset c0*plane + th*SW + tw -- is read from a shared-memory table built once per CTA, and
+// everything that depends only on the pixel (pixbase, hi0 = S*i + D0, wj0 = S*j + D0) is computed once per tile, so a
+// k-block costs one LDS, the bounds test and one 64-bit add before its 32 loads.
+struct IgPix { const float* base; int hi0, wj0; bool ok; };
+
+__device__ __forceinline__ IgPix ig_pix(const IgArgs& a, int m) {
+  const IgPixel p = ig_pixel(a, m);
+  IgPix q;
+  q.ok = p.ok;
+  q.hi0 = a.S * p.i + a.D0;
+  q.wj0 = a.S * p.j + a.D0;
+  q.base = a.src + ((int64_t)p.b * a.C * a.SH + q.hi0) * a.SW + q.wj0;
+  return q;
+}
+
+__device__ __forceinline__ void ig_gather_tab(const IgArgs& a, const IgPix& px, const int2 t, uint64_t step,
+                                              float (&v)[32]) {
+  const int th = t.y & 0xff, tw = (t.y >> 8) & 0xff;
+  const bool ok = px.ok && (t.y >> 16) != 0 && (unsigned)(px.hi0 + th) < (unsigned)a.SH &&
+                  (unsigned)(px.wj0 + tw) < (unsigned)a.SW;
+  if (ok) {
+    uint64_t addr = reinterpret_cast<uint64_t>(px.base + t.x);
+#pragma unroll
+    for (int j = 0; j < 32; ++j) {
+      asm("ld.global.nc.f32 %0, [%1];" : "=f"(v[j]) : "l"(addr));
+      addr += step;
+    }
+  } else {
+#pragma unroll
+    for (int j = 0; j < 32; ++j) v[j] = 0.f;
+  }
+}
+
 // pack 32 floats -> 4 x 16-byte chunks of row `row`, chunks [4*kq, 4*kq+4) of the swizzled K-major tile
 __device__ __forceinline__ void ig_store(unsigned char* tile, int row, int kq, const float (&v)[32]) {
 #pragma unroll
@@ -155,8 +189,18 @@ conv_igemm_kernel(const IgArgs a, const __grid_constant__ CUtensorMap mapW) {
   uint64_t* t_full = empty + S;      // 2: accumulator stage complete
   uint64_t* t_empty = t_full + 2;    // 2: accumulator stage drained by the 256 epilogue threads
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(t_empty + 2);
+  int2* ktab = reinterpret_cast<int2*>(tmem_slot + 2);   // [nkb][2]: {element offset, th | tw << 8 | valid << 16}
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (!kOneCh) {
+    const int ntaps = a.TH * a.TW, plane = a.SH * a.SW;
+    for (int e = threadIdx.x; e < 2 * a.nkb; e += IG_THREADS) {
+      const int k0 = e * 32;
+      const int tap = k0 / a.C, c0 = k0 - tap * a.C;
+      const int th = tap / a.TW, tw = tap - th * a.TW;
+      ktab[e] = make_int2(c0 * plane + th * a.SW + tw, th | (tw << 8) | ((tap < ntaps ? 1 : 0) << 16));
+    }
+  }
   const uint32_t tmem_cols = a.BN <= 32 ? 64u : (a.BN <= 64 ? 128u : (a.BN <= 128 ? 256u : 512u));  // 2 stages
 
   if (threadIdx.x == 0) {
@@ -176,10 +220,16 @@ conv_igemm_kernel(const IgArgs a, const __grid_constant__ CUtensorMap mapW) {
     // ===================== producers =====================
     const int row = threadIdx.x & 127, kq = threadIdx.x >> 7;
     const int total = my_tiles * a.nkb;
+    const uint64_t step = (uint64_t)a.SH * (uint64_t)a.SW * 4u;
     float nxt[32];
     IgPixel px = ig_pixel(a, (int)blockIdx.x * IG_BM + row);
-    if (total > 0) ig_gather<kOneCh>(a, px, kq * 32, nxt);
-    int t = 0, kb = 0;
+    IgPix pq = ig_pix(a, (int)blockIdx.x * IG_BM + row);
+    if (total > 0) {
+      if constexpr (kOneCh) ig_gather<true>(a, px, kq * 32, nxt);
+      else ig_gather_tab(a, pq, ktab[kq], step, nxt);
+    }
+    int t = 0, kb = 0, s = 0;
+    uint32_t ph = 1;   // parity to wait for on empty[s]
     for (int it = 0; it < total; ++it) {
       float cur[32];
 #pragma unroll
@@ -188,12 +238,15 @@ conv_igemm_kernel(const IgArgs a, const __grid_constant__ CUtensorMap mapW) {
       int kb2 = kb + 1, t2 = t;
       if (kb2 == a.nkb) { kb2 = 0; ++t2; }
       if (it + 1 < total) {
-        if (t2 != t) px = ig_pixel(a, ((int)blockIdx.x + t2 * (int)gridDim.x) * IG_BM + row);
-        ig_gather<kOneCh>(a, px, kb2 * 64 + kq * 32, nxt);
+        if (t2 != t) {
+          const int m = ((int)blockIdx.x + t2 * (int)gridDim.x) * IG_BM + row;
+          if constexpr (kOneCh) px = ig_pixel(a, m);
+          else pq = ig_pix(a, m);
+        }
+        if constexpr (kOneCh) ig_gather<true>(a, px, kb2 * 64 + kq * 32, nxt);
+        else ig_gather_tab(a, pq, ktab[2 * kb2 + kq], step, nxt);
       }
-      const int s = it % S;
-      const uint32_t ph = (uint32_t)(it / S) & 1u;
-      tma::mbar_wait(&empty[s], ph ^ 1u);
+      tma::mbar_wait(&empty[s], ph);
       unsigned char* tile = smem + (size_t)s * st_bytes;
       if (threadIdx.x == 0) {
         tma::mbar_expect_tx(&full[s], b_bytes);
@@ -203,6 +256,7 @@ conv_igemm_kernel(const IgArgs a, const __grid_constant__ CUtensorMap mapW) {
       tma::fence_proxy_async();
       tma::mbar_arrive(&full[s]);
       kb = kb2; t = t2;
+      if (++s == S) { s = 0; ph ^= 1u; }
     }
   } else if (warp == 8) {
     // ===================== MMA issuer =====================
@@ -398,7 +452,7 @@ int conv_igemm_run(int op, const float* in0, const float* in1, const float* bias
     int rc = tma::make_map(&mw, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, Wb, dims, str, box, CU_TENSOR_MAP_SWIZZLE_128B);
     if (rc != VC_OK) return rc;
   }
-  const size_t smem = (size_t)stages * st_bytes + (2 * stages + 4) * 8 + 16 + 1024;
+  const size_t smem = (size_t)stages * st_bytes + (2 * stages + 4) * 8 + 16 + (size_t)a.nkb * 16 + 1024;
   const int grid = a.tiles < sm_count() ? a.tiles : sm_count();
   if (p.C == 1) {
     VC_CUDA(cudaFuncSetAttribute(conv_igemm_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
