@@ -296,7 +296,7 @@ def roofline_from_summary(summ, steps, n_params, pk, ms_per_step):
     # DRAM bytes per launch of the headline family from the committed ncu capture (same command, --no-graph), next to
     # the algorithmic bytes per launch the `achieved` figure uses
     try:
-        tr = json.load(open(ROOT / "profiles" / "ncu_traffic_r1.json"))
+        tr = json.load(open(ROOT / "profiles" / "ncu_traffic_r1_final5.json"))
         if roof["kernel"] in tr:
             roof["traffic"] = tr[roof["kernel"]]["dram_bytes_per_launch"]
             roof["traffic_source"] = tr["_source"]
