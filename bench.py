@@ -496,7 +496,10 @@ def run_reference_arm(args, rank):
                                    f"{LYR}-d lyrics, z={ZDIM}, Adam lr 2e-3 (reference CPU path)"},
             "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
             "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-    print(json.dumps(line), flush=True)
+    print(json.dumps(line), file=_JSON_OUT or sys.stdout, flush=True)
+
+
+_JSON_OUT = None
 
 
 def main():
@@ -512,6 +515,12 @@ def main():
     ap.add_argument("--skip-cpu", action="store_true", help="do not time the CPU baseline")
     ap.add_argument("--no-graph", action="store_true", help="one GPU: run the step eagerly instead of replaying a CUDA graph")
     args = ap.parse_args()
+    # stdout carries exactly ONE JSON line: libraries that write to fd 1 (NCCL prints its version banner there when
+    # NCCL_DEBUG is set) are sent to stderr, and the line goes to the saved descriptor
+    sys.stdout.flush()
+    global _JSON_OUT
+    _JSON_OUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -583,7 +592,7 @@ def main():
                         "d2h_bytes_per_step": vae["d2h"], "ms_per_step": vae["ms_e2e"] / args.steps},
                 "gpu_launches": vae["launches"], "clocks": clk, "roofline": roof, "cpu_baseline": cpu,
                 "last_loss": vae["last_loss"], "extra_metrics": extra}
-        print(json.dumps(line), flush=True)
+        print(json.dumps(line), file=_JSON_OUT or sys.stdout, flush=True)
     if world > 1:
         td.barrier()
         td.destroy_process_group()

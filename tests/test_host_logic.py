@@ -115,3 +115,22 @@ def test_is_same_clustering():
     a = np.array([0, 0, 1, 2, 2])
     assert cluster._is_same_clustering(a, np.array([2, 2, 0, 1, 1]), 3)
     assert not cluster._is_same_clustering(a, np.array([2, 1, 0, 1, 1]), 3)
+
+
+def test_bench_reference_arm_prints_one_json_line():
+    """bench.py --impl reference: stdout is exactly one JSON line (library chatter on fd 1 goes to stderr) carrying
+    the reference-arm keys of the bench contract."""
+    import json
+    import subprocess
+    import sys
+    from pathlib import Path
+    root = Path(__file__).resolve().parents[1]
+    out = subprocess.run([sys.executable, str(root / "bench.py"), "--impl", "reference", "--steps", "1", "--warmup", "0"],
+                         capture_output=True, text=True, timeout=300, cwd=root)
+    assert out.returncode == 0, out.stderr[-500:]
+    lines = [l for l in out.stdout.splitlines() if l.strip()]
+    assert len(lines) == 1
+    d = json.loads(lines[0])
+    assert d["impl"] == "reference" and d["metric"] == "VAE train clips/s" and d["value"] > 0
+    assert d["cpu_baseline"]["kind"] in ("port", "reference") and d["cpu_baseline"]["cores"] >= 1
+    assert d["e2e"]["h2d_bytes_per_step"] == 0 and d["e2e"]["d2h_bytes_per_step"] == 0
