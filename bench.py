@@ -463,6 +463,9 @@ def cpu_vae_steps(batch: int, steps: int, warmup: int):
     + Adam (oracle/vae_ref.py, pinned against the reference classes by oracle/make_golden.py).  Returns clips/s."""
     import torch
     from oracle import vae_ref
+    if torch.get_num_threads() == 1 and len(os.sched_getaffinity(0)) > 1:
+        # torchrun exports OMP_NUM_THREADS=1 to its workers; the CPU arm uses all the host threads it can
+        torch.set_num_threads(len(os.sched_getaffinity(0)))
     torch.manual_seed(0)
     p = vae_ref.init_conv_vae_params((F_MEL, T_MEL), z_dim=ZDIM, lyr_dim=LYR, seed=42)
     opt = vae_ref.AdamRef(p, 2e-3)
