@@ -252,7 +252,6 @@ def bench_vae(args, rank, world, device, group):
     # stream (a graph replay cannot be bracketed per call); these durations feed `roofline`, shares are taken against
     # this pass's own step time.  Runs last: eager steps re-point the optimizer's chunk table away from the graph.
     eager = step.step if use_graph else step
-    eager.overlap = False   # per-kernel durations need serial launches: the early Adam updates go back into one launch
     resident_step(0, eager)
     prof = Profiler()
     L.profiler = prof
@@ -421,6 +420,61 @@ def bench_silhouette(rank, world, device, group):
                                                       "scaling": "strong"}, wall_s=time.time() - t0)
 
 
+# ------------------------------------------------------------------------------------- parity at bench sizes
+def vae_parity_at_bench_size(device, precision):
+    """One step of the product path next to the CPU oracle at the EXACT shapes the headline times (batch 64,
+    1x128x1024; plus T=646, the crop path), same state_dict, batch and eps: loss / per-parameter gradient / post-Adam
+    parameter agreement (oracle/parity.py states the tolerances).  The oracle here is the checker, never the thing
+    measured."""
+    import torch
+    from oracle import parity
+    from vaeclust import nn, ops as vops
+    from vaeclust.train import VAEStep
+    out = {}
+    for T in (T_MEL, 646):
+        vops.set_precision(precision)
+        torch.manual_seed(42)
+        model = nn.ConvMultiModalVAE(1, (F_MEL, T), ZDIM, LYR).to(device).train()
+        g = torch.Generator().manual_seed(9)
+        x = torch.randn(BATCH, 1, F_MEL, T, generator=g)
+        x = (x - x.mean(dim=(1, 2, 3), keepdim=True)) / x.std(dim=(1, 2, 3), keepdim=True)
+        lyr = torch.nn.functional.normalize(torch.randn(BATCH, LYR, generator=g), dim=1)
+        m = (torch.rand(BATCH, 1, generator=g) < 0.593).float()
+        batch = {k: v.to(device) for k, v in dict(x=x, lyr=lyr * m, m=m, eps=torch.randn(BATCH, ZDIM, generator=g)).items()}
+        r = parity.vae_step_parity(model, VAEStep(model, "conv12", lr=2e-3, beta=1.0), "conv", batch, 1.0, 2e-3,
+                                   "bf16" if precision == "bf16" else "fp32")
+        r.pop("grad_rel")
+        out[f"T{T}"] = r
+        del model, batch
+        torch.cuda.empty_cache()
+    out["ok"] = all(v["ok"] for v in out.values())
+    return out
+
+
+def cluster_parity_at_bench_size():
+    """KMeans.fit on a 4M x 32 sub-sample of the C4 workload vs scikit-learn (k=8: FFMA kernel, k=32: tcgen05 kernel):
+    bit-equal labels, equal n_iter_, inertia 1e-5; silhouette + Davies-Bouldin at 20k and 50k x 64 vs scikit-learn, 1e-5."""
+    import numpy as np
+    from oracle import parity
+    rng = np.random.default_rng(1)
+    n, d = 4_000_000, 32
+    cent = rng.normal(0, 3, size=(16, d)).astype(np.float32)
+    X = cent[rng.integers(0, 16, n)] + rng.standard_normal((n, d), dtype=np.float32)
+    perm = np.random.default_rng(2).permutation(n)
+    out = {"kmeans": {}, "silhouette": {}}
+    for k in (8, 32):
+        out["kmeans"][f"k{k}"] = parity.kmeans_fit_parity(X, X[perm[:k]].copy(), max_iter=15)
+    del X
+    rng = np.random.default_rng(3)
+    for n2 in (20_000, 50_000):
+        cent = rng.normal(0, 3, size=(8, 64)).astype(np.float32)
+        lab = rng.integers(0, 8, n2)
+        X2 = cent[lab] + rng.standard_normal((n2, 64), dtype=np.float32)
+        out["silhouette"][f"n{n2}"] = parity.silhouette_dbi_parity(X2, lab)
+    out["ok"] = all(v["ok"] for grp in ("kmeans", "silhouette") for v in out[grp].values())
+    return out
+
+
 # -------------------------------------------------------------------------- CPU baseline / reference arm
 def cpu_cluster_baselines():
     """The reference's clustering arithmetic IS scikit-learn (un-vendored dependency): time
@@ -559,6 +613,12 @@ def main():
         cpu = {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
                "sample": f"3 steps (+1 warm-up) of the full batch-{BATCH} step, torch-CPU fp32 restatement of the "
                          f"reference classes, {spstep:.2f} s/step"}
+    par = None
+    if rank == 0 and world == 1 and not args.skip_cpu:
+        par = {"vae_step": vae_parity_at_bench_size(device, args.precision)}
+        if extra:
+            par["clustering"] = cluster_parity_at_bench_size()
+        par["ok"] = all(v["ok"] for v in par.values())
     if rank == 0 and world == 1 and not args.skip_cpu and extra:
         try:
             cb = cpu_cluster_baselines()
@@ -594,8 +654,10 @@ def main():
                 "e2e": {"value": clips / (vae["ms_e2e"] * 1e-3), "unit": UNIT, "h2d_bytes_per_step": vae["h2d"],
                         "d2h_bytes_per_step": vae["d2h"], "ms_per_step": vae["ms_e2e"] / args.steps},
                 "gpu_launches": vae["launches"], "clocks": clk, "roofline": roof, "cpu_baseline": cpu,
-                "last_loss": vae["last_loss"], "extra_metrics": extra}
+                "last_loss": vae["last_loss"], "parity": par, "extra_metrics": extra}
         print(json.dumps(line), file=_JSON_OUT or sys.stdout, flush=True)
+        if par is not None and not par["ok"]:
+            raise SystemExit(f"bench.py: parity check against the oracle FAILED: {json.dumps(par)}")
     if world > 1:
         td.barrier()
         td.destroy_process_group()

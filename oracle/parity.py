@@ -1,0 +1,120 @@
+"""TEST INFRASTRUCTURE ONLY -- parity checkers that put ONE step of the CUDA path next to the CPU oracle on the same
+seeded inputs, at whatever size the caller runs (tests/, __graft_entry__.smoke() and the cpu_baseline leg of bench.py
+call these with the very shapes the benchmark times, so the tcgen05 instantiations of the headline meet the oracle).
+
+The oracle side is oracle/vae_ref.py (pinned against the reference classes, see its header) and scikit-learn itself
+for the clustering calls (the reference's clustering arithmetic IS scikit-learn).
+"""
+from __future__ import annotations
+
+import time
+from typing import Dict
+
+import numpy as np
+import torch
+
+from . import vae_ref
+
+# Stated tolerances of the bf16 tensor-core mode (operands rounded to 8 mantissa bits, fp32 accumulation), measured
+# on B200 at the benchmark shapes and rounded up with margin; fp32 mode must meet the north star's 1e-3 on the loss.
+TOL = {
+    "bf16": dict(loss_rel=5e-3, grad_rel=3e-2),
+    "fp32": dict(loss_rel=1e-3, grad_rel=2e-3),
+}
+
+
+def _rel(a: torch.Tensor, b: torch.Tensor) -> float:
+    """||a - b|| / ||b|| in float64."""
+    a, b = a.detach().double().cpu().reshape(-1), b.detach().double().cpu().reshape(-1)
+    den = float(b.norm())
+    return float((a - b).norm()) / den if den > 0 else float((a - b).norm())
+
+
+def vae_step_parity(model, step, kind: str, batch: Dict[str, torch.Tensor], beta: float, lr: float,
+                    precision: str) -> dict:
+    """Run ONE optimisation step of `step` (a vaeclust.train.VAEStep over `model`, first step of its optimizer) and of
+    the oracle from the same parameters, batch and eps.  kind: "conv" | "mlp19" | "mlp06"; batch holds CUDA tensors
+    x, eps and (conv) lyr, m or (mlp19) c.  Returns the comparison and whether it is within TOL[precision]."""
+    names = [n for n, _ in model.named_parameters()]
+    p_ref = {n: p.detach().cpu().clone() for n, p in model.named_parameters()}
+    b_cpu = {k: v.detach().cpu() for k, v in batch.items()}
+    if kind == "conv":
+        args = (batch["x"], batch["lyr"], batch["m"])
+    elif kind == "mlp19" and "c" in batch:
+        args = (batch["x"], batch["c"])
+    else:
+        args = (batch["x"],)
+    stats = step(*args, eps=batch["eps"]).detach().cpu().numpy()
+    torch.cuda.synchronize()
+    grads = {n: (p.grad.detach().clone() if p.grad is not None else None) for n, p in model.named_parameters()}
+    after = {n: p.detach().cpu().clone() for n, p in model.named_parameters()}
+    opt = vae_ref.AdamRef(p_ref, lr)
+    t0 = time.perf_counter()
+    ref = vae_ref.train_step(p_ref, opt, kind, b_cpu, beta)
+    dt = time.perf_counter() - t0
+    out = {"loss": float(stats[0]), "loss_ref": ref[0], "recon_ref": ref[1], "kl_ref": ref[2],
+           "loss_rel": abs(float(stats[0]) - ref[0]) / abs(ref[0]),
+           "recon_rel": abs(float(stats[1]) - ref[1]) / abs(ref[1]),
+           "kl_rel": abs(float(stats[2]) - ref[2]) / max(abs(ref[2]), 1e-12), "oracle_step_s": dt}
+    grad_rel, none_mismatch = {}, []
+    for n in names:
+        g_ref, g = opt.last_grads[n], grads[n]
+        if (g_ref is None) != (g is None):
+            none_mismatch.append(n)
+        elif g is not None:
+            grad_rel[n] = _rel(g, g_ref)
+    worst = max(grad_rel, key=grad_rel.get)
+    out["grad_rel_max"] = grad_rel[worst]
+    out["grad_rel_max_param"] = worst
+    out["grad_rel"] = {n: round(v, 6) for n, v in grad_rel.items()}
+    out["grad_none_mismatch"] = none_mismatch
+    # parameters after the first Adam step: |delta| = lr wherever |g| >> eps, so a sign flip of a near-zero gradient
+    # element moves a parameter by 2 lr; reported relative to the parameter norm and to the update norm
+    out["param_rel_after_adam"] = max(_rel(after[n], p_ref[n]) for n in names)
+    tol = TOL[precision]
+    out["tolerance"] = dict(tol, precision=precision)
+    out["ok"] = bool(out["loss_rel"] <= tol["loss_rel"] and out["grad_rel_max"] <= tol["grad_rel"] and not none_mismatch)
+    return out
+
+
+def kmeans_fit_parity(X: np.ndarray, init: np.ndarray, max_iter: int = 300, tol: float = 1e-4) -> dict:
+    """vaeclust.cluster.KMeans(init=array, n_init=1).fit(X) against sklearn.cluster.KMeans on the same array:
+    labels bit-equal, n_iter_ equal, inertia within 1e-5 relative.  Returns the comparison and both wall times."""
+    from sklearn.cluster import KMeans as SkKMeans
+    from vaeclust import cluster
+    k = init.shape[0]
+    t0 = time.perf_counter()
+    ours = cluster.KMeans(k, init=init, n_init=1, max_iter=max_iter, tol=tol).fit(X)
+    torch.cuda.synchronize()
+    t_ours = time.perf_counter() - t0
+    t0 = time.perf_counter()
+    ref = SkKMeans(k, init=init, n_init=1, max_iter=max_iter, tol=tol).fit(X)
+    t_ref = time.perf_counter() - t0
+    mism = int((ours.labels_ != ref.labels_).sum())
+    out = {"n": int(X.shape[0]), "d": int(X.shape[1]), "k": int(k), "label_mismatches": mism,
+           "n_iter": int(ours.n_iter_), "n_iter_ref": int(ref.n_iter_),
+           "inertia_rel": abs(ours.inertia_ - ref.inertia_) / abs(ref.inertia_),
+           "centers_max_abs_diff": float(np.abs(ours.cluster_centers_ - ref.cluster_centers_).max()),
+           "fit_s": t_ours, "sklearn_fit_s": t_ref}
+    out["ok"] = bool(mism == 0 and out["n_iter"] == out["n_iter_ref"] and out["inertia_rel"] <= 1e-5)
+    return out
+
+
+def silhouette_dbi_parity(X: np.ndarray, labels: np.ndarray) -> dict:
+    """vaeclust silhouette_score / davies_bouldin_score against sklearn on the same array and labels (1e-5 relative)."""
+    from sklearn.metrics import davies_bouldin_score as sk_dbi
+    from sklearn.metrics import silhouette_score as sk_sil
+    from vaeclust import cluster
+    t0 = time.perf_counter()
+    s = cluster.silhouette_score(X, labels)
+    d = cluster.davies_bouldin_score(X, labels)
+    t_ours = time.perf_counter() - t0
+    t0 = time.perf_counter()
+    s_ref = float(sk_sil(X, labels))
+    t_sil = time.perf_counter() - t0
+    d_ref = float(sk_dbi(X, labels))
+    out = {"n": int(X.shape[0]), "d": int(X.shape[1]), "k": int(len(np.unique(labels))), "silhouette": s,
+           "silhouette_ref": s_ref, "silhouette_rel": abs(s - s_ref) / abs(s_ref), "dbi": d, "dbi_ref": d_ref,
+           "dbi_rel": abs(d - d_ref) / abs(d_ref), "ours_s": t_ours, "sklearn_silhouette_s": t_sil}
+    out["ok"] = bool(out["silhouette_rel"] <= 1e-5 and out["dbi_rel"] <= 1e-5)
+    return out

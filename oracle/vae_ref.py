@@ -209,3 +209,57 @@ def train_step(p: Dict[str, Tensor], opt: AdamRef, kind: str, batch: dict, beta:
     opt.last_grads = grads
     opt.step(grads)
     return float(loss.detach()), float(rec.detach()), float(kl.detach())
+
+
+# --------------------------------------------------------------------------- loops
+def train_loop(p: Dict[str, Tensor], kind: str, arrays, epochs: int, batch_size: int, lr: float, beta: float,
+               eps_fn, seed: int):
+    """The reference's epoch loop on CPU with the reference's own batch order: a real
+    DataLoader(shuffle=True, drop_last=False, num_workers=0) over the sample indices under
+    torch.manual_seed(seed) (12:226-227,246-276; 19:191-192,209-242; 06:300-339).
+    arrays: (X, lyr, m) for kind "conv"; (X,) or (X, c) for "mlp19"; (X,) for "mlp06".
+    eps_fn(epoch, step, rows) -> [rows, z] noise of that batch (stands in for randn_like).
+    Epoch value = unweighted mean of batch values for conv / mlp06 (12:274-276, 06:330-331),
+    sample-weighted mean for mlp19 (19:234-242).  Returns {"loss": [...], "recon": [...], "kl": [...]}."""
+    from torch.utils.data import DataLoader
+    if seed is not None:   # None: continue from the caller's generator state (model construction came first)
+        torch.manual_seed(seed)
+    opt = AdamRef(p, lr)
+    arrays = [torch.as_tensor(a) for a in arrays]
+    n = arrays[0].shape[0]
+    dl = DataLoader(torch.arange(n), batch_size=batch_size, shuffle=True, drop_last=False, num_workers=0)
+    log = {"loss": [], "recon": [], "kl": []}
+    for epoch in range(1, epochs + 1):
+        tot = [0.0, 0.0, 0.0]
+        den = 0.0
+        for s_i, idx in enumerate(dl):
+            bs = idx.numel()
+            b = {"x": arrays[0][idx], "eps": eps_fn(epoch, s_i, bs)}
+            if kind == "conv":
+                b["lyr"], b["m"] = arrays[1][idx], arrays[2][idx]
+            elif kind == "mlp19" and len(arrays) > 1:
+                b["c"] = arrays[1][idx]
+            vals = train_step(p, opt, kind, b, beta)
+            w = float(bs) if kind == "mlp19" else 1.0
+            for j in range(3):
+                tot[j] += vals[j] * w
+            den += w
+        for j, k in enumerate(("loss", "recon", "kl")):
+            log[k].append(tot[j] / max(den, 1.0))
+    return log
+
+
+@torch.no_grad()
+def encode_mu(p: Dict[str, Tensor], kind: str, arrays) -> Tensor:
+    """Latent export: mu of every sample in the original order (12:289-309, 19:269-287, 06:354-358)."""
+    arrays = [torch.as_tensor(a) for a in arrays]
+    x = arrays[0]
+    z_dim = p["mu.weight"].shape[0]
+    eps = torch.zeros(x.shape[0], z_dim)
+    if kind == "conv":
+        _, mu, _ = conv_vae_forward(p, x, arrays[1], arrays[2], eps)
+    elif kind == "mlp19":
+        _, mu, _ = mlp_vae_forward(p, x, eps, arrays[1] if len(arrays) > 1 else None, "19")
+    else:
+        _, mu, _ = mlp_vae_forward(p, x, eps, None, "06")
+    return mu

@@ -361,11 +361,8 @@ __global__ void __launch_bounds__(WG_THREADS, 1) conv_wgrad_igemm_kernel(const W
 template <int T, int NG, int NA>
 struct WgBuf { float a[NA]; float q[(NG / 2) * (T + 2)]; uint32_t mk[T == 4 ? 1 : 3]; };
 
-#ifndef VC_WG_OCC
-#define VC_WG_OCC 1   // resident CTAs per SM of the fast kernel (2: <= 112 registers, half the ring, twice the split-K)
-#endif
 template <int T, int NG, int NA>
-__global__ void __launch_bounds__(WG_THREADS, VC_WG_OCC) conv_wgrad_fast_kernel(const WgArgs a) {
+__global__ void __launch_bounds__(WG_THREADS, 1) conv_wgrad_fast_kernel(const WgArgs a) {
   constexpr int BN = 8 * NG * T;
   constexpr int NC = T == 4 ? 1 : 3;   // th classes of a warp's groups: th(g) = (Gi0 + w + 8g) % T has period NC in g
   constexpr int V = T + 2;             // source columns 2j-1 .. 2j+T of a pixel pair
@@ -602,7 +599,7 @@ static WgPlan wg_plan(int op, int B, int Cin, int H, int W, int Cout, bool allow
   if (!p.ok) return p;
   p.K = (int)K;
   p.nkb = (p.K + 63) / 64;
-  int ns = sm_count() * (p.fast ? VC_WG_OCC : 1) / p.ntiles;
+  int ns = sm_count() / p.ntiles;
   if (ns < 1) ns = 1;
   if (ns > p.nkb) ns = p.nkb;
   p.kbs = (p.nkb + ns - 1) / ns;
@@ -640,7 +637,7 @@ int conv_wgrad_igemm_run(int op, const float* dy, const float* x, float* dw, int
   a.B = B; a.Cp = p.Cp; a.GH = p.GH; a.GW = p.GW; a.Cq = p.Cq; a.SH = p.SH; a.SW = p.SW;
   a.T = p.T; a.taps = p.T * p.T; a.N = p.N; a.BN = p.BN; a.K = p.K; a.nkb = p.nkb; a.kbs = p.kbs;
   const size_t st_bytes = WG_A_BYTES + (size_t)p.BN * 128;
-  int stages = (int)((p.fast && VC_WG_OCC > 1 ? (212 * 1024) / VC_WG_OCC : 200 * 1024) / st_bytes);
+  int stages = (int)((200 * 1024) / st_bytes);
   if (stages > 10) stages = 10;
   if (stages < 2) stages = 2;
   a.stages = stages;

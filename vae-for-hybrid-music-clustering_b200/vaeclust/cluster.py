@@ -323,7 +323,8 @@ class KMeans:
             elif init == "random":
                 if multi:
                     raise VaeclustError("init='random' over a sharded X is not implemented: pass init=<array>")
-                seeds = rs.choice(N, size=k, replace=False)
+                # sklearn passes p=sample_weight/sum (a different numpy algorithm than p=None): same call here
+                seeds = rs.choice(N, size=k, replace=False, p=np.ones(N) / N)
                 c0 = Xc[torch.from_numpy(seeds).to(Xc.device)][:, :d_true]
             else:
                 raise ValueError(f"init should be 'k-means++', 'random' or an array, got {init!r}")
@@ -532,6 +533,8 @@ def safe_silhouette(X, labels):
             Xm = X[torch.from_numpy(mask).to(X.device)] if isinstance(X, torch.Tensor) else X[mask]
             return float(silhouette_score(Xm, labels[mask]))
         return float(silhouette_score(X, labels))
+    except VaeclustError:
+        raise   # a failed CUDA launch / missing library is not a "metric undefined" case
     except Exception:
         return None
 
@@ -550,6 +553,8 @@ def safe_db_index(X, labels):
             Xm = X[torch.from_numpy(mask).to(X.device)] if isinstance(X, torch.Tensor) else X[mask]
             return float(davies_bouldin_score(Xm, labels[mask]))
         return float(davies_bouldin_score(X, labels))
+    except VaeclustError:
+        raise
     except Exception:
         return None
 

@@ -178,14 +178,16 @@ class OverlappedGradSync:
             return
         live = [p for p in self.small if p.grad is not None]
         if live:
-            flat = torch.cat([p.grad.reshape(-1) for p in live])
+            n = sum(p.numel() for p in live)
+            if self._flat is None or self._flat.numel() != n or self._flat.device != live[0].device:
+                self._flat = torch.empty(n, dtype=torch.float32, device=live[0].device)
+            flat = torch.cat([p.grad.reshape(-1) for p in live], out=self._flat)   # packed into the cached buffer
             self._reduce(flat, False)
             o = 0
             for p in live:
                 n = p.numel()
                 p.grad = flat[o: o + n].view_as(p)
                 o += n
-            self._flat = flat
         for w in self.works:
             w.wait()
         self.works = []

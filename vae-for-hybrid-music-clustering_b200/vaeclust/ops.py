@@ -12,13 +12,18 @@ import torch
 from ._lib import VC_LOSS_MEAN_MEAN, VC_LOSS_SUM_MEAN, VaeclustError, lib, ptr, stream_ptr
 
 _ws_cache: dict = {}
+_ws_retired: list = []   # superseded buffers stay alive: a captured CUDA graph may have baked their address in
 
 
 def _workspace(nbytes: int, device) -> torch.Tensor:
-    """Grow-only per-device scratch buffer (the library never allocates)."""
+    """Grow-only per-device scratch buffer (the library never allocates).  A buffer that is outgrown is RETIRED, not
+    freed: GraphedVAEStep records the scratch address of its launches at capture time, so returning that memory to
+    the caching allocator would let a later replay scribble over somebody else's tensor."""
     key = (device.type, device.index)
     buf = _ws_cache.get(key)
     if buf is None or buf.numel() < nbytes:
+        if buf is not None:
+            _ws_retired.append(buf)
         buf = torch.empty(max(int(nbytes), 1 << 20), dtype=torch.uint8, device=device)
         _ws_cache[key] = buf
     return buf

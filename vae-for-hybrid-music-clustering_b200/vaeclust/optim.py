@@ -3,11 +3,15 @@
 One vc_adam_multi launch per step over a device-resident chunk table instead of torch's ~4 foreach kernels per
 state tensor.  Parameters whose .grad is None are skipped and their step counter does not advance (this is what
 keeps `audio_enc.logvar` of script 12 frozen).
+
+Sharded mode (`shard(rank, world)`, used by the data-parallel script-12 step): each rank keeps the
+Adam moments of, and updates, only its 1/world slice of every LARGE parameter; the gradient slice comes from a
+reduce-scatter and the updated slices are all-gathered by the caller (vaeclust.dist.ShardedGradSync).  Small
+parameters are updated in full on every rank from all-reduced gradients, which yields bit-identical replicas.
 """
 from __future__ import annotations
 
-import math
-from typing import Dict, Iterable, List
+from typing import Dict, Iterable, List, Optional
 
 import numpy as np
 import torch
@@ -30,17 +34,16 @@ class Adam:
                 raise VaeclustError("vaeclust.optim.Adam: parameters must be float32 CUDA tensors (no CPU path)")
         self.lr, self.betas, self.eps = float(lr), (float(betas[0]), float(betas[1])), float(eps)
         self.state: Dict[int, dict] = {}
-        self._tables: Dict[tuple, dict] = {}   # chunk tables on the device, one per launch group
+        self._table: Optional[dict] = None     # the chunk table on the device (key, dev, pinned)
+        self._retired: list = []               # superseded tables: a captured graph may still read them
+        self._spare: Optional[dict] = None     # pre-allocated (pinned, device) pair for the next table change
         # capturable (torch.optim.Adam(capturable=True)): step counter and bias corrections live on the device, so a
         # step recorded in a CUDA graph advances correctly on every replay (vc_adam_multi_graph)
         self.capturable = bool(capturable)
         self._dev_step = None
-        self._early: Dict[int, int] = {}       # id(param) -> slot of the parameters updated from a grad hook
-        self._early_stream = None
-        self._early_done = None                # ids updated early in the current step (None: not in overlap mode)
-        self._early_pending = False
-        self._ticked = False
-        self._hooks: list = []
+        # id(param) -> (lo, hi, grad_slice_fn): this rank owns elements [lo, hi) of the flattened parameter
+        self._shards: Dict[int, tuple] = {}
+        self.skip: set = set()                 # ids of parameters some fused kernel updates itself this step
         self.param_groups = [{"params": self.params, "lr": self.lr, "betas": self.betas, "eps": self.eps}]
 
     def zero_grad(self, set_to_none: bool = True) -> None:
@@ -53,132 +56,130 @@ class Adam:
                 p.grad.detach_()
                 p.grad.zero_()
 
+    def shard(self, p: torch.nn.Parameter, lo: int, hi: int, grad_slice) -> None:
+        """From now on update only elements [lo, hi) of `p` (flattened), reading their gradient from the 1-D fp32
+        tensor `grad_slice` (hi - lo elements; the output of a reduce-scatter).  Must be called before the first step
+        that touches `p`: the moments are allocated for the slice only."""
+        if id(p) in self.state:
+            raise VaeclustError("Adam.shard: parameter already has full-size optimizer state")
+        if grad_slice.numel() != hi - lo or grad_slice.dtype != torch.float32 or not grad_slice.is_contiguous():
+            raise VaeclustError("Adam.shard: grad_slice must be a contiguous float32 tensor of hi - lo elements")
+        self._shards[id(p)] = (int(lo), int(hi), grad_slice)
+
     def _state(self, p) -> dict:
         st = self.state.get(id(p))
         if st is None:
-            st = {"step": 0, "exp_avg": torch.zeros_like(p.data), "exp_avg_sq": torch.zeros_like(p.data)}
+            sh = self._shards.get(id(p))
+            n = p.numel() if sh is None else sh[1] - sh[0]
+            shape = p.shape if sh is None else (n,)
+            st = {"step": 0, "exp_avg": torch.zeros(shape, dtype=torch.float32, device=p.device),
+                  "exp_avg_sq": torch.zeros(shape, dtype=torch.float32, device=p.device)}
             self.state[id(p)] = st
         return st
 
-    # ------------------------------------------------------------------ overlap of large updates with backward
-    def overlap(self, params: Iterable[torch.nn.Parameter], stream: "torch.cuda.Stream | None" = None) -> None:
-        """Update `params` EARLY: a post-accumulate-grad hook launches the Adam update of each of them on `stream`
-        (a side stream) the moment backward has written its gradient, so the 28 B/parameter sweep over a large
-        tensor runs under the remaining (instruction-bound, not HBM-bound) backward kernels instead of after them.
-        `step()` then updates only the other parameters and joins the side stream.  The caller must call
-        `begin_step()` before backward of every step.  Arithmetic is unchanged (same kernel, same step count)."""
-        params = [p for p in params]
-        known = {id(p) for p in self.params}
-        for p in params:
-            if id(p) not in known:
-                raise ValueError("Adam.overlap: parameter is not managed by this optimizer")
-        for h in self._hooks:
-            h.remove()
-        self._hooks = []
-        self._early = {id(p): i for i, p in enumerate(params)}
-        self._early_stream = stream if stream is not None else torch.cuda.Stream(device=params[0].device)
-        for p in params:
-            self._hooks.append(p.register_post_accumulate_grad_hook(self._early_hook))
-
-    @torch.no_grad()
-    def begin_step(self) -> None:
-        """Start of a step in overlap mode: forget which parameters were updated early and, in capturable mode,
-        advance the device step counter once for all launches of this step."""
-        self._early_done = set()
-        self._ticked = False
-        if self._early and self.capturable:
-            if self._dev_step is None:
-                dev = self.params[0].device
-                t0 = max((st["step"] for st in self.state.values()), default=0)
-                self._dev_step = torch.zeros(4, dtype=torch.int32, device=dev)
-                self._dev_step[0] = t0
-            lib().call("vc_adam_tick", ptr(self._dev_step), self.betas[0], self.betas[1], stream_ptr())
-            self._ticked = True
-
-    def _early_hook(self, p) -> None:
-        if self._early_done is None or p.grad is None:   # begin_step() not called: step() handles p as usual
-            return
-        cur = torch.cuda.current_stream(p.device)
-        side = self._early_stream
-        side.wait_stream(cur)
-        with torch.cuda.stream(side), torch.no_grad():
-            self._update([p], slot=("early", self._early[id(p)]))
-        self._early_done.add(id(p))
-        self._early_pending = True
-
     # ----------------------------------------------------------------------------------------------- the update
-    def _update(self, plist, slot) -> None:
-        """One launch per distinct step count over the chunk table of `plist` on the current stream."""
-        by_step: Dict[int, list] = {}
+    def _segments(self, plist):
+        """(param base ptr, grad base ptr, m ptr, v ptr, n) of what this rank updates for each parameter."""
+        segs = []
         for p in plist:
-            g = p.grad
-            if not g.is_contiguous():
-                g = g.contiguous()
-                p.grad = g
             if not p.data.is_contiguous():
                 raise VaeclustError("vaeclust.optim.Adam: non-contiguous parameter")
             st = self._state(p)
             st["step"] += 1
-            by_step.setdefault(st["step"], []).append((p, g, st))
-        for t, items in by_step.items():
+            sh = self._shards.get(id(p))
+            if sh is None:
+                g = p.grad
+                if not g.is_contiguous():
+                    g = g.contiguous()
+                    p.grad = g
+                segs.append((p.data_ptr(), g.data_ptr(), st, p.numel()))
+            else:
+                lo, hi, gs = sh
+                segs.append((p.data_ptr() + 4 * lo, gs.data_ptr(), st, hi - lo))
+        return segs
+
+    def _update(self, plist) -> None:
+        """One launch over the chunk table of `plist` on the current stream (one launch per distinct step count)."""
+        by_step: Dict[int, list] = {}
+        for p, seg in zip(plist, self._segments(plist)):
+            by_step.setdefault(seg[2]["step"], []).append(seg)
+        if self.capturable and len(by_step) > 1:
+            raise VaeclustError("vaeclust.optim.Adam(capturable=True): every stepped parameter must share one step count")
+        for t, segs in by_step.items():
             rows = []
-            for p, g, st in items:
-                n = p.numel()
+            for pp, gp, st, n in segs:
+                if n == 0:
+                    continue
                 base = np.arange(0, n, _CHUNK, dtype=np.int64)
-                cnt = np.minimum(_CHUNK, n - base)
                 tab = np.empty((base.size, 5), dtype=np.int64)
-                tab[:, 0] = p.data_ptr() + 4 * base
-                tab[:, 1] = g.data_ptr() + 4 * base
+                tab[:, 0] = pp + 4 * base
+                tab[:, 1] = gp + 4 * base
                 tab[:, 2] = st["exp_avg"].data_ptr() + 4 * base
                 tab[:, 3] = st["exp_avg_sq"].data_ptr() + 4 * base
-                tab[:, 4] = cnt
+                tab[:, 4] = np.minimum(_CHUNK, n - base)
                 rows.append(tab)
+            if not rows:
+                continue
             table = np.concatenate(rows, axis=0)
             key = table.tobytes()
-            dev = items[0][0].device
+            dev = plist[0].device
+            c = self._table
+            if c is None or c["key"] != key or c["dev"].device != dev:
+                if not self.capturable:
+                    c = {"key": key, "dev": torch.from_numpy(table).to(dev, non_blocking=False)}
+                else:
+                    # never rewrite a table in place: a captured graph's memcpy node re-reads the pinned buffer and
+                    # its kernel node the device buffer on every replay, so a changed table gets FRESH buffers and
+                    # the old pair is retired (kept alive).  Nothing may be allocated while a stream is capturing,
+                    # so one spare pair of the right shape is always kept ready.
+                    if c is not None:
+                        self._retired.append(c)
+                        # tables filled during a capture belong to a graph and live as long as the optimizer; of the
+                        # others only the most recent few can still be in flight
+                        keep = [r for r in self._retired if r.get("captured")]
+                        self._retired = keep + [r for r in self._retired if not r.get("captured")][-4:]
+                    sp = self._spare
+                    if sp is None or tuple(sp["pinned"].shape) != table.shape or sp["dev"].device != dev:
+                        sp = self._new_pair(table.shape, dev)
+                    self._spare = None
+                    sp["pinned"].numpy()[...] = table
+                    sp["dev"].copy_(sp["pinned"], non_blocking=True)   # async + pinned: legal inside a capture
+                    sp["key"] = key
+                    sp["captured"] = torch.cuda.is_current_stream_capturing()
+                    c = sp
+                self._table = c
+            if self.capturable and self._spare is None and not torch.cuda.is_current_stream_capturing():
+                self._spare = self._new_pair(table.shape, dev)
             b1, b2 = self.betas
-            c = self._tables.setdefault(slot, {"key": None, "dev": None, "pinned": None})
             if self.capturable:
-                if len(by_step) != 1:
-                    raise VaeclustError("vaeclust.optim.Adam(capturable=True): every stepped parameter must share one "
-                                        "step count")
                 if self._dev_step is None:
                     self._dev_step = torch.zeros(4, dtype=torch.int32, device=dev)
                     self._dev_step[0] = t - 1
-                if c["key"] != key or c["dev"] is None or c["dev"].device != dev:
-                    # pinned + async so the upload is legal inside a capture (a replay re-reads the same host buffer);
-                    # both buffers are allocated by the first eager step and only rewritten afterwards
-                    if c["pinned"] is None or tuple(c["pinned"].shape) != table.shape:
-                        c["pinned"] = torch.empty(table.shape, dtype=torch.int64).pin_memory()
-                        c["dev"] = torch.empty(table.shape, dtype=torch.int64, device=dev)
-                    c["pinned"].numpy()[...] = table
-                    c["dev"].copy_(c["pinned"], non_blocking=True)
-                    c["key"] = key
-                if self._ticked:
-                    lib().call("vc_adam_multi_at", ptr(c["dev"]), int(table.shape[0]), self.lr, b1, b2, self.eps,
-                               ptr(self._dev_step), stream_ptr())
-                else:
-                    lib().call("vc_adam_multi_graph", ptr(c["dev"]), int(table.shape[0]), self.lr, b1, b2, self.eps,
-                               ptr(self._dev_step), stream_ptr())
-                continue
-            if c["key"] != key or c["dev"] is None or c["dev"].device != dev:
-                c["dev"] = torch.from_numpy(table).to(dev, non_blocking=False)
-                c["key"] = key
-            lib().call("vc_adam_multi", ptr(c["dev"]), int(table.shape[0]), self.lr, b1, b2, self.eps,
-                       1.0 - b1 ** t, 1.0 - b2 ** t, stream_ptr())
+                lib().call("vc_adam_multi_graph", ptr(c["dev"]), int(table.shape[0]), self.lr, b1, b2, self.eps,
+                           ptr(self._dev_step), stream_ptr())
+            else:
+                lib().call("vc_adam_multi", ptr(c["dev"]), int(table.shape[0]), self.lr, b1, b2, self.eps,
+                           1.0 - b1 ** t, 1.0 - b2 ** t, stream_ptr())
+
+    @staticmethod
+    def _new_pair(shape, dev) -> dict:
+        return {"key": None, "pinned": torch.empty(shape, dtype=torch.int64).pin_memory(),
+                "dev": torch.empty(shape, dtype=torch.int64, device=dev)}
 
     @torch.no_grad()
     def step(self) -> None:
         self.lr = float(self.param_groups[0]["lr"])
-        done = self._early_done or ()
-        rest = [p for p in self.params if p.grad is not None and id(p) not in done]
-        if rest:
-            self._update(rest, slot=("rest",))
-        if self._early_pending:
-            torch.cuda.current_stream(self.params[0].device).wait_stream(self._early_stream)
-            self._early_pending = False
-        self._early_done = None
-        self._ticked = False
+        todo = [p for p in self.params if id(p) not in self.skip and (p.grad is not None or id(p) in self._shards)]
+        if todo:
+            self._update(todo)
+
+    def device_step(self) -> torch.Tensor:
+        """The device-resident VcAdamDeviceStep of capturable mode (allocated on first use)."""
+        if self._dev_step is None:
+            t0 = max((st["step"] for st in self.state.values()), default=0)
+            self._dev_step = torch.zeros(4, dtype=torch.int32, device=self.params[0].device)
+            self._dev_step[0] = t0
+        return self._dev_step
 
     def state_dict(self) -> dict:
         if self.capturable and self._dev_step is not None:   # replays advance the device counter only

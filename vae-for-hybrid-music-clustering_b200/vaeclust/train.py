@@ -20,8 +20,6 @@ from . import ops
 from ._lib import VC_LOSS_MEAN_MEAN, VC_LOSS_SUM_MEAN
 from .optim import Adam
 
-_OVERLAP_MIN_NUMEL = 1 << 22   # parameters at least this large are updated early, on a side stream (Adam.overlap)
-
 
 def epoch_permutation(n: int) -> torch.Tensor:
     """The index order DataLoader(shuffle=True, num_workers=0) would produce for one epoch: the loader iterator
@@ -51,24 +49,17 @@ class VAEStep:
         self.multi = group is not None and vdist.world_size(group) > 1
         self.opt = Adam(model.parameters(), lr=lr, capturable=capturable)
         self.sync = vdist.OverlappedGradSync(model.parameters(), group) if self.multi else None
-        # opt-in (VAECLUST_ADAM_OVERLAP=1), one GPU: the Adam sweep over a large weight (28 B/parameter) starts on a
-        # side stream as soon as backward has produced its gradient and runs under the remaining backward kernels.
-        # Bit-identical, but measured SLOWER on script 12 (4.86 -> 4.95-5.00 ms/step, B200): the co-resident Adam CTAs
-        # take issue slots and L2 bandwidth from the instruction-bound implicit-GEMM producers, which costs more than
-        # the 0.6 ms sweep that gets hidden.  Kept off by default; DESIGN.md 5 records the experiment.
-        big = [p for p in model.parameters() if p.numel() >= _OVERLAP_MIN_NUMEL]
-        self.overlap = bool(big) and not self.multi and os.environ.get("VAECLUST_ADAM_OVERLAP", "0") == "1"
-        if self.overlap:
-            self.opt.overlap(big)
 
-    def __call__(self, x, *extra, eps: Optional[torch.Tensor] = None, global_batch: Optional[int] = None):
+    def __call__(self, x, *extra, eps: Optional[torch.Tensor] = None, global_batch: Optional[int] = None,
+                 local_rows: Optional[int] = None):
+        """`local_rows` overrides the weight of this rank's contribution (default: x.shape[0]); a rank whose shard of
+        the last batch is empty passes one dummy row with local_rows=0 so that it still takes part in the collectives."""
         m = self.model
         if self.sync is not None:
-            self.sync.begin(x.shape[0], global_batch or x.shape[0] * vdist.world_size(self.group))
+            rows = x.shape[0] if local_rows is None else int(local_rows)
+            self.sync.begin(rows, global_batch or x.shape[0] * vdist.world_size(self.group))
         else:
             self.opt.zero_grad()
-        if self.overlap:
-            self.opt.begin_step()
         if self.kind == "conv12":
             lyr, mask = extra
             mu, lv = m.encode(x, lyr, mask)
@@ -158,7 +149,8 @@ class HostBatchFeeder:
             dev = [torch.empty((batch_size,) + tuple(a.shape[1:]), dtype=a.dtype, device=device) for a in self.host]
             stage = [torch.empty((batch_size,) + tuple(a.shape[1:]), dtype=a.dtype).pin_memory()
                      if a[0].numel() * a.element_size() <= small_bytes else None for a in self.host]
-            self.slots.append(dict(dev=dev, stage=stage, ready=torch.cuda.Event(), free=torch.cuda.Event(), n=0))
+            self.slots.append(dict(dev=dev, stage=stage, ready=torch.cuda.Event(), free=torch.cuda.Event(),
+                                   copied=torch.cuda.Event(), used=False, n=0))
         self.bytes_per_sample = sum(a[0].numel() * a.element_size() for a in self.host)
         self._next = 0
         self._queue = []
@@ -170,6 +162,10 @@ class HostBatchFeeder:
         idx_t = idx if isinstance(idx, torch.Tensor) else torch.as_tensor(idx)
         ids = idx_t.tolist()
         n = len(ids)
+        if slot["used"]:
+            # the pinned staging rows are rewritten by the HOST below: the H2D copies that last read them must have
+            # completed (a stream-side wait is not enough when the host runs ahead of the GPU)
+            slot["copied"].synchronize()
         with torch.cuda.stream(self.copy_stream):
             self.copy_stream.wait_event(slot["free"])  # the step that last used this slot has been enqueued and finished
             for h, d, st in zip(self.host, slot["dev"], slot["stage"]):
@@ -179,8 +175,9 @@ class HostBatchFeeder:
                 else:
                     for i, j in enumerate(ids):
                         d[i].copy_(h[j], non_blocking=True)
+            slot["copied"].record(self.copy_stream)
             slot["ready"].record(self.copy_stream)
-        slot["n"] = n
+        slot["n"], slot["used"] = n, True
         self._queue.append(slot)
 
     def get(self):
@@ -208,11 +205,15 @@ def _to_dev(a, device):
 
 
 def fit(model, kind: str, arrays, epochs: int, batch_size: int, lr: float, beta: float, device=None,
-        on_epoch: Optional[Callable] = None, group=None) -> TrainLog:
+        on_epoch: Optional[Callable] = None, group=None, eps_fn: Optional[Callable] = None) -> TrainLog:
     """The hot loop of 12:246-287 / 19:209-245 / 06:314-344 with a device-resident dataset.
     arrays: (X, lyr, mask) for conv12; (X,) or (X, cond) for mlp19; (X,) for mlp06.
     Epoch averages follow the scripts: unweighted mean of batch means for 06/12 (12:274-276), sample-weighted
-    for 19 (19:234-242)."""
+    for 19 (19:234-242).  `eps_fn(epoch, step, rows)` (optional) supplies the reparameterisation noise of a GLOBAL
+    batch as a CPU tensor (parity tests inject the oracle's stream); default: torch.randn on the device.
+    Under a process group every rank draws the same permutation and trains on its slice of each global batch; all
+    ranks take part in every step (a rank with an empty slice contributes a zero-weight dummy row) and the logged
+    statistics are the global-batch values, all-reduced once per epoch."""
     device = device or torch.device("cuda", torch.cuda.current_device())
     data = [_to_dev(a, device) for a in arrays]
     n = data[0].shape[0]
@@ -223,21 +224,96 @@ def fit(model, kind: str, arrays, epochs: int, batch_size: int, lr: float, beta:
     for epoch in range(1, epochs + 1):
         acc = torch.zeros(3, dtype=torch.float64, device=device)
         denom = 0.0
-        for idx in batches(n, batch_size):  # every rank draws the same permutation (same seed)
+        for s_i, idx in enumerate(batches(n, batch_size)):  # every rank draws the same permutation (same seed)
             gb = idx.numel()
             lo, hi = vdist.shard_bounds(gb, rank, world)
-            if hi <= lo:
-                continue
+            rows = hi - lo
+            if rows == 0:
+                lo, hi = 0, 1           # dummy row, weight 0: keeps this rank inside the step's collectives
             sel = idx[lo:hi].to(device)
-            stats = step(*[t.index_select(0, sel) for t in data], global_batch=gb)
-            w = float(hi - lo) if kind == "mlp19" else 1.0
-            acc += stats.to(torch.float64) * w
+            eps = None
+            if eps_fn is not None:
+                eps = eps_fn(epoch, s_i, gb)[lo:hi].to(device)
+            stats = step(*[t.index_select(0, sel) for t in data], eps=eps, global_batch=gb, local_rows=rows)
+            w = float(gb) if kind == "mlp19" else 1.0
+            acc += stats.to(torch.float64) * (w * rows / gb)   # this rank's share of the global-batch mean
             denom += w
+        if world > 1:
+            vdist.all_reduce_sum(acc, group)
         tot = acc.cpu().numpy() / max(denom, 1.0)  # the one host sync of the epoch
         log.loss.append(float(tot[0])); log.recon.append(float(tot[1])); log.kl.append(float(tot[2]))
         if on_epoch is not None:
             on_epoch(epoch, log, model)
     return log
+
+
+# ------------------------------------------------------------------- host helpers around the loop (drop-in formats)
+def align_lyrics_to_audio(audio_ids: np.ndarray, lyr_ids: np.ndarray, lyr_emb: np.ndarray, verbose: bool = True):
+    """12:35-60: (lyr_aligned [N, D] float32, mask [N, 1] float32); rows of tracks without lyrics stay zero.  Same
+    semantics as the reference's dict lookup (a track id listed twice keeps its LAST embedding), vectorised."""
+    audio_ids = np.asarray(audio_ids).astype(np.int64)
+    lyr_ids = np.asarray(lyr_ids).astype(np.int64)
+    D = lyr_emb.shape[1]
+    lyr_aligned = np.zeros((len(audio_ids), D), dtype=np.float32)
+    mask = np.zeros((len(audio_ids), 1), dtype=np.float32)
+    if len(lyr_ids):
+        # last occurrence of every id: reverse, unique (first of the reversed = last of the original)
+        uniq, first_rev = np.unique(lyr_ids[::-1], return_index=True)
+        last = len(lyr_ids) - 1 - first_rev
+        pos = np.searchsorted(uniq, audio_ids)
+        pos_c = np.clip(pos, 0, len(uniq) - 1)
+        hit = uniq[pos_c] == audio_ids
+        lyr_aligned[hit] = lyr_emb[last[pos_c[hit]]]
+        mask[hit, 0] = 1.0
+    if verbose:
+        print(f"Lyrics aligned: {int(mask.sum())}/{len(audio_ids)} tracks have embeddings.")
+    return lyr_aligned, mask
+
+
+class Script12Writer:
+    """Per-epoch outputs of script 12 (12:236-240,278-285): `train_log.csv` with header `epoch,loss,recon,kl` and
+    `%.6f` rows, and `ckpt_epoch_XXX.pt` = {"model": state_dict, "cfg": dict, "feat_hw", "lyr_dim"}.  Pass an instance
+    as fit(on_epoch=...)."""
+
+    def __init__(self, out_dir, cfg: dict, feat_hw, lyr_dim: int, save_ckpt: bool = True):
+        from pathlib import Path
+        self.out_dir = Path(out_dir)
+        self.out_dir.mkdir(parents=True, exist_ok=True)
+        self.cfg, self.feat_hw, self.lyr_dim, self.save_ckpt = dict(cfg), tuple(feat_hw), int(lyr_dim), save_ckpt
+        self.log_path = self.out_dir / "train_log.csv"
+        with self.log_path.open("w", encoding="utf-8") as f:
+            f.write("epoch,loss,recon,kl\n")
+
+    def __call__(self, epoch: int, log: TrainLog, model) -> None:
+        with self.log_path.open("a", encoding="utf-8") as f:
+            f.write(f"{epoch},{log.loss[-1]:.6f},{log.recon[-1]:.6f},{log.kl[-1]:.6f}\n")
+        if self.save_ckpt:
+            torch.save({"model": model.state_dict(), "cfg": self.cfg, "feat_hw": self.feat_hw, "lyr_dim": self.lyr_dim},
+                       self.out_dir / f"ckpt_epoch_{epoch:03d}.pt")
+
+
+def save_script19_model(path, model, *, input_dim: int, latent_dim: int, hidden_dim: int, beta: float, use_cvae: bool,
+                        cond_dim: int, include_genre_in_input: bool = False, include_lang_in_input: bool = False,
+                        cond_on: str = "genre_lang", seed: int = 42) -> None:
+    """The model dict of 19:248-264 (keys and value types as the reference writes them)."""
+    torch.save({"state_dict": model.state_dict(), "input_dim": int(input_dim), "latent_dim": int(latent_dim),
+                "hidden_dim": int(hidden_dim), "beta": float(beta), "use_cvae": bool(use_cvae), "cond_dim": int(cond_dim),
+                "include_genre_in_input": bool(include_genre_in_input),
+                "include_lang_in_input": bool(include_lang_in_input), "cond_on": cond_on, "seed": int(seed)}, path)
+
+
+def save_script06_outputs(out_dir, model, cfg: dict, log: TrainLog) -> None:
+    """06:347-351: bare state_dict `vae_basic.pt`, `train_config.json`, `history.json` {"epoch","recon","kl","total"}."""
+    import json
+    from pathlib import Path
+    out = Path(out_dir)
+    out.mkdir(parents=True, exist_ok=True)
+    torch.save(model.state_dict(), out / "vae_basic.pt")
+    with open(out / "train_config.json", "w", encoding="utf-8") as f:
+        json.dump(cfg, f, indent=2)
+    hist = {"epoch": list(range(1, len(log.loss) + 1)), "recon": log.recon, "kl": log.kl, "total": log.loss}
+    with open(out / "history.json", "w", encoding="utf-8") as f:
+        json.dump(hist, f, indent=2)
 
 
 @torch.no_grad()
