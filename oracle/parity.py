@@ -15,10 +15,15 @@ import torch
 
 from . import vae_ref
 
-# Stated tolerances of the bf16 tensor-core mode (operands rounded to 8 mantissa bits, fp32 accumulation), measured
-# on B200 at the benchmark shapes and rounded up with margin; fp32 mode must meet the north star's 1e-3 on the loss.
+# Stated tolerances.  fp32 mode must meet the north star's 1e-3 on the loss against the reference arithmetic.  The bf16
+# tensor-core mode (operands rounded to 8 mantissa bits, fp32 accumulation) is checked twice:
+#   * against the oracle computing in the SAME arithmetic (vae_ref.emulate_bf16: operands rounded at the same points,
+#     fp32 accumulate) -- only summation order differs, so the bound is tight and this is the correctness gate;
+#   * against the plain fp32 oracle -- the loss agrees to ~1e-5, but gradients of layers below a ReLU differ by a few
+#     per cent because pre-activations within rounding distance of 0 flip their mask (a fraction p of flipped units
+#     moves the gradient by ~sqrt(p)); measured on B200 at the benchmark shapes: <= 0.09.  Reported, bounded at 0.15.
 TOL = {
-    "bf16": dict(loss_rel=5e-3, grad_rel=3e-2),
+    "bf16": dict(loss_rel=1e-4, grad_rel=2e-2, loss_rel_vs_fp32=5e-3, grad_rel_vs_fp32=0.15),
     "fp32": dict(loss_rel=1e-3, grad_rel=2e-3),
 }
 
@@ -30,13 +35,47 @@ def _rel(a: torch.Tensor, b: torch.Tensor) -> float:
     return float((a - b).norm()) / den if den > 0 else float((a - b).norm())
 
 
+def _oracle_step(p0, kind, b_cpu, beta, lr, emulate):
+    p_ref = {n: v.clone() for n, v in p0.items()}
+    opt = vae_ref.AdamRef(p_ref, lr)
+    vae_ref.emulate_bf16(emulate)
+    try:
+        t0 = time.perf_counter()
+        ref = vae_ref.train_step(p_ref, opt, kind, b_cpu, beta)
+        dt = time.perf_counter() - t0
+    finally:
+        vae_ref.emulate_bf16(False)
+    return ref, opt.last_grads, p_ref, dt
+
+
+def _compare(stats, grads, after, ref, g_ref, p_ref, names):
+    out = {"loss_ref": ref[0], "loss_rel": abs(float(stats[0]) - ref[0]) / abs(ref[0]),
+           "recon_rel": abs(float(stats[1]) - ref[1]) / abs(ref[1]),
+           "kl_rel": abs(float(stats[2]) - ref[2]) / max(abs(ref[2]), 1e-12)}
+    grad_rel, none_mismatch = {}, []
+    for n in names:
+        if (g_ref[n] is None) != (grads[n] is None):
+            none_mismatch.append(n)
+        elif grads[n] is not None:
+            grad_rel[n] = _rel(grads[n], g_ref[n])
+    worst = max(grad_rel, key=grad_rel.get)
+    out["grad_rel_max"], out["grad_rel_max_param"] = grad_rel[worst], worst
+    out["grad_rel"] = {n: float(f"{v:.3g}") for n, v in grad_rel.items()}
+    out["grad_none_mismatch"] = none_mismatch
+    # parameters after the first Adam step: |delta| ~ lr wherever |g| >> eps, so a sign flip of a near-zero gradient
+    # element moves a parameter by 2 lr; relative to the parameter norm
+    out["param_rel_after_adam"] = max(_rel(after[n], p_ref[n]) for n in names)
+    return out
+
+
 def vae_step_parity(model, step, kind: str, batch: Dict[str, torch.Tensor], beta: float, lr: float,
                     precision: str) -> dict:
-    """Run ONE optimisation step of `step` (a vaeclust.train.VAEStep over `model`, first step of its optimizer) and of
-    the oracle from the same parameters, batch and eps.  kind: "conv" | "mlp19" | "mlp06"; batch holds CUDA tensors
-    x, eps and (conv) lyr, m or (mlp19) c.  Returns the comparison and whether it is within TOL[precision]."""
+    """Run ONE optimisation step of `step` (a vaeclust.train.VAEStep or a fused-step object over `model`, first step of
+    its optimizer) and of the oracle from the same parameters, batch and eps.  kind: "conv" | "mlp19" | "mlp06";
+    batch holds CUDA tensors x, eps and (conv) lyr, m or (mlp19) c.  Returns the comparison and whether it is within
+    TOL[precision]."""
     names = [n for n, _ in model.named_parameters()]
-    p_ref = {n: p.detach().cpu().clone() for n, p in model.named_parameters()}
+    p0 = {n: p.detach().cpu().clone() for n, p in model.named_parameters()}
     b_cpu = {k: v.detach().cpu() for k, v in batch.items()}
     if kind == "conv":
         args = (batch["x"], batch["lyr"], batch["m"])
@@ -46,34 +85,27 @@ def vae_step_parity(model, step, kind: str, batch: Dict[str, torch.Tensor], beta
         args = (batch["x"],)
     stats = step(*args, eps=batch["eps"]).detach().cpu().numpy()
     torch.cuda.synchronize()
-    grads = {n: (p.grad.detach().clone() if p.grad is not None else None) for n, p in model.named_parameters()}
+    if hasattr(step, "last_grads"):      # fused steps never materialise .grad; they expose a debug copy
+        grads = {n: (g.detach().clone() if g is not None else None) for n, g in step.last_grads().items()}
+    else:
+        grads = {n: (p.grad.detach().clone() if p.grad is not None else None) for n, p in model.named_parameters()}
     after = {n: p.detach().cpu().clone() for n, p in model.named_parameters()}
-    opt = vae_ref.AdamRef(p_ref, lr)
-    t0 = time.perf_counter()
-    ref = vae_ref.train_step(p_ref, opt, kind, b_cpu, beta)
-    dt = time.perf_counter() - t0
-    out = {"loss": float(stats[0]), "loss_ref": ref[0], "recon_ref": ref[1], "kl_ref": ref[2],
-           "loss_rel": abs(float(stats[0]) - ref[0]) / abs(ref[0]),
-           "recon_rel": abs(float(stats[1]) - ref[1]) / abs(ref[1]),
-           "kl_rel": abs(float(stats[2]) - ref[2]) / max(abs(ref[2]), 1e-12), "oracle_step_s": dt}
-    grad_rel, none_mismatch = {}, []
-    for n in names:
-        g_ref, g = opt.last_grads[n], grads[n]
-        if (g_ref is None) != (g is None):
-            none_mismatch.append(n)
-        elif g is not None:
-            grad_rel[n] = _rel(g, g_ref)
-    worst = max(grad_rel, key=grad_rel.get)
-    out["grad_rel_max"] = grad_rel[worst]
-    out["grad_rel_max_param"] = worst
-    out["grad_rel"] = {n: round(v, 6) for n, v in grad_rel.items()}
-    out["grad_none_mismatch"] = none_mismatch
-    # parameters after the first Adam step: |delta| = lr wherever |g| >> eps, so a sign flip of a near-zero gradient
-    # element moves a parameter by 2 lr; reported relative to the parameter norm and to the update norm
-    out["param_rel_after_adam"] = max(_rel(after[n], p_ref[n]) for n in names)
     tol = TOL[precision]
-    out["tolerance"] = dict(tol, precision=precision)
-    out["ok"] = bool(out["loss_rel"] <= tol["loss_rel"] and out["grad_rel_max"] <= tol["grad_rel"] and not none_mismatch)
+    ref, g_ref, p_ref, dt = _oracle_step(p0, kind, b_cpu, beta, lr, emulate=False)
+    out = {"loss": float(stats[0]), "oracle_step_s": dt, "precision": precision, "tolerance": tol}
+    if precision == "fp32":
+        out.update(_compare(stats, grads, after, ref, g_ref, p_ref, names))
+        out["ok"] = bool(out["loss_rel"] <= tol["loss_rel"] and out["grad_rel_max"] <= tol["grad_rel"]
+                         and not out["grad_none_mismatch"])
+        return out
+    vs32 = _compare(stats, grads, after, ref, g_ref, p_ref, names)
+    ref_e, g_e, p_e, _ = _oracle_step(p0, kind, b_cpu, beta, lr, emulate=True)
+    out.update(_compare(stats, grads, after, ref_e, g_e, p_e, names))   # headline fields: same-arithmetic oracle
+    out["vs_fp32_oracle"] = {k: vs32[k] for k in ("loss_ref", "loss_rel", "recon_rel", "kl_rel", "grad_rel_max",
+                                                   "grad_rel_max_param", "param_rel_after_adam")}
+    out["ok"] = bool(out["loss_rel"] <= tol["loss_rel"] and out["grad_rel_max"] <= tol["grad_rel"]
+                     and not out["grad_none_mismatch"] and vs32["loss_rel"] <= tol["loss_rel_vs_fp32"]
+                     and vs32["grad_rel_max"] <= tol["grad_rel_vs_fp32"])
     return out
 
 

@@ -99,6 +99,52 @@ def init_mlp_vae_params(input_dim, latent_dim=16, hidden_dim=256, cond_dim=0, se
     return p
 
 
+# ------------------------------------------------- emulation of the bf16 tensor-core mode of the product
+# The product's bf16 mode rounds BOTH operands of every tensor-core contraction to bf16 (8 mantissa bits) and
+# accumulates in fp32: activations and weights in the forward and data-gradient ops, the incoming gradient and the saved
+# input in the weight-gradient op.  The single-channel ends of script 12 (Conv2d 1->32, ConvTranspose2d 32->1) run on
+# fp32 FFMA kernels and are not rounded.  With `emulate_bf16(True)` the functions below round at exactly those points
+# (straight-through in the other direction), so a CUDA step can be checked against an oracle that computes in the SAME
+# arithmetic with a tight tolerance; what remains is fp32 summation order.  Default: plain fp32 (the reference).
+_EMU_BF16 = False
+
+
+def emulate_bf16(on: bool) -> None:
+    global _EMU_BF16
+    _EMU_BF16 = bool(on)
+
+
+class _RoundFwd(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, t):
+        return t.to(torch.bfloat16).to(torch.float32)
+
+    @staticmethod
+    def backward(ctx, g):
+        return g
+
+
+class _RoundBwd(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, t):
+        return t.view_as(t)
+
+    @staticmethod
+    def backward(ctx, g):
+        return g.to(torch.bfloat16).to(torch.float32)
+
+
+def _tc(op, x, w, b, rounded=True, **kw):
+    """One tensor-core layer op(x, w, b): fp32, or operands rounded to bf16 in forward and backward."""
+    if not (_EMU_BF16 and rounded):
+        return op(x, w, b, **kw)
+    # bias joins after the contraction: the gradient is rounded where the dgrad / wgrad kernels consume it
+    y = _RoundBwd.apply(op(_RoundFwd.apply(x), _RoundFwd.apply(w), None, **kw))
+    if b is None:
+        return y
+    return y + (b.view(1, -1, 1, 1) if y.dim() == 4 else b)
+
+
 # ------------------------------------------------------------------------- forward
 def reparam(mu: Tensor, logvar: Tensor, eps: Tensor) -> Tensor:
     """12:168-172 / 19:105-108 / 06:164-168 with eps injected instead of randn_like."""
@@ -107,26 +153,30 @@ def reparam(mu: Tensor, logvar: Tensor, eps: Tensor) -> Tensor:
 
 def conv_vae_forward(p: Dict[str, Tensor], x: Tensor, lyr: Tensor, m: Tensor, eps: Tensor):
     """ConvMultiModalVAE.forward (12:174-186) -> (xhat_uncropped, mu, lv)."""
+    lin = lambda t, k: _tc(F.linear, t, p[k + ".weight"], p[k + ".bias"])
     h = x
     for i in (0, 2, 4):  # AudioEncoder.conv 12:86-90
-        h = F.relu(F.conv2d(h, p[f"audio_enc.conv.{i}.weight"], p[f"audio_enc.conv.{i}.bias"], stride=2, padding=1))
+        h = F.relu(_tc(F.conv2d, h, p[f"audio_enc.conv.{i}.weight"], p[f"audio_enc.conv.{i}.bias"],
+                       rounded=h.shape[1] > 1, stride=2, padding=1))
     hshape = h.shape[1:]
-    h = F.relu(F.linear(h.flatten(1), p["audio_enc.fc.0.weight"], p["audio_enc.fc.0.bias"]))  # 12:98-101,106-107
-    mu_a = F.linear(h, p["audio_enc.mu.weight"], p["audio_enc.mu.bias"])  # lv_a unused (12:175)
-    l = F.relu(F.linear(lyr, p["lyr_proj.net.0.weight"], p["lyr_proj.net.0.bias"]))  # 12:114-117
-    l = F.relu(F.linear(l, p["lyr_proj.net.2.weight"], p["lyr_proj.net.2.bias"]))
+    h = F.relu(lin(h.flatten(1), "audio_enc.fc.0"))  # 12:98-101,106-107
+    mu_a = lin(h, "audio_enc.mu")  # lv_a unused (12:175)
+    l = F.relu(lin(lyr, "lyr_proj.net.0"))  # 12:114-117
+    l = F.relu(lin(l, "lyr_proj.net.2"))
     l = l * m  # 12:178
-    hf = F.relu(F.linear(torch.cat([mu_a, l, m], dim=1), p["fuse.0.weight"], p["fuse.0.bias"]))  # 12:180
-    mu = F.linear(hf, p["mu.weight"], p["mu.bias"])
-    lv = F.linear(hf, p["logvar.weight"], p["logvar.bias"])
+    hf = F.relu(lin(torch.cat([mu_a, l, m], dim=1), "fuse.0"))  # 12:180
+    mu = lin(hf, "mu")
+    lv = lin(hf, "logvar")
     z = reparam(mu, lv, eps)
-    d = F.relu(F.linear(z, p["audio_dec.fc.0.weight"], p["audio_dec.fc.0.bias"]))  # 12:129-132
-    d = F.relu(F.linear(d, p["audio_dec.fc.2.weight"], p["audio_dec.fc.2.bias"]))
+    d = F.relu(lin(z, "audio_dec.fc.0"))  # 12:129-132
+    d = F.relu(lin(d, "audio_dec.fc.2"))
     d = d.view(z.size(0), *hshape)
-    d = F.relu(F.conv_transpose2d(d, p["audio_dec.deconv.0.weight"], p["audio_dec.deconv.0.bias"], stride=2, padding=1))
-    d = F.relu(F.conv_transpose2d(d, p["audio_dec.deconv.2.weight"], p["audio_dec.deconv.2.bias"], stride=2, padding=1))
-    xhat = F.conv_transpose2d(d, p["audio_dec.deconv.4.weight"], p["audio_dec.deconv.4.bias"], stride=2, padding=1)
-    return xhat, mu, lv
+    for i in (0, 2, 4):  # AudioDecoder.deconv 12:134-138 (no activation after the last one)
+        w = p[f"audio_dec.deconv.{i}.weight"]
+        d = _tc(F.conv_transpose2d, d, w, p[f"audio_dec.deconv.{i}.bias"], rounded=w.shape[1] > 1, stride=2, padding=1)
+        if i != 4:
+            d = F.relu(d)
+    return d, mu, lv
 
 
 def conv_vae_loss(xhat: Tensor, x: Tensor, mu: Tensor, lv: Tensor, beta: float):
@@ -141,7 +191,7 @@ def mlp_vae_forward(p: Dict[str, Tensor], x: Tensor, eps: Tensor, c: Optional[Te
     """MLPVAE.forward 19:117-121 (cond concatenated on both sides, 19:97-115) / 06:175-179."""
     n = (["enc.0", "enc.2", "mu", "logvar", "dec.0", "dec.2", "dec.4"] if style == "19"
          else ["enc1", "enc2", "mu", "logvar", "dec1", "dec2", "out"])
-    lin = lambda t, k: F.linear(t, p[k + ".weight"], p[k + ".bias"])
+    lin = lambda t, k: _tc(F.linear, t, p[k + ".weight"], p[k + ".bias"])
     xi = x if c is None else torch.cat([x, c], dim=1)
     h = F.relu(lin(F.relu(lin(xi, n[0])), n[1]))
     mu, lv = lin(h, n[2]), lin(h, n[3])
