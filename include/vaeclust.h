@@ -165,12 +165,57 @@ typedef struct VcAdamDeviceStep {
 int vc_adam_multi_graph(const VcAdamChunk* table, int n_chunks, float lr, float beta1, float beta2, float eps,
                         VcAdamDeviceStep* step_state, void* stream);
 /* The two halves of vc_adam_multi_graph on their own, for a step that updates its parameters in several launches
- * (vaeclust.optim.Adam.overlap: the 67 M-element FC weights are updated on a side stream as soon as backward has
- * produced their gradients, under the rest of backward): vc_adam_tick advances the counter once per step,
- * vc_adam_multi_at updates the chunks of `table` with the bias corrections of the current device step. */
+ * (sharded / bucketed updates that start as soon as a gradient bucket has been reduced): vc_adam_tick advances the
+ * counter once per step, vc_adam_multi_at updates the chunks of `table` with the bias corrections of the current
+ * device step. */
 int vc_adam_tick(VcAdamDeviceStep* step_state, float beta1, float beta2, void* stream);
 int vc_adam_multi_at(const VcAdamChunk* table, int n_chunks, float lr, float beta1, float beta2, float eps,
                      const VcAdamDeviceStep* step_state, void* stream);
+
+/* ------------------------------------------------------------------ fused MLP-VAE train step (scripts 19 / 06 / 22)
+ * The whole optimisation step of MLPVAE (19:64-121 model, 19:226-232 step), of script 06's MLPVAE (06:145-188,
+ * 06:322-327) and of script 22's AE baseline (22:66-87,150-156) in four launches: pack -> [forward + loss + data
+ * gradients per 128-row tile, tcgen05] -> [weight gradients with the batch as the contraction, tcgen05] -> [fold +
+ * Adam + bf16 weight shadows].  hidden must be 256, latent in {8,16,32}, input_dim + cond_dim <= 512,
+ * latent + cond_dim <= 64; anything else is VC_ERR_UNSUPPORTED (callers then use the per-layer ops above).
+ *   variational = 1: heads mu | logvar, z = mu + eps*exp(logvar/2), loss = recon + beta*KL under `loss_mode`
+ *   variational = 0: one head z (22:66-87), loss = mean squared error (VC_LOSS_MEAN_MEAN), no KL
+ * Parameter order in VcMlpVaeParams: 0 enc.0 / enc1, 1 enc.2 / enc2, 2 mu (or the AE's enc.4), 3 logvar (unused for
+ * the AE), 4 dec.0 / dec1, 5 dec.2 / dec2, 6 dec.4 / out; p = fp32 master, m / v = Adam moments (same shape).
+ * The struct itself lives in HOST memory and holds device pointers.
+ * The workspace belongs to ONE model instance and must persist between calls (it holds the bf16 weight shadows):
+ * call vc_mlpvae_prepare once, and again whenever the fp32 masters were changed from outside (load_state_dict).
+ * `phases` bit 0: pack + rows + weight-gradient partials; bit 1: fold the partials into the flat gradient block
+ * (scaled by grad_weight = B_local / B_global) and write out3 = {loss, recon, kl} of THIS batch; bit 2: Adam from the
+ * flat block + refresh the shadows.  One GPU: phases = 7.  Data parallel: 3, all-reduce(sum) the flat block
+ * (vc_mlpvae_grad_layout), then 4.  step_state != NULL: bias corrections are read from (and, with bit 0, the step
+ * counter advanced in) device memory, so the call sequence can be replayed from a CUDA graph. */
+typedef struct VcMlpVaeDesc {
+  int32_t input_dim, cond_dim, hidden, latent, variational, loss_mode;
+  float beta;
+  int32_t pad;
+} VcMlpVaeDesc;
+typedef struct VcMlpTensor {
+  float* p;
+  float* m;
+  float* v;
+} VcMlpTensor;
+typedef struct VcMlpVaeParams {
+  VcMlpTensor W[7];
+  VcMlpTensor b[7];
+} VcMlpVaeParams;
+int vc_mlpvae_supported(const VcMlpVaeDesc* desc);
+size_t vc_mlpvae_workspace_bytes(const VcMlpVaeDesc* desc, int B);
+/* out[0] = byte offset (from the workspace pointer rounded up to 1024) of the flat fp32 gradient block, out[1] = its
+ * element count; then for each of the 6 layers (heads = mu rows then logvar rows): weight offset in elements, row
+ * pitch in elements, bias offset in elements.  Gradient of W_l[o][i] = block[woff + o*pitch + i]. */
+int vc_mlpvae_grad_layout(const VcMlpVaeDesc* desc, int B, int64_t* out);
+int vc_mlpvae_prepare(const VcMlpVaeDesc* desc, const VcMlpVaeParams* params, int B, void* workspace,
+                      size_t workspace_bytes, void* stream);
+int vc_mlpvae_step(const VcMlpVaeDesc* desc, const VcMlpVaeParams* params, const float* x, const float* c,
+                   const float* eps, int B, float grad_weight, int phases, float lr, float beta1, float beta2,
+                   float adam_eps, float bias_corr1, float bias_corr2, VcAdamDeviceStep* step_state, float* out3,
+                   void* workspace, size_t workspace_bytes, int variant, void* stream);
 
 /* --------------------------------------------------------------------------------------------- KMeans
  * One Lloyd iteration of sklearn:cluster/_k_means_lloyd.pyx:23-218 reached from 07:70-71, 13:120-121, 16:183,

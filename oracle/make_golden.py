@@ -28,6 +28,7 @@ CASES = {
     "cvae19": dict(kind="mlp19", input_dim=464, cond=6, latent=16, hidden=256, B=32, beta=4.0, lr=1e-3, steps=3),
     "beta19": dict(kind="mlp19", input_dim=464, cond=0, latent=16, hidden=256, B=17, beta=4.0, lr=1e-3, steps=3),
     "easy06": dict(kind="mlp06", input_dim=80, cond=0, latent=16, hidden=256, B=16, beta=1.0, lr=1e-3, steps=3),
+    "ae22": dict(kind="ae22", input_dim=464, cond=0, latent=16, hidden=256, B=24, beta=0.0, lr=1e-3, steps=3),
 }
 
 
@@ -49,7 +50,7 @@ def case_inputs(name: str, step: int) -> dict:
     else:
         D = c["input_dim"]
         x = rng.standard_normal((B, D)).astype(np.float32)
-        if c["kind"] == "mlp19":
+        if c["kind"] in ("mlp19", "ae22"):
             x[:, :80] *= np.logspace(1.0, 0.0, 80, dtype=np.float32)  # raw MFCC-stat scale (tamed for tests)
             x[:, 80:] *= 0.05
         eps = rng.standard_normal((B, c["latent"])).astype(np.float32)
@@ -66,6 +67,8 @@ def case_params(name: str) -> dict:
     c = CASES[name]
     if c["kind"] == "conv":
         return vae_ref.init_conv_vae_params(c["feat_hw"], z_dim=c["z"], lyr_dim=c["lyr"], seed=7)
+    if c["kind"] == "ae22":
+        return vae_ref.init_ae_params(c["input_dim"], c["latent"], c["hidden"], seed=7)
     style = "19" if c["kind"] == "mlp19" else "06"
     return vae_ref.init_mlp_vae_params(c["input_dim"], c["latent"], c["hidden"], c["cond"], seed=7, style=style)
 
@@ -90,6 +93,9 @@ def run_reference(name: str):
     elif c["kind"] == "mlp19":
         mod = ref_loader.load("19")
         model = mod.MLPVAE(c["input_dim"], c["latent"], c["hidden"], cond_dim=c["cond"], conditional=bool(c["cond"]))
+    elif c["kind"] == "ae22":
+        mod = ref_loader.load("22")
+        model = mod.AE(in_dim=c["input_dim"], z_dim=c["latent"])
     else:
         mod = ref_loader.load("06")
         model = mod.MLPVAE(c["input_dim"], c["hidden"], c["latent"])
@@ -116,6 +122,11 @@ def run_reference(name: str):
                 k = mod.kl_divergence(mu, lv)
                 loss = (r + c["beta"] * k).mean()
                 recon, kl = r.mean(), k.mean()
+            elif c["kind"] == "ae22":
+                xhat, mu = model(b["x"])          # (x_hat, z): z stands where mu does in the fixture
+                lv = torch.zeros_like(mu)
+                loss = torch.nn.functional.mse_loss(xhat, b["x"])
+                recon, kl = loss, torch.zeros(())
             else:
                 xhat, mu, lv = model(b["x"])
                 loss, parts = mod.vae_loss(xhat, b["x"], mu, lv, c["beta"])

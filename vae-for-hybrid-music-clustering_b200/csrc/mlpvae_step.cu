@@ -1,0 +1,1036 @@
+// vc_mlpvae_step: the whole train step of the MLP VAEs of scripts 19 / 06 / 22 (19:64-121,209-232; 06:145-188,314-344;
+// 22:66-87,135-171) -- forward, reparameterisation, loss, backward, Adam -- as FOUR launches instead of ~50:
+//
+//   P  mv_pack_kernel    [x | c] -> bf16 rows (K padded to 64), the first tensor-core operand; ticks the Adam step
+//   A  mv_rows_kernel    one persistent CTA per SM, 128 batch rows per tile: the six forward GEMMs chained through ONE
+//                        64 KB shared-memory activation buffer (each epilogue overwrites it in place: bias, ReLU,
+//                        bf16, 128-byte-swizzled K-major rows = the next A operand), reparameterisation + KL, the
+//                        reconstruction loss straight from the accumulators, and the six data-gradient GEMMs back
+//                        down.  tcgen05.mma with accumulators in tensor memory; weights (bf16 shadows, forward and
+//                        transposed) stream from L2 through a 3-stage TMA ring that runs ahead across layers; the next
+//                        tile's input rows are prefetched by TMA during the current tile's backward.  ReLU masks stay
+//                        in registers (the thread that wrote an activation row also masks its gradient).  Activations
+//                        and pre-activation gradients leave as bf16 rows for kernel B.
+//   B  mv_wgrad_kernel   weight gradients dW_l = G_l^T A_l with the BATCH as the contraction: both operands are the
+//                        row-major [batch][features] matrices kernel A wrote, fetched by TMA and used as MN-major
+//                        tcgen05 operands (no transpose anywhere); bias gradients ride along as an extra N=16 MMA against a
+//                        constant ones tile; deterministic split-K partials.
+//   C  mv_adam_kernel    fixed-order fold of the partials, Adam on the fp32 masters (torch's arithmetic order), and
+//                        the bf16 shadows (forward + transposed) kernel A reads next step.  Gradients are never
+//                        materialised per parameter tensor; a padded flat copy is kept for the data-parallel
+//                        all-reduce and for parity checks.
+//
+// Layers: 0 enc.0  1 enc.2  2 heads [mu ; logvar] (or the AE's single z head)  3 dec.0  4 dec.2  5 dec.4 / out.
+#include <string.h>
+#include "common.cuh"
+#include "tc05.cuh"
+
+namespace vc {
+
+constexpr int MV_H = 256;                       // hidden width the fused path supports
+constexpr int MV_THREADS = 320;                 // warp 0: TMA producers, warp 1: MMA issuer + TMEM, warps 2..9: workers
+constexpr uint32_t MV_ABLK = 128 * 128;         // one K-major A k-block: [128 rows][64 bf16]
+constexpr uint32_t MV_WSTAGE = 256 * 128;       // one weight k-block: [<=256 rows][64 bf16]
+constexpr int MV_XS = 3, MV_WS = 3;             // ring depths
+constexpr int MV_NBIAS = 1600;                  // b1 256 | b2 256 | b3 64 | b4 256 | b5 256 | b6 512
+constexpr int MV_MAXPH = 13;
+
+enum { EPI_NONE = 0, EPI_RELU_F, EPI_HEADS, EPI_LOSS_A, EPI_LOSS_B, EPI_RELU_B, EPI_DZ };
+enum { MAP_X = 0, MAP_W1, MAP_W2, MAP_W3, MAP_W4, MAP_W5, MAP_W6A, MAP_W6B, MAP_W6T, MAP_W5T, MAP_W4T, MAP_W3T,
+       MAP_W2T, MAP_COUNT };
+
+struct MvMaps { CUtensorMap m[MAP_COUNT]; };
+
+struct MvPhase {
+  int map, nkb, kb0, n, row0, a_x, tcol, acc_init, has_epi, wait_prev;
+};
+
+struct MvTensor { float* p; float* m; float* v; };
+struct MvParams { MvTensor W[7], b[7]; };   // 0 enc.0, 1 enc.2, 2 mu, 3 logvar, 4 dec.0, 5 dec.2, 6 dec.4
+
+struct MvRowsArgs {
+  int nph;
+  int B, Bp, ntiles, D, Cc, Z, NH, variational, N6a, N6b, nk1, nkd;
+  float gs2;        // 2 * d(loss)/d(sum of squared errors)
+  float ks;         // d(loss)/d(kl row sum)
+  const float* x; const float* c; const float* eps;
+  const float* bias[6];                   // fp32 biases of the 6 layers (heads: mu then logvar via bias3b)
+  const float* bias_lv;
+  __nv_bfloat16* A[6];                    // A2..A6 at [1..5] (A[0] = packed input, written by the pack kernel)
+  __nv_bfloat16* G[6];                    // G1..G6
+  float* mulv;                            // [Bp][64] fp32: mu | logvar of the row (re-read by the backward)
+  double* tile_part;                      // [ntiles][2]: sum of squared errors, sum of KL rows
+};
+
+// The GEMM phases of one tile, in issue order (canonical numbering for D > 256, where the output layer and the first
+// data-gradient GEMM are split in two because dxhat has more k-blocks than the activation buffer):
+//   0 enc.0   1 enc.2   2 heads   3 dec.0   4 dec.2   5 out[:, :256]   6 out[:, 256:]   7 dd2 from dxhat[:, :256]
+//   8 dd2 += dxhat[:, 256:]   9 dd1   10 dz   11 dh2   12 dh1
+// Computed arithmetically (no table): a dynamically indexed kernel-parameter array would be copied to local memory.
+__device__ __forceinline__ MvPhase mv_phase(int p, int nk1, int N6a, int N6b, int nkd) {
+  int c = p;
+  if (N6b == 0) {
+    if (p >= 6) c = p + 1;
+    if (c >= 8) c = c + 1;
+  }
+  MvPhase q;
+  q.kb0 = 0; q.row0 = 0; q.a_x = 0; q.tcol = 0; q.acc_init = 0; q.has_epi = 1; q.wait_prev = 1; q.n = 256; q.nkb = 4;
+  switch (c) {
+    case 0: q.map = MAP_W1; q.nkb = nk1; q.a_x = 1; break;
+    case 1: q.map = MAP_W2; break;
+    case 2: q.map = MAP_W3; q.n = 64; break;
+    case 3: q.map = MAP_W4; q.nkb = 1; break;
+    case 4: q.map = MAP_W5; break;
+    case 5: q.map = MAP_W6A; q.n = N6a; q.has_epi = N6b == 0; break;
+    case 6: q.map = MAP_W6B; q.n = N6b; q.row0 = 256; q.tcol = 256; q.wait_prev = 0; break;
+    case 7: q.map = MAP_W6T; q.nkb = N6b ? 4 : nkd; break;
+    case 8: q.map = MAP_W6T; q.nkb = nkd - 4; q.kb0 = 4; q.acc_init = 1; break;
+    case 9: q.map = MAP_W5T; break;
+    case 10: q.map = MAP_W4T; q.n = 64; break;
+    case 11: q.map = MAP_W3T; q.nkb = 1; break;
+    default: q.map = MAP_W2T; break;
+  }
+  return q;
+}
+
+__device__ __forceinline__ uint32_t mv_pack(float a, float b) {
+  __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
+  return *reinterpret_cast<uint32_t*>(&h);
+}
+
+// ------------------------------------------------------------------------------------------------ kernel P
+__global__ void mv_pack_kernel(const float* __restrict__ x, const float* __restrict__ c, int B, int Bp, int D, int Cc,
+                               int K1p, __nv_bfloat16* __restrict__ out, VcAdamDeviceStep* step, float b1, float b2) {
+  if (step && blockIdx.x == 0 && threadIdx.x == 0) {
+    const int t = step->step + 1;
+    step->step = t;
+    step->bias_corr1 = (float)(1.0 - pow((double)b1, (double)t));
+    step->bias_corr2 = (float)(1.0 - pow((double)b2, (double)t));
+  }
+  const int groups = K1p >> 3;
+  const int64_t total = (int64_t)Bp * groups;
+  for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (int64_t)gridDim.x * blockDim.x) {
+    const int row = (int)(e / groups), c0 = (int)(e - (int64_t)row * groups) * 8;
+    float v[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const int col = c0 + j;
+      float t = 0.f;
+      if (row < B) {
+        if (col < D) t = __ldg(x + (int64_t)row * D + col);
+        else if (col < D + Cc) t = __ldg(c + (int64_t)row * Cc + (col - D));
+      }
+      v[j] = t;
+    }
+    *reinterpret_cast<uint4*>(out + (int64_t)row * K1p + c0) =
+        make_uint4(mv_pack(v[0], v[1]), mv_pack(v[2], v[3]), mv_pack(v[4], v[5]), mv_pack(v[6], v[7]));
+  }
+}
+
+// ------------------------------------------------------------------------------------------------ kernel A
+struct MvSmem {
+  unsigned char* P;      // 4 k-blocks
+  unsigned char* XR;     // MV_XS k-blocks
+  unsigned char* WR;     // MV_WS stages
+  float* bias;
+  uint64_t* wfull; uint64_t* wempty; uint64_t* xfull; uint64_t* xempty;
+  uint64_t* acc_bar; uint64_t* a_bar;
+  uint32_t* tmem_slot;
+  double* red;           // [8][2]
+};
+
+__device__ __forceinline__ MvSmem mv_carve(unsigned char* raw) {
+  MvSmem s;
+  unsigned char* base = raw + ((1024u - (tma::s32(raw) & 1023u)) & 1023u);
+  s.P = base;
+  s.XR = s.P + 4 * MV_ABLK;
+  s.WR = s.XR + MV_XS * MV_ABLK;
+  s.bias = reinterpret_cast<float*>(s.WR + MV_WS * MV_WSTAGE);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(s.bias + MV_NBIAS);
+  s.wfull = bars; s.wempty = bars + MV_WS; s.xfull = bars + 2 * MV_WS; s.xempty = bars + 2 * MV_WS + MV_XS;
+  s.acc_bar = bars + 2 * MV_WS + 2 * MV_XS; s.a_bar = s.acc_bar + 1;
+  s.red = reinterpret_cast<double*>(s.a_bar + 1);
+  s.tmem_slot = reinterpret_cast<uint32_t*>(s.red + 16);
+  return s;
+}
+constexpr size_t MV_SMEM_BYTES = 1024 + 4 * MV_ABLK + MV_XS * MV_ABLK + MV_WS * MV_WSTAGE + MV_NBIAS * 4 +
+                                 (2 * MV_WS + 2 * MV_XS + 2) * 8 + 16 * 8 + 16;
+
+struct MvWorker {
+  const MvRowsArgs& a;
+  const MvSmem& s;
+  uint32_t tmem;       // accumulator base of this thread's lane quarter
+  int r, grow, hh, lane;
+  bool valid;
+  uint32_t acc_cnt;
+  uint32_t mask[4][4];
+  float sq, kl;
+
+  __device__ __forceinline__ void wait_acc() {
+    tma::mbar_wait_backoff(s.acc_bar, acc_cnt & 1u, 20);
+    ++acc_cnt;
+    tc05::fence_after();
+  }
+  // this thread's shared / tensor memory accesses of the phase are done: hand P and the accumulator back to the issuer
+  __device__ __forceinline__ void release() {
+    tc05::fence_before();
+    tma::fence_proxy_async();
+    __syncwarp();
+    if (lane == 0) tma::mbar_arrive(s.a_bar);
+  }
+  __device__ __forceinline__ void store_chunk(const float (&v)[32], int col, __nv_bfloat16* gout, int pitch, bool smem) {
+    uint32_t w[16];
+#pragma unroll
+    for (int j = 0; j < 16; ++j) w[j] = mv_pack(v[2 * j], v[2 * j + 1]);
+    if (smem) {
+      unsigned char* blk = s.P + (uint32_t)(col >> 6) * MV_ABLK;
+      const uint32_t cb = (uint32_t)(col & 63) >> 3;
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+        *reinterpret_cast<uint4*>(blk + tma::sw128((uint32_t)r, cb + i)) = make_uint4(w[4 * i], w[4 * i + 1], w[4 * i + 2], w[4 * i + 3]);
+    }
+    if (gout) {
+      uint4* g = reinterpret_cast<uint4*>(gout + (int64_t)grow * pitch + col);
+#pragma unroll
+      for (int i = 0; i < 4; ++i) g[i] = make_uint4(w[4 * i], w[4 * i + 1], w[4 * i + 2], w[4 * i + 3]);
+    }
+  }
+
+  template <int SLOT>
+  __device__ __forceinline__ void relu_fwd(int bias_off, __nv_bfloat16* aout) {
+    wait_acc();
+#pragma unroll 1
+    for (int cc = 0; cc < 4; ++cc) {
+      const int col = hh * 128 + cc * 32;
+      float v[32];
+      tc05::ld_32x32(tmem + col, v);
+      tc05::ld_wait();
+      uint32_t mk = 0;
+      const float4* b4 = reinterpret_cast<const float4*>(s.bias + bias_off + col);   // warp-uniform: broadcast reads
+#pragma unroll
+      for (int j4 = 0; j4 < 8; ++j4) {
+        const float4 bb = b4[j4];
+        const float bj[4] = {bb.x, bb.y, bb.z, bb.w};
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          const int j = 4 * j4 + u;
+          const float t = v[j] + bj[u];
+          mk |= (t > 0.f ? 1u : 0u) << j;
+          v[j] = fmaxf(t, 0.f);
+        }
+      }
+      mask[SLOT][cc] = mk;
+      store_chunk(v, col, aout, MV_H, true);
+    }
+    release();
+  }
+
+  template <int SLOT>
+  __device__ __forceinline__ void relu_bwd(__nv_bfloat16* gout, bool smem) {
+    wait_acc();
+#pragma unroll 1
+    for (int cc = 0; cc < 4; ++cc) {
+      const int col = hh * 128 + cc * 32;
+      float v[32];
+      tc05::ld_32x32(tmem + col, v);
+      tc05::ld_wait();
+      const uint32_t mk = mask[SLOT][cc];
+#pragma unroll
+      for (int j = 0; j < 32; ++j) v[j] = ((mk >> j) & 1u) ? v[j] : 0.f;
+      store_chunk(v, col, gout, MV_H, smem);
+    }
+    release();
+  }
+
+  // reconstruction loss of one half of the output columns straight from the accumulators: sum (xhat - x)^2 and
+  // dxhat = gs2 * (xhat - x) as bf16 rows (the A operand of the first data-gradient GEMM, and G6 for kernel B)
+  __device__ __forceinline__ void loss_half(int half) {
+    wait_acc();
+    const int n = half ? a.N6b : a.N6a;
+    const int cbase = half ? 256 : 0;
+    const int nchunks = ((n + 63) >> 6) << 1;
+#pragma unroll 1
+    for (int cc = hh * 4; cc < hh * 4 + 4; ++cc) {
+      if (cc >= nchunks) break;
+      const int col = cc * 32;              // column inside the half (= inside P)
+      float v[32];
+      tc05::ld_32x32(tmem + cbase + col, v);
+      tc05::ld_wait();
+      const float* xr = a.x + (int64_t)grow * a.D + cbase + col;
+#pragma unroll
+      for (int j = 0; j < 32; ++j) {
+        const int gc = cbase + col + j;
+        float d = 0.f;
+        if (valid && gc < a.D) d = v[j] + s.bias[1088 + gc] - __ldg(xr + j);
+        sq = fmaf(d, d, sq);
+        v[j] = a.gs2 * d;
+      }
+      store_chunk(v, col, nullptr, 0, true);
+      {   // G6 rows have pitch 512 and absolute columns
+        uint32_t w[16];
+#pragma unroll
+        for (int j = 0; j < 16; ++j) w[j] = mv_pack(v[2 * j], v[2 * j + 1]);
+        uint4* g = reinterpret_cast<uint4*>(a.G[5] + (int64_t)grow * 512 + cbase + col);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) g[i] = make_uint4(w[4 * i], w[4 * i + 1], w[4 * i + 2], w[4 * i + 3]);
+      }
+    }
+    release();
+  }
+
+  // one bf16 element of row r into the activation buffer (k-block 0) and into a global row
+  __device__ __forceinline__ void put_elem(int col, float val, __nv_bfloat16* gout, int pitch) {
+    const __nv_bfloat16 h = __float2bfloat16_rn(val);
+    *reinterpret_cast<__nv_bfloat16*>(s.P + tma::sw128((uint32_t)r, (uint32_t)col >> 3) + ((uint32_t)col & 7u) * 2u) = h;
+    gout[(int64_t)grow * pitch + col] = h;
+  }
+
+  // heads: mu | logvar from the accumulator, z = mu + eps * exp(logvar / 2), KL row; [z | c | 0] is the decoder's input
+  template <int Z>
+  __device__ __forceinline__ void heads() {
+    wait_acc();
+    if (hh == 0) {
+      float h0[32];
+      float zlo[32];
+#pragma unroll
+      for (int j = 0; j < 32; ++j) zlo[j] = 0.f;
+      float* mv = a.mulv + (int64_t)grow * 64;
+      float klr = 0.f;
+      tc05::ld_32x32(tmem, h0);
+      tc05::ld_wait();
+      if (Z == 32) {          // mu in columns [0, 32), logvar in [32, 64)
+        float h1[32];
+        tc05::ld_32x32(tmem + 32, h1);
+        tc05::ld_wait();
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+          const float mu = h0[j] + s.bias[512 + j];
+          float zz = mu;
+          if (a.variational) {
+            const float lv = h1[j] + s.bias[512 + Z + j];
+            const float e = valid ? __ldg(a.eps + (int64_t)grow * Z + j) : 0.f;
+            zz = mu + e * expf(0.5f * lv);
+            klr += 1.f + lv - mu * mu - expf(lv);
+            mv[Z + j] = lv;
+          }
+          mv[j] = mu;
+          zlo[j] = zz;
+        }
+      } else {
+#pragma unroll
+        for (int j = 0; j < Z; ++j) {
+          const float mu = h0[j] + s.bias[512 + j];
+          float zz = mu;
+          if (a.variational) {
+            const float lv = h0[(Z + j) & 31] + s.bias[512 + Z + j];
+            const float e = valid ? __ldg(a.eps + (int64_t)grow * Z + j) : 0.f;
+            zz = mu + e * expf(0.5f * lv);
+            klr += 1.f + lv - mu * mu - expf(lv);
+            mv[Z + j] = lv;
+          }
+          mv[j] = mu;
+          zlo[j] = zz;
+        }
+      }
+      if (valid) kl += -0.5f * klr;
+      store_chunk(zlo, 0, a.A[3], 64, true);
+#pragma unroll
+      for (int j = 0; j < 32; ++j) zlo[j] = 0.f;
+      store_chunk(zlo, 32, a.A[3], 64, true);
+      // the conditioning vector follows z (19:110-115); Z + Cc <= 64
+      for (int j = 0; j < a.Cc; ++j) put_elem(Z + j, valid ? __ldg(a.c + (int64_t)grow * a.Cc + j) : 0.f, a.A[3], 64);
+    }
+    release();
+  }
+
+  // backward of the reparameterisation + KL (12:168-172 / 19:105-108,124-126): G3 = [dmu | dlogvar] (or dz for the AE)
+  template <int Z>
+  __device__ __forceinline__ void dz() {
+    wait_acc();
+    if (hh == 0) {
+      float d0[32];
+      tc05::ld_32x32(tmem, d0);
+      tc05::ld_wait();
+      float glo[32], ghi[32];
+#pragma unroll
+      for (int j = 0; j < 32; ++j) { glo[j] = 0.f; ghi[j] = 0.f; }
+      const float* mv = a.mulv + (int64_t)grow * 64;
+#pragma unroll
+      for (int j = 0; j < Z; ++j) {
+        const float dzj = d0[j];
+        if (a.variational) {
+          const float mu = mv[j], lv = mv[Z + j];
+          const float e = valid ? __ldg(a.eps + (int64_t)grow * Z + j) : 0.f;
+          const float dmu = valid ? dzj + a.ks * mu : 0.f;
+          const float dlv = valid ? dzj * e * 0.5f * expf(0.5f * lv) + a.ks * 0.5f * (expf(lv) - 1.f) : 0.f;
+          glo[j] = dmu;
+          if (Z + j < 32) glo[(Z + j) & 31] = dlv; else ghi[(Z + j) & 31] = dlv;
+        } else {
+          glo[j] = valid ? dzj : 0.f;
+        }
+      }
+      store_chunk(glo, 0, a.G[2], 128, true);
+      store_chunk(ghi, 32, a.G[2], 128, true);
+      // columns [64, 128) of G3 only pad the weight-gradient tile to 128 rows: keep them zero
+      uint4* gz = reinterpret_cast<uint4*>(a.G[2] + (int64_t)grow * 128 + 64);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) gz[i] = make_uint4(0u, 0u, 0u, 0u);
+    }
+    release();
+  }
+};
+
+template <int Z>
+__global__ void __launch_bounds__(MV_THREADS, 1)
+mv_rows_kernel(const MvRowsArgs a, const __grid_constant__ MvMaps maps) {
+  extern __shared__ unsigned char smem_raw[];
+  const MvSmem s = mv_carve(smem_raw);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < MAP_COUNT; ++i) tma::prefetch_map(&maps.m[i]);
+    for (int i = 0; i < MV_WS; ++i) { tma::mbar_init(&s.wfull[i], 1); tma::mbar_init(&s.wempty[i], 1); }
+    for (int i = 0; i < MV_XS; ++i) { tma::mbar_init(&s.xfull[i], 1); tma::mbar_init(&s.xempty[i], 1); }
+    tma::mbar_init(s.acc_bar, 1);
+    tma::mbar_init(s.a_bar, 8);
+    tma::mbar_fence_init();
+  }
+  // biases -> shared memory (zero padded): b1 @0, b2 @256, b3 @512 (mu | logvar), b4 @576, b5 @832, b6 @1088
+  for (int i = threadIdx.x; i < MV_NBIAS; i += MV_THREADS) {
+    float v = 0.f;
+    if (i < 256) v = a.bias[0][i];
+    else if (i < 512) v = a.bias[1][i - 256];
+    else if (i < 576) {
+      const int j = i - 512;
+      if (j < a.Z) v = a.bias[2][j];
+      else if (a.variational && j < 2 * a.Z) v = a.bias_lv[j - a.Z];
+    } else if (i < 832) v = a.bias[3][i - 576];
+    else if (i < 1088) v = a.bias[4][i - 832];
+    else if (i - 1088 < a.D) v = a.bias[5][i - 1088];
+    s.bias[i] = v;
+  }
+  if (warp == 1) tc05::tmem_alloc(s.tmem_slot, 512);
+  tc05::fence_before();
+  __syncthreads();
+  tc05::fence_after();
+  const uint32_t tmem_base = *s.tmem_slot;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      // ===================== weight producer: runs ahead of the issuer across phases and tiles =====================
+      uint32_t it = 0;
+      for (int tile = blockIdx.x; tile < a.ntiles; tile += gridDim.x)
+        for (int p = 0; p < a.nph; ++p) {
+          const MvPhase ph = mv_phase(p, a.nk1, a.N6a, a.N6b, a.nkd);
+          const uint32_t bytes = (uint32_t)ph.n * 128u;
+          for (int kb = 0; kb < ph.nkb; ++kb, ++it) {
+            const uint32_t st = it % MV_WS;
+            tma::mbar_wait(&s.wempty[st], ((it / MV_WS) & 1u) ^ 1u);
+            tma::mbar_expect_tx(&s.wfull[st], bytes);
+            tma::load_2d(s.WR + st * MV_WSTAGE, &maps.m[ph.map], &s.wfull[st], (ph.kb0 + kb) * 64, ph.row0);
+          }
+        }
+    } else if (lane == 1) {
+      // ===================== input producer: the next tile's rows arrive during this tile's backward ================
+      uint32_t it = 0;
+      for (int tile = blockIdx.x; tile < a.ntiles; tile += gridDim.x)
+        for (int kb = 0; kb < a.nk1; ++kb, ++it) {
+          const uint32_t st = it % MV_XS;
+          tma::mbar_wait(&s.xempty[st], ((it / MV_XS) & 1u) ^ 1u);
+          tma::mbar_expect_tx(&s.xfull[st], MV_ABLK);
+          tma::load_2d(s.XR + st * MV_ABLK, &maps.m[MAP_X], &s.xfull[st], kb * 64, tile * 128);
+        }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer =====================
+    if (lane == 0) {
+      uint32_t wit = 0, xit = 0, a_cnt = 0;
+      bool first = true;
+      for (int tile = blockIdx.x; tile < a.ntiles; tile += gridDim.x)
+        for (int p = 0; p < a.nph; ++p) {
+          const MvPhase ph = mv_phase(p, a.nk1, a.N6a, a.N6b, a.nkd);
+          if (ph.wait_prev && !first) {
+            tma::mbar_wait(s.a_bar, a_cnt & 1u);
+            ++a_cnt;
+            tc05::fence_after();
+          }
+          first = false;
+          const uint32_t idesc = tc05::idesc(tc05::kFmtBF16, 128, ph.n, 0, 0);
+          for (int kb = 0; kb < ph.nkb; ++kb, ++wit) {
+            const uint32_t st = wit % MV_WS;
+            uint32_t sa;
+            if (ph.a_x) {
+              const uint32_t xs = xit % MV_XS;
+              tma::mbar_wait(&s.xfull[xs], (xit / MV_XS) & 1u);
+              sa = tma::s32(s.XR + xs * MV_ABLK);
+            } else {
+              sa = tma::s32(s.P + (uint32_t)(ph.kb0 + kb) % 4u * MV_ABLK);
+            }
+            tma::mbar_wait(&s.wfull[st], (wit / MV_WS) & 1u);
+            tc05::fence_after();
+            const uint32_t sb = tma::s32(s.WR + st * MV_WSTAGE);
+#pragma unroll
+            for (int kk = 0; kk < 4; ++kk)
+              tc05::mma_bf16(tmem_base + ph.tcol, tc05::desc_k_sw128(sa + kk * 32), tc05::desc_k_sw128(sb + kk * 32), idesc,
+                             (uint32_t)((ph.acc_init | kb | kk) != 0));
+            tc05::commit(&s.wempty[st]);
+            if (ph.a_x) { tc05::commit(&s.xempty[xit % MV_XS]); ++xit; }
+          }
+          if (ph.has_epi) tc05::commit(s.acc_bar);
+        }
+    }
+  } else {
+    // ===================== workers: the epilogue of every phase =====================
+    MvWorker w{a, s};
+    const int q = warp & 3;
+    w.hh = (warp - 2) >> 2;
+    w.lane = lane;
+    w.r = q * 32 + lane;
+    w.tmem = tmem_base + ((uint32_t)(q * 32) << 16);
+    w.acc_cnt = 0;
+    for (int tile = blockIdx.x; tile < a.ntiles; tile += gridDim.x) {
+      w.grow = tile * 128 + w.r;
+      w.valid = w.grow < a.B;
+      w.sq = 0.f; w.kl = 0.f;
+      w.template relu_fwd<0>(0, a.A[1]);
+      w.template relu_fwd<1>(256, a.A[2]);
+      w.template heads<Z>();
+      w.template relu_fwd<2>(576, a.A[4]);
+      w.template relu_fwd<3>(832, a.A[5]);
+      w.loss_half(0);
+      if (a.N6b > 0) w.loss_half(1);
+      w.template relu_bwd<3>(a.G[4], true);
+      w.template relu_bwd<2>(a.G[3], true);
+      w.template dz<Z>();
+      w.template relu_bwd<1>(a.G[1], true);
+      w.template relu_bwd<0>(a.G[0], false);
+      // tile loss partials, fixed order: lanes -> warp (shuffle tree), 8 warps -> thread of warp 2
+      const double sqw = warp_sum((double)w.sq), klw = warp_sum((double)w.kl);
+      if (lane == 0) { s.red[2 * (warp - 2)] = sqw; s.red[2 * (warp - 2) + 1] = klw; }
+      asm volatile("bar.sync 1, 256;" ::: "memory");
+      if (warp == 2 && lane == 0) {
+        double t0 = 0.0, t1 = 0.0;
+        for (int i = 0; i < 8; ++i) { t0 += s.red[2 * i]; t1 += s.red[2 * i + 1]; }
+        a.tile_part[2 * tile] = t0;
+        a.tile_part[2 * tile + 1] = t1;
+      }
+      asm volatile("bar.sync 1, 256;" ::: "memory");
+    }
+  }
+
+  tc05::fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc05::fence_after();
+    tc05::tmem_dealloc(tmem_base, 512);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------ kernel B
+constexpr int MVW_THREADS = 192;                // warp 0: TMA, warp 1: MMA + TMEM, warps 2..5: epilogue
+constexpr int MVW_STAGES = 4;
+constexpr uint32_t MVW_BOX = 64 * 128;          // one [64 batch rows][64 features] box
+constexpr uint32_t MVW_STAGE = 2 * MVW_BOX + 4 * MVW_BOX;
+constexpr size_t MVW_SMEM_BYTES = 1024 + MVW_STAGES * MVW_STAGE + MVW_BOX + (2 * MVW_STAGES + 1) * 8 + 16;
+constexpr int MVW_MAXT = 16;
+
+struct MvwTile { int layer, m0, n0, n, part_off, ld, bias_off; };
+struct MvwMaps { CUtensorMap g[6], a[6]; };
+struct MvwArgs {
+  MvwTile t[MVW_MAXT];
+  int ntiles, nkb, kbs;          // batch k-blocks in total and per split
+  int64_t ptot, btot;            // elements of one partial copy (weights, biases)
+  float* part; float* bpart;
+  int variant;                   // descriptor experiment switch (0 = canonical)
+};
+
+__global__ void __launch_bounds__(MVW_THREADS, 1)
+mv_wgrad_kernel(const MvwArgs a, const __grid_constant__ MvwMaps maps) {
+  extern __shared__ unsigned char smem_raw[];
+  unsigned char* smem = smem_raw + ((1024u - (tma::s32(smem_raw) & 1023u)) & 1023u);
+  unsigned char* ones = smem + MVW_STAGES * MVW_STAGE;
+  uint64_t* full = reinterpret_cast<uint64_t*>(ones + MVW_BOX);
+  uint64_t* empty = full + MVW_STAGES;
+  uint64_t* accb = empty + MVW_STAGES;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(accb + 1);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const MvwTile t = a.t[blockIdx.x];
+  const int z = blockIdx.y;
+  const int kb0 = z * a.kbs, kb1 = min(a.nkb, kb0 + a.kbs);
+  const int nkb = max(kb1 - kb0, 0);
+  const int nbox = t.n >> 6;
+
+  if (threadIdx.x == 0) {
+    tma::prefetch_map(&maps.g[t.layer]);
+    tma::prefetch_map(&maps.a[t.layer]);
+    for (int i = 0; i < MVW_STAGES; ++i) { tma::mbar_init(&full[i], 1); tma::mbar_init(&empty[i], 1); }
+    tma::mbar_init(accb, 1);
+    tma::mbar_fence_init();
+  }
+  // ones tile, MN-major [64 k rows][64 n]: element (n = 0, k) = 1.0 -- column 0 of the extra N=16 MMA sums G over k
+  for (int i = threadIdx.x; i < (int)(MVW_BOX / 4); i += MVW_THREADS) reinterpret_cast<uint32_t*>(ones)[i] = 0u;
+  __syncthreads();
+  if (threadIdx.x < 64) {
+    const uint32_t k = threadIdx.x;
+    *reinterpret_cast<uint16_t*>(ones + k * 128u + ((0u ^ (k & 7u)) << 4)) = 0x3F80;
+  }
+  tma::fence_proxy_async();
+  if (warp == 1) tc05::tmem_alloc(tmem_slot, 512);
+  tc05::fence_before();
+  __syncthreads();
+  tc05::fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    if (lane == 0)
+      for (int it = 0; it < nkb; ++it) {
+        const int st = it % MVW_STAGES;
+        tma::mbar_wait(&empty[st], (((uint32_t)it / MVW_STAGES) & 1u) ^ 1u);
+        unsigned char* sa = smem + (size_t)st * MVW_STAGE;
+        tma::mbar_expect_tx(&full[st], (2 + nbox) * MVW_BOX);
+        const int row = (kb0 + it) * 64;
+        tma::load_2d(sa, &maps.g[t.layer], &full[st], t.m0, row);
+        tma::load_2d(sa + MVW_BOX, &maps.g[t.layer], &full[st], t.m0 + 64, row);
+        for (int b = 0; b < nbox; ++b) tma::load_2d(sa + (2 + b) * MVW_BOX, &maps.a[t.layer], &full[st], t.n0 + 64 * b, row);
+      }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      const uint32_t idesc = tc05::idesc(tc05::kFmtBF16, 128, t.n, 1, 1);
+      const uint32_t idesc1 = tc05::idesc(tc05::kFmtBF16, 128, 16, 1, 1);
+      const uint32_t so = tma::s32(ones);
+      for (int it = 0; it < nkb; ++it) {
+        const int st = it % MVW_STAGES;
+        tma::mbar_wait(&full[st], ((uint32_t)it / MVW_STAGES) & 1u);
+        tc05::fence_after();
+        const uint32_t sa = tma::s32(smem + (size_t)st * MVW_STAGE), sb = sa + 2 * MVW_BOX;
+#pragma unroll
+        for (int kk = 0; kk < 4; ++kk) {
+          uint64_t da, db, d1;
+          if (a.variant == 0) {
+            da = tc05::desc_mn_sw128(sa + kk * 2048, MVW_BOX);
+            db = tc05::desc_mn_sw128(sb + kk * 2048, MVW_BOX);
+            d1 = tc05::desc_mn_sw128(so + kk * 2048, MVW_BOX);
+          } else {   // LBO / SBO roles exchanged
+            da = tc05::desc_mn_sw128_x(sa + kk * 2048, MVW_BOX);
+            db = tc05::desc_mn_sw128_x(sb + kk * 2048, MVW_BOX);
+            d1 = tc05::desc_mn_sw128_x(so + kk * 2048, MVW_BOX);
+          }
+          tc05::mma_bf16(tmem_base, da, db, idesc, (uint32_t)((it | kk) != 0));
+          if (t.bias_off >= 0) tc05::mma_bf16(tmem_base + 256, da, d1, idesc1, (uint32_t)((it | kk) != 0));
+        }
+        tc05::commit(&empty[st]);
+      }
+      if (nkb > 0) tc05::commit(accb);
+    }
+  } else {
+    const int q = warp & 3;
+    const int m = q * 32 + lane;
+    if (nkb > 0) {
+      tma::mbar_wait_backoff(accb, 0, 64);
+      tc05::fence_after();
+    }
+    float* prow = a.part + (int64_t)z * a.ptot + t.part_off + (int64_t)m * t.ld;
+    for (int cc = 0; cc < (t.n >> 5); ++cc) {
+      float v[32];
+      if (nkb > 0) {
+        tc05::ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + cc * 32, v);
+        tc05::ld_wait();
+      } else {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) v[j] = 0.f;
+      }
+#pragma unroll
+      for (int j = 0; j < 8; ++j)
+        reinterpret_cast<float4*>(prow + cc * 32)[j] = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+    }
+    if (t.bias_off >= 0) {
+      float v[32];
+      if (nkb > 0) {
+        tc05::ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + 256, v);
+        tc05::ld_wait();
+      } else {
+        v[0] = 0.f;
+      }
+      a.bpart[(int64_t)z * a.btot + t.bias_off + m] = v[0];
+    }
+  }
+  tc05::fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc05::fence_after();
+    tc05::tmem_dealloc(tmem_base, 512);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------ kernel C
+struct MvLayerDesc {
+  int nout, kin, kp, mpad;       // true dims, padded in-dim (= pitch of partial rows and of the forward shadow), padded rows
+  int split;                     // rows >= split belong to the second parameter tensor (heads: logvar), else nout
+  int poff, boff;                // offsets in the padded flat layouts
+  int tpitch;                    // pitch of the transposed shadow (0: none)
+  int p0, p1;                    // parameter indices (MvParams) of the two tensors
+  __nv_bfloat16* wp; __nv_bfloat16* wt;
+};
+struct MvAdamArgs {
+  MvLayerDesc L[6];
+  MvParams prm;
+  const float* part; const float* bpart; int nsplit; int64_t ptot, btot;
+  float* gflat; float* gbflat;   // reduced gradients, padded flat layout
+  float gscale;                  // data-parallel weight B_local / B_global applied in the fold
+  int do_fold, do_adam, do_shadow;
+  float lr, b1, b2, eps, bc1, bc2;
+  const VcAdamDeviceStep* step;
+  // loss
+  const double* tile_part; int ntiles; int B, D, Z, mode, variational; float beta; float* out3;
+};
+
+__device__ __forceinline__ void mv_adam1(float& p, float& m, float& v, float g, float b1, float b2, float eps,
+                                         float step_size, float inv_sqrt_bc2) {
+  m = b1 * m + (1.f - b1) * g;
+  v = b2 * v + (1.f - b2) * g * g;
+  p -= step_size * (m / (sqrtf(v) * inv_sqrt_bc2 + eps));
+}
+
+__global__ void __launch_bounds__(256) mv_adam_kernel(const MvAdamArgs a) {
+  const MvLayerDesc L = a.L[blockIdx.y];
+  float bc1 = a.bc1, bc2 = a.bc2;
+  if (a.step) { bc1 = a.step->bias_corr1; bc2 = a.step->bias_corr2; }
+  const float step_size = a.lr / bc1, inv_sqrt_bc2 = 1.f / sqrtf(bc2);
+  const int total = L.mpad * L.kp;
+  for (int e = blockIdx.x * blockDim.x + threadIdx.x; e < total; e += gridDim.x * blockDim.x) {
+    const int o = e / L.kp, i = e - o * L.kp;
+    float g;
+    if (a.do_fold) {
+      g = 0.f;
+      for (int zz = 0; zz < a.nsplit; ++zz) g += a.part[(int64_t)zz * a.ptot + L.poff + e];
+      g *= a.gscale;
+      a.gflat[L.poff + e] = g;
+    } else {
+      g = a.gflat[L.poff + e];
+    }
+    if (o >= L.nout || i >= L.kin) continue;
+    const bool second = o >= L.split;
+    const MvTensor T = a.prm.W[second ? L.p1 : L.p0];
+    const int64_t idx = (int64_t)(second ? o - L.split : o) * L.kin + i;
+    float p = T.p[idx];
+    if (a.do_adam) {
+      float m = T.m[idx], v = T.v[idx];
+      mv_adam1(p, m, v, g, a.b1, a.b2, a.eps, step_size, inv_sqrt_bc2);
+      T.p[idx] = p; T.m[idx] = m; T.v[idx] = v;
+    }
+    if (a.do_shadow) {
+      const __nv_bfloat16 h = __float2bfloat16_rn(p);
+      L.wp[(int64_t)o * L.kp + i] = h;
+      if (L.wt) L.wt[(int64_t)i * L.tpitch + o] = h;
+    }
+  }
+  if (blockIdx.x == 0)
+    for (int o = threadIdx.x; o < L.mpad; o += blockDim.x) {
+      float g;
+      if (a.do_fold) {
+        g = 0.f;
+        for (int zz = 0; zz < a.nsplit; ++zz) g += a.bpart[(int64_t)zz * a.btot + L.boff + o];
+        g *= a.gscale;
+        a.gbflat[L.boff + o] = g;
+      } else {
+        g = a.gbflat[L.boff + o];
+      }
+      if (o >= L.nout || !a.do_adam) continue;
+      const bool second = o >= L.split;
+      const MvTensor T = a.prm.b[second ? L.p1 : L.p0];
+      const int idx = second ? o - L.split : o;
+      float p = T.p[idx], m = T.m[idx], v = T.v[idx];
+      mv_adam1(p, m, v, g, a.b1, a.b2, a.eps, step_size, inv_sqrt_bc2);
+      T.p[idx] = p; T.m[idx] = m; T.v[idx] = v;
+    }
+  if (blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0 && a.out3) {
+    double sq = 0.0, kl = 0.0;
+    for (int t = 0; t < a.ntiles; ++t) { sq += a.tile_part[2 * t]; kl += a.tile_part[2 * t + 1]; }
+    double recon, klm;
+    if (a.mode == VC_LOSS_MEAN_MEAN) { recon = sq / ((double)a.B * a.D); klm = kl / ((double)a.B * a.Z); }
+    else { recon = sq / (double)a.B; klm = kl / (double)a.B; }
+    if (!a.variational) klm = 0.0;
+    a.out3[0] = (float)(recon + (double)a.beta * klm);
+    a.out3[1] = (float)recon;
+    a.out3[2] = (float)klm;
+  }
+}
+
+// ------------------------------------------------------------------------------------------------ host
+struct MvPlan {
+  bool ok;
+  int D, Cc, Z, NH, variational, mode;
+  int K1, K1p, nk1, N6a, N6b, B, Bp, ntiles;
+  // workspace offsets (bytes)
+  size_t o_wp[6], o_wt[6], o_A[6], o_G[6], o_mulv, o_tile, o_part, o_bpart, o_gflat, o_gbflat, total;
+  size_t persist_bytes;          // shadows live in [0, persist_bytes)
+  int kin[6], nout[6], kp[6], mpad[6], poff[6], boff[6], apitch[6], gpitch[6], tpitch[6];
+  int64_t ptot, btot;
+  int nsplit, nkbB, kbs;
+  MvwTile tiles[MVW_MAXT];
+  int nwt;
+};
+
+static inline size_t mv_al(size_t x) { return (x + 1023) & ~(size_t)1023; }
+
+static MvPlan mv_plan(const VcMlpVaeDesc* d, int B) {
+  MvPlan p;
+  memset(&p, 0, sizeof(p));
+  if (!d) return p;
+  p.D = d->input_dim; p.Cc = d->cond_dim; p.Z = d->latent; p.variational = d->variational ? 1 : 0; p.mode = d->loss_mode;
+  p.NH = p.variational ? 2 * p.Z : p.Z;
+  p.K1 = p.D + p.Cc;
+  p.K1p = (p.K1 + 63) / 64 * 64;
+  p.nk1 = p.K1p / 64;
+  if (d->hidden != MV_H || !(p.Z == 8 || p.Z == 16 || p.Z == 32) || p.Cc < 0 || p.Z + p.Cc > 64 || p.D < 16 ||
+      p.D > 512 || p.K1p > 512 || B < 1)
+    return p;
+  p.N6a = p.D >= 256 ? 256 : (p.D + 15) / 16 * 16;
+  p.N6b = p.D > 256 ? (p.D - 256 + 15) / 16 * 16 : 0;
+  p.B = B; p.Bp = (B + 127) / 128 * 128; p.ntiles = p.Bp / 128;
+  const int kin[6] = {p.K1, 256, 256, p.Z + p.Cc, 256, 256};
+  const int nout[6] = {256, 256, p.NH, 256, 256, p.D};
+  const int kp[6] = {p.K1p, 256, 256, 64, 256, 256};
+  const int mpad[6] = {256, 256, 128, 256, 256, (p.D + 127) / 128 * 128};
+  const int wrows[6] = {256, 256, 64, 256, 256, 512};          // rows of the forward shadow
+  const int tpitch[6] = {0, 256, 64, 256, 256, 512};            // transposed shadow [kp][tpitch]
+  const int apitch[6] = {p.K1p, 256, 256, 64, 256, 256};
+  const int gpitch[6] = {256, 256, 128, 256, 256, 512};
+  size_t o = 0;
+  int poff = 0, boff = 0;
+  for (int l = 0; l < 6; ++l) {
+    p.kin[l] = kin[l]; p.nout[l] = nout[l]; p.kp[l] = kp[l]; p.mpad[l] = mpad[l]; p.tpitch[l] = tpitch[l];
+    p.apitch[l] = apitch[l]; p.gpitch[l] = gpitch[l];
+    p.poff[l] = poff; poff += mpad[l] * kp[l];
+    p.boff[l] = boff; boff += mpad[l];
+    p.o_wp[l] = o; o = mv_al(o + (size_t)wrows[l] * kp[l] * 2);
+    p.o_wt[l] = o; if (tpitch[l]) o = mv_al(o + (size_t)kp[l] * tpitch[l] * 2);
+  }
+  p.persist_bytes = o;
+  p.ptot = poff; p.btot = boff;
+  for (int l = 0; l < 6; ++l) { p.o_A[l] = o; o = mv_al(o + (size_t)p.Bp * apitch[l] * 2); }
+  for (int l = 0; l < 6; ++l) { p.o_G[l] = o; o = mv_al(o + (size_t)p.Bp * gpitch[l] * 2); }
+  p.o_mulv = o; o = mv_al(o + (size_t)p.Bp * 64 * 4);
+  p.o_tile = o; o = mv_al(o + (size_t)p.ntiles * 16);
+  // wgrad tiles
+  int nt = 0;
+  for (int l = 0; l < 6; ++l)
+    for (int m0 = 0; m0 < mpad[l]; m0 += 128)
+      for (int n0 = 0; n0 < kp[l]; n0 += 256) {
+        MvwTile& t = p.tiles[nt++];
+        t.layer = l; t.m0 = m0; t.n0 = n0; t.n = kp[l] - n0 < 256 ? kp[l] - n0 : 256;
+        t.ld = kp[l]; t.part_off = p.poff[l] + m0 * kp[l] + n0; t.bias_off = n0 == 0 ? p.boff[l] + m0 : -1;
+      }
+  p.nwt = nt;
+  p.nkbB = p.Bp / 64;
+  int ns = sm_count() / nt;
+  if (ns < 1) ns = 1;
+  if (ns > p.nkbB) ns = p.nkbB;
+  p.kbs = (p.nkbB + ns - 1) / ns;
+  p.nsplit = (p.nkbB + p.kbs - 1) / p.kbs;
+  p.o_part = o; o = mv_al(o + (size_t)p.nsplit * p.ptot * 4);
+  p.o_bpart = o; o = mv_al(o + (size_t)p.nsplit * p.btot * 4);
+  p.o_gflat = o; o += (size_t)p.ptot * 4;          // weights then biases: ONE contiguous block (all-reduced as such)
+  p.o_gbflat = o; o = mv_al(o + (size_t)p.btot * 4);
+  p.total = o + 1024;
+  p.ok = nt <= MVW_MAXT;
+  return p;
+}
+
+static unsigned char* mv_base(void* ws) {
+  return reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(ws) + 1023) & ~(uintptr_t)1023);
+}
+
+static int mv_map2d(CUtensorMap* m, const void* base, uint64_t inner, uint64_t rows, uint64_t pitch_elems, uint32_t box_rows) {
+  const uint64_t dims[2] = {inner, rows};
+  const uint64_t strides[1] = {pitch_elems * 2};
+  const uint32_t box[2] = {64, box_rows};
+  return tma::make_map(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, base, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B);
+}
+
+static void mv_fill_adam_args(MvAdamArgs& c, const MvPlan& p, const VcMlpVaeParams* prm, unsigned char* w) {
+  memset(&c, 0, sizeof(c));
+  for (int l = 0; l < 6; ++l) {
+    MvLayerDesc& L = c.L[l];
+    L.nout = p.nout[l]; L.kin = p.kin[l]; L.kp = p.kp[l]; L.mpad = p.mpad[l];
+    L.split = (l == 2 && p.variational) ? p.Z : p.nout[l];
+    L.poff = p.poff[l]; L.boff = p.boff[l]; L.tpitch = p.tpitch[l];
+    L.p0 = l < 2 ? l : (l == 2 ? 2 : l + 1);
+    L.p1 = l == 2 ? 3 : L.p0;
+    L.wp = reinterpret_cast<__nv_bfloat16*>(w + p.o_wp[l]);
+    L.wt = p.tpitch[l] ? reinterpret_cast<__nv_bfloat16*>(w + p.o_wt[l]) : nullptr;
+  }
+  for (int i = 0; i < 7; ++i) {
+    c.prm.W[i].p = prm->W[i].p; c.prm.W[i].m = prm->W[i].m; c.prm.W[i].v = prm->W[i].v;
+    c.prm.b[i].p = prm->b[i].p; c.prm.b[i].m = prm->b[i].m; c.prm.b[i].v = prm->b[i].v;
+  }
+  c.ptot = p.ptot; c.btot = p.btot;
+  c.gflat = reinterpret_cast<float*>(w + p.o_gflat);
+  c.gbflat = reinterpret_cast<float*>(w + p.o_gbflat);
+  c.part = reinterpret_cast<float*>(w + p.o_part);
+  c.bpart = reinterpret_cast<float*>(w + p.o_bpart);
+  c.nsplit = p.nsplit;
+  c.gscale = 1.f;
+}
+
+}  // namespace vc
+
+using namespace vc;
+
+extern "C" int vc_mlpvae_supported(const VcMlpVaeDesc* d) { return mv_plan(d, 128).ok ? 1 : 0; }
+
+extern "C" size_t vc_mlpvae_workspace_bytes(const VcMlpVaeDesc* d, int B) {
+  const MvPlan p = mv_plan(d, B);
+  return p.ok ? p.total : 0;
+}
+
+extern "C" int vc_mlpvae_grad_layout(const VcMlpVaeDesc* d, int B, int64_t* out) {
+  const MvPlan p = mv_plan(d, B);
+  VC_REQUIRE(p.ok && out, VC_ERR_UNSUPPORTED, "vc_mlpvae_grad_layout: unsupported model");
+  // out[0] = byte offset of the flat gradient block in the workspace, out[1] = its element count (weights then biases),
+  // then per layer: weight offset (elements), pitch, bias offset (elements, relative to the block start)
+  out[0] = (int64_t)p.o_gflat;   // relative to the workspace pointer rounded up to 1024 bytes
+  out[1] = (int64_t)((p.o_gbflat - p.o_gflat) / 4 + p.btot);
+  for (int l = 0; l < 6; ++l) {
+    out[2 + 3 * l] = p.poff[l];
+    out[3 + 3 * l] = p.kp[l];
+    out[4 + 3 * l] = (int64_t)((p.o_gbflat - p.o_gflat) / 4) + p.boff[l];
+  }
+  return VC_OK;
+}
+
+extern "C" int vc_mlpvae_prepare(const VcMlpVaeDesc* d, const VcMlpVaeParams* prm, int B, void* workspace,
+                                 size_t workspace_bytes, void* stream) {
+  const MvPlan p = mv_plan(d, B);
+  VC_REQUIRE(p.ok && prm, VC_ERR_UNSUPPORTED, "vc_mlpvae_prepare: unsupported model");
+  VC_REQUIRE(workspace && workspace_bytes >= p.total, VC_ERR_WORKSPACE, "vc_mlpvae_prepare: workspace too small");
+  unsigned char* w = mv_base(workspace);
+  cudaStream_t s = as_stream(stream);
+  VC_CUDA(cudaMemsetAsync(w, 0, p.o_part, s));     // shadows (zero padding), activation / gradient rows, scratch
+  MvAdamArgs c;
+  mv_fill_adam_args(c, p, prm, w);
+  c.do_fold = 0; c.do_adam = 0; c.do_shadow = 1;
+  VC_CUDA(cudaMemsetAsync(w + p.o_gflat, 0, (size_t)p.ptot * 4, s));
+  VC_CUDA(cudaMemsetAsync(w + p.o_gbflat, 0, (size_t)p.btot * 4, s));
+  mv_adam_kernel<<<dim3(32, 6), 256, 0, s>>>(c);
+  VC_LAUNCH_CHECK();
+  return VC_OK;
+}
+
+extern "C" int vc_mlpvae_step(const VcMlpVaeDesc* d, const VcMlpVaeParams* prm, const float* x, const float* c,
+                              const float* eps, int B, float grad_weight, int phases, float lr, float beta1, float beta2,
+                              float adam_eps, float bias_corr1, float bias_corr2, VcAdamDeviceStep* step_state,
+                              float* out3, void* workspace, size_t workspace_bytes, int variant, void* stream) {
+  const MvPlan p = mv_plan(d, B);
+  VC_REQUIRE(p.ok && prm && x, VC_ERR_UNSUPPORTED, "vc_mlpvae_step: unsupported model (hidden must be 256, latent in "
+             "{8,16,32}, input_dim + cond_dim <= 512, latent + cond_dim <= 64)");
+  VC_REQUIRE((p.Cc == 0 || c) && (!p.variational || eps), VC_ERR_BAD_ARG, "vc_mlpvae_step: missing c or eps");
+  VC_REQUIRE(workspace && workspace_bytes >= p.total, VC_ERR_WORKSPACE, "vc_mlpvae_step: workspace too small");
+  unsigned char* w = mv_base(workspace);
+  cudaStream_t s = as_stream(stream);
+  auto bf = [&](size_t off) { return reinterpret_cast<__nv_bfloat16*>(w + off); };
+
+  if (phases & 1) {
+    // ---- P: pack the input rows (and tick the device step counter)
+    {
+      const int64_t total = (int64_t)p.Bp * (p.K1p / 8);
+      int blocks = (int)((total + 255) / 256);
+      if (blocks > 8 * sm_count()) blocks = 8 * sm_count();
+      mv_pack_kernel<<<blocks, 256, 0, s>>>(x, c, B, p.Bp, p.D, p.Cc, p.K1p, bf(p.o_A[0]), step_state, beta1, beta2);
+      VC_LAUNCH_CHECK();
+    }
+    // ---- A: forward + loss + data gradients per 128-row tile
+    MvRowsArgs a;
+    memset(&a, 0, sizeof(a));
+    MvMaps maps;
+    int rc = VC_OK;
+    auto mk = [&](int id, size_t off, uint64_t inner, uint64_t rows, uint64_t pitch, uint32_t box_rows) {
+      if (rc == VC_OK) rc = mv_map2d(&maps.m[id], w + off, inner, rows, pitch, box_rows);
+    };
+    mk(MAP_X, p.o_A[0], p.K1p, p.Bp, p.K1p, 128);
+    mk(MAP_W1, p.o_wp[0], p.K1p, 256, p.K1p, 256);
+    mk(MAP_W2, p.o_wp[1], 256, 256, 256, 256);
+    mk(MAP_W3, p.o_wp[2], 256, 64, 256, 64);
+    mk(MAP_W4, p.o_wp[3], 64, 256, 64, 256);
+    mk(MAP_W5, p.o_wp[4], 256, 256, 256, 256);
+    mk(MAP_W6A, p.o_wp[5], 256, 512, 256, p.N6a);
+    mk(MAP_W6B, p.o_wp[5], 256, 512, 256, p.N6b ? p.N6b : 16);
+    mk(MAP_W6T, p.o_wt[5], 512, 256, 512, 256);
+    mk(MAP_W5T, p.o_wt[4], 256, 256, 256, 256);
+    mk(MAP_W4T, p.o_wt[3], 256, 64, 256, 64);
+    mk(MAP_W3T, p.o_wt[2], 64, 256, 64, 256);
+    mk(MAP_W2T, p.o_wt[1], 256, 256, 256, 256);
+    if (rc != VC_OK) return rc;
+    const int nkd = (p.D + 63) / 64;                 // k-blocks of dxhat
+    a.nkd = nkd;
+    const int np = p.N6b ? 13 : 11;
+    a.nph = np;
+    a.B = B; a.Bp = p.Bp; a.ntiles = p.ntiles; a.D = p.D; a.Cc = p.Cc; a.Z = p.Z; a.NH = p.NH;
+    a.variational = p.variational; a.N6a = p.N6a; a.N6b = p.N6b; a.nk1 = p.nk1;
+    const double gs = p.mode == VC_LOSS_MEAN_MEAN ? 1.0 / ((double)B * p.D) : 1.0 / (double)B;
+    a.gs2 = (float)(2.0 * gs);
+    a.ks = p.variational ? (float)((double)d->beta * (p.mode == VC_LOSS_MEAN_MEAN ? 1.0 / ((double)B * p.Z) : 1.0 / (double)B)) : 0.f;
+    a.x = x; a.c = c; a.eps = eps;
+    a.bias[0] = prm->b[0].p; a.bias[1] = prm->b[1].p; a.bias[2] = prm->b[2].p; a.bias_lv = prm->b[3].p;
+    a.bias[3] = prm->b[4].p; a.bias[4] = prm->b[5].p; a.bias[5] = prm->b[6].p;
+    for (int l = 0; l < 6; ++l) { a.A[l] = bf(p.o_A[l]); a.G[l] = bf(p.o_G[l]); }
+    a.mulv = reinterpret_cast<float*>(w + p.o_mulv);
+    a.tile_part = reinterpret_cast<double*>(w + p.o_tile);
+    int grid = p.ntiles < sm_count() ? p.ntiles : sm_count();
+#define MV_LAUNCH_ROWS(ZZ)                                                                                           \
+  do {                                                                                                               \
+    static bool attr_##ZZ = false;                                                                                   \
+    if (!attr_##ZZ) {                                                                                                \
+      VC_CUDA(cudaFuncSetAttribute(mv_rows_kernel<ZZ>, cudaFuncAttributeMaxDynamicSharedMemorySize,                  \
+                                   (int)MV_SMEM_BYTES));                                                             \
+      attr_##ZZ = true;                                                                                              \
+    }                                                                                                                \
+    mv_rows_kernel<ZZ><<<grid, MV_THREADS, MV_SMEM_BYTES, s>>>(a, maps);                                             \
+  } while (0)
+    if (p.Z == 8) MV_LAUNCH_ROWS(8);
+    else if (p.Z == 16) MV_LAUNCH_ROWS(16);
+    else MV_LAUNCH_ROWS(32);
+#undef MV_LAUNCH_ROWS
+    VC_LAUNCH_CHECK();
+
+    // ---- B: weight / bias gradients, split over the batch
+    MvwArgs b;
+    memset(&b, 0, sizeof(b));
+    MvwMaps wm;
+    for (int l = 0; l < 6 && rc == VC_OK; ++l) {
+      rc = mv_map2d(&wm.g[l], w + p.o_G[l], p.gpitch[l], p.Bp, p.gpitch[l], 64);
+      if (rc == VC_OK) rc = mv_map2d(&wm.a[l], w + p.o_A[l], p.apitch[l], p.Bp, p.apitch[l], 64);
+    }
+    if (rc != VC_OK) return rc;
+    for (int i = 0; i < p.nwt; ++i) b.t[i] = p.tiles[i];
+    b.ntiles = p.nwt; b.nkb = p.nkbB; b.kbs = p.kbs; b.ptot = p.ptot; b.btot = p.btot;
+    b.part = reinterpret_cast<float*>(w + p.o_part);
+    b.bpart = reinterpret_cast<float*>(w + p.o_bpart);
+    b.variant = variant;
+    static bool attr_w = false;
+    if (!attr_w) {
+      VC_CUDA(cudaFuncSetAttribute(mv_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)MVW_SMEM_BYTES));
+      attr_w = true;
+    }
+    mv_wgrad_kernel<<<dim3(p.nwt, p.nsplit), MVW_THREADS, MVW_SMEM_BYTES, s>>>(b, wm);
+    VC_LAUNCH_CHECK();
+  }
+  // ---- C: fold (phase 2), Adam + shadows (phase 4); a data-parallel caller all-reduces the flat gradients in between
+  if (phases & 6) {
+    MvAdamArgs ca;
+    mv_fill_adam_args(ca, p, prm, w);
+    ca.do_fold = (phases & 2) ? 1 : 0;
+    ca.do_adam = (phases & 4) ? 1 : 0;
+    ca.do_shadow = ca.do_adam;
+    ca.gscale = grad_weight;
+    ca.lr = lr; ca.b1 = beta1; ca.b2 = beta2; ca.eps = adam_eps; ca.bc1 = bias_corr1; ca.bc2 = bias_corr2;
+    ca.step = step_state;
+    ca.tile_part = reinterpret_cast<const double*>(w + p.o_tile);
+    ca.ntiles = p.ntiles; ca.B = B; ca.D = p.D; ca.Z = p.Z; ca.mode = p.mode; ca.variational = p.variational;
+    ca.beta = d->beta;
+    ca.out3 = (phases & 2) ? out3 : nullptr;
+    mv_adam_kernel<<<dim3(32, 6), 256, 0, s>>>(ca);
+    VC_LAUNCH_CHECK();
+  }
+  return VC_OK;
+}

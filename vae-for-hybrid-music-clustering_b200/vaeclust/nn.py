@@ -4,7 +4,8 @@ Same class names, constructor signatures, attribute names, return tuples and sta
   scripts/12_train_conv_multimodal_vae_medium.py:83-190   (AudioEncoder, LyricsProjector, AudioDecoder,
                                                             ConvMultiModalVAE, kl_div)
   scripts/19_train_beta_cvae_multimodal_hard.py:64-132     (MLPVAE, kl_divergence, make_onehot)
-  scripts/06_train_basic_vae_easy.py:145-188               (MLPVAE -> EasyMLPVAE here, vae_loss)
+  scripts/06_train_basic_vae_easy.py:145-188               (MLPVAE -> EasyMLPVAE here / vaeclust.nn06.MLPVAE, vae_loss)
+  scripts/22_compare_with_baselines_hard.py:66-87          (AE)
 The torch.nn.Linear / Conv2d / ConvTranspose2d submodules are kept ONLY as parameter containers: constructing them
 consumes the RNG exactly like the reference (identical initialisation under one seed) and yields the same
 state_dict keys, so checkpoints interchange in both directions.  Their own forward() is never called; the layers
@@ -220,6 +221,26 @@ class EasyMLPVAE(nn.Module):
     def forward(self, x):
         mu, logvar = self.encode(x)
         return self.decode(self.reparameterize(mu, logvar)), mu, logvar
+
+
+# ------------------------------------------------------------------------------------------------ script 22
+class AE(nn.Module):
+    """22:66-87: the plain auto-encoder baseline.  forward(x) -> (x_hat, z)."""
+
+    def __init__(self, in_dim: int, z_dim: int = 16, hidden: int = 256):
+        super().__init__()
+        self.enc = nn.Sequential(nn.Linear(in_dim, hidden), nn.ReLU(), nn.Linear(hidden, hidden), nn.ReLU(),
+                                 nn.Linear(hidden, z_dim))
+        self.dec = nn.Sequential(nn.Linear(z_dim, hidden), nn.ReLU(), nn.Linear(hidden, hidden), nn.ReLU(),
+                                 nn.Linear(hidden, in_dim))
+
+    def encode(self, x):
+        """(z, None): the pair shape of the VAEs' encode(), so the latent export treats all models alike."""
+        return _lin(self.enc[4], _lin(self.enc[2], _lin(self.enc[0], x, relu=True), relu=True)), None
+
+    def forward(self, x):
+        z, _ = self.encode(x)
+        return _lin(self.dec[4], _lin(self.dec[2], _lin(self.dec[0], z, relu=True), relu=True)), z
 
 
 def vae_loss(xhat, x, mu, logvar, beta: float) -> Tuple[torch.Tensor, Dict[str, float]]:

@@ -38,8 +38,21 @@ def batches(n: int, batch_size: int, shuffle: bool = True):
         yield order[s: s + batch_size]
 
 
+def make_step(model, kind: str, lr: float, beta: float, group=None, capturable: bool = False, fused: str = "auto"):
+    """The optimisation step for `model`: the fused four-launch step of vaeclust.fused (vc_mlpvae_step) for the MLP
+    models when the dense precision is "bf16" and the shape qualifies, else the per-layer VAEStep.
+    fused: "auto" | "never" | "always" (raise if the fused kernel cannot run this model)."""
+    from . import fused as vfused
+    want = fused != "never" and kind in ("mlp19", "mlp06", "ae22") and (ops.PRECISION == "bf16" or fused == "always")
+    if want and next(model.parameters()).is_cuda and vfused.supported(model, kind):
+        return vfused.FusedMLPStep(model, kind, lr, beta, group=group, capturable=capturable)
+    if fused == "always":
+        raise ValueError(f"make_step: the fused step does not support this {kind} model")
+    return VAEStep(model, kind, lr, beta, group=group, capturable=capturable)
+
+
 class VAEStep:
-    """One optimisation step for any of the three models.  kind: "conv12" | "mlp19" | "mlp06".
+    """One optimisation step for any of the models.  kind: "conv12" | "mlp19" | "mlp06" | "ae22".
     Under a process group each rank passes ITS slice of the global batch; gradients are combined with weights
     B_local/B_global so the result equals the reference's single-process batch mean."""
 
@@ -66,6 +79,15 @@ class VAEStep:
         elif self.kind == "mlp19":
             c = extra[0] if extra else None
             mu, lv = m.encode(x, c)
+        elif self.kind == "ae22":   # 22:150-156: plain MSE, no sampling, no KL
+            xhat, _z = m(x)
+            klr = torch.zeros(x.shape[0], dtype=torch.float32, device=x.device)
+            loss, stats = ops.vae_loss(xhat, x, klr, 0.0, self.mode, 1, unit_grad=True)
+            loss.backward()
+            if self.multi:
+                self.sync.finish()
+            self.opt.step()
+            return stats
         else:
             mu, lv = m.encode(x)
         if eps is None:
@@ -95,8 +117,8 @@ class GraphedVAEStep:
     the overlapped NCCL gradient exchange is captured with the step (set TORCH_NCCL_ASYNC_ERROR_HANDLING=0 before
     init_process_group, as for any NCCL-in-graph capture); `global_batch` is fixed at capture."""
 
-    def __init__(self, model, kind: str, lr: float, beta: float, warmup: int = 2, group=None):
-        self.step = VAEStep(model, kind, lr, beta, group=group, capturable=True)
+    def __init__(self, model, kind: str, lr: float, beta: float, warmup: int = 2, group=None, fused: str = "auto"):
+        self.step = make_step(model, kind, lr, beta, group=group, capturable=True, fused=fused)
         self.warmup, self.calls = int(warmup), 0
         self.graph = None
         self.static_in = None
@@ -114,7 +136,8 @@ class GraphedVAEStep:
         if self.graph is None:
             self.static_in = [t.clone() if torch.is_tensor(t) else t for t in (x,) + tuple(extra)]
             self.static_eps = eps.clone() if eps is not None else None
-            self.step.opt.zero_grad()       # gradients must be (re)allocated from the graph's private pool
+            if hasattr(self.step.opt, "zero_grad"):
+                self.step.opt.zero_grad()   # gradients must be (re)allocated from the graph's private pool
             torch.cuda.synchronize()
             self.graph = torch.cuda.CUDAGraph()
             with torch.cuda.graph(self.graph):
@@ -218,7 +241,7 @@ def fit(model, kind: str, arrays, epochs: int, batch_size: int, lr: float, beta:
     data = [_to_dev(a, device) for a in arrays]
     n = data[0].shape[0]
     model.to(device).train()
-    step = VAEStep(model, kind, lr, beta, group)
+    step = make_step(model, kind, lr, beta, group)
     world, rank = (vdist.world_size(group), vdist.rank(group)) if group is not None else (1, 0)
     log = TrainLog()
     for epoch in range(1, epochs + 1):
@@ -235,7 +258,7 @@ def fit(model, kind: str, arrays, epochs: int, batch_size: int, lr: float, beta:
             if eps_fn is not None:
                 eps = eps_fn(epoch, s_i, gb)[lo:hi].to(device)
             stats = step(*[t.index_select(0, sel) for t in data], eps=eps, global_batch=gb, local_rows=rows)
-            w = float(gb) if kind == "mlp19" else 1.0
+            w = float(gb) if kind in ("mlp19", "ae22") else 1.0   # 19:234-237, 22:157-158: sample-weighted
             acc += stats.to(torch.float64) * (w * rows / gb)   # this rank's share of the global-batch mean
             denom += w
         if world > 1:
@@ -329,6 +352,8 @@ def export_latents(model, kind: str, arrays, batch_size: int = 512, device=None)
             mu, _ = model.encode(*part)
         elif kind == "mlp19":
             mu, _ = model.encode(part[0], part[1] if len(part) > 1 else None)
+        elif kind == "ae22":
+            mu, _ = model.encode(part[0])     # z of 22:84-87
         else:
             mu, _ = model.encode(part[0])
         outs.append(mu)
