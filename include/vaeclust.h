@@ -215,7 +215,7 @@ int vc_mlpvae_prepare(const VcMlpVaeDesc* desc, const VcMlpVaeParams* params, in
 int vc_mlpvae_step(const VcMlpVaeDesc* desc, const VcMlpVaeParams* params, const float* x, const float* c,
                    const float* eps, int B, float grad_weight, int phases, float lr, float beta1, float beta2,
                    float adam_eps, float bias_corr1, float bias_corr2, VcAdamDeviceStep* step_state, float* out3,
-                   void* workspace, size_t workspace_bytes, int variant, void* stream);
+                   void* workspace, size_t workspace_bytes, void* stream);
 
 /* --------------------------------------------------------------------------------------------- KMeans
  * One Lloyd iteration of sklearn:cluster/_k_means_lloyd.pyx:23-218 reached from 07:70-71, 13:120-121, 16:183,
@@ -232,6 +232,18 @@ int vc_kmeans_assign_update(const float* X, int64_t N, int d, const float* C, in
  * *shift_sq = sum_j ||c_new_j - c_old_j||^2 (:298-311). */
 int vc_kmeans_finalize(const double* sums, const double* counts, const float* C_old, int k, int d, float* C_new,
                        double* shift_sq, void* stream);
+/* Sync-free form of the Lloyd loop (sklearn:cluster/_kmeans.py:705-738): the host enqueues
+ *   begin ; { estep ; [all-reduce(stats[0 .. k*d+k+1)) when X is sharded] ; finalize } x m ; read ctl back ONCE
+ * stats = [sums k*d | counts k | n_changed | shift_sq] (doubles, k*d+k+2); ctl = {state, n_iter, -, -} (int32 x 4):
+ * state 0 running, 1 strict convergence (no label changed), 2 centre shift <= tol, 3 an empty cluster needs the host's
+ * relocation path (_k_means_common.pyx:167-211; centres untouched, iteration not counted).  finalize replaces C by the
+ * new centres in place (C_scratch: k*d floats); once state != 0 every later estep / finalize launch is a no-op, so
+ * over-enqueued iterations change nothing.  Results are bit-identical to the stepwise entry points above. */
+int vc_kmeans_lloyd_begin(int32_t* ctl, void* workspace, size_t workspace_bytes, int k, int d, void* stream);
+int vc_kmeans_lloyd_estep(const float* X, int64_t N, int d, const float* C, int k, int32_t* labels, double* stats,
+                          const int32_t* ctl, void* workspace, size_t workspace_bytes, void* stream);
+int vc_kmeans_lloyd_finalize(double* stats, float* C, float* C_scratch, int k, int d, double tol, int32_t* ctl,
+                             void* stream);
 /* inertia = sum_i ||x_i - c_label(i)||^2 by direct differences (_k_means_common.pyx:94-124); optionally writes
  * per-point squared distances (used by the empty-cluster relocation, :167-211). */
 int vc_kmeans_inertia(const float* X, int64_t N, int d, const float* C, int k, const int32_t* labels,

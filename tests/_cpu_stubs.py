@@ -34,13 +34,14 @@ def install(monkeypatch_or_module, cluster):
     class State:
         def __init__(self, N, d, k, device):
             self.labels = torch.empty(N, dtype=torch.int32)
-            self.stats = torch.zeros(k * d + k + 1, dtype=torch.float64)
+            self.stats = torch.zeros(k * d + k + 2, dtype=torch.float64)
             self.nchg = torch.zeros(1, dtype=torch.int64)
+            self.ctl = torch.zeros(4, dtype=torch.int32)
             self.centers_new = torch.empty((k, d), dtype=torch.float32)
             self.k, self.d = k, d
         sums = property(lambda s: s.stats[: s.k * s.d])
         counts = property(lambda s: s.stats[s.k * s.d: s.k * s.d + s.k])
-        shift = property(lambda s: s.stats[s.k * s.d + s.k:])
+        shift = property(lambda s: s.stats[s.k * s.d + s.k + 1:])
 
     def estep(X, centers, st, update):
         Xn, Cn = X.numpy(), centers.numpy()
@@ -63,6 +64,30 @@ def install(monkeypatch_or_module, cluster):
             new[~nz] = new[int(np.argmax(cnt))]
         st.centers_new.copy_(torch.from_numpy(new))
         st.shift[0] = float(((new.astype(np.float64) - centers.numpy().astype(np.float64)) ** 2).sum())
+
+    # the sync-free loop's entry points (vc_kmeans_lloyd_*): same device-side state machine, on CPU tensors
+    def lloyd_begin(st):
+        st.ctl.zero_()
+
+    def lloyd_estep(X, centers, st):
+        if int(st.ctl[0]) != 0:
+            return
+        estep(X, centers, st, True)
+        st.stats[st.k * st.d + st.k] = float(st.nchg[0])
+
+    def lloyd_finalize(centers, st, tol):
+        if int(st.ctl[0]) != 0:
+            return
+        if (st.counts.numpy() == 0).any():
+            st.ctl[0] = 3
+            return
+        finalize(centers, st)
+        centers.copy_(st.centers_new)
+        st.ctl[1] += 1
+        if float(st.stats[st.k * st.d + st.k]) == 0.0:
+            st.ctl[0] = 1
+        elif float(st.shift[0]) <= tol:
+            st.ctl[0] = 2
 
     def point_sqdist(X, centers, st):
         diff = X.numpy() - centers.numpy()[st.labels.numpy()]
@@ -93,6 +118,7 @@ def install(monkeypatch_or_module, cluster):
     for name, fn in dict(_cluster_sums=cluster_sums, _dbi_intra=dbi_intra).items():
         setattr_(name, fn)
     for name, fn in dict(_as_dev_f32=as_dev, _col_stats=col_stats, _col_affine=col_affine, _LloydState=State,
-                         _estep=estep, _finalize=finalize, _point_sqdist=point_sqdist, _sil_prepare=sil_prepare,
+                         _estep=estep, _finalize=finalize, _lloyd_begin=lloyd_begin, _lloyd_estep=lloyd_estep,
+                         _lloyd_finalize=lloyd_finalize, _point_sqdist=point_sqdist, _sil_prepare=sil_prepare,
                          _sil_block=sil_block).items():
         setattr_(name, fn)

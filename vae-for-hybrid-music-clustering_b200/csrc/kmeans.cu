@@ -64,6 +64,7 @@ struct KmArgs {
   const float* X; int64_t N; int d; const float* C; int k; int32_t* labels; double* part_sums;
   long long* part_counts; unsigned long long* n_changed; int update, assign, tp, ncopies;
   size_t off_acc, off_dsum, off_c, off_c2, off_cnt, off_bar;
+  const int* skip;   // device flag: non-zero -> the launch is a no-op (Lloyd loop already converged, vc_kmeans_lloyd_*)
 };
 
 // 16-byte chunk j of row r of a tile.  SW: panel j/8 of [tp][128 B] rows, chunk index XORed with r%8 (what TMA wrote);
@@ -112,6 +113,7 @@ __device__ __forceinline__ void update_rows_lane_dim(float* accw, const unsigned
 template <int D4, bool SW, bool LD>
 __global__ void __launch_bounds__(kKmThreads)
 kmeans_assign_update_kernel(const KmArgs a, const __grid_constant__ CUtensorMap tmap) {
+  if (a.skip && *a.skip) return;
   extern __shared__ unsigned char smem_raw[];
   unsigned char* smem = smem_raw + ((1024u - (tma::s32(smem_raw) & 1023u)) & 1023u);
   const int d = a.d, k = a.k, tp = a.tp, update = a.update;
@@ -374,6 +376,7 @@ __host__ __device__ constexpr int tc_slots(int tp) { return tp == 128 ? 3 : 4; }
 template <int KP, int TP>
 __global__ void __launch_bounds__(TP + 32, 256 / TP)
 kmeans_tc_kernel(const KmTcArgs ta, const __grid_constant__ CUtensorMap tmap) {
+  if (ta.a.skip && *ta.a.skip) return;
   extern __shared__ unsigned char smem_raw[];
   unsigned char* smem = smem_raw + ((1024u - (tma::s32(smem_raw) & 1023u)) & 1023u);
   const KmArgs& a = ta.a;
@@ -660,6 +663,73 @@ __global__ void kmeans_reduce_partials_kernel(const double* __restrict__ part_su
 }
 
 
+// Tail of one Lloyd iteration of the sync-free loop: fold the per-CTA partials into stats = [sums k*d | counts k |
+// n_changed 1] (ONE buffer, so a sharded fit needs one all-reduce) and re-arm the label-change counter.
+__global__ void kmeans_lloyd_tail_kernel(const double* __restrict__ part_sums, const long long* __restrict__ part_counts,
+                                         int nblocks, int k, int d, double* __restrict__ stats,
+                                         unsigned long long* __restrict__ nchg, const int* __restrict__ skip) {
+  if (skip && *skip) return;
+  const int e = blockIdx.x * blockDim.x + threadIdx.x;
+  const int kd = k * d;
+  if (e < kd) {
+    double s = 0.0;
+    for (int b = 0; b < nblocks; ++b) s += part_sums[(size_t)b * kd + e];
+    stats[e] = s;
+  }
+  if (e < k) {
+    long long c = 0;
+    for (int b = 0; b < nblocks; ++b) c += part_counts[(size_t)b * k + e];
+    stats[kd + e] = (double)c;
+  }
+  if (e == 0) {
+    stats[kd + k] = (double)*nchg;
+    *nchg = 0ull;
+  }
+}
+
+// M-step + convergence test of the sync-free loop (sklearn:cluster/_kmeans.py:705-738) on the (all-reduced) stats:
+// ctl = {state, n_iter}.  state 0: running, 1: strict convergence (no label changed), 2: centre shift <= tol,
+// 3: an empty cluster needs the host's relocation path (centres left untouched, iteration not counted).
+__global__ void kmeans_lloyd_finalize_kernel(double* __restrict__ stats, float* __restrict__ C, float* __restrict__ C_new,
+                                             int k, int d, double tol, int* __restrict__ ctl) {
+  __shared__ double scratch[32];
+  __shared__ int big, empty;
+  if (ctl[0] != 0) return;
+  const double* sums = stats;
+  const double* counts = stats + (size_t)k * d;
+  if (threadIdx.x == 0) {
+    int b = 0, em = 0;
+    for (int c = 0; c < k; ++c) {
+      if (counts[c] > counts[b]) b = c;
+      if (counts[c] == 0.0) em = 1;
+    }
+    big = b;
+    empty = em;
+  }
+  __syncthreads();
+  if (empty) {
+    if (threadIdx.x == 0) ctl[0] = 3;
+    return;
+  }
+  double acc = 0.0;
+  for (int e = threadIdx.x; e < k * d; e += blockDim.x) {
+    const int c = e / d;
+    const float nw = (float)(sums[e] / counts[c]);
+    const double df = (double)nw - (double)C[e];
+    acc += df * df;
+    C_new[e] = nw;
+  }
+  acc = block_sum<double>(acc, scratch);
+  __syncthreads();
+  for (int e = threadIdx.x; e < k * d; e += blockDim.x) C[e] = C_new[e];   // centers, centers_new = centers_new, centers
+  if (threadIdx.x == 0) {
+    stats[(size_t)k * d + k + 1] = acc;
+    ctl[1] += 1;
+    if (stats[(size_t)k * d + k] == 0.0) ctl[0] = 1;
+    else if (acc <= tol) ctl[0] = 2;
+  }
+}
+
 __global__ void kmeans_finalize_kernel(const double* __restrict__ sums, const double* __restrict__ counts,
                                        const float* __restrict__ C_old, int k, int d, float* __restrict__ C_new,
                                        double* __restrict__ shift_sq) {
@@ -795,15 +865,17 @@ static cudaError_t km_launch(int grid, const KmSmem& L, cudaStream_t s, const Km
   return cudaGetLastError();
 }
 
-static int km_run(const float* X, int64_t N, int d, const float* C, int k, int32_t* labels, double* sums,
-                  double* counts, int64_t* n_changed, int update, int assign, void* workspace, size_t workspace_bytes,
-                  void* stream, const char* who) {
+// lloyd_stats != NULL selects the sync-free Lloyd form: the launch honours the device flag `skip`, the label-change
+// counter is not cleared here (the tail kernel re-arms it) and the tail kernel folds everything into lloyd_stats.
+static int km_run_impl(const float* X, int64_t N, int d, const float* C, int k, int32_t* labels, double* sums,
+                       double* counts, int64_t* n_changed, int update, int assign, void* workspace,
+                       size_t workspace_bytes, void* stream, const char* who, const int* skip, double* lloyd_stats) {
   VC_REQUIRE(X && labels && N > 0 && d > 0 && k > 0, VC_ERR_BAD_ARG, "%s: bad arguments (N=%lld d=%d k=%d)", who,
              (long long)N, d, k);
   VC_REQUIRE(d % 4 == 0 && d <= 256 && k <= 256, VC_ERR_UNSUPPORTED,
              "%s: need d %% 4 == 0, d <= 256, k <= 256 (got d=%d k=%d)", who, d, k);
   VC_REQUIRE((reinterpret_cast<uintptr_t>(X) & 15) == 0, VC_ERR_BAD_ARG, "%s: X must be 16-byte aligned", who);
-  VC_REQUIRE(!update || (sums && counts), VC_ERR_BAD_ARG, "%s: update requested without sums/counts", who);
+  VC_REQUIRE(!update || (sums && counts) || lloyd_stats, VC_ERR_BAD_ARG, "%s: update requested without sums/counts", who);
   VC_REQUIRE(workspace && workspace_bytes >= vc_kmeans_workspace_bytes(k, d), VC_ERR_WORKSPACE,
              "%s: workspace too small", who);
   const KmSmem L = km_layout(k, d, update);
@@ -815,9 +887,9 @@ static int km_run(const float* X, int64_t N, int d, const float* C, int k, int32
   double* ps = static_cast<double*>(workspace);
   long long* pc = reinterpret_cast<long long*>(ps + blocks * (size_t)k * d);
   unsigned long long* nchg = reinterpret_cast<unsigned long long*>(pc + blocks * (size_t)k);
-  VC_CUDA(cudaMemsetAsync(nchg, 0, 8, s));
+  if (!lloyd_stats) VC_CUDA(cudaMemsetAsync(nchg, 0, 8, s));
   KmArgs a{X, N, d, C, k, labels, ps, pc, nchg, update, assign, L.tp, L.ncopies,
-           L.off_acc, L.off_dsum, L.off_c, L.off_c2, L.off_cnt, L.off_bar};
+           L.off_acc, L.off_dsum, L.off_c, L.off_c2, L.off_cnt, L.off_bar, skip};
   CUtensorMap tm;
   memset(&tm, 0, sizeof(tm));
   if (L.swz) {
@@ -873,6 +945,11 @@ static int km_run(const float* X, int64_t N, int d, const float* C, int k, int32
       e = cudaGetLastError();
     }
     VC_REQUIRE(e == cudaSuccess, VC_ERR_CUDA, "%s: tensor-core launch failed: %s", who, cudaGetErrorString(e));
+    if (lloyd_stats) {
+      kmeans_lloyd_tail_kernel<<<(k * d + 127) / 128, 128, 0, s>>>(ps, pc, (int)g, k, d, lloyd_stats, nchg, skip);
+      VC_LAUNCH_CHECK();
+      return VC_OK;
+    }
     if (update) {
       const int n = k * d;
       kmeans_reduce_partials_kernel<<<(n + 127) / 128, 128, 0, s>>>(ps, pc, (int)g, k, d, sums, counts);
@@ -903,12 +980,53 @@ static int km_run(const float* X, int64_t N, int d, const float* C, int k, int32
     }
   }
   VC_REQUIRE(e == cudaSuccess, VC_ERR_CUDA, "%s: launch failed: %s", who, cudaGetErrorString(e));
+  if (lloyd_stats) {
+    kmeans_lloyd_tail_kernel<<<(k * d + 127) / 128, 128, 0, s>>>(ps, pc, grid, k, d, lloyd_stats, nchg, skip);
+    VC_LAUNCH_CHECK();
+    return VC_OK;
+  }
   if (update) {
     const int n = k * d;
     kmeans_reduce_partials_kernel<<<(n + 127) / 128, 128, 0, s>>>(ps, pc, grid, k, d, sums, counts);
     VC_LAUNCH_CHECK();
   }
   if (n_changed) VC_CUDA(cudaMemcpyAsync(n_changed, nchg, 8, cudaMemcpyDeviceToDevice, s));
+  return VC_OK;
+}
+
+static int km_run(const float* X, int64_t N, int d, const float* C, int k, int32_t* labels, double* sums, double* counts,
+                  int64_t* n_changed, int update, int assign, void* workspace, size_t workspace_bytes, void* stream,
+                  const char* who) {
+  return km_run_impl(X, N, d, C, k, labels, sums, counts, n_changed, update, assign, workspace, workspace_bytes, stream,
+                     who, nullptr, nullptr);
+}
+
+// ---- sync-free Lloyd loop: the host enqueues iterations without reading anything back; convergence is decided on
+// the device and a converged loop turns the remaining launches into no-ops.
+extern "C" int vc_kmeans_lloyd_begin(int32_t* ctl, void* workspace, size_t workspace_bytes, int k, int d, void* stream) {
+  VC_REQUIRE(ctl && workspace && workspace_bytes >= vc_kmeans_workspace_bytes(k, d), VC_ERR_BAD_ARG,
+             "vc_kmeans_lloyd_begin: bad arguments");
+  const size_t blocks = (size_t)sm_count() * 2;
+  double* ps = static_cast<double*>(workspace);
+  long long* pc = reinterpret_cast<long long*>(ps + blocks * (size_t)k * d);
+  VC_CUDA(cudaMemsetAsync(pc + blocks * (size_t)k, 0, 8, as_stream(stream)));
+  VC_CUDA(cudaMemsetAsync(ctl, 0, 16, as_stream(stream)));
+  return VC_OK;
+}
+
+extern "C" int vc_kmeans_lloyd_estep(const float* X, int64_t N, int d, const float* C, int k, int32_t* labels,
+                                     double* stats, const int32_t* ctl, void* workspace, size_t workspace_bytes,
+                                     void* stream) {
+  VC_REQUIRE(C && stats && ctl, VC_ERR_BAD_ARG, "vc_kmeans_lloyd_estep: bad arguments");
+  return km_run_impl(X, N, d, C, k, labels, nullptr, nullptr, nullptr, 1, 1, workspace, workspace_bytes, stream,
+                     "vc_kmeans_lloyd_estep", ctl, stats);
+}
+
+extern "C" int vc_kmeans_lloyd_finalize(double* stats, float* C, float* C_scratch, int k, int d, double tol,
+                                        int32_t* ctl, void* stream) {
+  VC_REQUIRE(stats && C && C_scratch && ctl && k > 0 && d > 0, VC_ERR_BAD_ARG, "vc_kmeans_lloyd_finalize: bad arguments");
+  kmeans_lloyd_finalize_kernel<<<1, 256, 0, as_stream(stream)>>>(stats, C, C_scratch, k, d, tol, ctl);
+  VC_LAUNCH_CHECK();
   return VC_OK;
 }
 

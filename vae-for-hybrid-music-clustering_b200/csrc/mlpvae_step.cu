@@ -541,7 +541,6 @@ struct MvwArgs {
   int ntiles, nkb, kbs;          // batch k-blocks in total and per split
   int64_t ptot, btot;            // elements of one partial copy (weights, biases)
   float* part; float* bpart;
-  int variant;                   // descriptor experiment switch (0 = canonical)
 };
 
 __global__ void __launch_bounds__(MVW_THREADS, 1)
@@ -605,16 +604,11 @@ mv_wgrad_kernel(const MvwArgs a, const __grid_constant__ MvwMaps maps) {
         const uint32_t sa = tma::s32(smem + (size_t)st * MVW_STAGE), sb = sa + 2 * MVW_BOX;
 #pragma unroll
         for (int kk = 0; kk < 4; ++kk) {
-          uint64_t da, db, d1;
-          if (a.variant == 0) {
-            da = tc05::desc_mn_sw128(sa + kk * 2048, MVW_BOX);
-            db = tc05::desc_mn_sw128(sb + kk * 2048, MVW_BOX);
-            d1 = tc05::desc_mn_sw128(so + kk * 2048, MVW_BOX);
-          } else {   // LBO / SBO roles exchanged
-            da = tc05::desc_mn_sw128_x(sa + kk * 2048, MVW_BOX);
-            db = tc05::desc_mn_sw128_x(sb + kk * 2048, MVW_BOX);
-            d1 = tc05::desc_mn_sw128_x(so + kk * 2048, MVW_BOX);
-          }
+          // MN-major operands as TMA delivers them: [k row][64 features = 128 B, swizzled]; 8 k rows = 1024 B (SBO), the
+          // next 64 features = the next box (LBO); one K16 step = 2 groups of 8 k rows = 2048 B
+          const uint64_t da = tc05::desc_mn_sw128(sa + kk * 2048, MVW_BOX);
+          const uint64_t db = tc05::desc_mn_sw128(sb + kk * 2048, MVW_BOX);
+          const uint64_t d1 = tc05::desc_mn_sw128(so + kk * 2048, MVW_BOX);
           tc05::mma_bf16(tmem_base, da, db, idesc, (uint32_t)((it | kk) != 0));
           if (t.bias_off >= 0) tc05::mma_bf16(tmem_base + 256, da, d1, idesc1, (uint32_t)((it | kk) != 0));
         }
@@ -920,7 +914,7 @@ extern "C" int vc_mlpvae_prepare(const VcMlpVaeDesc* d, const VcMlpVaeParams* pr
 extern "C" int vc_mlpvae_step(const VcMlpVaeDesc* d, const VcMlpVaeParams* prm, const float* x, const float* c,
                               const float* eps, int B, float grad_weight, int phases, float lr, float beta1, float beta2,
                               float adam_eps, float bias_corr1, float bias_corr2, VcAdamDeviceStep* step_state,
-                              float* out3, void* workspace, size_t workspace_bytes, int variant, void* stream) {
+                              float* out3, void* workspace, size_t workspace_bytes, void* stream) {
   const MvPlan p = mv_plan(d, B);
   VC_REQUIRE(p.ok && prm && x, VC_ERR_UNSUPPORTED, "vc_mlpvae_step: unsupported model (hidden must be 256, latent in "
              "{8,16,32}, input_dim + cond_dim <= 512, latent + cond_dim <= 64)");
@@ -1006,7 +1000,6 @@ extern "C" int vc_mlpvae_step(const VcMlpVaeDesc* d, const VcMlpVaeParams* prm, 
     b.ntiles = p.nwt; b.nkb = p.nkbB; b.kbs = p.kbs; b.ptot = p.ptot; b.btot = p.btot;
     b.part = reinterpret_cast<float*>(w + p.o_part);
     b.bpart = reinterpret_cast<float*>(w + p.o_bpart);
-    b.variant = variant;
     static bool attr_w = false;
     if (!attr_w) {
       VC_CUDA(cudaFuncSetAttribute(mv_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)MVW_SMEM_BYTES));

@@ -35,13 +35,6 @@ __device__ __forceinline__ uint64_t desc_mn_sw128(uint32_t smem_addr, uint32_t l
          ((uint64_t)(1024 >> 4) << 32) | ((uint64_t)1 << 46) | ((uint64_t)2 << 61);
 }
 
-// the same operand with the roles of the two offset fields exchanged (probe of the descriptor convention; unused by
-// default paths)
-__device__ __forceinline__ uint64_t desc_mn_sw128_x(uint32_t smem_addr, uint32_t lbo_bytes) {
-  return (uint64_t)((smem_addr >> 4) & 0x3FFFu) | ((uint64_t)(1024 >> 4) << 16) |
-         ((uint64_t)((lbo_bytes >> 4) & 0x3FFFu) << 32) | ((uint64_t)1 << 46) | ((uint64_t)2 << 61);
-}
-
 // ---- instruction descriptor (upper 32 bits of the 64-bit idesc operand are passed as a b32 register)
 // [4,6) D format (1 = f32) | [7,10) A format | [10,13) B format (kind::f16: 0 = f16, 1 = bf16; kind::tf32: 2) |
 // [15] A major (0 = K) | [16] B major | [17,23) N >> 3 | [24,29) M >> 4

@@ -108,11 +108,12 @@ class _LloydState:
 
     def __init__(self, N: int, d: int, k: int, device):
         self.labels = torch.empty(N, dtype=torch.int32, device=device)
-        # stats = [sums k*d | counts k | shift_sq 1]  (float64) ; nchg int64
-        self.stats = torch.zeros(k * d + k + 1, dtype=torch.float64, device=device)
+        # stats = [sums k*d | counts k | n_changed 1 | shift_sq 1]  (float64): one buffer, one all-reduce per iteration
+        self.stats = torch.zeros(k * d + k + 2, dtype=torch.float64, device=device)
         self.nchg = torch.zeros(1, dtype=torch.int64, device=device)
+        self.ctl = torch.zeros(4, dtype=torch.int32, device=device)      # {state, n_iter, -, -} of the sync-free loop
         self.centers_new = torch.empty((k, d), dtype=torch.float32, device=device)
-        self.ws = _workspace(lib().size("vc_kmeans_workspace_bytes", k, d), device)
+        self.ws = torch.empty(max(lib().size("vc_kmeans_workspace_bytes", k, d), 1 << 16), dtype=torch.uint8, device=device)
         self.k, self.d = k, d
 
     @property
@@ -125,7 +126,7 @@ class _LloydState:
 
     @property
     def shift(self):
-        return self.stats[self.k * self.d + self.k:]
+        return self.stats[self.k * self.d + self.k + 1:]
 
 
 def _estep(X, centers, st: _LloydState, update: bool):
@@ -168,38 +169,62 @@ def _relocate_empty(X, centers, st: _LloydState, counts_host: np.ndarray, group)
         st.counts[old_id] -= 1.0
 
 
+def _lloyd_begin(st: _LloydState) -> None:
+    lib().call("vc_kmeans_lloyd_begin", ptr(st.ctl), ptr(st.ws), st.ws.numel(), st.k, st.d, stream_ptr())
+
+
+def _lloyd_estep(X, centers, st: _LloydState) -> None:
+    lib().call("vc_kmeans_lloyd_estep", ptr(X), X.shape[0], X.shape[1], ptr(centers), st.k, ptr(st.labels),
+               ptr(st.stats), ptr(st.ctl), ptr(st.ws), st.ws.numel(), stream_ptr())
+
+
+def _lloyd_finalize(centers, st: _LloydState, tol: float) -> None:
+    lib().call("vc_kmeans_lloyd_finalize", ptr(st.stats), ptr(centers), ptr(st.centers_new), st.k, st.d, float(tol),
+               ptr(st.ctl), stream_ptr())
+
+
+LLOYD_SYNC_EVERY = 4   # iterations enqueued between two read-backs of the device-side convergence state
+
+
 def lloyd(X: torch.Tensor, centers_init: torch.Tensor, max_iter: int = 300, tol: float = 0.0, group=None,
-          state: Optional[_LloydState] = None):
+          state: Optional[_LloydState] = None, sync_every: Optional[int] = None):
     """_kmeans_single_lloyd (sklearn:cluster/_kmeans.py:630-758) on device.  X is this rank's (centred) shard.
-    Returns (labels int32 [N_local], inertia float, centers float32 [k,d], n_iter)."""
+    Returns (labels int32 [N_local], inertia float, centers float32 [k,d], n_iter).
+
+    The loop is sync-free: per iteration the host enqueues the fused E+M pass, (sharded X) ONE all-reduce of
+    [sums | counts | n_changed], and the M-step / convergence kernel; the convergence state lives on the device and is
+    read back every `sync_every` iterations.  Iterations enqueued after convergence are no-ops on the device, so labels,
+    centres and n_iter_ are the same as for a loop that checks after every iteration."""
     N, d = X.shape
     k = centers_init.shape[0]
     st = state or _LloydState(N, d, k, X.device)
     st.labels.fill_(-1)
     centers = centers_init.to(torch.float32).contiguous().clone()
     multi = group is not None and vdist.world_size(group) > 1
-    strict = False
-    n_iter = 0
-    for i in range(max_iter):
-        _estep(X, centers, st, update=True)
-        if multi:
-            vdist.all_reduce_sum(st.stats[: k * d + k], group)
-            vdist.all_reduce_sum(st.nchg, group)
-        _finalize(centers, st)
-        host = torch.cat([st.counts, st.shift, st.nchg.to(torch.float64)]).cpu().numpy()  # the one sync per iteration
-        counts_h, shift_sq, n_changed = host[:k], float(host[k]), int(host[k + 1])
-        if (counts_h == 0).any():
-            _relocate_empty(X, centers, st, counts_h, group)
+    every = int(sync_every or LLOYD_SYNC_EVERY)
+    kd = k * d
+    _lloyd_begin(st)
+    n_iter, code = 0, 0
+    while n_iter < max_iter and code == 0:
+        for _ in range(min(every, max_iter - n_iter)):
+            _lloyd_estep(X, centers, st)
+            if multi:
+                vdist.all_reduce_sum(st.stats[: kd + k + 1], group)
+            _lloyd_finalize(centers, st, tol)
+        ctl = st.ctl.cpu()   # the one host sync of these iterations
+        code, n_iter = int(ctl[0]), int(ctl[1])
+        if code == 3:
+            # an empty cluster: this iteration goes through the host's relocation path (identical on every rank: the
+            # statistics are all-reduced), then the device loop resumes
+            host = st.stats[kd:].cpu().numpy()
+            _relocate_empty(X, centers, st, host[:k], group)
             _finalize(centers, st)
             shift_sq = float(st.shift.item())
-        centers, st.centers_new = st.centers_new, centers
-        n_iter = i + 1
-        if n_changed == 0:
-            strict = True
-            break
-        if shift_sq <= tol:
-            break
-    if not strict:
+            centers.copy_(st.centers_new)
+            n_iter += 1
+            code = 1 if int(host[k]) == 0 else (2 if shift_sq <= tol else 0)
+            st.ctl[:2] = torch.tensor([code, n_iter], dtype=torch.int32, device=X.device)
+    if code != 1:   # not strict convergence: one more E-step with the final centres (_kmeans.py:742-754)
         _estep(X, centers, st, update=False)
     inertia, _ = _point_sqdist(X, centers, st)
     if multi:

@@ -103,7 +103,6 @@ class FusedMLPStep:
         self._versions = None
         self._t = 0
         self._need(max_batch)
-        self.variant = 0
 
     # ------------------------------------------------------------------------------------------------ workspace
     def _need(self, B: int) -> None:
@@ -164,7 +163,7 @@ class FusedMLPStep:
         def call(phases):
             lib().call("vc_mlpvae_step", ctypes.addressof(d), ctypes.addressof(self.params), ptr(x), ptr(c), ptr(eps), B,
                        float(weight), phases, self.lr, b1, b2, self.adam_eps, bc1, bc2, dev_step, ptr(out3),
-                       ptr(self.ws), self.ws.numel(), int(self.variant), stream_ptr())
+                       ptr(self.ws), self.ws.numel(), stream_ptr())
 
         if self.multi:
             call(3)
