@@ -89,6 +89,10 @@ def install(monkeypatch_or_module, cluster):
         elif float(st.shift[0]) <= tol:
             st.ctl[0] = 2
 
+    def sqdist_rows(X, Q):
+        diff = Q.float().unsqueeze(1) - X.float().unsqueeze(0)
+        return (diff * diff).sum(-1)
+
     def point_sqdist(X, centers, st):
         diff = X.numpy() - centers.numpy()[st.labels.numpy()]
         d2 = (diff * diff).sum(1)
@@ -119,6 +123,6 @@ def install(monkeypatch_or_module, cluster):
         setattr_(name, fn)
     for name, fn in dict(_as_dev_f32=as_dev, _col_stats=col_stats, _col_affine=col_affine, _LloydState=State,
                          _estep=estep, _finalize=finalize, _lloyd_begin=lloyd_begin, _lloyd_estep=lloyd_estep,
-                         _lloyd_finalize=lloyd_finalize, _point_sqdist=point_sqdist, _sil_prepare=sil_prepare,
+                         _lloyd_finalize=lloyd_finalize, _sqdist_rows=sqdist_rows, _point_sqdist=point_sqdist, _sil_prepare=sil_prepare,
                          _sil_block=sil_block).items():
         setattr_(name, fn)

@@ -73,6 +73,14 @@ def _worker(rank, world, port, out_dir):
     init2[3] = 1000.0
     km2 = cluster.KMeans(4, init=init2, n_init=1, group=td.group.WORLD).fit(X[lo:hi])
     res["labels2"], res["inertia2"] = km2.labels_, km2.inertia_
+    # k-means++ over row shards (device-prefix-sum path) and best-of-n_init restarts dealt to the ranks
+    cluster._HOST_CUMSUM_MAX = 0
+    km3 = cluster.KMeans(4, n_init=1, random_state=7, group=td.group.WORLD).fit(X[lo:hi])
+    res["pp_centers"], res["pp_labels"] = km3.cluster_centers_, km3.labels_
+    cluster._HOST_CUMSUM_MAX = 1 << 21
+    km4 = cluster.KMeans(4, n_init=5, random_state=3, group=td.group.WORLD, parallel="restarts").fit(X)
+    res["rs_labels"], res["rs_inertia"], res["rs_centers"] = km4.labels_, km4.inertia_, km4.cluster_centers_
+    res["rs_n_iter"] = km4.n_iter_
     np.savez(os.path.join(out_dir, f"r{rank}.npz"), **res)
     td.destroy_process_group()
 
@@ -110,3 +118,20 @@ def test_world2_matches_single_process(tmp_path):
     labels2, inertia2, _, _ = cr.kmeans_lloyd(X, init2)
     assert np.array_equal(np.concatenate([r[0]["labels2"], r[1]["labels2"]]), labels2)
     assert float(r[0]["inertia2"]) == pytest.approx(inertia2, rel=1e-6)
+    # sharded k-means++ == the same (float64 prefix-sum) path on one process; restarts over ranks == sequential n_init
+    import _cpu_stubs
+    from vaeclust import cluster
+    _cpu_stubs.install(None, cluster)
+    cluster._HOST_CUMSUM_MAX = 0
+    one = cluster.KMeans(4, n_init=1, random_state=7).fit(X)
+    cluster._HOST_CUMSUM_MAX = 1 << 21
+    np.testing.assert_allclose(r[0]["pp_centers"], one.cluster_centers_, rtol=1e-6, atol=1e-6)
+    assert np.array_equal(np.concatenate([r[0]["pp_labels"], r[1]["pp_labels"]]), one.labels_)
+    seq = cluster.KMeans(4, n_init=5, random_state=3).fit(X)
+    sk = pytest.importorskip("sklearn.cluster").KMeans(4, n_init=5, random_state=3).fit(X)
+    for i in range(2):
+        assert np.array_equal(r[i]["rs_labels"], seq.labels_) and int(r[i]["rs_n_iter"]) == seq.n_iter_
+        assert float(r[i]["rs_inertia"]) == pytest.approx(seq.inertia_, rel=1e-9)
+        np.testing.assert_array_equal(r[i]["rs_centers"], seq.cluster_centers_)
+    # ... and the seeds are sklearn's own draws: same winner as scikit-learn's sequential best-of-n_init
+    assert float(seq.inertia_) == pytest.approx(float(sk.inertia_), rel=1e-5)

@@ -232,7 +232,7 @@ def lloyd(X: torch.Tensor, centers_init: torch.Tensor, max_iter: int = 300, tol:
     return st.labels, float(inertia.item()), centers, n_iter
 
 
-_HOST_CUMSUM_MAX = 1 << 21  # below this, the k-means++ prefix sum replays numpy's sequential float32 cumsum
+_HOST_CUMSUM_MAX = 1 << 21  # below this (and unsharded), the k-means++ prefix sum replays numpy's sequential float32 cumsum
 
 
 def _sqdist_rows(X: torch.Tensor, Q: torch.Tensor) -> torch.Tensor:
@@ -242,60 +242,136 @@ def _sqdist_rows(X: torch.Tensor, Q: torch.Tensor) -> torch.Tensor:
     return out
 
 
-def kmeans_plusplus(X: torch.Tensor, k: int, random_state: np.random.RandomState):
+def _fetch_rows(X: torch.Tensor, gids: np.ndarray, lo: int, group) -> torch.Tensor:
+    """Rows with GLOBAL indices `gids` of a row-sharded matrix (this rank holds [lo, lo + N_local)): the owner of each
+    row contributes it, everybody else zeros, one all-reduce (k-means++ candidates: a handful of rows)."""
+    loc = torch.from_numpy(np.asarray(gids, dtype=np.int64) - lo).to(X.device)
+    mine = (loc >= 0) & (loc < X.shape[0])
+    rows = torch.zeros((loc.numel(), X.shape[1]), dtype=torch.float32, device=X.device)
+    if bool(mine.any()):
+        rows[mine] = X[loc[mine]]
+    return vdist.all_reduce_sum(rows, group)
+
+
+def kmeans_plusplus(X: torch.Tensor, k: int, random_state: np.random.RandomState, group=None):
     """_kmeans_plusplus (sklearn:cluster/_kmeans.py:180-278): greedy k-means++ with 2+floor(ln k) local trials.
-    The RandomState draws happen on the host in sklearn's order; the distance scans run on the GPU."""
+    The RandomState draws happen on the host in sklearn's order (every rank holds the same generator state); the
+    distance scans run on the GPU.
+
+    One GPU and N <= 2^21: the potentials and the prefix sum are evaluated exactly as numpy does (float32 sequential
+    cumsum, float32 dot), so the seeds are sklearn's own -- every real-size call site of the reference.  Larger N, or X
+    sharded by rows over `group`: float64 prefix sums on the device (per-rank cumsum + exclusive prefix of the rank
+    totals) and `randint` for the first seed; the draw sequence is still sklearn's but a candidate may differ where
+    a uniform draw falls within rounding distance of a prefix-sum step, so parity there is statistical
+    (SURVEY.md 8(f)-1), and so is the choice of seeds."""
     N, d = X.shape
+    multi = group is not None and vdist.world_size(group) > 1
     n_trials = 2 + int(np.log(k))
     centers = torch.empty((k, d), dtype=torch.float32, device=X.device)
     indices = np.full(k, -1, dtype=np.int64)
-    if N <= _HOST_CUMSUM_MAX:  # same call, same float32 weights as sklearn (sample_weight / sample_weight.sum())
+    if not multi and N <= _HOST_CUMSUM_MAX:  # same call, same float32 weights as sklearn (sample_weight / sample_weight.sum())
         w = np.ones(N, dtype=np.float32)
         center_id = int(random_state.choice(N, p=w / w.sum()))
-    else:
-        center_id = int(random_state.randint(N))
-    centers[0] = X[center_id]
-    indices[0] = center_id
-    closest = _sqdist_rows(X, centers[0:1])[0]
-    pot = float(closest.sum(dtype=torch.float64)) if N > _HOST_CUMSUM_MAX else float(
-        np.float32(closest.cpu().numpy() @ np.ones(N, dtype=np.float32)))
-    for c in range(1, k):
-        rand_vals = random_state.uniform(size=n_trials) * pot
-        if N <= _HOST_CUMSUM_MAX:
+        centers[0] = X[center_id]
+        indices[0] = center_id
+        closest = _sqdist_rows(X, centers[0:1])[0]
+        pot = float(np.float32(closest.cpu().numpy() @ np.ones(N, dtype=np.float32)))
+        for c in range(1, k):
+            rand_vals = random_state.uniform(size=n_trials) * pot
             cs = np.cumsum(closest.cpu().numpy())  # float32 sequential, like np.cumsum(sample_weight*closest)
             cand = np.searchsorted(cs, rand_vals)
-        else:
-            cs = torch.cumsum(closest.to(torch.float64), 0)
-            cand = torch.searchsorted(cs, torch.from_numpy(rand_vals).to(X.device)).cpu().numpy()
-        np.clip(cand, None, N - 1, out=cand)
-        cand_t = torch.from_numpy(cand.astype(np.int64)).to(X.device)
-        dist = _sqdist_rows(X, X[cand_t])
-        torch.minimum(dist, closest.unsqueeze(0), out=dist)
-        if N <= _HOST_CUMSUM_MAX:
+            np.clip(cand, None, N - 1, out=cand)
+            cand_t = torch.from_numpy(cand.astype(np.int64)).to(X.device)
+            dist = _sqdist_rows(X, X[cand_t])
+            torch.minimum(dist, closest.unsqueeze(0), out=dist)
             pots = dist.cpu().numpy() @ np.ones(N, dtype=np.float32)
-        else:
-            pots = dist.sum(dim=1, dtype=torch.float64).cpu().numpy()
-        best = int(np.argmin(pots))
-        pot = float(pots[best])
+            best = int(np.argmin(pots))
+            pot = float(pots[best])
+            closest = dist[best].clone()
+            centers[c] = X[int(cand[best])]
+            indices[c] = int(cand[best])
+        return centers, indices
+    # ---- large or sharded X: global row index = rank offset + local index
+    world, rank = (vdist.world_size(group), vdist.rank(group)) if multi else (1, 0)
+    sizes = torch.zeros(world, dtype=torch.int64, device=X.device)
+    sizes[rank] = N
+    vdist.all_reduce_sum(sizes, group)
+    sizes_h = sizes.cpu().numpy()
+    lo = int(sizes_h[:rank].sum())
+    n_total = int(sizes_h.sum())
+    center_id = int(random_state.randint(n_total))
+    centers[0] = _fetch_rows(X, np.array([center_id]), lo, group)[0]
+    indices[0] = center_id
+    closest = _sqdist_rows(X, centers[0:1])[0]
+
+    def rank_totals(v: torch.Tensor) -> np.ndarray:
+        t = torch.zeros(world, dtype=torch.float64, device=X.device)
+        t[rank] = v.sum(dtype=torch.float64)
+        return vdist.all_reduce_sum(t, group).cpu().numpy()
+
+    tot = rank_totals(closest)
+    for c in range(1, k):
+        pot = float(tot.sum())
+        rand_vals = random_state.uniform(size=n_trials) * pot
+        prefix = float(tot[:rank].sum())
+        cs = torch.cumsum(closest.to(torch.float64), 0) + prefix
+        rv = torch.from_numpy(rand_vals).to(X.device)
+        loc = torch.searchsorted(cs, rv)
+        # the rank whose prefix range holds the value owns the candidate; values beyond the last step clip to N-1
+        upper = prefix + float(tot[rank])
+        mine = (rv > prefix if rank > 0 else torch.ones_like(rv, dtype=torch.bool)) & \
+               ((rv <= upper) if rank < world - 1 else torch.ones_like(rv, dtype=torch.bool))
+        gid = torch.where(mine, loc.clamp_max(N - 1) + lo, torch.zeros_like(loc))
+        cand = vdist.all_reduce_sum(gid, group).cpu().numpy()
+        np.clip(cand, None, n_total - 1, out=cand)
+        dist = _sqdist_rows(X, _fetch_rows(X, cand, lo, group))
+        torch.minimum(dist, closest.unsqueeze(0), out=dist)
+        per_rank = torch.zeros((world, n_trials), dtype=torch.float64, device=X.device)
+        per_rank[rank] = dist.sum(dim=1, dtype=torch.float64)
+        per_rank = vdist.all_reduce_sum(per_rank, group).cpu().numpy()
+        best = int(np.argmin(per_rank.sum(axis=0)))
+        tot = per_rank[:, best].copy()
         closest = dist[best].clone()
-        centers[c] = X[int(cand[best])]
+        centers[c] = _fetch_rows(X, cand[best: best + 1], lo, group)[0]
         indices[c] = int(cand[best])
     return centers, indices
+
+
+def _skip_kmeans_plusplus_draws(n: int, k: int, random_state: np.random.RandomState, exact: bool) -> None:
+    """Advance `random_state` by exactly what one k-means++ initialisation consumes (restarts handled by another rank)."""
+    if exact:
+        w = np.ones(n, dtype=np.float32)
+        random_state.choice(n, p=w / w.sum())
+    else:
+        random_state.randint(n)
+    for _ in range(1, k):
+        random_state.uniform(size=2 + int(np.log(k)))
 
 
 class KMeans:
     """sklearn.cluster.KMeans as the reference uses it: KMeans(n_clusters, n_init, random_state[, init, max_iter,
     tol]).fit / fit_predict; attributes labels_ (int32), cluster_centers_ (float32), inertia_, n_iter_.
-    Lloyd only (sklearn's default algorithm).  `init` may be "k-means++" (default), "random" or an ndarray."""
+    Lloyd only (sklearn's default algorithm).  `init` may be "k-means++" (default), "random" or an ndarray.
+
+    Multi-GPU (`group` = a torch.distributed process group), two ways to use the ranks:
+      parallel="points"    X is THIS RANK'S ROW SHARD of the data; every Lloyd iteration all-reduces the per-centroid
+                           statistics, k-means++ scans are sharded too.  labels_ are the local rows' labels.
+      parallel="restarts"  X is the full (small) matrix on every rank; the n_init restarts are dealt round-robin to
+                           the ranks (each advances the shared RandomState past the restarts it skips, so restart i
+                           starts from the seeds sklearn would draw for it), then all-reduce(min) on the inertia and a
+                           broadcast of the winner (sklearn:cluster/_kmeans.py:1506-1541; ties -> lowest restart)."""
 
     def __init__(self, n_clusters: int = 8, *, init="k-means++", n_init="auto", max_iter: int = 300,
                  tol: float = 1e-4, verbose: int = 0, random_state=None, copy_x: bool = True, algorithm: str = "lloyd",
-                 group=None):
+                 group=None, parallel: str = "points"):
         if algorithm not in ("lloyd", "auto", "full"):
             raise VaeclustError("vaeclust KMeans implements Lloyd only")
+        if parallel not in ("points", "restarts"):
+            raise ValueError("parallel must be 'points' or 'restarts'")
         self.n_clusters, self.init, self.n_init = int(n_clusters), init, n_init
         self.max_iter, self.tol, self.verbose = int(max_iter), float(tol), verbose
         self.random_state, self.copy_x, self.algorithm, self.group = random_state, copy_x, algorithm, group
+        self.parallel = parallel
 
     def _check_rs(self):
         rs = self.random_state
@@ -310,7 +386,10 @@ class KMeans:
         Xd = _as_dev_f32(X)
         N, d_true = Xd.shape
         k = self.n_clusters
-        multi = self.group is not None and vdist.world_size(self.group) > 1
+        world = vdist.world_size(self.group) if self.group is not None else 1
+        restarts = world > 1 and self.parallel == "restarts"
+        multi = world > 1 and not restarts                      # rows sharded
+        grp = self.group if multi else None
         n_total = N if not multi else int(vdist.all_reduce_sum(torch.tensor([N], dtype=torch.int64, device=Xd.device),
                                                                self.group).item())
         if n_total < k:
@@ -322,6 +401,8 @@ class KMeans:
             if tuple(init_t.shape) != (k, d_true):
                 raise ValueError(f"The shape of the initial centers {tuple(init_t.shape)} does not match "
                                  f"(n_clusters, n_features) = ({k}, {d_true}).")
+        elif init not in ("k-means++", "random"):
+            raise ValueError(f"init should be 'k-means++', 'random' or an array, got {init!r}")
         n_init = self.n_init
         if n_init == "auto":
             n_init = 1 if (init_is_array or init == "k-means++") else 10
@@ -330,37 +411,64 @@ class KMeans:
                           f"n_init={n_init}.", RuntimeWarning, stacklevel=2)
             n_init = 1
         # tolerance and centring (_kmeans.py:285-293, 1487-1490)
-        mean64, var64, _ = _col_stats(Xd, self.group)
+        mean64, var64, _ = _col_stats(Xd, grp)
         tol_abs = float(var64.mean().item()) * self.tol if self.tol != 0 else 0.0
         mean32 = mean64.to(torch.float32)
         Xc = _pad_cols(_col_affine(Xd, mean32.to(torch.float64), None))
         d = Xc.shape[1]
         rs = self._check_rs()
         st = _LloydState(N, d, k, Xc.device)
-        best = None
-        for _ in range(int(n_init)):
+        rank = vdist.rank(self.group) if world > 1 else 0
+        exact_draws = not multi and N <= _HOST_CUMSUM_MAX
+        best = None   # (labels, inertia, centers, n_iter, restart index)
+        for i in range(int(n_init)):
+            if restarts and i % world != rank:
+                # another rank runs this restart: consume its share of the random stream
+                if init == "k-means++":
+                    _skip_kmeans_plusplus_draws(N, k, rs, exact_draws)
+                elif init == "random":
+                    rs.choice(N, size=k, replace=False, p=np.ones(N) / N)
+                continue
             if init_is_array:
                 c0 = init_t - mean32
             elif init == "k-means++":
-                if multi:
-                    raise VaeclustError("k-means++ over a sharded X is not implemented: pass init=<array>")
-                c0, _idx = kmeans_plusplus(Xc, k, rs)
-            elif init == "random":
-                if multi:
-                    raise VaeclustError("init='random' over a sharded X is not implemented: pass init=<array>")
-                # sklearn passes p=sample_weight/sum (a different numpy algorithm than p=None): same call here
-                seeds = rs.choice(N, size=k, replace=False, p=np.ones(N) / N)
-                c0 = Xc[torch.from_numpy(seeds).to(Xc.device)][:, :d_true]
+                c0, _idx = kmeans_plusplus(Xc, k, rs, grp)
             else:
-                raise ValueError(f"init should be 'k-means++', 'random' or an array, got {init!r}")
+                # sklearn passes p=sample_weight/sum (a different numpy algorithm than p=None): same call here
+                seeds = rs.choice(n_total, size=k, replace=False, p=np.ones(n_total) / n_total)
+                if multi:
+                    sizes = torch.zeros(world, dtype=torch.int64, device=Xc.device)
+                    sizes[rank] = N
+                    lo = int(vdist.all_reduce_sum(sizes, grp).cpu().numpy()[:rank].sum())
+                    c0 = _fetch_rows(Xc, seeds, lo, grp)
+                else:
+                    c0 = Xc[torch.from_numpy(seeds).to(Xc.device)]
             c0 = _pad_cols(c0.contiguous())
-            labels, inertia, centers, n_iter = lloyd(Xc, c0, self.max_iter, tol_abs, self.group, st)
+            labels, inertia, centers, n_iter = lloyd(Xc, c0, self.max_iter, tol_abs, grp, st)
             take = best is None
             if not take and inertia < best[1]:
                 take = multi or not _is_same_clustering(labels.cpu().numpy(), best[0].cpu().numpy(), k)
             if take:
-                best = (labels.clone(), inertia, centers.clone(), n_iter)
-        labels, inertia, centers, n_iter = best
+                best = (labels.clone(), inertia, centers.clone(), n_iter, i)
+        if restarts:
+            # all-reduce(min) on (inertia, restart index), then the winner broadcasts its result
+            mine = torch.tensor([best[1] if best is not None else float("inf"),
+                                 float(best[4]) if best is not None else float("inf")], dtype=torch.float64,
+                                device=Xc.device)
+            allv = [torch.empty_like(mine) for _ in range(world)]
+            torch.distributed.all_gather(allv, mine, group=self.group)
+            table = torch.stack(allv).cpu().numpy()
+            order = np.lexsort((table[:, 1], table[:, 0]))           # lowest inertia, then lowest restart index
+            owner = int(order[0])
+            src = torch.distributed.get_global_rank(self.group, owner)
+            lab = best[0] if rank == owner else torch.empty(N, dtype=torch.int32, device=Xc.device)
+            cen = best[2] if rank == owner else torch.empty((k, d), dtype=torch.float32, device=Xc.device)
+            torch.distributed.broadcast(lab, src=src, group=self.group)
+            torch.distributed.broadcast(cen, src=src, group=self.group)
+            meta = torch.tensor([float(best[3]) if rank == owner else 0.0], dtype=torch.float64, device=Xc.device)
+            torch.distributed.broadcast(meta, src=src, group=self.group)
+            best = (lab, float(table[owner, 0]), cen, int(meta.item()), int(table[owner, 1]))
+        labels, inertia, centers, n_iter = best[:4]
         centers = centers[:, :d_true] + mean32
         self._labels_d, self._centers_d = labels, centers
         self.labels_ = labels.cpu().numpy() if return_numpy else labels
