@@ -313,58 +313,99 @@ def roofline_from_summary(summ, steps, n_params, pk, ms_per_step):
     return roof
 
 
+def _synth_kmeans_points(n, d, device, seed, n_blobs=16):
+    """mixture of 16 Gaussians, centres ~ N(0, 9 I), unit covariance, fp32."""
+    import torch
+    g = torch.Generator(device=device).manual_seed(seed)
+    cent = torch.randn(n_blobs, d, device=device, generator=torch.Generator(device=device).manual_seed(5)) * 3
+    X = torch.empty(n, d, device=device)
+    chunk = 5_000_000
+    for s in range(0, n, chunk):
+        e = min(n, s + chunk)
+        X[s:e] = cent[torch.randint(0, n_blobs, (e - s,), device=device, generator=g)] + \
+            torch.randn(e - s, d, device=device, generator=g)
+    return X
+
+
 def bench_kmeans(rank, world, device, group, pk):
-    """Lloyd iteration (fused assign+update, all-reduce of sums/counts, finalize) on 50M x 32 points sharded over the
-    ranks; k in {2,4,8,16,32}.  Algorithmic traffic 132 B/point/iteration."""
+    """C4: the Lloyd loop of the PUBLIC driver (vaeclust.cluster.lloyd: fused assign+update pass, one all-reduce of
+    [sums | counts | n_changed] when sharded, device-side M-step + convergence test, host read-back every 4 iterations)
+    on 50M x 32 points sharded over the ranks, k = 2..32.  Per-iteration time = (t(30 iterations) - t(10)) / 20, which
+    cancels the final E-step and inertia pass.  Algorithmic traffic 132 B/point/iteration.
+    e2e: KMeans(k, init=array, n_init=1, max_iter=20, tol=0).fit(X_host) with X in (pageable) HOST memory, wall clock:
+    host->device copy of the shard, centring, 20 iterations, final E-step, inertia, labels back to the host."""
+    import numpy as np
     import torch
     from vaeclust import cluster, dist as vdist
     N_total, d = 50_000_000, 32
     lo, hi = vdist.shard_bounds(N_total, rank, world)
     n = hi - lo
-    g = torch.Generator(device=device).manual_seed(100 + rank)
-    cent = torch.randn(16, d, device=device, generator=torch.Generator(device=device).manual_seed(5)) * 3
-    X = torch.empty(n, d, device=device)
-    chunk = 5_000_000
-    for s in range(0, n, chunk):
-        e = min(n, s + chunk)
-        X[s:e] = cent[torch.randint(0, 16, (e - s,), device=device, generator=g)] + torch.randn(e - s, d, device=device, generator=g)
+    X = _synth_kmeans_points(n, d, device, 100 + rank)
+    grp = group if world > 1 else None
     out = {}
     tot_pts, tot_ms = 0.0, 0.0
-    for k in (2, 4, 8, 16, 32):
+    for k in range(2, 33):
         st = cluster._LloydState(n, d, k, device)
-        st.labels.fill_(-1)
-        C = X[:k].clone().contiguous()
+        C0 = X[:k].clone().contiguous()
+        if world > 1:
+            import torch.distributed as td
+            td.broadcast(C0, src=0)
 
-        def it(_s):
-            cluster._estep(X, C, st, True)
-            if world > 1:
-                vdist.all_reduce_sum(st.stats[: k * d + k], group)
-            cluster._finalize(C, st)
-            C.copy_(st.centers_new)
+        def run(iters):
+            return timed_max_ms(lambda _s: cluster.lloyd(X, C0, max_iter=iters, tol=0.0, group=grp, state=st), 1, world,
+                                device)
 
-        for _ in range(3):
-            it(0)
-        iters = 10
-        ms = timed_max_ms(it, iters, world, device)
-        out[f"k{k}"] = dict(ms_per_iter=ms / iters, point_assigns_per_s=N_total * iters / (ms * 1e-3),
-                            hbm_gbs_per_gpu=132.0 * n * iters / (ms * 1e-3) / 1e9,
-                            frac_of_hbm=132.0 * n * iters / (ms * 1e-3) / 1e9 / pk["hbm"])
-        tot_pts += N_total * iters; tot_ms += ms
-    del X
+        run(3)
+        t10, t30 = run(10), run(30)
+        ms = (t30 - t10) / 20.0
+        gbs = 132.0 * n / (ms * 1e-3) / 1e9
+        out[f"k{k}"] = dict(ms_per_iter=ms, point_assigns_per_s=N_total / (ms * 1e-3), hbm_gbs_per_gpu=gbs,
+                            frac_of_hbm=gbs / pk["hbm"], kernel="kmeans_tc_kernel (tcgen05 tf32 hi/lo)" if k >= 11
+                            else "kmeans_assign_update_kernel (FFMA)")
+        tot_pts += N_total * 20; tot_ms += t30 - t10
+    worst = min(out.values(), key=lambda r: r["frac_of_hbm"])
+    roof = dict(bound="hbm", achieved=worst["hbm_gbs_per_gpu"], peak=pk["hbm"], unit="GB/s",
+                frac=worst["frac_of_hbm"], kernel=worst["kernel"], traffic=None,
+                note="worst k of the sweep; 132 B/point/iteration algorithmic (X read once, label written); "
+                     "per-k fractions in per_k", peak_source=pk["src"] + " copy bandwidth")
+    # ---- e2e through the public API with host buffers (k = 8: FFMA kernel, k = 32: tensor-core kernel)
+    Xh = X.cpu().numpy()
+    e2e = {}
+    for k in (8, 32):
+        init = Xh[:k].copy()
+        if world > 1:
+            t = torch.from_numpy(init).to(device)
+            import torch.distributed as td
+            td.broadcast(t, src=0)
+            init = t.cpu().numpy()
+            td.barrier()
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        km = cluster.KMeans(k, init=init, n_init=1, max_iter=20, tol=0.0, group=grp).fit(Xh)
+        torch.cuda.synchronize()
+        dt = time.perf_counter() - t0
+        tmax = torch.tensor([dt], dtype=torch.float64, device=device)
+        if world > 1:
+            td.all_reduce(tmax, op=td.ReduceOp.MAX)
+        dt = float(tmax.item())
+        e2e[f"k{k}"] = dict(value=N_total * km.n_iter_ / dt, unit="point-assigns/s", wall_s=dt, n_iter=int(km.n_iter_),
+                            h2d_bytes=int(n) * d * 4, d2h_bytes=int(n) * 4, inertia=float(km.inertia_))
+    del X, Xh
     torch.cuda.empty_cache()
     return dict(metric="KMeans point-assigns/s", value=tot_pts / (tot_ms * 1e-3), unit="point-assigns/s",
-                config={"workload": "Lloyd iteration, 50M x 32 fp32 points sharded over ranks, k in 2,4,8,16,32",
-                        "scaling": "strong"}, per_k=out, bytes_per_point=132)
+                config={"workload": "Lloyd loop (vaeclust.cluster.lloyd), 50M x 32 fp32 points sharded over ranks, "
+                                    "k = 2..32, explicit init", "scaling": "strong"},
+                per_k=out, bytes_per_point=132, roofline=roof, e2e=e2e)
 
 
-def bench_cvae19(args, rank, world, device, group):
+def bench_cvae19(args, rank, world, device, group, pk):
     """script-19 CVAE (464 + 6 cond -> 256 -> 256 -> 16 -> ... -> 464, beta 4, lr 1e-3), 200 k
-    synthetic rows resident on the device, data-parallel and weak-scaled: 256 rows per GPU (the script's batch) and
-    8192 per GPU, in the precision of the run (bf16 operands / fp32 accumulate by default), the step replayed from a CUDA
-    graph like the headline."""
+    synthetic rows resident on the device, data-parallel and weak-scaled: 256 rows per GPU (the script's batch), 8192 and
+    32768 per GPU; the fused four-launch step (vc_mlpvae_step) replayed from a CUDA graph.  e2e: every step's rows come
+    from pinned HOST memory and the step's loss is read back to the host."""
     import torch
     from vaeclust import nn, ops as vops
-    from vaeclust.train import GraphedVAEStep, VAEStep
+    from vaeclust.train import GraphedVAEStep, VAEStep, make_step
     vops.set_precision(args.precision)
     N, D, COND = 200_000, 464, 6
     g = torch.Generator(device=device).manual_seed(11 + rank)
@@ -372,52 +413,114 @@ def bench_cvae19(args, rank, world, device, group):
     X = torch.cat([torch.randn(N, 80, device=device, generator=g) * sig,
                    torch.randn(N, 384, device=device, generator=g) * 0.05], dim=1).contiguous()
     cond = torch.nn.functional.one_hot(torch.randint(0, COND, (N,), device=device, generator=g), COND).float()
+    Xh, ch = X.cpu().pin_memory(), cond.cpu().pin_memory()
     out = {}
-    for B in (256, 8192):
+    fused = None
+    for B in (256, 8192, 32768):
         torch.manual_seed(42)
         model = nn.MLPVAE(D, 16, 256, cond_dim=COND, conditional=True).to(device).train()
         grp = group if world > 1 else None
-        step = (VAEStep(model, "mlp19", lr=1e-3, beta=4.0, group=grp) if args.no_graph
+        step = (make_step(model, "mlp19", lr=1e-3, beta=4.0, group=grp) if args.no_graph
                 else GraphedVAEStep(model, "mlp19", lr=1e-3, beta=4.0, warmup=2, group=grp))
+        inner = step if args.no_graph else step.step
+        fused = type(inner).__name__ == "FusedMLPStep"
 
         def run(s):
             lo = (s * B) % (N - B)
             return step(X[lo: lo + B], cond[lo: lo + B], global_batch=B * world)
 
+        def run_host(s):
+            lo = (s * B) % (N - B)
+            return step(Xh[lo: lo + B], ch[lo: lo + B], global_batch=B * world).cpu()
+
         for s in range(5):
             run(s)
         iters = 50
         ms = timed_max_ms(lambda s: run(5 + s), iters, world, device)
-        out[f"B{B}"] = dict(ms_per_step=ms / iters, clips_per_s=B * world * iters / (ms * 1e-3),
-                            last_loss=float(run(0)[0]))
-    return dict(metric="CVAE (script 19) train clips/s", unit="clips/s", value=out["B8192"]["clips_per_s"],
+        e2e_ok = not args.no_graph     # the graphed step copies its inputs into static buffers: host tensors are fine
+        ms_e2e = timed_max_ms(lambda s: run_host(60 + s), iters, world, device) if e2e_ok else None
+        clips = B * world * iters / (ms * 1e-3)
+        # SURVEY.md 8(d) C3 roofline: max(tensor time, HBM time of rows + Adam state) per step
+        t_roof = max(B * 2.304e6 / (pk["tf_sust"] * 1e12), (B * 1880 + 1.08e7) / (pk["hbm"] * 1e9))
+        out[f"B{B}"] = dict(ms_per_step=ms / iters, clips_per_s=clips, last_loss=float(run(0)[0]),
+                            roofline_clips_per_s_per_gpu=B / t_roof, frac_of_roofline=(t_roof * 1e3) / (ms / iters),
+                            e2e_clips_per_s=(B * world * iters / (ms_e2e * 1e-3)) if ms_e2e else None,
+                            e2e_ms_per_step=(ms_e2e / iters) if ms_e2e else None,
+                            h2d_bytes_per_step=B * (D + COND) * 4, d2h_bytes_per_step=12)
+    top = out["B32768"]
+    roof = dict(bound="tensor", achieved=top["clips_per_s"] / world * 2.304e6 / 1e12, peak=pk["tf_sust"], unit="TFLOP/s",
+                frac=top["clips_per_s"] / world * 2.304e6 / 1e12 / pk["tf_sust"], kernel="mv_rows_kernel + mv_wgrad_kernel",
+                traffic=None, note="2.304 MFLOP/clip (6 x 384000 MAC) at 32768 rows/GPU; at 256 rows/GPU the step is "
+                                   "bound by the latency of its 13 dependent GEMM+epilogue phases, see per_batch",
+                peak_source=pk["src"] + " sustained bf16")
+    return dict(metric="CVAE (script 19) train clips/s", unit="clips/s", value=top["clips_per_s"],
                 dtype="bf16" if args.precision == "bf16" else "f32",
                 config={"workload": "script-19 CVAE 470->256->256->16->22->256->256->464, beta 4, Adam 1e-3, "
-                                    "200k x 464 resident rows, batch per GPU 256 and 8192", "scaling": "weak",
-                        "submission": "eager" if args.no_graph else "one CUDA graph replay per step"},
-                per_batch=out)
+                                    "200k x 464 resident rows, batch per GPU 256 / 8192 / 32768", "scaling": "weak",
+                        "submission": "eager" if args.no_graph else "one CUDA graph replay per step",
+                        "step": "fused vc_mlpvae_step (4 launches)" if fused else "per-layer ops"},
+                per_batch=out, roofline=roof,
+                e2e={"value": top["e2e_clips_per_s"], "unit": "clips/s", "h2d_bytes_per_step": top["h2d_bytes_per_step"],
+                     "d2h_bytes_per_step": 12})
 
 
-def bench_silhouette(rank, world, device, group):
-    """Silhouette row blocks on 500k x 64 (script 16 sweep shape), k=8; rows sharded over ranks."""
+def bench_silhouette(rank, world, device, group, pk):
+    """C5 (script 16 sweep shape): silhouette_score + davies_bouldin_score on 500k x 64 latents for k = 4..8, labels
+    from the build's own KMeans(k, n_init=10, random_state=42) (16:142,183); silhouette rows sharded over ranks, DBI rows
+    too.  e2e: the same two calls on HOST arrays (numpy in, python floats out), wall clock."""
+    import numpy as np
     import torch
     from vaeclust import cluster, dist as vdist
-    N, d, k = 500_000, 64, 8
+    N, d = 500_000, 64
     g = torch.Generator(device=device).manual_seed(3)
-    cent = torch.randn(k, d, device=device, generator=g) * 3
-    lab = torch.randint(0, k, (N,), device=device, generator=g)
-    X = cent[lab] + torch.randn(N, d, device=device, generator=g)
-    cluster.silhouette_samples(X[:8192].contiguous(), lab[:8192], _return_sum=True)  # warm-up (small)
-    t0 = time.time()
-    res = {}
+    cent = torch.randn(8, d, device=device, generator=g) * 3
+    X = cent[torch.randint(0, 8, (N,), device=device, generator=g)] + torch.randn(N, d, device=device, generator=g)
+    grp = group if world > 1 else None
+    cluster.silhouette_samples(X[:8192].contiguous(), torch.arange(8192, device=device) % 4, _return_sum=True)  # warm-up
+    lo, hi = vdist.shard_bounds(N, rank, world)
+    per_k, tot_ms = {}, 0.0
+    Xh = X.cpu().numpy()
+    for k in (4, 5, 6, 7, 8):
+        t0 = time.perf_counter()
+        lab = cluster.KMeans(k, n_init=10, random_state=42).fit(X).labels_     # replicated fit: same labels on every rank
+        torch.cuda.synchronize()
+        t_km = time.perf_counter() - t0
+        res = {}
 
-    def run(_s):
-        res["s"] = cluster.silhouette_samples(X, lab, group=group if world > 1 else None, _return_sum=True)
+        def sil(_s):
+            res["s"] = cluster.silhouette_samples(X, lab, group=grp, _return_sum=True)
 
-    ms = timed_max_ms(run, 1, world, device)
-    return dict(metric="silhouette pairs/s", value=float(N) * N / (ms * 1e-3), unit="ordered pairs/s",
-                ms=ms, score=res["s"][0] / N, config={"workload": "silhouette_score 500k x 64 fp32, k=8, rows sharded",
-                                                      "scaling": "strong"}, wall_s=time.time() - t0)
+        def dbi(_s):
+            res["d"] = cluster.davies_bouldin_score(X[lo:hi], lab[lo:hi], group=grp)
+
+        ms = timed_max_ms(sil, 1, world, device)
+        ms_dbi = timed_max_ms(dbi, 1, world, device)
+        lab_h = lab.cpu().numpy()
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        s_h = cluster.silhouette_score(Xh, lab_h, group=grp)
+        d_h = cluster.davies_bouldin_score(Xh[lo:hi], lab_h[lo:hi], group=grp)
+        torch.cuda.synchronize()
+        t_e2e = time.perf_counter() - t0
+        per_k[f"k{k}"] = dict(silhouette_ms=ms, pairs_per_s=float(N) * N / (ms * 1e-3), dbi_ms=ms_dbi,
+                              silhouette=res["s"][0] / N, dbi=res["d"], kmeans_n_init10_s=t_km,
+                              e2e_wall_s=t_e2e, e2e_pairs_per_s=float(N) * N / t_e2e, e2e_silhouette=s_h, e2e_dbi=d_h)
+        tot_ms += ms
+    mean_ms = tot_ms / 5
+    flops = 2.0 * N * N * d
+    ach = flops / (mean_ms * 1e-3) / 1e12 / world
+    roof = dict(bound="tensor", achieved=ach, peak=pk["tf_sust"], unit="TFLOP/s", frac=ach / pk["tf_sust"],
+                kernel="silhouette_tc_kernel<256,16>", traffic=None, issued_mma_per_product=cluster.SILHOUETTE_MMA_PER_PRODUCT,
+                note="algorithmic 2 N^2 d FLOP per call over the mean silhouette time of k = 4..8, per GPU; the bf16 hi/lo "
+                     "split issues issued_mma_per_product MMAs per product, so the kernel's own tensor work is that many "
+                     "times the algorithmic figure; the per-pair sqrt epilogue (MUFU) is co-binding (SURVEY.md 7.3-5)",
+                peak_source=pk["src"] + " sustained bf16")
+    return dict(metric="silhouette pairs/s", value=float(N) * N * 5 / (tot_ms * 1e-3), unit="ordered pairs/s",
+                config={"workload": "silhouette_score + davies_bouldin_score, 500k x 64 fp32, k = 4..8 (labels: own "
+                                    "KMeans n_init=10), rows sharded", "scaling": "strong"},
+                per_k=per_k, roofline=roof,
+                e2e={"value": float(N) * N * 5 / sum(v["e2e_wall_s"] for v in per_k.values()), "unit": "ordered pairs/s",
+                     "h2d_bytes_per_call": N * d * 4 + N * 8, "d2h_bytes_per_call": 8})
 
 
 # ------------------------------------------------------------------------------------- parity at bench sizes
@@ -473,6 +576,110 @@ def cluster_parity_at_bench_size():
         out["silhouette"][f"n{n2}"] = parity.silhouette_dbi_parity(X2, lab)
     out["ok"] = all(v["ok"] for grp in ("kmeans", "silhouette") for v in out[grp].values())
     return out
+
+
+def cvae19_cpu_and_parity(device, precision):
+    """C3 next to the reference's CPU path: the oracle's script-19 step (19:226-232) timed on the host cores at the
+    script's batch (256) and at 8192, and ONE fused step checked against it at both sizes (same state_dict, batch, eps):
+    loss and every parameter's gradient (oracle/parity.py)."""
+    import torch
+    from oracle import parity, vae_ref
+    from vaeclust import nn, ops as vops
+    from vaeclust.train import make_step
+    if torch.get_num_threads() == 1 and len(os.sched_getaffinity(0)) > 1:
+        torch.set_num_threads(len(os.sched_getaffinity(0)))
+    vops.set_precision(precision)
+    D, COND, Z = 464, 6, 16
+    out = {"cpu_baseline": {}, "parity": {}}
+    g = torch.Generator().manual_seed(21)
+    for B in (256, 8192):
+        x = torch.cat([torch.randn(B, 80, generator=g) * torch.logspace(2, 0, 80), torch.randn(B, 384, generator=g) * 0.05], 1)
+        c = torch.nn.functional.one_hot(torch.randint(0, COND, (B,), generator=g), COND).float()
+        batch = dict(x=x, c=c, eps=torch.randn(B, Z, generator=g))
+        p = vae_ref.init_mlp_vae_params(D, Z, 256, COND, seed=42, style="19")
+        opt = vae_ref.AdamRef(p, 1e-3)
+        vae_ref.train_step(p, opt, "mlp19", batch, 4.0)
+        n = 20 if B == 256 else 5
+        t0 = time.perf_counter()
+        for _ in range(n):
+            vae_ref.train_step(p, opt, "mlp19", batch, 4.0)
+        dt = (time.perf_counter() - t0) / n
+        out["cpu_baseline"][f"B{B}"] = {"value": B / dt, "unit": "clips/s", "cores": torch.get_num_threads(), "kind": "port",
+                                        "sample": f"{n} steps of batch {B}, torch-CPU fp32 restatement of script 19's "
+                                                  f"CVAE step, {dt * 1e3:.1f} ms/step"}
+        model = nn.MLPVAE(D, Z, 256, cond_dim=COND, conditional=True)
+        model.load_state_dict(vae_ref.init_mlp_vae_params(D, Z, 256, COND, seed=42, style="19"))
+        model.to(device).train()
+        step = make_step(model, "mlp19", lr=1e-3, beta=4.0)
+        r = parity.vae_step_parity(model, step, "mlp19", {k: v.to(device) for k, v in batch.items()}, 4.0, 1e-3,
+                                   "bf16" if precision == "bf16" else "fp32")
+        r.pop("grad_rel")
+        r["step"] = type(step).__name__
+        out["parity"][f"B{B}"] = r
+    out["parity"]["ok"] = all(v["ok"] for v in out["parity"].values())
+    return out
+
+
+def c1_record(device, precision):
+    """BASELINE.json configs[0] / SURVEY.md 8(d) C1: scripts 06 + 07 end to end on synthetic 3000 x 80 MFCC-statistic
+    vectors (6 Gaussian centres) -- StandardScaler, MLPVAE(80, 256, 16) for 40 epochs (batch 128, lr 1e-3, beta 1,
+    seed 42), latent export, StandardScaler + KMeans(k=6, n_init=20, random_state=42) -- run ONCE through the product
+    (GPU) and ONCE through the reference's own CPU path (the pinned oracle loop + scikit-learn), same seed, same eps
+    stream: wall times, epoch-40 loss / recon / kl and the cluster sizes of both, and their agreement."""
+    import numpy as np
+    import torch
+    from sklearn.cluster import KMeans as SkKMeans
+    from sklearn.metrics import adjusted_rand_score
+    from sklearn.preprocessing import StandardScaler as SkScaler
+    from oracle import vae_ref
+    from vaeclust import cluster, ops as vops, train
+    from vaeclust.nn06 import MLPVAE
+    vops.set_precision(precision)
+    rng = np.random.default_rng(0)
+    cen = rng.normal(0, 2, size=(6, 80))
+    lab = np.arange(3000) % 6
+    X_raw = (cen[lab] + rng.normal(size=(3000, 80))).astype(np.float32)
+    epochs, B, lr, beta, seed = 40, 128, 1e-3, 1.0, 42
+    spe = (3000 + B - 1) // B
+    eps_fn = lambda ep, st, rows: torch.randn(rows, 16, generator=torch.Generator().manual_seed(9000 + (ep - 1) * spe + st))
+    # ---- product
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    Xs = cluster.StandardScaler().fit_transform(X_raw).astype(np.float32)            # 06:291-292
+    torch.manual_seed(seed)                                                          # 06:set_seed
+    model = MLPVAE(80, 256, 16)
+    log = train.fit(model, "mlp06", (Xs,), epochs, B, lr, beta, device=device, eps_fn=eps_fn)
+    Z = train.export_latents(model, "mlp06", (Xs,), batch_size=3000, device=device)  # 06:354-358
+    Zs = cluster.StandardScaler().fit_transform(Z)                                   # 07:67-68
+    km = cluster.KMeans(n_clusters=6, n_init=20, random_state=42).fit(Zs)            # 07:70-71
+    torch.cuda.synchronize()
+    t_gpu = time.perf_counter() - t0
+    # ---- reference CPU path
+    t0 = time.perf_counter()
+    Xs_ref = SkScaler().fit_transform(X_raw).astype(np.float32)
+    torch.manual_seed(seed)
+    ref_model = MLPVAE(80, 256, 16)      # CPU construction draws the reference's initial parameters (tests/test_loops.py)
+    p = {k: v.detach().clone() for k, v in ref_model.state_dict().items()}
+    ref_log = vae_ref.train_loop(p, "mlp06", (Xs_ref,), epochs, B, lr, beta, eps_fn, seed=None)
+    Z_ref = vae_ref.encode_mu(p, "mlp06", (Xs_ref,)).numpy().astype(np.float32)
+    Zs_ref = SkScaler().fit_transform(Z_ref)
+    km_ref = SkKMeans(n_clusters=6, n_init=20, random_state=42).fit(Zs_ref)
+    t_cpu = time.perf_counter() - t0
+    sizes = sorted(np.bincount(km.labels_, minlength=6).tolist())
+    sizes_ref = sorted(np.bincount(km_ref.labels_, minlength=6).tolist())
+    return {"config": "scripts 06+07: 3000 x 80 synthetic, MLPVAE(80,256,16), 40 epochs, batch 128, lr 1e-3, beta 1, seed 42; "
+                      "StandardScaler + KMeans(k=6, n_init=20, random_state=42)",
+            "gpu_wall_s": t_gpu, "cpu_reference_wall_s": t_cpu, "cores": torch.get_num_threads(),
+            "epoch40": {"loss": log.loss[-1], "recon": log.recon[-1], "kl": log.kl[-1]},
+            "epoch40_reference": {"loss": ref_log["loss"][-1], "recon": ref_log["recon"][-1], "kl": ref_log["kl"][-1]},
+            "epoch40_loss_rel": abs(log.loss[-1] - ref_log["loss"][-1]) / abs(ref_log["loss"][-1]),
+            "epoch1_loss_rel": abs(log.loss[0] - ref_log["loss"][0]) / abs(ref_log["loss"][0]),
+            "kmeans_cluster_sizes": sizes, "kmeans_cluster_sizes_reference": sizes_ref,
+            "kmeans_inertia": float(km.inertia_), "kmeans_inertia_reference": float(km_ref.inertia_),
+            "labels_ari_vs_reference": float(adjusted_rand_score(km_ref.labels_, km.labels_)),
+            "labels_ari_vs_truth": float(adjusted_rand_score(lab, km.labels_)),
+            "labels_ari_reference_vs_truth": float(adjusted_rand_score(lab, km_ref.labels_)),
+            "kind": "port (oracle loop pinned to the reference's script-06 loop by tests/golden/loop06.npz) + scikit-learn"}
 
 
 # -------------------------------------------------------------------------- CPU baseline / reference arm
@@ -605,8 +812,8 @@ def main():
     if not args.skip_extra:
         torch.cuda.empty_cache()
         extra["kmeans"] = bench_kmeans(rank, world, device, group, pk)
-        extra["silhouette"] = bench_silhouette(rank, world, device, group)
-        extra["cvae19"] = bench_cvae19(args, rank, world, device, group)
+        extra["silhouette"] = bench_silhouette(rank, world, device, group, pk)
+        extra["cvae19"] = bench_cvae19(args, rank, world, device, group, pk)
     cpu = None
     if rank == 0 and world == 1 and not args.skip_cpu:
         v, spstep, cores = cpu_vae_steps(BATCH, 3, 1)
@@ -618,6 +825,10 @@ def main():
         par = {"vae_step": vae_parity_at_bench_size(device, args.precision)}
         if extra:
             par["clustering"] = cluster_parity_at_bench_size()
+            c3 = cvae19_cpu_and_parity(device, args.precision)
+            extra["cvae19"]["cpu_baseline"] = c3["cpu_baseline"]
+            par["cvae19_step"] = c3["parity"]
+            extra["c1_scripts_06_07"] = c1_record(device, args.precision)
         par["ok"] = all(v["ok"] for v in par.values())
     if rank == 0 and world == 1 and not args.skip_cpu and extra:
         try:

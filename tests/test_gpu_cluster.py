@@ -210,7 +210,7 @@ def test_logical_shards_equal_one_shard():
         acc += s2.stats
         labs.append(s2.labels.clone())
     assert torch.equal(torch.cat(labs), full_labels)
-    assert torch.equal(acc[-9:-1], full_counts)
+    assert torch.equal(acc[8 * 32: 8 * 32 + 8], full_counts)
     # sums are accumulated in fp32 per warp before the double fold, so a different tiling moves the last bits
     torch.testing.assert_close(acc[: 8 * 32], full_sums, rtol=1e-5, atol=1e-3)
 

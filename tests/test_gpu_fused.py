@@ -44,9 +44,11 @@ def test_fused_steps_follow_reference_golden(name, graphed, golden_dir):
         stats = step(*_args(b, c), eps=b.get("eps")).cpu().numpy()
         assert stats[0] == pytest.approx(float(gold["loss"][s]), rel=BF16_LOSS_RTOL), s
         assert stats[1] == pytest.approx(float(gold["recon"][s]), rel=BF16_LOSS_RTOL), s
+    # Adam moves every element by ~lr per step whatever the gradient's size, so an element whose bf16 gradient has the
+    # other sign ends 2*lr*steps away: 1e-2 relative on the |.|-sums of the small tensors
     for n_, p in model.named_parameters():
         got = float(p.detach().double().abs().sum())
-        assert got == pytest.approx(gold["param/" + n_][1], rel=2e-3, abs=1e-6), n_
+        assert got == pytest.approx(gold["param/" + n_][1], rel=1e-2, abs=1e-6), n_
     if graphed:
         assert step.graph is not None
         assert max(st["step"] for st in step.opt.state_dict()["state"].values()) == c["steps"]

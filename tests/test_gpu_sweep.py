@@ -116,3 +116,26 @@ def test_label_scores_from_device_labels():
     assert sc["ari"] == pytest.approx(skm.adjusted_rand_score(a, b), abs=1e-12)
     assert sc["nmi"] == pytest.approx(skm.normalized_mutual_info_score(a, b), rel=1e-9, abs=1e-12)
     assert np.array_equal(sweep.contingency_table(torch.from_numpy(a).cuda(), b), skm.cluster.contingency_matrix(a, b))
+
+
+def test_pca_matches_sklearn():
+    """scripts 09:77-80 / 22:122-124: PCA(n_components, random_state).fit_transform on MFCC-statistics-sized inputs."""
+    from sklearn.decomposition import PCA as SkPCA
+    from vaeclust.cluster import PCA
+    rng = np.random.default_rng(4)
+    for n, d, nc in ((3000, 80, 16), (5000, 464, 32)):
+        A = rng.normal(size=(d, d)) / np.sqrt(d)
+        X = (rng.normal(size=(n, d)) * np.logspace(1, -1, d) @ A + rng.normal(size=d)).astype(np.float32)
+        ref = SkPCA(n_components=nc, random_state=42).fit(X)
+        ours = PCA(n_components=nc, random_state=42)
+        Z = ours.fit_transform(X)
+        np.testing.assert_allclose(ours.explained_variance_, ref.explained_variance_, rtol=2e-4)
+        np.testing.assert_allclose(ours.explained_variance_ratio_, ref.explained_variance_ratio_, rtol=2e-4)
+        np.testing.assert_allclose(ours.mean_, ref.mean_, rtol=1e-5, atol=1e-5)
+        # well-separated leading components agree element-wise (same svd_flip sign rule); the projection too
+        lead = 8
+        np.testing.assert_allclose(ours.components_[:lead], ref.components_[:lead], atol=2e-3)
+        Zr = ref.transform(X)
+        assert Z.shape == Zr.shape and Z.dtype == np.float32
+        np.testing.assert_allclose(Z[:, :lead], Zr[:, :lead], atol=2e-3 * np.abs(Zr[:, :lead]).max())
+        np.testing.assert_allclose(ours.transform(X[:100]), Z[:100], rtol=1e-5, atol=1e-5)

@@ -91,6 +91,70 @@ class StandardScaler:
         return self.fit(X, group).transform(X)
 
 
+class PCA:
+    """sklearn.decomposition.PCA as scripts 09 and 22 use it (09:77-80, 22:122-124: PCA(n_components, random_state)
+    .fit_transform(X) on a few hundred features): the `covariance_eigh` solver sklearn selects for such shapes --
+    column means and the d x d covariance X^T X on the GPU (fp32 FFMA GEMM with a fixed-order split over the rows), the
+    eigendecomposition of the small symmetric matrix on the host in float64, the projection on the GPU again.
+    Component signs follow sklearn's svd_flip (largest-magnitude entry of each component positive)."""
+
+    def __init__(self, n_components: Optional[int] = None, *, random_state=None, whiten: bool = False):
+        if whiten:
+            raise VaeclustError("vaeclust PCA: whiten is not used by the reference and not supported")
+        self.n_components, self.random_state = n_components, random_state
+
+    def fit(self, X, y=None):
+        self._fit(X)
+        return self
+
+    def _fit(self, X):
+        from .ops import _dense
+        Xd = _as_dev_f32(X)
+        N, d = Xd.shape
+        nc = min(N, d) if self.n_components is None else int(self.n_components)
+        if not 1 <= nc <= min(N, d):
+            raise ValueError(f"n_components={nc} must be between 1 and min(n_samples, n_features)={min(N, d)}")
+        mean64, _, _ = _col_stats(Xd)
+        Xc = _col_affine(Xd, mean64, None)
+        cov = torch.empty((d, d), dtype=torch.float32, device=Xd.device)
+        _dense(2, 0, Xc, Xc, None, cov, N, d, 1, 1, d, False)          # LINEAR_WGRAD, fp32: Xc^T Xc
+        C = cov.cpu().numpy().astype(np.float64) / (N - 1)
+        C = 0.5 * (C + C.T)
+        evals, evecs = np.linalg.eigh(C)
+        evals, evecs = evals[::-1], evecs[:, ::-1]
+        evals = np.clip(evals, 0.0, None)
+        comps = evecs.T
+        signs = np.sign(comps[np.arange(comps.shape[0]), np.argmax(np.abs(comps), axis=1)])
+        signs[signs == 0] = 1.0
+        comps = comps * signs[:, None]
+        total = evals.sum()
+        self.mean_ = mean64.cpu().numpy().astype(np.float32)
+        self.components_ = comps[:nc].astype(np.float32)
+        self.explained_variance_ = evals[:nc].astype(np.float32)
+        self.explained_variance_ratio_ = (evals[:nc] / total).astype(np.float32)
+        self.singular_values_ = np.sqrt(evals[:nc] * (N - 1)).astype(np.float32)
+        self.n_components_, self.n_features_in_, self.n_samples_ = nc, d, N
+        self._comp_d = torch.from_numpy(self.components_).to(Xd.device).contiguous()
+        self._mean_d = mean64
+        return Xc
+
+    def _project(self, Xc: torch.Tensor) -> torch.Tensor:
+        from .ops import _dense
+        out = torch.empty((Xc.shape[0], self.n_components_), dtype=torch.float32, device=Xc.device)
+        _dense(0, 0, Xc, self._comp_d, None, out, Xc.shape[0], Xc.shape[1], 1, 1, self.n_components_, False)
+        return out
+
+    def transform(self, X):
+        is_np = not isinstance(X, torch.Tensor)
+        out = self._project(_col_affine(_as_dev_f32(X), self._mean_d, None))
+        return out.cpu().numpy() if is_np else out
+
+    def fit_transform(self, X, y=None):
+        is_np = not isinstance(X, torch.Tensor)
+        out = self._project(self._fit(X))
+        return out.cpu().numpy() if is_np else out
+
+
 # ------------------------------------------------------------------------------------------------- KMeans
 def _is_same_clustering(a: np.ndarray, b: np.ndarray, k: int) -> bool:
     """sklearn:cluster/_k_means_common.pyx:_is_same_clustering -- equal up to a permutation of labels."""
@@ -517,6 +581,7 @@ def _sil_prepare(Xd: torch.Tensor, order: torch.Tensor, mean64: torch.Tensor):
     return Xs, sqn
 
 
+SILHOUETTE_MMA_PER_PRODUCT = 4   # bf16 hi/lo split: hi.hi + hi.lo + lo.hi + lo.lo
 SILHOUETTE_PRECISION = "tc"  # "tc": tcgen05 bf16 hi/lo split (d <= 128); "fp32": FFMA tile kernel
 
 
@@ -708,6 +773,6 @@ def eval_kmeans(X, k: int, seed: int, n_init: int = 20):
     return labels, safe_silhouette_nan(X, labels)
 
 
-__all__ = ["KMeans", "StandardScaler", "silhouette_score", "silhouette_samples", "davies_bouldin_score",
+__all__ = ["KMeans", "StandardScaler", "PCA", "silhouette_score", "silhouette_samples", "davies_bouldin_score",
            "safe_silhouette", "safe_db_index", "safe_dbi", "safe_silhouette_nan", "eval_kmeans", "lloyd",
            "kmeans_plusplus"]
