@@ -6,17 +6,18 @@
 //                        64 KB shared-memory activation buffer (each epilogue overwrites it in place: bias, ReLU,
 //                        bf16, 128-byte-swizzled K-major rows = the next A operand), reparameterisation + KL, the
 //                        reconstruction loss straight from the accumulators, and the six data-gradient GEMMs back
-//                        down.  tcgen05.mma with accumulators in tensor memory; weights (bf16 shadows, forward and
-//                        transposed) stream from L2 through a 3-stage TMA ring that runs ahead across layers; the next
-//                        tile's input rows are prefetched by TMA during the current tile's backward.  ReLU masks stay
-//                        in registers (the thread that wrote an activation row also masks its gradient).  Activations
-//                        and pre-activation gradients leave as bf16 rows for kernel B.
+//                        down.  tcgen05.mma with accumulators in tensor memory; the bf16 weight shadows stream from L2
+//                        through a 3-stage TMA ring that runs ahead across layers (K-major boxes forward, the SAME
+//                        matrices as MN-major boxes for the data gradients: no transposed copy); the next tile's input
+//                        rows are prefetched by TMA during the current tile's backward.  ReLU masks stay with the thread
+//                        that wrote the activation row.  Activations and pre-activation gradients leave for kernel B
+//                        as TMA stores straight out of the activation buffer.
 //   B  mv_wgrad_kernel   weight gradients dW_l = G_l^T A_l with the BATCH as the contraction: both operands are the
 //                        row-major [batch][features] matrices kernel A wrote, fetched by TMA and used as MN-major
 //                        tcgen05 operands (no transpose anywhere); bias gradients ride along as an extra N=16 MMA against a
 //                        constant ones tile; deterministic split-K partials.
 //   C  mv_adam_kernel    fixed-order fold of the partials, Adam on the fp32 masters (torch's arithmetic order), and
-//                        the bf16 shadows (forward + transposed) kernel A reads next step.  Gradients are never
+//                        the bf16 shadows kernel A reads next step.  Gradients are never
 //                        materialised per parameter tensor; a padded flat copy is kept for the data-parallel
 //                        all-reduce and for parity checks.
 //
@@ -33,16 +34,21 @@ constexpr uint32_t MV_ABLK = 128 * 128;         // one K-major A k-block: [128 r
 constexpr uint32_t MV_WSTAGE = 256 * 128;       // one weight k-block: [<=256 rows][64 bf16]
 constexpr int MV_XS = 3, MV_WS = 3;             // ring depths
 constexpr int MV_NBIAS = 1600;                  // b1 256 | b2 256 | b3 64 | b4 256 | b5 256 | b6 512
-constexpr int MV_MAXPH = 13;
 
 enum { EPI_NONE = 0, EPI_RELU_F, EPI_HEADS, EPI_LOSS_A, EPI_LOSS_B, EPI_RELU_B, EPI_DZ };
-enum { MAP_X = 0, MAP_W1, MAP_W2, MAP_W3, MAP_W4, MAP_W5, MAP_W6A, MAP_W6B, MAP_W6T, MAP_W5T, MAP_W4T, MAP_W3T,
-       MAP_W2T, MAP_COUNT };
+// tensor maps of the rows kernel: the packed input, the forward weight shadows as K-major boxes (64 k x N rows), the
+// same shadows as MN-major 64 x 64 boxes for the data-gradient GEMMs (B(n = in-feature, k = out-feature) = W[k][n]:
+// no transposed copy exists anywhere), and the activation / gradient row matrices the epilogues store through TMA
+enum { MAP_X = 0, MAP_W1, MAP_W2, MAP_W3, MAP_W4, MAP_W5, MAP_W6A, MAP_W6B, MAP_W6M, MAP_W5M, MAP_W4M, MAP_W3M,
+       MAP_W2M, MAP_SA1, MAP_SA2, MAP_SA3, MAP_SA4, MAP_SA5, MAP_SG0, MAP_SG1, MAP_SG2, MAP_SG3, MAP_SG4, MAP_SG5,
+       MAP_COUNT };
 
 struct MvMaps { CUtensorMap m[MAP_COUNT]; };
 
 struct MvPhase {
   int map, nkb, kb0, n, row0, a_x, tcol, acc_init, has_epi, wait_prev;
+  int b_mn, nbox;                 // data-gradient phases: weights as MN-major boxes, nbox = n / 64 per k-block
+  int st_map, st_nblk, st_col0;   // what the phase's epilogue leaves in P and where it goes (TMA store), -1: nothing
 };
 
 struct MvTensor { float* p; float* m; float* v; };
@@ -50,14 +56,12 @@ struct MvParams { MvTensor W[7], b[7]; };   // 0 enc.0, 1 enc.2, 2 mu, 3 logvar,
 
 struct MvRowsArgs {
   int nph;
-  int B, Bp, ntiles, D, Cc, Z, NH, variational, N6a, N6b, nk1, nkd;
+  int B, Bp, ntiles, D, Cc, Z, NH, variational, N6a, N6b, nk1, nkd, xvec;
   float gs2;        // 2 * d(loss)/d(sum of squared errors)
   float ks;         // d(loss)/d(kl row sum)
   const float* x; const float* c; const float* eps;
   const float* bias[6];                   // fp32 biases of the 6 layers (heads: mu then logvar via bias3b)
   const float* bias_lv;
-  __nv_bfloat16* A[6];                    // A2..A6 at [1..5] (A[0] = packed input, written by the pack kernel)
-  __nv_bfloat16* G[6];                    // G1..G6
   float* mulv;                            // [Bp][64] fp32: mu | logvar of the row (re-read by the backward)
   double* tile_part;                      // [ntiles][2]: sum of squared errors, sum of KL rows
 };
@@ -75,20 +79,23 @@ __device__ __forceinline__ MvPhase mv_phase(int p, int nk1, int N6a, int N6b, in
   }
   MvPhase q;
   q.kb0 = 0; q.row0 = 0; q.a_x = 0; q.tcol = 0; q.acc_init = 0; q.has_epi = 1; q.wait_prev = 1; q.n = 256; q.nkb = 4;
+  q.b_mn = 0; q.nbox = 4; q.st_nblk = 4; q.st_col0 = 0;
   switch (c) {
-    case 0: q.map = MAP_W1; q.nkb = nk1; q.a_x = 1; break;
-    case 1: q.map = MAP_W2; break;
-    case 2: q.map = MAP_W3; q.n = 64; break;
-    case 3: q.map = MAP_W4; q.nkb = 1; break;
-    case 4: q.map = MAP_W5; break;
-    case 5: q.map = MAP_W6A; q.n = N6a; q.has_epi = N6b == 0; break;
-    case 6: q.map = MAP_W6B; q.n = N6b; q.row0 = 256; q.tcol = 256; q.wait_prev = 0; break;
-    case 7: q.map = MAP_W6T; q.nkb = N6b ? 4 : nkd; break;
-    case 8: q.map = MAP_W6T; q.nkb = nkd - 4; q.kb0 = 4; q.acc_init = 1; break;
-    case 9: q.map = MAP_W5T; break;
-    case 10: q.map = MAP_W4T; q.n = 64; break;
-    case 11: q.map = MAP_W3T; q.nkb = 1; break;
-    default: q.map = MAP_W2T; break;
+    case 0: q.map = MAP_W1; q.nkb = nk1; q.a_x = 1; q.st_map = MAP_SA1; break;
+    case 1: q.map = MAP_W2; q.st_map = MAP_SA2; break;
+    case 2: q.map = MAP_W3; q.n = 64; q.st_map = MAP_SA3; q.st_nblk = 1; break;
+    case 3: q.map = MAP_W4; q.nkb = 1; q.st_map = MAP_SA4; break;
+    case 4: q.map = MAP_W5; q.st_map = MAP_SA5; break;
+    case 5: q.map = MAP_W6A; q.n = N6a; q.has_epi = N6b == 0; q.st_map = N6b == 0 ? MAP_SG5 : -1;
+            q.st_nblk = (N6a + 63) >> 6; break;
+    case 6: q.map = MAP_W6B; q.n = N6b; q.row0 = 256; q.tcol = 256; q.wait_prev = 0; q.st_map = MAP_SG5; break;
+    case 7: q.map = MAP_W6M; q.b_mn = 1; q.nkb = N6b ? 4 : nkd; q.st_map = N6b ? MAP_SG5 : MAP_SG4;
+            q.st_nblk = N6b ? (N6b + 63) >> 6 : 4; q.st_col0 = N6b ? 256 : 0; break;
+    case 8: q.map = MAP_W6M; q.b_mn = 1; q.nkb = nkd - 4; q.kb0 = 4; q.acc_init = 1; q.st_map = MAP_SG4; break;
+    case 9: q.map = MAP_W5M; q.b_mn = 1; q.st_map = MAP_SG3; break;
+    case 10: q.map = MAP_W4M; q.b_mn = 1; q.n = 64; q.nbox = 1; q.st_map = MAP_SG2; q.st_nblk = 1; break;
+    case 11: q.map = MAP_W3M; q.b_mn = 1; q.nkb = 1; q.st_map = MAP_SG1; break;
+    default: q.map = MAP_W2M; q.b_mn = 1; q.st_map = MAP_SG0; break;
   }
   return q;
 }
@@ -100,7 +107,11 @@ __device__ __forceinline__ uint32_t mv_pack(float a, float b) {
 
 // ------------------------------------------------------------------------------------------------ kernel P
 __global__ void mv_pack_kernel(const float* __restrict__ x, const float* __restrict__ c, int B, int Bp, int D, int Cc,
-                               int K1p, __nv_bfloat16* __restrict__ out, VcAdamDeviceStep* step, float b1, float b2) {
+                               int K1p, __nv_bfloat16* __restrict__ out, __nv_bfloat16* __restrict__ g3,
+                               VcAdamDeviceStep* step, float b1, float b2) {
+  // columns [64, 128) of G3 only pad the head layer's weight-gradient tile to 128 rows: the rows kernel never writes them
+  for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < (int64_t)Bp * 8; e += (int64_t)gridDim.x * blockDim.x)
+    *reinterpret_cast<uint4*>(g3 + (e >> 3) * 128 + 64 + (e & 7) * 8) = make_uint4(0u, 0u, 0u, 0u);
   if (step && blockIdx.x == 0 && threadIdx.x == 0) {
     const int t = step->step + 1;
     step->step = t;
@@ -178,26 +189,21 @@ struct MvWorker {
     __syncwarp();
     if (lane == 0) tma::mbar_arrive(s.a_bar);
   }
-  __device__ __forceinline__ void store_chunk(const float (&v)[32], int col, __nv_bfloat16* gout, int pitch, bool smem) {
+  // 32 columns of this thread's row as bf16 into the activation buffer (swizzled K-major: the next GEMM's A operand AND
+  // the source of the TMA store that takes the rows to global memory for the weight-gradient kernel)
+  __device__ __forceinline__ void store_chunk(const float (&v)[32], int col) {
     uint32_t w[16];
 #pragma unroll
     for (int j = 0; j < 16; ++j) w[j] = mv_pack(v[2 * j], v[2 * j + 1]);
-    if (smem) {
-      unsigned char* blk = s.P + (uint32_t)(col >> 6) * MV_ABLK;
-      const uint32_t cb = (uint32_t)(col & 63) >> 3;
+    unsigned char* blk = s.P + (uint32_t)(col >> 6) * MV_ABLK;
+    const uint32_t cb = (uint32_t)(col & 63) >> 3;
 #pragma unroll
-      for (int i = 0; i < 4; ++i)
-        *reinterpret_cast<uint4*>(blk + tma::sw128((uint32_t)r, cb + i)) = make_uint4(w[4 * i], w[4 * i + 1], w[4 * i + 2], w[4 * i + 3]);
-    }
-    if (gout) {
-      uint4* g = reinterpret_cast<uint4*>(gout + (int64_t)grow * pitch + col);
-#pragma unroll
-      for (int i = 0; i < 4; ++i) g[i] = make_uint4(w[4 * i], w[4 * i + 1], w[4 * i + 2], w[4 * i + 3]);
-    }
+    for (int i = 0; i < 4; ++i)
+      *reinterpret_cast<uint4*>(blk + tma::sw128((uint32_t)r, cb + i)) = make_uint4(w[4 * i], w[4 * i + 1], w[4 * i + 2], w[4 * i + 3]);
   }
 
   template <int SLOT>
-  __device__ __forceinline__ void relu_fwd(int bias_off, __nv_bfloat16* aout) {
+  __device__ __forceinline__ void relu_fwd(int bias_off) {
     wait_acc();
 #pragma unroll 1
     for (int cc = 0; cc < 4; ++cc) {
@@ -220,13 +226,13 @@ struct MvWorker {
         }
       }
       mask[SLOT][cc] = mk;
-      store_chunk(v, col, aout, MV_H, true);
+      store_chunk(v, col);
     }
     release();
   }
 
   template <int SLOT>
-  __device__ __forceinline__ void relu_bwd(__nv_bfloat16* gout, bool smem) {
+  __device__ __forceinline__ void relu_bwd() {
     wait_acc();
 #pragma unroll 1
     for (int cc = 0; cc < 4; ++cc) {
@@ -237,14 +243,15 @@ struct MvWorker {
       const uint32_t mk = mask[SLOT][cc];
 #pragma unroll
       for (int j = 0; j < 32; ++j) v[j] = ((mk >> j) & 1u) ? v[j] : 0.f;
-      store_chunk(v, col, gout, MV_H, smem);
+      store_chunk(v, col);
     }
     release();
   }
 
   // reconstruction loss of one half of the output columns straight from the accumulators: sum (xhat - x)^2 and
   // dxhat = gs2 * (xhat - x) as bf16 rows (the A operand of the first data-gradient GEMM, and G6 for kernel B)
-  __device__ __forceinline__ void loss_half(int half) {
+  // (__noinline__: nvcc 12.9's optimizer crashes on this body when it is inlined into the unrolled epilogue sequence)
+  __device__ __noinline__ void loss_half(int half) {
     wait_acc();
     const int n = half ? a.N6b : a.N6a;
     const int cbase = half ? 256 : 0;
@@ -257,32 +264,34 @@ struct MvWorker {
       tc05::ld_32x32(tmem + cbase + col, v);
       tc05::ld_wait();
       const float* xr = a.x + (int64_t)grow * a.D + cbase + col;
+      float xv[32];
+      if (valid && a.xvec && cbase + col + 32 <= a.D) {      // 8 x 16-byte loads of the row instead of 32 scalar ones
+#pragma unroll
+        for (int j4 = 0; j4 < 8; ++j4) {
+          const float4 t = __ldg(reinterpret_cast<const float4*>(xr) + j4);
+          xv[4 * j4] = t.x; xv[4 * j4 + 1] = t.y; xv[4 * j4 + 2] = t.z; xv[4 * j4 + 3] = t.w;
+        }
+      } else {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) xv[j] = (valid && cbase + col + j < a.D) ? __ldg(xr + j) : 0.f;
+      }
 #pragma unroll
       for (int j = 0; j < 32; ++j) {
         const int gc = cbase + col + j;
         float d = 0.f;
-        if (valid && gc < a.D) d = v[j] + s.bias[1088 + gc] - __ldg(xr + j);
+        if (valid && gc < a.D) d = v[j] + s.bias[1088 + gc] - xv[j];
         sq = fmaf(d, d, sq);
         v[j] = a.gs2 * d;
       }
-      store_chunk(v, col, nullptr, 0, true);
-      {   // G6 rows have pitch 512 and absolute columns
-        uint32_t w[16];
-#pragma unroll
-        for (int j = 0; j < 16; ++j) w[j] = mv_pack(v[2 * j], v[2 * j + 1]);
-        uint4* g = reinterpret_cast<uint4*>(a.G[5] + (int64_t)grow * 512 + cbase + col);
-#pragma unroll
-        for (int i = 0; i < 4; ++i) g[i] = make_uint4(w[4 * i], w[4 * i + 1], w[4 * i + 2], w[4 * i + 3]);
-      }
+      store_chunk(v, col);
     }
     release();
   }
 
   // one bf16 element of row r into the activation buffer (k-block 0) and into a global row
-  __device__ __forceinline__ void put_elem(int col, float val, __nv_bfloat16* gout, int pitch) {
-    const __nv_bfloat16 h = __float2bfloat16_rn(val);
-    *reinterpret_cast<__nv_bfloat16*>(s.P + tma::sw128((uint32_t)r, (uint32_t)col >> 3) + ((uint32_t)col & 7u) * 2u) = h;
-    gout[(int64_t)grow * pitch + col] = h;
+  __device__ __forceinline__ void put_elem(int col, float val) {
+    *reinterpret_cast<__nv_bfloat16*>(s.P + tma::sw128((uint32_t)r, (uint32_t)col >> 3) + ((uint32_t)col & 7u) * 2u) =
+        __float2bfloat16_rn(val);
   }
 
   // heads: mu | logvar from the accumulator, z = mu + eps * exp(logvar / 2), KL row; [z | c | 0] is the decoder's input
@@ -291,56 +300,65 @@ struct MvWorker {
     wait_acc();
     if (hh == 0) {
       float h0[32];
+      float mu[Z];
+      float lv[Z];
+      float ep[Z];
       float zlo[32];
 #pragma unroll
       for (int j = 0; j < 32; ++j) zlo[j] = 0.f;
-      float* mv = a.mulv + (int64_t)grow * 64;
-      float klr = 0.f;
       tc05::ld_32x32(tmem, h0);
       tc05::ld_wait();
-      if (Z == 32) {          // mu in columns [0, 32), logvar in [32, 64)
-        float h1[32];
-        tc05::ld_32x32(tmem + 32, h1);
+#pragma unroll
+      for (int j = 0; j < Z; ++j) mu[j] = h0[j] + s.bias[512 + j];
+      if (Z == 32) {          // logvar sits in accumulator columns [32, 64)
+        tc05::ld_32x32(tmem + 32, h0);
         tc05::ld_wait();
+      }
 #pragma unroll
-        for (int j = 0; j < 32; ++j) {
-          const float mu = h0[j] + s.bias[512 + j];
-          float zz = mu;
-          if (a.variational) {
-            const float lv = h1[j] + s.bias[512 + Z + j];
-            const float e = valid ? __ldg(a.eps + (int64_t)grow * Z + j) : 0.f;
-            zz = mu + e * expf(0.5f * lv);
-            klr += 1.f + lv - mu * mu - expf(lv);
-            mv[Z + j] = lv;
-          }
-          mv[j] = mu;
-          zlo[j] = zz;
-        }
-      } else {
+      for (int j = 0; j < Z; ++j) lv[j] = a.variational ? h0[(Z + j) & 31] + s.bias[512 + Z + j] : 0.f;
 #pragma unroll
-        for (int j = 0; j < Z; ++j) {
-          const float mu = h0[j] + s.bias[512 + j];
-          float zz = mu;
-          if (a.variational) {
-            const float lv = h0[(Z + j) & 31] + s.bias[512 + Z + j];
-            const float e = valid ? __ldg(a.eps + (int64_t)grow * Z + j) : 0.f;
-            zz = mu + e * expf(0.5f * lv);
-            klr += 1.f + lv - mu * mu - expf(lv);
-            mv[Z + j] = lv;
-          }
-          mv[j] = mu;
-          zlo[j] = zz;
+      for (int j4 = 0; j4 < Z / 4; ++j4) {
+        float4 e = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (valid && a.variational) e = __ldg(reinterpret_cast<const float4*>(a.eps + (int64_t)grow * Z) + j4);
+        ep[4 * j4] = e.x; ep[4 * j4 + 1] = e.y; ep[4 * j4 + 2] = e.z; ep[4 * j4 + 3] = e.w;
+      }
+      float klr = 0.f;
+#pragma unroll
+      for (int j = 0; j < Z; ++j) {
+        float zz = mu[j];
+        if (a.variational) {
+          zz = mu[j] + ep[j] * expf(0.5f * lv[j]);
+          klr += 1.f + lv[j] - mu[j] * mu[j] - expf(lv[j]);
         }
+        if (Z <= 32) zlo[j & 31] = zz;
       }
       if (valid) kl += -0.5f * klr;
-      store_chunk(zlo, 0, a.A[3], 64, true);
+      float4* mv = reinterpret_cast<float4*>(a.mulv + (int64_t)grow * 64);
+#pragma unroll
+      for (int j4 = 0; j4 < Z / 4; ++j4) {
+        mv[j4] = make_float4(mu[4 * j4], mu[4 * j4 + 1], mu[4 * j4 + 2], mu[4 * j4 + 3]);
+        mv[Z / 4 + j4] = make_float4(lv[4 * j4], lv[4 * j4 + 1], lv[4 * j4 + 2], lv[4 * j4 + 3]);
+      }
+      store_chunk(zlo, 0);
 #pragma unroll
       for (int j = 0; j < 32; ++j) zlo[j] = 0.f;
-      store_chunk(zlo, 32, a.A[3], 64, true);
+      store_chunk(zlo, 32);
       // the conditioning vector follows z (19:110-115); Z + Cc <= 64
-      for (int j = 0; j < a.Cc; ++j) put_elem(Z + j, valid ? __ldg(a.c + (int64_t)grow * a.Cc + j) : 0.f, a.A[3], 64);
+      for (int j = 0; j < a.Cc; ++j) put_elem(Z + j, valid ? __ldg(a.c + (int64_t)grow * a.Cc + j) : 0.f);
     }
     release();
+  }
+
+  template <int Z>
+  __device__ __forceinline__ void one(int j, float dzj, float e, float mu, float lv, float (&glo)[32], float (&ghi)[32]) {
+    if (a.variational) {
+      const float dmu = valid ? dzj + a.ks * mu : 0.f;
+      const float dlv = valid ? dzj * e * 0.5f * expf(0.5f * lv) + a.ks * 0.5f * (expf(lv) - 1.f) : 0.f;
+      glo[j] = dmu;
+      if (Z + j < 32) glo[(Z + j) & 31] = dlv; else ghi[(Z + j) & 31] = dlv;
+    } else {
+      glo[j] = valid ? dzj : 0.f;
+    }
   }
 
   // backward of the reparameterisation + KL (12:168-172 / 19:105-108,124-126): G3 = [dmu | dlogvar] (or dz for the AE)
@@ -354,27 +372,19 @@ struct MvWorker {
       float glo[32], ghi[32];
 #pragma unroll
       for (int j = 0; j < 32; ++j) { glo[j] = 0.f; ghi[j] = 0.f; }
-      const float* mv = a.mulv + (int64_t)grow * 64;
+      const float4* mv = reinterpret_cast<const float4*>(a.mulv + (int64_t)grow * 64);
 #pragma unroll
-      for (int j = 0; j < Z; ++j) {
-        const float dzj = d0[j];
-        if (a.variational) {
-          const float mu = mv[j], lv = mv[Z + j];
-          const float e = valid ? __ldg(a.eps + (int64_t)grow * Z + j) : 0.f;
-          const float dmu = valid ? dzj + a.ks * mu : 0.f;
-          const float dlv = valid ? dzj * e * 0.5f * expf(0.5f * lv) + a.ks * 0.5f * (expf(lv) - 1.f) : 0.f;
-          glo[j] = dmu;
-          if (Z + j < 32) glo[(Z + j) & 31] = dlv; else ghi[(Z + j) & 31] = dlv;
-        } else {
-          glo[j] = valid ? dzj : 0.f;
-        }
+      for (int j4 = 0; j4 < Z / 4; ++j4) {
+        float4 e = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (valid && a.variational) e = __ldg(reinterpret_cast<const float4*>(a.eps + (int64_t)grow * Z) + j4);
+        const float4 m4 = mv[j4], l4 = mv[Z / 4 + j4];
+        one<Z>(4 * j4 + 0, d0[4 * j4 + 0], e.x, m4.x, l4.x, glo, ghi);
+        one<Z>(4 * j4 + 1, d0[4 * j4 + 1], e.y, m4.y, l4.y, glo, ghi);
+        one<Z>(4 * j4 + 2, d0[4 * j4 + 2], e.z, m4.z, l4.z, glo, ghi);
+        one<Z>(4 * j4 + 3, d0[4 * j4 + 3], e.w, m4.w, l4.w, glo, ghi);
       }
-      store_chunk(glo, 0, a.G[2], 128, true);
-      store_chunk(ghi, 32, a.G[2], 128, true);
-      // columns [64, 128) of G3 only pad the weight-gradient tile to 128 rows: keep them zero
-      uint4* gz = reinterpret_cast<uint4*>(a.G[2] + (int64_t)grow * 128 + 64);
-#pragma unroll
-      for (int i = 0; i < 8; ++i) gz[i] = make_uint4(0u, 0u, 0u, 0u);
+      store_chunk(glo, 0);
+      store_chunk(ghi, 32);
     }
     release();
   }
@@ -422,12 +432,18 @@ mv_rows_kernel(const MvRowsArgs a, const __grid_constant__ MvMaps maps) {
       for (int tile = blockIdx.x; tile < a.ntiles; tile += gridDim.x)
         for (int p = 0; p < a.nph; ++p) {
           const MvPhase ph = mv_phase(p, a.nk1, a.N6a, a.N6b, a.nkd);
-          const uint32_t bytes = (uint32_t)ph.n * 128u;
+          const uint32_t bytes = ph.b_mn ? (uint32_t)ph.nbox * 8192u : (uint32_t)ph.n * 128u;
           for (int kb = 0; kb < ph.nkb; ++kb, ++it) {
             const uint32_t st = it % MV_WS;
             tma::mbar_wait(&s.wempty[st], ((it / MV_WS) & 1u) ^ 1u);
             tma::mbar_expect_tx(&s.wfull[st], bytes);
-            tma::load_2d(s.WR + st * MV_WSTAGE, &maps.m[ph.map], &s.wfull[st], (ph.kb0 + kb) * 64, ph.row0);
+            unsigned char* dst = s.WR + st * MV_WSTAGE;
+            if (ph.b_mn) {   // [64 out-features (k)][64 in-features (n)] boxes of the row-major shadow: MN-major B operand
+              for (int b = 0; b < ph.nbox; ++b)
+                tma::load_2d(dst + b * 8192, &maps.m[ph.map], &s.wfull[st], 64 * b, (ph.kb0 + kb) * 64);
+            } else {
+              tma::load_2d(dst, &maps.m[ph.map], &s.wfull[st], (ph.kb0 + kb) * 64, ph.row0);
+            }
           }
         }
     } else if (lane == 1) {
@@ -442,20 +458,29 @@ mv_rows_kernel(const MvRowsArgs a, const __grid_constant__ MvMaps maps) {
         }
     }
   } else if (warp == 1) {
-    // ===================== MMA issuer =====================
+    // ===================== MMA issuer (also issues the TMA stores of what the epilogues leave in P) ==============
     if (lane == 0) {
       uint32_t wit = 0, xit = 0, a_cnt = 0;
       bool first = true;
+      int st_map = -1, st_nblk = 0, st_col0 = 0, st_row = 0;     // pending store: output of the previous epilogue
       for (int tile = blockIdx.x; tile < a.ntiles; tile += gridDim.x)
         for (int p = 0; p < a.nph; ++p) {
           const MvPhase ph = mv_phase(p, a.nk1, a.N6a, a.N6b, a.nkd);
+          bool stored = false;
           if (ph.wait_prev && !first) {
             tma::mbar_wait(s.a_bar, a_cnt & 1u);
             ++a_cnt;
             tc05::fence_after();
+            if (st_map >= 0) {     // P now holds the rows of the previous phase: send them to global memory
+              for (int b = 0; b < st_nblk; ++b)
+                tma::store_2d(&maps.m[st_map], s.P + (uint32_t)b * MV_ABLK, st_col0 + 64 * b, st_row);
+              tma::bulk_commit();
+              stored = true;
+              st_map = -1;
+            }
           }
           first = false;
-          const uint32_t idesc = tc05::idesc(tc05::kFmtBF16, 128, ph.n, 0, 0);
+          const uint32_t idesc = tc05::idesc(tc05::kFmtBF16, 128, ph.n, 0, ph.b_mn);
           for (int kb = 0; kb < ph.nkb; ++kb, ++wit) {
             const uint32_t st = wit % MV_WS;
             uint32_t sa;
@@ -470,14 +495,30 @@ mv_rows_kernel(const MvRowsArgs a, const __grid_constant__ MvMaps maps) {
             tc05::fence_after();
             const uint32_t sb = tma::s32(s.WR + st * MV_WSTAGE);
 #pragma unroll
-            for (int kk = 0; kk < 4; ++kk)
-              tc05::mma_bf16(tmem_base + ph.tcol, tc05::desc_k_sw128(sa + kk * 32), tc05::desc_k_sw128(sb + kk * 32), idesc,
+            for (int kk = 0; kk < 4; ++kk) {
+              const uint64_t db = ph.b_mn ? tc05::desc_mn_sw128(sb + kk * 2048, 8192) : tc05::desc_k_sw128(sb + kk * 32);
+              tc05::mma_bf16(tmem_base + ph.tcol, tc05::desc_k_sw128(sa + kk * 32), db, idesc,
                              (uint32_t)((ph.acc_init | kb | kk) != 0));
+            }
             tc05::commit(&s.wempty[st]);
             if (ph.a_x) { tc05::commit(&s.xempty[xit % MV_XS]); ++xit; }
           }
-          if (ph.has_epi) tc05::commit(s.acc_bar);
+          // the epilogue of THIS phase overwrites P: the store issued above must have finished reading it
+          if (stored) tma::bulk_wait_read0();
+          if (ph.has_epi) {
+            tc05::commit(s.acc_bar);
+            st_map = ph.st_map; st_nblk = ph.st_nblk; st_col0 = ph.st_col0; st_row = tile * 128;
+          }
         }
+      if (!first) {          // rows of the very last epilogue
+        tma::mbar_wait(s.a_bar, a_cnt & 1u);
+        if (st_map >= 0) {
+          for (int b = 0; b < st_nblk; ++b)
+            tma::store_2d(&maps.m[st_map], s.P + (uint32_t)b * MV_ABLK, st_col0 + 64 * b, st_row);
+          tma::bulk_commit();
+        }
+      }
+      tma::bulk_wait0();     // every store of this CTA has landed before the kernel ends
     }
   } else {
     // ===================== workers: the epilogue of every phase =====================
@@ -492,18 +533,18 @@ mv_rows_kernel(const MvRowsArgs a, const __grid_constant__ MvMaps maps) {
       w.grow = tile * 128 + w.r;
       w.valid = w.grow < a.B;
       w.sq = 0.f; w.kl = 0.f;
-      w.template relu_fwd<0>(0, a.A[1]);
-      w.template relu_fwd<1>(256, a.A[2]);
+      w.template relu_fwd<0>(0);
+      w.template relu_fwd<1>(256);
       w.template heads<Z>();
-      w.template relu_fwd<2>(576, a.A[4]);
-      w.template relu_fwd<3>(832, a.A[5]);
+      w.template relu_fwd<2>(576);
+      w.template relu_fwd<3>(832);
       w.loss_half(0);
       if (a.N6b > 0) w.loss_half(1);
-      w.template relu_bwd<3>(a.G[4], true);
-      w.template relu_bwd<2>(a.G[3], true);
+      w.template relu_bwd<3>();
+      w.template relu_bwd<2>();
       w.template dz<Z>();
-      w.template relu_bwd<1>(a.G[1], true);
-      w.template relu_bwd<0>(a.G[0], false);
+      w.template relu_bwd<1>();
+      w.template relu_bwd<0>();
       // tile loss partials, fixed order: lanes -> warp (shuffle tree), 8 warps -> thread of warp 2
       const double sqw = warp_sum((double)w.sq), klw = warp_sum((double)w.kl);
       if (lane == 0) { s.red[2 * (warp - 2)] = sqw; s.red[2 * (warp - 2) + 1] = klw; }
@@ -661,9 +702,8 @@ struct MvLayerDesc {
   int nout, kin, kp, mpad;       // true dims, padded in-dim (= pitch of partial rows and of the forward shadow), padded rows
   int split;                     // rows >= split belong to the second parameter tensor (heads: logvar), else nout
   int poff, boff;                // offsets in the padded flat layouts
-  int tpitch;                    // pitch of the transposed shadow (0: none)
   int p0, p1;                    // parameter indices (MvParams) of the two tensors
-  __nv_bfloat16* wp; __nv_bfloat16* wt;
+  __nv_bfloat16* wp;
 };
 struct MvAdamArgs {
   MvLayerDesc L[6];
@@ -712,11 +752,7 @@ __global__ void __launch_bounds__(256) mv_adam_kernel(const MvAdamArgs a) {
       mv_adam1(p, m, v, g, a.b1, a.b2, a.eps, step_size, inv_sqrt_bc2);
       T.p[idx] = p; T.m[idx] = m; T.v[idx] = v;
     }
-    if (a.do_shadow) {
-      const __nv_bfloat16 h = __float2bfloat16_rn(p);
-      L.wp[(int64_t)o * L.kp + i] = h;
-      if (L.wt) L.wt[(int64_t)i * L.tpitch + o] = h;
-    }
+    if (a.do_shadow) L.wp[(int64_t)o * L.kp + i] = __float2bfloat16_rn(p);
   }
   if (blockIdx.x == 0)
     for (int o = threadIdx.x; o < L.mpad; o += blockDim.x) {
@@ -756,9 +792,9 @@ struct MvPlan {
   int D, Cc, Z, NH, variational, mode;
   int K1, K1p, nk1, N6a, N6b, B, Bp, ntiles;
   // workspace offsets (bytes)
-  size_t o_wp[6], o_wt[6], o_A[6], o_G[6], o_mulv, o_tile, o_part, o_bpart, o_gflat, o_gbflat, total;
+  size_t o_wp[6], o_A[6], o_G[6], o_mulv, o_tile, o_part, o_bpart, o_gflat, o_gbflat, total;
   size_t persist_bytes;          // shadows live in [0, persist_bytes)
-  int kin[6], nout[6], kp[6], mpad[6], poff[6], boff[6], apitch[6], gpitch[6], tpitch[6];
+  int kin[6], nout[6], kp[6], mpad[6], poff[6], boff[6], apitch[6], gpitch[6];
   int64_t ptot, btot;
   int nsplit, nkbB, kbs;
   MvwTile tiles[MVW_MAXT];
@@ -786,19 +822,17 @@ static MvPlan mv_plan(const VcMlpVaeDesc* d, int B) {
   const int nout[6] = {256, 256, p.NH, 256, 256, p.D};
   const int kp[6] = {p.K1p, 256, 256, 64, 256, 256};
   const int mpad[6] = {256, 256, 128, 256, 256, (p.D + 127) / 128 * 128};
-  const int wrows[6] = {256, 256, 64, 256, 256, 512};          // rows of the forward shadow
-  const int tpitch[6] = {0, 256, 64, 256, 256, 512};            // transposed shadow [kp][tpitch]
+  const int wrows[6] = {256, 256, 64, 256, 256, 512};          // rows of the bf16 shadow (zero padded)
   const int apitch[6] = {p.K1p, 256, 256, 64, 256, 256};
   const int gpitch[6] = {256, 256, 128, 256, 256, 512};
   size_t o = 0;
   int poff = 0, boff = 0;
   for (int l = 0; l < 6; ++l) {
-    p.kin[l] = kin[l]; p.nout[l] = nout[l]; p.kp[l] = kp[l]; p.mpad[l] = mpad[l]; p.tpitch[l] = tpitch[l];
+    p.kin[l] = kin[l]; p.nout[l] = nout[l]; p.kp[l] = kp[l]; p.mpad[l] = mpad[l];
     p.apitch[l] = apitch[l]; p.gpitch[l] = gpitch[l];
     p.poff[l] = poff; poff += mpad[l] * kp[l];
     p.boff[l] = boff; boff += mpad[l];
     p.o_wp[l] = o; o = mv_al(o + (size_t)wrows[l] * kp[l] * 2);
-    p.o_wt[l] = o; if (tpitch[l]) o = mv_al(o + (size_t)kp[l] * tpitch[l] * 2);
   }
   p.persist_bytes = o;
   p.ptot = poff; p.btot = boff;
@@ -848,11 +882,10 @@ static void mv_fill_adam_args(MvAdamArgs& c, const MvPlan& p, const VcMlpVaePara
     MvLayerDesc& L = c.L[l];
     L.nout = p.nout[l]; L.kin = p.kin[l]; L.kp = p.kp[l]; L.mpad = p.mpad[l];
     L.split = (l == 2 && p.variational) ? p.Z : p.nout[l];
-    L.poff = p.poff[l]; L.boff = p.boff[l]; L.tpitch = p.tpitch[l];
+    L.poff = p.poff[l]; L.boff = p.boff[l];
     L.p0 = l < 2 ? l : (l == 2 ? 2 : l + 1);
     L.p1 = l == 2 ? 3 : L.p0;
     L.wp = reinterpret_cast<__nv_bfloat16*>(w + p.o_wp[l]);
-    L.wt = p.tpitch[l] ? reinterpret_cast<__nv_bfloat16*>(w + p.o_wt[l]) : nullptr;
   }
   for (int i = 0; i < 7; ++i) {
     c.prm.W[i].p = prm->W[i].p; c.prm.W[i].m = prm->W[i].m; c.prm.W[i].v = prm->W[i].v;
@@ -906,7 +939,7 @@ extern "C" int vc_mlpvae_prepare(const VcMlpVaeDesc* d, const VcMlpVaeParams* pr
   c.do_fold = 0; c.do_adam = 0; c.do_shadow = 1;
   VC_CUDA(cudaMemsetAsync(w + p.o_gflat, 0, (size_t)p.ptot * 4, s));
   VC_CUDA(cudaMemsetAsync(w + p.o_gbflat, 0, (size_t)p.btot * 4, s));
-  mv_adam_kernel<<<dim3(32, 6), 256, 0, s>>>(c);
+  mv_adam_kernel<<<dim3(64, 6), 256, 0, s>>>(c);
   VC_LAUNCH_CHECK();
   return VC_OK;
 }
@@ -930,7 +963,8 @@ extern "C" int vc_mlpvae_step(const VcMlpVaeDesc* d, const VcMlpVaeParams* prm, 
       const int64_t total = (int64_t)p.Bp * (p.K1p / 8);
       int blocks = (int)((total + 255) / 256);
       if (blocks > 8 * sm_count()) blocks = 8 * sm_count();
-      mv_pack_kernel<<<blocks, 256, 0, s>>>(x, c, B, p.Bp, p.D, p.Cc, p.K1p, bf(p.o_A[0]), step_state, beta1, beta2);
+      mv_pack_kernel<<<blocks, 256, 0, s>>>(x, c, B, p.Bp, p.D, p.Cc, p.K1p, bf(p.o_A[0]), bf(p.o_G[2]), step_state, beta1,
+                                            beta2);
       VC_LAUNCH_CHECK();
     }
     // ---- A: forward + loss + data gradients per 128-row tile
@@ -949,11 +983,13 @@ extern "C" int vc_mlpvae_step(const VcMlpVaeDesc* d, const VcMlpVaeParams* prm, 
     mk(MAP_W5, p.o_wp[4], 256, 256, 256, 256);
     mk(MAP_W6A, p.o_wp[5], 256, 512, 256, p.N6a);
     mk(MAP_W6B, p.o_wp[5], 256, 512, 256, p.N6b ? p.N6b : 16);
-    mk(MAP_W6T, p.o_wt[5], 512, 256, 512, 256);
-    mk(MAP_W5T, p.o_wt[4], 256, 256, 256, 256);
-    mk(MAP_W4T, p.o_wt[3], 256, 64, 256, 64);
-    mk(MAP_W3T, p.o_wt[2], 64, 256, 64, 256);
-    mk(MAP_W2T, p.o_wt[1], 256, 256, 256, 256);
+    mk(MAP_W6M, p.o_wp[5], 256, 512, 256, 64);
+    mk(MAP_W5M, p.o_wp[4], 256, 256, 256, 64);
+    mk(MAP_W4M, p.o_wp[3], 64, 256, 64, 64);
+    mk(MAP_W3M, p.o_wp[2], 256, 64, 256, 64);
+    mk(MAP_W2M, p.o_wp[1], 256, 256, 256, 64);
+    for (int l = 1; l < 6; ++l) mk(MAP_SA1 + (l - 1), p.o_A[l], p.apitch[l], p.Bp, p.apitch[l], 128);
+    for (int l = 0; l < 6; ++l) mk(MAP_SG0 + l, p.o_G[l], p.gpitch[l], p.Bp, p.gpitch[l], 128);
     if (rc != VC_OK) return rc;
     const int nkd = (p.D + 63) / 64;                 // k-blocks of dxhat
     a.nkd = nkd;
@@ -967,7 +1003,7 @@ extern "C" int vc_mlpvae_step(const VcMlpVaeDesc* d, const VcMlpVaeParams* prm, 
     a.x = x; a.c = c; a.eps = eps;
     a.bias[0] = prm->b[0].p; a.bias[1] = prm->b[1].p; a.bias[2] = prm->b[2].p; a.bias_lv = prm->b[3].p;
     a.bias[3] = prm->b[4].p; a.bias[4] = prm->b[5].p; a.bias[5] = prm->b[6].p;
-    for (int l = 0; l < 6; ++l) { a.A[l] = bf(p.o_A[l]); a.G[l] = bf(p.o_G[l]); }
+    a.xvec = (p.D % 4 == 0 && (reinterpret_cast<uintptr_t>(x) & 15) == 0) ? 1 : 0;
     a.mulv = reinterpret_cast<float*>(w + p.o_mulv);
     a.tile_part = reinterpret_cast<double*>(w + p.o_tile);
     int grid = p.ntiles < sm_count() ? p.ntiles : sm_count();
@@ -1022,7 +1058,7 @@ extern "C" int vc_mlpvae_step(const VcMlpVaeDesc* d, const VcMlpVaeParams* prm, 
     ca.ntiles = p.ntiles; ca.B = B; ca.D = p.D; ca.Z = p.Z; ca.mode = p.mode; ca.variational = p.variational;
     ca.beta = d->beta;
     ca.out3 = (phases & 2) ? out3 : nullptr;
-    mv_adam_kernel<<<dim3(32, 6), 256, 0, s>>>(ca);
+    mv_adam_kernel<<<dim3(64, 6), 256, 0, s>>>(ca);
     VC_LAUNCH_CHECK();
   }
   return VC_OK;

@@ -118,6 +118,19 @@ __device__ __forceinline__ void load_5d(void* dst, const CUtensorMap* m, uint64_
       : "memory");
 }
 
+// shared -> global tile store (bulk async-group completion): the smem tile must have been written by the generic proxy
+// and fenced with fence.proxy.async before the issuing thread learns about it
+__device__ __forceinline__ void store_2d(const CUtensorMap* m, const void* src, int c0, int c1) {
+  asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];" ::"l"(m), "r"(s32(src)),
+               "r"(c0), "r"(c1)
+               : "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+// all committed bulk groups of this thread have finished READING their shared-memory source
+__device__ __forceinline__ void bulk_wait_read0() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+// ... and have completed entirely (writes visible)
+__device__ __forceinline__ void bulk_wait0() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+
 // Byte offset of 16-byte chunk `c` (0..7) of row `r` inside a [rows][128 B] tile written by TMA with
 // CU_TENSOR_MAP_SWIZZLE_128B (tile base 1024-byte aligned): the chunk index is XORed with the row index mod 8.
 __device__ __forceinline__ uint32_t sw128(uint32_t r, uint32_t c) { return r * 128u + ((c ^ (r & 7u)) << 4); }
