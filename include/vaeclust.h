@@ -205,6 +205,9 @@ typedef struct VcMlpVaeParams {
   VcMlpTensor b[7];
 } VcMlpVaeParams;
 int vc_mlpvae_supported(const VcMlpVaeDesc* desc);
+/* debug / profiling hook: a device buffer of >= 128 int64 receives clock64 stamps of the rows kernel's first tile
+ * (NULL switches it off again); see profiles/trace_fused.py */
+int vc_mlpvae_debug_trace(int64_t* device_buffer);
 size_t vc_mlpvae_workspace_bytes(const VcMlpVaeDesc* desc, int B);
 /* out[0] = byte offset (from the workspace pointer rounded up to 1024) of the flat fp32 gradient block, out[1] = its
  * element count; then for each of the 6 layers (heads = mu rows then logvar rows): weight offset in elements, row

@@ -22,6 +22,7 @@
 //                        all-reduce and for parity checks.
 //
 // Layers: 0 enc.0  1 enc.2  2 heads [mu ; logvar] (or the AE's single z head)  3 dec.0  4 dec.2  5 dec.4 / out.
+#include <stdlib.h>
 #include <string.h>
 #include "common.cuh"
 #include "tc05.cuh"
@@ -29,11 +30,14 @@
 namespace vc {
 
 constexpr int MV_H = 256;                       // hidden width the fused path supports
-constexpr int MV_THREADS = 320;                 // warp 0: TMA producers, warp 1: MMA issuer + TMEM, warps 2..9: workers
+constexpr int MV_NWORK = 16;                    // worker (epilogue) warps: 4 lane quarters x 4 column blocks of 64
+constexpr int MV_THREADS = 64 + 32 * MV_NWORK;  // warp 0: TMA producers, warp 1: MMA issuer + TMEM, then the workers
 constexpr uint32_t MV_ABLK = 128 * 128;         // one K-major A k-block: [128 rows][64 bf16]
 constexpr uint32_t MV_WSTAGE = 256 * 128;       // one weight k-block: [<=256 rows][64 bf16]
-constexpr int MV_XS = 3, MV_WS = 3;             // ring depths
-constexpr int MV_NBIAS = 1600;                  // b1 256 | b2 256 | b3 64 | b4 256 | b5 256 | b6 512
+constexpr int MV_XS = 2, MV_WS = 4;             // ring depths: 4 weight stages hold one whole 256-wide layer, so the
+                                                // weights of phase p+1 arrive while phase p computes
+constexpr int MV_NBIAS = 64;                    // head biases (mu | logvar) in shared memory; the others are read through
+                                                // the read-only path (warp-uniform 16-byte loads) to leave room for the ring
 
 enum { EPI_NONE = 0, EPI_RELU_F, EPI_HEADS, EPI_LOSS_A, EPI_LOSS_B, EPI_RELU_B, EPI_DZ };
 // tensor maps of the rows kernel: the packed input, the forward weight shadows as K-major boxes (64 k x N rows), the
@@ -46,9 +50,10 @@ enum { MAP_X = 0, MAP_W1, MAP_W2, MAP_W3, MAP_W4, MAP_W5, MAP_W6A, MAP_W6B, MAP_
 struct MvMaps { CUtensorMap m[MAP_COUNT]; };
 
 struct MvPhase {
-  int map, nkb, kb0, n, row0, a_x, tcol, acc_init, has_epi, wait_prev;
+  int map, nkb, kb0, n, row0, a_x, tcol, acc_init, has_epi;
   int b_mn, nbox;                 // data-gradient phases: weights as MN-major boxes, nbox = n / 64 per k-block
   int st_map, st_nblk, st_col0;   // what the phase's epilogue leaves in P and where it goes (TMA store), -1: nothing
+  int wait_all;                   // the accumulator buffer is the one the previous epilogue drains: wait for all of it
 };
 
 struct MvTensor { float* p; float* m; float* v; };
@@ -60,16 +65,20 @@ struct MvRowsArgs {
   float gs2;        // 2 * d(loss)/d(sum of squared errors)
   float ks;         // d(loss)/d(kl row sum)
   const float* x; const float* c; const float* eps;
-  const float* bias[6];                   // fp32 biases of the 6 layers (heads: mu then logvar via bias3b)
+  const float* bias[6];                   // fp32 biases of the 6 layers (heads: mu, then logvar via bias_lv)
   const float* bias_lv;
   float* mulv;                            // [Bp][64] fp32: mu | logvar of the row (re-read by the backward)
   double* tile_part;                      // [ntiles][2]: sum of squared errors, sum of KL rows
+  long long* trace;                       // debug: clock64 stamps of CTA 0 ([phase][4]), or NULL
+  int dbg;                                // debug experiments (timing only): bit 0 = skip the TMA stores
 };
 
 // The GEMM phases of one tile, in issue order (canonical numbering for D > 256, where the output layer and the first
 // data-gradient GEMM are split in two because dxhat has more k-blocks than the activation buffer):
 //   0 enc.0   1 enc.2   2 heads   3 dec.0   4 dec.2   5 out[:, :256]   6 out[:, 256:]   7 dd2 from dxhat[:, :256]
 //   8 dd2 += dxhat[:, 256:]   9 dd1   10 dz   11 dh2   12 dh1
+// Accumulators alternate between the two 256-column halves of tensor memory, so that the MMAs of phase p+1 can start
+// on the first k-blocks the epilogue of phase p has produced while that epilogue is still draining the other half.
 // Computed arithmetically (no table): a dynamically indexed kernel-parameter array would be copied to local memory.
 __device__ __forceinline__ MvPhase mv_phase(int p, int nk1, int N6a, int N6b, int nkd) {
   int c = p;
@@ -78,24 +87,26 @@ __device__ __forceinline__ MvPhase mv_phase(int p, int nk1, int N6a, int N6b, in
     if (c >= 8) c = c + 1;
   }
   MvPhase q;
-  q.kb0 = 0; q.row0 = 0; q.a_x = 0; q.tcol = 0; q.acc_init = 0; q.has_epi = 1; q.wait_prev = 1; q.n = 256; q.nkb = 4;
-  q.b_mn = 0; q.nbox = 4; q.st_nblk = 4; q.st_col0 = 0;
+  q.kb0 = 0; q.row0 = 0; q.a_x = 0; q.tcol = 0; q.acc_init = 0; q.has_epi = 1; q.n = 256; q.nkb = 4;
+  q.b_mn = 0; q.nbox = 4; q.st_nblk = 4; q.st_col0 = 0; q.wait_all = 0;
+  const bool two = N6b != 0;
   switch (c) {
-    case 0: q.map = MAP_W1; q.nkb = nk1; q.a_x = 1; q.st_map = MAP_SA1; break;
-    case 1: q.map = MAP_W2; q.st_map = MAP_SA2; break;
+    case 0: q.map = MAP_W1; q.nkb = nk1; q.a_x = 1; q.st_map = MAP_SA1; q.wait_all = 1; break;
+    case 1: q.map = MAP_W2; q.tcol = 256; q.st_map = MAP_SA2; break;
     case 2: q.map = MAP_W3; q.n = 64; q.st_map = MAP_SA3; q.st_nblk = 1; break;
-    case 3: q.map = MAP_W4; q.nkb = 1; q.st_map = MAP_SA4; break;
+    case 3: q.map = MAP_W4; q.nkb = 1; q.tcol = 256; q.st_map = MAP_SA4; break;
     case 4: q.map = MAP_W5; q.st_map = MAP_SA5; break;
-    case 5: q.map = MAP_W6A; q.n = N6a; q.has_epi = N6b == 0; q.st_map = N6b == 0 ? MAP_SG5 : -1;
+    case 5: q.map = MAP_W6A; q.n = N6a; q.tcol = 256; q.has_epi = !two; q.st_map = two ? -1 : MAP_SG5;
             q.st_nblk = (N6a + 63) >> 6; break;
-    case 6: q.map = MAP_W6B; q.n = N6b; q.row0 = 256; q.tcol = 256; q.wait_prev = 0; q.st_map = MAP_SG5; break;
-    case 7: q.map = MAP_W6M; q.b_mn = 1; q.nkb = N6b ? 4 : nkd; q.st_map = N6b ? MAP_SG5 : MAP_SG4;
-            q.st_nblk = N6b ? (N6b + 63) >> 6 : 4; q.st_col0 = N6b ? 256 : 0; break;
-    case 8: q.map = MAP_W6M; q.b_mn = 1; q.nkb = nkd - 4; q.kb0 = 4; q.acc_init = 1; q.st_map = MAP_SG4; break;
-    case 9: q.map = MAP_W5M; q.b_mn = 1; q.st_map = MAP_SG3; break;
-    case 10: q.map = MAP_W4M; q.b_mn = 1; q.n = 64; q.nbox = 1; q.st_map = MAP_SG2; q.st_nblk = 1; break;
-    case 11: q.map = MAP_W3M; q.b_mn = 1; q.nkb = 1; q.st_map = MAP_SG1; break;
-    default: q.map = MAP_W2M; q.b_mn = 1; q.st_map = MAP_SG0; break;
+    case 6: q.map = MAP_W6B; q.n = N6b; q.row0 = 256; q.tcol = 0; q.st_map = MAP_SG5; break;   // after 5: dec.2 is drained
+    case 7: q.map = MAP_W6M; q.b_mn = 1; q.nkb = two ? 4 : nkd; q.st_map = two ? MAP_SG5 : MAP_SG4;
+            q.st_nblk = two ? (N6b + 63) >> 6 : 4; q.st_col0 = two ? 256 : 0;
+            q.tcol = two ? 256 : 0; q.wait_all = two ? 1 : 0; break;      // two: the loss epilogue drains buffer 256
+    case 8: q.map = MAP_W6M; q.b_mn = 1; q.nkb = nkd - 4; q.kb0 = 4; q.acc_init = 1; q.tcol = 256; q.st_map = MAP_SG4; break;
+    case 9: q.map = MAP_W5M; q.b_mn = 1; q.tcol = two ? 0 : 256; q.st_map = MAP_SG3; break;
+    case 10: q.map = MAP_W4M; q.b_mn = 1; q.n = 64; q.nbox = 1; q.tcol = two ? 256 : 0; q.st_map = MAP_SG2; q.st_nblk = 1; break;
+    case 11: q.map = MAP_W3M; q.b_mn = 1; q.nkb = 1; q.tcol = two ? 0 : 256; q.st_map = MAP_SG1; break;
+    default: q.map = MAP_W2M; q.b_mn = 1; q.tcol = two ? 256 : 0; q.st_map = MAP_SG0; break;
   }
   return q;
 }
@@ -145,9 +156,11 @@ struct MvSmem {
   unsigned char* WR;     // MV_WS stages
   float* bias;
   uint64_t* wfull; uint64_t* wempty; uint64_t* xfull; uint64_t* xempty;
-  uint64_t* acc_bar; uint64_t* a_bar;
+  uint64_t* acc_bar;     // accumulator of the current phase complete (tcgen05.commit)
+  uint64_t* kready;      // [4]: k-block j of P written by the epilogue (4 warps each)
+  uint64_t* pfree;       // the TMA stores of the previous epilogue's rows have finished reading P
   uint32_t* tmem_slot;
-  double* red;           // [8][2]
+  double* red;           // [MV_NWORK][2]
 };
 
 __device__ __forceinline__ MvSmem mv_carve(unsigned char* raw) {
@@ -159,63 +172,148 @@ __device__ __forceinline__ MvSmem mv_carve(unsigned char* raw) {
   s.bias = reinterpret_cast<float*>(s.WR + MV_WS * MV_WSTAGE);
   uint64_t* bars = reinterpret_cast<uint64_t*>(s.bias + MV_NBIAS);
   s.wfull = bars; s.wempty = bars + MV_WS; s.xfull = bars + 2 * MV_WS; s.xempty = bars + 2 * MV_WS + MV_XS;
-  s.acc_bar = bars + 2 * MV_WS + 2 * MV_XS; s.a_bar = s.acc_bar + 1;
-  s.red = reinterpret_cast<double*>(s.a_bar + 1);
-  s.tmem_slot = reinterpret_cast<uint32_t*>(s.red + 16);
+  s.acc_bar = bars + 2 * MV_WS + 2 * MV_XS; s.kready = s.acc_bar + 1;
+  s.pfree = s.kready + 4;
+  s.red = reinterpret_cast<double*>(s.pfree + 1);
+  s.tmem_slot = reinterpret_cast<uint32_t*>(s.red + 2 * MV_NWORK);
   return s;
 }
 constexpr size_t MV_SMEM_BYTES = 1024 + 4 * MV_ABLK + MV_XS * MV_ABLK + MV_WS * MV_WSTAGE + MV_NBIAS * 4 +
-                                 (2 * MV_WS + 2 * MV_XS + 2) * 8 + 16 * 8 + 16;
+                                 (2 * MV_WS + 2 * MV_XS + 6) * 8 + 2 * MV_NWORK * 8 + 16;
+
+__device__ __forceinline__ float4 mv_lds4(uint32_t addr) {
+  float4 v;
+  asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr));
+  return v;
+}
+__device__ __forceinline__ void mv_sts4(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+  asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
+}
+// this warp's part of k-block `blk` of P is written (and the accumulator columns it came from are in registers): tell
+// the issuer, which may start the next GEMM on that block and send it to global memory
+__device__ __forceinline__ void mv_block_done(uint64_t* kready, int blk, int lane) {
+  tc05::fence_before();
+  tma::fence_proxy_async();
+  __syncwarp();
+  if (lane == 0) tma::mbar_arrive(&kready[blk]);
+}
+
+// Loss epilogue of one half (<= 256 columns) of the output layer for ONE thread (row r, column chunks 2*hh, 2*hh+1):
+// xhat = accumulator + bias, d = xhat - x (fp32 x straight from global memory, 16-byte loads, the next chunk's loads in
+// flight while the current one is reduced), sum of d^2 returned, dxhat = gs2 * d stored as bf16 into the activation
+// buffer P (the A operand of the first data-gradient GEMM and the source of the G6 TMA store).  Everything arrives by
+// value and the function is NOT inlined: nvcc 12.9's optimizer crashes when this body is merged into the unrolled
+// epilogue sequence of the caller.
+__device__ __noinline__ float mv_loss_half(uint32_t tmem, uint32_t sP, const float* bias6, const float* xrow, int ncols,
+                                           int nchunks, int hh, int r, int valid, int xvec, float gs2, uint64_t* kready,
+                                           int lane) {
+  float sq = 0.f;
+  const int c0 = hh * 4, c1 = min(hh * 4 + 4, 2 * nchunks);     // 16-column pieces of this warp's k-block
+#pragma unroll 1
+  for (int cc = c0; cc < c1; ++cc) {
+    const int col = cc * 16;
+    float v[16];
+    tc05::ld_32x16(tmem + col, v);
+    tc05::ld_wait();
+    const bool vec = xvec && col + 16 <= ncols;     // (bias6 + col is 16-byte aligned whenever the x rows are)
+#pragma unroll
+    for (int j4 = 0; j4 < 4; ++j4) {
+      float4 bb, xx;
+      if (vec) {
+        bb = __ldg(reinterpret_cast<const float4*>(bias6 + col) + j4);
+        xx = valid ? __ldg(reinterpret_cast<const float4*>(xrow + col) + j4) : make_float4(0.f, 0.f, 0.f, 0.f);
+      } else {
+        const int c = col + 4 * j4;
+        bb.x = c < ncols ? __ldg(bias6 + c) : 0.f;         bb.y = c + 1 < ncols ? __ldg(bias6 + c + 1) : 0.f;
+        bb.z = c + 2 < ncols ? __ldg(bias6 + c + 2) : 0.f; bb.w = c + 3 < ncols ? __ldg(bias6 + c + 3) : 0.f;
+        xx.x = (valid && c < ncols) ? __ldg(xrow + c) : 0.f;         xx.y = (valid && c + 1 < ncols) ? __ldg(xrow + c + 1) : 0.f;
+        xx.z = (valid && c + 2 < ncols) ? __ldg(xrow + c + 2) : 0.f; xx.w = (valid && c + 3 < ncols) ? __ldg(xrow + c + 3) : 0.f;
+      }
+      const float bj[4] = {bb.x, bb.y, bb.z, bb.w}, xj[4] = {xx.x, xx.y, xx.z, xx.w};
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int j = 4 * j4 + u;
+        float d = 0.f;
+        if (valid && col + j < ncols) d = v[j] + bj[u] - xj[u];
+        sq = fmaf(d, d, sq);
+        v[j] = gs2 * d;
+      }
+    }
+    const uint32_t blk = sP + (uint32_t)(col >> 6) * MV_ABLK;
+    const uint32_t cb = (uint32_t)(col & 63) >> 3;
+#pragma unroll
+    for (int i = 0; i < 2; ++i)
+      mv_sts4(blk + tma::sw128((uint32_t)r, cb + i), mv_pack(v[8 * i], v[8 * i + 1]), mv_pack(v[8 * i + 2], v[8 * i + 3]),
+              mv_pack(v[8 * i + 4], v[8 * i + 5]), mv_pack(v[8 * i + 6], v[8 * i + 7]));
+  }
+  if (c0 < c1) mv_block_done(kready, hh, lane);
+  return sq;
+}
 
 struct MvWorker {
   const MvRowsArgs& a;
   const MvSmem& s;
-  uint32_t tmem;       // accumulator base of this thread's lane quarter
+  uint32_t tmem;       // tensor-memory address of this thread's lane quarter, column 0
   int r, grow, hh, lane;
   bool valid;
-  uint32_t acc_cnt;
-  uint32_t mask[4][4];
+  uint32_t acc_cnt, pf_cnt;
+  uint32_t mask[4][2];
   float sq, kl;
 
   __device__ __forceinline__ void wait_acc() {
-    tma::mbar_wait_backoff(s.acc_bar, acc_cnt & 1u, 20);
+    tma::mbar_wait_backoff(s.acc_bar, acc_cnt & 1u, 32);
+    if (a.trace && blockIdx.x == 0 && threadIdx.x == 64 && acc_cnt < 13) a.trace[64 + acc_cnt] = clock64();   // accumulator ready
     ++acc_cnt;
     tc05::fence_after();
   }
-  // this thread's shared / tensor memory accesses of the phase are done: hand P and the accumulator back to the issuer
-  __device__ __forceinline__ void release() {
-    tc05::fence_before();
-    tma::fence_proxy_async();
-    __syncwarp();
-    if (lane == 0) tma::mbar_arrive(s.a_bar);
+  // once per epilogue, before the first write into P
+  __device__ __forceinline__ void wait_pfree() {
+    tma::mbar_wait_backoff(s.pfree, pf_cnt & 1u, 32);
+    ++pf_cnt;
   }
   // 32 columns of this thread's row as bf16 into the activation buffer (swizzled K-major: the next GEMM's A operand AND
   // the source of the TMA store that takes the rows to global memory for the weight-gradient kernel)
   __device__ __forceinline__ void store_chunk(const float (&v)[32], int col) {
-    uint32_t w[16];
-#pragma unroll
-    for (int j = 0; j < 16; ++j) w[j] = mv_pack(v[2 * j], v[2 * j + 1]);
-    unsigned char* blk = s.P + (uint32_t)(col >> 6) * MV_ABLK;
+    const uint32_t blk = tma::s32(s.P) + (uint32_t)(col >> 6) * MV_ABLK;
     const uint32_t cb = (uint32_t)(col & 63) >> 3;
 #pragma unroll
     for (int i = 0; i < 4; ++i)
-      *reinterpret_cast<uint4*>(blk + tma::sw128((uint32_t)r, cb + i)) = make_uint4(w[4 * i], w[4 * i + 1], w[4 * i + 2], w[4 * i + 3]);
+      mv_sts4(blk + tma::sw128((uint32_t)r, cb + i), mv_pack(v[8 * i], v[8 * i + 1]), mv_pack(v[8 * i + 2], v[8 * i + 3]),
+              mv_pack(v[8 * i + 4], v[8 * i + 5]), mv_pack(v[8 * i + 6], v[8 * i + 7]));
   }
 
-  template <int SLOT>
-  __device__ __forceinline__ void relu_fwd(int bias_off) {
-    wait_acc();
-#pragma unroll 1
-    for (int cc = 0; cc < 4; ++cc) {
-      const int col = hh * 128 + cc * 32;
-      float v[32];
-      tc05::ld_32x32(tmem + col, v);
-      tc05::ld_wait();
-      uint32_t mk = 0;
-      const float4* b4 = reinterpret_cast<const float4*>(s.bias + bias_off + col);   // warp-uniform: broadcast reads
+  // 16 columns of this thread's row as bf16 into P
+  __device__ __forceinline__ void store16(const float (&v)[16], int col) {
+    const uint32_t blk = tma::s32(s.P) + (uint32_t)(col >> 6) * MV_ABLK;
+    const uint32_t cb = (uint32_t)(col & 63) >> 3;
 #pragma unroll
-      for (int j4 = 0; j4 < 8; ++j4) {
-        const float4 bb = b4[j4];
+    for (int i = 0; i < 2; ++i)
+      mv_sts4(blk + tma::sw128((uint32_t)r, cb + i), mv_pack(v[8 * i], v[8 * i + 1]), mv_pack(v[8 * i + 2], v[8 * i + 3]),
+              mv_pack(v[8 * i + 4], v[8 * i + 5]), mv_pack(v[8 * i + 6], v[8 * i + 7]));
+  }
+
+  // hidden layer forward: bias + ReLU, mask bits kept, rows to P.  This warp owns the 64 columns of k-block hh and
+  // walks them 16 at a time (four warps per scheduler hide each other's latencies; 96 registers per thread).
+  template <int SLOT>
+  __device__ __forceinline__ void relu_fwd(const float* bias, int tcol) {
+    wait_acc();
+    const bool tr = a.trace && blockIdx.x == 0 && threadIdx.x == 64 && SLOT == 1;
+    if (tr) a.trace[96] = clock64();
+    wait_pfree();
+    if (tr) a.trace[97] = clock64();
+    uint32_t mlo = 0, mhi = 0;
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+      const int col = hh * 64 + c * 16;
+      float v[16];
+      tc05::ld_32x16(tmem + tcol + col, v);
+      tc05::ld_wait();
+      if (tr) a.trace[98 + c] = clock64();
+      const float4* b4 = reinterpret_cast<const float4*>(bias + col);   // warp-uniform address: one broadcast transaction
+      uint32_t mk = 0;
+#pragma unroll
+      for (int j4 = 0; j4 < 4; ++j4) {
+        const float4 bb = __ldg(b4 + j4);
         const float bj[4] = {bb.x, bb.y, bb.z, bb.w};
 #pragma unroll
         for (int u = 0; u < 4; ++u) {
@@ -225,168 +323,170 @@ struct MvWorker {
           v[j] = fmaxf(t, 0.f);
         }
       }
-      mask[SLOT][cc] = mk;
-      store_chunk(v, col);
+      if (c < 2) mlo |= mk << (16 * c); else mhi |= mk << (16 * (c - 2));
+      store16(v, col);
     }
-    release();
+    mask[SLOT][0] = mlo;
+    mask[SLOT][1] = mhi;
+    if (tr) a.trace[102] = clock64();
+    mv_block_done(s.kready, hh, lane);
+    if (tr) a.trace[103] = clock64();
   }
 
   template <int SLOT>
-  __device__ __forceinline__ void relu_bwd() {
+  __device__ __forceinline__ void relu_bwd(int tcol) {
     wait_acc();
-#pragma unroll 1
-    for (int cc = 0; cc < 4; ++cc) {
-      const int col = hh * 128 + cc * 32;
-      float v[32];
-      tc05::ld_32x32(tmem + col, v);
-      tc05::ld_wait();
-      const uint32_t mk = mask[SLOT][cc];
+    wait_pfree();
 #pragma unroll
-      for (int j = 0; j < 32; ++j) v[j] = ((mk >> j) & 1u) ? v[j] : 0.f;
-      store_chunk(v, col);
+    for (int c = 0; c < 4; ++c) {
+      const int col = hh * 64 + c * 16;
+      float v[16];
+      tc05::ld_32x16(tmem + tcol + col, v);
+      tc05::ld_wait();
+      const uint32_t mk = (c < 2 ? mask[SLOT][0] : mask[SLOT][1]) >> (16 * (c & 1));
+#pragma unroll
+      for (int j = 0; j < 16; ++j) v[j] = ((mk >> j) & 1u) ? v[j] : 0.f;
+      store16(v, col);
     }
-    release();
+    mv_block_done(s.kready, hh, lane);
   }
 
-  // reconstruction loss of one half of the output columns straight from the accumulators: sum (xhat - x)^2 and
-  // dxhat = gs2 * (xhat - x) as bf16 rows (the A operand of the first data-gradient GEMM, and G6 for kernel B)
-  // (__noinline__: nvcc 12.9's optimizer crashes on this body when it is inlined into the unrolled epilogue sequence)
-  __device__ __noinline__ void loss_half(int half) {
+  // reconstruction loss of one half of the output columns straight from the accumulators (mv_loss_half above)
+  __device__ __forceinline__ void loss_half(int half, int tcol) {
     wait_acc();
+    wait_pfree();
     const int n = half ? a.N6b : a.N6a;
     const int cbase = half ? 256 : 0;
-    const int nchunks = ((n + 63) >> 6) << 1;
-#pragma unroll 1
-    for (int cc = hh * 4; cc < hh * 4 + 4; ++cc) {
-      if (cc >= nchunks) break;
-      const int col = cc * 32;              // column inside the half (= inside P)
-      float v[32];
-      tc05::ld_32x32(tmem + cbase + col, v);
-      tc05::ld_wait();
-      const float* xr = a.x + (int64_t)grow * a.D + cbase + col;
-      float xv[32];
-      if (valid && a.xvec && cbase + col + 32 <= a.D) {      // 8 x 16-byte loads of the row instead of 32 scalar ones
-#pragma unroll
-        for (int j4 = 0; j4 < 8; ++j4) {
-          const float4 t = __ldg(reinterpret_cast<const float4*>(xr) + j4);
-          xv[4 * j4] = t.x; xv[4 * j4 + 1] = t.y; xv[4 * j4 + 2] = t.z; xv[4 * j4 + 3] = t.w;
-        }
-      } else {
-#pragma unroll
-        for (int j = 0; j < 32; ++j) xv[j] = (valid && cbase + col + j < a.D) ? __ldg(xr + j) : 0.f;
-      }
-#pragma unroll
-      for (int j = 0; j < 32; ++j) {
-        const int gc = cbase + col + j;
-        float d = 0.f;
-        if (valid && gc < a.D) d = v[j] + s.bias[1088 + gc] - xv[j];
-        sq = fmaf(d, d, sq);
-        v[j] = a.gs2 * d;
-      }
-      store_chunk(v, col);
-    }
-    release();
+    const float part = mv_loss_half(tmem + tcol, tma::s32(s.P), a.bias[5] + cbase,
+                                    a.x + (int64_t)grow * a.D + cbase, a.D - cbase, ((n + 63) >> 6) << 1, hh, r,
+                                    valid ? 1 : 0, a.xvec, a.gs2, s.kready, lane);
+    sq += part;
   }
 
-  // one bf16 element of row r into the activation buffer (k-block 0) and into a global row
+  // one bf16 element of row r into the activation buffer (k-block 0)
   __device__ __forceinline__ void put_elem(int col, float val) {
     *reinterpret_cast<__nv_bfloat16*>(s.P + tma::sw128((uint32_t)r, (uint32_t)col >> 3) + ((uint32_t)col & 7u) * 2u) =
         __float2bfloat16_rn(val);
   }
 
-  // heads: mu | logvar from the accumulator, z = mu + eps * exp(logvar / 2), KL row; [z | c | 0] is the decoder's input
+  // heads: mu | logvar from the accumulator, z = mu + eps * exp(logvar / 2), KL row; [z | c | 0] is the decoder's input.
+  // Streams four latent columns at a time (the 4-warp-per-scheduler layout leaves 96 registers per thread).
   template <int Z>
-  __device__ __forceinline__ void heads() {
+  __device__ __forceinline__ void heads(int tcol) {
     wait_acc();
     if (hh == 0) {
-      float h0[32];
-      float mu[Z];
-      float lv[Z];
-      float ep[Z];
-      float zlo[32];
+      float h0[32], zlo[32];
 #pragma unroll
       for (int j = 0; j < 32; ++j) zlo[j] = 0.f;
-      tc05::ld_32x32(tmem, h0);
+      tc05::ld_32x32(tmem + tcol, h0);
       tc05::ld_wait();
-#pragma unroll
-      for (int j = 0; j < Z; ++j) mu[j] = h0[j] + s.bias[512 + j];
-      if (Z == 32) {          // logvar sits in accumulator columns [32, 64)
-        tc05::ld_32x32(tmem + 32, h0);
-        tc05::ld_wait();
-      }
-#pragma unroll
-      for (int j = 0; j < Z; ++j) lv[j] = a.variational ? h0[(Z + j) & 31] + s.bias[512 + Z + j] : 0.f;
-#pragma unroll
-      for (int j4 = 0; j4 < Z / 4; ++j4) {
-        float4 e = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (valid && a.variational) e = __ldg(reinterpret_cast<const float4*>(a.eps + (int64_t)grow * Z) + j4);
-        ep[4 * j4] = e.x; ep[4 * j4 + 1] = e.y; ep[4 * j4 + 2] = e.z; ep[4 * j4 + 3] = e.w;
-      }
+      float4* mv = reinterpret_cast<float4*>(a.mulv + (int64_t)grow * 64);
       float klr = 0.f;
+      if (Z == 32) {      // mu fills the chunk; logvar sits in accumulator columns [32, 64)
 #pragma unroll
-      for (int j = 0; j < Z; ++j) {
-        float zz = mu[j];
+        for (int j = 0; j < 32; ++j) zlo[j] = h0[j] + s.bias[j];                      // mu
+#pragma unroll
+        for (int j4 = 0; j4 < 8; ++j4) mv[j4] = make_float4(zlo[4 * j4], zlo[4 * j4 + 1], zlo[4 * j4 + 2], zlo[4 * j4 + 3]);
         if (a.variational) {
-          zz = mu[j] + ep[j] * expf(0.5f * lv[j]);
-          klr += 1.f + lv[j] - mu[j] * mu[j] - expf(lv[j]);
+          tc05::ld_32x32(tmem + tcol + 32, h0);
+          tc05::ld_wait();
+#pragma unroll
+          for (int j4 = 0; j4 < 8; ++j4) {
+            float4 e = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (valid) e = __ldg(reinterpret_cast<const float4*>(a.eps + (int64_t)grow * Z) + j4);
+            const float ee[4] = {e.x, e.y, e.z, e.w};
+            float lq[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+              const int j = 4 * j4 + u;
+              const float lv = h0[j] + s.bias[Z + j], mu = zlo[j];
+              lq[u] = lv;
+              klr += 1.f + lv - mu * mu - expf(lv);
+              zlo[j] = mu + ee[u] * expf(0.5f * lv);
+            }
+            mv[8 + j4] = make_float4(lq[0], lq[1], lq[2], lq[3]);
+          }
         }
-        if (Z <= 32) zlo[j & 31] = zz;
+      } else {
+#pragma unroll
+        for (int j4 = 0; j4 < Z / 4; ++j4) {
+          float4 e = make_float4(0.f, 0.f, 0.f, 0.f);
+          if (valid && a.variational) e = __ldg(reinterpret_cast<const float4*>(a.eps + (int64_t)grow * Z) + j4);
+          const float ee[4] = {e.x, e.y, e.z, e.w};
+          float mq[4], lq[4];
+#pragma unroll
+          for (int u = 0; u < 4; ++u) {
+            const int j = 4 * j4 + u;
+            const float mu = h0[j] + s.bias[j];
+            const float lv = a.variational ? h0[Z + j] + s.bias[Z + j] : 0.f;
+            mq[u] = mu; lq[u] = lv;
+            float zz = mu;
+            if (a.variational) {
+              zz = mu + ee[u] * expf(0.5f * lv);
+              klr += 1.f + lv - mu * mu - expf(lv);
+            }
+            zlo[j] = zz;
+          }
+          mv[j4] = make_float4(mq[0], mq[1], mq[2], mq[3]);
+          mv[Z / 4 + j4] = make_float4(lq[0], lq[1], lq[2], lq[3]);
+        }
       }
       if (valid) kl += -0.5f * klr;
-      float4* mv = reinterpret_cast<float4*>(a.mulv + (int64_t)grow * 64);
-#pragma unroll
-      for (int j4 = 0; j4 < Z / 4; ++j4) {
-        mv[j4] = make_float4(mu[4 * j4], mu[4 * j4 + 1], mu[4 * j4 + 2], mu[4 * j4 + 3]);
-        mv[Z / 4 + j4] = make_float4(lv[4 * j4], lv[4 * j4 + 1], lv[4 * j4 + 2], lv[4 * j4 + 3]);
-      }
+      wait_pfree();
       store_chunk(zlo, 0);
 #pragma unroll
       for (int j = 0; j < 32; ++j) zlo[j] = 0.f;
       store_chunk(zlo, 32);
       // the conditioning vector follows z (19:110-115); Z + Cc <= 64
       for (int j = 0; j < a.Cc; ++j) put_elem(Z + j, valid ? __ldg(a.c + (int64_t)grow * a.Cc + j) : 0.f);
-    }
-    release();
-  }
-
-  template <int Z>
-  __device__ __forceinline__ void one(int j, float dzj, float e, float mu, float lv, float (&glo)[32], float (&ghi)[32]) {
-    if (a.variational) {
-      const float dmu = valid ? dzj + a.ks * mu : 0.f;
-      const float dlv = valid ? dzj * e * 0.5f * expf(0.5f * lv) + a.ks * 0.5f * (expf(lv) - 1.f) : 0.f;
-      glo[j] = dmu;
-      if (Z + j < 32) glo[(Z + j) & 31] = dlv; else ghi[(Z + j) & 31] = dlv;
+      mv_block_done(s.kready, 0, lane);
     } else {
-      glo[j] = valid ? dzj : 0.f;
+      wait_pfree();
     }
   }
 
   // backward of the reparameterisation + KL (12:168-172 / 19:105-108,124-126): G3 = [dmu | dlogvar] (or dz for the AE)
   template <int Z>
-  __device__ __forceinline__ void dz() {
+  __device__ __forceinline__ void dz(int tcol) {
     wait_acc();
+    wait_pfree();
     if (hh == 0) {
-      float d0[32];
-      tc05::ld_32x32(tmem, d0);
+      float d0[32], g[32];
+      tc05::ld_32x32(tmem + tcol, d0);
       tc05::ld_wait();
-      float glo[32], ghi[32];
-#pragma unroll
-      for (int j = 0; j < 32; ++j) { glo[j] = 0.f; ghi[j] = 0.f; }
       const float4* mv = reinterpret_cast<const float4*>(a.mulv + (int64_t)grow * 64);
+#pragma unroll
+      for (int j = 0; j < 32; ++j) g[j] = 0.f;
+      // first chunk: dmu (and, for Z <= 16, dlogvar behind it)
 #pragma unroll
       for (int j4 = 0; j4 < Z / 4; ++j4) {
         float4 e = make_float4(0.f, 0.f, 0.f, 0.f);
         if (valid && a.variational) e = __ldg(reinterpret_cast<const float4*>(a.eps + (int64_t)grow * Z) + j4);
         const float4 m4 = mv[j4], l4 = mv[Z / 4 + j4];
-        one<Z>(4 * j4 + 0, d0[4 * j4 + 0], e.x, m4.x, l4.x, glo, ghi);
-        one<Z>(4 * j4 + 1, d0[4 * j4 + 1], e.y, m4.y, l4.y, glo, ghi);
-        one<Z>(4 * j4 + 2, d0[4 * j4 + 2], e.z, m4.z, l4.z, glo, ghi);
-        one<Z>(4 * j4 + 3, d0[4 * j4 + 3], e.w, m4.w, l4.w, glo, ghi);
+        const float ee[4] = {e.x, e.y, e.z, e.w}, mm[4] = {m4.x, m4.y, m4.z, m4.w}, ll[4] = {l4.x, l4.y, l4.z, l4.w};
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          const int j = 4 * j4 + u;
+          const float dzj = valid ? d0[j] : 0.f;
+          if (a.variational) {
+            g[j] = valid ? dzj + a.ks * mm[u] : 0.f;
+            const float dlv = valid ? dzj * ee[u] * 0.5f * expf(0.5f * ll[u]) + a.ks * 0.5f * (expf(ll[u]) - 1.f) : 0.f;
+            if (Z <= 16) g[Z + j] = dlv; else d0[j] = dlv;     // Z = 32: dlogvar is the second chunk (d0 is dead at j)
+          } else {
+            g[j] = dzj;
+          }
+        }
       }
-      store_chunk(glo, 0);
-      store_chunk(ghi, 32);
+      store_chunk(g, 0);
+      if (Z == 32 && a.variational) {
+        store_chunk(d0, 32);
+      } else {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) g[j] = 0.f;
+        store_chunk(g, 32);
+      }
+      mv_block_done(s.kready, 0, lane);
     }
-    release();
   }
 };
 
@@ -402,21 +502,15 @@ mv_rows_kernel(const MvRowsArgs a, const __grid_constant__ MvMaps maps) {
     for (int i = 0; i < MV_WS; ++i) { tma::mbar_init(&s.wfull[i], 1); tma::mbar_init(&s.wempty[i], 1); }
     for (int i = 0; i < MV_XS; ++i) { tma::mbar_init(&s.xfull[i], 1); tma::mbar_init(&s.xempty[i], 1); }
     tma::mbar_init(s.acc_bar, 1);
-    tma::mbar_init(s.a_bar, 8);
+    for (int i = 0; i < 4; ++i) tma::mbar_init(&s.kready[i], 4);
+    tma::mbar_init(s.pfree, 1);
     tma::mbar_fence_init();
   }
-  // biases -> shared memory (zero padded): b1 @0, b2 @256, b3 @512 (mu | logvar), b4 @576, b5 @832, b6 @1088
+  // head biases -> shared memory: mu | logvar, zero padded
   for (int i = threadIdx.x; i < MV_NBIAS; i += MV_THREADS) {
     float v = 0.f;
-    if (i < 256) v = a.bias[0][i];
-    else if (i < 512) v = a.bias[1][i - 256];
-    else if (i < 576) {
-      const int j = i - 512;
-      if (j < a.Z) v = a.bias[2][j];
-      else if (a.variational && j < 2 * a.Z) v = a.bias_lv[j - a.Z];
-    } else if (i < 832) v = a.bias[3][i - 576];
-    else if (i < 1088) v = a.bias[4][i - 832];
-    else if (i - 1088 < a.D) v = a.bias[5][i - 1088];
+    if (i < a.Z) v = a.bias[2][i];
+    else if (a.variational && i < 2 * a.Z) v = a.bias_lv[i - a.Z];
     s.bias[i] = v;
   }
   if (warp == 1) tc05::tmem_alloc(s.tmem_slot, 512);
@@ -435,7 +529,7 @@ mv_rows_kernel(const MvRowsArgs a, const __grid_constant__ MvMaps maps) {
           const uint32_t bytes = ph.b_mn ? (uint32_t)ph.nbox * 8192u : (uint32_t)ph.n * 128u;
           for (int kb = 0; kb < ph.nkb; ++kb, ++it) {
             const uint32_t st = it % MV_WS;
-            tma::mbar_wait(&s.wempty[st], ((it / MV_WS) & 1u) ^ 1u);
+            tma::mbar_wait_backoff(&s.wempty[st], ((it / MV_WS) & 1u) ^ 1u, 100);   // (spinning would take issue slots from the workers)
             tma::mbar_expect_tx(&s.wfull[st], bytes);
             unsigned char* dst = s.WR + st * MV_WSTAGE;
             if (ph.b_mn) {   // [64 out-features (k)][64 in-features (n)] boxes of the row-major shadow: MN-major B operand
@@ -452,7 +546,7 @@ mv_rows_kernel(const MvRowsArgs a, const __grid_constant__ MvMaps maps) {
       for (int tile = blockIdx.x; tile < a.ntiles; tile += gridDim.x)
         for (int kb = 0; kb < a.nk1; ++kb, ++it) {
           const uint32_t st = it % MV_XS;
-          tma::mbar_wait(&s.xempty[st], ((it / MV_XS) & 1u) ^ 1u);
+          tma::mbar_wait_backoff(&s.xempty[st], ((it / MV_XS) & 1u) ^ 1u, 200);
           tma::mbar_expect_tx(&s.xfull[st], MV_ABLK);
           tma::load_2d(s.XR + st * MV_ABLK, &maps.m[MAP_X], &s.xfull[st], kb * 64, tile * 128);
         }
@@ -460,38 +554,47 @@ mv_rows_kernel(const MvRowsArgs a, const __grid_constant__ MvMaps maps) {
   } else if (warp == 1) {
     // ===================== MMA issuer (also issues the TMA stores of what the epilogues leave in P) ==============
     if (lane == 0) {
-      uint32_t wit = 0, xit = 0, a_cnt = 0;
-      bool first = true;
-      int st_map = -1, st_nblk = 0, st_col0 = 0, st_row = 0;     // pending store: output of the previous epilogue
+      uint32_t wit = 0, xit = 0;
+      uint32_t kcnt[4] = {0u, 0u, 0u, 0u};                       // completions consumed per k-block barrier
+      int st_map = -1, st_nblk = 0, st_col0 = 0, st_row = 0;     // what the previous epilogue is leaving in P
+      uint32_t seen = 0;                                         // bit j: block j of the previous epilogue has been taken
+      // wait for block j of the previous epilogue (once), and send it on its way to global memory
+      auto take = [&](int j) {
+        if (st_map < 0 || j >= st_nblk || ((seen >> j) & 1u)) return false;
+        tma::mbar_wait_backoff(&s.kready[j], kcnt[j] & 1u, 32);
+        ++kcnt[j];
+        seen |= 1u << j;
+        tc05::fence_after();
+        if (a.dbg & 1) return false;
+        tma::store_2d(&maps.m[st_map], s.P + (uint32_t)j * MV_ABLK, st_col0 + 64 * j, st_row);
+        tma::bulk_commit();
+        return true;
+      };
       for (int tile = blockIdx.x; tile < a.ntiles; tile += gridDim.x)
         for (int p = 0; p < a.nph; ++p) {
           const MvPhase ph = mv_phase(p, a.nk1, a.N6a, a.N6b, a.nkd);
+          const bool tr = a.trace && blockIdx.x == 0 && tile == 0;
+          if (tr) a.trace[p * 4 + 0] = clock64();          // issuer reaches the phase
           bool stored = false;
-          if (ph.wait_prev && !first) {
-            tma::mbar_wait(s.a_bar, a_cnt & 1u);
-            ++a_cnt;
-            tc05::fence_after();
-            if (st_map >= 0) {     // P now holds the rows of the previous phase: send them to global memory
-              for (int b = 0; b < st_nblk; ++b)
-                tma::store_2d(&maps.m[st_map], s.P + (uint32_t)b * MV_ABLK, st_col0 + 64 * b, st_row);
-              tma::bulk_commit();
-              stored = true;
-              st_map = -1;
-            }
-          }
-          first = false;
+          if (ph.wait_all)                                 // the accumulator half is still being drained
+            for (int j = 0; j < 4; ++j) stored |= take(j);
+          if (tr) a.trace[p * 4 + 1] = clock64();
           const uint32_t idesc = tc05::idesc(tc05::kFmtBF16, 128, ph.n, 0, ph.b_mn);
           for (int kb = 0; kb < ph.nkb; ++kb, ++wit) {
             const uint32_t st = wit % MV_WS;
             uint32_t sa;
             if (ph.a_x) {
               const uint32_t xs = xit % MV_XS;
-              tma::mbar_wait(&s.xfull[xs], (xit / MV_XS) & 1u);
+              tma::mbar_wait_backoff(&s.xfull[xs], (xit / MV_XS) & 1u, 32);
               sa = tma::s32(s.XR + xs * MV_ABLK);
             } else {
-              sa = tma::s32(s.P + (uint32_t)(ph.kb0 + kb) % 4u * MV_ABLK);
+              const int blk = (ph.kb0 + kb) & 3;
+              stored |= take(blk);                         // the epilogue has produced this k-block of the A operand
+              sa = tma::s32(s.P + (uint32_t)blk * MV_ABLK);
+              if (tr && p == 2) a.trace[104 + kb * 2] = clock64();
             }
-            tma::mbar_wait(&s.wfull[st], (wit / MV_WS) & 1u);
+            tma::mbar_wait_backoff(&s.wfull[st], (wit / MV_WS) & 1u, 32);
+            if (tr && p == 2) a.trace[105 + kb * 2] = clock64();
             tc05::fence_after();
             const uint32_t sb = tma::s32(s.WR + st * MV_WSTAGE);
 #pragma unroll
@@ -503,59 +606,58 @@ mv_rows_kernel(const MvRowsArgs a, const __grid_constant__ MvMaps maps) {
             tc05::commit(&s.wempty[st]);
             if (ph.a_x) { tc05::commit(&s.xempty[xit % MV_XS]); ++xit; }
           }
-          // the epilogue of THIS phase overwrites P: the store issued above must have finished reading it
-          if (stored) tma::bulk_wait_read0();
+          if (tr) a.trace[p * 4 + 2] = clock64();          // all MMAs of the phase issued (operands had arrived)
           if (ph.has_epi) {
             tc05::commit(s.acc_bar);
-            st_map = ph.st_map; st_nblk = ph.st_nblk; st_col0 = ph.st_col0; st_row = tile * 128;
+            // the epilogue of THIS phase overwrites P: it may load and compute right away, but stores only after the
+            // TMA stores issued above have finished reading the buffer
+            if (stored) tma::bulk_wait_read0();
+            tma::mbar_arrive(s.pfree);
+            st_map = ph.st_map; st_nblk = ph.st_nblk; st_col0 = ph.st_col0; st_row = tile * 128; seen = 0;
           }
+          if (tr) a.trace[p * 4 + 3] = clock64();          // ... and the previous rows have left P
         }
-      if (!first) {          // rows of the very last epilogue
-        tma::mbar_wait(s.a_bar, a_cnt & 1u);
-        if (st_map >= 0) {
-          for (int b = 0; b < st_nblk; ++b)
-            tma::store_2d(&maps.m[st_map], s.P + (uint32_t)b * MV_ABLK, st_col0 + 64 * b, st_row);
-          tma::bulk_commit();
-        }
-      }
-      tma::bulk_wait0();     // every store of this CTA has landed before the kernel ends
+      for (int j = 0; j < 4; ++j) take(j);   // rows of the very last epilogue
+      tma::bulk_wait0();                     // every store of this CTA has landed before the kernel ends
     }
   } else {
     // ===================== workers: the epilogue of every phase =====================
     MvWorker w{a, s};
     const int q = warp & 3;
-    w.hh = (warp - 2) >> 2;
+    w.hh = (warp - 2) >> 2;            // k-block (64 columns) of a 256-wide layer this warp produces
     w.lane = lane;
     w.r = q * 32 + lane;
     w.tmem = tmem_base + ((uint32_t)(q * 32) << 16);
     w.acc_cnt = 0;
+    w.pf_cnt = 0;
+    const bool two = a.N6b > 0;
     for (int tile = blockIdx.x; tile < a.ntiles; tile += gridDim.x) {
       w.grow = tile * 128 + w.r;
       w.valid = w.grow < a.B;
       w.sq = 0.f; w.kl = 0.f;
-      w.template relu_fwd<0>(0);
-      w.template relu_fwd<1>(256);
-      w.template heads<Z>();
-      w.template relu_fwd<2>(576);
-      w.template relu_fwd<3>(832);
-      w.loss_half(0);
-      if (a.N6b > 0) w.loss_half(1);
-      w.template relu_bwd<3>();
-      w.template relu_bwd<2>();
-      w.template dz<Z>();
-      w.template relu_bwd<1>();
-      w.template relu_bwd<0>();
-      // tile loss partials, fixed order: lanes -> warp (shuffle tree), 8 warps -> thread of warp 2
+      w.template relu_fwd<0>(a.bias[0], 0);
+      w.template relu_fwd<1>(a.bias[1], 256);
+      w.template heads<Z>(0);
+      w.template relu_fwd<2>(a.bias[3], 256);
+      w.template relu_fwd<3>(a.bias[4], 0);
+      w.loss_half(0, 256);
+      if (two) w.loss_half(1, 0);
+      w.template relu_bwd<3>(two ? 256 : 0);
+      w.template relu_bwd<2>(two ? 0 : 256);
+      w.template dz<Z>(two ? 256 : 0);
+      w.template relu_bwd<1>(two ? 0 : 256);
+      w.template relu_bwd<0>(two ? 256 : 0);
+      // tile loss partials, fixed order: lanes -> warp (shuffle tree), worker warps -> thread of warp 2
       const double sqw = warp_sum((double)w.sq), klw = warp_sum((double)w.kl);
       if (lane == 0) { s.red[2 * (warp - 2)] = sqw; s.red[2 * (warp - 2) + 1] = klw; }
-      asm volatile("bar.sync 1, 256;" ::: "memory");
+      asm volatile("bar.sync 1, %0;" ::"n"(32 * MV_NWORK) : "memory");
       if (warp == 2 && lane == 0) {
         double t0 = 0.0, t1 = 0.0;
-        for (int i = 0; i < 8; ++i) { t0 += s.red[2 * i]; t1 += s.red[2 * i + 1]; }
+        for (int i = 0; i < MV_NWORK; ++i) { t0 += s.red[2 * i]; t1 += s.red[2 * i + 1]; }
         a.tile_part[2 * tile] = t0;
         a.tile_part[2 * tile + 1] = t1;
       }
-      asm volatile("bar.sync 1, 256;" ::: "memory");
+      asm volatile("bar.sync 1, %0;" ::"n"(32 * MV_NWORK) : "memory");
     }
   }
 
@@ -865,6 +967,8 @@ static MvPlan mv_plan(const VcMlpVaeDesc* d, int B) {
   return p;
 }
 
+static long long* g_mv_trace = nullptr;
+
 static unsigned char* mv_base(void* ws) {
   return reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(ws) + 1023) & ~(uintptr_t)1023);
 }
@@ -903,6 +1007,12 @@ static void mv_fill_adam_args(MvAdamArgs& c, const MvPlan& p, const VcMlpVaePara
 }  // namespace vc
 
 using namespace vc;
+
+// debug hook (profiles/trace_fused.py): device buffer of >= 128 int64 that receives clock64 stamps of CTA 0's first tile
+extern "C" int vc_mlpvae_debug_trace(int64_t* device_buffer) {
+  g_mv_trace = reinterpret_cast<long long*>(device_buffer);
+  return VC_OK;
+}
 
 extern "C" int vc_mlpvae_supported(const VcMlpVaeDesc* d) { return mv_plan(d, 128).ok ? 1 : 0; }
 
@@ -1006,6 +1116,8 @@ extern "C" int vc_mlpvae_step(const VcMlpVaeDesc* d, const VcMlpVaeParams* prm, 
     a.xvec = (p.D % 4 == 0 && (reinterpret_cast<uintptr_t>(x) & 15) == 0) ? 1 : 0;
     a.mulv = reinterpret_cast<float*>(w + p.o_mulv);
     a.tile_part = reinterpret_cast<double*>(w + p.o_tile);
+    a.trace = g_mv_trace;
+    { const char* e = getenv("VAECLUST_MV_DEBUG"); a.dbg = e ? atoi(e) : 0; }
     int grid = p.ntiles < sm_count() ? p.ntiles : sm_count();
 #define MV_LAUNCH_ROWS(ZZ)                                                                                           \
   do {                                                                                                               \
