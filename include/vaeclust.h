@@ -241,7 +241,8 @@ int vc_kmeans_finalize(const double* sums, const double* counts, const float* C_
  * state 0 running, 1 strict convergence (no label changed), 2 centre shift <= tol, 3 an empty cluster needs the host's
  * relocation path (_k_means_common.pyx:167-211; centres untouched, iteration not counted).  finalize replaces C by the
  * new centres in place (C_scratch: k*d floats); once state != 0 every later estep / finalize launch is a no-op, so
- * over-enqueued iterations change nothing.  Results are bit-identical to the stepwise entry points above. */
+ * over-enqueued iterations change nothing.  Results are bit-identical to the stepwise entry points above.
+ * tol < 0 disables both stopping rules (benchmarks of the steady loop run exactly the enqueued iterations). */
 int vc_kmeans_lloyd_begin(int32_t* ctl, void* workspace, size_t workspace_bytes, int k, int d, void* stream);
 int vc_kmeans_lloyd_estep(const float* X, int64_t N, int d, const float* C, int k, int32_t* labels, double* stats,
                           const int32_t* ctl, void* workspace, size_t workspace_bytes, void* stream);

@@ -725,8 +725,10 @@ __global__ void kmeans_lloyd_finalize_kernel(double* __restrict__ stats, float* 
   if (threadIdx.x == 0) {
     stats[(size_t)k * d + k + 1] = acc;
     ctl[1] += 1;
-    if (stats[(size_t)k * d + k] == 0.0) ctl[0] = 1;
-    else if (acc <= tol) ctl[0] = 2;
+    if (tol >= 0.0) {   // tol < 0: run exactly the iterations the host enqueues (benchmarks of the steady loop)
+      if (stats[(size_t)k * d + k] == 0.0) ctl[0] = 1;
+      else if (acc <= tol) ctl[0] = 2;
+    }
   }
 }
 
