@@ -73,6 +73,30 @@ def _worker(rank, world, port, out_dir):
     init2[3] = 1000.0
     km2 = cluster.KMeans(4, init=init2, n_init=1, group=td.group.WORLD).fit(X[lo:hi])
     res["labels2"], res["inertia2"] = km2.labels_, km2.inertia_
+    # sharded optimizer: reduce-scatter -> update of this rank's slice -> all-gather (here: SGD on CPU tensors)
+    bigp = torch.nn.Parameter(torch.arange(40, dtype=torch.float32))
+    smallp = torch.nn.Parameter(torch.ones(3))
+
+    class _Opt:   # minimal stand-in with the two methods ShardedGradSync uses
+        def __init__(self):
+            self.sh = {}
+
+        def shard(self, p, lo_, hi_, gs):
+            self.sh[id(p)] = (lo_, hi_, gs)
+
+        def update_now(self, p):
+            lo_, hi_, gs = self.sh[id(p)]
+            p.data.view(-1)[lo_:hi_] -= 0.1 * gs
+
+    sopt = _Opt()
+    ssync = dist.ShardedGradSync([bigp, smallp], td.group.WORLD, sopt, big_numel=16)
+    for _ in range(2):
+        ssync.begin(nloc, 8)
+        ((rank + 1.0) * ((bigp * torch.arange(40.0)).sum() + smallp.sum())).backward()
+        ssync.finish()
+        smallp.data -= 0.1 * smallp.grad
+        ssync.join()
+    res["sh_big"], res["sh_small"] = bigp.detach().numpy().copy(), smallp.detach().numpy().copy()
     # k-means++ over row shards (device-prefix-sum path) and best-of-n_init restarts dealt to the ranks
     cluster._HOST_CUMSUM_MAX = 0
     km3 = cluster.KMeans(4, n_init=1, random_state=7, group=td.group.WORLD).fit(X[lo:hi])
@@ -113,6 +137,11 @@ def test_world2_matches_single_process(tmp_path):
         np.testing.assert_allclose(r[i]["ov_s2"], np.full((2, 2), 3 * w), rtol=1e-6)
         assert bool(r[i]["ov_unused_none"])
     np.testing.assert_array_equal(r[0]["centers"], r[1]["centers"])  # bit-identical replicas
+    # sharded optimizer: both ranks hold the same, fully updated parameter = 2 SGD steps on the weighted mean gradient
+    w = (5 * 1.0 + 3 * 2.0) / 8
+    np.testing.assert_allclose(r[0]["sh_big"], np.arange(40.0) - 2 * 0.1 * w * np.arange(40.0), rtol=1e-6)
+    np.testing.assert_array_equal(r[0]["sh_big"], r[1]["sh_big"])
+    np.testing.assert_allclose(r[0]["sh_small"], np.ones(3) - 2 * 0.1 * w, rtol=1e-6)
     init2 = init.copy()
     init2[3] = 1000.0
     labels2, inertia2, _, _ = cr.kmeans_lloyd(X, init2)

@@ -1,0 +1,78 @@
+"""GPU, two ranks over NCCL (skipped on a one-GPU box): the data-parallel script-12 step -- reduce-scatter -> Adam on the
+rank's slice -> all-gather for the large tensors (vaeclust.dist.ShardedGradSync), flat all-reduce for the small ones --
+follows the reference's golden loss curve when the global batch is split over the ranks, leaves bit-identical
+parameters on both ranks, and agrees with the plain all-reduce + replicated-Adam path; eager and graph-replayed."""
+import os
+import socket
+import sys
+from pathlib import Path
+
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+ROOT = Path(__file__).resolve().parents[1]
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _worker(rank, world, port, out_dir, mode, graphed):
+    for p in (str(ROOT), str(ROOT / "vae-for-hybrid-music-clustering_b200")):
+        sys.path.insert(0, p)
+    os.environ["VAECLUST_DP"] = mode
+    os.environ["VAECLUST_DP_BIG_NUMEL"] = "100000"          # the 16x22 model's FC weights (196608) count as "large"
+    os.environ["TORCH_NCCL_ASYNC_ERROR_HANDLING"] = "0"
+    import torch.distributed as td
+    torch.cuda.set_device(rank)
+    td.init_process_group("nccl", init_method=f"tcp://127.0.0.1:{port}", rank=rank, world_size=world,
+                          device_id=torch.device("cuda", rank))
+    from oracle import make_golden as mg
+    from vaeclust import nn
+    from vaeclust.train import GraphedVAEStep, VAEStep
+    name = "conv_16x22"
+    c = mg.CASES[name]
+    model = nn.ConvMultiModalVAE(1, c["feat_hw"], c["z"], c["lyr"])
+    model.load_state_dict(mg.case_params(name))
+    model.cuda().train()
+    step = (GraphedVAEStep(model, "conv12", lr=c["lr"], beta=c["beta"], warmup=1, group=td.group.WORLD) if graphed
+            else VAEStep(model, "conv12", lr=c["lr"], beta=c["beta"], group=td.group.WORLD))
+    losses = []
+    lo, hi = rank * c["B"] // world, (rank + 1) * c["B"] // world
+    for s in range(c["steps"]):
+        b = {k: v[lo:hi].cuda() for k, v in mg.case_inputs(name, s).items()}
+        st = step(b["x"], b["lyr"], b["m"], eps=b["eps"], global_batch=c["B"])
+        w = torch.tensor([float(st[0]) * (hi - lo) / c["B"]], device="cuda")
+        td.all_reduce(w)                                   # loss of the global batch = weighted mean of the rank means
+        losses.append(float(w))
+    torch.cuda.synchronize()
+    np.savez(os.path.join(out_dir, f"{mode}_{int(graphed)}_r{rank}.npz", ), losses=np.array(losses),
+             **{n: p.detach().cpu().numpy() for n, p in model.named_parameters()})
+    td.destroy_process_group()
+
+
+@pytest.mark.timeout(600)
+@pytest.mark.parametrize("graphed", [False, True])
+def test_two_rank_step_matches_golden_and_replicas_agree(graphed, tmp_path, golden_dir):
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs (run under gpurun --gpus 2)")
+    import torch.multiprocessing as mp
+    gold = np.load(golden_dir / "vae_conv_16x22.npz")
+    res = {}
+    for mode in ("sharded", "allreduce"):
+        mp.spawn(_worker, args=(2, _free_port(), str(tmp_path), mode, graphed), nprocs=2, join=True)
+        r = [np.load(tmp_path / f"{mode}_{int(graphed)}_r{i}.npz") for i in range(2)]
+        for s, l in enumerate(r[0]["losses"]):
+            assert l == pytest.approx(float(gold["loss"][s]), rel=1e-3), (mode, s)
+        for n in r[0].files:
+            if n != "losses":
+                np.testing.assert_array_equal(r[0][n], r[1][n], err_msg=f"{mode}: replicas differ in {n}")
+                ref = gold["param/" + n][1]
+                assert float(np.abs(r[0][n].astype(np.float64)).sum()) == pytest.approx(ref, rel=1e-5, abs=1e-7), (mode, n)
+        res[mode] = r[0]
+    for n in res["sharded"].files:      # same arithmetic, different data movement
+        np.testing.assert_allclose(res["sharded"][n], res["allreduce"][n], rtol=1e-5, atol=1e-7)

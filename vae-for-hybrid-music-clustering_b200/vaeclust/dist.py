@@ -191,3 +191,75 @@ class OverlappedGradSync:
         for w in self.works:
             w.wait()
         self.works = []
+
+
+class ShardedGradSync(OverlappedGradSync):
+    """Gradient exchange + optimizer for the data-parallel script-12 step with the optimizer state SHARDED over the ranks
+    (SURVEY.md 8(e) C1): for each large parameter (the two 67 M-element FC weights, 99.5 % of the model)
+        reduce-scatter(gradient)  ->  Adam on this rank's 1/world slice  ->  all-gather(parameter)
+    issued from the parameter's post-accumulate hook, so all three run under the rest of backward: the reduce-scatter
+    and the all-gather on NCCL's stream, the slice update on a side stream between them.  The wire bytes equal the
+    all-reduce they replace, but the 28 B/parameter Adam sweep and the moments shrink by the world size.  Small
+    parameters keep the flat all-reduce + replicated update (bit-identical replicas).
+    Protocol per step: begin() -> forward/backward -> finish() -> opt.step() -> join()."""
+
+    def __init__(self, params, group, opt, big_numel: int = 1 << 20, update=None):
+        super().__init__(params, group, big_numel=big_numel)
+        self.opt = opt
+        self.update = update or opt.update_now        # (tests on CPU tensors pass their own slice update)
+        w, r = world_size(group), rank(group)
+        self.sharded = {}
+        keep_big = []
+        for p in self.big:
+            if w > 1 and p.numel() % w == 0:
+                n = p.numel() // w
+                gs = torch.empty(n, dtype=torch.float32, device=p.device)
+                self.sharded[id(p)] = (r * n, (r + 1) * n, gs)
+                if hasattr(opt, "shard"):
+                    opt.shard(p, r * n, (r + 1) * n, gs)
+            else:
+                keep_big.append(p)          # not divisible: stays on the in-place all-reduce path
+        self._plain_big = {id(p) for p in keep_big}
+        self.side = torch.cuda.Stream(device=self.params[0].device) if self.params[0].is_cuda else None
+        self.gathers = []
+
+    def _on_big_grad(self, p) -> None:
+        if world_size(self.group) <= 1 or p.grad is None:
+            return
+        if id(p) in self._plain_big:
+            return super()._on_big_grad(p)
+        lo, hi, gs = self.sharded[id(p)]
+        flat_g = p.grad.reshape(-1)
+        if td.get_backend(self.group) == "nccl":
+            cur = torch.cuda.current_stream(p.device)
+            self.side.wait_stream(cur)
+            with torch.cuda.stream(self.side):
+                flat_g.mul_(self.factor)                                              # weight B_local / B_global
+                td.reduce_scatter_tensor(gs, flat_g, op=td.ReduceOp.SUM, group=self.group)   # side waits for the result
+                with torch.no_grad():
+                    self.update(p)
+                    flat_p = p.data.view(-1)
+                    self.gathers.append(td.all_gather_into_tensor(flat_p, flat_p[lo:hi], group=self.group, async_op=True))
+        else:   # gloo (CPU tests): no reduce-scatter there; same data movement through an all-reduce
+            flat_g.mul_(self.factor)
+            td.all_reduce(flat_g, op=td.ReduceOp.SUM, group=self.group)
+            gs.copy_(flat_g[lo:hi])
+            with torch.no_grad():
+                self.update(p)
+                flat_p = p.data.view(-1)
+                parts = [torch.empty(hi - lo, dtype=flat_p.dtype) for _ in range(world_size(self.group))]
+                td.all_gather(parts, flat_p[lo:hi].clone(), group=self.group)
+                flat_p.copy_(torch.cat(parts))
+
+    def begin(self, local_batch: int, global_batch: int) -> None:
+        super().begin(local_batch, global_batch)
+        if hasattr(self.opt, "begin_step"):
+            self.opt.begin_step()
+
+    def join(self) -> None:
+        """Call after opt.step(): the updated slices of every rank have arrived before the next forward reads them."""
+        for w in self.gathers:
+            w.wait()
+        self.gathers = []
+        if self.side is not None:
+            torch.cuda.current_stream(self.params[0].device).wait_stream(self.side)

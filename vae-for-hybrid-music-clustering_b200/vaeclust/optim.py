@@ -34,13 +34,14 @@ class Adam:
                 raise VaeclustError("vaeclust.optim.Adam: parameters must be float32 CUDA tensors (no CPU path)")
         self.lr, self.betas, self.eps = float(lr), (float(betas[0]), float(betas[1])), float(eps)
         self.state: Dict[int, dict] = {}
-        self._table: Optional[dict] = None     # the chunk table on the device (key, dev, pinned)
+        self._tables: Dict[object, Optional[dict]] = {}   # chunk tables on the device, one per launch slot
         self._retired: list = []               # superseded tables: a captured graph may still read them
-        self._spare: Optional[dict] = None     # pre-allocated (pinned, device) pair for the next table change
+        self._spares: Dict[object, Optional[dict]] = {}   # pre-allocated (pinned, device) pair per slot
         # capturable (torch.optim.Adam(capturable=True)): step counter and bias corrections live on the device, so a
         # step recorded in a CUDA graph advances correctly on every replay (vc_adam_multi_graph)
         self.capturable = bool(capturable)
         self._dev_step = None
+        self._ticked = False                   # capturable: the device step counter was advanced by begin_step()
         # id(param) -> (lo, hi, grad_slice_fn): this rank owns elements [lo, hi) of the flattened parameter
         self._shards: Dict[int, tuple] = {}
         self.skip: set = set()                 # ids of parameters some fused kernel updates itself this step
@@ -98,7 +99,23 @@ class Adam:
                 segs.append((p.data_ptr() + 4 * lo, gs.data_ptr(), st, hi - lo))
         return segs
 
-    def _update(self, plist) -> None:
+    @torch.no_grad()
+    def begin_step(self) -> None:
+        """Call once at the start of a step whose parameters are updated by SEVERAL launches (update_now for sharded
+        tensors as soon as their gradient slice has been reduced, step() for the rest): in capturable mode the device
+        step counter advances here, once, and every launch of the step reads the bias corrections of that step."""
+        self._done = set()
+        if self.capturable:
+            lib().call("vc_adam_tick", ptr(self.device_step()), self.betas[0], self.betas[1], stream_ptr())
+            self._ticked = True
+
+    @torch.no_grad()
+    def update_now(self, p) -> None:
+        """Adam update of ONE parameter (its shard, if sharded) on the current stream, now; step() then skips it."""
+        self._update([p], slot=("now", id(p)))
+        self._done.add(id(p))
+
+    def _update(self, plist, slot="rest") -> None:
         """One launch over the chunk table of `plist` on the current stream (one launch per distinct step count)."""
         by_step: Dict[int, list] = {}
         for p, seg in zip(plist, self._segments(plist)):
@@ -123,7 +140,7 @@ class Adam:
             table = np.concatenate(rows, axis=0)
             key = table.tobytes()
             dev = plist[0].device
-            c = self._table
+            c = self._tables.get(slot)
             if c is None or c["key"] != key or c["dev"].device != dev:
                 if not self.capturable:
                     c = {"key": key, "dev": torch.from_numpy(table).to(dev, non_blocking=False)}
@@ -138,25 +155,25 @@ class Adam:
                         # others only the most recent few can still be in flight
                         keep = [r for r in self._retired if r.get("captured")]
                         self._retired = keep + [r for r in self._retired if not r.get("captured")][-4:]
-                    sp = self._spare
+                    sp = self._spares.get(slot)
                     if sp is None or tuple(sp["pinned"].shape) != table.shape or sp["dev"].device != dev:
                         sp = self._new_pair(table.shape, dev)
-                    self._spare = None
+                    self._spares[slot] = None
                     sp["pinned"].numpy()[...] = table
                     sp["dev"].copy_(sp["pinned"], non_blocking=True)   # async + pinned: legal inside a capture
                     sp["key"] = key
                     sp["captured"] = torch.cuda.is_current_stream_capturing()
                     c = sp
-                self._table = c
-            if self.capturable and self._spare is None and not torch.cuda.is_current_stream_capturing():
-                self._spare = self._new_pair(table.shape, dev)
+                self._tables[slot] = c
+            if self.capturable and self._spares.get(slot) is None and not torch.cuda.is_current_stream_capturing():
+                self._spares[slot] = self._new_pair(table.shape, dev)
             b1, b2 = self.betas
             if self.capturable:
                 if self._dev_step is None:
                     self._dev_step = torch.zeros(4, dtype=torch.int32, device=dev)
                     self._dev_step[0] = t - 1
-                lib().call("vc_adam_multi_graph", ptr(c["dev"]), int(table.shape[0]), self.lr, b1, b2, self.eps,
-                           ptr(self._dev_step), stream_ptr())
+                lib().call("vc_adam_multi_at" if self._ticked else "vc_adam_multi_graph", ptr(c["dev"]),
+                           int(table.shape[0]), self.lr, b1, b2, self.eps, ptr(self._dev_step), stream_ptr())
             else:
                 lib().call("vc_adam_multi", ptr(c["dev"]), int(table.shape[0]), self.lr, b1, b2, self.eps,
                            1.0 - b1 ** t, 1.0 - b2 ** t, stream_ptr())
@@ -169,9 +186,13 @@ class Adam:
     @torch.no_grad()
     def step(self) -> None:
         self.lr = float(self.param_groups[0]["lr"])
-        todo = [p for p in self.params if id(p) not in self.skip and (p.grad is not None or id(p) in self._shards)]
+        done = getattr(self, "_done", None) or ()
+        todo = [p for p in self.params if id(p) not in self.skip and id(p) not in done
+                and (p.grad is not None or id(p) in self._shards)]
         if todo:
             self._update(todo)
+        self._done = set()
+        self._ticked = False
 
     def device_step(self) -> torch.Tensor:
         """The device-resident VcAdamDeviceStep of capturable mode (allocated on first use)."""

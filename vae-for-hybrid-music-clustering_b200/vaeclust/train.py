@@ -61,7 +61,15 @@ class VAEStep:
         self.mode = VC_LOSS_SUM_MEAN if kind == "mlp19" else VC_LOSS_MEAN_MEAN
         self.multi = group is not None and vdist.world_size(group) > 1
         self.opt = Adam(model.parameters(), lr=lr, capturable=capturable)
-        self.sync = vdist.OverlappedGradSync(model.parameters(), group) if self.multi else None
+        # data parallel: the big tensors go reduce-scatter -> Adam on the slice -> all-gather (sharded optimizer state);
+        # VAECLUST_DP=allreduce selects the plain overlapped all-reduce + replicated Adam of round 1
+        self.sync = None
+        if self.multi:
+            big = int(os.environ.get("VAECLUST_DP_BIG_NUMEL", str(1 << 20)))   # tensors at least this large are sharded
+            if os.environ.get("VAECLUST_DP", "sharded") == "sharded":
+                self.sync = vdist.ShardedGradSync(model.parameters(), group, self.opt, big_numel=big)
+            else:
+                self.sync = vdist.OverlappedGradSync(model.parameters(), group, big_numel=big)
 
     def __call__(self, x, *extra, eps: Optional[torch.Tensor] = None, global_batch: Optional[int] = None,
                  local_rows: Optional[int] = None):
@@ -87,6 +95,8 @@ class VAEStep:
             if self.multi:
                 self.sync.finish()
             self.opt.step()
+            if self.multi and hasattr(self.sync, "join"):
+                self.sync.join()
             return stats
         else:
             mu, lv = m.encode(x)
@@ -104,6 +114,8 @@ class VAEStep:
         if self.multi:
             self.sync.finish()
         self.opt.step()
+        if self.multi and hasattr(self.sync, "join"):
+            self.sync.join()
         return stats  # device tensor [loss, recon, kl] of the local batch
 
 
