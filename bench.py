@@ -872,7 +872,12 @@ def main():
             raise SystemExit(f"bench.py: parity check against the oracle FAILED: {json.dumps(par)}")
     if world > 1:
         td.barrier()
-        td.destroy_process_group()
+        torch.cuda.synchronize()
+        # the step graphs captured this group's collectives; tearing the group down while they are alive can block in
+        # NCCL's abort path, so every rank leaves right after the final barrier (the JSON line is already flushed)
+        sys.stdout.flush()
+        sys.stderr.flush()
+        os._exit(0)
 
 
 if __name__ == "__main__":

@@ -52,6 +52,11 @@ def _worker(rank, world, port, out_dir, mode, graphed):
     torch.cuda.synchronize()
     np.savez(os.path.join(out_dir, f"{mode}_{int(graphed)}_r{rank}.npz", ), losses=np.array(losses),
              **{n: p.detach().cpu().numpy() for n, p in model.named_parameters()})
+    if graphed:
+        # tearing a process group down while a CUDA graph that captured its collectives is alive can block in NCCL's
+        # abort path: the results are on disk, leave without the teardown
+        sys.stdout.flush()
+        os._exit(0)
     td.destroy_process_group()
 
 
