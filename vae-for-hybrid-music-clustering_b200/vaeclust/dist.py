@@ -222,6 +222,7 @@ class ShardedGradSync(OverlappedGradSync):
         self._plain_big = {id(p) for p in keep_big}
         self.side = torch.cuda.Stream(device=self.params[0].device) if self.params[0].is_cuda else None
         self.gathers = []
+        self._premul = None if hasattr(td, "_make_nccl_premul_sum") else False
 
     def _on_big_grad(self, p) -> None:
         if world_size(self.group) <= 1 or p.grad is None:
@@ -234,8 +235,21 @@ class ShardedGradSync(OverlappedGradSync):
             cur = torch.cuda.current_stream(p.device)
             self.side.wait_stream(cur)
             with torch.cuda.stream(self.side):
-                flat_g.mul_(self.factor)                                              # weight B_local / B_global
-                td.reduce_scatter_tensor(gs, flat_g, op=td.ReduceOp.SUM, group=self.group)   # side waits for the result
+                # weight B_local / B_global inside the reduction when NCCL's pre-multiplied sum is available for
+                # reduce-scatter (saves a pass over the gradient), else as a separate scaling pass
+                if self._premul is None:
+                    try:
+                        td.reduce_scatter_tensor(gs, flat_g, op=td._make_nccl_premul_sum(self.factor), group=self.group)
+                        self._premul = True
+                    except Exception:   # noqa: BLE001  (older NCCL / torch builds)
+                        self._premul = False
+                        flat_g.mul_(self.factor)
+                        td.reduce_scatter_tensor(gs, flat_g, op=td.ReduceOp.SUM, group=self.group)
+                elif self._premul:
+                    td.reduce_scatter_tensor(gs, flat_g, op=td._make_nccl_premul_sum(self.factor), group=self.group)
+                else:
+                    flat_g.mul_(self.factor)
+                    td.reduce_scatter_tensor(gs, flat_g, op=td.ReduceOp.SUM, group=self.group)   # side waits for the result
                 with torch.no_grad():
                     self.update(p)
                     flat_p = p.data.view(-1)
