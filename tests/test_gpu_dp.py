@@ -49,6 +49,7 @@ def _worker(rank, world, port, out_dir, mode, graphed):
         w = torch.tensor([float(st[0]) * (hi - lo) / c["B"]], device="cuda")
         td.all_reduce(w)                                   # loss of the global batch = weighted mean of the rank means
         losses.append(float(w))
+    step.sync_params()       # sharded mode defers the all-gather of the last step's slices
     torch.cuda.synchronize()
     np.savez(os.path.join(out_dir, f"{mode}_{int(graphed)}_r{rank}.npz", ), losses=np.array(losses),
              **{n: p.detach().cpu().numpy() for n, p in model.named_parameters()})

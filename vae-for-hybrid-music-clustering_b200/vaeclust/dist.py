@@ -197,11 +197,15 @@ class ShardedGradSync(OverlappedGradSync):
     """Gradient exchange + optimizer for the data-parallel script-12 step with the optimizer state SHARDED over the ranks
     (SURVEY.md 8(e) C1): for each large parameter (the two 67 M-element FC weights, 99.5 % of the model)
         reduce-scatter(gradient)  ->  Adam on this rank's 1/world slice  ->  all-gather(parameter)
-    issued from the parameter's post-accumulate hook, so all three run under the rest of backward: the reduce-scatter
-    and the all-gather on NCCL's stream, the slice update on a side stream between them.  The wire bytes equal the
-    all-reduce they replace, but the 28 B/parameter Adam sweep and the moments shrink by the world size.  Small
-    parameters keep the flat all-reduce + replicated update (bit-identical replicas).
-    Protocol per step: begin() -> forward/backward -> finish() -> opt.step() -> join()."""
+    The reduce-scatter and the slice update are issued from the parameter's post-accumulate hook and run under the rest
+    of backward (NCCL's stream, then a side stream).  The all-gather of the updated slices is DEFERRED to the start of
+    the next step, where it runs under the forward convolutions; the layer that reads the parameter waits for it
+    (vaeclust.ops.linear looks for `weight._vc_gather`).  So per step the wire carries the same bytes as the all-reduce
+    it replaces, but half of them move while the forward computes instead of after backward, and the 28 B/parameter
+    Adam sweep and the moments shrink by the world size.  Small parameters keep the flat all-reduce + replicated update
+    (bit-identical replicas).
+    Protocol per step: begin() -> forward/backward -> finish() -> opt.step() -> join();  flush() brings every replica
+    up to date (call it before reading parameters: checkpoints, evaluation, the end of training)."""
 
     def __init__(self, params, group, opt, big_numel: int = 1 << 20, update=None):
         super().__init__(params, group, big_numel=big_numel)
@@ -222,6 +226,7 @@ class ShardedGradSync(OverlappedGradSync):
         self._plain_big = {id(p) for p in keep_big}
         self.side = torch.cuda.Stream(device=self.params[0].device) if self.params[0].is_cuda else None
         self.gathers = []
+        self.dirty = []      # sharded parameters whose other slices are stale (updated by their owners, not gathered yet)
         self._premul = None if hasattr(td, "_make_nccl_premul_sum") else False
 
     def _on_big_grad(self, p) -> None:
@@ -252,8 +257,7 @@ class ShardedGradSync(OverlappedGradSync):
                     td.reduce_scatter_tensor(gs, flat_g, op=td.ReduceOp.SUM, group=self.group)   # side waits for the result
                 with torch.no_grad():
                     self.update(p)
-                    flat_p = p.data.view(-1)
-                    self.gathers.append(td.all_gather_into_tensor(flat_p, flat_p[lo:hi], group=self.group, async_op=True))
+            self.dirty.append(p)
         else:   # gloo (CPU tests): no reduce-scatter there; same data movement through an all-reduce
             flat_g.mul_(self.factor)
             td.all_reduce(flat_g, op=td.ReduceOp.SUM, group=self.group)
@@ -265,15 +269,42 @@ class ShardedGradSync(OverlappedGradSync):
                 td.all_gather(parts, flat_p[lo:hi].clone(), group=self.group)
                 flat_p.copy_(torch.cat(parts))
 
+    def _start_gathers(self) -> None:
+        """All-gather the slices updated last step; the consumer of each parameter waits for `p._vc_gather`."""
+        if not self.dirty:
+            return
+        cur = torch.cuda.current_stream(self.params[0].device)
+        self.side.wait_stream(cur)
+        with torch.cuda.stream(self.side), torch.no_grad():
+            for p in self.dirty:
+                lo, hi, _ = self.sharded[id(p)]
+                flat_p = p.data.view(-1)
+                p._vc_gather = td.all_gather_into_tensor(flat_p, flat_p[lo:hi], group=self.group, async_op=True)
+        self.dirty = []
+
     def begin(self, local_batch: int, global_batch: int) -> None:
         super().begin(local_batch, global_batch)
         if hasattr(self.opt, "begin_step"):
             self.opt.begin_step()
+        if self.side is not None:
+            self._start_gathers()
 
     def join(self) -> None:
-        """Call after opt.step(): the updated slices of every rank have arrived before the next forward reads them."""
-        for w in self.gathers:
-            w.wait()
-        self.gathers = []
+        """Call after opt.step(): the side stream (slice updates) joins the step's stream."""
         if self.side is not None:
             torch.cuda.current_stream(self.params[0].device).wait_stream(self.side)
+        for p in self.big:          # a gather nobody waited for (layer not evaluated this step) must not dangle
+            w = getattr(p, "_vc_gather", None)
+            if w is not None:
+                w.wait()
+                p._vc_gather = None
+
+    def flush(self, force: bool = False) -> None:
+        """Bring every replica up to date now (before parameters are read outside the step).  force: gather every
+        sharded parameter whatever the bookkeeping says (graph replays update slices without running the hooks)."""
+        if force:
+            self.dirty = [p for p in self.big if id(p) in self.sharded]
+        if self.side is None or not self.dirty:
+            return
+        self._start_gathers()
+        self.join()

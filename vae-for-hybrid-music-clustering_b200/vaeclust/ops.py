@@ -137,6 +137,10 @@ class _DenseFn(torch.autograd.Function):
 
 def linear(x, weight, bias=None, relu: bool = False):
     """y = act(x W^T + b): nn.Linear(+ReLU) of 12:98-103,114-117,129-132,159-164; 19:79-95; 06:149-157."""
+    g = getattr(weight, "_vc_gather", None)
+    if g is not None:      # sharded data parallelism: the other ranks' slices of this weight are still arriving
+        g.wait()
+        weight._vc_gather = None
     return _DenseFn.apply("linear", x, weight, bias, relu)
 
 

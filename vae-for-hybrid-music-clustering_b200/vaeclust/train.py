@@ -119,6 +119,13 @@ class VAEStep:
         return stats  # device tensor [loss, recon, kl] of the local batch
 
 
+    def sync_params(self, force: bool = False) -> None:
+        """Data parallel with sharded optimizer state: bring every rank's copy of the parameters up to date (the
+        all-gather of the last step's slices is otherwise deferred into the next step).  Call before reading them."""
+        if self.sync is not None and hasattr(self.sync, "flush"):
+            self.sync.flush(force)
+
+
 class GraphedVAEStep:
     """The same optimisation step recorded once into a CUDA graph and replayed: the ~125 kernel launches
     of a step are submitted by one cudaGraphLaunch, which removes the host launch gaps between the short kernels of
@@ -140,6 +147,10 @@ class GraphedVAEStep:
     @property
     def opt(self):
         return self.step.opt
+
+    def sync_params(self) -> None:
+        if hasattr(self.step, "sync_params"):
+            self.step.sync_params(force=self.graph is not None)
 
     def __call__(self, x, *extra, eps: Optional[torch.Tensor] = None, global_batch: Optional[int] = None):
         self.calls += 1
@@ -275,6 +286,8 @@ def fit(model, kind: str, arrays, epochs: int, batch_size: int, lr: float, beta:
             denom += w
         if world > 1:
             vdist.all_reduce_sum(acc, group)
+            if hasattr(step, "sync_params"):
+                step.sync_params()      # replicas up to date before the epoch callback (checkpoints) reads them
         tot = acc.cpu().numpy() / max(denom, 1.0)  # the one host sync of the epoch
         log.loss.append(float(tot[0])); log.recon.append(float(tot[1])); log.kl.append(float(tot[2]))
         if on_epoch is not None:
