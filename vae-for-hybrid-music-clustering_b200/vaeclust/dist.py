@@ -276,7 +276,9 @@ class ShardedGradSync(OverlappedGradSync):
         cur = torch.cuda.current_stream(self.params[0].device)
         self.side.wait_stream(cur)
         with torch.cuda.stream(self.side), torch.no_grad():
-            for p in self.dirty:
+            # backward produced the gradients in reverse layer order, the forward needs the weights in layer order: gather
+            # in the reverse of the order the hooks fired, so the first layer's weight arrives first
+            for p in reversed(self.dirty):
                 lo, hi, _ = self.sharded[id(p)]
                 flat_p = p.data.view(-1)
                 p._vc_gather = td.all_gather_into_tensor(flat_p, flat_p[lo:hi], group=self.group, async_op=True)
