@@ -581,7 +581,10 @@ def _sil_prepare(Xd: torch.Tensor, order: torch.Tensor, mean64: torch.Tensor):
     return Xs, sqn
 
 
-SILHOUETTE_MMA_PER_PRODUCT = 4   # bf16 hi/lo split: hi.hi + hi.lo + lo.hi + lo.lo
+import os as _os
+
+# bf16 hi/lo split of both operands: hi.hi + hi.lo + lo.hi (+ lo.lo, 2^-16 of the product, with VAECLUST_SIL_MMA=4)
+SILHOUETTE_MMA_PER_PRODUCT = 4 if _os.environ.get("VAECLUST_SIL_MMA", "3").startswith("4") else 3
 SILHOUETTE_PRECISION = "tc"  # "tc": tcgen05 bf16 hi/lo split (d <= 128); "fp32": FFMA tile kernel
 
 
