@@ -108,6 +108,22 @@ int vc_convT2d_s2k4_dgrad(const float* dy, const float* W, float* dx, int B, int
 int vc_convT2d_s2k4_wgrad(const float* dy, const float* x, float* dW, int B, int Cin, int H, int Wd, int Cout,
                           void* workspace, size_t workspace_bytes, void* stream);
 
+/* TMA-fed data gradients (bf16 tensor-core mode): the masked gradient g = dy * (y > 0) of a ReLU(conv) / ReLU(convT)
+ * layer of 12:87-89,135-137 is produced ONCE, by the pass that also yields the bias gradient, as fp32 NCHW (for the
+ * weight-gradient kernel) and as a bf16 NHWC copy; the data-gradient implicit GEMM then fetches its A tiles from
+ * that copy with 4-D TMA boxes (no gather warps).  vc_relu_bwd_bias_nhwc: dy, y [B,C,H,W] fp32 -> g [B,C,H,W] fp32,
+ * g_nhwc [B,H,W,C] bf16, db [C]; needs C % 8 == 0, C <= 256, W % 64 == 0.  vc_conv_dgrad_nhwc: op is
+ * VC_OP_CONV_DGRAD (g_nhwc [B,OH,OW,Cout] -> dx [B,Cin,H,W]) or VC_OP_CONVT_DGRAD (g_nhwc [B,2H,2W,Cout] ->
+ * dx [B,Cin,H,W]); geometry arguments as in vc_dense_op; ..._supported() says whether the shape qualifies (rows of 128
+ * pixels, 32 / 64 / 128 channels), otherwise callers use vc_relu_bwd_bias + vc_dense_op. */
+size_t vc_relu_bwd_bias_nhwc_workspace_bytes(int C);
+int vc_relu_bwd_bias_nhwc(const float* dy, const float* y, int B, int C, int H, int W, float* g, void* g_nhwc, float* db,
+                          void* workspace, size_t workspace_bytes, void* stream);
+int vc_conv_dgrad_nhwc_supported(int op, int B, int Cin, int H, int W, int Cout);
+size_t vc_conv_dgrad_nhwc_workspace_bytes(int op, int B, int Cin, int H, int W, int Cout);
+int vc_conv_dgrad_nhwc(int op, const void* g_nhwc, const float* W, float* dx, int B, int Cin, int H, int Wd, int Cout,
+                       void* workspace, size_t workspace_bytes, void* stream);
+
 /* One entry point for every dense-layer op in either precision.  VC_PREC_FP32: the fp32 FFMA kernels above
  * (reference-precision path).  VC_PREC_BF16_TC: operands rounded to bf16, tcgen05 tensor-core MMAs with fp32
  * accumulation in tensor memory, fp32 outputs.  Argument meaning per op (in0, in1 -> out):

@@ -306,3 +306,46 @@ def test_convT2d_s2k4_bf16(B, Cin, H, W, Cout, relu, bf16_mode):
         y = F.conv_transpose2d(x, w, b, stride=2, padding=1)
         return F.relu(y) if relu else y
     _check_bf16(lambda x, w, b: ops.convT2d_s2k4(x, w, b, relu), ref, x, w, b)
+
+
+@pytest.mark.parametrize("kind,B,Cin,H,W,Cout", [
+    ("conv", 2, 32, 8, 512, 64),      # script-12 conv.2: dy 64 channels, rows of 256 pixels, phase-merged N = 128
+    ("conv", 3, 64, 6, 256, 128),     # conv.4: dy 128 channels = two 64-channel chunks per tap, N = 256
+    ("convT", 2, 128, 4, 128, 64),    # deconv.0: stride-2 traversal of the tensor map, 16 taps
+    ("convT", 2, 64, 5, 256, 32),     # deconv.2: 32-channel source through the pixel-pair view (12 k-blocks)
+    ("convT", 1, 64, 3, 128, 32),
+])
+def test_tma_fed_data_gradients(kind, B, Cin, H, W, Cout, bf16_mode):
+    """The TMA-fed data-gradient path (vc_relu_bwd_bias_nhwc + vc_conv_dgrad_nhwc: bf16 NHWC copy of g = dy * (y > 0),
+    4-D tensor-map boxes with zero-filled padding and traversal stride) against (a) the gather kernel it replaces --
+    the same bf16 products, so dx agrees to fp32 summation order and g / db / dw bit for bit or nearly -- and (b) fp32
+    autograd on bf16-rounded operands."""
+    from vaeclust import ops
+    if kind == "conv":
+        x, w, b = _rand(B, Cin, H, W, seed=1), _rand(Cout, Cin, 3, 3, seed=2, scale=(Cin * 9) ** -0.5), _rand(Cout, seed=3)
+        ours = lambda x, w, b: ops.conv2d_s2k3(x, w, b, True)
+        ref = lambda x, w, b: F.relu(F.conv2d(x, w, b, stride=2, padding=1))
+    else:
+        x, w, b = _rand(B, Cin, H, W, seed=1), _rand(Cin, Cout, 4, 4, seed=2, scale=(Cin * 4) ** -0.5), _rand(Cout, seed=3)
+        ours = lambda x, w, b: ops.convT2d_s2k4(x, w, b, True)
+        ref = lambda x, w, b: F.relu(F.conv_transpose2d(x, w, b, stride=2, padding=1))
+    grads = {}
+    calls = {}
+    for flag in (True, False):
+        ops.USE_TMA_DGRAD = flag
+        n0 = ops.lib().n_calls
+        try:
+            xa, wa, ba = (t.clone().requires_grad_(True) for t in (x, w, b))
+            y = ours(xa, wa, ba)
+            gsrc = torch.randn(y.shape, generator=torch.Generator().manual_seed(5)).cuda()
+            y.backward(gsrc)
+        finally:
+            ops.USE_TMA_DGRAD = True
+        grads[flag] = (xa.grad.clone(), wa.grad.clone(), ba.grad.clone())
+        calls[flag] = ops.lib().n_calls - n0
+    assert calls[True] != calls[False]          # the new entry points really ran
+    sx = float(grads[False][0].abs().max())
+    torch.testing.assert_close(grads[True][0], grads[False][0], rtol=1e-4, atol=1e-5 * sx)
+    torch.testing.assert_close(grads[True][1], grads[False][1], rtol=1e-5, atol=1e-6 * float(grads[False][1].abs().max()))
+    torch.testing.assert_close(grads[True][2], grads[False][2], rtol=1e-5, atol=1e-5 * float(grads[False][2].abs().max()))
+    _check_bf16(ours, ref, x, w, b)

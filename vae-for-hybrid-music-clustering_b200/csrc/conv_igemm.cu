@@ -370,6 +370,15 @@ conv_igemm_kernel(const IgArgs a, const __grid_constant__ CUtensorMap mapW) {
 // ---- host side ----------------------------------------------------------------------------------------------------
 namespace vc {
 
+// tap-major weight slab Bw[n][k] for the other implicit-GEMM translation unit (conv_igemm_tma.cu)
+int ig_build_weights(const float* w, int mode, int Cin, int Cout, int N, int BN, int K, int Kp, __nv_bfloat16* out,
+                     cudaStream_t s) {
+  const int total = BN * Kp;
+  ig_weights_kernel<<<(total + 255) / 256, 256, 0, s>>>(w, mode, Cin, Cout, N, BN, K, Kp, out);
+  VC_LAUNCH_CHECK();
+  return VC_OK;
+}
+
 struct IgPlan { int mode, C, taps, N, BN, K, Kp; bool ok; };
 
 static IgPlan ig_plan(int op, int B, int Cin, int H, int W, int Cout) {

@@ -61,6 +61,7 @@ _LAUNCHES = {
     "vc_recon_loss_fwd_bwd": 2, "vc_conv2d_s2k3_wgrad": 2, "vc_convT2d_s2k4_wgrad": 2, "vc_convT2d_s2k4_fwd": 4,
     "vc_kmeans_assign_update": 2, "vc_cluster_sums": 2, "vc_kmeans_inertia": 2, "vc_dbi_intra": 2, "vc_col_stats": 2,
     "vc_silhouette_finalize": 2, "vc_bias_grad": 2, "vc_relu_bwd_bias": 2, "vc_dense_op": 2,
+    "vc_relu_bwd_bias_nhwc": 2, "vc_conv_dgrad_nhwc": 2, "vc_mlpvae_step": 4, "vc_kmeans_lloyd_estep": 2,
 }
 
 

@@ -38,6 +38,7 @@ def _f32(t: torch.Tensor, name: str) -> torch.Tensor:
 
 
 # ----------------------------------------------------------------------------------------------- dense layers
+USE_TMA_DGRAD = True  # bf16 mode: conv / convT data gradients from a bf16 NHWC copy of the masked gradient, fed by TMA
 PRECISION = "fp32"  # "fp32": FFMA reference-precision kernels; "bf16": tcgen05 tensor cores (bf16 in, fp32 accumulate)
 _PREC = {"fp32": 0, "bf16": 1}
 _OPS = {"linear": (0, 1, 2), "conv": (3, 4, 5), "convT": (6, 7, 8)}  # (fwd, dgrad, wgrad) ids of vc_dense_op
@@ -110,6 +111,23 @@ class _DenseFn(torch.autograd.Function):
             dx = torch.empty_like(x) if ctx.needs_input_grad[1] else None
             lib().call("vc_linear_bwd_small", ptr(dy), ptr(y) if ctx.relu else None, ptr(x), ptr(weight), ptr(dw),
                        ptr(db), ptr(dx), B, Cin, Cout, s)
+            return None, dx, dw, db, None
+        if (ctx.kind != "linear" and ctx.prec == _PREC["bf16"] and ctx.relu and want_db and ctx.needs_input_grad[1]
+                and USE_TMA_DGRAD and dy.shape[1] % 8 == 0 and dy.shape[1] <= 256 and dy.shape[3] % 64 == 0
+                and lib().size("vc_conv_dgrad_nhwc_supported", op_d, B, Cin, H, W, Cout)):
+            # g = dy * (y > 0) once, as fp32 NCHW (weight gradient) and bf16 NHWC (TMA-fed data gradient), + db
+            g = torch.empty_like(dy)
+            gn = torch.empty((dy.shape[0], dy.shape[2], dy.shape[3], dy.shape[1]), dtype=torch.bfloat16, device=dy.device)
+            db = torch.empty(Cout, dtype=torch.float32, device=x.device)
+            ws = _workspace(max(lib().size("vc_relu_bwd_bias_nhwc_workspace_bytes", Cout),
+                                lib().size("vc_conv_dgrad_nhwc_workspace_bytes", op_d, B, Cin, H, W, Cout)), x.device)
+            lib().call("vc_relu_bwd_bias_nhwc", ptr(dy), ptr(y), B, Cout, dy.shape[2], dy.shape[3], ptr(g), ptr(gn),
+                       ptr(db), ptr(ws), ws.numel(), s)
+            dx = torch.empty_like(x)
+            lib().call("vc_conv_dgrad_nhwc", op_d, ptr(gn), ptr(weight), ptr(dx), B, Cin, H, W, Cout, ptr(ws), ws.numel(), s)
+            if ctx.needs_input_grad[2]:
+                dw = torch.empty_like(weight)
+                _dense(op_w, ctx.prec, g, x, None, dw, B, Cin, H, W, Cout, False)
             return None, dx, dw, db, None
         if ctx.relu and want_db:  # ReLU mask and bias gradient in one pass over dy / y
             g = torch.empty_like(dy)
