@@ -343,7 +343,7 @@ def test_tma_fed_data_gradients(kind, B, Cin, H, W, Cout, bf16_mode):
             gsrc = torch.randn(y.shape, generator=torch.Generator().manual_seed(5)).cuda()
             y.backward(gsrc)
         finally:
-            ops.USE_TMA_DGRAD = True
+            ops.USE_TMA_DGRAD = False
             L.call = real_call
         grads[flag] = (xa.grad.clone(), wa.grad.clone(), ba.grad.clone())
         calls[flag] = names
@@ -352,4 +352,8 @@ def test_tma_fed_data_gradients(kind, B, Cin, H, W, Cout, bf16_mode):
     torch.testing.assert_close(grads[True][0], grads[False][0], rtol=1e-4, atol=1e-5 * sx)
     torch.testing.assert_close(grads[True][1], grads[False][1], rtol=1e-5, atol=1e-6 * float(grads[False][1].abs().max()))
     torch.testing.assert_close(grads[True][2], grads[False][2], rtol=1e-5, atol=1e-5 * float(grads[False][2].abs().max()))
-    _check_bf16(ours, ref, x, w, b)
+    ops.USE_TMA_DGRAD = True
+    try:
+        _check_bf16(ours, ref, x, w, b)
+    finally:
+        ops.USE_TMA_DGRAD = False

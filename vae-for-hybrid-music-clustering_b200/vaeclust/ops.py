@@ -38,7 +38,11 @@ def _f32(t: torch.Tensor, name: str) -> torch.Tensor:
 
 
 # ----------------------------------------------------------------------------------------------- dense layers
-USE_TMA_DGRAD = True  # bf16 mode: conv / convT data gradients from a bf16 NHWC copy of the masked gradient, fed by TMA
+# bf16 mode: conv / convT data gradients from a bf16 NHWC copy of the masked gradient, fetched by TMA
+# (csrc/conv_igemm_tma.cu).  Measured on B200 at the script-12 shapes: the four data-gradient kernels drop from 0.494 to
+# 0.335 ms/step, but emitting the NHWC copy from the fp32-NCHW ReLU-backward pass costs 0.33 ms more than the plain pass
+# (step 3.90 -> 4.07 ms), so it stays OFF until activations flow in bf16 NHWC end to end.
+USE_TMA_DGRAD = False
 PRECISION = "fp32"  # "fp32": FFMA reference-precision kernels; "bf16": tcgen05 tensor cores (bf16 in, fp32 accumulate)
 _PREC = {"fp32": 0, "bf16": 1}
 _OPS = {"linear": (0, 1, 2), "conv": (3, 4, 5), "convT": (6, 7, 8)}  # (fwd, dgrad, wgrad) ids of vc_dense_op
