@@ -371,12 +371,21 @@ tap_wgrad_kernel(const float* __restrict__ A, const float* __restrict__ S, doubl
     }
 }
 
-// out[e] = sum over the nblk block partials part[blk][C*T], in block order
-__global__ void tap_wgrad_fold_kernel(const double* __restrict__ part, int nblk, int n, float* __restrict__ out) {
-  const int e = blockIdx.x * blockDim.x + threadIdx.x;
-  if (e >= n) return;
+// out[e] = sum over the nblk block partials part[blk][C*T].  A block owns 32 consecutive outputs; its eight warps each
+// add every eighth partial and the eight sub-sums are added in warp order (fixed order: bit-identical from run to run)
+__global__ void __launch_bounds__(256) tap_wgrad_fold_kernel(const double* __restrict__ part, int nblk, int n,
+                                                             float* __restrict__ out) {
+  __shared__ double sub[8][32];
+  const int lane = threadIdx.x & 31, g = threadIdx.x >> 5;
+  const int e = blockIdx.x * 32 + lane;
   double v = 0.0;
-  for (int b = 0; b < nblk; ++b) v += part[(int64_t)b * n + e];
+  if (e < n)
+    for (int b = g; b < nblk; b += 8) v += part[(int64_t)b * n + e];
+  sub[g][lane] = v;
+  __syncthreads();
+  if (g != 0 || e >= n) return;
+#pragma unroll
+  for (int i = 1; i < 8; ++i) v += sub[i][lane];
   out[e] = (float)v;
 }
 
@@ -415,7 +424,7 @@ int conv_direct_wgrad_run(int op, const float* dy, const float* x, float* dw, in
     if ((int64_t)nblk * 32 > quads) nblk = (int)((quads + 31) / 32);
     tap_wgrad_kernel<3, CG><<<dim3(nblk, (groups + 7) / 8), 256, 0, s>>>(dy, x, part, B, Cout, OH, OW, H, W, round_bf16);
     VC_LAUNCH_CHECK();
-    tap_wgrad_fold_kernel<<<(Cout * T + 127) / 128, 128, 0, s>>>(part, nblk, Cout * T, dw);
+    tap_wgrad_fold_kernel<<<(Cout * T + 31) / 32, 256, 0, s>>>(part, nblk, Cout * T, dw);
   } else {                        // A = x [B,Cin,H,W], S = dy [B,1,2H,2W]
     constexpr int CG = 4, T = 16;
     const int groups = Cin / CG;
@@ -424,7 +433,7 @@ int conv_direct_wgrad_run(int op, const float* dy, const float* x, float* dw, in
     tap_wgrad_kernel<4, CG><<<dim3(nblk, (groups + 7) / 8), 256, 0, s>>>(x, dy, part, B, Cin, H, W, 2 * H, 2 * W,
                                                                           round_bf16);
     VC_LAUNCH_CHECK();
-    tap_wgrad_fold_kernel<<<(Cin * T + 127) / 128, 128, 0, s>>>(part, nblk, Cin * T, dw);
+    tap_wgrad_fold_kernel<<<(Cin * T + 31) / 32, 256, 0, s>>>(part, nblk, Cin * T, dw);
   }
   VC_LAUNCH_CHECK();
   return VC_OK;

@@ -562,12 +562,21 @@ __global__ void __launch_bounds__(WG_THREADS, 1) conv_wgrad_fast_kernel(const Wg
   }
 }
 
-__global__ void wgrad_fold_kernel(const float* __restrict__ part, int nsplit, int total, float* __restrict__ out) {
-
-  const int e = blockIdx.x * blockDim.x + threadIdx.x;
-  if (e >= total) return;
+// split-K partials -> dw.  A block owns 32 consecutive outputs; its eight warps each add every eighth partial and the
+// eight sub-sums are added in warp order (a fixed order: the gradient is bit-identical from run to run)
+__global__ void __launch_bounds__(256) wgrad_fold_kernel(const float* __restrict__ part, int nsplit, int total,
+                                                         float* __restrict__ out) {
+  __shared__ float sub[8][32];
+  const int lane = threadIdx.x & 31, g = threadIdx.x >> 5;
+  const int e = blockIdx.x * 32 + lane;
   float acc = 0.f;
-  for (int zz = 0; zz < nsplit; ++zz) acc += part[(int64_t)zz * total + e];
+  if (e < total)
+    for (int zz = g; zz < nsplit; zz += 8) acc += part[(int64_t)zz * total + e];
+  sub[g][lane] = acc;
+  __syncthreads();
+  if (g != 0 || e >= total) return;
+#pragma unroll
+  for (int i = 1; i < 8; ++i) acc += sub[i][lane];
   out[e] = acc;
 }
 
@@ -658,7 +667,7 @@ int conv_wgrad_igemm_run(int op, const float* dy, const float* x, float* dw, int
     fk<<<dim3((unsigned)p.nsplit, (unsigned)p.ntiles), WG_THREADS, fsmem, s>>>(a);
     VC_LAUNCH_CHECK();
     const int tot = p.Cp * p.N;
-    wgrad_fold_kernel<<<(tot + 255) / 256, 256, 0, s>>>(a.part, p.nsplit, tot, dw);
+    wgrad_fold_kernel<<<(tot + 31) / 32, 256, 0, s>>>(a.part, p.nsplit, tot, dw);
     VC_LAUNCH_CHECK();
     return VC_OK;
   }
@@ -672,7 +681,7 @@ int conv_wgrad_igemm_run(int op, const float* dy, const float* x, float* dw, int
   kern<<<grid, WG_THREADS, smem, s>>>(a);
   VC_LAUNCH_CHECK();
   const int total = p.Cp * p.N;
-  wgrad_fold_kernel<<<(total + 255) / 256, 256, 0, s>>>(a.part, p.nsplit, total, dw);
+  wgrad_fold_kernel<<<(total + 31) / 32, 256, 0, s>>>(a.part, p.nsplit, total, dw);
   VC_LAUNCH_CHECK();
   return VC_OK;
 }

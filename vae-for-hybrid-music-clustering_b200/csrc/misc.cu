@@ -210,6 +210,26 @@ __global__ void bias_grad_stage2(const double* __restrict__ part, int C, int S, 
   db[c] = (accumulate ? db[c] : 0.f) + (float)acc;
 }
 
+// the same with one warp per channel (many partials, few channels: the single-channel reconstruction bias has 512+):
+// lane l adds partials l, l+32, ... and the 32 sub-sums meet in a fixed butterfly, so the result does not vary by run
+__global__ void bias_grad_stage2_warp(const double* __restrict__ part, int C, int S, float* __restrict__ db,
+                                      int accumulate) {
+  const int c = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (c >= C) return;
+  double acc = 0.0;
+  for (int s = lane; s < S; s += 32) acc += part[(int64_t)c * S + s];
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+  if (lane == 0) db[c] = (accumulate ? db[c] : 0.f) + (float)acc;
+}
+
+static void launch_bias_stage2(const double* part, int C, int S, float* db, int accumulate, cudaStream_t st) {
+  if (S >= 32 && C <= 65536)
+    bias_grad_stage2_warp<<<(C * 32 + 127) / 128, 128, 0, st>>>(part, C, S, db, accumulate);
+  else
+    bias_grad_stage2<<<(C + 127) / 128, 128, 0, st>>>(part, C, S, db, accumulate);
+}
+
 __global__ void cat_gate_fwd_kernel(const float* __restrict__ a, int na, const float* __restrict__ l, int nl,
                                     const float* __restrict__ gate, int append_gate, int B,
                                     float* __restrict__ out) {
@@ -433,7 +453,7 @@ extern "C" int vc_relu_bwd_bias(const float* dy, const float* y, int64_t outer, 
     relu_bwd_bias_stage1<<<dim3(C, S), 256, 0, as_stream(stream)>>>(dy, y, g, outer, C, inner, S, part);
   }
   VC_LAUNCH_CHECK();
-  bias_grad_stage2<<<(C + 127) / 128, 128, 0, as_stream(stream)>>>(part, C, S, db, 0);
+  launch_bias_stage2(part, C, S, db, 0, as_stream(stream));
   VC_LAUNCH_CHECK();
   return VC_OK;
 }
@@ -460,7 +480,7 @@ extern "C" int vc_bias_grad(const float* dy, int64_t outer, int C, int64_t inner
     bias_grad_stage1<<<dim3(C, S), 256, 0, as_stream(stream)>>>(dy, outer, C, inner, S, part);
   }
   VC_LAUNCH_CHECK();
-  bias_grad_stage2<<<(C + 127) / 128, 128, 0, as_stream(stream)>>>(part, C, S, db, accumulate);
+  launch_bias_stage2(part, C, S, db, accumulate, as_stream(stream));
   VC_LAUNCH_CHECK();
   return VC_OK;
 }

@@ -65,6 +65,31 @@ __global__ void sk_small_operand_kernel(const float* __restrict__ src, int64_t l
   }
 }
 
+// the same for a row-major source with 16-byte aligned rows (the 64 x 262144 activations of the two wide layers): eight
+// consecutive k per thread, two 16-byte loads and one 16-byte store, so the pass runs at copy speed instead of one
+// division and one 2-byte store per element
+__global__ void sk_small_operand_rows_kernel(const float* __restrict__ src, int64_t ld, int N, int K, int BN, int Kp,
+                                             __nv_bfloat16* __restrict__ out) {
+  const int g8 = Kp >> 3;
+  const int64_t total = (int64_t)BN * g8;
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += stride) {
+    const int n = (int)(e / g8), k = (int)(e - (int64_t)n * g8) << 3;
+    uint4 o = make_uint4(0u, 0u, 0u, 0u);
+    if (n < N && k + 8 <= K) {
+      const float4* p = reinterpret_cast<const float4*>(src + (int64_t)n * ld + k);
+      const float4 a = __ldg(p), b = __ldg(p + 1);
+      o = make_uint4(sk_pack(a.x, a.y), sk_pack(a.z, a.w), sk_pack(b.x, b.y), sk_pack(b.z, b.w));
+    } else if (n < N && k < K) {
+      float v[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) v[j] = k + j < K ? src[(int64_t)n * ld + k + j] : 0.f;
+      o = make_uint4(sk_pack(v[0], v[1]), sk_pack(v[2], v[3]), sk_pack(v[4], v[5]), sk_pack(v[6], v[7]));
+    }
+    *reinterpret_cast<uint4*>(out + (int64_t)n * Kp + k) = o;
+  }
+}
+
 __global__ void __launch_bounds__(SK_THREADS, 2)
 skinny_gemm_kernel(const SkArgs a, const __grid_constant__ CUtensorMap mapB) {
   extern __shared__ unsigned char smem_raw[];
@@ -244,15 +269,25 @@ skinny_gemm_kernel(const SkArgs a, const __grid_constant__ CUtensorMap mapB) {
   }
 }
 
-// fold split-K partials [nsplit][N][M] in a fixed order, then bias (per m) / ReLU / layout
-__global__ void sk_fold_kernel(const float* __restrict__ part, int nsplit, int M, int N, const float* __restrict__ bias,
-                               int relu, int transposed, int64_t ldo, float* __restrict__ out) {
-  const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+// fold split-K partials [nsplit][N][M] in a fixed order, then bias (per m) / ReLU / layout.  A block owns 32 consecutive
+// outputs; its eight warps each add every eighth partial (coalesced 128-byte rows), and the eight sub-sums are added in
+// warp order -- the same order on every run.
+__global__ void __launch_bounds__(256) sk_fold_kernel(const float* __restrict__ part, int nsplit, int M, int N,
+                                                      const float* __restrict__ bias, int relu, int transposed,
+                                                      int64_t ldo, float* __restrict__ out) {
+  __shared__ float sub[8][32];
+  const int lane = threadIdx.x & 31, g = threadIdx.x >> 5;
+  const int64_t e = (int64_t)blockIdx.x * 32 + lane;
   const int64_t MN = (int64_t)M * N;
-  if (e >= MN) return;
-  const int n = (int)(e / M), m = (int)(e - (int64_t)n * M);
   float acc = 0.f;
-  for (int zz = 0; zz < nsplit; ++zz) acc += part[(int64_t)zz * MN + e];
+  if (e < MN)
+    for (int zz = g; zz < nsplit; zz += 8) acc += __ldg(part + (int64_t)zz * MN + e);
+  sub[g][lane] = acc;
+  __syncthreads();
+  if (g != 0 || e >= MN) return;
+#pragma unroll
+  for (int i = 1; i < 8; ++i) acc += sub[i][lane];
+  const int n = (int)(e / M), m = (int)(e - (int64_t)n * M);
   if (bias) acc += bias[m];
   if (relu) acc = fmaxf(acc, 0.f);
   out[transposed ? (int64_t)n * ldo + m : (int64_t)m * ldo + n] = acc;
@@ -344,7 +379,13 @@ int skinny_gemm_run(int op, const float* in0, const float* in1, const float* bia
     const int64_t total = (int64_t)p.BN * p.Kp;
     int64_t blocks = (total + 255) / 256;
     if (blocks > (int64_t)sm_count() * 16) blocks = (int64_t)sm_count() * 16;
-    sk_small_operand_kernel<<<(int)blocks, 256, 0, s>>>(small, p.ld_small, p.small_colmajor, p.N, p.K, p.BN, p.Kp, Bs);
+    if (!p.small_colmajor && (p.ld_small & 3) == 0 && (reinterpret_cast<uintptr_t>(small) & 15) == 0) {
+      blocks = (total / 8 + 255) / 256;
+      if (blocks > (int64_t)sm_count() * 16) blocks = (int64_t)sm_count() * 16;
+      sk_small_operand_rows_kernel<<<(int)blocks, 256, 0, s>>>(small, p.ld_small, p.N, p.K, p.BN, p.Kp, Bs);
+    } else {
+      sk_small_operand_kernel<<<(int)blocks, 256, 0, s>>>(small, p.ld_small, p.small_colmajor, p.N, p.K, p.BN, p.Kp, Bs);
+    }
     VC_LAUNCH_CHECK();
   }
   CUtensorMap mb;
@@ -370,7 +411,7 @@ int skinny_gemm_run(int op, const float* in0, const float* in1, const float* bia
   VC_LAUNCH_CHECK();
   if (part) {
     const int64_t MN = (int64_t)p.M * p.N;
-    sk_fold_kernel<<<(int)((MN + 255) / 256), 256, 0, s>>>(part, p.nsplit, p.M, p.N, a.bias, relu, p.transposed, p.ldo, out);
+    sk_fold_kernel<<<(int)((MN + 31) / 32), 256, 0, s>>>(part, p.nsplit, p.M, p.N, a.bias, relu, p.transposed, p.ldo, out);
     VC_LAUNCH_CHECK();
   }
   return VC_OK;
