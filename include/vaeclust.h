@@ -78,6 +78,14 @@ int vc_linear_wgrad(const float* dy, const float* x, float* dW, int M, int N, in
 size_t vc_bias_grad_workspace_bytes(int C);
 int vc_bias_grad(const float* dy, int64_t outer, int C, int64_t inner, float* db, int accumulate, void* workspace,
                  size_t workspace_bytes, void* stream);
+/* vc_bias_grad with NO workspace argument and no allocation of any kind (no counterpart in the reference: added
+ * for callers that cannot call cudaMalloc -- CUDA graph capture, serving loops).  The
+ * partial sums live in a 2 MiB file-scope device array that every GPU loading the library holds until exit; C is limited
+ * to vc_bias_grad_noalloc_max_channels() (4096), larger C returns VC_ERR_UNSUPPORTED.  Results are bit-identical to
+ * vc_bias_grad.  All calls on a device share the array: calls that overlap on the GPU (different streams without a
+ * dependency) race; calls ordered on one stream are safe and nothing needs clearing between them. */
+int vc_bias_grad_noalloc_max_channels(void);
+int vc_bias_grad_noalloc(const float* dy, int64_t outer, int C, int64_t inner, float* db, int accumulate, void* stream);
 /* dx = dy * (y > 0) */
 int vc_relu_bwd(const float* dy, const float* y, float* dx, int64_t n, void* stream);
 /* Both of the above in one pass over dy/y ([outer, C, inner] layout): g = dy * (y > 0) and db[c] = sum g, the two

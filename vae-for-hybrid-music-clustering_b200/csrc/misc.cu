@@ -485,6 +485,59 @@ extern "C" int vc_bias_grad(const float* dy, int64_t outer, int C, int64_t inner
   return VC_OK;
 }
 
+// ---- vc_bias_grad without any caller-provided or allocated scratch ---------------------------------------------------
+// For callers that cannot allocate (CUDA graph capture, serving loops): the per-channel double partials live in a
+// file-scope device array.  Every GPU that loads the library holds these 2 MiB until the process exits.  In host code
+// the array's NAME is only a host-side stand-in; the device address is looked up once per device with
+// cudaGetSymbolAddress and that pointer is what the kernels receive.  All calls on a device share the array: two calls
+// that overlap on the GPU (different streams, no dependency) race.  Nothing in it has to start at zero -- stage 1 writes
+// every partial that stage 2 reads -- so leftovers of the previous call are harmless.
+constexpr int kNoAllocMaxC = 4096;                                   // channels per call
+static __device__ __align__(256) double g_bias_scratch[(size_t)kBiasSplits * kNoAllocMaxC];
+constexpr int kNoAllocMaxDevices = 64;
+static double* g_bias_scratch_ptr[kNoAllocMaxDevices] = {nullptr};   // device address of the array, per device ordinal
+
+static int bias_scratch_address(double** out) {
+  int dev = -1;
+  VC_CUDA(cudaGetDevice(&dev));
+  VC_REQUIRE(dev >= 0 && dev < kNoAllocMaxDevices, VC_ERR_UNSUPPORTED, "vc_bias_grad_noalloc: device ordinal %d >= %d",
+             dev, kNoAllocMaxDevices);
+  if (!g_bias_scratch_ptr[dev]) {
+    double* p = nullptr;
+    VC_CUDA(cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_bias_scratch));
+    VC_REQUIRE(p != nullptr, VC_ERR_CUDA, "vc_bias_grad_noalloc: cudaGetSymbolAddress returned a null address");
+    g_bias_scratch_ptr[dev] = p;
+  }
+  *out = g_bias_scratch_ptr[dev];
+  return VC_OK;
+}
+
+extern "C" int vc_bias_grad_noalloc_max_channels(void) { return kNoAllocMaxC; }
+
+extern "C" int vc_bias_grad_noalloc(const float* dy, int64_t outer, int C, int64_t inner, float* db, int accumulate,
+                                    void* stream) {
+  VC_REQUIRE(dy && db && outer > 0 && C > 0 && inner > 0, VC_ERR_BAD_ARG, "vc_bias_grad_noalloc: bad arguments");
+  VC_REQUIRE(C <= kNoAllocMaxC, VC_ERR_UNSUPPORTED,
+             "vc_bias_grad_noalloc: C = %d exceeds the built-in scratch (at most %d channels); use vc_bias_grad with a "
+             "caller workspace", C, kNoAllocMaxC);
+  double* part = nullptr;
+  const int rc = bias_scratch_address(&part);
+  if (rc != VC_OK) return rc;
+  int S = kBiasSplits;   // same split rules as vc_bias_grad: S <= kBiasSplits or C * S <= 1024 <= the array
+  if (inner == 1) {
+    while (S > 1 && (S > outer || (int64_t)C * S > 262144)) S >>= 1;
+    bias_grad_cols_stage1<<<dim3((C + 127) / 128, S), 128, 0, as_stream(stream)>>>(dy, outer, C, S, part);
+  } else {
+    while ((int64_t)C * S < 512) S <<= 1;
+    while (S > 1 && outer * inner / S < 1024) S >>= 1;
+    bias_grad_stage1<<<dim3(C, S), 256, 0, as_stream(stream)>>>(dy, outer, C, inner, S, part);
+  }
+  VC_LAUNCH_CHECK();
+  launch_bias_stage2(part, C, S, db, accumulate, as_stream(stream));
+  VC_LAUNCH_CHECK();
+  return VC_OK;
+}
+
 extern "C" int vc_cat_gate_fwd(const float* a, int na, const float* l, int nl, const float* gate, int append_gate,
                                int B, float* out, void* stream) {
   VC_REQUIRE(out && B > 0 && na >= 0 && nl >= 0 && (na == 0 || a) && (nl == 0 || l), VC_ERR_BAD_ARG,
