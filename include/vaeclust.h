@@ -116,6 +116,37 @@ int vc_convT2d_s2k4_dgrad(const float* dy, const float* W, float* dx, int B, int
 int vc_convT2d_s2k4_wgrad(const float* dy, const float* x, float* dW, int B, int Cin, int H, int Wd, int Cout,
                           void* workspace, size_t workspace_bytes, void* stream);
 
+/* Small kernels around the bf16-NHWC convolution path (csrc/nhwc_misc.cu).
+ *  vc_nhwc_conv1_fwd    : nn.Conv2d(1, Cout, 3, 2, 1) (+ReLU) of 12:87 with y written as bf16 NHWC [B,H/2,W/2,Cout].
+ *  vc_nhwc_convT1_dgrad : data gradient of nn.ConvTranspose2d(Cin, 1, 4, 2, 1) (12:137) with the ReLU mask of its input
+ *                         activation act_nhwc (bf16 [B,H,W,Cin], may be NULL) applied; g written as bf16 NHWC.
+ *  vc_nhwc_from_nchw    : fp32 [B,C,H,W] -> bf16 [B,H,W,C]  (the decoder's Linear output reshaped, 12:133); W % 64 == 0.
+ *  vc_nhwc_bias_grad    : db[c] = sum over rows of a bf16 [rows, C] matrix (bias gradient of a conv layer whose output
+ *                         gradient lives in NHWC), fixed summation order. */
+int vc_nhwc_conv1_fwd(const float* x, const float* W, const float* bias, int relu, void* y_nhwc, int B, int H, int Wd,
+                      int Cout, void* stream);
+int vc_nhwc_convT1_dgrad(const float* dy, const float* W, const void* act_nhwc, void* g_nhwc, int B, int Cin, int H,
+                         int Wd, void* stream);
+int vc_nhwc_from_nchw(const float* src, void* dst_nhwc, int B, int C, int H, int Wd, void* stream);
+size_t vc_nhwc_bias_grad_workspace_bytes(int C);
+int vc_nhwc_bias_grad(const void* g_nhwc, int64_t rows, int C, float* db, void* workspace, size_t workspace_bytes,
+                      void* stream);
+/* TMA-fed implicit-GEMM convolutions on bf16 NHWC activations (csrc/conv_nhwc.cu): the hidden conv layers of script 12
+ * (nn.Conv2d(k3,s2,p1) 12:87-89 and nn.ConvTranspose2d(k4,s2,p1) 12:135-137), forward and data gradient, with the
+ * elementwise neighbours fused into the epilogue.  op = VC_OP_CONV_FWD / CONVT_FWD / CONV_DGRAD / CONVT_DGRAD;
+ * (B, Cin, H, W, Cout) is the LAYER's forward geometry (x is [B,Cin,H,W]) as in vc_dense_op.
+ *   src_nhwc : bf16 [B][h][w][C] -- the layer input (forward) or the masked output gradient (data gradient)
+ *   Wt       : fp32 weights in the reference's state_dict layout ([Cout,Cin,3,3] / [Cin,Cout,4,4])
+ *   bias, relu : forward epilogue (bias may be NULL)
+ *   mask_nhwc  : bf16 NHWC tensor of the OUTPUT's shape or NULL; out = acc * (mask > 0)  (ReLU backward of the layer below)
+ *   out_nhwc / out_nchw : bf16 NHWC and / or fp32 NCHW result (either may be NULL, not both)
+ * Supported: H, W even, output row width W/2 (conv) or W (convT) a multiple of 128, source channels 32 (Conv forward,
+ * ConvT data gradient) or a multiple of 64, at most 256 GEMM columns (Cout, 4*Cout, 4*Cin, Cin respectively). */
+int vc_conv_nhwc_supported(int op, int B, int Cin, int H, int W, int Cout);
+size_t vc_conv_nhwc_workspace_bytes(int op, int B, int Cin, int H, int W, int Cout);
+int vc_conv_nhwc(int op, const void* src_nhwc, const float* Wt, const float* bias, int relu, const void* mask_nhwc,
+                 void* out_nhwc, float* out_nchw, int B, int Cin, int H, int W, int Cout, void* workspace,
+                 size_t workspace_bytes, void* stream);
 /* TMA-fed data gradients (bf16 tensor-core mode): the masked gradient g = dy * (y > 0) of a ReLU(conv) / ReLU(convT)
  * layer of 12:87-89,135-137 is produced ONCE, by the pass that also yields the bias gradient, as fp32 NCHW (for the
  * weight-gradient kernel) and as a bf16 NHWC copy; the data-gradient implicit GEMM then fetches its A tiles from

@@ -49,7 +49,10 @@ def launches(path, out, header):
         if r["Metric Name"] != "gpu__time_duration.sum":
             continue
         k = short(r["Kernel Name"])
-        tot[k] += to_float(r["Metric Value"]) * scale(r["Metric Unit"], "time")
+        val = to_float(r["Metric Value"])
+        if val != val:      # ncu writes nan for a launch it could not measure (the process was ending)
+            continue
+        tot[k] += val * scale(r["Metric Unit"], "time")
         cnt[k] += 1
     total = sum(tot.values())
     with open(out, "w") as f:

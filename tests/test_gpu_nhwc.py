@@ -1,0 +1,135 @@
+"""TMA-fed bf16-NHWC convolution kernels (csrc/conv_nhwc.cu and friends) against torch fp32 on bf16-rounded operands.
+
+The kernels multiply bf16 operands exactly and accumulate in fp32, so against an fp32 torch convolution of the ROUNDED
+inputs the only differences are summation order (1e-5 level) and, for bf16 outputs, the final rounding (2^-9 relative).
+"""
+import sys
+from pathlib import Path
+
+import pytest
+import torch
+import torch.nn.functional as F
+
+ROOT = Path(__file__).resolve().parents[1]
+sys.path[:0] = [str(ROOT / "vae-for-hybrid-music-clustering_b200")]
+
+pytestmark = pytest.mark.gpu
+
+OPS = {"conv_fwd": 3, "conv_dgrad": 4, "convT_fwd": 6, "convT_dgrad": 7}
+
+
+def _r(*shape, seed, scale=1.0):
+    g = torch.Generator(device="cuda").manual_seed(seed)
+    return torch.randn(*shape, device="cuda", generator=g) * scale
+
+
+def _bf(t):
+    return t.to(torch.bfloat16).float()
+
+
+def _nhwc(t):
+    return t.permute(0, 2, 3, 1).contiguous().to(torch.bfloat16)
+
+
+def _run(op, src_nchw, w, bias, relu, mask_nchw, dims, want_nhwc=True, want_nchw=True):
+    from vaeclust._lib import lib, ptr, stream_ptr
+    L = lib()
+    B, Cin, H, W, Cout = dims
+    assert L.size("vc_conv_nhwc_supported", op, B, Cin, H, W, Cout) == 1
+    if op == OPS["conv_fwd"]:
+        oshape = (B, Cout, H // 2, W // 2)
+    elif op == OPS["convT_fwd"]:
+        oshape = (B, Cout, 2 * H, 2 * W)
+    else:
+        oshape = (B, Cin, H, W)
+    src = _nhwc(src_nchw)
+    mask = _nhwc(mask_nchw) if mask_nchw is not None else None
+    o_nhwc = torch.full((oshape[0], oshape[2], oshape[3], oshape[1]), float("nan"), dtype=torch.bfloat16, device="cuda") \
+        if want_nhwc else None
+    o_nchw = torch.full(oshape, float("nan"), device="cuda") if want_nchw else None
+    ws = torch.empty(L.size("vc_conv_nhwc_workspace_bytes", op, B, Cin, H, W, Cout), dtype=torch.uint8, device="cuda")
+    L.call("vc_conv_nhwc", op, ptr(src), ptr(w), ptr(bias), int(relu), ptr(mask), ptr(o_nhwc), ptr(o_nchw), B, Cin, H, W,
+           Cout, ptr(ws), ws.numel(), stream_ptr())
+    torch.cuda.synchronize()
+    return o_nhwc, o_nchw
+
+
+def _check(o_nhwc, o_nchw, want):
+    scale = float(want.abs().max())
+    if o_nchw is not None:
+        torch.testing.assert_close(o_nchw, want, rtol=2e-5, atol=2e-5 * scale)
+    if o_nhwc is not None:
+        got = o_nhwc.float().permute(0, 3, 1, 2)
+        torch.testing.assert_close(got, want, rtol=2 ** -8, atol=2 ** -8 * scale * 0.05 + 1e-6)
+
+
+@pytest.mark.parametrize("B,Cin,H,W,Cout", [(2, 32, 8, 512, 64),      # conv.2 of script 12: 32-channel source, pair view
+                                            (3, 64, 6, 256, 128),     # conv.4: one 64-channel chunk per tap
+                                            (1, 128, 4, 256, 64)])    # two chunks per tap
+def test_conv_forward(B, Cin, H, W, Cout):
+    x, w, b = _r(B, Cin, H, W, seed=1), _r(Cout, Cin, 3, 3, seed=2, scale=(Cin * 9) ** -0.5), _r(Cout, seed=3)
+    want = F.relu(F.conv2d(_bf(x), _bf(w), b, stride=2, padding=1))
+    _check(*_run(OPS["conv_fwd"], x, w, b, True, None, (B, Cin, H, W, Cout)), want)
+    want = F.conv2d(_bf(x), _bf(w), None, stride=2, padding=1)
+    _check(*_run(OPS["conv_fwd"], x, w, None, False, None, (B, Cin, H, W, Cout), want_nhwc=False), want)
+
+
+@pytest.mark.parametrize("B,Cin,H,W,Cout", [(2, 128, 4, 128, 64),     # deconv.0: slab streams (N = 256, 18 k-blocks)
+                                            (2, 64, 5, 256, 32)])     # deconv.2: resident slab, N = 128
+def test_convT_forward(B, Cin, H, W, Cout):
+    x, w, b = _r(B, Cin, H, W, seed=1), _r(Cin, Cout, 4, 4, seed=2, scale=(Cin * 4) ** -0.5), _r(Cout, seed=3)
+    want = F.relu(F.conv_transpose2d(_bf(x), _bf(w), b, stride=2, padding=1))
+    _check(*_run(OPS["convT_fwd"], x, w, b, True, None, (B, Cin, H, W, Cout)), want)
+
+
+@pytest.mark.parametrize("B,Cin,H,W,Cout", [(2, 32, 8, 512, 64), (3, 64, 6, 256, 128)])
+def test_conv_data_gradient_with_mask(B, Cin, H, W, Cout):
+    g, w = _r(B, Cout, H // 2, W // 2, seed=4), _r(Cout, Cin, 3, 3, seed=2, scale=(Cin * 9) ** -0.5)
+    yprev = _r(B, Cin, H, W, seed=5)
+    dx = torch.nn.grad.conv2d_input((B, Cin, H, W), _bf(w), _bf(g), stride=2, padding=1)
+    want = dx * (_bf(yprev) > 0)
+    _check(*_run(OPS["conv_dgrad"], g, w, None, False, yprev, (B, Cin, H, W, Cout)), want)
+    _check(*_run(OPS["conv_dgrad"], g, w, None, False, None, (B, Cin, H, W, Cout), want_nhwc=False), dx)
+
+
+@pytest.mark.parametrize("B,Cin,H,W,Cout", [(2, 128, 4, 128, 64), (2, 64, 5, 256, 32), (1, 64, 3, 128, 32)])
+def test_convT_data_gradient_with_mask(B, Cin, H, W, Cout):
+    g, w = _r(B, Cout, 2 * H, 2 * W, seed=4), _r(Cin, Cout, 4, 4, seed=2, scale=(Cin * 4) ** -0.5)
+    yprev = _r(B, Cin, H, W, seed=5)
+    dx = F.conv2d(_bf(g), _bf(w), None, stride=2, padding=1)      # the data gradient of a transposed conv is a conv
+    want = dx * (_bf(yprev) > 0)
+    _check(*_run(OPS["convT_dgrad"], g, w, None, False, yprev, (B, Cin, H, W, Cout)), want)
+    _check(*_run(OPS["convT_dgrad"], g, w, None, False, None, (B, Cin, H, W, Cout), want_nhwc=False), dx)
+
+
+def test_single_channel_ends_and_helpers():
+    from vaeclust._lib import lib, ptr, stream_ptr
+    L = lib()
+    B, H, W, C = 2, 16, 256, 32
+    # Conv2d(1 -> 32) forward into NHWC
+    x, w, b = _r(B, 1, H, W, seed=1), _r(C, 1, 3, 3, seed=2, scale=1 / 3), _r(C, seed=3)
+    y = torch.empty(B, H // 2, W // 2, C, dtype=torch.bfloat16, device="cuda")
+    L.call("vc_nhwc_conv1_fwd", ptr(x), ptr(w), ptr(b), 1, ptr(y), B, H, W, C, stream_ptr())
+    want = F.relu(F.conv2d(_bf(x), _bf(w), b, stride=2, padding=1))
+    _check(y, None, want)
+    # ConvTranspose2d(32 -> 1) data gradient + mask into NHWC
+    dy, wt, act = _r(B, 1, 2 * H, 2 * W, seed=4), _r(C, 1, 4, 4, seed=5, scale=0.25), _r(B, C, H, W, seed=6)
+    g = torch.empty(B, H, W, C, dtype=torch.bfloat16, device="cuda")
+    an = _nhwc(act)
+    L.call("vc_nhwc_convT1_dgrad", ptr(dy), ptr(wt), ptr(an), ptr(g), B, C, H, W, stream_ptr())
+    want = F.conv2d(_bf(dy), _bf(wt), None, stride=2, padding=1) * (_bf(act) > 0)
+    _check(g, None, want)
+    # layout conversion
+    src = _r(B, 128, 4, 128, seed=7)
+    dst = torch.empty(B, 4, 128, 128, dtype=torch.bfloat16, device="cuda")
+    L.call("vc_nhwc_from_nchw", ptr(src), ptr(dst), B, 128, 4, 128, stream_ptr())
+    torch.cuda.synchronize()
+    assert torch.equal(dst, _nhwc(src))
+    # bias gradient of an NHWC tensor
+    for Cc, rows in ((32, 70001), (64, 4099), (128, 513)):
+        gm = _r(rows, Cc, seed=8).to(torch.bfloat16)
+        db = torch.empty(Cc, device="cuda")
+        ws = torch.empty(L.size("vc_nhwc_bias_grad_workspace_bytes", Cc), dtype=torch.uint8, device="cuda")
+        L.call("vc_nhwc_bias_grad", ptr(gm), rows, Cc, ptr(db), ptr(ws), ws.numel(), stream_ptr())
+        wantb = gm.double().sum(0).float()
+        torch.testing.assert_close(db, wantb, rtol=1e-5, atol=1e-5 * float(wantb.abs().max()) + 1e-4)

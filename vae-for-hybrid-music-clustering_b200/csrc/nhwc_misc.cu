@@ -1,0 +1,282 @@
+// The small kernels around the TMA-fed bf16-NHWC convolution path of script 12 (conv_nhwc.cu, conv_nhwc_wgrad.cu):
+//   * Conv2d(1 -> C, k3 s2 p1) forward (12:87) writing bf16 NHWC directly (thread = output pixel: its C channels are one
+//     contiguous run of the NHWC tensor),
+//   * ConvTranspose2d(C -> 1, k4 s2 p1) data gradient (12:137) with the ReLU mask of the layer below applied and the result
+//     written as bf16 NHWC (what used to be a gather kernel + a 12 B/element ReLU-backward pass),
+//   * fp32 NCHW -> bf16 NHWC conversion (the decoder's fully connected output, 12:129-133),
+//   * per-channel sums of a bf16 NHWC tensor (bias gradients, fixed summation order).
+// All HBM-bound streaming kernels; operands are rounded to bf16 exactly as the tensor-core kernels do.
+#include "common.cuh"
+
+namespace vc {
+
+__device__ __forceinline__ float nm_rb(float v) { return __bfloat162float(__float2bfloat16_rn(v)); }
+__device__ __forceinline__ uint32_t nm_pack(float a, float b) {
+  __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
+  return *reinterpret_cast<uint32_t*>(&h);
+}
+__device__ __forceinline__ float nm_ldg_pred(const float* p, uint32_t pred) {
+  float v;
+  asm("{\n\t.reg .pred q;\n\tsetp.ne.b32 q, %2, 0;\n\tmov.f32 %0, 0f00000000;\n\t@q ld.global.nc.f32 %0, [%1];\n\t}"
+      : "=f"(v)
+      : "l"(p), "r"(pred));
+  return v;
+}
+
+// ---- Conv2d(1 -> Cout) forward, y as bf16 NHWC [B][OH][OW][Cout]; Cout % 8 == 0
+__global__ void __launch_bounds__(256)
+nm_conv1_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ bias,
+                    __nv_bfloat16* __restrict__ y, int B, int H, int W, int Cout, int OH, int OW, int relu) {
+  extern __shared__ float sm[];
+  float* wt = sm;                // [9][Cout]
+  float* bs = sm + 9 * Cout;     // [Cout]
+  for (int e = threadIdx.x; e < 9 * Cout; e += blockDim.x) {
+    const int t = e / Cout, co = e - t * Cout;
+    wt[e] = nm_rb(w[co * 9 + t]);
+  }
+  for (int e = threadIdx.x; e < Cout; e += blockDim.x) bs[e] = bias ? bias[e] : 0.f;
+  __syncthreads();
+  const int64_t total = (int64_t)B * OH * OW;
+  for (int64_t m = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; m < total; m += (int64_t)gridDim.x * blockDim.x) {
+    const int ow = (int)(m % OW);
+    const int64_t t2 = m / OW;
+    const int oh = (int)(t2 % OH), b = (int)(t2 / OH);
+    float xin[9];
+    const float* xb = x + (int64_t)b * H * W;
+#pragma unroll
+    for (int kh = 0; kh < 3; ++kh)
+#pragma unroll
+      for (int kw = 0; kw < 3; ++kw) {
+        const int ih = 2 * oh + kh - 1, iw = 2 * ow + kw - 1;
+        const uint32_t ok = ((unsigned)ih < (unsigned)H && (unsigned)iw < (unsigned)W) ? 1u : 0u;
+        xin[kh * 3 + kw] = nm_rb(nm_ldg_pred(xb + (int64_t)ih * W + iw, ok));
+      }
+    uint4* yo = reinterpret_cast<uint4*>(y + m * Cout);
+    for (int c0 = 0; c0 < Cout; c0 += 8) {
+      float acc[8];
+      const float4 b0 = *reinterpret_cast<const float4*>(bs + c0), b1 = *reinterpret_cast<const float4*>(bs + c0 + 4);
+      acc[0] = b0.x; acc[1] = b0.y; acc[2] = b0.z; acc[3] = b0.w; acc[4] = b1.x; acc[5] = b1.y; acc[6] = b1.z; acc[7] = b1.w;
+#pragma unroll
+      for (int t = 0; t < 9; ++t) {
+        const float4 w0 = *reinterpret_cast<const float4*>(wt + t * Cout + c0);
+        const float4 w1 = *reinterpret_cast<const float4*>(wt + t * Cout + c0 + 4);
+        acc[0] = fmaf(xin[t], w0.x, acc[0]); acc[1] = fmaf(xin[t], w0.y, acc[1]);
+        acc[2] = fmaf(xin[t], w0.z, acc[2]); acc[3] = fmaf(xin[t], w0.w, acc[3]);
+        acc[4] = fmaf(xin[t], w1.x, acc[4]); acc[5] = fmaf(xin[t], w1.y, acc[5]);
+        acc[6] = fmaf(xin[t], w1.z, acc[6]); acc[7] = fmaf(xin[t], w1.w, acc[7]);
+      }
+      if (relu) {
+#pragma unroll
+        for (int c = 0; c < 8; ++c) acc[c] = fmaxf(acc[c], 0.f);
+      }
+      yo[c0 >> 3] = make_uint4(nm_pack(acc[0], acc[1]), nm_pack(acc[2], acc[3]), nm_pack(acc[4], acc[5]),
+                               nm_pack(acc[6], acc[7]));
+    }
+  }
+}
+
+// ---- ConvTranspose2d(Cin -> 1) data gradient with the ReLU mask of the layer's INPUT activation (bf16 NHWC) applied:
+//   g[b,i,j,ci] = (act[b,i,j,ci] > 0) * sum_{kh,kw} dy[b,0,2i-1+kh,2j-1+kw] * W[ci,0,kh,kw]      (bf16 NHWC out)
+__global__ void __launch_bounds__(256)
+nm_convT1_dgrad_kernel(const float* __restrict__ dy, const float* __restrict__ w, const __nv_bfloat16* __restrict__ act,
+                       __nv_bfloat16* __restrict__ g, int B, int Cin, int H, int W) {
+  extern __shared__ float sm[];   // [16][Cin]: tap-major so eight channels of one tap are two LDS.128
+  for (int e = threadIdx.x; e < Cin * 16; e += blockDim.x) {
+    const int t = e / Cin, ci = e - t * Cin;
+    sm[e] = nm_rb(w[ci * 16 + t]);
+  }
+  __syncthreads();
+  const int64_t total = (int64_t)B * H * W;
+  const int OH = 2 * H, OW = 2 * W;
+  for (int64_t m = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; m < total; m += (int64_t)gridDim.x * blockDim.x) {
+    const int j = (int)(m % W);
+    const int64_t t2 = m / W;
+    const int i = (int)(t2 % H), b = (int)(t2 / H);
+    float d[16];
+    const float* db = dy + (int64_t)b * OH * OW;
+#pragma unroll
+    for (int kh = 0; kh < 4; ++kh)
+#pragma unroll
+      for (int kw = 0; kw < 4; ++kw) {
+        const int oh = 2 * i - 1 + kh, ow = 2 * j - 1 + kw;
+        const uint32_t ok = ((unsigned)oh < (unsigned)OH && (unsigned)ow < (unsigned)OW) ? 1u : 0u;
+        d[kh * 4 + kw] = nm_rb(nm_ldg_pred(db + (int64_t)oh * OW + ow, ok));
+      }
+    const uint4* a4 = reinterpret_cast<const uint4*>(act + m * Cin);
+    uint4* g4 = reinterpret_cast<uint4*>(g + m * Cin);
+    for (int c0 = 0; c0 < Cin; c0 += 8) {
+      float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+      for (int t = 0; t < 16; ++t) {
+        const float4 w0 = *reinterpret_cast<const float4*>(sm + t * Cin + c0);
+        const float4 w1 = *reinterpret_cast<const float4*>(sm + t * Cin + c0 + 4);
+        acc[0] = fmaf(d[t], w0.x, acc[0]); acc[1] = fmaf(d[t], w0.y, acc[1]);
+        acc[2] = fmaf(d[t], w0.z, acc[2]); acc[3] = fmaf(d[t], w0.w, acc[3]);
+        acc[4] = fmaf(d[t], w1.x, acc[4]); acc[5] = fmaf(d[t], w1.y, acc[5]);
+        acc[6] = fmaf(d[t], w1.z, acc[6]); acc[7] = fmaf(d[t], w1.w, acc[7]);
+      }
+      if (act) {
+        const uint4 mm = __ldg(a4 + (c0 >> 3));
+        const uint32_t mw[4] = {mm.x, mm.y, mm.z, mm.w};
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          acc[2 * u] = __uint_as_float(mw[u] << 16) > 0.f ? acc[2 * u] : 0.f;
+          acc[2 * u + 1] = __uint_as_float(mw[u] & 0xffff0000u) > 0.f ? acc[2 * u + 1] : 0.f;
+        }
+      }
+      g4[c0 >> 3] = make_uint4(nm_pack(acc[0], acc[1]), nm_pack(acc[2], acc[3]), nm_pack(acc[4], acc[5]),
+                               nm_pack(acc[6], acc[7]));
+    }
+  }
+}
+
+// ---- fp32 NCHW -> bf16 NHWC.  A block takes (b, h, 64-pixel segment) x all channels; the transposition goes through
+// shared memory (reads coalesced along W, writes are one contiguous 64 x C block of the NHWC tensor).
+constexpr int NM_PX = 64;
+__global__ void __launch_bounds__(256)
+nm_from_nchw_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst, int B, int C, int H, int W, int ntiles) {
+  extern __shared__ unsigned char nm_smem[];
+  const int pitch = C + 8;
+  __nv_bfloat16* tile = reinterpret_cast<__nv_bfloat16*>(nm_smem);      // [NM_PX][pitch]
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int segs = W / NM_PX;
+  const int64_t plane = (int64_t)H * W;
+  for (int t = blockIdx.x; t < ntiles; t += gridDim.x) {
+    const int seg = t % segs, r = t / segs;
+    const int h = r % H, b = r / H;
+    const int64_t base = ((int64_t)b * C) * plane + (int64_t)h * W + seg * NM_PX;
+    for (int c = warp; c < C; c += 8) {
+      const float2 v = *reinterpret_cast<const float2*>(src + base + (int64_t)c * plane + 2 * lane);
+      tile[(2 * lane) * pitch + c] = __float2bfloat16_rn(v.x);
+      tile[(2 * lane + 1) * pitch + c] = __float2bfloat16_rn(v.y);
+    }
+    __syncthreads();
+    __nv_bfloat16* o = dst + (((int64_t)b * H + h) * W + seg * NM_PX) * C;
+    const int vec_per_px = C / 8;
+    for (int e = threadIdx.x; e < NM_PX * vec_per_px; e += blockDim.x) {
+      const int px = e / vec_per_px, q = e - px * vec_per_px;
+      reinterpret_cast<uint4*>(o)[e] = *reinterpret_cast<const uint4*>(tile + px * pitch + q * 8);
+    }
+    __syncthreads();
+  }
+}
+
+// ---- per-channel sums of a bf16 [rows][C] matrix (C % 8 == 0, C <= 2048): thread = eight channels of a row; the
+// block's row groups meet in shared memory in a fixed order, block partials (double) are folded by nm_colsum_fold_kernel
+__global__ void __launch_bounds__(256)
+nm_colsum_kernel(const __nv_bfloat16* __restrict__ g, int64_t rows, int C, double* __restrict__ part) {
+  extern __shared__ float nm_red[];          // [groups][C]
+  const int vecs = C >> 3;                   // threads per row
+  const int groups = 256 / vecs;             // rows per pass of the block
+  const int grp = threadIdx.x / vecs, q = threadIdx.x - grp * vecs;
+  float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+  if (grp < groups) {
+    for (int64_t r = (int64_t)blockIdx.x * groups + grp; r < rows; r += (int64_t)gridDim.x * groups) {
+      const uint4 v = __ldcs(reinterpret_cast<const uint4*>(g + r * C) + q);
+      const uint32_t u[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        acc[2 * k] += __uint_as_float(u[k] << 16);
+        acc[2 * k + 1] += __uint_as_float(u[k] & 0xffff0000u);
+      }
+    }
+#pragma unroll
+    for (int k = 0; k < 8; ++k) nm_red[grp * C + q * 8 + k] = acc[k];
+  }
+  __syncthreads();
+  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    double s = 0.0;
+    for (int gi = 0; gi < groups; ++gi) s += (double)nm_red[gi * C + c];
+    part[(int64_t)blockIdx.x * C + c] = s;
+  }
+}
+
+// db[c] = sum over blocks, eight warps per 32 channels, sub-sums added in warp order
+__global__ void __launch_bounds__(256)
+nm_colsum_fold_kernel(const double* __restrict__ part, int nblk, int C, float* __restrict__ db) {
+  __shared__ double sub[8][32];
+  const int lane = threadIdx.x & 31, gw = threadIdx.x >> 5;
+  const int c = blockIdx.x * 32 + lane;
+  double v = 0.0;
+  if (c < C)
+    for (int b = gw; b < nblk; b += 8) v += part[(int64_t)b * C + c];
+  sub[gw][lane] = v;
+  __syncthreads();
+  if (gw != 0 || c >= C) return;
+#pragma unroll
+  for (int i = 1; i < 8; ++i) v += sub[i][lane];
+  db[c] = (float)v;
+}
+
+static int nm_grid(int64_t total) {
+  int64_t blocks = (total + 255) / 256;
+  const int64_t cap = (int64_t)sm_count() * 8;
+  return (int)(blocks > cap ? cap : blocks);
+}
+constexpr int kColsumBlocks = 148 * 4;
+
+}  // namespace vc
+
+using namespace vc;
+
+extern "C" int vc_nhwc_conv1_fwd(const float* x, const float* Wt, const float* bias, int relu, void* y_nhwc, int B, int H,
+                                 int W, int Cout, void* stream) {
+  VC_REQUIRE(x && Wt && y_nhwc && B > 0 && H > 0 && W > 0, VC_ERR_BAD_ARG, "vc_nhwc_conv1_fwd: bad arguments");
+  VC_REQUIRE(Cout % 8 == 0 && Cout > 0 && Cout <= 256, VC_ERR_UNSUPPORTED, "vc_nhwc_conv1_fwd: Cout must be a multiple of 8, <= 256");
+  VC_REQUIRE((reinterpret_cast<uintptr_t>(y_nhwc) & 15) == 0, VC_ERR_BAD_ARG, "vc_nhwc_conv1_fwd: y must be 16-byte aligned");
+  const int OH = (H - 1) / 2 + 1, OW = (W - 1) / 2 + 1;
+  nm_conv1_fwd_kernel<<<nm_grid((int64_t)B * OH * OW), 256, (size_t)10 * Cout * sizeof(float), as_stream(stream)>>>(
+      x, Wt, bias, static_cast<__nv_bfloat16*>(y_nhwc), B, H, W, Cout, OH, OW, relu);
+  VC_LAUNCH_CHECK();
+  return VC_OK;
+}
+
+extern "C" int vc_nhwc_convT1_dgrad(const float* dy, const float* Wt, const void* act_nhwc, void* g_nhwc, int B, int Cin,
+                                    int H, int W, void* stream) {
+  VC_REQUIRE(dy && Wt && g_nhwc && B > 0 && H > 0 && W > 0, VC_ERR_BAD_ARG, "vc_nhwc_convT1_dgrad: bad arguments");
+  VC_REQUIRE(Cin % 8 == 0 && Cin > 0 && Cin <= 512, VC_ERR_UNSUPPORTED, "vc_nhwc_convT1_dgrad: Cin must be a multiple of 8, <= 512");
+  VC_REQUIRE(((reinterpret_cast<uintptr_t>(g_nhwc) | reinterpret_cast<uintptr_t>(act_nhwc)) & 15) == 0, VC_ERR_BAD_ARG,
+             "vc_nhwc_convT1_dgrad: NHWC tensors must be 16-byte aligned");
+  nm_convT1_dgrad_kernel<<<nm_grid((int64_t)B * H * W), 256, (size_t)16 * Cin * sizeof(float), as_stream(stream)>>>(
+      dy, Wt, static_cast<const __nv_bfloat16*>(act_nhwc), static_cast<__nv_bfloat16*>(g_nhwc), B, Cin, H, W);
+  VC_LAUNCH_CHECK();
+  return VC_OK;
+}
+
+extern "C" int vc_nhwc_from_nchw(const float* src, void* dst_nhwc, int B, int C, int H, int W, void* stream) {
+  VC_REQUIRE(src && dst_nhwc && B > 0 && H > 0, VC_ERR_BAD_ARG, "vc_nhwc_from_nchw: bad arguments");
+  VC_REQUIRE(C % 8 == 0 && C > 0 && C <= 512 && W % NM_PX == 0, VC_ERR_UNSUPPORTED,
+             "vc_nhwc_from_nchw: need C %% 8 == 0, C <= 512, W %% 64 == 0 (got C=%d W=%d)", C, W);
+  VC_REQUIRE((reinterpret_cast<uintptr_t>(src) & 7) == 0 && (reinterpret_cast<uintptr_t>(dst_nhwc) & 15) == 0, VC_ERR_BAD_ARG,
+             "vc_nhwc_from_nchw: misaligned pointers");
+  const int64_t ntiles = (int64_t)B * H * (W / NM_PX);
+  VC_REQUIRE(ntiles < 2147483647LL, VC_ERR_UNSUPPORTED, "vc_nhwc_from_nchw: tensor too large");
+  int grid = 4 * sm_count();
+  if (grid > ntiles) grid = (int)ntiles;
+  nm_from_nchw_kernel<<<grid, 256, (size_t)NM_PX * (C + 8) * 2, as_stream(stream)>>>(
+      src, static_cast<__nv_bfloat16*>(dst_nhwc), B, C, H, W, (int)ntiles);
+  VC_LAUNCH_CHECK();
+  return VC_OK;
+}
+
+extern "C" size_t vc_nhwc_bias_grad_workspace_bytes(int C) { return (size_t)kColsumBlocks * (C > 0 ? C : 1) * 8; }
+
+extern "C" int vc_nhwc_bias_grad(const void* g_nhwc, int64_t rows, int C, float* db, void* workspace, size_t workspace_bytes,
+                                 void* stream) {
+  VC_REQUIRE(g_nhwc && db && rows > 0, VC_ERR_BAD_ARG, "vc_nhwc_bias_grad: bad arguments");
+  VC_REQUIRE(C % 8 == 0 && C > 0 && C <= 2048, VC_ERR_UNSUPPORTED, "vc_nhwc_bias_grad: C must be a multiple of 8, <= 2048");
+  VC_REQUIRE(workspace && workspace_bytes >= vc_nhwc_bias_grad_workspace_bytes(C), VC_ERR_WORKSPACE,
+             "vc_nhwc_bias_grad: workspace too small");
+  VC_REQUIRE((reinterpret_cast<uintptr_t>(g_nhwc) & 15) == 0, VC_ERR_BAD_ARG, "vc_nhwc_bias_grad: g must be 16-byte aligned");
+  const int groups = 256 / (C >> 3);
+  VC_REQUIRE(groups >= 1, VC_ERR_UNSUPPORTED, "vc_nhwc_bias_grad: C too large");
+  int grid = kColsumBlocks;
+  if ((int64_t)grid * groups > rows) grid = (int)((rows + groups - 1) / groups);
+  double* part = static_cast<double*>(workspace);
+  nm_colsum_kernel<<<grid, 256, (size_t)groups * C * sizeof(float), as_stream(stream)>>>(
+      static_cast<const __nv_bfloat16*>(g_nhwc), rows, C, part);
+  VC_LAUNCH_CHECK();
+  nm_colsum_fold_kernel<<<(C + 31) / 32, 256, 0, as_stream(stream)>>>(part, grid, C, db);
+  VC_LAUNCH_CHECK();
+  return VC_OK;
+}
