@@ -116,6 +116,15 @@ int vc_convT2d_s2k4_dgrad(const float* dy, const float* W, float* dx, int B, int
 int vc_convT2d_s2k4_wgrad(const float* dy, const float* x, float* dW, int B, int Cin, int H, int Wd, int Cout,
                           void* workspace, size_t workspace_bytes, void* stream);
 
+/* TMA-fed weight gradients of the same layers (csrc/conv_nhwc_wgrad.cu; autograd of nn.Conv2d / nn.ConvTranspose2d at
+ * 12:87-89,135-137).  op = VC_OP_CONV_WGRAD or VC_OP_CONVT_WGRAD, (B, Cin, H, W, Cout) the layer's forward geometry;
+ * g_nhwc = bf16 NHWC gradient of the layer's output (ReLU mask already applied), x_nhwc = bf16 NHWC layer input; dW in the
+ * state_dict layout.  Supported: the channel count on the coarse side (Cout for Conv, Cin for ConvT) 64 or 128, on the
+ * sampled side 32 or 64, coarse row width a multiple of 64.  Deterministic (fixed-order split-K fold). */
+int vc_conv_nhwc_wgrad_supported(int op, int B, int Cin, int H, int W, int Cout);
+size_t vc_conv_nhwc_wgrad_workspace_bytes(int op, int B, int Cin, int H, int W, int Cout);
+int vc_conv_nhwc_wgrad(int op, const void* g_nhwc, const void* x_nhwc, float* dW, int B, int Cin, int H, int Wd, int Cout,
+                       void* workspace, size_t workspace_bytes, void* stream);
 /* Small kernels around the bf16-NHWC convolution path (csrc/nhwc_misc.cu).
  *  vc_nhwc_conv1_fwd    : nn.Conv2d(1, Cout, 3, 2, 1) (+ReLU) of 12:87 with y written as bf16 NHWC [B,H/2,W/2,Cout].
  *  vc_nhwc_convT1_dgrad : data gradient of nn.ConvTranspose2d(Cin, 1, 4, 2, 1) (12:137) with the ReLU mask of its input

@@ -133,3 +133,75 @@ def test_single_channel_ends_and_helpers():
         L.call("vc_nhwc_bias_grad", ptr(gm), rows, Cc, ptr(db), ptr(ws), ws.numel(), stream_ptr())
         wantb = gm.double().sum(0).float()
         torch.testing.assert_close(db, wantb, rtol=1e-5, atol=1e-5 * float(wantb.abs().max()) + 1e-4)
+
+
+@pytest.mark.parametrize("kind,B,Cin,H,W,Cout", [
+    ("conv", 2, 32, 8, 256, 64),      # conv.2: Q = 32-channel input through the pair view, 6 boxes, one CTA group
+    ("conv", 3, 64, 6, 128, 128),     # conv.4: P = 128 channels (two boxes), tap rows split over three CTA groups
+    ("convT", 2, 128, 4, 64, 64),     # deconv.0: 16 taps x 64 = 1024 columns -> two groups of 512
+    ("convT", 2, 64, 5, 128, 32),     # deconv.2: Q = 32-channel gradient, pair view, 12 boxes -> two groups
+    ("convT", 1, 64, 3, 192, 32),
+])
+def test_weight_gradients(kind, B, Cin, H, W, Cout):
+    from vaeclust._lib import lib, ptr, stream_ptr
+    L = lib()
+    x = _r(B, Cin, H, W, seed=1)
+    if kind == "conv":
+        op, w = 5, _r(Cout, Cin, 3, 3, seed=2)
+        g = _r(B, Cout, H // 2, W // 2, seed=3)
+        wr = w.clone().requires_grad_(True)
+        F.conv2d(_bf(x), wr, None, stride=2, padding=1).backward(_bf(g))
+    else:
+        op, w = 8, _r(Cin, Cout, 4, 4, seed=2)
+        g = _r(B, Cout, 2 * H, 2 * W, seed=3)
+        wr = w.clone().requires_grad_(True)
+        F.conv_transpose2d(_bf(x), wr, None, stride=2, padding=1).backward(_bf(g))
+    want = wr.grad
+    assert L.size("vc_conv_nhwc_wgrad_supported", op, B, Cin, H, W, Cout) == 1
+    ws = torch.empty(L.size("vc_conv_nhwc_wgrad_workspace_bytes", op, B, Cin, H, W, Cout), dtype=torch.uint8, device="cuda")
+    gn, xn = _nhwc(g), _nhwc(x)      # named: a temporary would be freed (and its block reused) before the launch runs
+    for _ in range(2):        # twice: the result must not depend on what the workspace held
+        dw = torch.full_like(w, float("nan"))
+        L.call("vc_conv_nhwc_wgrad", op, ptr(gn), ptr(xn), ptr(dw), B, Cin, H, W, Cout, ptr(ws), ws.numel(),
+               stream_ptr())
+        torch.cuda.synchronize()
+        torch.testing.assert_close(dw, want, rtol=2e-5, atol=2e-5 * float(want.abs().max()))
+        ws.fill_(255)
+
+
+def test_conv_stacks_match_the_per_layer_path():
+    """The NHWC conv stacks (vaeclust.convstack) inside the script-12 model against the per-layer fp32-NCHW path: the same
+    bf16 products and fp32 accumulation, so loss and gradients agree to summation order; only the hidden-layer bias
+    gradients differ by the bf16 rounding of the gradients they sum."""
+    from vaeclust import convstack, nn, ops
+    ops.set_precision("bf16")
+    try:
+        torch.manual_seed(0)
+        model = nn.ConvMultiModalVAE(1, (16, 1024), 32, 384).cuda()
+        B = 2
+        x, lyr = _r(B, 1, 16, 1024, seed=1), _r(B, 384, seed=2)
+        m = torch.tensor([[1.0], [0.0]], device="cuda")
+        eps = _r(B, 32, seed=3)
+        out = {}
+        for flag in (False, True):
+            convstack.ENABLED = flag
+            used = []
+            real = convstack.encoder_convs
+            model.zero_grad()
+            mu, lv = model.encode(x, lyr, m)
+            z, klr = ops.reparam_kl(mu, lv, eps)
+            xhat = model.audio_dec(z)
+            loss = ((xhat - x) ** 2).mean() + 1e-3 * klr.mean()
+            loss.backward()
+            out[flag] = (loss.detach().clone(), xhat.detach().clone(),
+                         {k: p.grad.detach().clone() for k, p in model.named_parameters() if p.grad is not None})
+        assert convstack.encoder_supported(x, [model.audio_enc.conv[i] for i in (0, 2, 4)])
+        torch.testing.assert_close(out[True][0], out[False][0], rtol=1e-5, atol=0)
+        torch.testing.assert_close(out[True][1], out[False][1], rtol=1e-4, atol=1e-5)
+        assert out[True][2].keys() == out[False][2].keys()
+        for k, g in out[False][2].items():
+            rel = float((out[True][2][k] - g).norm() / (g.norm() + 1e-30))
+            assert rel < (2e-2 if k.endswith("bias") else 2e-3), (k, rel)
+    finally:
+        convstack.ENABLED = True
+        ops.set_precision("fp32")

@@ -1,0 +1,215 @@
+"""The conv stacks of script 12 (12:87-89 encoder, 12:135-137 decoder) with bf16 NHWC activations between the layers.
+
+In bf16 mode the per-layer autograd Functions of `ops` exchange fp32 NCHW tensors: every hidden activation is written and
+re-read as fp32, the ReLU backward / bias gradient is a separate 12 B/element pass, and the implicit-GEMM kernels gather
+and convert their operands with eight producer warps.  Here a whole stack is ONE autograd Function: hidden activations and
+their gradients exist only as bf16 NHWC, every hidden-layer operator (forward, data gradient, weight gradient) is fed by
+TMA (csrc/conv_nhwc.cu, csrc/conv_nhwc_wgrad.cu), bias + ReLU and the ReLU masks are fused into the producing epilogues.
+The single-channel ends and the fully connected neighbours keep their fp32 NCHW interfaces, so the Functions drop into
+`AudioEncoder.features` / `AudioDecoder.forward` without changing anything around them.  Arithmetic is the same as the
+per-layer path (bf16 operands, fp32 accumulation); the only new rounding is that the bias gradients of the hidden layers
+sum bf16-rounded gradients.
+"""
+from __future__ import annotations
+
+import torch
+
+from . import ops
+from ._lib import lib, ptr, stream_ptr
+
+ENABLED = True      # bf16 mode only; `supported()` decides per shape, anything else takes the per-layer path
+
+CONV_FWD, CONV_DGRAD, CONV_WGRAD, CONVT_FWD, CONVT_DGRAD, CONVT_WGRAD = 3, 4, 5, 6, 7, 8
+_BF = torch.bfloat16
+
+
+def _conv(op, src, w, bias, relu, mask, out_nhwc, out_nchw, dims):
+    B, Cin, H, W, Cout = dims
+    L = lib()
+    ws = ops._workspace(L.size("vc_conv_nhwc_workspace_bytes", op, B, Cin, H, W, Cout), src.device)
+    L.call("vc_conv_nhwc", op, ptr(src), ptr(w), ptr(bias), int(relu), ptr(mask), ptr(out_nhwc), ptr(out_nchw), B, Cin, H, W,
+           Cout, ptr(ws), ws.numel(), stream_ptr())
+
+
+def _wgrad(op, g, x, w, dims):
+    B, Cin, H, W, Cout = dims
+    L = lib()
+    dw = torch.empty_like(w)
+    ws = ops._workspace(L.size("vc_conv_nhwc_wgrad_workspace_bytes", op, B, Cin, H, W, Cout), g.device)
+    L.call("vc_conv_nhwc_wgrad", op, ptr(g), ptr(x), ptr(dw), B, Cin, H, W, Cout, ptr(ws), ws.numel(), stream_ptr())
+    return dw
+
+
+def _bias_nhwc(g):
+    C = g.shape[-1]
+    L = lib()
+    db = torch.empty(C, dtype=torch.float32, device=g.device)
+    ws = ops._workspace(L.size("vc_nhwc_bias_grad_workspace_bytes", C), g.device)
+    L.call("vc_nhwc_bias_grad", ptr(g), g.numel() // C, C, ptr(db), ptr(ws), ws.numel(), stream_ptr())
+    return db
+
+
+def _bias_nchw(g):
+    B, C = g.shape[0], g.shape[1]
+    L = lib()
+    db = torch.empty(C, dtype=torch.float32, device=g.device)
+    ws = ops._workspace(L.size("vc_bias_grad_workspace_bytes", C), g.device)
+    L.call("vc_bias_grad", ptr(g), B, C, g.shape[2] * g.shape[3], ptr(db), 0, ptr(ws), ws.numel(), stream_ptr())
+    return db
+
+
+def _empty_nhwc(B, H, W, C, dev):
+    return torch.empty((B, H, W, C), dtype=_BF, device=dev)
+
+
+_ok_cache: dict = {}
+
+
+def _ok(*checks) -> bool:
+    r = _ok_cache.get(checks)
+    if r is None:
+        L = lib()
+        r = all(L.size(name, *args) == 1 for name, args in checks)
+        _ok_cache[checks] = r
+    return r
+
+
+def encoder_supported(x, convs) -> bool:
+    if not (ENABLED and ops.PRECISION == "bf16" and x.is_cuda and x.dim() == 4 and x.shape[1] == 1 and len(convs) == 3):
+        return False
+    B, _, H, W = x.shape
+    c1, c2, c3 = (c.weight.shape[0] for c in convs)
+    if H % 8 or W % 8 or c1 % 8 or convs[1].weight.shape[1] != c1 or convs[2].weight.shape[1] != c2:
+        return False
+    d2, d3 = (B, c1, H // 2, W // 2, c2), (B, c2, H // 4, W // 4, c3)
+    return _ok(("vc_conv_nhwc_supported", (CONV_FWD, *d2)), ("vc_conv_nhwc_supported", (CONV_FWD, *d3)),
+               ("vc_conv_nhwc_supported", (CONV_DGRAD, *d2)), ("vc_conv_nhwc_supported", (CONV_DGRAD, *d3)),
+               ("vc_conv_nhwc_wgrad_supported", (CONV_WGRAD, *d2)), ("vc_conv_nhwc_wgrad_supported", (CONV_WGRAD, *d3))) \
+        and (W // 8) % 64 == 0
+
+
+def decoder_supported(h, deconvs) -> bool:
+    if not (ENABLED and ops.PRECISION == "bf16" and h.is_cuda and h.dim() == 4 and len(deconvs) == 3):
+        return False
+    B, C0, H, W = h.shape
+    c1, c2, c3 = (d.weight.shape[1] for d in deconvs)
+    if c3 != 1 or C0 % 8 or W % 64 or deconvs[0].weight.shape[0] != C0 or c2 % 8:
+        return False
+    d1, d2 = (B, C0, H, W, c1), (B, c1, 2 * H, 2 * W, c2)
+    return _ok(("vc_conv_nhwc_supported", (CONVT_FWD, *d1)), ("vc_conv_nhwc_supported", (CONVT_FWD, *d2)),
+               ("vc_conv_nhwc_supported", (CONVT_DGRAD, *d1)), ("vc_conv_nhwc_supported", (CONVT_DGRAD, *d2)),
+               ("vc_conv_nhwc_wgrad_supported", (CONVT_WGRAD, *d1)), ("vc_conv_nhwc_wgrad_supported", (CONVT_WGRAD, *d2)))
+
+
+class EncoderConvFn(torch.autograd.Function):
+    """x [B,1,H,W] fp32 -> ReLU(conv3(ReLU(conv2(ReLU(conv1(x)))))) as fp32 NCHW [B,C3,H/8,W/8] (12:87-89, 12:105)."""
+
+    @staticmethod
+    def forward(ctx, x, w1, b1, w2, b2, w3, b3):
+        x = ops._f32(x, "encoder.x")
+        B, _, H, W = x.shape
+        c1, c2, c3 = w1.shape[0], w2.shape[0], w3.shape[0]
+        dev = x.device
+        L = lib()
+        a1 = _empty_nhwc(B, H // 2, W // 2, c1, dev)
+        L.call("vc_nhwc_conv1_fwd", ptr(x), ptr(w1), ptr(b1), 1, ptr(a1), B, H, W, c1, stream_ptr())
+        a2 = _empty_nhwc(B, H // 4, W // 4, c2, dev)
+        _conv(CONV_FWD, a1, w2, b2, True, None, a2, None, (B, c1, H // 2, W // 2, c2))
+        a3 = torch.empty((B, c3, H // 8, W // 8), dtype=torch.float32, device=dev)
+        _conv(CONV_FWD, a2, w3, b3, True, None, None, a3, (B, c2, H // 4, W // 4, c3))
+        ctx.save_for_backward(x, a1, a2, a3, w1, w2, w3)
+        return a3
+
+    @staticmethod
+    def backward(ctx, da3):
+        x, a1, a2, a3, w1, w2, w3 = ctx.saved_tensors
+        da3 = ops._f32(da3, "encoder.da3")
+        B, _, H, W = x.shape
+        c1, c2, c3 = w1.shape[0], w2.shape[0], w3.shape[0]
+        dev = x.device
+        L = lib()
+        s = stream_ptr()
+        d2, d3 = (B, c1, H // 2, W // 2, c2), (B, c2, H // 4, W // 4, c3)
+        # conv3: g3 = da3 * (a3 > 0) as bf16 NHWC (+ db3) from the fp32 NCHW pair the fully connected layer exchanges
+        g3 = torch.empty_like(a3)
+        g3n = _empty_nhwc(B, H // 8, W // 8, c3, dev)
+        db3 = torch.empty(c3, dtype=torch.float32, device=dev)
+        ws = ops._workspace(L.size("vc_relu_bwd_bias_nhwc_workspace_bytes", c3), dev)
+        L.call("vc_relu_bwd_bias_nhwc", ptr(da3), ptr(a3), B, c3, H // 8, W // 8, ptr(g3), ptr(g3n), ptr(db3), ptr(ws),
+               ws.numel(), s)
+        dw3 = _wgrad(CONV_WGRAD, g3n, a2, w3, d3)
+        g2n = torch.empty_like(a2)
+        _conv(CONV_DGRAD, g3n, w3, None, False, a2, g2n, None, d3)          # ReLU mask of a2 in the epilogue
+        db2 = _bias_nhwc(g2n)
+        dw2 = _wgrad(CONV_WGRAD, g2n, a1, w2, d2)
+        # conv1's gradient leaves the NHWC world: fp32 NCHW for the single-channel weight-gradient kernel
+        g1 = torch.empty((B, c1, H // 2, W // 2), dtype=torch.float32, device=dev)
+        _conv(CONV_DGRAD, g2n, w2, None, False, a1, None, g1, d2)
+        db1 = _bias_nchw(g1)
+        dw1 = torch.empty_like(w1)
+        ops._dense(CONV_WGRAD, 1, g1, x, None, dw1, B, 1, H, W, c1, False)
+        dx = None
+        if ctx.needs_input_grad[0]:
+            dx = torch.empty_like(x)
+            ops._dense(CONV_DGRAD, 1, g1, w1, None, dx, B, 1, H, W, c1, False)
+        return dx, dw1, db1, dw2, db2, dw3, db3
+
+
+class DecoderConvFn(torch.autograd.Function):
+    """h [B,C0,H,W] fp32 -> deconv3(ReLU(deconv2(ReLU(deconv1(h))))) as fp32 NCHW [B,1,8H,8W] (12:135-137, 12:141)."""
+
+    @staticmethod
+    def forward(ctx, h, w1, b1, w2, b2, w3, b3):
+        h = ops._f32(h, "decoder.h").contiguous()
+        B, C0, H, W = h.shape
+        c1, c2 = w1.shape[1], w2.shape[1]
+        dev = h.device
+        L = lib()
+        d0n = _empty_nhwc(B, H, W, C0, dev)
+        L.call("vc_nhwc_from_nchw", ptr(h), ptr(d0n), B, C0, H, W, stream_ptr())
+        d1n = _empty_nhwc(B, 2 * H, 2 * W, c1, dev)
+        _conv(CONVT_FWD, d0n, w1, b1, True, None, d1n, None, (B, C0, H, W, c1))
+        d2n = _empty_nhwc(B, 4 * H, 4 * W, c2, dev)
+        d2 = torch.empty((B, c2, 4 * H, 4 * W), dtype=torch.float32, device=dev)   # the single-channel end reads fp32 NCHW
+        _conv(CONVT_FWD, d1n, w2, b2, True, None, d2n, d2, (B, c1, 2 * H, 2 * W, c2))
+        xhat = torch.empty((B, 1, 8 * H, 8 * W), dtype=torch.float32, device=dev)
+        ops._dense(CONVT_FWD, 1, d2, w3, b3, xhat, B, c2, 4 * H, 4 * W, 1, False)
+        ctx.save_for_backward(d0n, d1n, d2n, d2, w1, w2, w3)
+        ctx.dims = (B, C0, H, W)
+        return xhat
+
+    @staticmethod
+    def backward(ctx, dxhat):
+        d0n, d1n, d2n, d2, w1, w2, w3 = ctx.saved_tensors
+        dxhat = ops._f32(dxhat, "decoder.dxhat")
+        B, C0, H, W = ctx.dims
+        c1, c2 = w1.shape[1], w2.shape[1]
+        dev = dxhat.device
+        L = lib()
+        e1, e2 = (B, C0, H, W, c1), (B, c1, 2 * H, 2 * W, c2)
+        db3 = _bias_nchw(dxhat)
+        dw3 = torch.empty_like(w3)
+        ops._dense(CONVT_WGRAD, 1, dxhat, d2, None, dw3, B, c2, 4 * H, 4 * W, 1, False)
+        g2n = torch.empty_like(d2n)
+        L.call("vc_nhwc_convT1_dgrad", ptr(dxhat), ptr(w3), ptr(d2n), ptr(g2n), B, c2, 4 * H, 4 * W, stream_ptr())
+        db2 = _bias_nhwc(g2n)
+        dw2 = _wgrad(CONVT_WGRAD, g2n, d1n, w2, e2)
+        g1n = torch.empty_like(d1n)
+        _conv(CONVT_DGRAD, g2n, w2, None, False, d1n, g1n, None, e2)
+        db1 = _bias_nhwc(g1n)
+        dw1 = _wgrad(CONVT_WGRAD, g1n, d0n, w1, e1)
+        dh = None
+        if ctx.needs_input_grad[0]:
+            dh = torch.empty((B, C0, H, W), dtype=torch.float32, device=dev)
+            _conv(CONVT_DGRAD, g1n, w1, None, False, None, None, dh, e1)
+        return dh, dw1, db1, dw2, db2, dw3, db3
+
+
+def encoder_convs(x, convs):
+    return EncoderConvFn.apply(x, convs[0].weight, convs[0].bias, convs[1].weight, convs[1].bias, convs[2].weight,
+                               convs[2].bias)
+
+
+def decoder_deconvs(h, deconvs):
+    return DecoderConvFn.apply(h, deconvs[0].weight, deconvs[0].bias, deconvs[1].weight, deconvs[1].bias,
+                               deconvs[2].weight, deconvs[2].bias)

@@ -19,7 +19,7 @@ import numpy as np
 import torch
 import torch.nn as nn
 
-from . import ops
+from . import convstack, ops
 
 
 def _conv_out(n: int) -> int:
@@ -52,9 +52,13 @@ class AudioEncoder(nn.Module):
         self.logvar = nn.Linear(256, z_dim)
 
     def features(self, x: torch.Tensor) -> torch.Tensor:
-        h = x
-        for i in (0, 2, 4):
-            h = ops.conv2d_s2k3(h, self.conv[i].weight, self.conv[i].bias, relu=True)
+        convs = [self.conv[0], self.conv[2], self.conv[4]]
+        if convstack.encoder_supported(x, convs):      # bf16 mode, T a multiple of 1024: bf16 NHWC between the layers
+            h = convstack.encoder_convs(x, convs)
+        else:
+            h = x
+            for c in convs:
+                h = ops.conv2d_s2k3(h, c.weight, c.bias, relu=True)
         return _lin(self.fc[0], h.flatten(1), relu=True)
 
     def forward(self, x: torch.Tensor) -> Tuple[torch.Tensor, torch.Tensor]:
@@ -90,6 +94,9 @@ class AudioDecoder(nn.Module):
     def forward(self, z: torch.Tensor) -> torch.Tensor:
         h = _lin(self.fc[2], _lin(self.fc[0], z, relu=True), relu=True)
         h = h.view(z.size(0), *self.h_shape)
+        deconvs = [self.deconv[0], self.deconv[2], self.deconv[4]]
+        if convstack.decoder_supported(h, deconvs):
+            return convstack.decoder_deconvs(h, deconvs)
         h = ops.convT2d_s2k4(h, self.deconv[0].weight, self.deconv[0].bias, relu=True)
         h = ops.convT2d_s2k4(h, self.deconv[2].weight, self.deconv[2].bias, relu=True)
         return ops.convT2d_s2k4(h, self.deconv[4].weight, self.deconv[4].bias, relu=False)
