@@ -113,6 +113,11 @@ def flops_of(name: str, sig) -> float:
         if name.startswith("vc_linear_"):
             M, N, K = sig[:3]
             return 2.0 * M * N * K
+        if name in ("vc_conv_nhwc", "vc_conv_nhwc_wgrad"):
+            op, B, Cin, H, W, Cout = (sig[0],) + tuple(sig[2:7]) if name == "vc_conv_nhwc" else tuple(sig[:6])
+            if op <= 5:
+                return 2.0 * B * (H // 2) * (W // 2) * Cout * Cin * 9
+            return 2.0 * B * (4 * H * W) * Cout * Cin * 4
         if name.startswith("vc_conv2d_s2k3_"):
             B, Cin, H, W, Cout = sig[:5]
             return 2.0 * B * ((H - 1) // 2 + 1) * ((W - 1) // 2 + 1) * Cout * Cin * 9
@@ -144,6 +149,28 @@ def bytes_of(name: str, sig) -> float:
             return 12.0 * sig[0] * sig[1] * sig[2]
         if name == "vc_bias_grad":
             return 4.0 * sig[0] * sig[1] * sig[2]
+        # bf16 NHWC path (csrc/conv_nhwc*.cu, nhwc_misc.cu): 2 B per activation element read or written; the fp32 NCHW
+        # copies some boundary layers also write are NOT counted (so `achieved` is a lower bound for those launches)
+        if name == "vc_conv_nhwc":
+            op, _relu, B, Cin, H, W, Cout = sig[:7]
+            small, big = B * Cin * H * W, B * Cout * (H * W // 4 if op <= 4 else 4 * H * W)
+            act = small + big + (small if op in (4, 7) else 0)      # data gradients also read the ReLU mask
+            return 2.0 * act + 4.0 * Cin * Cout * (9 if op <= 4 else 16)
+        if name == "vc_conv_nhwc_wgrad":
+            op, B, Cin, H, W, Cout = sig[:6]
+            return 2.0 * (B * Cin * H * W + B * Cout * (H * W // 4 if op == 5 else 4 * H * W))
+        if name == "vc_nhwc_conv1_fwd":
+            _relu, B, H, W, Cout = sig[:5]
+            return 4.0 * B * H * W + 2.0 * B * (H // 2) * (W // 2) * Cout
+        if name == "vc_nhwc_convT1_dgrad":
+            B, Cin, H, W = sig[:4]
+            return 4.0 * B * 4 * H * W + 4.0 * B * Cin * H * W      # dy fp32; mask read + g written, bf16
+        if name == "vc_nhwc_bias_grad":
+            return 2.0 * sig[0] * sig[1]
+        if name == "vc_nhwc_from_nchw":
+            return 6.0 * sig[0] * sig[1] * sig[2] * sig[3]
+        if name == "vc_relu_bwd_bias_nhwc":
+            return 14.0 * sig[0] * sig[1] * sig[2] * sig[3]
     except Exception:
         pass
     return 0.0
@@ -151,6 +178,10 @@ def bytes_of(name: str, sig) -> float:
 
 def family_of(name: str, sig) -> str:
     """Kernel family behind an entry point (vc_dense_op dispatches on op and shape, csrc/tc_gemm.cu)."""
+    if name in ("vc_conv_nhwc", "vc_conv_nhwc_wgrad"):
+        return "conv_nhwc (TMA-fed fwd / dgrad)" if name == "vc_conv_nhwc" else "conv_nhwc_wgrad (TMA-fed)"
+    if name in ("vc_nhwc_conv1_fwd", "vc_nhwc_convT1_dgrad"):
+        return "conv_direct (1-channel ends)"
     if name != "vc_dense_op":
         return name
     op, _prec, B, Cin, H, W, Cout = sig[:7]
@@ -295,7 +326,7 @@ def roofline_from_summary(summ, steps, n_params, pk, ms_per_step):
     # DRAM bytes per launch of the headline family from the committed ncu capture (same command, --no-graph), next to
     # the algorithmic bytes per launch the `achieved` figure uses
     try:
-        tr = json.load(open(ROOT / "profiles" / "ncu_traffic_r1_final5.json"))
+        tr = json.load(open(ROOT / "profiles" / "ncu_traffic_r2.json"))
         if roof["kernel"] in tr:
             roof["traffic"] = tr[roof["kernel"]]["dram_bytes_per_launch"]
             roof["traffic_source"] = tr["_source"]

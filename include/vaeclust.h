@@ -137,6 +137,17 @@ int vc_nhwc_conv1_fwd(const float* x, const float* W, const float* bias, int rel
 int vc_nhwc_convT1_dgrad(const float* dy, const float* W, const void* act_nhwc, void* g_nhwc, int B, int Cin, int H,
                          int Wd, void* stream);
 int vc_nhwc_from_nchw(const float* src, void* dst_nhwc, int B, int C, int H, int Wd, void* stream);
+/*  vc_nhwc_convT1_fwd   : nn.ConvTranspose2d(Cin, 1, 4, 2, 1) forward (12:137) from a bf16 NHWC input [B,H,W,Cin]; y fp32
+ *                         [B,1,2H,2W].
+ *  vc_nhwc_tap_wgrad    : weight gradient of either single-channel end from a bf16 NHWC tensor a_nhwc [B,PH,PW,C] and the
+ *                         one-channel fp32 tensor S [B,2PH,2PW]: dW[c][kh][kw] = sum a[b,i,j,c] * S[b,2i-1+kh,2j-1+kw].
+ *                         KS = 3: Conv2d(1,C,3,2,1) (a = output gradient, S = x, 12:87); KS = 4: ConvTranspose2d(C,1,4,2,1)
+ *                         (a = layer input, S = output gradient, 12:137).  C % 32 == 0, PW % 32 == 0. */
+int vc_nhwc_convT1_fwd(const void* x_nhwc, const float* W, const float* bias, float* y, int B, int Cin, int H, int Wd,
+                       void* stream);
+size_t vc_nhwc_tap_wgrad_workspace_bytes(int C, int KS);
+int vc_nhwc_tap_wgrad(int KS, const void* a_nhwc, const float* S, float* dW, int B, int C, int PH, int PW, void* workspace,
+                      size_t workspace_bytes, void* stream);
 size_t vc_nhwc_bias_grad_workspace_bytes(int C);
 int vc_nhwc_bias_grad(const void* g_nhwc, int64_t rows, int C, float* db, void* workspace, size_t workspace_bytes,
                       void* stream);
@@ -152,6 +163,8 @@ int vc_nhwc_bias_grad(const void* g_nhwc, int64_t rows, int C, float* db, void* 
  * Supported: H, W even, output row width W/2 (conv) or W (convT) a multiple of 128, source channels 32 (Conv forward,
  * ConvT data gradient) or a multiple of 64, at most 256 GEMM columns (Cout, 4*Cout, 4*Cin, Cin respectively). */
 int vc_conv_nhwc_supported(int op, int B, int Cin, int H, int W, int Cout);
+/* profiling aid: clock64 stamps of CTA 0's producers / MMA issuer for the first 64 k-blocks (8 int64 each); NULL = off */
+int vc_conv_nhwc_debug_trace(long long* buf);
 size_t vc_conv_nhwc_workspace_bytes(int op, int B, int Cin, int H, int W, int Cout);
 int vc_conv_nhwc(int op, const void* src_nhwc, const float* Wt, const float* bias, int relu, const void* mask_nhwc,
                  void* out_nhwc, float* out_nchw, int B, int Cin, int H, int W, int Cout, void* workspace,

@@ -119,6 +119,28 @@ def test_single_channel_ends_and_helpers():
     L.call("vc_nhwc_convT1_dgrad", ptr(dy), ptr(wt), ptr(an), ptr(g), B, C, H, W, stream_ptr())
     want = F.conv2d(_bf(dy), _bf(wt), None, stride=2, padding=1) * (_bf(act) > 0)
     _check(g, None, want)
+    # ConvTranspose2d(32 -> 1) forward from NHWC
+    xin, bb = _r(B, C, H, W, seed=9), _r(1, seed=10)
+    xn = _nhwc(xin)
+    yo = torch.empty(B, 1, 2 * H, 2 * W, device="cuda")
+    L.call("vc_nhwc_convT1_fwd", ptr(xn), ptr(wt), ptr(bb), ptr(yo), B, C, H, W, stream_ptr())
+    want = F.conv_transpose2d(_bf(xin), _bf(wt), bb, stride=2, padding=1)
+    _check(None, yo, want)
+    # weight gradients of both ends from NHWC
+    for KS in (3, 4):
+        a_t = _r(B, C, H, W, seed=11)
+        S = _r(B, 1, 2 * H, 2 * W, seed=12)
+        an2 = _nhwc(a_t)
+        dwt = torch.full((C, 1, KS, KS), float("nan"), device="cuda")
+        ws = torch.empty(L.size("vc_nhwc_tap_wgrad_workspace_bytes", C, KS), dtype=torch.uint8, device="cuda")
+        L.call("vc_nhwc_tap_wgrad", KS, ptr(an2), ptr(S), ptr(dwt), B, C, H, W, ptr(ws), ws.numel(), stream_ptr())
+        if KS == 3:      # Conv2d(1 -> C): a = output gradient on the H x W grid, S = input [2H, 2W]
+            wr = torch.zeros(C, 1, 3, 3, device="cuda", requires_grad=True)
+            F.conv2d(_bf(S), wr, None, stride=2, padding=1).backward(_bf(a_t))
+        else:            # ConvTranspose2d(C -> 1): a = layer input, S = output gradient
+            wr = torch.zeros(C, 1, 4, 4, device="cuda", requires_grad=True)
+            F.conv_transpose2d(_bf(a_t), wr, None, stride=2, padding=1).backward(_bf(S))
+        torch.testing.assert_close(dwt, wr.grad, rtol=2e-5, atol=2e-5 * float(wr.grad.abs().max()))
     # layout conversion
     src = _r(B, 128, 4, 128, seed=7)
     dst = torch.empty(B, 4, 128, 128, dtype=torch.bfloat16, device="cuda")
@@ -169,7 +191,8 @@ def test_weight_gradients(kind, B, Cin, H, W, Cout):
         ws.fill_(255)
 
 
-def test_conv_stacks_match_the_per_layer_path():
+@pytest.mark.parametrize("ends_nhwc", [False, True])
+def test_conv_stacks_match_the_per_layer_path(ends_nhwc):
     """The NHWC conv stacks (vaeclust.convstack) inside the script-12 model against the per-layer fp32-NCHW path: the same
     bf16 products and fp32 accumulation, so loss and gradients agree to summation order; only the hidden-layer bias
     gradients differ by the bf16 rounding of the gradients they sum."""
@@ -183,6 +206,7 @@ def test_conv_stacks_match_the_per_layer_path():
         m = torch.tensor([[1.0], [0.0]], device="cuda")
         eps = _r(B, 32, seed=3)
         out = {}
+        convstack.ENDS_NHWC = ends_nhwc
         for flag in (False, True):
             convstack.ENABLED = flag
             used = []
@@ -201,7 +225,8 @@ def test_conv_stacks_match_the_per_layer_path():
         assert out[True][2].keys() == out[False][2].keys()
         for k, g in out[False][2].items():
             rel = float((out[True][2][k] - g).norm() / (g.norm() + 1e-30))
-            assert rel < (2e-2 if k.endswith("bias") else 2e-3), (k, rel)
+            assert rel < (2e-2 if k.endswith("bias") else 5e-3), (k, rel)
     finally:
         convstack.ENABLED = True
+        convstack.ENDS_NHWC = False
         ops.set_precision("fp32")

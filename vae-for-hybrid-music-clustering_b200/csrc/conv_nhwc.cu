@@ -13,7 +13,9 @@
 // Weight slabs that fit (<= 150 KB) are loaded once per CTA and stay resident in shared memory; larger ones stream
 // through the ring with the A boxes.
 //
-// warp 0: TMA producer, warp 1: tcgen05.mma issuer (2 accumulator stages in TMEM), warps 2..9: epilogue.
+// warps 0, 10, 11, 12: TMA producers (k-block `it` belongs to producer it % 4), warp 1: tcgen05.mma issuer (2 accumulator
+// stages in TMEM), warps 2..9: epilogue.
+#include <stdlib.h>
 #include <string.h>
 #include "common.cuh"
 #include "tc05.cuh"
@@ -22,7 +24,8 @@ namespace vc {
 
 constexpr int NH_BM = 128;
 constexpr int NH_EPI = 256;
-constexpr int NH_THREADS = 64 + NH_EPI;
+constexpr int NH_PROD = 4;                       // TMA-issuing warps: one thread sustains only ~1 box per 460 clocks
+constexpr int NH_THREADS = 64 + NH_EPI + 32 * (NH_PROD - 1);   // (profiles/tma_rate.cu), four warps 4x that
 constexpr uint32_t NH_A_BYTES = NH_BM * 128;
 
 struct NhArgs {
@@ -32,6 +35,10 @@ struct NhArgs {
   int B, GH, GW, tilesW;     // GEMM rows = grid pixels (b, i, j); a tile = 128 consecutive j
   int N, BN, OC, OH, OW, quad;
   int tiles, nkb, stages, wres;
+  int G;                     // k-blocks per ring stage (one barrier round trip per G k-blocks)
+  int nprod;                 // active producer warps; divides `stages` (see nh_plan)
+  long long* trace;          // experiments only (vc_conv_nhwc_debug_trace): clock64 stamps of CTA 0
+  int dbg;                   // VAECLUST_NH_DEBUG (experiments only): 1 = every A box from image 0 / row 0, 4 = no epilogue traffic, 8 = no MMAs, 16 = no TMA loads
   uint32_t idesc;
   // epilogue
   const float* bias;         // [OC] or null
@@ -86,7 +93,8 @@ conv_nhwc_kernel(const NhArgs a, const __grid_constant__ CUtensorMap mapA, const
   unsigned char* smem = smem_raw + ((1024u - (tma::s32(smem_raw) & 1023u)) & 1023u);
   const int S = a.stages;
   const uint32_t b_bytes = (uint32_t)a.BN * 128u;
-  const uint32_t st_bytes = NH_A_BYTES + (a.wres ? 0u : b_bytes);
+  const uint32_t kb_bytes = NH_A_BYTES + (a.wres ? 0u : b_bytes);     // one k-block: A box (+ its weight rows)
+  const uint32_t st_bytes = (uint32_t)a.G * kb_bytes;
   unsigned char* slab = smem;                                            // resident weight slab: nkb x [BN][64] bf16
   unsigned char* ring = smem + (a.wres ? (size_t)a.nkb * b_bytes : 0);
   uint64_t* bars = reinterpret_cast<uint64_t*>(ring + (size_t)S * st_bytes);
@@ -96,6 +104,11 @@ conv_nhwc_kernel(const NhArgs a, const __grid_constant__ CUtensorMap mapA, const
   uint64_t* t_empty = t_full + 2;    // 2: accumulator stage drained by the epilogue threads
   uint64_t* w_full = t_empty + 2;    // 1: resident slab has landed
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(w_full + 1);
+  // per-k-block box offsets (c, dw, dh): the hot loops contain no integer division (a runtime division is ~150 clocks of
+  // dependent latency for a one-warp loop: it was most of the ~500 clocks per k-block the bare pipeline used to cost)
+  int* kb_c = reinterpret_cast<int*>(tmem_slot + 2);
+  int* kb_w = kb_c + 32;
+  int* kb_h = kb_w + 32;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t tmem_cols = a.BN <= 32 ? 64u : (a.BN <= 64 ? 128u : (a.BN <= 128 ? 256u : 512u));  // 2 stages
 
@@ -108,60 +121,113 @@ conv_nhwc_kernel(const NhArgs a, const __grid_constant__ CUtensorMap mapA, const
     tma::mbar_fence_init();
   }
   if (warp == 1) tc05::tmem_alloc(tmem_slot, tmem_cols);
+  if (threadIdx.x >= 64 && (int)threadIdx.x - 64 < a.nkb) {
+    const int kb = (int)threadIdx.x - 64;
+    int c, w, h;
+    nh_coords(a, kb, 0, 0, c, w, h);     // offsets relative to (S*i, S*j0)  [pair: (2i, j0)]
+    kb_c[kb] = c; kb_w[kb] = w; kb_h[kb] = h;
+  }
   tc05::fence_before();
   __syncthreads();
   tc05::fence_after();
   const uint32_t tmem_base = *tmem_slot;
   const int my_tiles = (a.tiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
 
-  if (warp == 0) {
-    // ===================== TMA producer =====================
-    if (lane == 0) {
-      if (a.wres) {
-        tma::mbar_expect_tx(w_full, (uint32_t)a.nkb * b_bytes);
-        for (int kb = 0; kb < a.nkb; ++kb) tma::load_2d(slab + (size_t)kb * b_bytes, &mapW, w_full, kb * 64, 0);
-      }
-      uint32_t it = 0;
-      for (int tl = 0; tl < my_tiles; ++tl) {
-        const int t = (int)blockIdx.x + tl * (int)gridDim.x;
-        const int tw = t % a.tilesW, r = t / a.tilesW;
-        const int i = r % a.GH, b = r / a.GH, j0 = tw * NH_BM;
-        for (int kb = 0; kb < a.nkb; ++kb, ++it) {
-          const int s = it % S;
-          tma::mbar_wait_backoff(&empty[s], ((it / S) & 1u) ^ 1u, 64);
-          unsigned char* tile = ring + (size_t)s * st_bytes;
-          int c, w, h;
-          nh_coords(a, kb, i, j0, c, w, h);
-          tma::mbar_expect_tx(&full[s], st_bytes);
-          tma::load_4d(tile, &mapA, &full[s], c, w, h, b);
-          if (!a.wres) tma::load_2d(tile + NH_A_BYTES, &mapW, &full[s], kb * 64, 0);
+  if (warp == 0 || warp >= 10) {
+    // ===================== TMA producers =====================
+    // whole warp, uniform control flow, one elected lane issues (see the MMA issuer below for why)
+    {
+      const uint32_t me = warp == 0 ? 0u : (uint32_t)(warp - 9);
+      if (a.wres && me == 0) {
+        if (tc05::elect_one()) {
+          tma::mbar_expect_tx(w_full, (uint32_t)a.nkb * b_bytes);
+          for (int kb = 0; kb < a.nkb; ++kb) tma::load_2d(slab + (size_t)kb * b_bytes, &mapW, w_full, kb * 64, 0);
         }
+        __syncwarp();
+      }
+      // this producer owns ring stages me, me + 4, ... of the CTA's flat (tile, k-group) sequence -- a stage holds G
+      // k-blocks; ring slot and phase advance by additions only
+      const int wS = a.pair ? 1 : a.S, hS = a.pair ? 2 : a.S;
+      const int ngr = a.nkb / a.G;                          // k-groups per tile
+      const int NP = a.nprod;
+      uint32_t it = me;
+      int s = (int)me % S, ph = ((int)me / S) & 1;         // (once, outside the loop)
+      int tl = (int)me < NP ? 0 : my_tiles, kg = (int)me;
+      while (kg >= ngr) { kg -= ngr; ++tl; }
+      while (tl < my_tiles) {
+        const int t = (int)blockIdx.x + tl * (int)gridDim.x;
+        const int tw = t % a.tilesW, r = t / a.tilesW;       // per tile only
+        const int i = r % a.GH, b = r / a.GH, j0 = tw * NH_BM;
+        for (; kg < ngr; kg += NP, it += NP) {
+          const bool tr = a.trace && blockIdx.x == 0 && it < 64 && lane == 0;
+          if (tr) a.trace[it * 8 + 0] = clock64();
+          tma::mbar_wait_backoff(&empty[s], (uint32_t)ph ^ 1u, 64);
+          if (tr) a.trace[it * 8 + 1] = clock64();
+          unsigned char* tile = ring + (size_t)s * st_bytes;
+          if (a.dbg & 16) {
+            if (tc05::elect_one()) tma::mbar_arrive(&full[s]);
+          } else if (tc05::elect_one()) {
+            tma::mbar_expect_tx(&full[s], st_bytes);
+            for (int g = 0; g < a.G; ++g) {
+              const int kb = kg * a.G + g;
+              const int c = kb_c[kb], w = wS * j0 + kb_w[kb], h = hS * i + kb_h[kb];
+              if (a.dbg & 1) tma::load_4d(tile + g * kb_bytes, &mapA, &full[s], c, w & 255, h & 3, 0);
+              else tma::load_4d(tile + g * kb_bytes, &mapA, &full[s], c, w, h, b);
+              if (!a.wres) tma::load_2d(tile + g * kb_bytes + NH_A_BYTES, &mapW, &full[s], kb * 64, 0);
+            }
+          }
+          __syncwarp();
+          if (tr) a.trace[it * 8 + 2] = clock64();
+          s += NP;
+          while (s >= S) { s -= S; ph ^= 1; }
+        }
+        kg -= ngr;
+        ++tl;
+        while (kg >= ngr) { kg -= ngr; ++tl; }
       }
     }
   } else if (warp == 1) {
     // ===================== MMA issuer =====================
-    if (lane == 0) {
+    // The WHOLE warp walks the loop (uniform control flow, warp-uniform values) and one ELECTED lane issues: issued from a
+    // `lane == 0` branch the compiler cannot prove a single active lane and wraps every tcgen05.mma / commit in an
+    // ELECT ... BRA.U.ANY waterfall loop, which cost ~670 clocks per k-block (profiles/trace_nhwc.py).
+    {
       if (a.wres) tma::mbar_wait_backoff(w_full, 0, 64);
       uint32_t it = 0;
+      int s = 0;
+      uint32_t ph = 0;
       for (int tl = 0; tl < my_tiles; ++tl) {
         const int as = tl & 1;
         const uint32_t aph = (uint32_t)(tl >> 1) & 1u;
         tma::mbar_wait_backoff(&t_empty[as], aph ^ 1u, 64);
         tc05::fence_after();
         const uint32_t tacc = tmem_base + (uint32_t)(as * a.BN);
-        for (int kb = 0; kb < a.nkb; ++kb, ++it) {
-          const int s = it % S;
-          tma::mbar_wait_backoff(&full[s], (it / S) & 1u, 32);
+        for (int kb = 0; kb < a.nkb; kb += a.G, ++it) {
+          const bool tr = a.trace && blockIdx.x == 0 && it < 64 && lane == 0;
+          if (tr) a.trace[it * 8 + 3] = clock64();
+          tma::mbar_wait_backoff(&full[s], ph, 32);
+          if (tr) a.trace[it * 8 + 4] = clock64();
           tc05::fence_after();
-          const uint32_t sa = tma::s32(ring + (size_t)s * st_bytes);
-          const uint32_t sb = a.wres ? tma::s32(slab + (size_t)kb * b_bytes) : sa + NH_A_BYTES;
+          const uint32_t st0 = tma::s32(ring + (size_t)s * st_bytes);
+          if (tc05::elect_one()) {
+            if (!(a.dbg & 8)) {
+              for (int g = 0; g < a.G; ++g) {
+                const uint32_t sa = st0 + (uint32_t)g * kb_bytes;
+                const uint32_t sb = a.wres ? tma::s32(slab + (size_t)(kb + g) * b_bytes) : sa + NH_A_BYTES;
 #pragma unroll
-          for (int kk = 0; kk < 4; ++kk)
-            tc05::mma_bf16(tacc, tc05::desc_k_sw128(sa + kk * 32), tc05::desc_k_sw128(sb + kk * 32), a.idesc,
-                           (uint32_t)((kb | kk) != 0));
-          tc05::commit(&empty[s]);
+                for (int kk = 0; kk < 4; ++kk)
+                  tc05::mma_bf16(tacc, tc05::desc_k_sw128(sa + kk * 32), tc05::desc_k_sw128(sb + kk * 32), a.idesc,
+                                 (uint32_t)((kb | g | kk) != 0));
+              }
+            }
+            tc05::commit(&empty[s]);
+          }
+          __syncwarp();
+          if (tr) a.trace[it * 8 + 5] = clock64();
+          if (++s == S) { s = 0; ph ^= 1u; }
         }
-        tc05::commit(&t_full[as]);
+        if (tc05::elect_one()) tc05::commit(&t_full[as]);
+        __syncwarp();
       }
     }
   } else {
@@ -191,6 +257,7 @@ conv_nhwc_kernel(const NhArgs a, const __grid_constant__ CUtensorMap mapA, const
           tc05::fence_before();
           tma::mbar_arrive(&t_empty[as]);
         }
+        if (a.dbg & 4) continue;
         if (!a.quad) {
           const int c0 = cc * 32;
           const int64_t px = ((int64_t)pb * a.OH + pi) * a.OW + pj;
@@ -316,7 +383,7 @@ int nh_make_map(CUtensorMap* m, const void* base, int Cv, int SWv, int SH, int B
 
 struct NhPlan {
   bool ok;
-  int wmode, pair, nblk, C, cchunks, TW, S, D0, taps, N, BN, nkb, Kp, GH, GW, SH, SW, OC, OH, OW, quad, wres, stages;
+  int wmode, pair, nblk, C, cchunks, TW, S, D0, taps, N, BN, nkb, Kp, GH, GW, SH, SW, OC, OH, OW, quad, wres, stages, G, nprod;
   size_t smem;
 };
 
@@ -349,19 +416,34 @@ static NhPlan nh_plan(int op, int B, int Cin, int H, int W, int Cout) {
   }
   if (p.pair) { p.cchunks = 1; p.nkb = (p.taps / p.TW) * p.nblk; }
   else { if (p.C % 64) return p; p.cchunks = p.C / 64; p.nkb = p.taps * p.cchunks; }
-  if (p.N % 32 || p.N > 256 || p.GW % NH_BM) return p;
+  if (p.N % 32 || p.N > 256 || p.GW % NH_BM || p.nkb > 32) return p;
   if ((int64_t)B * p.GH * (p.GW / NH_BM) >= 2147483647LL) return p;
   p.BN = p.N;
   p.Kp = p.nkb * 64;
-  const size_t avail = 232448 - 1024 - 512;
+  const size_t avail = 232448 - 1024 - 1024;
   const size_t slab = (size_t)p.nkb * p.BN * 128;
   p.wres = slab + 4 * NH_A_BYTES <= avail ? 1 : 0;
-  const size_t st_bytes = NH_A_BYTES + (p.wres ? 0 : (size_t)p.BN * 128);
-  int stages = (int)((avail - (p.wres ? slab : 0)) / st_bytes);
+  const size_t kb_bytes = NH_A_BYTES + (p.wres ? 0 : (size_t)p.BN * 128);
+  const size_t ring = avail - (p.wres ? slab : 0);
+  // k-blocks per ring stage: a barrier round trip (producer wait / arrive, issuer wait / commit) costs ~380 clocks however
+  // little a stage holds, so group up to four k-blocks while at least two stages (and six k-blocks in flight) remain
+  p.G = 1;
+  for (int g = 4; g >= 2; --g)
+    if (p.nkb % g == 0 && ring / (g * kb_bytes) >= 2 && (ring / (g * kb_bytes)) * g >= 8) { p.G = g; break; }
+  {
+    static const char* g_env = getenv("VAECLUST_NH_GROUP");
+    if (g_env && atoi(g_env) >= 1 && p.nkb % atoi(g_env) == 0 && ring / (atoi(g_env) * kb_bytes) >= 2) p.G = atoi(g_env);
+  }
+  int stages = (int)(ring / (p.G * kb_bytes));
   if (stages > 8) stages = 8;
   if (stages < 2) return p;
+  // Producer warp w fills stages w, w + nprod, ...  The stage count must be a multiple of nprod: then a producer meets
+  // each of its ring slots in EVERY round; otherwise it can skip a round of a slot and the one-bit phase parity of the
+  // slot's `empty` barrier aliases (the wait passes two phases early and the slot is overwritten while in use).
+  if (stages >= 4) { stages -= stages % 4; p.nprod = 4; }
+  else { stages = 2; p.nprod = 2; }
   p.stages = stages;
-  p.smem = (p.wres ? slab : 0) + (size_t)stages * st_bytes + (2 * stages + 5) * 8 + 16 + 1024;
+  p.smem = (p.wres ? slab : 0) + (size_t)stages * p.G * kb_bytes + (2 * stages + 5) * 8 + 16 + 3 * 32 * 4 + 1024;
   p.ok = true;
   return p;
 }
@@ -372,6 +454,9 @@ int ig_build_weights(const float* w, int mode, int Cin, int Cout, int N, int BN,
 }  // namespace vc
 
 using namespace vc;
+
+static long long* g_nh_trace = nullptr;
+extern "C" int vc_conv_nhwc_debug_trace(long long* buf) { g_nh_trace = buf; return VC_OK; }
 
 extern "C" int vc_conv_nhwc_supported(int op, int B, int Cin, int H, int W, int Cout) {
   return nh_plan(op, B, Cin, H, W, Cout).ok ? 1 : 0;
@@ -421,7 +506,14 @@ extern "C" int vc_conv_nhwc(int op, const void* src_nhwc, const float* Wt, const
   a.pair = p.pair; a.nblk = p.nblk; a.cchunks = p.cchunks; a.TW = p.TW; a.S = p.S; a.D0 = p.D0;
   a.B = B; a.GH = p.GH; a.GW = p.GW; a.tilesW = p.GW / NH_BM;
   a.N = p.N; a.BN = p.BN; a.OC = p.OC; a.OH = p.OH; a.OW = p.OW; a.quad = p.quad;
-  a.tiles = B * p.GH * a.tilesW; a.nkb = p.nkb; a.stages = p.stages; a.wres = p.wres;
+  a.tiles = B * p.GH * a.tilesW; a.nkb = p.nkb; a.stages = p.stages; a.wres = p.wres; a.G = p.G; a.nprod = p.nprod;
+  {
+    static const char* dbg_env = getenv("VAECLUST_NH_DEBUG");
+    static const char* st_env = getenv("VAECLUST_NH_STAGES");
+    a.dbg = dbg_env ? atoi(dbg_env) : 0;
+    a.trace = g_nh_trace;
+    if (st_env && atoi(st_env) >= 2 && atoi(st_env) < a.stages) a.stages = atoi(st_env);
+  }
   a.idesc = tc05::idesc(tc05::kFmtBF16, NH_BM, p.BN, 0, 0);
   a.bias = bias; a.relu = relu; a.mask = static_cast<const __nv_bfloat16*>(mask_nhwc);
   a.out_nhwc = static_cast<__nv_bfloat16*>(out_nhwc); a.out_nchw = out_nchw;

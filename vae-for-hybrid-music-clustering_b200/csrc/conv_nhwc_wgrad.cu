@@ -13,14 +13,16 @@
 //
 // One accumulator tile [Cp rows][taps x 64 columns] lives in tensor memory for the whole kernel (up to all 512 columns);
 // when the taps of a layer do not fit, tap rows are split over blockIdx.y.  blockIdx.x splits the pixels (split-K), the
-// partials are folded in a fixed order.  warp 0: TMA producer, warp 1: MMA issuer, warps 2..5: TMEM -> partials.
+// partials are folded in a fixed order.  warps 0, 6, 7, 8: TMA producers (box x of a chunk belongs to producer x % 4, each
+// announces its own bytes on the stage barrier), warp 1: MMA issuer, warps 2..5: TMEM -> partials.
 #include <string.h>
 #include "common.cuh"
 #include "tc05.cuh"
 
 namespace vc {
 
-constexpr int NW_THREADS = 192;
+constexpr int NW_PROD = 4;               // TMA-issuing warps (one thread sustains ~1 box per 460 clocks, profiles/tma_rate.cu)
+constexpr int NW_THREADS = 192 + 32 * (NW_PROD - 1);
 constexpr uint32_t NW_BOX = 64 * 128;    // [64 pixels][64 bf16]
 
 struct NwArgs {
@@ -53,7 +55,8 @@ conv_nhwc_wgrad_kernel(const NwArgs a, const __grid_constant__ CUtensorMap mapP,
   if (threadIdx.x == 0) {
     tma::prefetch_map(&mapP);
     tma::prefetch_map(&mapQ);
-    for (int s = 0; s < S; ++s) { tma::mbar_init(&full[s], 1); tma::mbar_init(&empty[s], 1); }
+    const int nprod = min(NW_PROD, a.pboxes + a.nblk);
+    for (int s = 0; s < S; ++s) { tma::mbar_init(&full[s], nprod); tma::mbar_init(&empty[s], 1); }
     tma::mbar_init(accb, 1);
     tma::mbar_fence_init();
   }
@@ -63,8 +66,13 @@ conv_nhwc_wgrad_kernel(const NwArgs a, const __grid_constant__ CUtensorMap mapP,
   tc05::fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
-  if (warp == 0) {
-    if (lane == 0)
+  if (warp == 0 || warp >= 6) {
+    const int me = warp == 0 ? 0 : warp - 5;
+    const int nbox = a.pboxes + a.nblk;
+    // whole warp, uniform control flow, one elected lane issues: from a `lane == 0` branch every UTMALDG / UTCHMMA sits in
+    // an ELECT ... BRA.U.ANY waterfall loop (~460 clocks per box, profiles/tma_rate.cu)
+    if (me < nbox) {
+      const int mine = (nbox - me + NW_PROD - 1) / NW_PROD;      // boxes me, me + 4, ...
       for (int it = 0; it < n; ++it) {
         const int st = it % S;
         tma::mbar_wait_backoff(&empty[st], (((uint32_t)it / S) & 1u) ^ 1u, 64);
@@ -72,17 +80,24 @@ conv_nhwc_wgrad_kernel(const NwArgs a, const __grid_constant__ CUtensorMap mapP,
         const int ch = c0 + it;
         const int seg = ch % a.segs, r = ch / a.segs;
         const int i = r % a.GH, b = r / a.GH, j0 = seg * 64;
-        tma::mbar_expect_tx(&full[st], st_bytes);
-        for (int pb = 0; pb < a.pboxes; ++pb) tma::load_4d(sp + pb * NW_BOX, &mapP, &full[st], pb * 64, j0, i, b);
-        unsigned char* sq = sp + a.pboxes * NW_BOX;
-        for (int lb = 0; lb < a.nblk; ++lb) {
-          const int th = gy * a.g + lb / a.bpt, blk = lb % a.bpt;
-          const int w = a.pair ? j0 + blk - 1 : 2 * j0 + blk - 1;
-          tma::load_4d(sq + lb * NW_BOX, &mapQ, &full[st], 0, w, 2 * i + th - 1, b);
+        if (tc05::elect_one()) {
+          tma::mbar_expect_tx(&full[st], (uint32_t)mine * NW_BOX);
+          for (int x = me; x < nbox; x += NW_PROD) {
+            if (x < a.pboxes) {
+              tma::load_4d(sp + x * NW_BOX, &mapP, &full[st], x * 64, j0, i, b);
+            } else {
+              const int lb = x - a.pboxes;
+              const int th = gy * a.g + lb / a.bpt, blk = lb % a.bpt;
+              const int w = a.pair ? j0 + blk - 1 : 2 * j0 + blk - 1;
+              tma::load_4d(sp + x * NW_BOX, &mapQ, &full[st], 0, w, 2 * i + th - 1, b);
+            }
+          }
         }
+        __syncwarp();
       }
+    }
   } else if (warp == 1) {
-    if (lane == 0) {
+    {
       // M = 128 always: with a 64-channel P the second 64-row atom re-reads the first box (LBO = 0), rows 64..127 of the
       // accumulator are never read back
       const uint32_t lbo_a = a.pboxes == 2 ? NW_BOX : 0u;
@@ -91,19 +106,23 @@ conv_nhwc_wgrad_kernel(const NwArgs a, const __grid_constant__ CUtensorMap mapP,
         tma::mbar_wait_backoff(&full[st], ((uint32_t)it / S) & 1u, 32);
         tc05::fence_after();
         const uint32_t sa = tma::s32(smem + (size_t)st * st_bytes), sb = sa + a.pboxes * NW_BOX;
+        if (tc05::elect_one()) {
 #pragma unroll
-        for (int kk = 0; kk < 4; ++kk) {
-          const uint64_t da = tc05::desc_mn_sw128(sa + kk * 2048, lbo_a);
-          for (int b0 = 0; b0 < a.nblk; b0 += 4) {      // up to four 64-column boxes (N = 256) per instruction
-            const int nb = min(4, a.nblk - b0);
-            const uint64_t db = tc05::desc_mn_sw128(sb + b0 * NW_BOX + kk * 2048, NW_BOX);
-            tc05::mma_bf16(tmem_base + b0 * 64, da, db, tc05::idesc(tc05::kFmtBF16, 128, nb * 64, 1, 1),
-                           (uint32_t)((it | kk) != 0));
+          for (int kk = 0; kk < 4; ++kk) {
+            const uint64_t da = tc05::desc_mn_sw128(sa + kk * 2048, lbo_a);
+            for (int b0 = 0; b0 < a.nblk; b0 += 4) {      // up to four 64-column boxes (N = 256) per instruction
+              const int nb = min(4, a.nblk - b0);
+              const uint64_t db = tc05::desc_mn_sw128(sb + b0 * NW_BOX + kk * 2048, NW_BOX);
+              tc05::mma_bf16(tmem_base + b0 * 64, da, db, tc05::idesc(tc05::kFmtBF16, 128, nb * 64, 1, 1),
+                             (uint32_t)((it | kk) != 0));
+            }
           }
+          tc05::commit(&empty[st]);
         }
-        tc05::commit(&empty[st]);
+        __syncwarp();
       }
-      if (n > 0) tc05::commit(accb);
+      if (n > 0 && tc05::elect_one()) tc05::commit(accb);
+      __syncwarp();
     }
   } else {
     const int q = warp & 3;

@@ -208,6 +208,144 @@ nm_colsum_fold_kernel(const double* __restrict__ part, int nblk, int C, float* _
   db[c] = (float)v;
 }
 
+// ---- ConvTranspose2d(C -> 1, k4 s2 p1) forward from a bf16 NHWC input (12:137): thread = coarse pixel (i, j) -> the 2x2
+// output block y[2i..2i+1][2j..2j+1].  Output row 2i+ph takes input rows i+dh with kernel row kh = 1 + ph - 2 dh
+// (dh = -1: ph 0 only, kh 3; dh = 0: kh 1 / 2; dh = +1: ph 1 only, kh 0); columns likewise: 16 products per channel.
+__global__ void __launch_bounds__(256)
+nm_convT1_fwd_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ w, const float* __restrict__ bias,
+                     float* __restrict__ y, int B, int C, int H, int W) {
+  extern __shared__ float sm[];   // [C][16] (kh, kw), bf16-rounded
+  for (int e = threadIdx.x; e < C * 16; e += blockDim.x) sm[e] = nm_rb(w[e]);
+  __syncthreads();
+  const float b0 = bias ? __ldg(bias) : 0.f;
+  const int64_t total = (int64_t)B * H * W;
+  const int OW = 2 * W;
+  for (int64_t m = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; m < total; m += (int64_t)gridDim.x * blockDim.x) {
+    const int j = (int)(m % W);
+    const int64_t t2 = m / W;
+    const int i = (int)(t2 % H), b = (int)(t2 / H);
+    float o00 = b0, o01 = b0, o10 = b0, o11 = b0;
+#pragma unroll
+    for (int dh = -1; dh <= 1; ++dh) {
+      const int ih = i + dh;
+      if ((unsigned)ih >= (unsigned)H) continue;
+#pragma unroll
+      for (int dw = -1; dw <= 1; ++dw) {
+        const int iw = j + dw;
+        if ((unsigned)iw >= (unsigned)W) continue;
+        const uint4* px = reinterpret_cast<const uint4*>(x + (((int64_t)b * H + ih) * W + iw) * C);
+        for (int c0 = 0; c0 < C; c0 += 8) {
+          const uint4 v = __ldg(px + (c0 >> 3));
+          const uint32_t u[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+          for (int k = 0; k < 8; ++k) {
+            const float xv = (k & 1) ? __uint_as_float(u[k >> 1] & 0xffff0000u) : __uint_as_float(u[k >> 1] << 16);
+            const float* wc = sm + (c0 + k) * 16;
+            // (ph, kh) pairs for this dh, (pw, kw) pairs for this dw -- resolved at compile time by the unrolling
+            if (dh <= 0 && dw <= 0) o00 = fmaf(xv, wc[(1 - 2 * dh) * 4 + (1 - 2 * dw)], o00);
+            if (dh <= 0 && dw >= 0) o01 = fmaf(xv, wc[(1 - 2 * dh) * 4 + (2 - 2 * dw)], o01);
+            if (dh >= 0 && dw <= 0) o10 = fmaf(xv, wc[(2 - 2 * dh) * 4 + (1 - 2 * dw)], o10);
+            if (dh >= 0 && dw >= 0) o11 = fmaf(xv, wc[(2 - 2 * dh) * 4 + (2 - 2 * dw)], o11);
+          }
+        }
+      }
+    }
+    float* yo = y + ((int64_t)b * 2 * H + 2 * i) * OW + 2 * j;
+    *reinterpret_cast<float2*>(yo) = make_float2(o00, o01);
+    *reinterpret_cast<float2*>(yo + OW) = make_float2(o10, o11);
+  }
+}
+
+// ---- weight gradients of the two single-channel ends from a bf16 NHWC tensor A [B][PH][PW][C] and the ONE-channel fp32
+// tensor S [B][SH][SW] it is correlated with (conv_direct.cu has the fp32-NCHW version):
+//   out[c][kh][kw] = sum_{b,i,j} A[b,i,j,c] * S[b, 2i-1+kh, 2j-1+kw]
+//   Conv2d(1 -> C) k3: A = g (output gradient), S = x;   ConvTranspose2d(C -> 1) k4: A = x (layer input), S = dy.
+// lane = channel (a warp owns 32 channels: one coalesced 64-byte read per pixel), a warp walks 32-pixel row segments: the
+// KS rows of S it needs (66..67 values each) are staged in shared memory once per segment, the taps of a pixel are two
+// 8-byte broadcast reads per row.  KS*KS register accumulators per lane over the warp's whole range, then a fixed-order
+// block / grid reduction in double.
+template <int KS>
+__global__ void __launch_bounds__(256)
+nm_tap_wgrad_kernel(const __nv_bfloat16* __restrict__ A, const float* __restrict__ S, double* __restrict__ part, int B, int C,
+                    int PH, int PW, int SH, int SW) {
+  constexpr int T = KS * KS, RW = 72;
+  __shared__ __align__(16) float srow[8][KS][RW];
+  __shared__ float red[8][32][T + 1];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int cg = blockIdx.y;
+  const int segs = PW >> 5;
+  const int64_t units = (int64_t)B * PH * segs;
+  float acc[T];
+#pragma unroll
+  for (int t = 0; t < T; ++t) acc[t] = 0.f;
+  for (int64_t u = (int64_t)blockIdx.x * 8 + warp; u < units; u += (int64_t)gridDim.x * 8) {
+    const int seg = (int)(u % segs);
+    const int64_t r = u / segs;
+    const int i = (int)(r % PH), b = (int)(r / PH), j0 = seg * 32;
+    const float* sb = S + (int64_t)b * SH * SW;
+    __syncwarp();
+#pragma unroll
+    for (int th = 0; th < KS; ++th) {
+      const int h = 2 * i - 1 + th;
+      const bool hok = (unsigned)h < (unsigned)SH;
+#pragma unroll
+      for (int k = 0; k < 3; ++k) {
+        const int idx = lane + 32 * k;            // srow[..][idx] = S[h][2*j0 - 1 + idx]
+        const int wcol = 2 * j0 - 1 + idx;
+        if (idx < 64 + KS - 1)
+          srow[warp][th][idx] = nm_rb(nm_ldg_pred(sb + (int64_t)h * SW + wcol, (hok && (unsigned)wcol < (unsigned)SW) ? 1u : 0u));
+      }
+    }
+    __syncwarp();
+    const __nv_bfloat16* ap = A + ((((int64_t)b * PH + i) * PW + j0) * C + cg * 32 + lane);
+#pragma unroll 4
+    for (int p = 0; p < 32; ++p) {
+      const float a = __bfloat162float(ap[(int64_t)p * C]);
+#pragma unroll
+      for (int th = 0; th < KS; ++th) {
+        const float2 s01 = *reinterpret_cast<const float2*>(&srow[warp][th][2 * p]);
+        acc[th * KS] = fmaf(a, s01.x, acc[th * KS]);
+        acc[th * KS + 1] = fmaf(a, s01.y, acc[th * KS + 1]);
+        if (KS == 3) {
+          acc[th * KS + 2] = fmaf(a, srow[warp][th][2 * p + 2], acc[th * KS + 2]);
+        } else {
+          const float2 s23 = *reinterpret_cast<const float2*>(&srow[warp][th][2 * p + 2]);
+          acc[th * KS + 2] = fmaf(a, s23.x, acc[th * KS + 2]);
+          acc[th * KS + 3] = fmaf(a, s23.y, acc[th * KS + 3]);
+        }
+      }
+    }
+  }
+#pragma unroll
+  for (int t = 0; t < T; ++t) red[warp][lane][t] = acc[t];
+  __syncthreads();
+  for (int e = threadIdx.x; e < 32 * T; e += blockDim.x) {
+    const int c = e / T, t = e - c * T;
+    double v = 0.0;
+#pragma unroll
+    for (int wq = 0; wq < 8; ++wq) v += (double)red[wq][c][t];
+    part[((int64_t)blockIdx.x * C + cg * 32 + c) * T + t] = v;
+  }
+}
+
+// out[e] = sum over blocks of part[blk][C*T]: eight warps per 32 outputs, sub-sums added in warp order
+__global__ void __launch_bounds__(256)
+nm_tap_fold_kernel(const double* __restrict__ part, int nblk, int n, float* __restrict__ out) {
+  __shared__ double sub[8][32];
+  const int lane = threadIdx.x & 31, g = threadIdx.x >> 5;
+  const int e = blockIdx.x * 32 + lane;
+  double v = 0.0;
+  if (e < n)
+    for (int b = g; b < nblk; b += 8) v += part[(int64_t)b * n + e];
+  sub[g][lane] = v;
+  __syncthreads();
+  if (g != 0 || e >= n) return;
+#pragma unroll
+  for (int i = 1; i < 8; ++i) v += sub[i][lane];
+  out[e] = (float)v;
+}
+constexpr int kTapBlocksNhwc = 148 * 4;
+
 static int nm_grid(int64_t total) {
   int64_t blocks = (total + 255) / 256;
   const int64_t cap = (int64_t)sm_count() * 8;
@@ -277,6 +415,47 @@ extern "C" int vc_nhwc_bias_grad(const void* g_nhwc, int64_t rows, int C, float*
       static_cast<const __nv_bfloat16*>(g_nhwc), rows, C, part);
   VC_LAUNCH_CHECK();
   nm_colsum_fold_kernel<<<(C + 31) / 32, 256, 0, as_stream(stream)>>>(part, grid, C, db);
+  VC_LAUNCH_CHECK();
+  return VC_OK;
+}
+
+extern "C" int vc_nhwc_convT1_fwd(const void* x_nhwc, const float* Wt, const float* bias, float* y, int B, int Cin, int H,
+                                  int W, void* stream) {
+  VC_REQUIRE(x_nhwc && Wt && y && B > 0 && H > 0 && W > 0, VC_ERR_BAD_ARG, "vc_nhwc_convT1_fwd: bad arguments");
+  VC_REQUIRE(Cin % 8 == 0 && Cin > 0 && Cin <= 512, VC_ERR_UNSUPPORTED, "vc_nhwc_convT1_fwd: Cin must be a multiple of 8, <= 512");
+  VC_REQUIRE((reinterpret_cast<uintptr_t>(x_nhwc) & 15) == 0 && (reinterpret_cast<uintptr_t>(y) & 7) == 0, VC_ERR_BAD_ARG,
+             "vc_nhwc_convT1_fwd: misaligned pointers");
+  nm_convT1_fwd_kernel<<<nm_grid((int64_t)B * H * W), 256, (size_t)16 * Cin * sizeof(float), as_stream(stream)>>>(
+      static_cast<const __nv_bfloat16*>(x_nhwc), Wt, bias, y, B, Cin, H, W);
+  VC_LAUNCH_CHECK();
+  return VC_OK;
+}
+
+extern "C" size_t vc_nhwc_tap_wgrad_workspace_bytes(int C, int KS) {
+  return (size_t)kTapBlocksNhwc * (C > 0 ? C : 1) * KS * KS * sizeof(double);
+}
+
+extern "C" int vc_nhwc_tap_wgrad(int KS, const void* a_nhwc, const float* S, float* dW, int B, int C, int PH, int PW,
+                                 void* workspace, size_t workspace_bytes, void* stream) {
+  VC_REQUIRE(a_nhwc && S && dW && B > 0 && PH > 0 && PW > 0, VC_ERR_BAD_ARG, "vc_nhwc_tap_wgrad: bad arguments");
+  VC_REQUIRE((KS == 3 || KS == 4) && C % 32 == 0 && C > 0 && C <= 512 && PW % 32 == 0, VC_ERR_UNSUPPORTED,
+             "vc_nhwc_tap_wgrad: need KS 3 or 4, C %% 32 == 0, row width %% 32 == 0 (got KS=%d C=%d PW=%d)", KS, C, PW);
+  VC_REQUIRE(workspace && workspace_bytes >= vc_nhwc_tap_wgrad_workspace_bytes(C, KS), VC_ERR_WORKSPACE,
+             "vc_nhwc_tap_wgrad: workspace too small");
+  const int64_t units = (int64_t)B * PH * (PW / 32);
+  int nblk = kTapBlocksNhwc / (C / 32);
+  if (nblk < 1) nblk = 1;
+  if ((int64_t)nblk * 8 > units) nblk = (int)((units + 7) / 8);
+  double* part = static_cast<double*>(workspace);
+  const dim3 grid(nblk, C / 32);
+  if (KS == 3)
+    nm_tap_wgrad_kernel<3><<<grid, 256, 0, as_stream(stream)>>>(static_cast<const __nv_bfloat16*>(a_nhwc), S, part, B, C, PH,
+                                                                   PW, 2 * PH, 2 * PW);
+  else
+    nm_tap_wgrad_kernel<4><<<grid, 256, 0, as_stream(stream)>>>(static_cast<const __nv_bfloat16*>(a_nhwc), S, part, B, C, PH,
+                                                                   PW, 2 * PH, 2 * PW);
+  VC_LAUNCH_CHECK();
+  nm_tap_fold_kernel<<<(C * KS * KS + 31) / 32, 256, 0, as_stream(stream)>>>(part, nblk, C * KS * KS, dW);
   VC_LAUNCH_CHECK();
   return VC_OK;
 }

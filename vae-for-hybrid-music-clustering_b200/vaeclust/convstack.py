@@ -18,6 +18,11 @@ from . import ops
 from ._lib import lib, ptr, stream_ptr
 
 ENABLED = True      # bf16 mode only; `supported()` decides per shape, anything else takes the per-layer path
+# The single-channel ends can also run on bf16 NHWC (vc_nhwc_convT1_fwd, vc_nhwc_tap_wgrad: no fp32 copies of the widest
+# activations at all), but measured on B200 those CUDA-core kernels are slower than the fp32-NCHW ones they replace
+# (deconv.4 forward 0.27 vs 0.115 ms, tap weight gradients 0.16 / 0.13 vs 0.09 / 0.12 ms), so the default keeps fp32 NCHW
+# at the two ends.
+ENDS_NHWC = False
 
 CONV_FWD, CONV_DGRAD, CONV_WGRAD, CONVT_FWD, CONVT_DGRAD, CONVT_WGRAD = 3, 4, 5, 6, 7, 8
 _BF = torch.bfloat16
@@ -37,6 +42,15 @@ def _wgrad(op, g, x, w, dims):
     dw = torch.empty_like(w)
     ws = ops._workspace(L.size("vc_conv_nhwc_wgrad_workspace_bytes", op, B, Cin, H, W, Cout), g.device)
     L.call("vc_conv_nhwc_wgrad", op, ptr(g), ptr(x), ptr(dw), B, Cin, H, W, Cout, ptr(ws), ws.numel(), stream_ptr())
+    return dw
+
+
+def _tap_wgrad(KS, a, S, w):
+    B, PH, PW, C = a.shape
+    L = lib()
+    dw = torch.empty_like(w)
+    ws = ops._workspace(L.size("vc_nhwc_tap_wgrad_workspace_bytes", C, KS), a.device)
+    L.call("vc_nhwc_tap_wgrad", KS, ptr(a), ptr(S), ptr(dw), B, C, PH, PW, ptr(ws), ws.numel(), stream_ptr())
     return dw
 
 
@@ -79,7 +93,7 @@ def encoder_supported(x, convs) -> bool:
         return False
     B, _, H, W = x.shape
     c1, c2, c3 = (c.weight.shape[0] for c in convs)
-    if H % 8 or W % 8 or c1 % 8 or convs[1].weight.shape[1] != c1 or convs[2].weight.shape[1] != c2:
+    if H % 8 or W % 8 or c1 % 32 or convs[1].weight.shape[1] != c1 or convs[2].weight.shape[1] != c2:
         return False
     d2, d3 = (B, c1, H // 2, W // 2, c2), (B, c2, H // 4, W // 4, c3)
     return _ok(("vc_conv_nhwc_supported", (CONV_FWD, *d2)), ("vc_conv_nhwc_supported", (CONV_FWD, *d3)),
@@ -93,7 +107,7 @@ def decoder_supported(h, deconvs) -> bool:
         return False
     B, C0, H, W = h.shape
     c1, c2, c3 = (d.weight.shape[1] for d in deconvs)
-    if c3 != 1 or C0 % 8 or W % 64 or deconvs[0].weight.shape[0] != C0 or c2 % 8:
+    if c3 != 1 or C0 % 8 or W % 64 or deconvs[0].weight.shape[0] != C0 or c2 % 32:
         return False
     d1, d2 = (B, C0, H, W, c1), (B, c1, 2 * H, 2 * W, c2)
     return _ok(("vc_conv_nhwc_supported", (CONVT_FWD, *d1)), ("vc_conv_nhwc_supported", (CONVT_FWD, *d2)),
@@ -142,14 +156,20 @@ class EncoderConvFn(torch.autograd.Function):
         _conv(CONV_DGRAD, g3n, w3, None, False, a2, g2n, None, d3)          # ReLU mask of a2 in the epilogue
         db2 = _bias_nhwc(g2n)
         dw2 = _wgrad(CONV_WGRAD, g2n, a1, w2, d2)
-        # conv1's gradient leaves the NHWC world: fp32 NCHW for the single-channel weight-gradient kernel
-        g1 = torch.empty((B, c1, H // 2, W // 2), dtype=torch.float32, device=dev)
-        _conv(CONV_DGRAD, g2n, w2, None, False, a1, None, g1, d2)
-        db1 = _bias_nchw(g1)
-        dw1 = torch.empty_like(w1)
-        ops._dense(CONV_WGRAD, 1, g1, x, None, dw1, B, 1, H, W, c1, False)
         dx = None
-        if ctx.needs_input_grad[0]:
+        if ENDS_NHWC:
+            g1n = torch.empty_like(a1)
+            _conv(CONV_DGRAD, g2n, w2, None, False, a1, g1n, None, d2)
+            db1 = _bias_nhwc(g1n)
+            dw1 = _tap_wgrad(3, g1n, x, w1)
+            g1 = g1n.float().permute(0, 3, 1, 2).contiguous() if ctx.needs_input_grad[0] else None
+        else:       # conv1's gradient leaves the NHWC world: fp32 NCHW for the single-channel weight-gradient kernel
+            g1 = torch.empty((B, c1, H // 2, W // 2), dtype=torch.float32, device=dev)
+            _conv(CONV_DGRAD, g2n, w2, None, False, a1, None, g1, d2)
+            db1 = _bias_nchw(g1)
+            dw1 = torch.empty_like(w1)
+            ops._dense(CONV_WGRAD, 1, g1, x, None, dw1, B, 1, H, W, c1, False)
+        if ctx.needs_input_grad[0]:      # not on the training path (x is data)
             dx = torch.empty_like(x)
             ops._dense(CONV_DGRAD, 1, g1, w1, None, dx, B, 1, H, W, c1, False)
         return dx, dw1, db1, dw2, db2, dw3, db3
@@ -170,10 +190,15 @@ class DecoderConvFn(torch.autograd.Function):
         d1n = _empty_nhwc(B, 2 * H, 2 * W, c1, dev)
         _conv(CONVT_FWD, d0n, w1, b1, True, None, d1n, None, (B, C0, H, W, c1))
         d2n = _empty_nhwc(B, 4 * H, 4 * W, c2, dev)
-        d2 = torch.empty((B, c2, 4 * H, 4 * W), dtype=torch.float32, device=dev)   # the single-channel end reads fp32 NCHW
-        _conv(CONVT_FWD, d1n, w2, b2, True, None, d2n, d2, (B, c1, 2 * H, 2 * W, c2))
         xhat = torch.empty((B, 1, 8 * H, 8 * W), dtype=torch.float32, device=dev)
-        ops._dense(CONVT_FWD, 1, d2, w3, b3, xhat, B, c2, 4 * H, 4 * W, 1, False)
+        if ENDS_NHWC:
+            d2 = None
+            _conv(CONVT_FWD, d1n, w2, b2, True, None, d2n, None, (B, c1, 2 * H, 2 * W, c2))
+            L.call("vc_nhwc_convT1_fwd", ptr(d2n), ptr(w3), ptr(b3), ptr(xhat), B, c2, 4 * H, 4 * W, stream_ptr())
+        else:       # the single-channel end reads fp32 NCHW: deconv2 writes both layouts
+            d2 = torch.empty((B, c2, 4 * H, 4 * W), dtype=torch.float32, device=dev)
+            _conv(CONVT_FWD, d1n, w2, b2, True, None, d2n, d2, (B, c1, 2 * H, 2 * W, c2))
+            ops._dense(CONVT_FWD, 1, d2, w3, b3, xhat, B, c2, 4 * H, 4 * W, 1, False)
         ctx.save_for_backward(d0n, d1n, d2n, d2, w1, w2, w3)
         ctx.dims = (B, C0, H, W)
         return xhat
@@ -188,8 +213,11 @@ class DecoderConvFn(torch.autograd.Function):
         L = lib()
         e1, e2 = (B, C0, H, W, c1), (B, c1, 2 * H, 2 * W, c2)
         db3 = _bias_nchw(dxhat)
-        dw3 = torch.empty_like(w3)
-        ops._dense(CONVT_WGRAD, 1, dxhat, d2, None, dw3, B, c2, 4 * H, 4 * W, 1, False)
+        if d2 is None:
+            dw3 = _tap_wgrad(4, d2n, dxhat, w3)
+        else:
+            dw3 = torch.empty_like(w3)
+            ops._dense(CONVT_WGRAD, 1, dxhat, d2, None, dw3, B, c2, 4 * H, 4 * W, 1, False)
         g2n = torch.empty_like(d2n)
         L.call("vc_nhwc_convT1_dgrad", ptr(dxhat), ptr(w3), ptr(d2n), ptr(g2n), B, c2, 4 * H, 4 * W, stream_ptr())
         db2 = _bias_nhwc(g2n)
