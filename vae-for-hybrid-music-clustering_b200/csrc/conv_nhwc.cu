@@ -244,100 +244,131 @@ conv_nhwc_kernel(const NhArgs a, const __grid_constant__ CUtensorMap mapA, const
       const int t = (int)blockIdx.x + tl * (int)gridDim.x;
       const int twi = t % a.tilesW, r = t / a.tilesW;
       const int pi = r % a.GH, pb = r / a.GH, pj = twi * NH_BM + row;
+      // output pixel(s) of this thread: one (non-quad) or the 2x2 block (quad)
+      const int64_t px0 = a.quad ? ((int64_t)pb * a.OH + 2 * pi) * a.OW + 2 * pj : ((int64_t)pb * a.OH + pi) * a.OW + pj;
+      // The ReLU mask of the layer below does not depend on the accumulator: fetch it for this thread's first two chunks
+      // BEFORE waiting for the main loop, so the ~1 us of memory latency hides under the MMAs of this tile (taken after the
+      // wait it was serial per chunk and made the phase-merged data gradients epilogue-bound: 144 vs 45 us).
+      uint4 mk[2][4];
+      if (a.mask) {
+#pragma unroll
+        for (int ci = 0; ci < 2; ++ci) {
+          const int cc = hh + 2 * ci;
+          if (cc < nchunks) {
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+              const int64_t off = a.quad ? (px0 + (u >> 1) * a.OW + (u & 1)) * a.OC + cc * 8 : px0 * a.OC + cc * 32 + u * 8;
+              mk[ci][u] = __ldg(reinterpret_cast<const uint4*>(a.mask + off));
+            }
+          }
+        }
+      }
       // one warp polls the accumulator barrier; the other seven park on a hardware named barrier (no issue slots)
       if (ew == 0) tma::mbar_wait_backoff(&t_full[as], aph, 128);
       asm volatile("bar.sync 1, 256;" ::: "memory");
       tc05::fence_after();
       const uint32_t tacc = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * a.BN);
-      for (int cc = hh; cc < nchunks; cc += 2) {
-        float v[32];
-        tc05::ld_32x32(tacc + cc * 32, v);
-        tc05::ld_wait();
-        if (cc + 2 >= nchunks) {  // last chunk of this thread: the accumulator stage is free once it sits in registers
-          tc05::fence_before();
-          tma::mbar_arrive(&t_empty[as]);
-        }
-        if (a.dbg & 4) continue;
-        if (!a.quad) {
-          const int c0 = cc * 32;
-          const int64_t px = ((int64_t)pb * a.OH + pi) * a.OW + pj;
-          if (a.bias) {
-            const float4* b4 = reinterpret_cast<const float4*>(a.bias + c0);
 #pragma unroll
-            for (int j4 = 0; j4 < 8; ++j4) {
-              const float4 bb = __ldg(b4 + j4);
-              v[4 * j4] += bb.x; v[4 * j4 + 1] += bb.y; v[4 * j4 + 2] += bb.z; v[4 * j4 + 3] += bb.w;
-            }
+      for (int ci = 0; ci < 4; ++ci) {
+        const int cc = hh + 2 * ci;
+        if (cc < nchunks) {
+          float v[32];
+          tc05::ld_32x32(tacc + cc * 32, v);
+          tc05::ld_wait();
+          if (cc + 2 >= nchunks) {  // last chunk of this thread: the accumulator stage is free once it sits in registers
+            tc05::fence_before();
+            tma::mbar_arrive(&t_empty[as]);
           }
-          if (a.relu) {
-#pragma unroll
-            for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.f);
-          }
+          if (a.dbg & 4) continue;
+          uint4 m4[4];
           if (a.mask) {
-            const uint4* m4 = reinterpret_cast<const uint4*>(a.mask + px * a.OC + c0);
 #pragma unroll
-            for (int j8 = 0; j8 < 4; ++j8) {
-              const uint4 mm = __ldg(m4 + j8);
-              const uint32_t mw[4] = {mm.x, mm.y, mm.z, mm.w};
-#pragma unroll
-              for (int u = 0; u < 4; ++u) {
-                v[8 * j8 + 2 * u] = nh_lo(mw[u]) > 0.f ? v[8 * j8 + 2 * u] : 0.f;
-                v[8 * j8 + 2 * u + 1] = nh_hi(mw[u]) > 0.f ? v[8 * j8 + 2 * u + 1] : 0.f;
+            for (int u = 0; u < 4; ++u) {
+              if (ci < 2) {
+                m4[u] = mk[ci][u];
+              } else {
+                const int64_t off = a.quad ? (px0 + (u >> 1) * a.OW + (u & 1)) * a.OC + cc * 8 : px0 * a.OC + cc * 32 + u * 8;
+                m4[u] = __ldg(reinterpret_cast<const uint4*>(a.mask + off));
               }
             }
           }
-          if (a.out_nhwc) {
-            uint4* o4 = reinterpret_cast<uint4*>(a.out_nhwc + px * a.OC + c0);
+          if (!a.quad) {
+            const int c0 = cc * 32;
+            if (a.bias) {
+              const float4* b4 = reinterpret_cast<const float4*>(a.bias + c0);
 #pragma unroll
-            for (int j8 = 0; j8 < 4; ++j8)
-              o4[j8] = make_uint4(nh_pack(v[8 * j8], v[8 * j8 + 1]), nh_pack(v[8 * j8 + 2], v[8 * j8 + 3]),
-                                  nh_pack(v[8 * j8 + 4], v[8 * j8 + 5]), nh_pack(v[8 * j8 + 6], v[8 * j8 + 7]));
-          }
-          if (a.out_nchw) {
-            float* o = a.out_nchw + ((int64_t)pb * a.OC + c0) * plane + (int64_t)pi * a.OW + pj;
-#pragma unroll
-            for (int j = 0; j < 32; ++j) o[j * plane] = v[j];
-          }
-        } else {
-          const int c0 = cc * 8;
-          const int oh = 2 * pi, ow = 2 * pj;
-          if (a.bias) {
-            const float4* b4 = reinterpret_cast<const float4*>(a.bias + c0);
-            const float4 b0 = __ldg(b4), b1 = __ldg(b4 + 1);
-            const float bj[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
-#pragma unroll
-            for (int g = 0; g < 8; ++g) {
-              v[4 * g] += bj[g]; v[4 * g + 1] += bj[g]; v[4 * g + 2] += bj[g]; v[4 * g + 3] += bj[g];
+              for (int j4 = 0; j4 < 8; ++j4) {
+                const float4 bb = __ldg(b4 + j4);
+                v[4 * j4] += bb.x; v[4 * j4 + 1] += bb.y; v[4 * j4 + 2] += bb.z; v[4 * j4 + 3] += bb.w;
+              }
             }
-          }
-          if (a.relu) {
+            if (a.relu) {
 #pragma unroll
-            for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.f);
-          }
-#pragma unroll
-          for (int p = 0; p < 4; ++p) {
-            const int64_t px = ((int64_t)pb * a.OH + oh + (p >> 1)) * a.OW + ow + (p & 1);
+              for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.f);
+            }
             if (a.mask) {
-              const uint4 mm = __ldg(reinterpret_cast<const uint4*>(a.mask + px * a.OC + c0));
-              const uint32_t mw[4] = {mm.x, mm.y, mm.z, mm.w};
 #pragma unroll
-              for (int u = 0; u < 4; ++u) {
-                v[4 * (2 * u) + p] = nh_lo(mw[u]) > 0.f ? v[4 * (2 * u) + p] : 0.f;
-                v[4 * (2 * u + 1) + p] = nh_hi(mw[u]) > 0.f ? v[4 * (2 * u + 1) + p] : 0.f;
+              for (int j8 = 0; j8 < 4; ++j8) {
+                const uint32_t mw[4] = {m4[j8].x, m4[j8].y, m4[j8].z, m4[j8].w};
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                  v[8 * j8 + 2 * u] = nh_lo(mw[u]) > 0.f ? v[8 * j8 + 2 * u] : 0.f;
+                  v[8 * j8 + 2 * u + 1] = nh_hi(mw[u]) > 0.f ? v[8 * j8 + 2 * u + 1] : 0.f;
+                }
               }
             }
-            if (a.out_nhwc)
-              *reinterpret_cast<uint4*>(a.out_nhwc + px * a.OC + c0) =
-                  make_uint4(nh_pack(v[p], v[4 + p]), nh_pack(v[8 + p], v[12 + p]), nh_pack(v[16 + p], v[20 + p]),
-                             nh_pack(v[24 + p], v[28 + p]));
-          }
-          if (a.out_nchw) {
-            float* o = a.out_nchw + ((int64_t)pb * a.OC + c0) * plane + (int64_t)oh * a.OW + ow;
+            if (a.out_nhwc) {
+              uint4* o4 = reinterpret_cast<uint4*>(a.out_nhwc + px0 * a.OC + c0);
 #pragma unroll
-            for (int g = 0; g < 8; ++g) {
-              float* r0 = o + g * plane;
-              *reinterpret_cast<float2*>(r0) = make_float2(v[4 * g], v[4 * g + 1]);
-              *reinterpret_cast<float2*>(r0 + a.OW) = make_float2(v[4 * g + 2], v[4 * g + 3]);
+              for (int j8 = 0; j8 < 4; ++j8)
+                o4[j8] = make_uint4(nh_pack(v[8 * j8], v[8 * j8 + 1]), nh_pack(v[8 * j8 + 2], v[8 * j8 + 3]),
+                                    nh_pack(v[8 * j8 + 4], v[8 * j8 + 5]), nh_pack(v[8 * j8 + 6], v[8 * j8 + 7]));
+            }
+            if (a.out_nchw) {
+              float* o = a.out_nchw + ((int64_t)pb * a.OC + c0) * plane + (int64_t)pi * a.OW + pj;
+#pragma unroll
+              for (int j = 0; j < 32; ++j) o[j * plane] = v[j];
+            }
+          } else {
+            const int c0 = cc * 8;
+            const int oh = 2 * pi, ow = 2 * pj;
+            if (a.bias) {
+              const float4* b4 = reinterpret_cast<const float4*>(a.bias + c0);
+              const float4 b0 = __ldg(b4), b1 = __ldg(b4 + 1);
+              const float bj[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+#pragma unroll
+              for (int g = 0; g < 8; ++g) {
+                v[4 * g] += bj[g]; v[4 * g + 1] += bj[g]; v[4 * g + 2] += bj[g]; v[4 * g + 3] += bj[g];
+              }
+            }
+            if (a.relu) {
+#pragma unroll
+              for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.f);
+            }
+#pragma unroll
+            for (int p = 0; p < 4; ++p) {
+              const int64_t px = px0 + (p >> 1) * a.OW + (p & 1);
+              if (a.mask) {
+                const uint32_t mw[4] = {m4[p].x, m4[p].y, m4[p].z, m4[p].w};
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                  v[4 * (2 * u) + p] = nh_lo(mw[u]) > 0.f ? v[4 * (2 * u) + p] : 0.f;
+                  v[4 * (2 * u + 1) + p] = nh_hi(mw[u]) > 0.f ? v[4 * (2 * u + 1) + p] : 0.f;
+                }
+              }
+              if (a.out_nhwc)
+                *reinterpret_cast<uint4*>(a.out_nhwc + px * a.OC + c0) =
+                    make_uint4(nh_pack(v[p], v[4 + p]), nh_pack(v[8 + p], v[12 + p]), nh_pack(v[16 + p], v[20 + p]),
+                               nh_pack(v[24 + p], v[28 + p]));
+            }
+            if (a.out_nchw) {
+              float* o = a.out_nchw + ((int64_t)pb * a.OC + c0) * plane + (int64_t)oh * a.OW + ow;
+#pragma unroll
+              for (int g = 0; g < 8; ++g) {
+                float* r0 = o + g * plane;
+                *reinterpret_cast<float2*>(r0) = make_float2(v[4 * g], v[4 * g + 1]);
+                *reinterpret_cast<float2*>(r0 + a.OW) = make_float2(v[4 * g + 2], v[4 * g + 3]);
+              }
             }
           }
         }
