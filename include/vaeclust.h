@@ -116,6 +116,12 @@ int vc_convT2d_s2k4_dgrad(const float* dy, const float* W, float* dx, int B, int
 int vc_convT2d_s2k4_wgrad(const float* dy, const float* x, float* dW, int B, int Cin, int H, int Wd, int Cout,
                           void* workspace, size_t workspace_bytes, void* stream);
 
+/* Weight AND bias gradient of nn.Conv2d(1, Cout, 3, 2, 1) (12:87) in one pass over dy [B,Cout,H/2,W/2] (fp32 NCHW) and
+ * x [B,1,H,W]: dW[co][kh][kw] = sum dy * x(tap), db[co] = sum dy.  round_bf16 = 1 rounds the multiplied operands as the
+ * tensor-core path does. */
+size_t vc_conv1_wgrad_bias_workspace_bytes(int Cout);
+int vc_conv1_wgrad_bias(const float* dy, const float* x, float* dW, float* db, int B, int H, int Wd, int Cout, int round_bf16,
+                        void* workspace, size_t workspace_bytes, void* stream);
 /* TMA-fed weight gradients of the same layers (csrc/conv_nhwc_wgrad.cu; autograd of nn.Conv2d / nn.ConvTranspose2d at
  * 12:87-89,135-137).  op = VC_OP_CONV_WGRAD or VC_OP_CONVT_WGRAD, (B, Cin, H, W, Cout) the layer's forward geometry;
  * g_nhwc = bf16 NHWC gradient of the layer's output (ReLU mask already applied), x_nhwc = bf16 NHWC layer input; dW in the
@@ -248,6 +254,15 @@ int vc_adam_multi_graph(const VcAdamChunk* table, int n_chunks, float lr, float 
 int vc_adam_tick(VcAdamDeviceStep* step_state, float beta1, float beta2, void* stream);
 int vc_adam_multi_at(const VcAdamChunk* table, int n_chunks, float lr, float beta1, float beta2, float eps,
                      const VcAdamDeviceStep* step_state, void* stream);
+/* Weight gradient of a wide nn.Linear (the two 67 M-parameter layers of 12:98-103,129-132) FUSED with its Adam update
+ * (12:233,270): dW = dy^T x is formed in tensor memory and applied to W / exp_avg / exp_avg_sq in the epilogue; the
+ * gradient is never written to memory.  Arithmetic order as vc_adam_multi.  step_state (device, advanced by vc_adam_tick)
+ * supplies the bias corrections when non-NULL, else bias_corr1 / bias_corr2 are used.  Single-process training only. */
+int vc_linear_wgrad_adam_supported(int B, int Cin, int Cout);
+size_t vc_linear_wgrad_adam_workspace_bytes(int B, int Cin, int Cout);
+int vc_linear_wgrad_adam(const float* dy, const float* x, float* W, float* exp_avg, float* exp_avg_sq, int B, int Cin,
+                         int Cout, float lr, float beta1, float beta2, float eps, float bias_corr1, float bias_corr2,
+                         const VcAdamDeviceStep* step_state, void* workspace, size_t workspace_bytes, void* stream);
 
 /* ------------------------------------------------------------------ fused MLP-VAE train step (scripts 19 / 06 / 22)
  * The whole optimisation step of MLPVAE (19:64-121 model, 19:226-232 step), of script 06's MLPVAE (06:145-188,

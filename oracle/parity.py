@@ -85,6 +85,11 @@ def vae_step_parity(model, step, kind: str, batch: Dict[str, torch.Tensor], beta
         args = (batch["x"], batch["c"])
     else:
         args = (batch["x"],)
+    # the per-parameter comparison needs every gradient: switch off the fused "weight gradient -> Adam" kernel of the wide
+    # Linear layers for this step (tests/test_gpu_models.py compares the fused update with the plain one separately)
+    for obj in (step, getattr(step, "step", None)):
+        if obj is not None and hasattr(obj, "fuse_fc_adam"):
+            obj.fuse_fc_adam = False
     stats = step(*args, eps=batch["eps"]).detach().cpu().numpy()
     torch.cuda.synchronize()
     if hasattr(step, "last_grads"):      # fused steps never materialise .grad; they expose a debug copy

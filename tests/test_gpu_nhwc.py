@@ -141,6 +141,16 @@ def test_single_channel_ends_and_helpers():
             wr = torch.zeros(C, 1, 4, 4, device="cuda", requires_grad=True)
             F.conv_transpose2d(_bf(a_t), wr, None, stride=2, padding=1).backward(_bf(S))
         torch.testing.assert_close(dwt, wr.grad, rtol=2e-5, atol=2e-5 * float(wr.grad.abs().max()))
+    # Conv2d(1 -> C) weight + bias gradient in one pass (fp32 NCHW dy)
+    dyc, xc = _r(B, C, H, W, seed=13), _r(B, 1, 2 * H, 2 * W, seed=14)
+    dwc, dbc = torch.full((C, 1, 3, 3), float("nan"), device="cuda"), torch.full((C,), float("nan"), device="cuda")
+    ws = torch.empty(L.size("vc_conv1_wgrad_bias_workspace_bytes", C), dtype=torch.uint8, device="cuda")
+    L.call("vc_conv1_wgrad_bias", ptr(dyc), ptr(xc), ptr(dwc), ptr(dbc), B, 2 * H, 2 * W, C, 1, ptr(ws), ws.numel(), stream_ptr())
+    wr = torch.zeros(C, 1, 3, 3, device="cuda", requires_grad=True)
+    F.conv2d(_bf(xc), wr, None, stride=2, padding=1).backward(_bf(dyc))
+    torch.testing.assert_close(dwc, wr.grad, rtol=2e-5, atol=2e-5 * float(wr.grad.abs().max()))
+    wantb = dyc.double().sum(dim=(0, 2, 3)).float()
+    torch.testing.assert_close(dbc, wantb, rtol=1e-5, atol=1e-5 * float(wantb.abs().max()) + 1e-4)
     # layout conversion
     src = _r(B, 128, 4, 128, seed=7)
     dst = torch.empty(B, 4, 128, 128, dtype=torch.bfloat16, device="cuda")
@@ -229,4 +239,47 @@ def test_conv_stacks_match_the_per_layer_path(ends_nhwc):
     finally:
         convstack.ENABLED = True
         convstack.ENDS_NHWC = False
+        ops.set_precision("fp32")
+
+
+@pytest.mark.parametrize("graphed", [False, True])
+def test_fused_fc_weight_gradient_adam_matches_plain_step(graphed, monkeypatch):
+    """vc_linear_wgrad_adam (the wide Linear weights updated from the weight-gradient kernel's accumulator, gradient never
+    written) against the ordinary wgrad + vc_adam_multi step: same arithmetic order, so parameters and moments after three
+    steps agree to fp32 summation order of the GEMM."""
+    from vaeclust import nn, ops, train
+    monkeypatch.setenv("VAECLUST_FUSE_FC_ADAM_NUMEL", str(1 << 22))     # 64 x 1024 model: FC layers are 65536 x 256
+    ops.set_precision("bf16")
+    try:
+        B = 64      # the skinny weight-gradient kernel wants the big operand to dominate: 65536 x 64 >= 2^22
+        x, lyr = _r(B, 1, 64, 1024, seed=1), _r(B, 384, seed=2)
+        m = torch.ones(B, 1, device="cuda")
+        eps = _r(B, 32, seed=3)
+        res = {}
+        for fuse in (False, True):
+            torch.manual_seed(0)
+            model = nn.ConvMultiModalVAE(1, (64, 1024), 32, 384).cuda()
+            if graphed:
+                step = train.GraphedVAEStep(model, "conv12", lr=2e-3, beta=1e-3, warmup=1)
+                step.step.fuse_fc_adam = fuse
+            else:
+                step = train.VAEStep(model, "conv12", lr=2e-3, beta=1e-3)
+                step.fuse_fc_adam = fuse
+            assert len((step.step if graphed else step)._wide) == 2
+            losses = [float(step(x, lyr, m, eps=eps)[0]) for _ in range(3)]
+            torch.cuda.synchronize()
+            opt = step.opt
+            wide = (step.step if graphed else step)._wide
+            res[fuse] = (losses, {k: p.detach().clone() for k, p in model.named_parameters()},
+                         [opt.state[id(p)]["exp_avg_sq"].clone() for p in wide],
+                         [p.grad is None for p in wide])
+        assert res[True][3] == [True, True] and res[False][3] == [False, False]
+        torch.testing.assert_close(torch.tensor(res[True][0]), torch.tensor(res[False][0]), rtol=1e-5, atol=0)
+        for k, p in res[False][1].items():
+            # (lr = 2e-3: where |g| is at Adam's eps = 1e-8 scale, m / (sqrt(v) + eps) amplifies a last-bit difference of the
+            #  contracted multiply-adds, so a handful of the 33 M elements differ by up to ~1e-3 of one update)
+            torch.testing.assert_close(res[True][1][k], p, rtol=1e-4, atol=1e-5, msg=lambda s, k=k: f"{k}: {s}")
+        for a, b in zip(res[True][2], res[False][2]):
+            torch.testing.assert_close(a, b, rtol=1e-4, atol=1e-12)
+    finally:
         ops.set_precision("fp32")

@@ -284,10 +284,10 @@ convT_to1_dgrad_kernel(const float* __restrict__ dy, const float* __restrict__ w
 // streaming reduction bound by reading A once (268 MB): thread = four horizontally adjacent pixels of CG channels,
 // A as one 16-byte load per channel, a row of S as two 16-byte loads plus halo scalars, CG*KS*KS register accumulators
 // kept across the thread's whole pixel range, then a fixed-order warp / grid reduction in double.
-template <int KS, int CG>
+template <int KS, int CG, bool BIAS>
 __global__ void __launch_bounds__(256, 2)
 tap_wgrad_kernel(const float* __restrict__ A, const float* __restrict__ S, double* __restrict__ part, int B, int C,
-                 int PH, int PW, int SH, int SW, int round_bf16) {
+                 int PH, int PW, int SH, int SW, int round_bf16, double* __restrict__ bpart) {
   constexpr int T = KS * KS, NS = KS + 6;
   // warp = channel group, lane = pixel quad: the eight warps of a block walk the SAME 32 quads, so the S patch (160 of
   // the 224 bytes a thread loads per step) comes from L2 once per block and from L1 for the other seven warps.  With
@@ -304,6 +304,9 @@ tap_wgrad_kernel(const float* __restrict__ A, const float* __restrict__ S, doubl
   for (int c = 0; c < CG; ++c)
 #pragma unroll
     for (int t = 0; t < T; ++t) acc[c][t] = 0.f;
+  float bsum[CG];   // per-channel sums of A (unrounded): the bias gradient when A is the output gradient (bpart != null)
+#pragma unroll
+  for (int c = 0; c < CG; ++c) bsum[c] = 0.f;
   for (int64_t m = (int64_t)blockIdx.x * 32 + lane; m < total; m += (int64_t)gridDim.x * 32) {
     const int pw0 = (int)(m % PW4) * 4;
     const int64_t t2 = m / PW4;
@@ -335,6 +338,7 @@ tap_wgrad_kernel(const float* __restrict__ A, const float* __restrict__ S, doubl
 #pragma unroll
     for (int c = 0; c < CG; ++c) {
       a[c][0] = av[c].x; a[c][1] = av[c].y; a[c][2] = av[c].z; a[c][3] = av[c].w;
+      if (BIAS) bsum[c] += (av[c].x + av[c].y) + (av[c].z + av[c].w);
       rb2(a[c][0], a[c][1], round_bf16);
       rb2(a[c][2], a[c][3], round_bf16);
     }
@@ -369,6 +373,15 @@ tap_wgrad_kernel(const float* __restrict__ A, const float* __restrict__ S, doubl
       for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
       if (lane == 0) pp[c * T + t] = (double)v;
     }
+  if (BIAS) {
+#pragma unroll
+    for (int c = 0; c < CG; ++c) {
+      float v = bsum[c];
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+      if (lane == 0) bpart[(int64_t)blockIdx.x * C + c0 + c] = (double)v;
+    }
+  }
 }
 
 // out[e] = sum over the nblk block partials part[blk][C*T].  A block owns 32 consecutive outputs; its eight warps each
@@ -408,10 +421,17 @@ bool conv_direct_wgrad_supported(int op, int B, int Cin, int H, int W, int Cout)
 }
 size_t conv_direct_wgrad_workspace(int op, int Cin, int Cout) {
   const int C = op == VC_OP_CONV_WGRAD ? Cout : Cin, T = op == VC_OP_CONV_WGRAD ? 9 : 16;
-  return sizeof(double) * (size_t)kTapBlocks * C * T;
+  return sizeof(double) * (size_t)kTapBlocks * C * (T + 1);   // + one column of bias-gradient partials
 }
+int conv_direct_wgrad_bias_run(int op, const float* dy, const float* x, float* dw, float* db, int B, int Cin, int H, int W,
+                               int Cout, int round_bf16, void* ws, size_t wsb, cudaStream_t s);
 int conv_direct_wgrad_run(int op, const float* dy, const float* x, float* dw, int B, int Cin, int H, int W, int Cout,
                           int round_bf16, void* ws, size_t wsb, cudaStream_t s) {
+  return conv_direct_wgrad_bias_run(op, dy, x, dw, nullptr, B, Cin, H, W, Cout, round_bf16, ws, wsb, s);
+}
+// db (Conv2d(1 -> C) only): the bias gradient sum(dy) from the same pass over dy (12:87)
+int conv_direct_wgrad_bias_run(int op, const float* dy, const float* x, float* dw, float* db, int B, int Cin, int H, int W,
+                               int Cout, int round_bf16, void* ws, size_t wsb, cudaStream_t s) {
   VC_REQUIRE(ws && wsb >= conv_direct_wgrad_workspace(op, Cin, Cout), VC_ERR_WORKSPACE,
              "conv_direct_wgrad_run: workspace too small");
   double* part = static_cast<double*>(ws);
@@ -422,16 +442,25 @@ int conv_direct_wgrad_run(int op, const float* dy, const float* x, float* dw, in
     const int OH = (H - 1) / 2 + 1, OW = W / 2, groups = Cout / CG;
     const int64_t quads = (int64_t)B * OH * (OW / 4);
     if ((int64_t)nblk * 32 > quads) nblk = (int)((quads + 31) / 32);
-    tap_wgrad_kernel<3, CG><<<dim3(nblk, (groups + 7) / 8), 256, 0, s>>>(dy, x, part, B, Cout, OH, OW, H, W, round_bf16);
+    double* bpart = db ? part + (size_t)kTapBlocks * Cout * T : nullptr;
+    if (db)
+      tap_wgrad_kernel<3, CG, true><<<dim3(nblk, (groups + 7) / 8), 256, 0, s>>>(dy, x, part, B, Cout, OH, OW, H, W, round_bf16, bpart);
+    else
+      tap_wgrad_kernel<3, CG, false><<<dim3(nblk, (groups + 7) / 8), 256, 0, s>>>(dy, x, part, B, Cout, OH, OW, H, W, round_bf16, nullptr);
     VC_LAUNCH_CHECK();
     tap_wgrad_fold_kernel<<<(Cout * T + 31) / 32, 256, 0, s>>>(part, nblk, Cout * T, dw);
+    if (db) {
+      VC_LAUNCH_CHECK();
+      tap_wgrad_fold_kernel<<<(Cout + 31) / 32, 256, 0, s>>>(bpart, nblk, Cout, db);
+    }
   } else {                        // A = x [B,Cin,H,W], S = dy [B,1,2H,2W]
     constexpr int CG = 4, T = 16;
     const int groups = Cin / CG;
     const int64_t quads = (int64_t)B * H * (W / 4);
     if ((int64_t)nblk * 32 > quads) nblk = (int)((quads + 31) / 32);
-    tap_wgrad_kernel<4, CG><<<dim3(nblk, (groups + 7) / 8), 256, 0, s>>>(x, dy, part, B, Cin, H, W, 2 * H, 2 * W,
-                                                                          round_bf16);
+    VC_REQUIRE(!db, VC_ERR_UNSUPPORTED, "conv_direct_wgrad_bias_run: the fused bias gradient exists for Conv2d(1 -> C) only");
+    tap_wgrad_kernel<4, CG, false><<<dim3(nblk, (groups + 7) / 8), 256, 0, s>>>(x, dy, part, B, Cin, H, W, 2 * H, 2 * W,
+                                                                          round_bf16, nullptr);
     VC_LAUNCH_CHECK();
     tap_wgrad_fold_kernel<<<(Cin * T + 31) / 32, 256, 0, s>>>(part, nblk, Cin * T, dw);
   }
@@ -479,3 +508,17 @@ int conv_direct_run(int op, const float* in0, const float* in1, const float* bia
 }
 
 }  // namespace vc
+
+using namespace vc;
+
+extern "C" size_t vc_conv1_wgrad_bias_workspace_bytes(int Cout) { return conv_direct_wgrad_workspace(VC_OP_CONV_WGRAD, 1, Cout); }
+
+extern "C" int vc_conv1_wgrad_bias(const float* dy, const float* x, float* dW, float* db, int B, int H, int W, int Cout,
+                                   int round_bf16, void* workspace, size_t workspace_bytes, void* stream) {
+  VC_REQUIRE(dy && x && dW && db && B > 0, VC_ERR_BAD_ARG, "vc_conv1_wgrad_bias: bad arguments");
+  VC_REQUIRE(conv_direct_wgrad_supported(VC_OP_CONV_WGRAD, B, 1, H, W, Cout) &&
+                 ((reinterpret_cast<uintptr_t>(dy) | reinterpret_cast<uintptr_t>(x)) & 15) == 0,
+             VC_ERR_UNSUPPORTED, "vc_conv1_wgrad_bias: need Cout %% 4 == 0, Cout <= 512, W %% 8 == 0, 16-byte aligned tensors");
+  return conv_direct_wgrad_bias_run(VC_OP_CONV_WGRAD, dy, x, dW, db, B, 1, H, W, Cout, round_bf16, workspace, workspace_bytes,
+                                    as_stream(stream));
+}

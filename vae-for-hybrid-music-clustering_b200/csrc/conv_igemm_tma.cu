@@ -235,7 +235,7 @@ relu_bwd_bias_nhwc_kernel(const float* __restrict__ dy, const float* __restrict_
       const int64_t o = base + (int64_t)c * plane + 2 * lane;
       const float2 d = *reinterpret_cast<const float2*>(dy + o), v = *reinterpret_cast<const float2*>(y + o);
       const float2 r2 = make_float2(v.x > 0.f ? d.x : 0.f, v.y > 0.f ? d.y : 0.f);
-      *reinterpret_cast<float2*>(g + o) = r2;
+      if (g) *reinterpret_cast<float2*>(g + o) = r2;
       tile[(2 * lane) * pitch + c] = __float2bfloat16_rn(r2.x);
       tile[(2 * lane + 1) * pitch + c] = __float2bfloat16_rn(r2.y);
       const float s = warp_sum(r2.x + r2.y);
@@ -382,7 +382,7 @@ extern "C" size_t vc_relu_bwd_bias_nhwc_workspace_bytes(int C) { return (size_t)
 
 extern "C" int vc_relu_bwd_bias_nhwc(const float* dy, const float* y, int B, int C, int H, int W, float* g, void* g_nhwc,
                                      float* db, void* workspace, size_t workspace_bytes, void* stream) {
-  VC_REQUIRE(dy && y && g && g_nhwc && db && B > 0 && H > 0, VC_ERR_BAD_ARG, "vc_relu_bwd_bias_nhwc: bad arguments");
+  VC_REQUIRE(dy && y && g_nhwc && db && B > 0 && H > 0, VC_ERR_BAD_ARG, "vc_relu_bwd_bias_nhwc: bad arguments");   // g may be null
   VC_REQUIRE(C % 8 == 0 && C <= 256 && W % RN_PX == 0, VC_ERR_UNSUPPORTED,
              "vc_relu_bwd_bias_nhwc: need C %% 8 == 0, C <= 256, W %% 64 == 0 (got C=%d W=%d)", C, W);
   VC_REQUIRE(((reinterpret_cast<uintptr_t>(dy) | reinterpret_cast<uintptr_t>(y) | reinterpret_cast<uintptr_t>(g)) & 7) == 0 &&

@@ -28,7 +28,21 @@ struct SkArgs {
   float* part;                               // split-K partials [nsplit][N][M] (transposed: coalesced), or null
   int nkb, kbs, stages;
   uint32_t idesc;
+  // fused Adam (weight-gradient ops only): `out` is the PARAMETER, updated in place from the accumulator; the gradient
+  // is never written (saves its 4 B/element write and the optimizer's 4 B/element read)
+  int adam;
+  float* ad_m; float* ad_v;
+  const VcAdamDeviceStep* ad_step;          // device-side bias corrections (CUDA-graph replay), or null: use ad_bc1/2
+  float ad_lr, ad_b1, ad_b2, ad_eps, ad_bc1, ad_bc2;
 };
+
+// torch.optim.Adam's arithmetic in the order adam_multi_kernel (misc.cu) uses, so fused and unfused steps agree
+__device__ __forceinline__ void sk_adam(float g, float& p, float& m, float& v, float b1, float b2, float step_size,
+                                        float inv_sqrt_bc2, float eps) {
+  m = b1 * m + (1.f - b1) * g;
+  v = b2 * v + (1.f - b2) * g * g;
+  p -= step_size * (m / (sqrtf(v) * inv_sqrt_bc2 + eps));
+}
 
 __device__ __forceinline__ uint32_t sk_pack(float a, float b) {
   __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
@@ -212,7 +226,7 @@ skinny_gemm_kernel(const SkArgs a, const __grid_constant__ CUtensorMap mapB) {
 #pragma unroll
         for (int j = 0; j < 32; ++j) v[j] = 0.f;
       }
-      if (m >= a.M) continue;
+      if (m >= a.M && !a.adam) continue;
       if (a.part) {
         float* o = a.part + ((int64_t)z * a.N + cc * 32) * a.M + m;
 #pragma unroll
@@ -225,7 +239,61 @@ skinny_gemm_kernel(const SkArgs a, const __grid_constant__ CUtensorMap mapB) {
         v[j] += bm;
         if (a.relu) v[j] = fmaxf(v[j], 0.f);
       }
-      if (a.transposed) {
+      if (a.adam) {
+        float bc1 = a.ad_bc1, bc2 = a.ad_bc2;
+        if (a.ad_step) { bc1 = a.ad_step->bias_corr1; bc2 = a.ad_step->bias_corr2; }
+        const float step_size = a.ad_lr / bc1, inv_sqrt_bc2 = 1.f / sqrtf(bc2);
+        // The warp's 32 (m) x 32 (n) block goes through shared memory (the operand ring is idle once the accumulator is
+        // complete) so that a lane owns FOUR consecutive elements of the contiguous direction: every p / m / v access is a
+        // 16-byte load or store, 512 bytes per warp instruction, and a batch of 12 loads is issued before its first store
+        // (the three arrays are distinct allocations, but the compiler cannot know and would serialise load -> store).
+        float* tb = reinterpret_cast<float*>(smem) + warp * (32 * 36);
+        __syncwarp();
+#pragma unroll
+        for (int j4 = 0; j4 < 8; ++j4)
+          *reinterpret_cast<float4*>(tb + lane * 36 + 4 * j4) = make_float4(v[4 * j4], v[4 * j4 + 1], v[4 * j4 + 2], v[4 * j4 + 3]);
+        __syncwarp();
+        const int sub = lane >> 3, l4 = (lane & 7) * 4;
+        const int64_t mrow0 = (int64_t)(m0 + q * 32);
+#pragma unroll
+        for (int hb = 0; hb < 32; hb += 16) {
+          float4 gg[4], pp[4], mm[4], vv[4];
+          int64_t off[4];
+          bool ok[4];
+#pragma unroll
+          for (int u = 0; u < 4; ++u) {
+            const int r = hb + 4 * u + sub;           // the strided index of this lane in group u
+            if (a.transposed) {                       // element (m, n) at n*ldo + m: contiguous in m; r is n, l4.. are m
+              gg[u] = make_float4(tb[(l4 + 0) * 36 + r], tb[(l4 + 1) * 36 + r], tb[(l4 + 2) * 36 + r], tb[(l4 + 3) * 36 + r]);
+              off[u] = (int64_t)(cc * 32 + r) * a.ldo + mrow0 + l4;
+              ok[u] = cc * 32 + r < a.N && mrow0 + l4 + 3 < a.M;
+            } else {                                  // element (m, n) at m*ldo + n: contiguous in n; r is m, l4.. are n
+              gg[u] = *reinterpret_cast<const float4*>(tb + r * 36 + l4);
+              off[u] = (mrow0 + r) * a.ldo + cc * 32 + l4;
+              ok[u] = mrow0 + r < a.M && cc * 32 + l4 + 3 < a.N;
+            }
+            const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+            pp[u] = ok[u] ? *reinterpret_cast<const float4*>(a.out + off[u]) : z;
+            mm[u] = ok[u] ? __ldcs(reinterpret_cast<const float4*>(a.ad_m + off[u])) : z;
+            vv[u] = ok[u] ? __ldcs(reinterpret_cast<const float4*>(a.ad_v + off[u])) : z;
+          }
+#pragma unroll
+          for (int u = 0; u < 4; ++u) {
+            sk_adam(gg[u].x, pp[u].x, mm[u].x, vv[u].x, a.ad_b1, a.ad_b2, step_size, inv_sqrt_bc2, a.ad_eps);
+            sk_adam(gg[u].y, pp[u].y, mm[u].y, vv[u].y, a.ad_b1, a.ad_b2, step_size, inv_sqrt_bc2, a.ad_eps);
+            sk_adam(gg[u].z, pp[u].z, mm[u].z, vv[u].z, a.ad_b1, a.ad_b2, step_size, inv_sqrt_bc2, a.ad_eps);
+            sk_adam(gg[u].w, pp[u].w, mm[u].w, vv[u].w, a.ad_b1, a.ad_b2, step_size, inv_sqrt_bc2, a.ad_eps);
+          }
+#pragma unroll
+          for (int u = 0; u < 4; ++u) {
+            if (ok[u]) {
+              *reinterpret_cast<float4*>(a.out + off[u]) = pp[u];
+              __stcs(reinterpret_cast<float4*>(a.ad_m + off[u]), mm[u]);
+              __stcs(reinterpret_cast<float4*>(a.ad_v + off[u]), vv[u]);
+            }
+          }
+        }
+      } else if (a.transposed) {
         float* o = a.out + (int64_t)(cc * 32) * a.ldo + m;
 #pragma unroll
         for (int j = 0; j < 32; ++j)
@@ -365,9 +433,23 @@ size_t skinny_gemm_workspace(int op, int B, int Cin, int Cout) {
   return sk_align((size_t)p.BN * p.Kp * 2) + (p.nsplit > 1 ? sk_align((size_t)p.nsplit * p.M * p.N * 4) : 0) + 2048;
 }
 
+struct SkAdam { float* m; float* v; const VcAdamDeviceStep* step; float lr, b1, b2, eps, bc1, bc2; };
+static int skinny_gemm_run_impl(int op, const float* in0, const float* in1, const float* bias, float* out, int B, int Cin,
+                                int Cout, int relu, void* ws, size_t wsb, cudaStream_t s, const SkAdam* adam);
+
 int skinny_gemm_run(int op, const float* in0, const float* in1, const float* bias, float* out, int B, int Cin, int Cout,
                     int relu, void* ws, size_t wsb, cudaStream_t s) {
+  return skinny_gemm_run_impl(op, in0, in1, bias, out, B, Cin, Cout, relu, ws, wsb, s, nullptr);
+}
+
+static int skinny_gemm_run_impl(int op, const float* in0, const float* in1, const float* bias, float* out, int B, int Cin,
+                                int Cout, int relu, void* ws, size_t wsb, cudaStream_t s, const SkAdam* adam) {
   const SkPlan p = sk_plan(op, B, Cin, Cout, in0, in1);
+  if (adam) VC_REQUIRE(p.ok && p.nsplit == 1 && op == VC_OP_LINEAR_WGRAD && p.M % 4 == 0 && p.N % 4 == 0 && p.ldo % 4 == 0 &&
+                           ((reinterpret_cast<uintptr_t>(out) | reinterpret_cast<uintptr_t>(adam->m) |
+                             reinterpret_cast<uintptr_t>(adam->v)) & 15) == 0,
+                       VC_ERR_UNSUPPORTED, "skinny_gemm: the fused Adam epilogue needs an unsplit weight-gradient shape, "
+                       "dimensions that are multiples of 4 and 16-byte aligned tensors");
   VC_REQUIRE(p.ok, VC_ERR_UNSUPPORTED, "skinny_gemm: unsupported shape");
   VC_REQUIRE(ws && wsb >= skinny_gemm_workspace(op, B, Cin, Cout), VC_ERR_WORKSPACE, "skinny_gemm: workspace too small");
   unsigned char* w = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(ws) + 1023) & ~(uintptr_t)1023);
@@ -404,7 +486,14 @@ int skinny_gemm_run(int op, const float* in0, const float* in1, const float* bia
   a.bias = p.has_bias ? bias : nullptr; a.relu = relu;
   a.part = part; a.nkb = p.nkb; a.kbs = p.kbs; a.stages = p.stages;
   a.idesc = tc05::idesc(tc05::kFmtBF16, 128, p.BN, 0, 0);
-  const size_t smem = (size_t)p.stages * (SK_A_BYTES + (size_t)p.BN * 128) + (2 * p.stages + 1) * 8 + 16 + 1024;
+  size_t ring = (size_t)p.stages * (SK_A_BYTES + (size_t)p.BN * 128);
+  if (adam) {
+    a.adam = 1; a.ad_m = adam->m; a.ad_v = adam->v; a.ad_step = adam->step;
+    a.ad_lr = adam->lr; a.ad_b1 = adam->b1; a.ad_b2 = adam->b2; a.ad_eps = adam->eps; a.ad_bc1 = adam->bc1; a.ad_bc2 = adam->bc2;
+    // the non-transposed epilogue transposes 8 x (32 x 33) floats through the operand ring; the barriers sit behind it
+    VC_REQUIRE(ring >= 8 * 32 * 36 * 4, VC_ERR_UNSUPPORTED, "skinny_gemm: operand ring too small for the Adam epilogue");
+  }
+  const size_t smem = ring + (2 * p.stages + 1) * 8 + 16 + 1024;
   VC_CUDA(cudaFuncSetAttribute(skinny_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   dim3 grid((unsigned)((p.M + 127) / 128), (unsigned)p.nsplit);
   skinny_gemm_kernel<<<grid, SK_THREADS, smem, s>>>(a, mb);
@@ -418,3 +507,26 @@ int skinny_gemm_run(int op, const float* in0, const float* in1, const float* bia
 }
 
 }  // namespace vc
+
+using namespace vc;
+
+extern "C" int vc_linear_wgrad_adam_supported(int B, int Cin, int Cout) {
+  const SkPlan p = sk_plan(VC_OP_LINEAR_WGRAD, B, Cin, Cout, nullptr, nullptr);
+  return (p.ok && p.nsplit == 1 && p.M % 4 == 0 && p.N % 4 == 0 && (size_t)p.stages * (SK_A_BYTES + (size_t)p.BN * 128) >= 8 * 32 * 36 * 4) ? 1 : 0;
+}
+
+extern "C" size_t vc_linear_wgrad_adam_workspace_bytes(int B, int Cin, int Cout) {
+  return skinny_gemm_workspace(VC_OP_LINEAR_WGRAD, B, Cin, Cout);
+}
+
+extern "C" int vc_linear_wgrad_adam(const float* dy, const float* x, float* W, float* exp_avg, float* exp_avg_sq, int B,
+                                    int Cin, int Cout, float lr, float beta1, float beta2, float eps, float bias_corr1,
+                                    float bias_corr2, const VcAdamDeviceStep* step_state, void* workspace,
+                                    size_t workspace_bytes, void* stream) {
+  VC_REQUIRE(dy && x && W && exp_avg && exp_avg_sq, VC_ERR_BAD_ARG, "vc_linear_wgrad_adam: null pointer");
+  VC_REQUIRE(vc_linear_wgrad_adam_supported(B, Cin, Cout), VC_ERR_UNSUPPORTED,
+             "vc_linear_wgrad_adam: unsupported shape (B %d, Cin %d, Cout %d)", B, Cin, Cout);
+  SkAdam ad = {exp_avg, exp_avg_sq, step_state, lr, beta1, beta2, eps, bias_corr1, bias_corr2};
+  return skinny_gemm_run_impl(VC_OP_LINEAR_WGRAD, dy, x, nullptr, W, B, Cin, Cout, 0, workspace, workspace_bytes,
+                              as_stream(stream), &ad);
+}

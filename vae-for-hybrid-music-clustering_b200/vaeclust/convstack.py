@@ -145,11 +145,10 @@ class EncoderConvFn(torch.autograd.Function):
         s = stream_ptr()
         d2, d3 = (B, c1, H // 2, W // 2, c2), (B, c2, H // 4, W // 4, c3)
         # conv3: g3 = da3 * (a3 > 0) as bf16 NHWC (+ db3) from the fp32 NCHW pair the fully connected layer exchanges
-        g3 = torch.empty_like(a3)
         g3n = _empty_nhwc(B, H // 8, W // 8, c3, dev)
         db3 = torch.empty(c3, dtype=torch.float32, device=dev)
         ws = ops._workspace(L.size("vc_relu_bwd_bias_nhwc_workspace_bytes", c3), dev)
-        L.call("vc_relu_bwd_bias_nhwc", ptr(da3), ptr(a3), B, c3, H // 8, W // 8, ptr(g3), ptr(g3n), ptr(db3), ptr(ws),
+        L.call("vc_relu_bwd_bias_nhwc", ptr(da3), ptr(a3), B, c3, H // 8, W // 8, None, ptr(g3n), ptr(db3), ptr(ws),
                ws.numel(), s)
         dw3 = _wgrad(CONV_WGRAD, g3n, a2, w3, d3)
         g2n = torch.empty_like(a2)
@@ -166,9 +165,10 @@ class EncoderConvFn(torch.autograd.Function):
         else:       # conv1's gradient leaves the NHWC world: fp32 NCHW for the single-channel weight-gradient kernel
             g1 = torch.empty((B, c1, H // 2, W // 2), dtype=torch.float32, device=dev)
             _conv(CONV_DGRAD, g2n, w2, None, False, a1, None, g1, d2)
-            db1 = _bias_nchw(g1)
             dw1 = torch.empty_like(w1)
-            ops._dense(CONV_WGRAD, 1, g1, x, None, dw1, B, 1, H, W, c1, False)
+            db1 = torch.empty(c1, dtype=torch.float32, device=dev)
+            ws = ops._workspace(L.size("vc_conv1_wgrad_bias_workspace_bytes", c1), dev)
+            L.call("vc_conv1_wgrad_bias", ptr(g1), ptr(x), ptr(dw1), ptr(db1), B, H, W, c1, 1, ptr(ws), ws.numel(), s)
         if ctx.needs_input_grad[0]:      # not on the training path (x is data)
             dx = torch.empty_like(x)
             ops._dense(CONV_DGRAD, 1, g1, w1, None, dx, B, 1, H, W, c1, False)

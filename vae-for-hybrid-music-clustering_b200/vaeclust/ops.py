@@ -93,6 +93,10 @@ class _DenseFn(torch.autograd.Function):
         y = torch.empty(yshape, dtype=torch.float32, device=x.device)
         _dense(_OPS[kind][0], prec, x, weight, bias, y, B, Cin, H, W, Cout, relu)
         ctx.kind, ctx.prec, ctx.relu, ctx.has_bias = kind, prec, bool(relu), bias is not None
+        # single-GPU training: the optimizer that wants this (wide Linear) weight updated straight from the
+        # weight-gradient kernel's accumulator (train.VAEStep sets and clears the attribute around a step)
+        ctx.adam = getattr(weight, "_vc_adam", None) if kind == "linear" else None
+        ctx.wparam = weight if ctx.adam is not None else None
         ctx.dims = (B, Cin, H, W, Cout)
         ctx.save_for_backward(x, weight, y if relu else None)
         return y
@@ -148,13 +152,34 @@ class _DenseFn(torch.autograd.Function):
             dx = torch.empty_like(x)
             _dense(op_d, ctx.prec, g, weight, None, dx, B, Cin, H, W, Cout, False)
         if ctx.needs_input_grad[2]:
-            dw = torch.empty_like(weight)
-            _dense(op_w, ctx.prec, g, x, None, dw, B, Cin, H, W, Cout, False)
+            if (ctx.adam is not None and ctx.prec == _PREC["bf16"]
+                    and lib().size("vc_linear_wgrad_adam_supported", B, Cin, Cout)):
+                _linear_wgrad_adam(ctx.adam, ctx.wparam, g, x, B, Cin, Cout)      # no dW: the update happens here
+            else:
+                dw = torch.empty_like(weight)
+                _dense(op_w, ctx.prec, g, x, None, dw, B, Cin, H, W, Cout, False)
         if want_db:
             db = torch.empty(Cout, dtype=torch.float32, device=x.device)
             ws = _workspace(lib().size("vc_bias_grad_workspace_bytes", Cout), x.device)
             lib().call("vc_bias_grad", ptr(g), B, Cout, inner, ptr(db), 0, ptr(ws), ws.numel(), s)
         return None, dx, dw, db, None
+
+
+def _linear_wgrad_adam(opt, p, g, x, B, Cin, Cout) -> None:
+    """dW = g^T x formed in tensor memory and applied to p / exp_avg / exp_avg_sq by the same kernel
+    (vc_linear_wgrad_adam); the optimizer's later step() skips p because its .grad stays None."""
+    st = opt._state(p)
+    b1, b2 = opt.betas
+    if opt.capturable:
+        if not opt._ticked:
+            raise VaeclustError("fused Linear weight update: Adam.begin_step() must run before backward")
+        step_ptr, bc1, bc2 = ptr(opt.device_step()), 1.0, 1.0
+    else:
+        st["step"] += 1
+        step_ptr, bc1, bc2 = None, 1.0 - b1 ** st["step"], 1.0 - b2 ** st["step"]
+    ws = _workspace(lib().size("vc_linear_wgrad_adam_workspace_bytes", B, Cin, Cout), x.device)
+    lib().call("vc_linear_wgrad_adam", ptr(g), ptr(x), ptr(p.data), ptr(st["exp_avg"]), ptr(st["exp_avg_sq"]), B, Cin, Cout,
+               float(opt.param_groups[0]["lr"]), b1, b2, opt.eps, bc1, bc2, step_ptr, ptr(ws), ws.numel(), stream_ptr())
 
 
 def linear(x, weight, bias=None, relu: bool = False):

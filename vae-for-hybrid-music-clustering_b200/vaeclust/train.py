@@ -58,6 +58,12 @@ class VAEStep:
 
     def __init__(self, model, kind: str, lr: float, beta: float, group=None, capturable: bool = False):
         self.model, self.kind, self.beta, self.group = model, kind, float(beta), group
+        # single GPU, bf16 mode: the wide Linear weights (>= 2^24 elements: the two 67 M-parameter layers of script 12) are
+        # updated by their weight-gradient kernel itself (ops._linear_wgrad_adam); their .grad is never materialised.
+        # Set `fuse_fc_adam = False` (or VAECLUST_FUSE_FC_ADAM=0) to get ordinary gradients, e.g. to inspect them.
+        self.fuse_fc_adam = os.environ.get("VAECLUST_FUSE_FC_ADAM", "1") != "0"
+        wide = int(os.environ.get("VAECLUST_FUSE_FC_ADAM_NUMEL", str(1 << 24)))
+        self._wide = [m.weight for m in model.modules() if isinstance(m, torch.nn.Linear) and m.weight.numel() >= wide]
         self.mode = VC_LOSS_SUM_MEAN if kind == "mlp19" else VC_LOSS_MEAN_MEAN
         self.multi = group is not None and vdist.world_size(group) > 1
         self.opt = Adam(model.parameters(), lr=lr, capturable=capturable)
@@ -76,11 +82,24 @@ class VAEStep:
         """`local_rows` overrides the weight of this rank's contribution (default: x.shape[0]); a rank whose shard of
         the last batch is empty passes one dummy row with local_rows=0 so that it still takes part in the collectives."""
         m = self.model
+        fused = []
         if self.sync is not None:
             rows = x.shape[0] if local_rows is None else int(local_rows)
             self.sync.begin(rows, global_batch or x.shape[0] * vdist.world_size(self.group))
         else:
             self.opt.zero_grad()
+            if self.fuse_fc_adam and self._wide and ops.PRECISION == "bf16":
+                fused = self._wide
+                self.opt.begin_step()            # capturable: the device step counter advances here, once
+                for p in fused:
+                    p._vc_adam = self.opt
+        try:
+            return self._run(m, x, extra, eps, fused)
+        finally:
+            for p in fused:
+                p._vc_adam = None
+
+    def _run(self, m, x, extra, eps, fused):
         if self.kind == "conv12":
             lyr, mask = extra
             mu, lv = m.encode(x, lyr, mask)
