@@ -266,15 +266,18 @@ def test_fused_fc_weight_gradient_adam_matches_plain_step(graphed, monkeypatch):
                 step = train.VAEStep(model, "conv12", lr=2e-3, beta=1e-3)
                 step.fuse_fc_adam = fuse
             assert len((step.step if graphed else step)._wide) == 2
-            losses = [float(step(x, lyr, m, eps=eps)[0]) for _ in range(3)]
+            losses = [float(step(x, lyr, m, eps=eps)[0])]
             torch.cuda.synchronize()
             opt = step.opt
             wide = (step.step if graphed else step)._wide
-            res[fuse] = (losses, {k: p.detach().clone() for k, p in model.named_parameters()},
-                         [opt.state[id(p)]["exp_avg_sq"].clone() for p in wide],
-                         [p.grad is None for p in wide])
+            # parameters and moments after ONE step (later steps start from last-bit-different weights and Adam's
+            # m / (sqrt(v) + eps) amplifies that for near-zero gradients); the loss curve over three
+            snap = ({k: p.detach().clone() for k, p in model.named_parameters()},
+                    [opt.state[id(p)]["exp_avg_sq"].clone() for p in wide], [p.grad is None for p in wide])
+            losses += [float(step(x, lyr, m, eps=eps)[0]) for _ in range(2)]
+            res[fuse] = (losses,) + snap
         assert res[True][3] == [True, True] and res[False][3] == [False, False]
-        torch.testing.assert_close(torch.tensor(res[True][0]), torch.tensor(res[False][0]), rtol=1e-5, atol=0)
+        torch.testing.assert_close(torch.tensor(res[True][0]), torch.tensor(res[False][0]), rtol=1e-4, atol=0)
         for k, p in res[False][1].items():
             # (lr = 2e-3: where |g| is at Adam's eps = 1e-8 scale, m / (sqrt(v) + eps) amplifies a last-bit difference of the
             #  contracted multiply-adds, so a handful of the 33 M elements differ by up to ~1e-3 of one update)

@@ -214,38 +214,68 @@ conv_igemm_tma_kernel(const ItArgs a, const __grid_constant__ CUtensorMap mapA, 
 // the per-channel sums (bias gradient), in one pass over dy / y: 12 B/element of mandatory traffic + 2 B for the copy.
 // A block walks [64-pixel row segment] x [all channels] tiles; the transposition goes through shared memory.
 constexpr int RN_PX = 64;
+// PX = pixels per tile: 64 (8-byte loads, two pixels per lane) or 128 (16-byte loads, four per lane; needs W % 128 == 0)
+template <int PX>
 __global__ void __launch_bounds__(256)
 relu_bwd_bias_nhwc_kernel(const float* __restrict__ dy, const float* __restrict__ y, float* __restrict__ g,
                           __nv_bfloat16* __restrict__ gn, int B, int C, int H, int W, int ntiles,
                           double* __restrict__ part) {
   extern __shared__ unsigned char rn_smem[];
+  constexpr int PL = PX / 32;                                           // pixels per lane
   const int pitch = C + 8;                                              // bf16 elements per pixel row (16-byte multiple)
-  __nv_bfloat16* tile = reinterpret_cast<__nv_bfloat16*>(rn_smem);      // [RN_PX][pitch]
-  double* csum = reinterpret_cast<double*>(rn_smem + (size_t)RN_PX * pitch * 2);   // [C]
+  __nv_bfloat16* tile = reinterpret_cast<__nv_bfloat16*>(rn_smem);      // [PX][pitch]
+  double* csum = reinterpret_cast<double*>(rn_smem + (size_t)PX * pitch * 2);   // [C]
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   for (int c = threadIdx.x; c < C; c += blockDim.x) csum[c] = 0.0;
   __syncthreads();
-  const int segs = W / RN_PX;
+  const int segs = W / PX;
   const int64_t plane = (int64_t)H * W;
   for (int t = blockIdx.x; t < ntiles; t += gridDim.x) {
     const int seg = t % segs, r = t / segs;
     const int h = r % H, b = r / H;
-    const int64_t base = ((int64_t)b * C) * plane + (int64_t)h * W + seg * RN_PX;
-    for (int c = warp; c < C; c += 8) {      // a warp takes whole channel rows: 64 pixels = 2 per lane, coalesced
-      const int64_t o = base + (int64_t)c * plane + 2 * lane;
-      const float2 d = *reinterpret_cast<const float2*>(dy + o), v = *reinterpret_cast<const float2*>(y + o);
-      const float2 r2 = make_float2(v.x > 0.f ? d.x : 0.f, v.y > 0.f ? d.y : 0.f);
-      if (g) *reinterpret_cast<float2*>(g + o) = r2;
-      tile[(2 * lane) * pitch + c] = __float2bfloat16_rn(r2.x);
-      tile[(2 * lane + 1) * pitch + c] = __float2bfloat16_rn(r2.y);
-      const float s = warp_sum(r2.x + r2.y);
-      if (lane == 0) csum[c] += (double)s;   // channel c is always handled by this warp: no race, fixed order
+    const int64_t base = ((int64_t)b * C) * plane + (int64_t)h * W + seg * PX;
+    for (int c0 = warp; c0 < C; c0 += 16) {      // two channel rows per pass: four independent loads in flight per lane
+      float d[2][PL], v[2][PL];
+#pragma unroll
+      for (int k = 0; k < 2; ++k) {
+        const int c = c0 + 8 * k;
+        const int64_t o = base + (int64_t)c * plane + PL * lane;
+        if (c < C) {
+          if (PL == 4) {
+            const float4 dd = __ldcs(reinterpret_cast<const float4*>(dy + o)), vv = __ldcs(reinterpret_cast<const float4*>(y + o));
+            d[k][0] = dd.x; d[k][1] = dd.y; d[k][PL - 2] = dd.z; d[k][PL - 1] = dd.w;
+            v[k][0] = vv.x; v[k][1] = vv.y; v[k][PL - 2] = vv.z; v[k][PL - 1] = vv.w;
+          } else {
+            const float2 dd = __ldcs(reinterpret_cast<const float2*>(dy + o)), vv = __ldcs(reinterpret_cast<const float2*>(y + o));
+            d[k][0] = dd.x; d[k][1] = dd.y; v[k][0] = vv.x; v[k][1] = vv.y;
+          }
+        }
+      }
+#pragma unroll
+      for (int k = 0; k < 2; ++k) {
+        const int c = c0 + 8 * k;
+        if (c >= C) continue;
+        const int64_t o = base + (int64_t)c * plane + PL * lane;
+        float s = 0.f;
+#pragma unroll
+        for (int u = 0; u < PL; ++u) {
+          d[k][u] = v[k][u] > 0.f ? d[k][u] : 0.f;
+          s += d[k][u];
+          tile[(PL * lane + u) * pitch + c] = __float2bfloat16_rn(d[k][u]);
+        }
+        if (g) {
+          if (PL == 4) *reinterpret_cast<float4*>(g + o) = make_float4(d[k][0], d[k][1], d[k][PL - 2], d[k][PL - 1]);
+          else *reinterpret_cast<float2*>(g + o) = make_float2(d[k][0], d[k][1]);
+        }
+        s = warp_sum(s);
+        if (lane == 0) csum[c] += (double)s;   // channel c is always handled by this warp: no race, fixed order
+      }
     }
     __syncthreads();
-    // the tile's 64 pixels x C channels are one contiguous block of the NHWC tensor
-    __nv_bfloat16* dst = gn + (((int64_t)b * H + h) * W + seg * RN_PX) * C;
+    // the tile's PX pixels x C channels are one contiguous block of the NHWC tensor
+    __nv_bfloat16* dst = gn + (((int64_t)b * H + h) * W + seg * PX) * C;
     const int vec_per_px = C / 8;
-    for (int e = threadIdx.x; e < RN_PX * vec_per_px; e += blockDim.x) {
+    for (int e = threadIdx.x; e < PX * vec_per_px; e += blockDim.x) {
       const int px = e / vec_per_px, q = e - px * vec_per_px;
       reinterpret_cast<uint4*>(dst)[e] = *reinterpret_cast<const uint4*>(tile + px * pitch + q * 8);
     }
@@ -389,14 +419,22 @@ extern "C" int vc_relu_bwd_bias_nhwc(const float* dy, const float* y, int B, int
                  (reinterpret_cast<uintptr_t>(g_nhwc) & 15) == 0, VC_ERR_BAD_ARG, "vc_relu_bwd_bias_nhwc: misaligned pointers");
   int grid = 4 * sm_count();
   if (grid > 4 * 148) grid = 4 * 148;
-  const int64_t ntiles = (int64_t)B * H * (W / RN_PX);
+  const bool wide = W % 128 == 0 && ((reinterpret_cast<uintptr_t>(dy) | reinterpret_cast<uintptr_t>(y) | reinterpret_cast<uintptr_t>(g)) & 15) == 0;
+  const int PX = wide ? 128 : RN_PX;
+  const int64_t ntiles = (int64_t)B * H * (W / PX);
   VC_REQUIRE(ntiles < 2147483647LL, VC_ERR_UNSUPPORTED, "vc_relu_bwd_bias_nhwc: tensor too large");
   if (grid > ntiles) grid = (int)ntiles;
   VC_REQUIRE(workspace && workspace_bytes >= (size_t)grid * C * 8, VC_ERR_WORKSPACE, "vc_relu_bwd_bias_nhwc: workspace too small");
   double* part = static_cast<double*>(workspace);
-  const size_t smem = (size_t)RN_PX * (C + 8) * 2 + (size_t)C * 8;
-  relu_bwd_bias_nhwc_kernel<<<grid, 256, smem, as_stream(stream)>>>(dy, y, g, static_cast<__nv_bfloat16*>(g_nhwc), B, C, H,
-                                                                    W, (int)ntiles, part);
+  const size_t smem = (size_t)PX * (C + 8) * 2 + (size_t)C * 8;
+  if (wide) {
+    VC_CUDA(cudaFuncSetAttribute(relu_bwd_bias_nhwc_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    relu_bwd_bias_nhwc_kernel<128><<<grid, 256, smem, as_stream(stream)>>>(dy, y, g, static_cast<__nv_bfloat16*>(g_nhwc), B, C,
+                                                                            H, W, (int)ntiles, part);
+  } else {
+    relu_bwd_bias_nhwc_kernel<64><<<grid, 256, smem, as_stream(stream)>>>(dy, y, g, static_cast<__nv_bfloat16*>(g_nhwc), B, C,
+                                                                           H, W, (int)ntiles, part);
+  }
   VC_LAUNCH_CHECK();
   rn_fold_kernel<<<(C + 127) / 128, 128, 0, as_stream(stream)>>>(part, grid, C, db);
   VC_LAUNCH_CHECK();

@@ -23,7 +23,8 @@
 namespace vc {
 
 constexpr int NH_BM = 128;
-constexpr int NH_EPI = 256;
+constexpr int NH_EPI = 256;                      // epilogue threads of the one-CTA-per-SM variant (8 warps); the two-CTA
+                                                 // variant (EPW = 4) has 128
 constexpr int NH_PROD = 4;                       // TMA-issuing warps: one thread sustains only ~1 box per 460 clocks
 constexpr int NH_THREADS = 64 + NH_EPI + 32 * (NH_PROD - 1);   // (profiles/tma_rate.cu), four warps 4x that
 constexpr uint32_t NH_A_BYTES = NH_BM * 128;
@@ -87,8 +88,12 @@ __global__ void nh_weights_pair_kernel(const float* __restrict__ w, int mode, in
   }
 }
 
-__global__ void __launch_bounds__(NH_THREADS, 1)
+// EPW = epilogue warps (8: one CTA per SM; 4: two CTAs per SM, for operators with at most 128 GEMM columns -- two MMA issuers
+// and two epilogues per SM overlap the issue latency of small-N MMAs and the per-tile accumulator hand-over)
+template <int EPW, int OCC>
+__global__ void __launch_bounds__(64 + 32 * EPW + 32 * (NH_PROD - 1), OCC)
 conv_nhwc_kernel(const NhArgs a, const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapW) {
+  constexpr int NHALF = EPW / 4;                 // warps per TMEM lane quarter = column chunks processed side by side
   extern __shared__ unsigned char smem_raw[];
   unsigned char* smem = smem_raw + ((1024u - (tma::s32(smem_raw) & 1023u)) & 1023u);
   const int S = a.stages;
@@ -116,7 +121,7 @@ conv_nhwc_kernel(const NhArgs a, const __grid_constant__ CUtensorMap mapA, const
     tma::prefetch_map(&mapA);
     tma::prefetch_map(&mapW);
     for (int s = 0; s < S; ++s) { tma::mbar_init(&full[s], 1); tma::mbar_init(&empty[s], 1); }
-    for (int s = 0; s < 2; ++s) { tma::mbar_init(&t_full[s], 1); tma::mbar_init(&t_empty[s], NH_EPI); }
+    for (int s = 0; s < 2; ++s) { tma::mbar_init(&t_full[s], 1); tma::mbar_init(&t_empty[s], 32 * EPW); }
     tma::mbar_init(w_full, 1);
     tma::mbar_fence_init();
   }
@@ -133,11 +138,11 @@ conv_nhwc_kernel(const NhArgs a, const __grid_constant__ CUtensorMap mapA, const
   const uint32_t tmem_base = *tmem_slot;
   const int my_tiles = (a.tiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
 
-  if (warp == 0 || warp >= 10) {
+  if (warp == 0 || warp >= 2 + EPW) {
     // ===================== TMA producers =====================
     // whole warp, uniform control flow, one elected lane issues (see the MMA issuer below for why)
     {
-      const uint32_t me = warp == 0 ? 0u : (uint32_t)(warp - 9);
+      const uint32_t me = warp == 0 ? 0u : (uint32_t)(warp - (1 + EPW));
       if (a.wres && me == 0) {
         if (tc05::elect_one()) {
           tma::mbar_expect_tx(w_full, (uint32_t)a.nkb * b_bytes);
@@ -253,7 +258,7 @@ conv_nhwc_kernel(const NhArgs a, const __grid_constant__ CUtensorMap mapA, const
       if (a.mask) {
 #pragma unroll
         for (int ci = 0; ci < 2; ++ci) {
-          const int cc = hh + 2 * ci;
+          const int cc = hh + NHALF * ci;
           if (cc < nchunks) {
 #pragma unroll
             for (int u = 0; u < 4; ++u) {
@@ -265,17 +270,17 @@ conv_nhwc_kernel(const NhArgs a, const __grid_constant__ CUtensorMap mapA, const
       }
       // one warp polls the accumulator barrier; the other seven park on a hardware named barrier (no issue slots)
       if (ew == 0) tma::mbar_wait_backoff(&t_full[as], aph, 128);
-      asm volatile("bar.sync 1, 256;" ::: "memory");
+      asm volatile("bar.sync 1, %0;" ::"n"(32 * EPW) : "memory");
       tc05::fence_after();
       const uint32_t tacc = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * a.BN);
 #pragma unroll
       for (int ci = 0; ci < 4; ++ci) {
-        const int cc = hh + 2 * ci;
+        const int cc = hh + NHALF * ci;
         if (cc < nchunks) {
           float v[32];
           tc05::ld_32x32(tacc + cc * 32, v);
           tc05::ld_wait();
-          if (cc + 2 >= nchunks) {  // last chunk of this thread: the accumulator stage is free once it sits in registers
+          if (cc + NHALF >= nchunks) {  // last chunk of this thread: the accumulator stage is free once it sits in registers
             tc05::fence_before();
             tma::mbar_arrive(&t_empty[as]);
           }
@@ -414,7 +419,7 @@ int nh_make_map(CUtensorMap* m, const void* base, int Cv, int SWv, int SH, int B
 
 struct NhPlan {
   bool ok;
-  int wmode, pair, nblk, C, cchunks, TW, S, D0, taps, N, BN, nkb, Kp, GH, GW, SH, SW, OC, OH, OW, quad, wres, stages, G, nprod;
+  int wmode, pair, nblk, C, cchunks, TW, S, D0, taps, N, BN, nkb, Kp, GH, GW, SH, SW, OC, OH, OW, quad, wres, stages, G, nprod, occ2;
   size_t smem;
 };
 
@@ -451,7 +456,14 @@ static NhPlan nh_plan(int op, int B, int Cin, int H, int W, int Cout) {
   if ((int64_t)B * p.GH * (p.GW / NH_BM) >= 2147483647LL) return p;
   p.BN = p.N;
   p.Kp = p.nkb * 64;
-  const size_t avail = 232448 - 1024 - 1024;
+  // two CTAs per SM when the operator has at most 128 columns (2 x 128 TMEM columns per CTA) -- VAECLUST_NH_OCC=1 forces one
+  static const char* occ_env = getenv("VAECLUST_NH_OCC");
+  // measured at the script-12 shapes (profiles/README.md): it wins for the forward operators whose weight slab does not
+  // stay resident anyway (ConvT 64->32: 122 -> 97 us, Conv 64->128: 41 -> 37 us), loses for the pair views and the Conv
+  // data gradient (64 -> 71, 107 -> 121 us) and is neutral for the ConvT data gradients.  VAECLUST_NH_OCC=2 forces it.
+  const bool by_op = p.wmode == 2 || (p.wmode == 0 && !p.pair);
+  p.occ2 = (p.BN <= 128 && (by_op || (occ_env && atoi(occ_env) == 2)) && !(occ_env && atoi(occ_env) == 1)) ? 1 : 0;
+  const size_t avail = (p.occ2 ? 232448 / 2 - 1024 : 232448) - 1024 - 1024;
   const size_t slab = (size_t)p.nkb * p.BN * 128;
   p.wres = slab + 4 * NH_A_BYTES <= avail ? 1 : 0;
   const size_t kb_bytes = NH_A_BYTES + (p.wres ? 0 : (size_t)p.BN * 128);
@@ -549,8 +561,14 @@ extern "C" int vc_conv_nhwc(int op, const void* src_nhwc, const float* Wt, const
   a.bias = bias; a.relu = relu; a.mask = static_cast<const __nv_bfloat16*>(mask_nhwc);
   a.out_nhwc = static_cast<__nv_bfloat16*>(out_nhwc); a.out_nchw = out_nchw;
   const int grid = a.tiles < sm_count() ? a.tiles : sm_count();
-  VC_CUDA(cudaFuncSetAttribute(conv_nhwc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p.smem));
-  conv_nhwc_kernel<<<grid, NH_THREADS, p.smem, s>>>(a, ma, mw);
+  if (p.occ2) {
+    const int grid2 = a.tiles < 2 * sm_count() ? a.tiles : 2 * sm_count();
+    VC_CUDA(cudaFuncSetAttribute(conv_nhwc_kernel<4, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p.smem));
+    conv_nhwc_kernel<4, 2><<<grid2, 64 + 32 * 4 + 32 * (NH_PROD - 1), p.smem, s>>>(a, ma, mw);
+  } else {
+    VC_CUDA(cudaFuncSetAttribute(conv_nhwc_kernel<8, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p.smem));
+    conv_nhwc_kernel<8, 1><<<grid, NH_THREADS, p.smem, s>>>(a, ma, mw);
+  }
   VC_LAUNCH_CHECK();
   return VC_OK;
 }

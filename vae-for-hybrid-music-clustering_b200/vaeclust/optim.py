@@ -124,16 +124,20 @@ class Adam:
             raise VaeclustError("vaeclust.optim.Adam(capturable=True): every stepped parameter must share one step count")
         for t, segs in by_step.items():
             rows = []
+            # one block per chunk: few elements (everything but the wide layers) get smaller chunks so that the launch
+            # still fills the GPU (34 blocks of 64 Ki elements took 0.076 ms for 2 M parameters)
+            total = sum(n for _pp, _gp, _st, n in segs)
+            chunk = _CHUNK if total >= (1 << 25) else (1 << 12)
             for pp, gp, st, n in segs:
                 if n == 0:
                     continue
-                base = np.arange(0, n, _CHUNK, dtype=np.int64)
+                base = np.arange(0, n, chunk, dtype=np.int64)
                 tab = np.empty((base.size, 5), dtype=np.int64)
                 tab[:, 0] = pp + 4 * base
                 tab[:, 1] = gp + 4 * base
                 tab[:, 2] = st["exp_avg"].data_ptr() + 4 * base
                 tab[:, 3] = st["exp_avg_sq"].data_ptr() + 4 * base
-                tab[:, 4] = np.minimum(_CHUNK, n - base)
+                tab[:, 4] = np.minimum(chunk, n - base)
                 rows.append(tab)
             if not rows:
                 continue
