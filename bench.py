@@ -113,6 +113,8 @@ def flops_of(name: str, sig) -> float:
         if name.startswith("vc_linear_"):
             M, N, K = sig[:3]
             return 2.0 * M * N * K
+        if name == "vc_linear_wgrad_adam":
+            return 2.0 * sig[0] * sig[1] * sig[2]
         if name in ("vc_conv_nhwc", "vc_conv_nhwc_wgrad"):
             op, B, Cin, H, W, Cout = (sig[0],) + tuple(sig[2:7]) if name == "vc_conv_nhwc" else tuple(sig[:6])
             if op <= 5:
@@ -169,6 +171,12 @@ def bytes_of(name: str, sig) -> float:
             return 2.0 * sig[0] * sig[1]
         if name == "vc_nhwc_from_nchw":
             return 6.0 * sig[0] * sig[1] * sig[2] * sig[3]
+        if name == "vc_linear_wgrad_adam":      # p, m, v read and written once; the gradient never touches memory
+            B, Cin, Cout = sig[:3]
+            return 24.0 * Cin * Cout + 4.0 * B * (Cin + Cout)
+        if name == "vc_conv1_wgrad_bias":
+            B, H, W, Cout = sig[:4]
+            return 4.0 * B * (H * W + Cout * (H // 2) * (W // 2))
         if name == "vc_relu_bwd_bias_nhwc":
             return 14.0 * sig[0] * sig[1] * sig[2] * sig[3]
     except Exception:
@@ -180,7 +188,9 @@ def family_of(name: str, sig) -> str:
     """Kernel family behind an entry point (vc_dense_op dispatches on op and shape, csrc/tc_gemm.cu)."""
     if name in ("vc_conv_nhwc", "vc_conv_nhwc_wgrad"):
         return "conv_nhwc (TMA-fed fwd / dgrad)" if name == "vc_conv_nhwc" else "conv_nhwc_wgrad (TMA-fed)"
-    if name in ("vc_nhwc_conv1_fwd", "vc_nhwc_convT1_dgrad"):
+    if name == "vc_linear_wgrad_adam":
+        return "skinny_gemm wgrad + Adam (FC 262144<->256)"
+    if name in ("vc_nhwc_conv1_fwd", "vc_nhwc_convT1_dgrad", "vc_conv1_wgrad_bias"):
         return "conv_direct (1-channel ends)"
     if name != "vc_dense_op":
         return name

@@ -14,6 +14,8 @@ import sys
 from collections import OrderedDict, defaultdict
 
 FAMILIES = OrderedDict([
+    ("conv_nhwc_wgrad_kernel", "conv_nhwc_wgrad (TMA-fed)"),
+    ("conv_nhwc_kernel", "conv_nhwc (TMA-fed fwd / dgrad)"),
     ("conv_wgrad_igemm_kernel", "conv_wgrad_igemm"),
     ("conv_igemm_kernel", "conv_igemm (fwd / dgrad)"),
     ("skinny_gemm_kernel", "skinny_gemm (FC 262144<->256)"),
@@ -81,6 +83,8 @@ def traffic(path, out, out_json, header):
                                                            rd / 1e6, wr / 1e6))
             for key, label in FAMILIES.items():
                 if key in e["kernel"]:
+                    if key == "skinny_gemm_kernel" and wr > 4e8:    # the same kernel with the Adam epilogue: it writes p, m, v
+                        label = "skinny_gemm wgrad + Adam (FC 262144<->256)"
                     a = fam.setdefault(label, {"launches": 0, "rd": 0.0, "wr": 0.0, "ns": 0.0})
                     a["launches"] += 1
                     a["rd"] += rd
