@@ -162,10 +162,11 @@ kmeans_assign_update_kernel(const KmArgs a, const __grid_constant__ CUtensorMap 
     s = warp_sum(s);
     if (lane == 0) c2[c] = s;
   }
-  if (tid == 0) {
+  if (warp == 0) {     // warp-uniform branch + elect.sync: no waterfall loop around the copy instructions
     for (int b = 0; b < 2; ++b) {
       const int64_t t = (int64_t)blockIdx.x + (int64_t)b * gridDim.x;
-      if (t < ntiles) issue(b, t);
+      if (t < ntiles && tc05::elect_one()) issue(b, t);
+      __syncwarp();
     }
   }
   __syncthreads();
@@ -311,11 +312,12 @@ kmeans_assign_update_kernel(const KmArgs a, const __grid_constant__ CUtensorMap 
       }
       __syncthreads();
     }
-    if (tid == 0) {
+    if (warp == 0) {
       const int64_t tn = t + 2 * (int64_t)gridDim.x;
       if (tn < ntiles) {
         tma::fence_proxy_async();  // order the generic-proxy reads of the slot before the async-proxy overwrite
-        issue(b, tn);
+        if (tc05::elect_one()) issue(b, tn);
+        __syncwarp();
       }
     }
   }
@@ -452,15 +454,18 @@ kmeans_tc_kernel(const KmTcArgs ta, const __grid_constant__ CUtensorMap tmap) {
   __syncthreads();
 
   if (warp == NW) {
-    // ================= copy + MMA issuer (one thread) =================
-    if (lane == 0) {
+    // ================= copy + MMA issuer =================
+    // The whole warp walks the loop in uniform control flow and one ELECTED lane issues: from an `if (lane == 0)` branch
+    // every UTMALDG / UTCHMMA / UTCBAR is wrapped in an ELECT ... BRA.U.ANY waterfall loop (~70 clocks each).
+    {
       auto issue = [&](int slot, int64_t t) {
         mbar_expect_tx(&full[slot], (uint32_t)tile_bytes);
         tma::load_2d(smem + (size_t)slot * tile_bytes, &tmap, &full[slot], 0, (int)(t * tp));
       };
       for (int s = 0; s < kTcSlots; ++s) {
         const int64_t t = (int64_t)blockIdx.x + (int64_t)s * G;
-        if (t < ntiles) issue(s, t);
+        if (t < ntiles && tc05::elect_one()) issue(s, t);
+        __syncwarp();
       }
       const uint32_t sL = tma::s32(lo_tile), sCh = tma::s32(chi);
       int i = 0;
@@ -470,17 +475,20 @@ kmeans_tc_kernel(const KmTcArgs ta, const __grid_constant__ CUtensorMap tmap) {
         // A = the raw fp32 tile: kind::tf32 reads the upper 19 bits of each word, i.e. exactly hi.  One N = 2*KP
         // MMA gives hi.chi | hi.clo side by side (A is fetched once); lo.chi accumulates onto the first KP columns.
         const uint32_t sX = tma::s32(smem + (size_t)(i % kTcSlots) * tile_bytes);
+        if (tc05::elect_one()) {
 #pragma unroll
-        for (int hh = 0; hh < TP / 128; ++hh) {
-          const uint32_t tacc = tmem_base + (uint32_t)(hh * 2 * KP);
+          for (int hh = 0; hh < TP / 128; ++hh) {
+            const uint32_t tacc = tmem_base + (uint32_t)(hh * 2 * KP);
 #pragma unroll
-          for (int kk = 0; kk < 4; ++kk) {
-            const uint32_t oa = (uint32_t)(hh * 128 * 128 + kk * 32), ob = (uint32_t)(kk * 32);
-            mma_tf32(tacc, tc05::desc_k_sw128(sX + oa), tc05::desc_k_sw128(sCh + ob), ta.idesc2, kk != 0);
-            mma_tf32(tacc, tc05::desc_k_sw128(sL + oa), tc05::desc_k_sw128(sCh + ob), ta.idesc, 1);
+            for (int kk = 0; kk < 4; ++kk) {
+              const uint32_t oa = (uint32_t)(hh * 128 * 128 + kk * 32), ob = (uint32_t)(kk * 32);
+              mma_tf32(tacc, tc05::desc_k_sw128(sX + oa), tc05::desc_k_sw128(sCh + ob), ta.idesc2, kk != 0);
+              mma_tf32(tacc, tc05::desc_k_sw128(sL + oa), tc05::desc_k_sw128(sCh + ob), ta.idesc, 1);
+            }
           }
+          tc05::commit(done);
         }
-        tc05::commit(done);
+        __syncwarp();
         // refill the slot tile i-1 occupied (tile i-1+kTcSlots) once every worker warp has finished its phase B
         if (i >= 1) {
           const int64_t tn = t + (kTcSlots - 1) * G;
@@ -488,7 +496,8 @@ kmeans_tc_kernel(const KmTcArgs ta, const __grid_constant__ CUtensorMap tmap) {
             const int j = i - 1;
             tma::mbar_wait_backoff(&free_[j % kTcSlots], (uint32_t)((j / kTcSlots) & 1), 64);
             tma::fence_proxy_async();
-            issue(j % kTcSlots, tn);
+            if (tc05::elect_one()) issue(j % kTcSlots, tn);
+            __syncwarp();
           }
         }
       }

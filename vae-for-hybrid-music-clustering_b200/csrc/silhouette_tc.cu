@@ -122,12 +122,17 @@ silhouette_tc_kernel(const SilTcArgs a, const __grid_constant__ CUtensorMap mapH
 
   if (warp == 0) {
     // ===================== TMA producer =====================
-    if (lane == 0) {
-      tma::mbar_expect_tx(a_full, 2 * op_bytes);
-      for (int p = 0; p < P; ++p) {
-        tma::load_2d(sA + p * panel_bytes, &mapH, a_full, p * 64, (int)r0);
-        tma::load_2d(sA + op_bytes + p * panel_bytes, &mapL, a_full, p * 64, (int)r0);
+    // whole warp in uniform control flow, one elected lane issues: from an `if (lane == 0)` branch every UTMALDG / UTCHMMA is
+    // wrapped in an ELECT ... BRA.U.ANY waterfall loop (~70 clocks each, profiles/README.md round 2)
+    {
+      if (tc05::elect_one()) {
+        tma::mbar_expect_tx(a_full, 2 * op_bytes);
+        for (int p = 0; p < P; ++p) {
+          tma::load_2d(sA + p * panel_bytes, &mapH, a_full, p * 64, (int)r0);
+          tma::load_2d(sA + op_bytes + p * panel_bytes, &mapL, a_full, p * 64, (int)r0);
+        }
       }
+      __syncwarp();
       int64_t counter = 0;
       uint32_t it = 0;
       for (int c = 0; c < a.k; ++c) {
@@ -138,20 +143,23 @@ silhouette_tc_kernel(const SilTcArgs a, const __grid_constant__ CUtensorMap mapH
           const uint32_t ph = (it / S) & 1;
           tma::mbar_wait(&b_empty[s], ph ^ 1);
           unsigned char* dst = sB + (size_t)s * 2 * bop_bytes;
-          tma::mbar_expect_tx(&b_full[s], 2 * bop_bytes);
-          for (int p = 0; p < P; ++p)
-            for (int h = 0; h < ST_COLS / ST_ROWS; ++h) {   // the tensor-map box is 128 rows
-              const uint32_t o = p * bpanel_bytes + h * panel_bytes;
-              tma::load_2d(dst + o, &mapH, &b_full[s], p * 64, (int)j0 + h * ST_ROWS);
-              tma::load_2d(dst + bop_bytes + o, &mapL, &b_full[s], p * 64, (int)j0 + h * ST_ROWS);
-            }
+          if (tc05::elect_one()) {
+            tma::mbar_expect_tx(&b_full[s], 2 * bop_bytes);
+            for (int p = 0; p < P; ++p)
+              for (int h = 0; h < ST_COLS / ST_ROWS; ++h) {   // the tensor-map box is 128 rows
+                const uint32_t o = p * bpanel_bytes + h * panel_bytes;
+                tma::load_2d(dst + o, &mapH, &b_full[s], p * 64, (int)j0 + h * ST_ROWS);
+                tma::load_2d(dst + bop_bytes + o, &mapL, &b_full[s], p * 64, (int)j0 + h * ST_ROWS);
+              }
+          }
+          __syncwarp();
           ++it;
         }
       }
     }
   } else if (warp == 1) {
     // ===================== MMA issuer =====================
-    if (lane == 0) {
+    {
       constexpr uint32_t kIdesc = tc05::idesc(tc05::kFmtBF16, ST_ROWS, ST_COLS, 0, 0);
       tma::mbar_wait(a_full, 0);
       tc05::fence_after();
@@ -171,25 +179,28 @@ silhouette_tc_kernel(const SilTcArgs a, const __grid_constant__ CUtensorMap mapH
           tc05::fence_after();
           const uint32_t bH = tma::s32(sB + (size_t)s * 2 * bop_bytes), bL = bH + bop_bytes;
           const uint32_t tacc = tmem_base + as * ST_COLS;
-          uint32_t accum = 0;
-          for (int p = 0; p < P; ++p) {
+          if (tc05::elect_one()) {
+            uint32_t accum = 0;
+            for (int p = 0; p < P; ++p) {
 #pragma unroll
-            for (int kk = 0; kk < 4; ++kk) {  // 64 bf16 per panel / UMMA_K 16
-              const uint32_t o = p * panel_bytes + kk * 32, ob = p * bpanel_bytes + kk * 32;
-              const uint64_t dAH = tc05::desc_k_sw128(aH + o), dAL = tc05::desc_k_sw128(aL + o);
-              const uint64_t dBH = tc05::desc_k_sw128(bH + ob), dBL = tc05::desc_k_sw128(bL + ob);
-              tc05::mma_bf16(tacc, dAH, dBH, kIdesc, accum);
-              tc05::mma_bf16(tacc, dAH, dBL, kIdesc, 1);
-              tc05::mma_bf16(tacc, dAL, dBH, kIdesc, 1);
-              // lo.lo is 2^-16 of the product and zero-mean: it moves a squared distance that survives the close-pair
-              // rule (>= (|x|^2+|y|^2)/256) by at most 2^-8 of its value and the score by < 1e-6 (validated against
-              // scikit-learn at 1e-5 on every parity case); VAECLUST_SIL_MMA=4 keeps it
-              if (a.mma4) tc05::mma_bf16(tacc, dAL, dBL, kIdesc, 1);
-              accum = 1;
+              for (int kk = 0; kk < 4; ++kk) {  // 64 bf16 per panel / UMMA_K 16
+                const uint32_t o = p * panel_bytes + kk * 32, ob = p * bpanel_bytes + kk * 32;
+                const uint64_t dAH = tc05::desc_k_sw128(aH + o), dAL = tc05::desc_k_sw128(aL + o);
+                const uint64_t dBH = tc05::desc_k_sw128(bH + ob), dBL = tc05::desc_k_sw128(bL + ob);
+                tc05::mma_bf16(tacc, dAH, dBH, kIdesc, accum);
+                tc05::mma_bf16(tacc, dAH, dBL, kIdesc, 1);
+                tc05::mma_bf16(tacc, dAL, dBH, kIdesc, 1);
+                // lo.lo is 2^-16 of the product and zero-mean: it moves a squared distance that survives the close-pair
+                // rule (>= (|x|^2+|y|^2)/256) by at most 2^-8 of its value and the score by < 1e-6 (validated against
+                // scikit-learn at 1e-5 on every parity case); VAECLUST_SIL_MMA=4 keeps it
+                if (a.mma4) tc05::mma_bf16(tacc, dAL, dBL, kIdesc, 1);
+                accum = 1;
+              }
             }
+            tc05::commit(&b_empty[s]);   // ring slot reusable once these MMAs have read it
+            tc05::commit(&t_full[as]);   // accumulator ready for the epilogue
           }
-          tc05::commit(&b_empty[s]);   // ring slot reusable once these MMAs have read it
-          tc05::commit(&t_full[as]);   // accumulator ready for the epilogue
+          __syncwarp();
           ++it;
         }
       }
