@@ -255,7 +255,7 @@ conv_nhwc_kernel(const NhArgs a, const __grid_constant__ CUtensorMap mapA, const
       // BEFORE waiting for the main loop, so the ~1 us of memory latency hides under the MMAs of this tile (taken after the
       // wait it was serial per chunk and made the phase-merged data gradients epilogue-bound: 144 vs 45 us).
       uint4 mk[2][4];
-      if (a.mask) {
+      if (a.mask && !(a.dbg & 64)) {
 #pragma unroll
         for (int ci = 0; ci < 2; ++ci) {
           const int cc = hh + NHALF * ci;
@@ -285,8 +285,8 @@ conv_nhwc_kernel(const NhArgs a, const __grid_constant__ CUtensorMap mapA, const
             tma::mbar_arrive(&t_empty[as]);
           }
           if (a.dbg & 4) continue;
-          uint4 m4[4];
-          if (a.mask) {
+          uint4 m4[4] = {};
+          if (a.mask && !(a.dbg & 64)) {
 #pragma unroll
             for (int u = 0; u < 4; ++u) {
               if (ci < 2) {
@@ -322,7 +322,7 @@ conv_nhwc_kernel(const NhArgs a, const __grid_constant__ CUtensorMap mapA, const
                 }
               }
             }
-            if (a.out_nhwc) {
+            if (a.out_nhwc && !(a.dbg & 32)) {
               uint4* o4 = reinterpret_cast<uint4*>(a.out_nhwc + px0 * a.OC + c0);
 #pragma unroll
               for (int j8 = 0; j8 < 4; ++j8)
@@ -361,7 +361,7 @@ conv_nhwc_kernel(const NhArgs a, const __grid_constant__ CUtensorMap mapA, const
                   v[4 * (2 * u + 1) + p] = nh_hi(mw[u]) > 0.f ? v[4 * (2 * u + 1) + p] : 0.f;
                 }
               }
-              if (a.out_nhwc)
+              if (a.out_nhwc && !(a.dbg & 32))
                 *reinterpret_cast<uint4*>(a.out_nhwc + px * a.OC + c0) =
                     make_uint4(nh_pack(v[p], v[4 + p]), nh_pack(v[8 + p], v[12 + p]), nh_pack(v[16 + p], v[20 + p]),
                                nh_pack(v[24 + p], v[28 + p]));
