@@ -260,7 +260,7 @@ conv_igemm_kernel(const IgArgs a, const __grid_constant__ CUtensorMap mapW) {
     }
   } else if (warp == 8) {
     // ===================== MMA issuer =====================
-    if (lane == 0) {
+    if (tc05::elect_one()) {   // a single lane the compiler knows about: no waterfall loop around UTCHMMA / UTMALDG
       int it = 0;
       for (int tl = 0; tl < my_tiles; ++tl) {
         const int as = tl & 1;

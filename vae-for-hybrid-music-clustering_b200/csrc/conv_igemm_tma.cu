@@ -96,7 +96,7 @@ conv_igemm_tma_kernel(const ItArgs a, const __grid_constant__ CUtensorMap mapA, 
 
   if (warp == 0) {
     // ===================== TMA producer =====================
-    if (lane == 0) {
+    if (tc05::elect_one()) {   // a single lane the compiler knows about: no waterfall loop around UTCHMMA / UTMALDG
       uint32_t it = 0;
       for (int tl = 0; tl < my_tiles; ++tl) {
         const int t = (int)blockIdx.x + tl * (int)gridDim.x;
@@ -116,7 +116,7 @@ conv_igemm_tma_kernel(const ItArgs a, const __grid_constant__ CUtensorMap mapA, 
     }
   } else if (warp == 1) {
     // ===================== MMA issuer =====================
-    if (lane == 0) {
+    if (tc05::elect_one()) {   // a single lane the compiler knows about: no waterfall loop around UTCHMMA / UTMALDG
       uint32_t it = 0;
       for (int tl = 0; tl < my_tiles; ++tl) {
         const int as = tl & 1;

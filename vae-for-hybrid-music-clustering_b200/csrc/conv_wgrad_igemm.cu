@@ -322,7 +322,7 @@ __global__ void __launch_bounds__(WG_THREADS, 1) conv_wgrad_igemm_kernel(const W
     }
   } else {
     // ===================== MMA issuer =====================
-    if (lane == 0) {
+    if (tc05::elect_one()) {   // a single lane the compiler knows about: no waterfall loop around UTCHMMA / UTMALDG
       for (int it = 0; it < nkb; ++it) {
         const int s = it % S;
         const uint32_t ph = (uint32_t)(it / S) & 1u;
@@ -537,7 +537,7 @@ __global__ void __launch_bounds__(WG_THREADS, 1) conv_wgrad_fast_kernel(const Wg
     }
   } else {
     // ===================== MMA issuer =====================
-    if (lane == 0) {
+    if (tc05::elect_one()) {   // a single lane the compiler knows about: no waterfall loop around UTCHMMA / UTMALDG
       for (int it = 0; it < nkb; ++it) {
         const int s = it % S;
         const uint32_t ph = (uint32_t)(it / S) & 1u;

@@ -553,7 +553,8 @@ mv_rows_kernel(const MvRowsArgs a, const __grid_constant__ MvMaps maps) {
     }
   } else if (warp == 1) {
     // ===================== MMA issuer (also issues the TMA stores of what the epilogues leave in P) ==============
-    if (lane == 0) {
+    // elect.sync instead of `lane == 0`: a single active lane the compiler knows about (no waterfall around UTCHMMA / UTMA*)
+    if (tc05::elect_one()) {
       uint32_t wit = 0, xit = 0;
       uint32_t kcnt[4] = {0u, 0u, 0u, 0u};                       // completions consumed per k-block barrier
       int st_map = -1, st_nblk = 0, st_col0 = 0, st_row = 0;     // what the previous epilogue is leaving in P
@@ -724,7 +725,7 @@ mv_wgrad_kernel(const MvwArgs a, const __grid_constant__ MvwMaps maps) {
   const uint32_t tmem_base = *tmem_slot;
 
   if (warp == 0) {
-    if (lane == 0)
+    if (tc05::elect_one())
       for (int it = 0; it < nkb; ++it) {
         const int st = it % MVW_STAGES;
         tma::mbar_wait(&empty[st], (((uint32_t)it / MVW_STAGES) & 1u) ^ 1u);
@@ -736,7 +737,7 @@ mv_wgrad_kernel(const MvwArgs a, const __grid_constant__ MvwMaps maps) {
         for (int b = 0; b < nbox; ++b) tma::load_2d(sa + (2 + b) * MVW_BOX, &maps.a[t.layer], &full[st], t.n0 + 64 * b, row);
       }
   } else if (warp == 1) {
-    if (lane == 0) {
+    if (tc05::elect_one()) {
       const uint32_t idesc = tc05::idesc(tc05::kFmtBF16, 128, t.n, 1, 1);
       const uint32_t idesc1 = tc05::idesc(tc05::kFmtBF16, 128, 16, 1, 1);
       const uint32_t so = tma::s32(ones);

@@ -313,7 +313,7 @@ skinny_gemm_kernel(const SkArgs a, const __grid_constant__ CUtensorMap mapB) {
     }
   } else {
     // ===================== MMA issuer =====================
-    if (lane == 0) {
+    if (tc05::elect_one()) {   // a single lane the compiler knows about: no waterfall loop around UTCHMMA / UTMALDG
       for (int it = 0; it < nkb; ++it) {
         const int s = it % S;
         tma::mbar_wait_backoff(&full[s], (uint32_t)(it / S) & 1u, 32);

@@ -90,7 +90,7 @@ gemm_tc_kernel(const EP ep, int M, int N, int kb_total, int kbs, const __grid_co
   const uint32_t tmem_base = *tmem_slot;
 
   if (warp == 0) {
-    if (lane == 0) {
+    if (tc05::elect_one()) {   // a single lane the compiler knows about: no waterfall loop around UTCHMMA / UTMALDG
       for (int i = 0; i < nkb; ++i) {
         const int s = i % STAGES;
         const uint32_t ph = (i / STAGES) & 1;
@@ -102,7 +102,7 @@ gemm_tc_kernel(const EP ep, int M, int N, int kb_total, int kbs, const __grid_co
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
+    if (tc05::elect_one()) {   // a single lane the compiler knows about: no waterfall loop around UTCHMMA / UTMALDG
       constexpr uint32_t kIdesc = tc05::idesc(tc05::kFmtBF16, TG_BM, BN, 0, 0);
       for (int i = 0; i < nkb; ++i) {
         const int s = i % STAGES;
