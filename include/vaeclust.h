@@ -260,9 +260,19 @@ int vc_adam_multi_at(const VcAdamChunk* table, int n_chunks, float lr, float bet
  * supplies the bias corrections when non-NULL, else bias_corr1 / bias_corr2 are used.  Single-process training only. */
 int vc_linear_wgrad_adam_supported(int B, int Cin, int Cout);
 size_t vc_linear_wgrad_adam_workspace_bytes(int B, int Cin, int Cout);
-int vc_linear_wgrad_adam(const float* dy, const float* x, float* W, float* exp_avg, float* exp_avg_sq, int B, int Cin,
-                         int Cout, float lr, float beta1, float beta2, float eps, float bias_corr1, float bias_corr2,
-                         const VcAdamDeviceStep* step_state, void* workspace, size_t workspace_bytes, void* stream);
+int vc_linear_wgrad_adam(const float* dy, const float* x, float* W, float* exp_avg, float* exp_avg_sq, void* w_shadow,
+                         int B, int Cin, int Cout, float lr, float beta1, float beta2, float eps, float bias_corr1,
+                         float bias_corr2, const VcAdamDeviceStep* step_state, void* workspace, size_t workspace_bytes,
+                         void* stream);
+/* The same wide layers read from a bf16 SHADOW of the weight ([Cout][Cin], kept in step with the fp32 master by
+ * vc_linear_wgrad_adam's w_shadow argument, which may be NULL there): op = VC_OP_LINEAR_FWD (y = act(x W^T + b)) or
+ * VC_OP_LINEAR_DGRAD (dx = dy W).  The weight tile is one TMA load straight into the MMA's operand layout (K-major boxes
+ * forward, MN-major boxes for the data gradient) -- half the bytes of the fp32 stream and no conversion instructions;
+ * the products are the same bf16 x bf16 ones as vc_dense_op in bf16 mode. */
+int vc_linear_bf16w_supported(int op, int B, int Cin, int Cout);
+size_t vc_linear_bf16w_workspace_bytes(int op, int B, int Cin, int Cout);
+int vc_linear_bf16w(int op, const float* in, const void* w_shadow, const float* bias, float* out, int B, int Cin, int Cout,
+                    int relu, void* workspace, size_t workspace_bytes, void* stream);
 
 /* ------------------------------------------------------------------ fused MLP-VAE train step (scripts 19 / 06 / 22)
  * The whole optimisation step of MLPVAE (19:64-121 model, 19:226-232 step), of script 06's MLPVAE (06:145-188,

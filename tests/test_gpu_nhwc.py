@@ -286,3 +286,31 @@ def test_fused_fc_weight_gradient_adam_matches_plain_step(graphed, monkeypatch):
             torch.testing.assert_close(a, b, rtol=1e-4, atol=1e-12)
     finally:
         ops.set_precision("fp32")
+
+
+@pytest.mark.parametrize("Cin,Cout", [(65536, 256), (256, 65536)])
+def test_wide_linear_from_bf16_shadow(Cin, Cout):
+    """vc_linear_bf16w (weight tile by TMA from a bf16 copy: K-major boxes forward, MN-major boxes for the data gradient)
+    against vc_dense_op in bf16 mode on the fp32 weight: the same bf16 products, so only summation order differs."""
+    from vaeclust._lib import lib, ptr, stream_ptr
+    L = lib()
+    B = 64
+    w = _r(Cout, Cin, seed=1, scale=Cin ** -0.5)
+    sh = w.to(torch.bfloat16)
+    x, dy, b = _r(B, Cin, seed=2), _r(B, Cout, seed=3), _r(Cout, seed=4)
+    for op, inp, bias, relu, oshape in ((0, x, b, 1, (B, Cout)), (1, dy, None, 0, (B, Cin))):
+        assert L.size("vc_linear_bf16w_supported", op, B, Cin, Cout) == 1
+        want = torch.full(oshape, float("nan"), device="cuda")
+        ws = torch.empty(L.size("vc_dense_op_workspace_bytes", op, 1, B, Cin, 1, 1, Cout), dtype=torch.uint8, device="cuda")
+        L.call("vc_dense_op", op, 1, ptr(inp), ptr(w), ptr(bias), ptr(want), B, Cin, 1, 1, Cout, relu, ptr(ws), ws.numel(),
+               stream_ptr())
+        got = torch.full(oshape, float("nan"), device="cuda")
+        ws2 = torch.empty(L.size("vc_linear_bf16w_workspace_bytes", op, B, Cin, Cout), dtype=torch.uint8, device="cuda")
+        L.call("vc_linear_bf16w", op, ptr(inp), ptr(sh), ptr(bias), ptr(got), B, Cin, Cout, relu, ptr(ws2), ws2.numel(),
+               stream_ptr())
+        torch.cuda.synchronize()
+        torch.testing.assert_close(got, want, rtol=2e-5, atol=2e-5 * float(want.abs().max()))
+        ref = _bf(inp) @ (_bf(w).t() if op == 0 else _bf(w))
+        if op == 0:
+            ref = torch.relu(ref + b)
+        torch.testing.assert_close(got, ref, rtol=1e-4, atol=1e-4 * float(ref.abs().max()))

@@ -30,8 +30,12 @@ struct SkArgs {
   uint32_t idesc;
   // fused Adam (weight-gradient ops only): `out` is the PARAMETER, updated in place from the accumulator; the gradient
   // is never written (saves its 4 B/element write and the optimizer's 4 B/element read)
+  // bf16 shadow of the big matrix (a_bf16): the A tile is one TMA load (K-major box, or two MN-major boxes when the
+  // matrix is m-contiguous) instead of eight producer warps reading fp32 and converting -- half the bytes, no instructions
+  int a_bf16;
   int adam;
   float* ad_m; float* ad_v;
+  __nv_bfloat16* ad_shadow;                  // fused Adam also refreshes the shadow (same layout as the parameter) or null
   const VcAdamDeviceStep* ad_step;          // device-side bias corrections (CUDA-graph replay), or null: use ad_bc1/2
   float ad_lr, ad_b1, ad_b2, ad_eps, ad_bc1, ad_bc2;
 };
@@ -105,7 +109,7 @@ __global__ void sk_small_operand_rows_kernel(const float* __restrict__ src, int6
 }
 
 __global__ void __launch_bounds__(SK_THREADS, 2)
-skinny_gemm_kernel(const SkArgs a, const __grid_constant__ CUtensorMap mapB) {
+skinny_gemm_kernel(const SkArgs a, const __grid_constant__ CUtensorMap mapB, const __grid_constant__ CUtensorMap mapA) {
   extern __shared__ unsigned char smem_raw[];
   unsigned char* smem = smem_raw + ((1024u - (tma::s32(smem_raw) & 1023u)) & 1023u);
   const int S = a.stages;
@@ -124,7 +128,8 @@ skinny_gemm_kernel(const SkArgs a, const __grid_constant__ CUtensorMap mapB) {
 
   if (threadIdx.x == 0) {
     tma::prefetch_map(&mapB);
-    for (int s = 0; s < S; ++s) { tma::mbar_init(&full[s], 256 + 1); tma::mbar_init(&empty[s], 1); }
+    if (a.a_bf16) tma::prefetch_map(&mapA);
+    for (int s = 0; s < S; ++s) { tma::mbar_init(&full[s], a.a_bf16 ? 1 : 256 + 1); tma::mbar_init(&empty[s], 1); }
     tma::mbar_init(t_full, 1);
     tma::mbar_fence_init();
   }
@@ -197,7 +202,29 @@ skinny_gemm_kernel(const SkArgs a, const __grid_constant__ CUtensorMap mapB) {
       tma::fence_proxy_async();
       tma::mbar_arrive(&full[s]);
     };
-    {
+    if (a.a_bf16) {
+      // shadow mode: warp 0 alone feeds the ring by TMA (uniform control flow, elected lane), the other warps go straight
+      // to the epilogue wait
+      if (warp == 0) {
+        for (int it = 0; it < nkb; ++it) {
+          const int s = it % S;
+          tma::mbar_wait_backoff(&empty[s], ((uint32_t)(it / S) & 1u) ^ 1u, 64);
+          unsigned char* tile = smem + (size_t)s * st_bytes;
+          const int k0 = (kb0 + it) * 64;
+          if (tc05::elect_one()) {
+            tma::mbar_expect_tx(&full[s], st_bytes);
+            if (!a.a_mcontig) {
+              tma::load_2d(tile, &mapA, &full[s], k0, m0);                    // [128 m rows][64 k]: K-major
+            } else {
+              tma::load_2d(tile, &mapA, &full[s], m0, k0);                    // [64 k rows][64 m] x 2: MN-major
+              tma::load_2d(tile + SK_A_BYTES / 2, &mapA, &full[s], m0 + 64, k0);
+            }
+            tma::load_2d(tile + SK_A_BYTES, &mapB, &full[s], k0, 0);
+          }
+          __syncwarp();
+        }
+      }
+    } else {
       float buf0[32], buf1[32];
       if (nkb > 0) load_kb(0, buf0);
       for (int it = 0; it < nkb; it += 2) {
@@ -290,6 +317,8 @@ skinny_gemm_kernel(const SkArgs a, const __grid_constant__ CUtensorMap mapB) {
               *reinterpret_cast<float4*>(a.out + off[u]) = pp[u];
               __stcs(reinterpret_cast<float4*>(a.ad_m + off[u]), mm[u]);
               __stcs(reinterpret_cast<float4*>(a.ad_v + off[u]), vv[u]);
+              if (a.ad_shadow)
+                *reinterpret_cast<uint2*>(a.ad_shadow + off[u]) = make_uint2(sk_pack(pp[u].x, pp[u].y), sk_pack(pp[u].z, pp[u].w));
             }
           }
         }
@@ -320,9 +349,11 @@ skinny_gemm_kernel(const SkArgs a, const __grid_constant__ CUtensorMap mapB) {
         tc05::fence_after();
         const uint32_t sa = tma::s32(smem + (size_t)s * st_bytes), sb = sa + SK_A_BYTES;
 #pragma unroll
-        for (int kk = 0; kk < 4; ++kk)
-          tc05::mma_bf16(tmem_base, tc05::desc_k_sw128(sa + kk * 32), tc05::desc_k_sw128(sb + kk * 32), a.idesc,
-                         (uint32_t)((it | kk) != 0));
+        for (int kk = 0; kk < 4; ++kk) {
+          const uint64_t da = (a.a_bf16 && a.a_mcontig) ? tc05::desc_mn_sw128(sa + kk * 2048, SK_A_BYTES / 2)
+                                                        : tc05::desc_k_sw128(sa + kk * 32);
+          tc05::mma_bf16(tmem_base, da, tc05::desc_k_sw128(sb + kk * 32), a.idesc, (uint32_t)((it | kk) != 0));
+        }
         tc05::commit(&empty[s]);
       }
       if (nkb > 0) tc05::commit(t_full);
@@ -433,18 +464,24 @@ size_t skinny_gemm_workspace(int op, int B, int Cin, int Cout) {
   return sk_align((size_t)p.BN * p.Kp * 2) + (p.nsplit > 1 ? sk_align((size_t)p.nsplit * p.M * p.N * 4) : 0) + 2048;
 }
 
-struct SkAdam { float* m; float* v; const VcAdamDeviceStep* step; float lr, b1, b2, eps, bc1, bc2; };
+struct SkAdam { float* m; float* v; const VcAdamDeviceStep* step; float lr, b1, b2, eps, bc1, bc2; __nv_bfloat16* shadow; };
 static int skinny_gemm_run_impl(int op, const float* in0, const float* in1, const float* bias, float* out, int B, int Cin,
-                                int Cout, int relu, void* ws, size_t wsb, cudaStream_t s, const SkAdam* adam);
+                                int Cout, int relu, void* ws, size_t wsb, cudaStream_t s, const SkAdam* adam,
+                                const __nv_bfloat16* w_shadow);
 
 int skinny_gemm_run(int op, const float* in0, const float* in1, const float* bias, float* out, int B, int Cin, int Cout,
                     int relu, void* ws, size_t wsb, cudaStream_t s) {
-  return skinny_gemm_run_impl(op, in0, in1, bias, out, B, Cin, Cout, relu, ws, wsb, s, nullptr);
+  return skinny_gemm_run_impl(op, in0, in1, bias, out, B, Cin, Cout, relu, ws, wsb, s, nullptr, nullptr);
 }
 
+// w_shadow != null (forward / data gradient only): the weight operand is read from its bf16 copy [Cout][Cin] by TMA
 static int skinny_gemm_run_impl(int op, const float* in0, const float* in1, const float* bias, float* out, int B, int Cin,
-                                int Cout, int relu, void* ws, size_t wsb, cudaStream_t s, const SkAdam* adam) {
-  const SkPlan p = sk_plan(op, B, Cin, Cout, in0, in1);
+                                int Cout, int relu, void* ws, size_t wsb, cudaStream_t s, const SkAdam* adam,
+                                const __nv_bfloat16* w_shadow) {
+  const SkPlan p = sk_plan(op, B, Cin, Cout, w_shadow ? nullptr : in0, w_shadow ? nullptr : in1);
+  if (w_shadow) VC_REQUIRE(p.ok && op != VC_OP_LINEAR_WGRAD && p.a_from == 1 && Cin % 8 == 0 &&
+                               (reinterpret_cast<uintptr_t>(w_shadow) & 15) == 0,
+                           VC_ERR_UNSUPPORTED, "skinny_gemm: the bf16-shadow path serves forward / data gradient of aligned weights");
   if (adam) VC_REQUIRE(p.ok && p.nsplit == 1 && op == VC_OP_LINEAR_WGRAD && p.M % 4 == 0 && p.N % 4 == 0 && p.ldo % 4 == 0 &&
                            ((reinterpret_cast<uintptr_t>(out) | reinterpret_cast<uintptr_t>(adam->m) |
                              reinterpret_cast<uintptr_t>(adam->v)) & 15) == 0,
@@ -470,7 +507,16 @@ static int skinny_gemm_run_impl(int op, const float* in0, const float* in1, cons
     }
     VC_LAUNCH_CHECK();
   }
-  CUtensorMap mb;
+  CUtensorMap mb, ma;
+  memset(&ma, 0, sizeof(ma));
+  if (w_shadow) {   // bf16 [Cout][Cin]: K-major boxes [128 m][64 k] (forward) or MN-major boxes [64 k][64 m] (data gradient)
+    const uint64_t dims[2] = {(uint64_t)Cin, (uint64_t)Cout};
+    const uint64_t str[1] = {(uint64_t)Cin * 2};
+    const uint32_t box[2] = {64u, p.a_mcontig ? 64u : 128u};
+    int rc = tma::make_map(&ma, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<__nv_bfloat16*>(w_shadow), dims, str, box,
+                           CU_TENSOR_MAP_SWIZZLE_128B);
+    if (rc != VC_OK) return rc;
+  }
   {
     const uint64_t dims[2] = {(uint64_t)p.Kp, (uint64_t)p.BN};
     const uint64_t str[1] = {(uint64_t)p.Kp * 2};
@@ -485,10 +531,11 @@ static int skinny_gemm_run_impl(int op, const float* in0, const float* in1, cons
   a.out = out; a.ldo = p.ldo; a.transposed = p.transposed;
   a.bias = p.has_bias ? bias : nullptr; a.relu = relu;
   a.part = part; a.nkb = p.nkb; a.kbs = p.kbs; a.stages = p.stages;
-  a.idesc = tc05::idesc(tc05::kFmtBF16, 128, p.BN, 0, 0);
+  a.a_bf16 = w_shadow ? 1 : 0;
+  a.idesc = tc05::idesc(tc05::kFmtBF16, 128, p.BN, (w_shadow && p.a_mcontig) ? 1 : 0, 0);
   size_t ring = (size_t)p.stages * (SK_A_BYTES + (size_t)p.BN * 128);
   if (adam) {
-    a.adam = 1; a.ad_m = adam->m; a.ad_v = adam->v; a.ad_step = adam->step;
+    a.adam = 1; a.ad_m = adam->m; a.ad_v = adam->v; a.ad_step = adam->step; a.ad_shadow = adam->shadow;
     a.ad_lr = adam->lr; a.ad_b1 = adam->b1; a.ad_b2 = adam->b2; a.ad_eps = adam->eps; a.ad_bc1 = adam->bc1; a.ad_bc2 = adam->bc2;
     // the non-transposed epilogue transposes 8 x (32 x 33) floats through the operand ring; the barriers sit behind it
     VC_REQUIRE(ring >= 8 * 32 * 36 * 4, VC_ERR_UNSUPPORTED, "skinny_gemm: operand ring too small for the Adam epilogue");
@@ -496,7 +543,7 @@ static int skinny_gemm_run_impl(int op, const float* in0, const float* in1, cons
   const size_t smem = ring + (2 * p.stages + 1) * 8 + 16 + 1024;
   VC_CUDA(cudaFuncSetAttribute(skinny_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   dim3 grid((unsigned)((p.M + 127) / 128), (unsigned)p.nsplit);
-  skinny_gemm_kernel<<<grid, SK_THREADS, smem, s>>>(a, mb);
+  skinny_gemm_kernel<<<grid, SK_THREADS, smem, s>>>(a, mb, ma);
   VC_LAUNCH_CHECK();
   if (part) {
     const int64_t MN = (int64_t)p.M * p.N;
@@ -519,14 +566,36 @@ extern "C" size_t vc_linear_wgrad_adam_workspace_bytes(int B, int Cin, int Cout)
   return skinny_gemm_workspace(VC_OP_LINEAR_WGRAD, B, Cin, Cout);
 }
 
-extern "C" int vc_linear_wgrad_adam(const float* dy, const float* x, float* W, float* exp_avg, float* exp_avg_sq, int B,
-                                    int Cin, int Cout, float lr, float beta1, float beta2, float eps, float bias_corr1,
-                                    float bias_corr2, const VcAdamDeviceStep* step_state, void* workspace,
-                                    size_t workspace_bytes, void* stream) {
+extern "C" int vc_linear_wgrad_adam(const float* dy, const float* x, float* W, float* exp_avg, float* exp_avg_sq,
+                                    void* w_shadow, int B, int Cin, int Cout, float lr, float beta1, float beta2, float eps,
+                                    float bias_corr1, float bias_corr2, const VcAdamDeviceStep* step_state,
+                                    void* workspace, size_t workspace_bytes, void* stream) {
   VC_REQUIRE(dy && x && W && exp_avg && exp_avg_sq, VC_ERR_BAD_ARG, "vc_linear_wgrad_adam: null pointer");
   VC_REQUIRE(vc_linear_wgrad_adam_supported(B, Cin, Cout), VC_ERR_UNSUPPORTED,
              "vc_linear_wgrad_adam: unsupported shape (B %d, Cin %d, Cout %d)", B, Cin, Cout);
-  SkAdam ad = {exp_avg, exp_avg_sq, step_state, lr, beta1, beta2, eps, bias_corr1, bias_corr2};
+  VC_REQUIRE((reinterpret_cast<uintptr_t>(w_shadow) & 7) == 0, VC_ERR_BAD_ARG, "vc_linear_wgrad_adam: misaligned shadow");
+  SkAdam ad = {exp_avg, exp_avg_sq, step_state, lr, beta1, beta2, eps, bias_corr1, bias_corr2,
+               static_cast<__nv_bfloat16*>(w_shadow)};
   return skinny_gemm_run_impl(VC_OP_LINEAR_WGRAD, dy, x, nullptr, W, B, Cin, Cout, 0, workspace, workspace_bytes,
-                              as_stream(stream), &ad);
+                              as_stream(stream), &ad, nullptr);
+}
+
+extern "C" int vc_linear_bf16w_supported(int op, int B, int Cin, int Cout) {
+  if (op != VC_OP_LINEAR_FWD && op != VC_OP_LINEAR_DGRAD) return 0;
+  const SkPlan p = sk_plan(op, B, Cin, Cout, nullptr, nullptr);
+  return (p.ok && p.a_from == 1 && Cin % 8 == 0) ? 1 : 0;
+}
+
+extern "C" size_t vc_linear_bf16w_workspace_bytes(int op, int B, int Cin, int Cout) {
+  return skinny_gemm_workspace(op, B, Cin, Cout);
+}
+
+extern "C" int vc_linear_bf16w(int op, const float* in, const void* w_shadow, const float* bias, float* out, int B, int Cin,
+                               int Cout, int relu, void* workspace, size_t workspace_bytes, void* stream) {
+  VC_REQUIRE(in && w_shadow && out, VC_ERR_BAD_ARG, "vc_linear_bf16w: null pointer");
+  VC_REQUIRE(vc_linear_bf16w_supported(op, B, Cin, Cout), VC_ERR_UNSUPPORTED,
+             "vc_linear_bf16w: unsupported op / shape (op %d, B %d, Cin %d, Cout %d)", op, B, Cin, Cout);
+  // in1 of the fp32 path is the weight; only its bf16 shadow is read here
+  return skinny_gemm_run_impl(op, in, nullptr, bias, out, B, Cin, Cout, relu, workspace, workspace_bytes, as_stream(stream),
+                              nullptr, static_cast<const __nv_bfloat16*>(w_shadow));
 }

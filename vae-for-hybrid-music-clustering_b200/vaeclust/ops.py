@@ -91,7 +91,15 @@ class _DenseFn(torch.autograd.Function):
                 raise VaeclustError(f"convT2d_s2k4: weight {tuple(weight.shape)} does not match Cin={Cin}, k=4")
             yshape = (B, Cout, 2 * H, 2 * W)
         y = torch.empty(yshape, dtype=torch.float32, device=x.device)
-        _dense(_OPS[kind][0], prec, x, weight, bias, y, B, Cin, H, W, Cout, relu)
+        # wide Linear layers inside a fused training step: read the weight from its bf16 shadow (train.VAEStep keeps it)
+        sh = getattr(weight, "_vc_shadow", None) if kind == "linear" and prec == _PREC["bf16"] else None
+        if sh is not None and not lib().size("vc_linear_bf16w_supported", 0, B, Cin, Cout):
+            sh = None
+        if sh is not None:
+            _linear_bf16w(0, x, sh, bias, y, B, Cin, Cout, relu)
+        else:
+            _dense(_OPS[kind][0], prec, x, weight, bias, y, B, Cin, H, W, Cout, relu)
+        ctx.shadow = sh
         ctx.kind, ctx.prec, ctx.relu, ctx.has_bias = kind, prec, bool(relu), bias is not None
         # single-GPU training: the optimizer that wants this (wide Linear) weight updated straight from the
         # weight-gradient kernel's accumulator (train.VAEStep sets and clears the attribute around a step)
@@ -150,11 +158,14 @@ class _DenseFn(torch.autograd.Function):
             g = dy
         if ctx.needs_input_grad[1]:
             dx = torch.empty_like(x)
-            _dense(op_d, ctx.prec, g, weight, None, dx, B, Cin, H, W, Cout, False)
+            if ctx.shadow is not None and lib().size("vc_linear_bf16w_supported", 1, B, Cin, Cout):
+                _linear_bf16w(1, g, ctx.shadow, None, dx, B, Cin, Cout, False)
+            else:
+                _dense(op_d, ctx.prec, g, weight, None, dx, B, Cin, H, W, Cout, False)
         if ctx.needs_input_grad[2]:
             if (ctx.adam is not None and ctx.prec == _PREC["bf16"]
                     and lib().size("vc_linear_wgrad_adam_supported", B, Cin, Cout)):
-                _linear_wgrad_adam(ctx.adam, ctx.wparam, g, x, B, Cin, Cout)      # no dW: the update happens here
+                _linear_wgrad_adam(ctx.adam, ctx.wparam, g, x, B, Cin, Cout, ctx.shadow)   # no dW: the update happens here
             else:
                 dw = torch.empty_like(weight)
                 _dense(op_w, ctx.prec, g, x, None, dw, B, Cin, H, W, Cout, False)
@@ -165,7 +176,13 @@ class _DenseFn(torch.autograd.Function):
         return None, dx, dw, db, None
 
 
-def _linear_wgrad_adam(opt, p, g, x, B, Cin, Cout) -> None:
+def _linear_bf16w(op, inp, shadow, bias, out, B, Cin, Cout, relu) -> None:
+    ws = _workspace(lib().size("vc_linear_bf16w_workspace_bytes", op, B, Cin, Cout), out.device)
+    lib().call("vc_linear_bf16w", op, ptr(inp), ptr(shadow), ptr(bias), ptr(out), B, Cin, Cout, int(relu), ptr(ws), ws.numel(),
+               stream_ptr())
+
+
+def _linear_wgrad_adam(opt, p, g, x, B, Cin, Cout, shadow=None) -> None:
     """dW = g^T x formed in tensor memory and applied to p / exp_avg / exp_avg_sq by the same kernel
     (vc_linear_wgrad_adam); the optimizer's later step() skips p because its .grad stays None."""
     st = opt._state(p)
@@ -178,7 +195,8 @@ def _linear_wgrad_adam(opt, p, g, x, B, Cin, Cout) -> None:
         st["step"] += 1
         step_ptr, bc1, bc2 = None, 1.0 - b1 ** st["step"], 1.0 - b2 ** st["step"]
     ws = _workspace(lib().size("vc_linear_wgrad_adam_workspace_bytes", B, Cin, Cout), x.device)
-    lib().call("vc_linear_wgrad_adam", ptr(g), ptr(x), ptr(p.data), ptr(st["exp_avg"]), ptr(st["exp_avg_sq"]), B, Cin, Cout,
+    lib().call("vc_linear_wgrad_adam", ptr(g), ptr(x), ptr(p.data), ptr(st["exp_avg"]), ptr(st["exp_avg_sq"]), ptr(shadow), B,
+               Cin, Cout,
                float(opt.param_groups[0]["lr"]), b1, b2, opt.eps, bc1, bc2, step_ptr, ptr(ws), ws.numel(), stream_ptr())
 
 

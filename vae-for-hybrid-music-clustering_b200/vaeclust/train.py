@@ -64,6 +64,10 @@ class VAEStep:
         self.fuse_fc_adam = os.environ.get("VAECLUST_FUSE_FC_ADAM", "1") != "0"
         wide = int(os.environ.get("VAECLUST_FUSE_FC_ADAM_NUMEL", str(1 << 24)))
         self._wide = [m.weight for m in model.modules() if isinstance(m, torch.nn.Linear) and m.weight.numel() >= wide]
+        # bf16 shadows of those weights (forward / data gradient read them by TMA; the fused update refreshes them):
+        # id(p) -> (tensor, p._version, p.data_ptr()) -- rebuilt when the parameter was changed by anything else
+        self.bf16_shadows = os.environ.get("VAECLUST_FC_SHADOW", "1") != "0"
+        self._shadow = {}
         self.mode = VC_LOSS_SUM_MEAN if kind == "mlp19" else VC_LOSS_MEAN_MEAN
         self.multi = group is not None and vdist.world_size(group) > 1
         self.opt = Adam(model.parameters(), lr=lr, capturable=capturable)
@@ -93,11 +97,21 @@ class VAEStep:
                 self.opt.begin_step()            # capturable: the device step counter advances here, once
                 for p in fused:
                     p._vc_adam = self.opt
+                    if self.bf16_shadows:
+                        sh = self._shadow.get(id(p))
+                        if sh is None or sh[1] != p._version or sh[2] != p.data_ptr():
+                            if sh is None:
+                                sh = (torch.empty(p.shape, dtype=torch.bfloat16, device=p.device), 0, 0)
+                            sh[0].copy_(p.detach())          # (in place: a captured graph keeps reading this buffer)
+                            sh = (sh[0], p._version, p.data_ptr())
+                            self._shadow[id(p)] = sh
+                        p._vc_shadow = sh[0]
         try:
             return self._run(m, x, extra, eps, fused)
         finally:
             for p in fused:
                 p._vc_adam = None
+                p._vc_shadow = None
 
     def _run(self, m, x, extra, eps, fused):
         if self.kind == "conv12":
