@@ -115,6 +115,8 @@ def flops_of(name: str, sig) -> float:
             return 2.0 * M * N * K
         if name == "vc_linear_wgrad_adam":
             return 2.0 * sig[0] * sig[1] * sig[2]
+        if name == "vc_linear_bf16w":
+            return 2.0 * sig[1] * sig[2] * sig[3]
         if name in ("vc_conv_nhwc", "vc_conv_nhwc_wgrad"):
             op, B, Cin, H, W, Cout = (sig[0],) + tuple(sig[2:7]) if name == "vc_conv_nhwc" else tuple(sig[:6])
             if op <= 5:
@@ -174,6 +176,9 @@ def bytes_of(name: str, sig) -> float:
         if name == "vc_linear_wgrad_adam":      # p, m, v read and written once; the gradient never touches memory
             B, Cin, Cout = sig[:3]
             return 24.0 * Cin * Cout + 4.0 * B * (Cin + Cout)
+        if name == "vc_linear_bf16w":           # bf16 weight shadow read once, fp32 activations in and out
+            _op, B, Cin, Cout = sig[:4]
+            return 2.0 * Cin * Cout + 4.0 * B * (Cin + Cout)
         if name == "vc_conv1_wgrad_bias":
             B, H, W, Cout = sig[:4]
             return 4.0 * B * (H * W + Cout * (H // 2) * (W // 2))
@@ -190,6 +195,8 @@ def family_of(name: str, sig) -> str:
         return "conv_nhwc (TMA-fed fwd / dgrad)" if name == "vc_conv_nhwc" else "conv_nhwc_wgrad (TMA-fed)"
     if name == "vc_linear_wgrad_adam":
         return "skinny_gemm wgrad + Adam (FC 262144<->256)"
+    if name == "vc_linear_bf16w":
+        return "skinny_gemm from the bf16 shadow (FC fwd / dgrad)"
     if name in ("vc_nhwc_conv1_fwd", "vc_nhwc_convT1_dgrad", "vc_conv1_wgrad_bias"):
         return "conv_direct (1-channel ends)"
     if name != "vc_dense_op":
