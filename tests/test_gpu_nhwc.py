@@ -314,3 +314,32 @@ def test_wide_linear_from_bf16_shadow(Cin, Cout):
         if op == 0:
             ref = torch.relu(ref + b)
         torch.testing.assert_close(got, ref, rtol=1e-4, atol=1e-4 * float(ref.abs().max()))
+
+
+def test_shadows_follow_external_parameter_changes(monkeypatch):
+    """A graph-replayed fused step must see a parameter change made between steps by something else (here an in-place
+    scaling, as load_state_dict would do): the bf16 shadow is rebuilt before the replay."""
+    from vaeclust import nn, ops, train
+    monkeypatch.setenv("VAECLUST_FUSE_FC_ADAM_NUMEL", str(1 << 22))
+    ops.set_precision("bf16")
+    try:
+        B = 64
+        x, lyr = _r(B, 1, 64, 1024, seed=1), _r(B, 384, seed=2)
+        m = torch.ones(B, 1, device="cuda")
+        eps = _r(B, 32, seed=3)
+        losses = {}
+        for fuse in (False, True):
+            torch.manual_seed(0)
+            model = nn.ConvMultiModalVAE(1, (64, 1024), 32, 384).cuda()
+            step = train.GraphedVAEStep(model, "conv12", lr=2e-3, beta=1e-3, warmup=1)
+            step.step.fuse_fc_adam = fuse
+            out = [float(step(x, lyr, m, eps=eps)[0]) for _ in range(3)]       # eager, capture, replay
+            with torch.no_grad():
+                model.audio_dec.fc[2].weight.add_(0.02)      # shifts every decoder activation: the loss moves visibly
+                model.audio_enc.fc[0].weight.mul_(1.5)
+            out.append(float(step(x, lyr, m, eps=eps)[0]))                       # replay after the change
+            losses[fuse] = out
+        assert abs(losses[True][3] - losses[True][2]) > 1e-3 * abs(losses[True][2])      # the change is visible
+        torch.testing.assert_close(torch.tensor(losses[True]), torch.tensor(losses[False]), rtol=2e-4, atol=0)
+    finally:
+        ops.set_precision("fp32")

@@ -95,23 +95,31 @@ class VAEStep:
             if self.fuse_fc_adam and self._wide and ops.PRECISION == "bf16":
                 fused = self._wide
                 self.opt.begin_step()            # capturable: the device step counter advances here, once
+                if self.bf16_shadows:
+                    self.refresh_shadows()
                 for p in fused:
                     p._vc_adam = self.opt
                     if self.bf16_shadows:
-                        sh = self._shadow.get(id(p))
-                        if sh is None or sh[1] != p._version or sh[2] != p.data_ptr():
-                            if sh is None:
-                                sh = (torch.empty(p.shape, dtype=torch.bfloat16, device=p.device), 0, 0)
-                            sh[0].copy_(p.detach())          # (in place: a captured graph keeps reading this buffer)
-                            sh = (sh[0], p._version, p.data_ptr())
-                            self._shadow[id(p)] = sh
-                        p._vc_shadow = sh[0]
+                        p._vc_shadow = self._shadow[id(p)][0]
         try:
             return self._run(m, x, extra, eps, fused)
         finally:
             for p in fused:
                 p._vc_adam = None
                 p._vc_shadow = None
+
+    @torch.no_grad()
+    def refresh_shadows(self) -> None:
+        """Bring the bf16 shadows of the wide weights up to date with parameters that something other than the fused
+        update changed (load_state_dict, an ordinary optimizer step): torch bumps `_version` on every in-place write, the
+        C-ABI kernels do not.  Called at the start of every eager step and before every graph replay."""
+        for p in self._wide:
+            sh = self._shadow.get(id(p))
+            if sh is None or sh[1] != p._version or sh[2] != p.data_ptr():
+                if sh is None:
+                    sh = (torch.empty(p.shape, dtype=torch.bfloat16, device=p.device), 0, 0)
+                sh[0].copy_(p.detach())          # in place: a captured graph keeps reading this buffer
+                self._shadow[id(p)] = (sh[0], p._version, p.data_ptr())
 
     def _run(self, m, x, extra, eps, fused):
         if self.kind == "conv12":
@@ -209,6 +217,8 @@ class GraphedVAEStep:
                     s.copy_(t, non_blocking=True)
             if eps is not None:
                 self.static_eps.copy_(eps, non_blocking=True)
+        if getattr(self.step, "_shadow", None):      # parameters changed from outside since the last step?
+            self.step.refresh_shadows()
         self.graph.replay()
         return self.out
 
