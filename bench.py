@@ -182,6 +182,9 @@ def bytes_of(name: str, sig) -> float:
         if name == "vc_conv1_wgrad_bias":
             B, H, W, Cout = sig[:4]
             return 4.0 * B * (H * W + Cout * (H // 2) * (W // 2))
+        if name == "vc_convT1_wgrad":             # x [B,Cin,H,W] and dy [B,1,2H,2W] read once, fp32
+            B, Cin, H, W = sig[:4]
+            return 4.0 * B * H * W * (Cin + 4)
         if name == "vc_relu_bwd_bias_nhwc":
             return 14.0 * sig[0] * sig[1] * sig[2] * sig[3]
     except Exception:
@@ -197,7 +200,7 @@ def family_of(name: str, sig) -> str:
         return "skinny_gemm wgrad + Adam (FC 262144<->256)"
     if name == "vc_linear_bf16w":
         return "skinny_gemm from the bf16 shadow (FC fwd / dgrad)"
-    if name in ("vc_nhwc_conv1_fwd", "vc_nhwc_convT1_dgrad", "vc_conv1_wgrad_bias"):
+    if name in ("vc_nhwc_conv1_fwd", "vc_nhwc_convT1_dgrad", "vc_conv1_wgrad_bias", "vc_convT1_wgrad"):
         return "conv_direct (1-channel ends)"
     if name != "vc_dense_op":
         return name

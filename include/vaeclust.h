@@ -122,6 +122,13 @@ int vc_convT2d_s2k4_wgrad(const float* dy, const float* x, float* dW, int B, int
 size_t vc_conv1_wgrad_bias_workspace_bytes(int Cout);
 int vc_conv1_wgrad_bias(const float* dy, const float* x, float* dW, float* db, int B, int H, int Wd, int Cout, int round_bf16,
                         void* workspace, size_t workspace_bytes, void* stream);
+/* Weight gradient of nn.ConvTranspose2d(Cin, 1, 4, 2, 1) (12:137) in one pass over x [B,Cin,H,W] and dy [B,1,2H,2W]
+ * (fp32 NCHW): dW[ci][0][kh][kw] = sum x * dy(tap).  round_bf16 = 1 multiplies bf16-rounded operands (fp32 accumulation)
+ * and, for Cin in {16, 32, 64, 128} with W a multiple of 32, runs on the tensor cores (mma.sync); the same holds for
+ * vc_conv1_wgrad_bias above with Cout / W/2 in those roles. */
+size_t vc_convT1_wgrad_workspace_bytes(int Cin);
+int vc_convT1_wgrad(const float* dy, const float* x, float* dW, int B, int Cin, int H, int Wd, int round_bf16,
+                    void* workspace, size_t workspace_bytes, void* stream);
 /* TMA-fed weight gradients of the same layers (csrc/conv_nhwc_wgrad.cu; autograd of nn.Conv2d / nn.ConvTranspose2d at
  * 12:87-89,135-137).  op = VC_OP_CONV_WGRAD or VC_OP_CONVT_WGRAD, (B, Cin, H, W, Cout) the layer's forward geometry;
  * g_nhwc = bf16 NHWC gradient of the layer's output (ReLU mask already applied), x_nhwc = bf16 NHWC layer input; dW in the

@@ -102,6 +102,41 @@ def test_convT_data_gradient_with_mask(B, Cin, H, W, Cout):
     _check(*_run(OPS["convT_dgrad"], g, w, None, False, None, (B, Cin, H, W, Cout), want_nhwc=False), dx)
 
 
+@pytest.mark.parametrize("B,C,H,W", [(2, 32, 16, 256), (3, 16, 5, 64), (1, 64, 7, 96), (2, 128, 3, 32),
+                                     (2, 32, 4, 40), (1, 8, 6, 64)])   # the last two take the FFMA kernel
+def test_single_channel_weight_gradients_tensor_core(B, C, H, W):
+    """vc_conv1_wgrad_bias / vc_convT1_wgrad with round_bf16 = 1: C in {16, 32, 64, 128} and rows of 32-pixel segments run
+    tap_wgrad_mma_kernel (mma.sync on bf16-rounded operands, fp32 accumulation), other shapes the FFMA kernel with the
+    same rounding.  Against torch autograd on the rounded operands only the summation order differs."""
+    from vaeclust._lib import lib, ptr, stream_ptr
+    L = lib()
+    a, S = _r(B, C, H, W, seed=21), _r(B, 1, 2 * H, 2 * W, seed=22)
+    # Conv2d(1 -> C): a = gradient of the output [H, W], S = the input [2H, 2W]
+    dw, db = torch.full((C, 1, 3, 3), float("nan"), device="cuda"), torch.full((C,), float("nan"), device="cuda")
+    ws = torch.empty(L.size("vc_conv1_wgrad_bias_workspace_bytes", C), dtype=torch.uint8, device="cuda")
+    for _ in range(2):      # second call: same bits (fixed-order reduction)
+        prev = dw.clone()
+        L.call("vc_conv1_wgrad_bias", ptr(a), ptr(S), ptr(dw), ptr(db), B, 2 * H, 2 * W, C, 1, ptr(ws), ws.numel(), stream_ptr())
+    assert torch.equal(prev, dw)
+    wr = torch.zeros(C, 1, 3, 3, device="cuda", dtype=torch.float64, requires_grad=True)
+    F.conv2d(_bf(S).double(), wr, None, stride=2, padding=1).backward(_bf(a).double())
+    torch.testing.assert_close(dw.double(), wr.grad, rtol=2e-5, atol=2e-5 * float(wr.grad.abs().max()))
+    wantb = a.double().sum(dim=(0, 2, 3))
+    torch.testing.assert_close(db.double(), wantb, rtol=1e-5, atol=1e-5 * float(wantb.abs().max()) + 1e-4)
+    # ConvTranspose2d(C -> 1): a = the layer input [H, W], S = gradient of the output [2H, 2W]
+    dwt = torch.full((C, 1, 4, 4), float("nan"), device="cuda")
+    ws = torch.empty(L.size("vc_convT1_wgrad_workspace_bytes", C), dtype=torch.uint8, device="cuda")
+    L.call("vc_convT1_wgrad", ptr(S), ptr(a), ptr(dwt), B, C, H, W, 1, ptr(ws), ws.numel(), stream_ptr())
+    wr = torch.zeros(C, 1, 4, 4, device="cuda", dtype=torch.float64, requires_grad=True)
+    F.conv_transpose2d(_bf(a).double(), wr, None, stride=2, padding=1).backward(_bf(S).double())
+    torch.testing.assert_close(dwt.double(), wr.grad, rtol=2e-5, atol=2e-5 * float(wr.grad.abs().max()))
+    # round_bf16 = 0 keeps the fp32 values (FFMA kernel)
+    L.call("vc_convT1_wgrad", ptr(S), ptr(a), ptr(dwt), B, C, H, W, 0, ptr(ws), ws.numel(), stream_ptr())
+    wr = torch.zeros(C, 1, 4, 4, device="cuda", dtype=torch.float64, requires_grad=True)
+    F.conv_transpose2d(a.double(), wr, None, stride=2, padding=1).backward(S.double())
+    torch.testing.assert_close(dwt.double(), wr.grad, rtol=2e-5, atol=2e-5 * float(wr.grad.abs().max()))
+
+
 def test_single_channel_ends_and_helpers():
     from vaeclust._lib import lib, ptr, stream_ptr
     L = lib()

@@ -384,6 +384,173 @@ tap_wgrad_kernel(const float* __restrict__ A, const float* __restrict__ S, doubl
   }
 }
 
+// ---- the same correlation on the tensor cores (bf16 mode): per 32-pixel row segment and 16 channels,
+//   D[16 ch][16 taps] += A[16 ch x 32 px] * Sim2col[32 px x 16 taps]      (2 k-steps x 2 tap tiles of mma.sync m16n8k16)
+// instead of 16 x 32 x T scalar FMAs -- the FFMA kernel above is instruction-issue bound (25 instructions per element of A).
+// The K index (pixel) may be permuted freely as long as both fragments agree: thread (g, t) owns the EIGHT consecutive
+// pixels 8t .. 8t+7 of the segment, so A comes as two 16-byte loads per channel row (rows g and g+8); pixel 8t+e sits in
+// k-step e >> 2 at fragment column 2t + (e & 1) + 8 ((e >> 1) & 1).  The S patch of the segment (KS rows x 66..67 values,
+// bf16-rounded) is staged in shared memory per warp; B fragment element (k, n = tap) = S[2 p - 1 + tw] of row th.
+// BIAS: per-channel sums of the unrounded A (Conv2d(1 -> C): A is the output gradient).
+__device__ __forceinline__ void tap_mma16816(float (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+  asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+               : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+               : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+__device__ __forceinline__ uint32_t tap_pack(float lo, float hi) {
+  __nv_bfloat162 h = __floats2bfloat162_rn(lo, hi);
+  return *reinterpret_cast<uint32_t*>(&h);
+}
+
+__device__ __forceinline__ float2 ldg_pred2(const float* p, uint32_t pred) {   // 8-byte variant of ldg_pred
+  float2 v;
+  asm("{\n\t.reg .pred q;\n\tsetp.ne.b32 q, %3, 0;\n\tmov.f32 %0, 0f00000000;\n\tmov.f32 %1, 0f00000000;\n\t"
+      "@q ld.global.nc.v2.f32 {%0, %1}, [%2];\n\t}"
+      : "=f"(v.x), "=f"(v.y)
+      : "l"(p), "r"(pred));
+  return v;
+}
+
+// One unit = one 32-pixel row segment x 16 channels.  Its loads (A: four 16-byte loads per thread; S: per tap row one
+// 8-byte load per lane for columns 2 j0 .. 2 j0 + 63 and one scalar for the halo columns 2 j0 - 1 (lane 0) and
+// 2 j0 + 64 (lane 1)) are all issued before anything waits on them, and the loads of the NEXT unit go out before the
+// MMAs of this one (one memory round trip per unit, overlapped with the previous unit's arithmetic).
+template <int KS>
+struct TapUnit {
+  float4 x0, x1, y0, y1;
+  float2 sv[KS];
+  float sh[KS];
+};
+// (b, i, seg) = image, row and 32-pixel segment of the unit; offsets are 32-bit (host: both tensors < 2^31 elements)
+template <int KS>
+__device__ __forceinline__ void tap_unit_load(TapUnit<KS>& q, const float* __restrict__ A, const float* __restrict__ S, int b,
+                                              int i, int seg, int C, int PH, int PW, int SH, int SW, int cg, int t, int lane) {
+  const int j0 = seg * 32;
+  const int aplane = PH * PW;
+  const float* ap = A + (uint32_t)(((b * C + cg) * PH + i) * PW + j0 + 8 * t);      // cg = first channel of the tile + g
+  q.x0 = __ldcs(reinterpret_cast<const float4*>(ap));
+  q.x1 = __ldcs(reinterpret_cast<const float4*>(ap) + 1);
+  q.y0 = __ldcs(reinterpret_cast<const float4*>(ap + (uint32_t)(8 * aplane)));
+  q.y1 = __ldcs(reinterpret_cast<const float4*>(ap + (uint32_t)(8 * aplane)) + 1);
+  // row 2i - 1 of the patch may lie above the image (i = 0), row 2i - 1 + (KS - 1) below it (KS = 4, i = PH - 1): the
+  // offset of a row that does not exist is never dereferenced (predicated loads), so it may wrap
+  const int hcol = lane == 0 ? -1 : 64;                     // halo column of lanes 0 / 1 (relative to 2 j0)
+  const uint32_t hcok = lane < 2 && (unsigned)(2 * j0 + hcol) < (unsigned)SW ? 1u : 0u;
+  const int h0 = 2 * i - 1;
+  const float* sb = S + (int64_t)((b * SH + h0) * SW + 2 * j0);
+#pragma unroll
+  for (int th = 0; th < KS; ++th) {
+    const uint32_t hok = (unsigned)(h0 + th) < (unsigned)SH ? 1u : 0u;
+    const float* rowp = sb + th * SW;
+    q.sv[th] = ldg_pred2(rowp + 2 * lane, hok);
+    q.sh[th] = ldg_pred(rowp + hcol, hok & hcok);
+  }
+}
+
+template <int KS, bool BIAS>
+__global__ void __launch_bounds__(256, 3)
+tap_wgrad_mma_kernel(const float* __restrict__ A, const float* __restrict__ S, double* __restrict__ part, int B, int C,
+                     int PH, int PW, int SH, int SW, double* __restrict__ bpart) {
+  constexpr int T = KS * KS, RW = 72;
+  // srow[w][th][4 + c] = S[row th of the patch][2 j0 + c], c = -1 .. 64 (the +4 keeps the 8-byte stores aligned)
+  __shared__ __align__(16) float srow[8][KS][RW];
+  __shared__ float red[8][16][17];
+  __shared__ float bred[8][16];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int g = lane >> 2, t = lane & 3;
+  const int CT = C >> 4;                                   // 16-channel tiles
+  const int gw = blockIdx.x * 8 + warp;                    // consecutive warps share a segment (L1 hits on S), differ in tile
+  const int ct = gw % CT;
+  const int segs = PW >> 5;
+  const int units = B * PH * segs;                         // (host: < 2^31)
+  const int ustride = (int)gridDim.x * 8 / CT;
+  float d[2][4];
+#pragma unroll
+  for (int nt = 0; nt < 2; ++nt)
+#pragma unroll
+    for (int e = 0; e < 4; ++e) d[nt][e] = 0.f;
+  float bs0 = 0.f, bs1 = 0.f;
+  // tap (n = g for tile 0, g + 8 for tile 1) -> patch row / column offset; taps >= T contribute zeros
+  const int tap0 = g, tap1 = g + 8;
+  const int th0 = tap0 / KS, tw0 = tap0 % KS, th1 = tap1 < T ? tap1 / KS : 0, tw1 = tap1 < T ? tap1 % KS : 0;
+  // S index of pixel 8t + e of the segment for tap column tw: 2 (8t + e) - 1 + tw  ->  srow[..][3 + 16 t + 2 e + tw]
+  const float* p0 = &srow[warp][th0][3 + 16 * t + tw0];
+  const float* p1 = &srow[warp][th1][3 + 16 * t + tw1];
+  TapUnit<KS> q;
+  // (nb, ni, ns): the unit whose loads go out next; advanced by ustride units as a mixed-radix addition (no division in the loop)
+  int u = gw / CT;
+  int ns = u % segs, ni = (u / segs) % PH, nb = u / segs / PH;
+  const int ds = ustride % segs, di = (ustride / segs) % PH, db = ustride / segs / PH;
+  const int cg = ct * 16 + g;
+  auto advance = [&]() {
+    ns += ds;
+    if (ns >= segs) { ns -= segs; ++ni; }
+    ni += di;
+    if (ni >= PH) { ni -= PH; ++nb; }
+    nb += db;
+  };
+  if (u < units) tap_unit_load<KS>(q, A, S, nb, ni, ns, C, PH, PW, SH, SW, cg, t, lane);
+  advance();
+  for (; u < units; u += ustride) {
+    __syncwarp();                    // the previous unit's fragment reads are done
+#pragma unroll
+    for (int th = 0; th < KS; ++th) {
+      *reinterpret_cast<float2*>(&srow[warp][th][4 + 2 * lane]) = q.sv[th];
+      if (lane < 2) srow[warp][th][lane == 0 ? 3 : 68] = q.sh[th];
+    }
+    if (BIAS) {
+      bs0 += ((q.x0.x + q.x0.y) + (q.x0.z + q.x0.w)) + ((q.x1.x + q.x1.y) + (q.x1.z + q.x1.w));
+      bs1 += ((q.y0.x + q.y0.y) + (q.y0.z + q.y0.w)) + ((q.y1.x + q.y1.y) + (q.y1.z + q.y1.w));
+    }
+    // A fragments: rows g / g + 8 of the channel tile, k = this thread's pixels 8t + {0,1 | 2,3} and {4,5 | 6,7}
+    const uint32_t a0[4] = {tap_pack(q.x0.x, q.x0.y), tap_pack(q.y0.x, q.y0.y), tap_pack(q.x0.z, q.x0.w), tap_pack(q.y0.z, q.y0.w)};
+    const uint32_t a1[4] = {tap_pack(q.x1.x, q.x1.y), tap_pack(q.y1.x, q.y1.y), tap_pack(q.x1.z, q.x1.w), tap_pack(q.y1.z, q.y1.w)};
+    if (u + ustride < units) tap_unit_load<KS>(q, A, S, nb, ni, ns, C, PH, PW, SH, SW, cg, t, lane);
+    advance();
+    __syncwarp();
+    // B fragments (the packed conversion rounds to bf16): k rows = the same pixels, n = tap
+    tap_mma16816(d[0], a0, tap_pack(p0[0], p0[2]), tap_pack(p0[4], p0[6]));
+    tap_mma16816(d[0], a1, tap_pack(p0[8], p0[10]), tap_pack(p0[12], p0[14]));
+    // every lane executes every mma (.aligned); lanes whose second-tile tap does not exist (KS = 3: taps 9..15) feed zeros
+    uint32_t q0 = tap_pack(p1[0], p1[2]), q1 = tap_pack(p1[4], p1[6]), q2 = tap_pack(p1[8], p1[10]), q3 = tap_pack(p1[12], p1[14]);
+    if (T < 16 && tap1 >= T) q0 = q1 = q2 = q3 = 0u;
+    tap_mma16816(d[1], a0, q0, q1);
+    tap_mma16816(d[1], a1, q2, q3);
+  }
+  // accumulator (row g / g + 8 = channel, column 2t / 2t + 1 = tap within the tile) -> block reduction in a fixed order
+#pragma unroll
+  for (int nt = 0; nt < 2; ++nt) {
+    red[warp][g][nt * 8 + 2 * t] = d[nt][0];
+    red[warp][g][nt * 8 + 2 * t + 1] = d[nt][1];
+    red[warp][g + 8][nt * 8 + 2 * t] = d[nt][2];
+    red[warp][g + 8][nt * 8 + 2 * t + 1] = d[nt][3];
+  }
+  if (BIAS) {
+    bs0 += __shfl_xor_sync(0xffffffffu, bs0, 1); bs0 += __shfl_xor_sync(0xffffffffu, bs0, 2);
+    bs1 += __shfl_xor_sync(0xffffffffu, bs1, 1); bs1 += __shfl_xor_sync(0xffffffffu, bs1, 2);
+    if (t == 0) { bred[warp][g] = bs0; bred[warp][g + 8] = bs1; }
+  }
+  __syncthreads();
+  // warps w with (blockIdx.x * 8 + w) % CT == tile hold that tile's partials
+  for (int e = threadIdx.x; e < C * T; e += blockDim.x) {
+    const int c = e / T, tp = e - c * T;
+    const int tile = c >> 4;
+    double v = 0.0;
+    for (int w = 0; w < 8; ++w)
+      if ((blockIdx.x * 8 + w) % CT == tile) v += (double)red[w][c & 15][tp];
+    part[((int64_t)blockIdx.x * C + c) * T + tp] = v;
+  }
+  if (BIAS) {
+    for (int c = threadIdx.x; c < C; c += blockDim.x) {
+      const int tile = c >> 4;
+      double v = 0.0;
+      for (int w = 0; w < 8; ++w)
+        if ((blockIdx.x * 8 + w) % CT == tile) v += (double)bred[w][c & 15];
+      bpart[(int64_t)blockIdx.x * C + c] = v;
+    }
+  }
+}
+
 // out[e] = sum over the nblk block partials part[blk][C*T].  A block owns 32 consecutive outputs; its eight warps each
 // add every eighth partial and the eight sub-sums are added in warp order (fixed order: bit-identical from run to run)
 __global__ void __launch_bounds__(256) tap_wgrad_fold_kernel(const double* __restrict__ part, int nblk, int n,
@@ -437,6 +604,40 @@ int conv_direct_wgrad_bias_run(int op, const float* dy, const float* x, float* d
   double* part = static_cast<double*>(ws);
   int nblk = 2 * sm_count();   // two 256-thread blocks per SM, every block walks all channels of its blockIdx.y
   if (nblk > kTapBlocks) nblk = kTapBlocks;
+  {  // bf16 mode, 16 / 32 / 64 / 128 channels, rows of 32-pixel segments: the tensor-core kernel (three blocks per SM)
+    const int C = op == VC_OP_CONV_WGRAD ? Cout : Cin;
+    const int PH = op == VC_OP_CONV_WGRAD ? (H - 1) / 2 + 1 : H, PW = op == VC_OP_CONV_WGRAD ? W / 2 : W;
+    const int SH = op == VC_OP_CONV_WGRAD ? H : 2 * H, SW = op == VC_OP_CONV_WGRAD ? W : 2 * W;
+    const float* A = op == VC_OP_CONV_WGRAD ? dy : x;
+    const float* S = op == VC_OP_CONV_WGRAD ? x : dy;
+    static const bool off = getenv("VAECLUST_TAP_MMA") && atoi(getenv("VAECLUST_TAP_MMA")) == 0;
+    const bool ct_ok = C == 16 || C == 32 || C == 64 || C == 128;
+    if (!off && round_bf16 && ct_ok && PW % 32 == 0 && (reinterpret_cast<uintptr_t>(A) & 15) == 0 &&
+        (op == VC_OP_CONVT_WGRAD ? !db : true)) {
+      const int T = op == VC_OP_CONV_WGRAD ? 9 : 16, CT = C / 16;
+      int nb = 3 * sm_count();
+      if (nb > kTapBlocks) nb = kTapBlocks;
+      const int64_t units = (int64_t)B * PH * (PW / 32);
+      VC_REQUIRE((int64_t)B * C * PH * PW < 2147483647LL, VC_ERR_UNSUPPORTED,
+                 "conv_direct_wgrad_bias_run: tensor too large for 32-bit element offsets");
+      if ((int64_t)nb * 8 / CT > units) nb = (int)((units * CT + 7) / 8);
+      double* bpart = db ? part + (size_t)kTapBlocks * C * T : nullptr;
+      if (op == VC_OP_CONVT_WGRAD)
+        tap_wgrad_mma_kernel<4, false><<<nb, 256, 0, s>>>(A, S, part, B, C, PH, PW, SH, SW, nullptr);
+      else if (db)
+        tap_wgrad_mma_kernel<3, true><<<nb, 256, 0, s>>>(A, S, part, B, C, PH, PW, SH, SW, bpart);
+      else
+        tap_wgrad_mma_kernel<3, false><<<nb, 256, 0, s>>>(A, S, part, B, C, PH, PW, SH, SW, nullptr);
+      VC_LAUNCH_CHECK();
+      tap_wgrad_fold_kernel<<<(C * T + 31) / 32, 256, 0, s>>>(part, nb, C * T, dw);
+      if (db) {
+        VC_LAUNCH_CHECK();
+        tap_wgrad_fold_kernel<<<(C + 31) / 32, 256, 0, s>>>(bpart, nb, C, db);
+      }
+      VC_LAUNCH_CHECK();
+      return VC_OK;
+    }
+  }
   if (op == VC_OP_CONV_WGRAD) {   // A = dy [B,Cout,OH,OW], S = x [B,1,H,W]
     constexpr int CG = 4, T = 9;
     const int OH = (H - 1) / 2 + 1, OW = W / 2, groups = Cout / CG;
@@ -510,6 +711,18 @@ int conv_direct_run(int op, const float* in0, const float* in1, const float* bia
 }  // namespace vc
 
 using namespace vc;
+
+extern "C" size_t vc_convT1_wgrad_workspace_bytes(int Cin) { return conv_direct_wgrad_workspace(VC_OP_CONVT_WGRAD, Cin, 1); }
+
+extern "C" int vc_convT1_wgrad(const float* dy, const float* x, float* dW, int B, int Cin, int H, int W, int round_bf16,
+                               void* workspace, size_t workspace_bytes, void* stream) {
+  VC_REQUIRE(dy && x && dW && B > 0, VC_ERR_BAD_ARG, "vc_convT1_wgrad: bad arguments");
+  VC_REQUIRE(conv_direct_wgrad_supported(VC_OP_CONVT_WGRAD, B, Cin, H, W, 1) &&
+                 ((reinterpret_cast<uintptr_t>(dy) | reinterpret_cast<uintptr_t>(x)) & 15) == 0,
+             VC_ERR_UNSUPPORTED, "vc_convT1_wgrad: need Cin %% 4 == 0, Cin <= 512, W %% 4 == 0, 16-byte aligned tensors");
+  return conv_direct_wgrad_bias_run(VC_OP_CONVT_WGRAD, dy, x, dW, nullptr, B, Cin, H, W, 1, round_bf16, workspace,
+                                    workspace_bytes, as_stream(stream));
+}
 
 extern "C" size_t vc_conv1_wgrad_bias_workspace_bytes(int Cout) { return conv_direct_wgrad_workspace(VC_OP_CONV_WGRAD, 1, Cout); }
 

@@ -216,8 +216,9 @@ class DecoderConvFn(torch.autograd.Function):
         if d2 is None:
             dw3 = _tap_wgrad(4, d2n, dxhat, w3)
         else:
-            dw3 = torch.empty_like(w3)
-            ops._dense(CONVT_WGRAD, 1, dxhat, d2, None, dw3, B, c2, 4 * H, 4 * W, 1, False)
+            dw3 = torch.empty_like(w3)   # bf16-rounded operands like every other weight gradient of the stack
+            ws = ops._workspace(L.size("vc_convT1_wgrad_workspace_bytes", c2), dev)
+            L.call("vc_convT1_wgrad", ptr(dxhat), ptr(d2), ptr(dw3), B, c2, 4 * H, 4 * W, 1, ptr(ws), ws.numel(), stream_ptr())
         g2n = torch.empty_like(d2n)
         L.call("vc_nhwc_convT1_dgrad", ptr(dxhat), ptr(w3), ptr(d2n), ptr(g2n), B, c2, 4 * H, 4 * W, stream_ptr())
         db2 = _bias_nhwc(g2n)
