@@ -171,6 +171,15 @@ def bytes_of(name: str, sig) -> float:
             return 4.0 * B * 4 * H * W + 4.0 * B * Cin * H * W      # dy fp32; mask read + g written, bf16
         if name == "vc_nhwc_bias_grad":
             return 2.0 * sig[0] * sig[1]
+        if name == "vc_nhwc_convT1_fwd":          # x bf16 NHWC read, y fp32 [B,1,2H,2W] written
+            B, Cin, H, W = sig[:4]
+            return 2.0 * B * Cin * H * W + 4.0 * B * 4 * H * W
+        if name == "vc_nhwc_tap_wgrad":           # A bf16 NHWC [B,PH,PW,C] and S fp32 [B,2PH,2PW] read once
+            _ks, B, C, PH, PW = sig[:5]
+            return 2.0 * B * C * PH * PW + 4.0 * B * 4 * PH * PW
+        if name == "vc_nhwc_conv1_wgrad_bias":    # g bf16 NHWC [B,H/2,W/2,C] and x fp32 [B,H,W]
+            B, H, W, Cout = sig[:4]
+            return 2.0 * B * Cout * (H // 2) * (W // 2) + 4.0 * B * H * W
         if name == "vc_nhwc_from_nchw":
             return 6.0 * sig[0] * sig[1] * sig[2] * sig[3]
         if name == "vc_linear_wgrad_adam":      # p, m, v read and written once; the gradient never touches memory
@@ -200,7 +209,8 @@ def family_of(name: str, sig) -> str:
         return "skinny_gemm wgrad + Adam (FC 262144<->256)"
     if name == "vc_linear_bf16w":
         return "skinny_gemm from the bf16 shadow (FC fwd / dgrad)"
-    if name in ("vc_nhwc_conv1_fwd", "vc_nhwc_convT1_dgrad", "vc_conv1_wgrad_bias", "vc_convT1_wgrad"):
+    if name in ("vc_nhwc_conv1_fwd", "vc_nhwc_convT1_dgrad", "vc_conv1_wgrad_bias", "vc_convT1_wgrad", "vc_nhwc_convT1_fwd",
+                "vc_nhwc_tap_wgrad", "vc_nhwc_conv1_wgrad_bias"):
         return "conv_direct (1-channel ends)"
     if name != "vc_dense_op":
         return name

@@ -161,6 +161,12 @@ int vc_nhwc_convT1_fwd(const void* x_nhwc, const float* W, const float* bias, fl
 size_t vc_nhwc_tap_wgrad_workspace_bytes(int C, int KS);
 int vc_nhwc_tap_wgrad(int KS, const void* a_nhwc, const float* S, float* dW, int B, int C, int PH, int PW, void* workspace,
                       size_t workspace_bytes, void* stream);
+/* Weight AND bias gradient of nn.Conv2d(1, Cout, 3, 2, 1) (12:87) from the bf16 NHWC gradient g_nhwc [B,H/2,W/2,Cout] of its
+ * output and x [B,1,H,W]: vc_nhwc_tap_wgrad with KS = 3 plus db[c] = sum g (of the bf16 values).  For Cout % 32 == 0 the bias
+ * gradient comes out of the same tensor-core pass (a constant-one tap). */
+size_t vc_nhwc_conv1_wgrad_bias_workspace_bytes(int Cout);
+int vc_nhwc_conv1_wgrad_bias(const void* g_nhwc, const float* x, float* dW, float* db, int B, int H, int Wd, int Cout,
+                             void* workspace, size_t workspace_bytes, void* stream);
 size_t vc_nhwc_bias_grad_workspace_bytes(int C);
 int vc_nhwc_bias_grad(const void* g_nhwc, int64_t rows, int C, float* db, void* workspace, size_t workspace_bytes,
                       void* stream);

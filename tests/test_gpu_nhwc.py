@@ -137,6 +137,56 @@ def test_single_channel_weight_gradients_tensor_core(B, C, H, W):
     torch.testing.assert_close(dwt.double(), wr.grad, rtol=2e-5, atol=2e-5 * float(wr.grad.abs().max()))
 
 
+@pytest.mark.parametrize("B,H,W", [(2, 16, 256), (3, 5, 32), (1, 9, 96), (2, 1, 64)])
+def test_single_channel_ends_tensor_core(B, H, W):
+    """The mma.sync kernels of csrc/nhwc_mma.cu (32-channel layers): ConvTranspose2d(32 -> 1) forward from NHWC (tiles of 14
+    pixels, so W = 32 / 96 / 256 all end in a partial tile), its data gradient with and without the ReLU mask, and both
+    tap weight gradients incl. the bias gradient from the constant-one tap."""
+    from vaeclust._lib import lib, ptr, stream_ptr
+    L = lib()
+    C = 32
+    wt, bb = _r(C, 1, 4, 4, seed=5, scale=0.25), _r(1, seed=10)
+    # forward
+    xin = _r(B, C, H, W, seed=9)
+    xn = _nhwc(xin)
+    for bias in (bb, None):
+        yo = torch.full((B, 1, 2 * H, 2 * W), float("nan"), device="cuda")
+        L.call("vc_nhwc_convT1_fwd", ptr(xn), ptr(wt), ptr(bias), ptr(yo), B, C, H, W, stream_ptr())
+        want = F.conv_transpose2d(_bf(xin).double(), _bf(wt).double(), None if bias is None else bias.double(), stride=2, padding=1)
+        torch.testing.assert_close(yo.double(), want, rtol=2e-5, atol=2e-5 * float(want.abs().max()))
+    # data gradient
+    dy, act = _r(B, 1, 2 * H, 2 * W, seed=4), _r(B, C, H, W, seed=6)
+    an = _nhwc(act)
+    for mask in (an, None):
+        g = torch.full((B, H, W, C), float("nan"), dtype=torch.bfloat16, device="cuda")
+        L.call("vc_nhwc_convT1_dgrad", ptr(dy), ptr(wt), ptr(mask), ptr(g), B, C, H, W, stream_ptr())
+        want = F.conv2d(_bf(dy), _bf(wt), None, stride=2, padding=1)
+        if mask is not None:
+            want = want * (_bf(act) > 0)
+        _check(g, None, want)
+    # weight gradients (+ bias gradient for the k3 end)
+    a_t, S = _r(B, C, H, W, seed=11), _r(B, 1, 2 * H, 2 * W, seed=12)
+    an2 = _nhwc(a_t)
+    dwt = torch.full((C, 1, 4, 4), float("nan"), device="cuda")
+    ws = torch.empty(L.size("vc_nhwc_tap_wgrad_workspace_bytes", C, 4), dtype=torch.uint8, device="cuda")
+    L.call("vc_nhwc_tap_wgrad", 4, ptr(an2), ptr(S), ptr(dwt), B, C, H, W, ptr(ws), ws.numel(), stream_ptr())
+    wr = torch.zeros(C, 1, 4, 4, device="cuda", dtype=torch.float64, requires_grad=True)
+    F.conv_transpose2d(_bf(a_t).double(), wr, None, stride=2, padding=1).backward(_bf(S).double())
+    torch.testing.assert_close(dwt.double(), wr.grad, rtol=2e-5, atol=2e-5 * float(wr.grad.abs().max()))
+    dw3, db3 = torch.full((C, 1, 3, 3), float("nan"), device="cuda"), torch.full((C,), float("nan"), device="cuda")
+    ws = torch.empty(L.size("vc_nhwc_conv1_wgrad_bias_workspace_bytes", C), dtype=torch.uint8, device="cuda")
+    for _ in range(2):
+        prev = dw3.clone()
+        L.call("vc_nhwc_conv1_wgrad_bias", ptr(an2), ptr(S), ptr(dw3), ptr(db3), B, 2 * H, 2 * W, C, ptr(ws), ws.numel(),
+               stream_ptr())
+    assert torch.equal(prev, dw3)
+    wr = torch.zeros(C, 1, 3, 3, device="cuda", dtype=torch.float64, requires_grad=True)
+    F.conv2d(_bf(S).double(), wr, None, stride=2, padding=1).backward(_bf(a_t).double())
+    torch.testing.assert_close(dw3.double(), wr.grad, rtol=2e-5, atol=2e-5 * float(wr.grad.abs().max()))
+    wantb = _bf(a_t).double().sum(dim=(0, 2, 3))
+    torch.testing.assert_close(db3.double(), wantb, rtol=1e-5, atol=1e-5 * float(wantb.abs().max()) + 1e-4)
+
+
 def test_single_channel_ends_and_helpers():
     from vaeclust._lib import lib, ptr, stream_ptr
     L = lib()
@@ -251,6 +301,7 @@ def test_conv_stacks_match_the_per_layer_path(ends_nhwc):
         m = torch.tensor([[1.0], [0.0]], device="cuda")
         eps = _r(B, 32, seed=3)
         out = {}
+        ends_default = convstack.ENDS_NHWC
         convstack.ENDS_NHWC = ends_nhwc
         for flag in (False, True):
             convstack.ENABLED = flag
@@ -273,7 +324,7 @@ def test_conv_stacks_match_the_per_layer_path(ends_nhwc):
             assert rel < (2e-2 if k.endswith("bias") else 5e-3), (k, rel)
     finally:
         convstack.ENABLED = True
-        convstack.ENDS_NHWC = False
+        convstack.ENDS_NHWC = ends_default
         ops.set_precision("fp32")
 
 

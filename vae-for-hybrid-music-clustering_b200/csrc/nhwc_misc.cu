@@ -353,6 +353,17 @@ static int nm_grid(int64_t total) {
 }
 constexpr int kColsumBlocks = 148 * 4;
 
+// nhwc_mma.cu: the tensor-core (mma.sync) versions for 32-channel layers
+bool nhwc_mma_convT1_dgrad_supported(int B, int Cin, int H, int W);
+int nhwc_mma_convT1_dgrad_run(const float* dy, const float* w, const __nv_bfloat16* act, __nv_bfloat16* g, int B, int H, int W,
+                              cudaStream_t s);
+bool nhwc_mma_convT1_fwd_supported(int B, int Cin, int H, int W);
+int nhwc_mma_convT1_fwd_run(const __nv_bfloat16* x, const float* w, const float* bias, float* y, int B, int H, int W,
+                            cudaStream_t s);
+bool nhwc_mma_tap_wgrad_supported(int B, int C, int PH, int PW);
+int nhwc_mma_tap_wgrad_run(int KS, const __nv_bfloat16* a, const float* S, double* part, double* bpart, int B, int C, int PH,
+                           int PW, int max_blocks, int* nblk_out, cudaStream_t s);
+
 }  // namespace vc
 
 using namespace vc;
@@ -375,6 +386,9 @@ extern "C" int vc_nhwc_convT1_dgrad(const float* dy, const float* Wt, const void
   VC_REQUIRE(Cin % 8 == 0 && Cin > 0 && Cin <= 512, VC_ERR_UNSUPPORTED, "vc_nhwc_convT1_dgrad: Cin must be a multiple of 8, <= 512");
   VC_REQUIRE(((reinterpret_cast<uintptr_t>(g_nhwc) | reinterpret_cast<uintptr_t>(act_nhwc)) & 15) == 0, VC_ERR_BAD_ARG,
              "vc_nhwc_convT1_dgrad: NHWC tensors must be 16-byte aligned");
+  if (nhwc_mma_convT1_dgrad_supported(B, Cin, H, W))
+    return nhwc_mma_convT1_dgrad_run(dy, Wt, static_cast<const __nv_bfloat16*>(act_nhwc), static_cast<__nv_bfloat16*>(g_nhwc), B,
+                                     H, W, as_stream(stream));
   nm_convT1_dgrad_kernel<<<nm_grid((int64_t)B * H * W), 256, (size_t)16 * Cin * sizeof(float), as_stream(stream)>>>(
       dy, Wt, static_cast<const __nv_bfloat16*>(act_nhwc), static_cast<__nv_bfloat16*>(g_nhwc), B, Cin, H, W);
   VC_LAUNCH_CHECK();
@@ -425,6 +439,8 @@ extern "C" int vc_nhwc_convT1_fwd(const void* x_nhwc, const float* Wt, const flo
   VC_REQUIRE(Cin % 8 == 0 && Cin > 0 && Cin <= 512, VC_ERR_UNSUPPORTED, "vc_nhwc_convT1_fwd: Cin must be a multiple of 8, <= 512");
   VC_REQUIRE((reinterpret_cast<uintptr_t>(x_nhwc) & 15) == 0 && (reinterpret_cast<uintptr_t>(y) & 7) == 0, VC_ERR_BAD_ARG,
              "vc_nhwc_convT1_fwd: misaligned pointers");
+  if (nhwc_mma_convT1_fwd_supported(B, Cin, H, W))
+    return nhwc_mma_convT1_fwd_run(static_cast<const __nv_bfloat16*>(x_nhwc), Wt, bias, y, B, H, W, as_stream(stream));
   nm_convT1_fwd_kernel<<<nm_grid((int64_t)B * H * W), 256, (size_t)16 * Cin * sizeof(float), as_stream(stream)>>>(
       static_cast<const __nv_bfloat16*>(x_nhwc), Wt, bias, y, B, Cin, H, W);
   VC_LAUNCH_CHECK();
@@ -432,30 +448,70 @@ extern "C" int vc_nhwc_convT1_fwd(const void* x_nhwc, const float* Wt, const flo
 }
 
 extern "C" size_t vc_nhwc_tap_wgrad_workspace_bytes(int C, int KS) {
-  return (size_t)kTapBlocksNhwc * (C > 0 ? C : 1) * KS * KS * sizeof(double);
+  return (size_t)kTapBlocksNhwc * (C > 0 ? C : 1) * (KS * KS + 1) * sizeof(double);   // + one column of bias partials
+}
+
+// dW (and db = column sums of A when given: Conv2d(1 -> C), KS = 3 only) from the bf16 NHWC tensor A and the fp32 S
+static int nm_tap_wgrad_run(const char* who, int KS, const void* a_nhwc, const float* S, float* dW, float* db, int B, int C,
+                            int PH, int PW, void* workspace, size_t workspace_bytes, void* stream) {
+  VC_REQUIRE(a_nhwc && S && dW && B > 0 && PH > 0 && PW > 0, VC_ERR_BAD_ARG, "%s: bad arguments", who);
+  VC_REQUIRE((KS == 3 || KS == 4) && C % 32 == 0 && C > 0 && C <= 512 && PW % 32 == 0, VC_ERR_UNSUPPORTED,
+             "%s: need KS 3 or 4, C %% 32 == 0, row width %% 32 == 0 (got KS=%d C=%d PW=%d)", who, KS, C, PW);
+  VC_REQUIRE(!db || KS == 3, VC_ERR_UNSUPPORTED, "%s: the fused bias gradient exists for KS = 3 only", who);
+  VC_REQUIRE(workspace && workspace_bytes >= vc_nhwc_tap_wgrad_workspace_bytes(C, KS), VC_ERR_WORKSPACE,
+             "%s: workspace too small", who);
+  VC_REQUIRE((reinterpret_cast<uintptr_t>(a_nhwc) & 15) == 0 && (reinterpret_cast<uintptr_t>(S) & 7) == 0, VC_ERR_BAD_ARG,
+             "%s: misaligned pointers", who);
+  const int T = KS * KS;
+  double* part = static_cast<double*>(workspace);
+  double* bpart = part + (size_t)kTapBlocksNhwc * C * T;
+  const __nv_bfloat16* a = static_cast<const __nv_bfloat16*>(a_nhwc);
+  cudaStream_t s = as_stream(stream);
+  int nblk = 0;
+  if (nhwc_mma_tap_wgrad_supported(B, C, PH, PW)) {
+    const int rc = nhwc_mma_tap_wgrad_run(KS, a, S, part, db ? bpart : nullptr, B, C, PH, PW, kTapBlocksNhwc, &nblk, s);
+    if (rc != VC_OK) return rc;
+    if (db) {
+      nm_tap_fold_kernel<<<(C + 31) / 32, 256, 0, s>>>(bpart, nblk, C, db);
+      VC_LAUNCH_CHECK();
+    }
+  } else {
+    const int64_t units = (int64_t)B * PH * (PW / 32);
+    nblk = kTapBlocksNhwc / (C / 32);
+    if (nblk < 1) nblk = 1;
+    if ((int64_t)nblk * 8 > units) nblk = (int)((units + 7) / 8);
+    const dim3 grid(nblk, C / 32);
+    if (KS == 3)
+      nm_tap_wgrad_kernel<3><<<grid, 256, 0, s>>>(a, S, part, B, C, PH, PW, 2 * PH, 2 * PW);
+    else
+      nm_tap_wgrad_kernel<4><<<grid, 256, 0, s>>>(a, S, part, B, C, PH, PW, 2 * PH, 2 * PW);
+    VC_LAUNCH_CHECK();
+    if (db) {      // column sums of A by the generic NHWC bias-gradient kernels (their partials fit the same slot)
+      const int groups = 256 / (C >> 3);
+      int grid2 = kColsumBlocks;
+      const int64_t rows = (int64_t)B * PH * PW;
+      if ((int64_t)grid2 * groups > rows) grid2 = (int)((rows + groups - 1) / groups);
+      nm_colsum_kernel<<<grid2, 256, (size_t)groups * C * sizeof(float), s>>>(a, rows, C, bpart);
+      VC_LAUNCH_CHECK();
+      nm_colsum_fold_kernel<<<(C + 31) / 32, 256, 0, s>>>(bpart, grid2, C, db);
+      VC_LAUNCH_CHECK();
+    }
+  }
+  nm_tap_fold_kernel<<<(C * T + 31) / 32, 256, 0, s>>>(part, nblk, C * T, dW);
+  VC_LAUNCH_CHECK();
+  return VC_OK;
 }
 
 extern "C" int vc_nhwc_tap_wgrad(int KS, const void* a_nhwc, const float* S, float* dW, int B, int C, int PH, int PW,
                                  void* workspace, size_t workspace_bytes, void* stream) {
-  VC_REQUIRE(a_nhwc && S && dW && B > 0 && PH > 0 && PW > 0, VC_ERR_BAD_ARG, "vc_nhwc_tap_wgrad: bad arguments");
-  VC_REQUIRE((KS == 3 || KS == 4) && C % 32 == 0 && C > 0 && C <= 512 && PW % 32 == 0, VC_ERR_UNSUPPORTED,
-             "vc_nhwc_tap_wgrad: need KS 3 or 4, C %% 32 == 0, row width %% 32 == 0 (got KS=%d C=%d PW=%d)", KS, C, PW);
-  VC_REQUIRE(workspace && workspace_bytes >= vc_nhwc_tap_wgrad_workspace_bytes(C, KS), VC_ERR_WORKSPACE,
-             "vc_nhwc_tap_wgrad: workspace too small");
-  const int64_t units = (int64_t)B * PH * (PW / 32);
-  int nblk = kTapBlocksNhwc / (C / 32);
-  if (nblk < 1) nblk = 1;
-  if ((int64_t)nblk * 8 > units) nblk = (int)((units + 7) / 8);
-  double* part = static_cast<double*>(workspace);
-  const dim3 grid(nblk, C / 32);
-  if (KS == 3)
-    nm_tap_wgrad_kernel<3><<<grid, 256, 0, as_stream(stream)>>>(static_cast<const __nv_bfloat16*>(a_nhwc), S, part, B, C, PH,
-                                                                   PW, 2 * PH, 2 * PW);
-  else
-    nm_tap_wgrad_kernel<4><<<grid, 256, 0, as_stream(stream)>>>(static_cast<const __nv_bfloat16*>(a_nhwc), S, part, B, C, PH,
-                                                                   PW, 2 * PH, 2 * PW);
-  VC_LAUNCH_CHECK();
-  nm_tap_fold_kernel<<<(C * KS * KS + 31) / 32, 256, 0, as_stream(stream)>>>(part, nblk, C * KS * KS, dW);
-  VC_LAUNCH_CHECK();
-  return VC_OK;
+  return nm_tap_wgrad_run("vc_nhwc_tap_wgrad", KS, a_nhwc, S, dW, nullptr, B, C, PH, PW, workspace, workspace_bytes, stream);
+}
+
+extern "C" size_t vc_nhwc_conv1_wgrad_bias_workspace_bytes(int Cout) { return vc_nhwc_tap_wgrad_workspace_bytes(Cout, 3); }
+
+extern "C" int vc_nhwc_conv1_wgrad_bias(const void* g_nhwc, const float* x, float* dW, float* db, int B, int H, int W, int Cout,
+                                        void* workspace, size_t workspace_bytes, void* stream) {
+  VC_REQUIRE(db && H % 2 == 0 && W % 2 == 0, VC_ERR_BAD_ARG, "vc_nhwc_conv1_wgrad_bias: db is required, H and W must be even");
+  return nm_tap_wgrad_run("vc_nhwc_conv1_wgrad_bias", 3, g_nhwc, x, dW, db, B, Cout, H / 2, W / 2, workspace, workspace_bytes,
+                          stream);
 }

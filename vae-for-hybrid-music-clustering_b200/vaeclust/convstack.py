@@ -12,17 +12,20 @@ sum bf16-rounded gradients.
 """
 from __future__ import annotations
 
+import os
+
 import torch
 
 from . import ops
 from ._lib import lib, ptr, stream_ptr
 
 ENABLED = True      # bf16 mode only; `supported()` decides per shape, anything else takes the per-layer path
-# The single-channel ends can also run on bf16 NHWC (vc_nhwc_convT1_fwd, vc_nhwc_tap_wgrad: no fp32 copies of the widest
-# activations at all), but measured on B200 those CUDA-core kernels are slower than the fp32-NCHW ones they replace
-# (deconv.4 forward 0.27 vs 0.115 ms, tap weight gradients 0.16 / 0.13 vs 0.09 / 0.12 ms), so the default keeps fp32 NCHW
-# at the two ends.
-ENDS_NHWC = False
+# The single-channel ends run on bf16 NHWC as well (csrc/nhwc_mma.cu: mma.sync kernels for the 32-channel layers), so no
+# fp32 copy of the two widest activations exists at all: deconv2 writes one layout instead of two (0.145 -> 0.105 ms),
+# deconv.4 forward reads half the bytes (0.115 -> 0.059 ms), both tap weight gradients likewise (0.069 / 0.077 ->
+# 0.050 / 0.056 ms incl. the bias gradient).  VAECLUST_ENDS_NHWC=0 keeps fp32 NCHW at the two ends (the round-2 default
+# before the tensor-core kernels existed: as CUDA-core kernels the NHWC ends were slower than the fp32 ones).
+ENDS_NHWC = os.environ.get("VAECLUST_ENDS_NHWC", "1") == "1"
 
 CONV_FWD, CONV_DGRAD, CONV_WGRAD, CONVT_FWD, CONVT_DGRAD, CONVT_WGRAD = 3, 4, 5, 6, 7, 8
 _BF = torch.bfloat16
@@ -159,8 +162,10 @@ class EncoderConvFn(torch.autograd.Function):
         if ENDS_NHWC:
             g1n = torch.empty_like(a1)
             _conv(CONV_DGRAD, g2n, w2, None, False, a1, g1n, None, d2)
-            db1 = _bias_nhwc(g1n)
-            dw1 = _tap_wgrad(3, g1n, x, w1)
+            dw1 = torch.empty_like(w1)          # weight and bias gradient from one tensor-core pass over g1n
+            db1 = torch.empty(c1, dtype=torch.float32, device=dev)
+            ws = ops._workspace(L.size("vc_nhwc_conv1_wgrad_bias_workspace_bytes", c1), dev)
+            L.call("vc_nhwc_conv1_wgrad_bias", ptr(g1n), ptr(x), ptr(dw1), ptr(db1), B, H, W, c1, ptr(ws), ws.numel(), s)
             g1 = g1n.float().permute(0, 3, 1, 2).contiguous() if ctx.needs_input_grad[0] else None
         else:       # conv1's gradient leaves the NHWC world: fp32 NCHW for the single-channel weight-gradient kernel
             g1 = torch.empty((B, c1, H // 2, W // 2), dtype=torch.float32, device=dev)
