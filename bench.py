@@ -166,7 +166,7 @@ def bytes_of(name: str, sig) -> float:
         if name == "vc_nhwc_conv1_fwd":
             _relu, B, H, W, Cout = sig[:5]
             return 4.0 * B * H * W + 2.0 * B * (H // 2) * (W // 2) * Cout
-        if name == "vc_nhwc_convT1_dgrad":
+        if name in ("vc_nhwc_convT1_dgrad", "vc_nhwc_convT1_dgrad_bias"):
             B, Cin, H, W = sig[:4]
             return 4.0 * B * 4 * H * W + 4.0 * B * Cin * H * W      # dy fp32; mask read + g written, bf16
         if name == "vc_nhwc_bias_grad":
@@ -210,7 +210,7 @@ def family_of(name: str, sig) -> str:
     if name == "vc_linear_bf16w":
         return "skinny_gemm from the bf16 shadow (FC fwd / dgrad)"
     if name in ("vc_nhwc_conv1_fwd", "vc_nhwc_convT1_dgrad", "vc_conv1_wgrad_bias", "vc_convT1_wgrad", "vc_nhwc_convT1_fwd",
-                "vc_nhwc_tap_wgrad", "vc_nhwc_conv1_wgrad_bias"):
+                "vc_nhwc_tap_wgrad", "vc_nhwc_conv1_wgrad_bias", "vc_nhwc_convT1_dgrad_bias"):
         return "conv_direct (1-channel ends)"
     if name != "vc_dense_op":
         return name

@@ -149,6 +149,11 @@ int vc_nhwc_conv1_fwd(const float* x, const float* W, const float* bias, int rel
                       int Cout, void* stream);
 int vc_nhwc_convT1_dgrad(const float* dy, const float* W, const void* act_nhwc, void* g_nhwc, int B, int Cin, int H,
                          int Wd, void* stream);
+/* vc_nhwc_convT1_dgrad plus db[c] = sum over pixels of the (masked, bf16) result: the bias gradient of the layer below
+ * (12:136) from the same pass. */
+size_t vc_nhwc_convT1_dgrad_bias_workspace_bytes(int Cin);
+int vc_nhwc_convT1_dgrad_bias(const float* dy, const float* W, const void* act_nhwc, void* g_nhwc, float* db, int B, int Cin,
+                              int H, int Wd, void* workspace, size_t workspace_bytes, void* stream);
 int vc_nhwc_from_nchw(const float* src, void* dst_nhwc, int B, int C, int H, int Wd, void* stream);
 /*  vc_nhwc_convT1_fwd   : nn.ConvTranspose2d(Cin, 1, 4, 2, 1) forward (12:137) from a bf16 NHWC input [B,H,W,Cin]; y fp32
  *                         [B,1,2H,2W].

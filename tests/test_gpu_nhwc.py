@@ -164,6 +164,22 @@ def test_single_channel_ends_tensor_core(B, H, W):
         if mask is not None:
             want = want * (_bf(act) > 0)
         _check(g, None, want)
+    # data gradient + bias gradient of the layer below from the same pass
+    g2 = torch.full((B, H, W, C), float("nan"), dtype=torch.bfloat16, device="cuda")
+    db = torch.full((C,), float("nan"), device="cuda")
+    ws = torch.empty(L.size("vc_nhwc_convT1_dgrad_bias_workspace_bytes", C), dtype=torch.uint8, device="cuda")
+    L.call("vc_nhwc_convT1_dgrad_bias", ptr(dy), ptr(wt), ptr(an), ptr(g2), ptr(db), B, C, H, W, ptr(ws), ws.numel(), stream_ptr())
+    L.call("vc_nhwc_convT1_dgrad", ptr(dy), ptr(wt), ptr(an), ptr(g), B, C, H, W, stream_ptr())
+    assert torch.equal(g2, g)
+    wantb = g.double().sum(dim=(0, 1, 2))
+    torch.testing.assert_close(db.double(), wantb, rtol=1e-5, atol=1e-5 * float(wantb.abs().max()) + 1e-4)
+    # Conv2d(1 -> 32) forward into NHWC (W a multiple of 64 takes the tensor-core kernel)
+    xc, wc, bc = _r(B, 1, 2 * H, 2 * W, seed=31), _r(C, 1, 3, 3, seed=32, scale=1 / 3), _r(C, seed=33)
+    for bias, relu in ((bc, 1), (None, 0)):
+        yc = torch.full((B, H, W, C), float("nan"), dtype=torch.bfloat16, device="cuda")
+        L.call("vc_nhwc_conv1_fwd", ptr(xc), ptr(wc), ptr(bias), relu, ptr(yc), B, 2 * H, 2 * W, C, stream_ptr())
+        want = F.conv2d(_bf(xc), _bf(wc), bias, stride=2, padding=1)
+        _check(yc, None, F.relu(want) if relu else want)
     # weight gradients (+ bias gradient for the k3 end)
     a_t, S = _r(B, C, H, W, seed=11), _r(B, 1, 2 * H, 2 * W, seed=12)
     an2 = _nhwc(a_t)

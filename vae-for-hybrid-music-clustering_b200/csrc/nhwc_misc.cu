@@ -356,7 +356,10 @@ constexpr int kColsumBlocks = 148 * 4;
 // nhwc_mma.cu: the tensor-core (mma.sync) versions for 32-channel layers
 bool nhwc_mma_convT1_dgrad_supported(int B, int Cin, int H, int W);
 int nhwc_mma_convT1_dgrad_run(const float* dy, const float* w, const __nv_bfloat16* act, __nv_bfloat16* g, int B, int H, int W,
-                              cudaStream_t s);
+                              double* bpart, int* grid_out, cudaStream_t s);
+bool nhwc_mma_conv1_fwd_supported(int B, int H, int W, int Cout);
+int nhwc_mma_conv1_fwd_run(const float* x, const float* w, const float* bias, __nv_bfloat16* y, int B, int H, int W, int relu,
+                           cudaStream_t s);
 bool nhwc_mma_convT1_fwd_supported(int B, int Cin, int H, int W);
 int nhwc_mma_convT1_fwd_run(const __nv_bfloat16* x, const float* w, const float* bias, float* y, int B, int H, int W,
                             cudaStream_t s);
@@ -373,6 +376,8 @@ extern "C" int vc_nhwc_conv1_fwd(const float* x, const float* Wt, const float* b
   VC_REQUIRE(x && Wt && y_nhwc && B > 0 && H > 0 && W > 0, VC_ERR_BAD_ARG, "vc_nhwc_conv1_fwd: bad arguments");
   VC_REQUIRE(Cout % 8 == 0 && Cout > 0 && Cout <= 256, VC_ERR_UNSUPPORTED, "vc_nhwc_conv1_fwd: Cout must be a multiple of 8, <= 256");
   VC_REQUIRE((reinterpret_cast<uintptr_t>(y_nhwc) & 15) == 0, VC_ERR_BAD_ARG, "vc_nhwc_conv1_fwd: y must be 16-byte aligned");
+  if (nhwc_mma_conv1_fwd_supported(B, H, W, Cout))
+    return nhwc_mma_conv1_fwd_run(x, Wt, bias, static_cast<__nv_bfloat16*>(y_nhwc), B, H, W, relu, as_stream(stream));
   const int OH = (H - 1) / 2 + 1, OW = (W - 1) / 2 + 1;
   nm_conv1_fwd_kernel<<<nm_grid((int64_t)B * OH * OW), 256, (size_t)10 * Cout * sizeof(float), as_stream(stream)>>>(
       x, Wt, bias, static_cast<__nv_bfloat16*>(y_nhwc), B, H, W, Cout, OH, OW, relu);
@@ -388,11 +393,35 @@ extern "C" int vc_nhwc_convT1_dgrad(const float* dy, const float* Wt, const void
              "vc_nhwc_convT1_dgrad: NHWC tensors must be 16-byte aligned");
   if (nhwc_mma_convT1_dgrad_supported(B, Cin, H, W))
     return nhwc_mma_convT1_dgrad_run(dy, Wt, static_cast<const __nv_bfloat16*>(act_nhwc), static_cast<__nv_bfloat16*>(g_nhwc), B,
-                                     H, W, as_stream(stream));
+                                     H, W, nullptr, nullptr, as_stream(stream));
   nm_convT1_dgrad_kernel<<<nm_grid((int64_t)B * H * W), 256, (size_t)16 * Cin * sizeof(float), as_stream(stream)>>>(
       dy, Wt, static_cast<const __nv_bfloat16*>(act_nhwc), static_cast<__nv_bfloat16*>(g_nhwc), B, Cin, H, W);
   VC_LAUNCH_CHECK();
   return VC_OK;
+}
+
+/* ConvTranspose2d(Cin -> 1) data gradient AND the bias gradient of the layer below (column sums of the masked result) */
+extern "C" size_t vc_nhwc_convT1_dgrad_bias_workspace_bytes(int Cin) { return vc_nhwc_bias_grad_workspace_bytes(Cin); }
+
+extern "C" int vc_nhwc_convT1_dgrad_bias(const float* dy, const float* Wt, const void* act_nhwc, void* g_nhwc, float* db, int B,
+                                         int Cin, int H, int W, void* workspace, size_t workspace_bytes, void* stream) {
+  VC_REQUIRE(db, VC_ERR_BAD_ARG, "vc_nhwc_convT1_dgrad_bias: db is required");
+  VC_REQUIRE(workspace && workspace_bytes >= vc_nhwc_convT1_dgrad_bias_workspace_bytes(Cin), VC_ERR_WORKSPACE,
+             "vc_nhwc_convT1_dgrad_bias: workspace too small");
+  if (dy && Wt && g_nhwc && B > 0 && H > 0 && W > 0 && nhwc_mma_convT1_dgrad_supported(B, Cin, H, W) &&
+      ((reinterpret_cast<uintptr_t>(g_nhwc) | reinterpret_cast<uintptr_t>(act_nhwc)) & 15) == 0) {
+    int grid = 0;
+    double* bpart = static_cast<double*>(workspace);
+    const int rc = nhwc_mma_convT1_dgrad_run(dy, Wt, static_cast<const __nv_bfloat16*>(act_nhwc),
+                                             static_cast<__nv_bfloat16*>(g_nhwc), B, H, W, bpart, &grid, as_stream(stream));
+    if (rc != VC_OK) return rc;
+    nm_colsum_fold_kernel<<<(Cin + 31) / 32, 256, 0, as_stream(stream)>>>(bpart, grid, Cin, db);
+    VC_LAUNCH_CHECK();
+    return VC_OK;
+  }
+  const int rc = vc_nhwc_convT1_dgrad(dy, Wt, act_nhwc, g_nhwc, B, Cin, H, W, stream);
+  if (rc != VC_OK) return rc;
+  return vc_nhwc_bias_grad(g_nhwc, (int64_t)B * H * W, Cin, db, workspace, workspace_bytes, stream);
 }
 
 extern "C" int vc_nhwc_from_nchw(const float* src, void* dst_nhwc, int B, int C, int H, int W, void* stream) {

@@ -72,10 +72,15 @@ struct HmWalk {
 // tap row kh = t: its k slots 2t, 2t+1 are the taps (t, kw 1), (t, kw 2) -- the aligned pair dy[.., 2j .. 2j+1] -- and slots
 // 2t+8, 2t+9 the taps (t, kw 0), (t, kw 3) (two scalars); n-tile q, column n <-> channel 8 (n / 2) + 2 q + (n % 2), so a
 // thread's accumulators of pixel row g are the eight consecutive channels 8t .. 8t+7: one 16-byte store (and mask load).
+// BIAS: per-channel sums of the (masked, bf16-rounded) result as well -- the bias gradient of the layer below (12:136), which
+// otherwise costs another pass over g; block partials in double, folded in block order by nm_colsum_fold_kernel.
+template <bool BIAS>
 __global__ void __launch_bounds__(256, 3)
 hm_convT1_dgrad_kernel(const float* __restrict__ dy, const float* __restrict__ w, const __nv_bfloat16* __restrict__ act,
-                       __nv_bfloat16* __restrict__ gout, int B, int H, int W) {
+                       __nv_bfloat16* __restrict__ gout, int B, int H, int W, double* __restrict__ bpart) {
   constexpr int C = 32;
+  __shared__ float bred[8][32];
+  float bs[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
   const int lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
   const int SH = 2 * H, SW = 2 * W, segs = W >> 5;
   uint32_t bw[4][2];
@@ -135,7 +140,95 @@ hm_convT1_dgrad_kernel(const float* __restrict__ dy, const float* __restrict__ w
             v[2 * q + 1] = hm_hi(mw[q]) > 0.f ? v[2 * q + 1] : 0.f;
           }
         }
-        *reinterpret_cast<uint4*>(gout + pbase + (int64_t)e * 8 * C) =
+        const uint4 o = make_uint4(hm_pack(v[0], v[1]), hm_pack(v[2], v[3]), hm_pack(v[4], v[5]), hm_pack(v[6], v[7]));
+        *reinterpret_cast<uint4*>(gout + pbase + (int64_t)e * 8 * C) = o;
+        if (BIAS) {
+          const uint32_t ow[4] = {o.x, o.y, o.z, o.w};
+#pragma unroll
+          for (int q = 0; q < 4; ++q) { bs[2 * q] += hm_lo(ow[q]); bs[2 * q + 1] += hm_hi(ow[q]); }
+        }
+      }
+    }
+  }
+  if (BIAS) {      // lanes of equal t hold the same eight channels: add over g (fixed butterfly), then over the warps in order
+#pragma unroll
+    for (int c = 0; c < 8; ++c) {
+      float v = bs[c];
+      v += __shfl_xor_sync(0xffffffffu, v, 4);
+      v += __shfl_xor_sync(0xffffffffu, v, 8);
+      v += __shfl_xor_sync(0xffffffffu, v, 16);
+      if (g == 0) bred[threadIdx.x >> 5][8 * t + c] = v;
+    }
+    __syncthreads();
+    if (threadIdx.x < 32) {
+      double v = 0.0;
+#pragma unroll
+      for (int wq = 0; wq < 8; ++wq) v += (double)bred[wq][threadIdx.x];
+      bpart[(int64_t)blockIdx.x * C + threadIdx.x] = v;
+    }
+  }
+}
+
+// ---- Conv2d(1 -> 32, k3 s2 p1) forward (+ bias, ReLU) writing bf16 NHWC (12:87): the same GEMM shape,
+//   D[16 px][32 ch] = P[16 px][9 taps, padded to 16] * W[16][32]:  thread t < 3 owns tap row kh = t -- k slots 2t, 2t+1 = the
+// aligned pair x[.., 2 ow .. 2 ow + 1] (kw 1, 2), slot 2t+8 = x[.., 2 ow - 1] (kw 0), slot 2t+9 and all of t = 3 are zero.
+__global__ void __launch_bounds__(256, 3)
+hm_conv1_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ bias,
+                    __nv_bfloat16* __restrict__ y, int B, int H, int W, int relu) {
+  constexpr int C = 32;
+  const int lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
+  const int OH = (H - 1) / 2 + 1, OW = W >> 1, segs = OW >> 5;
+  uint32_t bw[4][2];
+  float bv[8];
+#pragma unroll
+  for (int q = 0; q < 4; ++q) {
+    const float* wc = w + (8 * (g >> 1) + 2 * q + (g & 1)) * 9 + 3 * (t < 3 ? t : 0);
+    bw[q][0] = t < 3 ? hm_pack(wc[1], wc[2]) : 0u;
+    bw[q][1] = t < 3 ? hm_pack(wc[0], 0.f) : 0u;
+  }
+#pragma unroll
+  for (int c = 0; c < 8; ++c) bv[c] = bias ? __ldg(bias + 8 * t + c) : 0.f;
+  const int units = B * OH * segs;
+  const int stride = (int)gridDim.x * 8;
+  int u = (int)blockIdx.x * 8 + (threadIdx.x >> 5);
+  HmWalk k;
+  k.init(u, stride, OH, segs);
+  for (; u < units; u += stride, k.advance(OH, segs)) {
+    const int row = 2 * k.i - 1 + t;
+    const uint32_t rok = (t < 3 && (unsigned)row < (unsigned)H) ? 1u : 0u;
+    const float* sp = x + (int64_t)((k.b * H + row) * W);
+    const int px0 = k.s * 32 + g;                           // this thread's pixels: px0 + 8 e, e = 0 .. 3
+    const int64_t pbase = ((int64_t)(k.b * OH + k.i) * OW + px0) * C + 8 * t;
+    float2 mid[4];
+    float lo[4];
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      const int c0 = 2 * (px0 + 8 * e);
+      mid[e] = hm_ldg2_pred(sp + c0, rok);
+      lo[e] = ldg_pred(sp + c0 - 1, rok & (c0 > 0 ? 1u : 0u));
+    }
+#pragma unroll
+    for (int m = 0; m < 2; ++m) {
+      const int e0 = 2 * m, e1 = 2 * m + 1;
+      const uint32_t a0 = hm_pack(mid[e0].x, mid[e0].y), a1 = hm_pack(mid[e1].x, mid[e1].y);
+      const uint32_t a2 = hm_pack(lo[e0], 0.f), a3 = hm_pack(lo[e1], 0.f);
+      float d[4][4];
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        d[q][0] = d[q][2] = bv[2 * q];
+        d[q][1] = d[q][3] = bv[2 * q + 1];
+        hm_mma(d[q], a0, a1, a2, a3, bw[q][0], bw[q][1]);
+      }
+#pragma unroll
+      for (int r = 0; r < 2; ++r) {
+        float v[8];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) { v[2 * q] = d[q][2 * r]; v[2 * q + 1] = d[q][2 * r + 1]; }
+        if (relu) {
+#pragma unroll
+          for (int c = 0; c < 8; ++c) v[c] = fmaxf(v[c], 0.f);
+        }
+        *reinterpret_cast<uint4*>(y + pbase + (int64_t)(2 * m + r) * 8 * C) =
             make_uint4(hm_pack(v[0], v[1]), hm_pack(v[2], v[3]), hm_pack(v[4], v[5]), hm_pack(v[6], v[7]));
       }
     }
@@ -359,12 +452,30 @@ static bool hm_enabled() {
 bool nhwc_mma_convT1_dgrad_supported(int B, int Cin, int H, int W) {
   return hm_enabled() && Cin == 32 && W % 32 == 0 && (int64_t)B * H * W * 4 < 2147483647LL;
 }
+// bpart (optional): [grid][32] block partials of the per-channel sums; *grid_out = blocks launched (<= 3 * 148)
 int nhwc_mma_convT1_dgrad_run(const float* dy, const float* w, const __nv_bfloat16* act, __nv_bfloat16* g, int B, int H, int W,
-                              cudaStream_t s) {
+                              double* bpart, int* grid_out, cudaStream_t s) {
   const int64_t units = (int64_t)B * H * (W / 32);
   int grid = 3 * sm_count();
+  if (grid > 3 * 148) grid = 3 * 148;
   if ((int64_t)grid * 8 > units) grid = (int)((units + 7) / 8);
-  hm_convT1_dgrad_kernel<<<grid, 256, 0, s>>>(dy, w, act, g, B, H, W);
+  if (bpart)
+    hm_convT1_dgrad_kernel<true><<<grid, 256, 0, s>>>(dy, w, act, g, B, H, W, bpart);
+  else
+    hm_convT1_dgrad_kernel<false><<<grid, 256, 0, s>>>(dy, w, act, g, B, H, W, nullptr);
+  VC_LAUNCH_CHECK();
+  if (grid_out) *grid_out = grid;
+  return VC_OK;
+}
+bool nhwc_mma_conv1_fwd_supported(int B, int H, int W, int Cout) {
+  return hm_enabled() && Cout == 32 && W % 64 == 0 && (int64_t)B * H * W < 2147483647LL;
+}
+int nhwc_mma_conv1_fwd_run(const float* x, const float* w, const float* bias, __nv_bfloat16* y, int B, int H, int W, int relu,
+                           cudaStream_t s) {
+  const int64_t units = (int64_t)B * ((H - 1) / 2 + 1) * (W / 64);
+  int grid = 3 * sm_count();
+  if ((int64_t)grid * 8 > units) grid = (int)((units + 7) / 8);
+  hm_conv1_fwd_kernel<<<grid, 256, 0, s>>>(x, w, bias, y, B, H, W, relu);
   VC_LAUNCH_CHECK();
   return VC_OK;
 }

@@ -62,7 +62,7 @@ _LAUNCHES = {
     "vc_kmeans_assign_update": 2, "vc_cluster_sums": 2, "vc_kmeans_inertia": 2, "vc_dbi_intra": 2, "vc_col_stats": 2,
     "vc_silhouette_finalize": 2, "vc_bias_grad": 2, "vc_relu_bwd_bias": 2, "vc_dense_op": 2,
     "vc_relu_bwd_bias_nhwc": 2, "vc_conv_dgrad_nhwc": 2, "vc_mlpvae_step": 4, "vc_kmeans_lloyd_estep": 2,
-    "vc_conv_nhwc": 2, "vc_conv_nhwc_wgrad": 2, "vc_nhwc_bias_grad": 2, "vc_nhwc_tap_wgrad": 2, "vc_conv1_wgrad_bias": 3, "vc_convT1_wgrad": 2, "vc_nhwc_conv1_wgrad_bias": 3,
+    "vc_conv_nhwc": 2, "vc_conv_nhwc_wgrad": 2, "vc_nhwc_bias_grad": 2, "vc_nhwc_tap_wgrad": 2, "vc_conv1_wgrad_bias": 3, "vc_convT1_wgrad": 2, "vc_nhwc_conv1_wgrad_bias": 3, "vc_nhwc_convT1_dgrad_bias": 2,
 }
 
 

@@ -225,8 +225,10 @@ class DecoderConvFn(torch.autograd.Function):
             ws = ops._workspace(L.size("vc_convT1_wgrad_workspace_bytes", c2), dev)
             L.call("vc_convT1_wgrad", ptr(dxhat), ptr(d2), ptr(dw3), B, c2, 4 * H, 4 * W, 1, ptr(ws), ws.numel(), stream_ptr())
         g2n = torch.empty_like(d2n)
-        L.call("vc_nhwc_convT1_dgrad", ptr(dxhat), ptr(w3), ptr(d2n), ptr(g2n), B, c2, 4 * H, 4 * W, stream_ptr())
-        db2 = _bias_nhwc(g2n)
+        db2 = torch.empty(c2, dtype=torch.float32, device=dev)     # bias gradient of deconv.2 from the same pass
+        ws = ops._workspace(L.size("vc_nhwc_convT1_dgrad_bias_workspace_bytes", c2), dev)
+        L.call("vc_nhwc_convT1_dgrad_bias", ptr(dxhat), ptr(w3), ptr(d2n), ptr(g2n), ptr(db2), B, c2, 4 * H, 4 * W, ptr(ws),
+               ws.numel(), stream_ptr())
         dw2 = _wgrad(CONVT_WGRAD, g2n, d1n, w2, e2)
         g1n = torch.empty_like(d1n)
         _conv(CONVT_DGRAD, g2n, w2, None, False, d1n, g1n, None, e2)
