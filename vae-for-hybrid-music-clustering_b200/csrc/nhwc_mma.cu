@@ -365,7 +365,7 @@ hm_tap_wgrad_kernel(const __nv_bfloat16* __restrict__ A, const float* __restrict
 // done with three warp shuffles.  A tile's 16 MMA rows are the pixels 14 jt - 1 .. 14 jt + 14: rows 0 and 15 only feed
 // their neighbours, rows 1 .. 14 are written (tiles overlap by two pixels instead of exchanging edges).  The eight warps
 // of a block take eight consecutive rows i of the same two column tiles, so rows i - 1 .. i + 8 are shared through L1.
-__global__ void __launch_bounds__(256, 2)
+__global__ void __launch_bounds__(256, 3)
 hm_convT1_fwd_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ w, const float* __restrict__ bias,
                      float* __restrict__ y, int B, int H, int W) {
   constexpr int C = 32, TP = 14;
@@ -394,24 +394,42 @@ hm_convT1_fwd_kernel(const __nv_bfloat16* __restrict__ x, const float* __restric
   // (row + 1, kw 0) from lane (g + 1, t - 1); rows 7 / 8 wrap between the two accumulator halves
   const bool even = (t & 1) == 0;
   const int src = even ? (((g - 1) & 7) << 2) + t + 1 : (((g + 1) & 7) << 2) + t - 1;
-  for (int bu = blockIdx.x; bu < total; bu += gridDim.x) {
-    const int jp = bu % npair, r0 = bu / npair;
-    const int ig = r0 % hg, b = r0 / hg;
-    const int i = ig * 8 + warp;
+  // block units (b, ig, jp) walked without divisions; element offsets are 32-bit (host: B H W C < 2^31)
+  HmWalk k3;
+  k3.init((int)blockIdx.x, (int)gridDim.x, hg, npair);
+  const int rowstride = W * C;
+  for (int bu = blockIdx.x; bu < total; bu += gridDim.x, k3.advance(hg, npair)) {
+    const int jp = k3.s, b = k3.b;
+    const int i = k3.i * 8 + warp;
     if (i >= H) continue;                                   // warp-uniform
     uint4 xa[2][3][2];
+    const int pxb = 2 * TP * jp - 1 + g;                    // pixel of (tile 0, row g)
+    const __nv_bfloat16* xb = x + (uint32_t)(((b * H + i) * W) * C + 8 * t);
+    const uint32_t up = i > 0 ? 1u : 0u, dn = i + 1 < H ? 1u : 0u;
+    // interior tiles (no image border within the 30 pixels x 3 rows: warp-uniform) take plain loads; the predicated form
+    // costs six instructions per load
+    if (up && dn && jp > 0 && 2 * TP * jp + TP + 14 < W) {
 #pragma unroll
-    for (int k = 0; k < 2; ++k) {
-      const int jt = 2 * jp + k;
-#pragma unroll
-      for (int dh = -1; dh <= 1; ++dh) {
-        const int ih = i + dh;
-        const bool rowok = (unsigned)ih < (unsigned)H && jt < ntj;
+      for (int k = 0; k < 2; ++k) {
 #pragma unroll
         for (int r2 = 0; r2 < 2; ++r2) {
-          const int px = TP * jt - 1 + g + 8 * r2;
-          xa[k][dh + 1][r2] = hm_ldg16_pred(x + ((int64_t)((b * H + ih) * W + px) * C + 8 * t),
-                                            rowok && (unsigned)px < (unsigned)W ? 1u : 0u);
+          const __nv_bfloat16* pp = xb + (pxb + TP * k + 8 * r2) * C;
+          xa[k][0][r2] = __ldg(reinterpret_cast<const uint4*>(pp - rowstride));
+          xa[k][1][r2] = __ldg(reinterpret_cast<const uint4*>(pp));
+          xa[k][2][r2] = __ldg(reinterpret_cast<const uint4*>(pp + rowstride));
+        }
+      }
+    } else {
+#pragma unroll
+      for (int k = 0; k < 2; ++k) {
+#pragma unroll
+        for (int r2 = 0; r2 < 2; ++r2) {
+          const int px = pxb + TP * k + 8 * r2;
+          const uint32_t pok = (unsigned)px < (unsigned)W && 2 * jp + k < ntj ? 1u : 0u;
+          const __nv_bfloat16* pp = xb + px * C;
+          xa[k][0][r2] = hm_ldg16_pred(pp - rowstride, pok & up);
+          xa[k][1][r2] = hm_ldg16_pred(pp, pok);
+          xa[k][2][r2] = hm_ldg16_pred(pp + rowstride, pok & dn);
         }
       }
     }
@@ -486,7 +504,7 @@ int nhwc_mma_convT1_fwd_run(const __nv_bfloat16* x, const float* w, const float*
                             cudaStream_t s) {
   const int ntj = (W + 13) / 14;
   const int64_t total = (int64_t)B * ((H + 7) / 8) * ((ntj + 1) / 2);
-  int grid = 2 * sm_count();
+  int grid = 3 * sm_count();
   if (grid > total) grid = (int)total;
   hm_convT1_fwd_kernel<<<grid, 256, 0, s>>>(x, w, bias, y, B, H, W);
   VC_LAUNCH_CHECK();

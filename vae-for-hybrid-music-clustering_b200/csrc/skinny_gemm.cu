@@ -465,6 +465,12 @@ size_t skinny_gemm_workspace(int op, int B, int Cin, int Cout) {
 }
 
 struct SkAdam { float* m; float* v; const VcAdamDeviceStep* step; float lr, b1, b2, eps, bc1, bc2; __nv_bfloat16* shadow; };
+// fc_adam.cu: the persistent TMA-staged version of the fused weight gradient + Adam (N = 256, batch <= 64, M % 128 == 0)
+struct FcAdamParams { float* m; float* v; const VcAdamDeviceStep* step; float lr, b1, b2, eps, bc1, bc2; __nv_bfloat16* shadow; };
+bool fc_adam_tma_supported(int M, int N, int K, int64_t lda, int64_t ldo, int transposed, const void* p, const void* m,
+                           const void* v, const void* shadow);
+int fc_adam_tma_run(const float* act, int64_t lda, const __nv_bfloat16* Bs, float* p, int M, int N, int K, int64_t ldo,
+                    int transposed, const FcAdamParams& ad, cudaStream_t s);
 static int skinny_gemm_run_impl(int op, const float* in0, const float* in1, const float* bias, float* out, int B, int Cin,
                                 int Cout, int relu, void* ws, size_t wsb, cudaStream_t s, const SkAdam* adam,
                                 const __nv_bfloat16* w_shadow);
@@ -506,6 +512,12 @@ static int skinny_gemm_run_impl(int op, const float* in0, const float* in1, cons
       sk_small_operand_kernel<<<(int)blocks, 256, 0, s>>>(small, p.ld_small, p.small_colmajor, p.N, p.K, p.BN, p.Kp, Bs);
     }
     VC_LAUNCH_CHECK();
+  }
+  if (adam && p.a_mcontig && p.nkb == 1 && p.BN == 256 && p.Kp == 64 &&
+      fc_adam_tma_supported(p.M, p.N, p.K, p.lda, p.ldo, p.transposed, out, adam->m, adam->v, adam->shadow)) {
+    const FcAdamParams fp = {adam->m, adam->v, adam->step, adam->lr, adam->b1, adam->b2, adam->eps, adam->bc1, adam->bc2,
+                             adam->shadow};
+    return fc_adam_tma_run(big, p.lda, Bs, out, p.M, p.N, p.K, p.ldo, p.transposed, fp, s);
   }
   CUtensorMap mb, ma;
   memset(&ma, 0, sizeof(ma));
