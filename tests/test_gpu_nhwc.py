@@ -203,6 +203,26 @@ def test_single_channel_ends_tensor_core(B, H, W):
     torch.testing.assert_close(db3.double(), wantb, rtol=1e-5, atol=1e-5 * float(wantb.abs().max()) + 1e-4)
 
 
+@pytest.mark.parametrize("B,C,H,W,with_g", [(2, 128, 3, 128, False), (3, 64, 2, 256, True), (1, 32, 5, 128, False),
+                                            (2, 128, 2, 64, False)])     # the last shape takes the 64-pixel kernel
+def test_relu_backward_to_nhwc(B, C, H, W, with_g):
+    """vc_relu_bwd_bias_nhwc: g = dy * (y > 0) as bf16 NHWC (+ optionally fp32 NCHW) and its per-channel sums."""
+    from vaeclust._lib import lib, ptr, stream_ptr
+    L = lib()
+    dy, y = _r(B, C, H, W, seed=41), _r(B, C, H, W, seed=42)
+    gn = torch.full((B, H, W, C), float("nan"), dtype=torch.bfloat16, device="cuda")
+    g = torch.full((B, C, H, W), float("nan"), device="cuda") if with_g else None
+    db = torch.full((C,), float("nan"), device="cuda")
+    ws = torch.empty(L.size("vc_relu_bwd_bias_nhwc_workspace_bytes", C), dtype=torch.uint8, device="cuda")
+    L.call("vc_relu_bwd_bias_nhwc", ptr(dy), ptr(y), B, C, H, W, ptr(g), ptr(gn), ptr(db), ptr(ws), ws.numel(), stream_ptr())
+    want = dy * (y > 0)
+    assert torch.equal(gn, _nhwc(want))
+    if with_g:
+        assert torch.equal(g, want)
+    wantb = want.double().sum(dim=(0, 2, 3))
+    torch.testing.assert_close(db.double(), wantb, rtol=1e-5, atol=1e-5 * float(wantb.abs().max()) + 1e-5)
+
+
 def test_single_channel_ends_and_helpers():
     from vaeclust._lib import lib, ptr, stream_ptr
     L = lib()
