@@ -142,7 +142,7 @@ int vc_conv_nhwc_wgrad(int op, const void* g_nhwc, const void* x_nhwc, float* dW
  *  vc_nhwc_conv1_fwd    : nn.Conv2d(1, Cout, 3, 2, 1) (+ReLU) of 12:87 with y written as bf16 NHWC [B,H/2,W/2,Cout].
  *  vc_nhwc_convT1_dgrad : data gradient of nn.ConvTranspose2d(Cin, 1, 4, 2, 1) (12:137) with the ReLU mask of its input
  *                         activation act_nhwc (bf16 [B,H,W,Cin], may be NULL) applied; g written as bf16 NHWC.
- *  vc_nhwc_from_nchw    : fp32 [B,C,H,W] -> bf16 [B,H,W,C]  (the decoder's Linear output reshaped, 12:133); W % 64 == 0.
+ *  vc_nhwc_from_nchw    : fp32 [B,C,H,W] -> bf16 [B,H,W,C]  (the decoder's Linear output reshaped, 12:133); C % 16 == 0, W % 64 == 0.
  *  vc_nhwc_bias_grad    : db[c] = sum over rows of a bf16 [rows, C] matrix (bias gradient of a conv layer whose output
  *                         gradient lives in NHWC), fixed summation order. */
 int vc_nhwc_conv1_fwd(const float* x, const float* W, const float* bias, int relu, void* y_nhwc, int B, int H, int Wd,

@@ -133,29 +133,47 @@ nm_convT1_dgrad_kernel(const float* __restrict__ dy, const float* __restrict__ w
 // ---- fp32 NCHW -> bf16 NHWC.  A block takes (b, h, 64-pixel segment) x all channels; the transposition goes through
 // shared memory (reads coalesced along W, writes are one contiguous 64 x C block of the NHWC tensor).
 constexpr int NM_PX = 64;
+// A lane owns pixels lane and lane + 32 of a channel PAIR (coalesced 128-byte loads) and stores one bf16x2 word per pixel
+// into rows of C/2 + 1 words: bank = pixel + pair, no conflicts on the way in or out (a lane owning two adjacent pixels of one
+// channel made its 2-byte stores 544 bytes apart: 8-way conflicts, 2.7 TB/s).  C % 16 == 0.
 __global__ void __launch_bounds__(256)
 nm_from_nchw_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst, int B, int C, int H, int W, int ntiles) {
   extern __shared__ unsigned char nm_smem[];
-  const int pitch = C + 8;
-  __nv_bfloat16* tile = reinterpret_cast<__nv_bfloat16*>(nm_smem);      // [NM_PX][pitch]
+  const int pw = (C >> 1) + 1;
+  uint32_t* tile = reinterpret_cast<uint32_t*>(nm_smem);      // [NM_PX][pw]
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int segs = W / NM_PX;
   const int64_t plane = (int64_t)H * W;
+  const int npairs = C >> 1;
   for (int t = blockIdx.x; t < ntiles; t += gridDim.x) {
     const int seg = t % segs, r = t / segs;
     const int h = r % H, b = r / H;
-    const int64_t base = ((int64_t)b * C) * plane + (int64_t)h * W + seg * NM_PX;
-    for (int c = warp; c < C; c += 8) {
-      const float2 v = *reinterpret_cast<const float2*>(src + base + (int64_t)c * plane + 2 * lane);
-      tile[(2 * lane) * pitch + c] = __float2bfloat16_rn(v.x);
-      tile[(2 * lane + 1) * pitch + c] = __float2bfloat16_rn(v.y);
+    const int64_t base = ((int64_t)b * C) * plane + (int64_t)h * W + seg * NM_PX + lane;
+    for (int cp0 = warp; cp0 < npairs; cp0 += 32) {      // four pairs per round: 16 independent loads per lane
+      float v[4][2][2];
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const int cp = cp0 + 8 * k;
+        if (cp < npairs) {
+          const float* p = src + base + (int64_t)(2 * cp) * plane;
+          v[k][0][0] = __ldcs(p); v[k][0][1] = __ldcs(p + 32);
+          v[k][1][0] = __ldcs(p + plane); v[k][1][1] = __ldcs(p + plane + 32);
+        }
+      }
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const int cp = cp0 + 8 * k;
+        if (cp < npairs) {
+          tile[lane * pw + cp] = nm_pack(v[k][0][0], v[k][1][0]);
+          tile[(lane + 32) * pw + cp] = nm_pack(v[k][0][1], v[k][1][1]);
+        }
+      }
     }
     __syncthreads();
-    __nv_bfloat16* o = dst + (((int64_t)b * H + h) * W + seg * NM_PX) * C;
-    const int vec_per_px = C / 8;
-    for (int e = threadIdx.x; e < NM_PX * vec_per_px; e += blockDim.x) {
-      const int px = e / vec_per_px, q = e - px * vec_per_px;
-      reinterpret_cast<uint4*>(o)[e] = *reinterpret_cast<const uint4*>(tile + px * pitch + q * 8);
+    uint32_t* o = reinterpret_cast<uint32_t*>(dst + (((int64_t)b * H + h) * W + seg * NM_PX) * C);
+    for (int e = threadIdx.x; e < NM_PX * npairs; e += blockDim.x) {
+      const int px = e / npairs, q = e - px * npairs;
+      o[e] = tile[px * pw + q];
     }
     __syncthreads();
   }
@@ -171,15 +189,25 @@ nm_colsum_kernel(const __nv_bfloat16* __restrict__ g, int64_t rows, int C, doubl
   const int grp = threadIdx.x / vecs, q = threadIdx.x - grp * vecs;
   float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
   if (grp < groups) {
-    for (int64_t r = (int64_t)blockIdx.x * groups + grp; r < rows; r += (int64_t)gridDim.x * groups) {
-      const uint4 v = __ldcs(reinterpret_cast<const uint4*>(g + r * C) + q);
+    // four independent 16-byte loads per round (one dependent load per iteration left the kernel latency-bound at 2.5 TB/s)
+    const int64_t step = (int64_t)gridDim.x * groups;
+    int64_t r = (int64_t)blockIdx.x * groups + grp;
+    auto add = [&](const uint4& v) {
       const uint32_t u[4] = {v.x, v.y, v.z, v.w};
 #pragma unroll
       for (int k = 0; k < 4; ++k) {
         acc[2 * k] += __uint_as_float(u[k] << 16);
         acc[2 * k + 1] += __uint_as_float(u[k] & 0xffff0000u);
       }
+    };
+    for (; r + 3 * step < rows; r += 4 * step) {
+      const uint4 v0 = __ldcs(reinterpret_cast<const uint4*>(g + r * C) + q);
+      const uint4 v1 = __ldcs(reinterpret_cast<const uint4*>(g + (r + step) * C) + q);
+      const uint4 v2 = __ldcs(reinterpret_cast<const uint4*>(g + (r + 2 * step) * C) + q);
+      const uint4 v3 = __ldcs(reinterpret_cast<const uint4*>(g + (r + 3 * step) * C) + q);
+      add(v0); add(v1); add(v2); add(v3);
     }
+    for (; r < rows; r += step) add(__ldcs(reinterpret_cast<const uint4*>(g + r * C) + q));
 #pragma unroll
     for (int k = 0; k < 8; ++k) nm_red[grp * C + q * 8 + k] = acc[k];
   }
@@ -426,15 +454,15 @@ extern "C" int vc_nhwc_convT1_dgrad_bias(const float* dy, const float* Wt, const
 
 extern "C" int vc_nhwc_from_nchw(const float* src, void* dst_nhwc, int B, int C, int H, int W, void* stream) {
   VC_REQUIRE(src && dst_nhwc && B > 0 && H > 0, VC_ERR_BAD_ARG, "vc_nhwc_from_nchw: bad arguments");
-  VC_REQUIRE(C % 8 == 0 && C > 0 && C <= 512 && W % NM_PX == 0, VC_ERR_UNSUPPORTED,
-             "vc_nhwc_from_nchw: need C %% 8 == 0, C <= 512, W %% 64 == 0 (got C=%d W=%d)", C, W);
+  VC_REQUIRE(C % 16 == 0 && C > 0 && C <= 512 && W % NM_PX == 0, VC_ERR_UNSUPPORTED,
+             "vc_nhwc_from_nchw: need C %% 16 == 0, C <= 512, W %% 64 == 0 (got C=%d W=%d)", C, W);
   VC_REQUIRE((reinterpret_cast<uintptr_t>(src) & 7) == 0 && (reinterpret_cast<uintptr_t>(dst_nhwc) & 15) == 0, VC_ERR_BAD_ARG,
              "vc_nhwc_from_nchw: misaligned pointers");
   const int64_t ntiles = (int64_t)B * H * (W / NM_PX);
   VC_REQUIRE(ntiles < 2147483647LL, VC_ERR_UNSUPPORTED, "vc_nhwc_from_nchw: tensor too large");
   int grid = 4 * sm_count();
   if (grid > ntiles) grid = (int)ntiles;
-  nm_from_nchw_kernel<<<grid, 256, (size_t)NM_PX * (C + 8) * 2, as_stream(stream)>>>(
+  nm_from_nchw_kernel<<<grid, 256, (size_t)NM_PX * ((C >> 1) + 1) * 4, as_stream(stream)>>>(
       src, static_cast<__nv_bfloat16*>(dst_nhwc), B, C, H, W, (int)ntiles);
   VC_LAUNCH_CHECK();
   return VC_OK;

@@ -110,7 +110,7 @@ def decoder_supported(h, deconvs) -> bool:
         return False
     B, C0, H, W = h.shape
     c1, c2, c3 = (d.weight.shape[1] for d in deconvs)
-    if c3 != 1 or C0 % 8 or W % 64 or deconvs[0].weight.shape[0] != C0 or c2 % 32:
+    if c3 != 1 or C0 % 16 or W % 64 or deconvs[0].weight.shape[0] != C0 or c2 % 32:
         return False
     d1, d2 = (B, C0, H, W, c1), (B, c1, 2 * H, 2 * W, c2)
     return _ok(("vc_conv_nhwc_supported", (CONVT_FWD, *d1)), ("vc_conv_nhwc_supported", (CONVT_FWD, *d2)),
