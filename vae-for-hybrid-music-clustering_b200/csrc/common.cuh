@@ -62,6 +62,24 @@ __device__ __forceinline__ float ldg_pred(const float* p, uint32_t pred) {
   return v;
 }
 
+// Sum of p[s * stride] for s = first, first + step, ... < n, added in that order (the result does not depend on the batching).
+// Eight loads are in flight at a time: the fold kernels that finish every split-K / per-block reduction were chains of
+// dependent L2 round trips (10-30 us for a few hundred partials) when written as a plain loop.
+template <typename T>
+__device__ __forceinline__ T strided_sum_ordered(const T* __restrict__ p, int64_t stride, int first, int n, int step) {
+  T acc = 0;
+  int s = first;
+  for (; s + 7 * step < n; s += 8 * step) {
+    T v[8];
+#pragma unroll
+    for (int u = 0; u < 8; ++u) v[u] = __ldcs(p + (int64_t)(s + u * step) * stride);
+#pragma unroll
+    for (int u = 0; u < 8; ++u) acc += v[u];
+  }
+  for (; s < n; s += step) acc += __ldcs(p + (int64_t)s * stride);
+  return acc;
+}
+
 // Block-wide sum, result valid in thread 0. `scratch` holds >= 32 elements.
 template <typename T>
 __device__ __forceinline__ T block_sum(T v, T* scratch) {

@@ -559,8 +559,7 @@ __global__ void __launch_bounds__(256) tap_wgrad_fold_kernel(const double* __res
   const int lane = threadIdx.x & 31, g = threadIdx.x >> 5;
   const int e = blockIdx.x * 32 + lane;
   double v = 0.0;
-  if (e < n)
-    for (int b = g; b < nblk; b += 8) v += part[(int64_t)b * n + e];
+  if (e < n) v = strided_sum_ordered(part + e, (int64_t)n, g, nblk, 8);
   sub[g][lane] = v;
   __syncthreads();
   if (g != 0 || e >= n) return;

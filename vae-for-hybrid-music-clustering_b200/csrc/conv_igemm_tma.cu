@@ -362,12 +362,19 @@ relu_bwd_bias_nhwc2_kernel(const float* __restrict__ dy, const float* __restrict
   for (int c = threadIdx.x; c < C; c += blockDim.x) part[(int64_t)blockIdx.x * C + c] = (double)csum[c];
 }
 
-__global__ void rn_fold_kernel(const double* __restrict__ part, int nblocks, int C, float* __restrict__ db) {
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
-  if (c >= C) return;
-  double s = 0.0;
-  for (int b = 0; b < nblocks; ++b) s += part[(int64_t)b * C + c];
-  db[c] = (float)s;
+// db[c] = sum over blocks: 256 threads per 32 channels, each warp adds every eighth partial, sub-sums added in warp order
+__global__ void __launch_bounds__(256) rn_fold_kernel(const double* __restrict__ part, int nblocks, int C, float* __restrict__ db) {
+  __shared__ double sub[8][32];
+  const int lane = threadIdx.x & 31, gw = threadIdx.x >> 5;
+  const int c = blockIdx.x * 32 + lane;
+  double v = 0.0;
+  if (c < C) v = strided_sum_ordered(part + c, (int64_t)C, gw, nblocks, 8);
+  sub[gw][lane] = v;
+  __syncthreads();
+  if (gw != 0 || c >= C) return;
+#pragma unroll
+  for (int i = 1; i < 8; ++i) v += sub[i][lane];
+  db[c] = (float)v;
 }
 
 // ---- host ---------------------------------------------------------------------------------------------------------
@@ -520,7 +527,7 @@ extern "C" int vc_relu_bwd_bias_nhwc(const float* dy, const float* y, int B, int
                                                                            H, W, (int)ntiles, part);
   }
   VC_LAUNCH_CHECK();
-  rn_fold_kernel<<<(C + 127) / 128, 128, 0, as_stream(stream)>>>(part, grid, C, db);
+  rn_fold_kernel<<<(C + 31) / 32, 256, 0, as_stream(stream)>>>(part, grid, C, db);
   VC_LAUNCH_CHECK();
   return VC_OK;
 }

@@ -167,8 +167,7 @@ nw_fold_kernel(const float* __restrict__ part, int nsplit, int ngroups, int Cp, 
   const int64_t per_split = (int64_t)ngroups * Cp * cols;
   const int64_t e = (int64_t)blockIdx.x * 32 + lane;
   float acc = 0.f;
-  if (e < per_split)
-    for (int s = wq; s < nsplit; s += 8) acc += part[(int64_t)s * per_split + e];
+  if (e < per_split) acc = strided_sum_ordered(part + e, per_split, wq, nsplit, 8);
   sub[wq][lane] = acc;
   __syncthreads();
   if (wq != 0 || e >= per_split) return;

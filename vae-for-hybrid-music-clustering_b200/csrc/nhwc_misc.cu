@@ -226,8 +226,7 @@ nm_colsum_fold_kernel(const double* __restrict__ part, int nblk, int C, float* _
   const int lane = threadIdx.x & 31, gw = threadIdx.x >> 5;
   const int c = blockIdx.x * 32 + lane;
   double v = 0.0;
-  if (c < C)
-    for (int b = gw; b < nblk; b += 8) v += part[(int64_t)b * C + c];
+  if (c < C) v = strided_sum_ordered(part + c, (int64_t)C, gw, nblk, 8);
   sub[gw][lane] = v;
   __syncthreads();
   if (gw != 0 || c >= C) return;
@@ -363,8 +362,7 @@ nm_tap_fold_kernel(const double* __restrict__ part, int nblk, int n, float* __re
   const int lane = threadIdx.x & 31, g = threadIdx.x >> 5;
   const int e = blockIdx.x * 32 + lane;
   double v = 0.0;
-  if (e < n)
-    for (int b = g; b < nblk; b += 8) v += part[(int64_t)b * n + e];
+  if (e < n) v = strided_sum_ordered(part + e, (int64_t)n, g, nblk, 8);
   sub[g][lane] = v;
   __syncthreads();
   if (g != 0 || e >= n) return;

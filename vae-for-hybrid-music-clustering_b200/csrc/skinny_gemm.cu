@@ -379,8 +379,7 @@ __global__ void __launch_bounds__(256) sk_fold_kernel(const float* __restrict__ 
   const int64_t e = (int64_t)blockIdx.x * 32 + lane;
   const int64_t MN = (int64_t)M * N;
   float acc = 0.f;
-  if (e < MN)
-    for (int zz = g; zz < nsplit; zz += 8) acc += __ldg(part + (int64_t)zz * MN + e);
+  if (e < MN) acc = strided_sum_ordered(part + e, MN, g, nsplit, 8);
   sub[g][lane] = acc;
   __syncthreads();
   if (g != 0 || e >= MN) return;
