@@ -33,6 +33,10 @@ struct SkArgs {
   // bf16 shadow of the big matrix (a_bf16): the A tile is one TMA load (K-major box, or two MN-major boxes when the
   // matrix is m-contiguous) instead of eight producer warps reading fp32 and converting -- half the bytes, no instructions
   int a_bf16;
+  // fused Adam on a parameter stored [N][M] (transposed): the MMA operands swap roles (D_h[n][m] = Bs_h . A^T, two 128-row
+  // halves of n), so the TMEM lane is the parameter ROW in both layouts and the epilogue below needs no second code path
+  // (the m-lane variant read its float4s as four scalar shared-memory loads with 8-way bank conflicts: 422 vs 348 us)
+  int swap;
   int adam;
   float* ad_m; float* ad_v;
   __nv_bfloat16* ad_shadow;                  // fused Adam also refreshes the shadow (same layout as the parameter) or null
@@ -290,7 +294,12 @@ skinny_gemm_kernel(const SkArgs a, const __grid_constant__ CUtensorMap mapB, con
 #pragma unroll
           for (int u = 0; u < 4; ++u) {
             const int r = hb + 4 * u + sub;           // the strided index of this lane in group u
-            if (a.transposed) {                       // element (m, n) at n*ldo + m: contiguous in m; r is n, l4.. are m
+            if (a.swap) {                             // lanes of the accumulator = n: row (cc / 4) * 128 + q * 32 + r, columns = m
+              gg[u] = *reinterpret_cast<const float4*>(tb + r * 36 + l4);
+              const int nrow = (cc >> 2) * 128 + q * 32 + r, mcol = m0 + (cc & 3) * 32 + l4;
+              off[u] = (int64_t)nrow * a.ldo + mcol;
+              ok[u] = nrow < a.N && mcol + 3 < a.M;
+            } else if (a.transposed) {                // element (m, n) at n*ldo + m: contiguous in m; r is n, l4.. are m
               gg[u] = make_float4(tb[(l4 + 0) * 36 + r], tb[(l4 + 1) * 36 + r], tb[(l4 + 2) * 36 + r], tb[(l4 + 3) * 36 + r]);
               off[u] = (int64_t)(cc * 32 + r) * a.ldo + mrow0 + l4;
               ok[u] = cc * 32 + r < a.N && mrow0 + l4 + 3 < a.M;
@@ -352,7 +361,13 @@ skinny_gemm_kernel(const SkArgs a, const __grid_constant__ CUtensorMap mapB, con
         for (int kk = 0; kk < 4; ++kk) {
           const uint64_t da = (a.a_bf16 && a.a_mcontig) ? tc05::desc_mn_sw128(sa + kk * 2048, SK_A_BYTES / 2)
                                                         : tc05::desc_k_sw128(sa + kk * 32);
-          tc05::mma_bf16(tmem_base, da, tc05::desc_k_sw128(sb + kk * 32), a.idesc, (uint32_t)((it | kk) != 0));
+          if (a.swap) {      // rows of D = n (128-row halves of the small operand), columns = the 128 m of this tile
+            for (int h = 0; h < (a.BN >> 7); ++h)
+              tc05::mma_bf16(tmem_base + h * 128, tc05::desc_k_sw128(sb + h * (128 * 128) + kk * 32), da, a.idesc,
+                             (uint32_t)((it | kk) != 0));
+          } else {
+            tc05::mma_bf16(tmem_base, da, tc05::desc_k_sw128(sb + kk * 32), a.idesc, (uint32_t)((it | kk) != 0));
+          }
         }
         tc05::commit(&empty[s]);
       }
@@ -545,6 +560,10 @@ static int skinny_gemm_run_impl(int op, const float* in0, const float* in1, cons
   a.a_bf16 = w_shadow ? 1 : 0;
   a.idesc = tc05::idesc(tc05::kFmtBF16, 128, p.BN, (w_shadow && p.a_mcontig) ? 1 : 0, 0);
   size_t ring = (size_t)p.stages * (SK_A_BYTES + (size_t)p.BN * 128);
+  if (adam && p.transposed && p.BN % 128 == 0 && !getenv("VAECLUST_SK_NOSWAP")) {
+    a.swap = 1;
+    a.idesc = tc05::idesc(tc05::kFmtBF16, 128, 128, 0, 0);
+  }
   if (adam) {
     a.adam = 1; a.ad_m = adam->m; a.ad_v = adam->v; a.ad_step = adam->step; a.ad_shadow = adam->shadow;
     a.ad_lr = adam->lr; a.ad_b1 = adam->b1; a.ad_b2 = adam->b2; a.ad_eps = adam->eps; a.ad_bc1 = adam->bc1; a.ad_bc2 = adam->bc2;
