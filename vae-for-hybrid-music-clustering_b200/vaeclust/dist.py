@@ -228,6 +228,26 @@ class ShardedGradSync(OverlappedGradSync):
         self.gathers = []
         self.dirty = []      # sharded parameters whose other slices are stale (updated by their owners, not gathered yet)
         self._premul = None if hasattr(td, "_make_nccl_premul_sum") else False
+        # bf16 mode (enable_bf16_gather): forward and data gradient of the wide Linear layers read a bf16 copy of the weight
+        # anyway, so the owners' updated slices travel as bf16 (half the all-gather bytes, and it is the all-gather the
+        # forward waits for); the fp32 master keeps only this rank's slice current until flush() gathers it in fp32.
+        self.shadow = {}     # id(p) -> bf16 tensor of p's shape
+        self._stale_fp32 = {}
+
+    def enable_bf16_gather(self, params) -> int:
+        """Give every sharded CUDA parameter in `params` a bf16 shadow (`p._vc_shadow`, read by vaeclust.ops.linear in
+        bf16 mode) and gather updated slices into it instead of into the fp32 parameter.  Returns how many took it."""
+        n = 0
+        if self.side is None or world_size(self.group) <= 1 or td.get_backend(self.group) != "nccl":
+            return 0
+        for p in params:
+            if id(p) in self.sharded and id(p) not in self.shadow and p.is_cuda and p.dim() == 2:
+                sh = torch.empty(p.shape, dtype=torch.bfloat16, device=p.device)
+                sh.copy_(p.detach())
+                self.shadow[id(p)] = sh
+                p._vc_shadow = sh
+                n += 1
+        return n
 
     def _on_big_grad(self, p) -> None:
         if world_size(self.group) <= 1 or p.grad is None:
@@ -257,6 +277,9 @@ class ShardedGradSync(OverlappedGradSync):
                     td.reduce_scatter_tensor(gs, flat_g, op=td.ReduceOp.SUM, group=self.group)   # side waits for the result
                 with torch.no_grad():
                     self.update(p)
+                    sh = self.shadow.get(id(p))
+                    if sh is not None:      # this rank's slice of the bf16 copy follows its fp32 master
+                        sh.view(-1)[lo:hi].copy_(p.data.view(-1)[lo:hi])
             self.dirty.append(p)
         else:   # gloo (CPU tests): no reduce-scatter there; same data movement through an all-reduce
             flat_g.mul_(self.factor)
@@ -280,8 +303,11 @@ class ShardedGradSync(OverlappedGradSync):
             # in the reverse of the order the hooks fired, so the first layer's weight arrives first
             for p in reversed(self.dirty):
                 lo, hi, _ = self.sharded[id(p)]
-                flat_p = p.data.view(-1)
+                sh = self.shadow.get(id(p))
+                flat_p = p.data.view(-1) if sh is None else sh.view(-1)
                 p._vc_gather = td.all_gather_into_tensor(flat_p, flat_p[lo:hi], group=self.group, async_op=True)
+                if sh is not None:
+                    self._stale_fp32[id(p)] = p
         self.dirty = []
 
     def begin(self, local_batch: int, global_batch: int) -> None:
@@ -306,7 +332,16 @@ class ShardedGradSync(OverlappedGradSync):
         sharded parameter whatever the bookkeeping says (graph replays update slices without running the hooks)."""
         if force:
             self.dirty = [p for p in self.big if id(p) in self.sharded]
-        if self.side is None or not self.dirty:
+            self._stale_fp32.update({id(p): p for p in self.dirty if id(p) in self.shadow})
+        if self.side is None:
             return
-        self._start_gathers()
-        self.join()
+        if self.dirty:
+            self._start_gathers()
+            self.join()
+        if self._stale_fp32:        # the fp32 masters: every rank holds only its own slice up to date
+            with torch.no_grad():
+                for p in self._stale_fp32.values():
+                    lo, hi, _ = self.sharded[id(p)]
+                    flat_p = p.data.view(-1)
+                    td.all_gather_into_tensor(flat_p, flat_p[lo:hi], group=self.group)
+            self._stale_fp32 = {}

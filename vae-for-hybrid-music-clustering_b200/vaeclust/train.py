@@ -68,6 +68,7 @@ class VAEStep:
         # id(p) -> (tensor, p._version, p.data_ptr()) -- rebuilt when the parameter was changed by anything else
         self.bf16_shadows = os.environ.get("VAECLUST_FC_SHADOW", "1") != "0"
         self._shadow = {}
+        self._dp_shadows = None      # data parallel: number of weights whose slices are gathered as bf16 (dist.ShardedGradSync)
         self.mode = VC_LOSS_SUM_MEAN if kind == "mlp19" else VC_LOSS_MEAN_MEAN
         self.multi = group is not None and vdist.world_size(group) > 1
         self.opt = Adam(model.parameters(), lr=lr, capturable=capturable)
@@ -88,6 +89,11 @@ class VAEStep:
         m = self.model
         fused = []
         if self.sync is not None:
+            if (self._dp_shadows is None and self.bf16_shadows and ops.PRECISION == "bf16"
+                    and hasattr(self.sync, "enable_bf16_gather") and os.environ.get("VAECLUST_DP_BF16_GATHER", "1") != "0"):
+                # the wide weights travel between the ranks as bf16 (what forward / data gradient read); sync_params()
+                # brings the fp32 masters up to date
+                self._dp_shadows = self.sync.enable_bf16_gather(self._wide)
             rows = x.shape[0] if local_rows is None else int(local_rows)
             self.sync.begin(rows, global_batch or x.shape[0] * vdist.world_size(self.group))
         else:
