@@ -182,9 +182,9 @@ def bytes_of(name: str, sig) -> float:
             return 2.0 * B * Cout * (H // 2) * (W // 2) + 4.0 * B * H * W
         if name == "vc_nhwc_from_nchw":
             return 6.0 * sig[0] * sig[1] * sig[2] * sig[3]
-        if name == "vc_linear_wgrad_adam":      # p, m, v read and written once; the gradient never touches memory
+        if name == "vc_linear_wgrad_adam":      # p, m, v read and written once (+ the bf16 shadow written); no gradient traffic
             B, Cin, Cout = sig[:3]
-            return 24.0 * Cin * Cout + 4.0 * B * (Cin + Cout)
+            return 26.0 * Cin * Cout + 4.0 * B * (Cin + Cout)
         if name == "vc_linear_bf16w":           # bf16 weight shadow read once, fp32 activations in and out
             _op, B, Cin, Cout = sig[:4]
             return 2.0 * Cin * Cout + 4.0 * B * (Cin + Cout)
@@ -211,14 +211,14 @@ def family_of(name: str, sig) -> str:
         return "skinny_gemm from the bf16 shadow (FC fwd / dgrad)"
     if name in ("vc_nhwc_conv1_fwd", "vc_nhwc_convT1_dgrad", "vc_conv1_wgrad_bias", "vc_convT1_wgrad", "vc_nhwc_convT1_fwd",
                 "vc_nhwc_tap_wgrad", "vc_nhwc_conv1_wgrad_bias", "vc_nhwc_convT1_dgrad_bias"):
-        return "conv_direct (1-channel ends)"
+        return "single-channel ends (mma.sync)"
     if name != "vc_dense_op":
         return name
     op, _prec, B, Cin, H, W, Cout = sig[:7]
     if op <= 2:
         return "skinny_gemm (FC 262144<->256)" if Cin * Cout >= (1 << 22) else "small_linear (mma.sync, latent head)"
     if (op in (3, 5) and Cin == 1) or (op in (6, 7, 8) and Cout == 1):   # incl. the tap-correlation weight gradients
-        return "conv_direct (1-channel ends)"
+        return "single-channel ends (mma.sync)"
     if op in (5, 8):
         return "conv_wgrad_igemm"
     return "conv_igemm (fwd / dgrad)"
@@ -356,7 +356,7 @@ def roofline_from_summary(summ, steps, n_params, pk, ms_per_step):
     # DRAM bytes per launch of the headline family from the committed ncu capture (same command, --no-graph), next to
     # the algorithmic bytes per launch the `achieved` figure uses
     try:
-        tr = json.load(open(ROOT / "profiles" / "ncu_traffic_r2.json"))
+        tr = json.load(open(ROOT / "profiles" / "ncu_traffic_r2b.json"))
         if roof["kernel"] in tr:
             roof["traffic"] = tr[roof["kernel"]]["dram_bytes_per_launch"]
             roof["traffic_source"] = tr["_source"]
