@@ -276,11 +276,209 @@ fc_adam_kernel(const FaArgs a, const __grid_constant__ CUtensorMap mapB, const _
   }
 }
 
+// ---- Variant 2 (VAECLUST_FC_ADAM_TMA=2): the accumulator tile goes to shared memory, p / m / v are swept in MEMORY ORDER.
+// Both kernels above (and the fused epilogue of skinny_gemm_kernel) touch every 1 KB row of the parameter eight separate
+// times per tile (once per 32-column chunk, microseconds apart): eight DRAM row activations instead of one, the suspected
+// reason why this read-modify-write stream stops at 5.2 TB/s while the linear multi-tensor Adam reaches 6.1 (measured: it is
+// NOT -- 382-392 us per launch against 337 us for the tile-order epilogue, profiles/fc_adam_tma_r2.txt).  Here the
+// 128 x 256 (or 256 x 128) fp32 accumulator tile is drained into a 128 KB shared-memory tile G (16-byte chunks XOR-swizzled
+// with the row, conflict-free for the row-per-lane drain AND the row-per-warp sweep), and the eight warps then walk the
+// tile's p / m / v in address order: a warp instruction moves 512 contiguous bytes, the CTA covers 16 KB contiguous per
+// batch, every DRAM page is consumed at once.  The sweep is software-pipelined across tile boundaries (the loads of the next
+// batch are in flight while the drain of the next tile runs), the MMA of the next tile runs under the sweep (two TMEM buffers).
+constexpr uint32_t FR_G_BYTES = 128 * 256 * 4;
+constexpr int FR_NW = 16;                         // worker warps (producers + drain + sweep); warp FR_NW issues the MMAs
+constexpr int FR_THREADS = (FR_NW + 1) * 32;
+
+template <bool APPROX>
+__global__ void __launch_bounds__(FR_THREADS, 1)
+fc_adam_rows_kernel(const FaArgs a, const __grid_constant__ CUtensorMap mapB, float* __restrict__ P, float* __restrict__ Mo,
+                    float* __restrict__ Vo) {
+  extern __shared__ unsigned char smem_raw[];
+  unsigned char* smem = smem_raw + ((1024u - (tma::s32(smem_raw) & 1023u)) & 1023u);
+  unsigned char* sG = smem;                                   // 128 KB
+  unsigned char* sB = sG + FR_G_BYTES;                        // 32 KB
+  unsigned char* sA = sB + FA_B_BYTES;                        // 2 x 16 KB
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sA + 2 * FA_A_BYTES);
+  uint64_t* a_full = bars;            // [2] FR_NW * 32 producer arrivals
+  uint64_t* a_empty = bars + 2;       // [2] tcgen05.commit
+  uint64_t* acc_full = bars + 4;      // [2] tcgen05.commit
+  uint64_t* acc_empty = bars + 6;     // [2] FR_NW warps
+  uint64_t* b_full = bars + 8;        // [1]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 9);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int ntiles = a.M >> 7;
+  const int my_tiles = ((int)blockIdx.x < ntiles) ? (ntiles - 1 - (int)blockIdx.x) / (int)gridDim.x + 1 : 0;
+
+  if (threadIdx.x == 0) {
+    tma::prefetch_map(&mapB);
+    for (int s = 0; s < 2; ++s) {
+      tma::mbar_init(&a_full[s], FR_NW * 32); tma::mbar_init(&a_empty[s], 1);
+      tma::mbar_init(&acc_full[s], 1); tma::mbar_init(&acc_empty[s], FR_NW);
+    }
+    tma::mbar_init(b_full, 1);
+    tma::mbar_fence_init();
+  }
+  if (warp == FR_NW) tc05::tmem_alloc(tmem_slot, 512);
+  tc05::fence_before();
+  __syncthreads();
+  tc05::fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp < FR_NW) {
+    // producer part: this warp converts rows 8 warp .. 8 warp + 7 of the fp32 [k][m] activation tile (lane = 8 rows x 4 k-pairs)
+    const int mq = lane & 7, kq = lane >> 3;
+    float alo[8], ahi[8];
+    auto a_load = [&](int it) {
+      const int m0 = ((int)blockIdx.x + it * (int)gridDim.x) << 7;
+#pragma unroll
+      for (int c = 0; c < 8; ++c) {
+        const int k = 2 * (4 * c + kq);
+        const float* p = a.A + (int64_t)k * a.lda + m0 + warp * 8 + mq;
+        alo[c] = ldg_pred(p, k < a.K ? 1u : 0u);
+        ahi[c] = ldg_pred(p + a.lda, k + 1 < a.K ? 1u : 0u);
+      }
+    };
+    auto a_store = [&](int it) {
+      const int s = it & 1;
+      tma::mbar_wait_backoff(&a_empty[s], (((uint32_t)it >> 1) & 1u) ^ 1u, 64);
+      unsigned char* tile = sA + (size_t)s * FA_A_BYTES;
+      const uint32_t r = (uint32_t)(warp * 8 + mq);
+#pragma unroll
+      for (int c = 0; c < 8; ++c)
+        *reinterpret_cast<uint32_t*>(tile + r * 128u + (((uint32_t)c ^ (r & 7u)) << 4) + ((uint32_t)kq << 2)) = fa_pack(alo[c], ahi[c]);
+      tma::fence_proxy_async();
+      tma::mbar_arrive(&a_full[s]);
+    };
+    const int q = warp & 3, hh = warp >> 2;                   // TMEM lane quarter, which two of the eight 32-column chunks
+    float bc1 = a.bc1, bc2 = a.bc2;
+    if (a.step) { bc1 = a.step->bias_corr1; bc2 = a.step->bias_corr2; }
+    const float step_size = a.lr / bc1, inv_sqrt_bc2 = 1.f / sqrtf(bc2);
+    // G: rows x cols fp32, 16-byte chunk ch of row r at r * pitch + ((ch ^ (r & 7)) << 4)
+    const uint32_t pitch = a.transposed ? 512u : 1024u;       // 128 or 256 columns
+    // unit u (0..255 per tile) = 128 consecutive floats of one row, in memory order: row = u / upr, column (u % upr) * 128
+    const int upr_shift = a.transposed ? 0 : 1;
+    auto goff = [&](int it, int u) -> int64_t {
+      const int m0 = ((int)blockIdx.x + it * (int)gridDim.x) << 7;
+      const int row = u >> upr_shift, c0 = (u & ((1 << upr_shift) - 1)) << 7;
+      return a.transposed ? (int64_t)row * a.ldo + m0 + c0 + 4 * lane : (int64_t)(m0 + row) * a.ldo + c0 + 4 * lane;
+    };
+    // batch bt (0..3 per tile) of this warp: units 64 bt + 16 i + warp, i = 0..3 -> the CTA covers 64 consecutive units (32 KB
+    // of each array) per batch, a warp instruction 512 contiguous bytes
+    float4 pp[4], mm[4], vv[4];
+    auto load_batch = [&](int it, int bt) {
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const int64_t o = goff(it, 64 * bt + 16 * i + warp);
+        pp[i] = *reinterpret_cast<const float4*>(P + o);
+        mm[i] = __ldcs(reinterpret_cast<const float4*>(Mo + o));
+        vv[i] = __ldcs(reinterpret_cast<const float4*>(Vo + o));
+      }
+    };
+    auto process_batch = [&](int it, int bt) {
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const int u = 64 * bt + 16 * i + warp;
+        const uint32_t row = (uint32_t)(u >> upr_shift), ch = (uint32_t)(((u & ((1 << upr_shift) - 1)) << 5) + lane);
+        const float4 g = *reinterpret_cast<const float4*>(sG + row * pitch + ((ch ^ (row & 7u)) << 4));
+        fa_adam<APPROX>(g.x, pp[i].x, mm[i].x, vv[i].x, a.b1, a.b2, step_size, inv_sqrt_bc2, a.eps);
+        fa_adam<APPROX>(g.y, pp[i].y, mm[i].y, vv[i].y, a.b1, a.b2, step_size, inv_sqrt_bc2, a.eps);
+        fa_adam<APPROX>(g.z, pp[i].z, mm[i].z, vv[i].z, a.b1, a.b2, step_size, inv_sqrt_bc2, a.eps);
+        fa_adam<APPROX>(g.w, pp[i].w, mm[i].w, vv[i].w, a.b1, a.b2, step_size, inv_sqrt_bc2, a.eps);
+      }
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const int64_t o = goff(it, 64 * bt + 16 * i + warp);
+        *reinterpret_cast<float4*>(P + o) = pp[i];
+        __stcs(reinterpret_cast<float4*>(Mo + o), mm[i]);
+        __stcs(reinterpret_cast<float4*>(Vo + o), vv[i]);
+        if (a.shadow)
+          *reinterpret_cast<uint2*>(a.shadow + o) = make_uint2(fa_pack(pp[i].x, pp[i].y), fa_pack(pp[i].z, pp[i].w));
+      }
+    };
+    if (my_tiles > 0) {
+      a_load(0);
+      a_store(0);
+    }
+    for (int it = 0; it < my_tiles; ++it) {
+      const int ab = it & 1;
+      if (it + 1 < my_tiles) a_load(it + 1);
+      load_batch(it, 0);                 // in flight under the drain
+      // ---- drain the accumulator of tile it into G (everybody is done reading G of tile it - 1: barrier at the loop end)
+      tma::mbar_wait_backoff(&acc_full[ab], ((uint32_t)it >> 1) & 1u, 64);
+      tc05::fence_after();
+#pragma unroll 1
+      for (int j = hh; j < 8; j += 4) {
+        float g[32];
+        tc05::ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(ab * 256 + j * 32), g);
+        tc05::ld_wait();
+        // TMEM (lane, column j * 32 + i) -> (row, column) of the parameter tile
+        const uint32_t row = a.transposed ? (uint32_t)((j >> 2) * 128 + q * 32 + lane) : (uint32_t)(q * 32 + lane);
+        const uint32_t ch0 = a.transposed ? (uint32_t)((j & 3) * 8) : (uint32_t)(j * 8);
+        unsigned char* gr = sG + row * pitch;
+#pragma unroll
+        for (int i = 0; i < 8; ++i)
+          *reinterpret_cast<float4*>(gr + (((ch0 + i) ^ (row & 7u)) << 4)) = make_float4(g[4 * i], g[4 * i + 1], g[4 * i + 2], g[4 * i + 3]);
+      }
+      tc05::fence_before();
+      if (lane == 0) tma::mbar_arrive(&acc_empty[ab]);
+      asm volatile("bar.sync 1, %0;" ::"n"(FR_NW * 32) : "memory");
+      if (it + 1 < my_tiles) a_store(it + 1);
+      // ---- sweep in memory order
+#pragma unroll 1
+      for (int bt = 0; bt < 4; ++bt) {
+        if (bt > 0) load_batch(it, bt);
+        process_batch(it, bt);
+      }
+      asm volatile("bar.sync 1, %0;" ::"n"(FR_NW * 32) : "memory");      // G may be overwritten
+    }
+  } else {
+    if (tc05::elect_one()) {
+      tma::mbar_expect_tx(b_full, FA_B_BYTES);
+      tma::load_2d(sB, &mapB, b_full, 0, 0);
+    }
+    __syncwarp();
+    tma::mbar_wait_backoff(b_full, 0, 64);
+    for (int it = 0; it < my_tiles; ++it) {
+      const int s = it & 1;
+      const uint32_t ph = ((uint32_t)it >> 1) & 1u;
+      tma::mbar_wait_backoff(&acc_empty[s], ph ^ 1u, 64);
+      tma::mbar_wait_backoff(&a_full[s], ph, 32);
+      tc05::fence_after();
+      if (tc05::elect_one()) {
+        const uint32_t sa = tma::s32(sA + (size_t)s * FA_A_BYTES), sb = tma::s32(sB);
+        const uint32_t d = tmem_base + (uint32_t)(s * 256);
+#pragma unroll
+        for (int kk = 0; kk < 4; ++kk) {
+          if (a.transposed) {
+            tc05::mma_bf16(d, tc05::desc_k_sw128(sb + kk * 32), tc05::desc_k_sw128(sa + kk * 32), a.idesc, (uint32_t)(kk != 0));
+            tc05::mma_bf16(d + 128, tc05::desc_k_sw128(sb + 128 * 128 + kk * 32), tc05::desc_k_sw128(sa + kk * 32), a.idesc,
+                           (uint32_t)(kk != 0));
+          } else {
+            tc05::mma_bf16(d, tc05::desc_k_sw128(sa + kk * 32), tc05::desc_k_sw128(sb + kk * 32), a.idesc, (uint32_t)(kk != 0));
+          }
+        }
+        tc05::commit(&a_empty[s]);
+        tc05::commit(&acc_full[s]);
+      }
+      __syncwarp();
+    }
+  }
+
+  tc05::fence_before();
+  __syncthreads();
+  if (warp == FR_NW) {
+    tc05::fence_after();
+    tc05::tmem_dealloc(tmem_base, 512);
+  }
+}
+
 // ---- host -----------------------------------------------------------------------------------------------------------
 bool fc_adam_tma_supported(int M, int N, int K, int64_t lda, int64_t ldo, int transposed, const void* p, const void* m,
                            const void* v, const void* shadow) {
   static const bool on = getenv("VAECLUST_FC_ADAM_TMA") && atoi(getenv("VAECLUST_FC_ADAM_TMA")) != 0;
-  if (!on) return false;
+  if (!on) return false;      // 1: TMA-staged boxes, 2: shared-memory accumulator tile + row-linear sweep
   if (N != 256 || M % 128 != 0 || K < 1 || K > 64 || lda < M || (ldo & 7)) return false;
   if (transposed ? ldo < M : ldo < N) return false;
   const uintptr_t al = reinterpret_cast<uintptr_t>(p) | reinterpret_cast<uintptr_t>(m) | reinterpret_cast<uintptr_t>(v) |
@@ -301,6 +499,27 @@ int fc_adam_tma_run(const float* act, int64_t lda, const __nv_bfloat16* Bs, floa
     const int rc = tma::make_map(&mb, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<__nv_bfloat16*>(Bs), dims, str, box,
                                  CU_TENSOR_MAP_SWIZZLE_128B);
     if (rc != VC_OK) return rc;
+  }
+  static const int variant = getenv("VAECLUST_FC_ADAM_TMA") ? atoi(getenv("VAECLUST_FC_ADAM_TMA")) : 0;
+  static const bool approx2 = getenv("VAECLUST_FC_ADAM_APPROX") && atoi(getenv("VAECLUST_FC_ADAM_APPROX")) != 0;
+  if (variant == 2) {
+    FaArgs a;
+    memset(&a, 0, sizeof(a));
+    a.A = act; a.lda = lda; a.M = M; a.K = K; a.transposed = transposed; a.ldo = ldo; a.shadow = ad.shadow; a.step = ad.step;
+    a.lr = ad.lr; a.b1 = ad.b1; a.b2 = ad.b2; a.eps = ad.eps; a.bc1 = ad.bc1; a.bc2 = ad.bc2;
+    a.idesc = tc05::idesc(tc05::kFmtBF16, 128, transposed ? 128 : 256, 0, 0);
+    const size_t smem = FR_G_BYTES + FA_B_BYTES + 2 * FA_A_BYTES + 9 * 8 + 16 + 1024;
+    int grid = sm_count();
+    if (grid > M / 128) grid = M / 128;
+    if (approx2) {
+      VC_CUDA(cudaFuncSetAttribute(fc_adam_rows_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      fc_adam_rows_kernel<true><<<grid, FR_THREADS, smem, s>>>(a, mb, p, ad.m, ad.v);
+    } else {
+      VC_CUDA(cudaFuncSetAttribute(fc_adam_rows_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      fc_adam_rows_kernel<false><<<grid, FR_THREADS, smem, s>>>(a, mb, p, ad.m, ad.v);
+    }
+    VC_LAUNCH_CHECK();
+    return VC_OK;
   }
   const uint64_t dims[2] = {(uint64_t)(transposed ? M : N), (uint64_t)(transposed ? N : M)};
   const uint64_t str[1] = {(uint64_t)ldo * 4};
