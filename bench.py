@@ -288,11 +288,16 @@ def bench_vae(args, rank, world, device, group):
     # ---- end to end: the dataset lives in pinned HOST memory; every step's batch is copied host->device inside the
     # timed region (vaeclust.train.HostBatchFeeder: double-buffered on a copy stream, overlapping the previous step) and
     # the step's (loss, recon, kl) is read back to the host every step, like the reference's three .item() calls.
-    from vaeclust.train import HostBatchFeeder
+    # The read is pipelined (vaeclust.train.StepResultReader): the 12-byte copy into pinned memory is enqueued right behind
+    # every step and the host takes it one step later, so the next step is already submitted when the host waits; the
+    # last step's copy is waited for inside the timed region.  VAECLUST_BENCH_SYNC_READ=1 reads synchronously instead.
+    from vaeclust.train import HostBatchFeeder, StepResultReader
     feeder = HostBatchFeeder([t.cpu() for t in (X, lyr, m)], BATCH, device)
     sink = []
+    sync_read = os.environ.get("VAECLUST_BENCH_SYNC_READ", "0") == "1"
 
     def e2e_run(first, n):
+        reader = StepResultReader(3, device)
         feeder.prefetch(batch_idx(first))
         for s in range(first, first + n):
             xb, lb, mb = feeder.get()
@@ -301,7 +306,14 @@ def bench_vae(args, rank, world, device, group):
             feeder.release()
             if s + 1 < first + n:   # enqueued after this step's launch, so the host-side copy calls hide behind it
                 feeder.prefetch(batch_idx(s + 1))
-            sink.append(st.cpu())  # device->host read of the step's result: one sync per step
+            if sync_read:
+                sink.append(st.cpu())  # device->host read of the step's result: one sync per step
+            else:
+                prev = reader.push(st)  # device->host read of every step's result, consumed one step later
+                if prev is not None:
+                    sink.append(prev)
+        if not sync_read:
+            sink.append(reader.flush())
 
     e2e_run(0, min(2, args.warmup))
     ms_e2e = timed_max_ms(lambda s: e2e_run(100, args.steps) if s == 0 else None, args.steps, world, device)

@@ -287,6 +287,33 @@ class HostBatchFeeder:
         self._last["free"].record(torch.cuda.current_stream(self.device))
 
 
+class StepResultReader:
+    """Per-step device->host read of a step's small result tensor (loss, recon, kl -- the reference's three `.item()` calls,
+    12:268-270) that does not idle the GPU: the copy into pinned host memory is enqueued right behind the step and the host
+    consumes it ONE STEP LATER, while the next step already runs.  `push(st)` returns the previous step's values (None on
+    the first call); `flush()` returns the last step's values (waits for its copy)."""
+
+    def __init__(self, numel: int, device, dtype=torch.float32, depth: int = 2):
+        self.buf = [torch.empty(numel, dtype=dtype).pin_memory() for _ in range(depth)]
+        self.ev = [torch.cuda.Event() for _ in range(depth)]
+        self.device = device
+        self.n = 0
+
+    def _take(self, k: int):
+        self.ev[k].synchronize()
+        return self.buf[k].clone()
+
+    def push(self, st: torch.Tensor):
+        k = self.n % len(self.buf)
+        self.buf[k].copy_(st.detach().reshape(-1), non_blocking=True)
+        self.ev[k].record(torch.cuda.current_stream(self.device))
+        self.n += 1
+        return self._take((self.n - 2) % len(self.buf)) if self.n >= 2 else None
+
+    def flush(self):
+        return self._take((self.n - 1) % len(self.buf)) if self.n >= 1 else None
+
+
 @dataclass
 class TrainLog:
     loss: List[float] = field(default_factory=list)
