@@ -100,6 +100,44 @@ def synth_vae_data(n, device, seed=0):
     return X.contiguous(), (lyr * m).contiguous(), m.contiguous()
 
 
+def bench_vae_t646(args, rank, world, device, group):
+    """The same script-12 step at the reference's real clip length T = 646 (12:260 crops 648 -> 646): odd widths
+    (323 / 162 / 81) keep it off the bf16-NHWC stack path, so this is the per-layer path of DESIGN.md 4a.  One GPU,
+    CUDA-graph replays, 512 resident clips."""
+    import torch
+    from vaeclust import nn, ops as vops
+    from vaeclust.train import GraphedVAEStep
+    T = 646
+    vops.set_precision(args.precision)
+    g = torch.Generator(device=device).manual_seed(3)
+    n = 512
+    X = torch.randn(n, 1, F_MEL, T, device=device, generator=g)
+    lyr = torch.randn(n, LYR, device=device, generator=g)
+    m = (torch.rand(n, 1, device=device, generator=g) < 0.593).float()
+    torch.manual_seed(42)
+    model = nn.ConvMultiModalVAE(1, (F_MEL, T), ZDIM, LYR).to(device).train()
+    step = GraphedVAEStep(model, "conv12", lr=2e-3, beta=1.0, warmup=2)
+    eps_gen = torch.Generator(device=device).manual_seed(11)
+
+    def run(s):
+        sel = torch.arange(s * BATCH, (s + 1) * BATCH, device=device) % n
+        eps = torch.randn(BATCH, ZDIM, device=device, generator=eps_gen)
+        return step(X.index_select(0, sel), lyr.index_select(0, sel), m.index_select(0, sel), eps=eps)
+
+    for s in range(4):
+        run(s)
+    ms = timed_max_ms(lambda s: run(4 + s), args.steps, 1, device)
+    loss = float(run(99)[0])
+    n_params = sum(p.numel() for p in model.parameters())
+    del step, model, X
+    torch.cuda.empty_cache()
+    return {"metric": "VAE train clips/s at T = 646", "value": BATCH * args.steps / (ms * 1e-3), "unit": UNIT,
+            "ms_per_step": ms / args.steps, "n_params": n_params, "last_loss": loss,
+            "config": {"workload": f"script-12 conv multimodal VAE train step, batch {BATCH}, 1x{F_MEL}x{T} (the reference's clip "
+                                   "length; output cropped 648 -> 646), per-layer fp32-NCHW path (odd widths)",
+                       "submission": "one CUDA graph replay per step"}}
+
+
 def flops_of(name: str, sig) -> float:
     """Algorithmic FLOPs of one C-ABI call from its integer arguments ('algorithmic work')."""
     try:
@@ -888,6 +926,11 @@ def main():
         extra["kmeans"] = bench_kmeans(rank, world, device, group, pk)
         extra["silhouette"] = bench_silhouette(rank, world, device, group, pk)
         extra["cvae19"] = bench_cvae19(args, rank, world, device, group, pk)
+        if rank == 0 and world == 1:
+            try:
+                extra["vae_t646"] = bench_vae_t646(args, rank, world, device, group)
+            except Exception as e:  # noqa: BLE001  (an extra line must not take the headline down)
+                extra["vae_t646"] = {"unavailable": repr(e)}
     cpu = None
     if rank == 0 and world == 1 and not args.skip_cpu:
         v, spstep, cores = cpu_vae_steps(BATCH, 3, 1)
