@@ -15,8 +15,16 @@ gen = torch.Generator(device="cuda").manual_seed(0)
 rnd = lambda *s: torch.randn(*s, device="cuda", generator=gen)
 reps = int(sys.argv[1]) if len(sys.argv) > 1 else 10
 flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+# argv[2] = "tlb": also touch one element per 64 KB of an 8 GB buffer between calls (4096 distinct 2 MB pages), so that the
+# address-translation caches are cold at every launch, as they are inside a training step
+thrash = torch.zeros(1 << 31, dtype=torch.float32, device="cuda") if len(sys.argv) > 2 and sys.argv[2] == "tlb" else None
 for name, (cin, cout) in {"enc W [256][262144]": (WIDE, HID), "dec W [262144][256]": (HID, WIDE)}.items():
     dy, x = rnd(B, cout) * 1e-2, rnd(B, cin)
+    if len(sys.argv) > 2 and sys.argv[2] == "sparse":
+        # what training data looks like: ReLU outputs with dead units -> whole rows / columns of the gradient are exactly 0,
+        # and exp_avg / exp_avg_sq stay exactly 0 there (IEEE sqrt and division take their special-case paths for 0)
+        x = torch.relu(x) * (torch.rand(1, cin, device="cuda", generator=gen) > 0.3)
+        dy = dy * (torch.rand(1, cout, device="cuda", generator=gen) > 0.3)
     W = rnd(cout, cin) * 0.01
     m, v = torch.zeros_like(W), torch.zeros_like(W)
     sh = W.to(torch.bfloat16)
@@ -28,6 +36,8 @@ for name, (cin, cout) in {"enc W [256][262144]": (WIDE, HID), "dec W [262144][25
     ts = []
     for _ in range(reps):
         flush.zero_()
+        if thrash is not None:
+            thrash[::16384].add_(1.0)
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record(); call(); e1.record()
         torch.cuda.synchronize()

@@ -45,11 +45,25 @@ struct SkArgs {
 };
 
 // torch.optim.Adam's arithmetic in the order adam_multi_kernel (misc.cu) uses, so fused and unfused steps agree
+// APPROX (the default of the fused update, which exists in bf16 mode only; VAECLUST_FC_ADAM_IEEE=1 restores IEEE): the square
+// root and the division as sqrt.approx / div.approx (1 + 2 ulp) -- 4 instructions instead of ~17, and no special-case paths.
+// The fused epilogue is instruction-latency bound (six more instructions per element cost 12 %), and the IEEE sequences
+// leave their fast path for zero / tiny inputs as soon as ONE lane of a warp holds one, which training data is full of
+// (weights that feed from dead ReLU units have gradient, exp_avg and exp_avg_sq exactly 0): 337 us per launch with dense random
+// gradients, 470 us with 30 % zero rows / columns (profiles/prof_fc_adam.py sparse).  The relative error of the update
+// (<= 4e-7) is four orders below the bf16 rounding of the operands that produced the gradient.
+template <bool APPROX>
 __device__ __forceinline__ void sk_adam(float g, float& p, float& m, float& v, float b1, float b2, float step_size,
                                         float inv_sqrt_bc2, float eps) {
   m = b1 * m + (1.f - b1) * g;
   v = b2 * v + (1.f - b2) * g * g;
-  p -= step_size * (m / (sqrtf(v) * inv_sqrt_bc2 + eps));
+  if (APPROX) {
+    float sq;
+    asm("sqrt.approx.f32 %0, %1;" : "=f"(sq) : "f"(v));
+    p -= step_size * __fdividef(m, sq * inv_sqrt_bc2 + eps);
+  } else {
+    p -= step_size * (m / (sqrtf(v) * inv_sqrt_bc2 + eps));
+  }
 }
 
 __device__ __forceinline__ uint32_t sk_pack(float a, float b) {
@@ -313,12 +327,22 @@ skinny_gemm_kernel(const SkArgs a, const __grid_constant__ CUtensorMap mapB, con
             mm[u] = ok[u] ? __ldcs(reinterpret_cast<const float4*>(a.ad_m + off[u])) : z;
             vv[u] = ok[u] ? __ldcs(reinterpret_cast<const float4*>(a.ad_v + off[u])) : z;
           }
+          if (a.adam == 2) {      // (uniform)
 #pragma unroll
-          for (int u = 0; u < 4; ++u) {
-            sk_adam(gg[u].x, pp[u].x, mm[u].x, vv[u].x, a.ad_b1, a.ad_b2, step_size, inv_sqrt_bc2, a.ad_eps);
-            sk_adam(gg[u].y, pp[u].y, mm[u].y, vv[u].y, a.ad_b1, a.ad_b2, step_size, inv_sqrt_bc2, a.ad_eps);
-            sk_adam(gg[u].z, pp[u].z, mm[u].z, vv[u].z, a.ad_b1, a.ad_b2, step_size, inv_sqrt_bc2, a.ad_eps);
-            sk_adam(gg[u].w, pp[u].w, mm[u].w, vv[u].w, a.ad_b1, a.ad_b2, step_size, inv_sqrt_bc2, a.ad_eps);
+            for (int u = 0; u < 4; ++u) {
+              sk_adam<true>(gg[u].x, pp[u].x, mm[u].x, vv[u].x, a.ad_b1, a.ad_b2, step_size, inv_sqrt_bc2, a.ad_eps);
+              sk_adam<true>(gg[u].y, pp[u].y, mm[u].y, vv[u].y, a.ad_b1, a.ad_b2, step_size, inv_sqrt_bc2, a.ad_eps);
+              sk_adam<true>(gg[u].z, pp[u].z, mm[u].z, vv[u].z, a.ad_b1, a.ad_b2, step_size, inv_sqrt_bc2, a.ad_eps);
+              sk_adam<true>(gg[u].w, pp[u].w, mm[u].w, vv[u].w, a.ad_b1, a.ad_b2, step_size, inv_sqrt_bc2, a.ad_eps);
+            }
+          } else {
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+              sk_adam<false>(gg[u].x, pp[u].x, mm[u].x, vv[u].x, a.ad_b1, a.ad_b2, step_size, inv_sqrt_bc2, a.ad_eps);
+              sk_adam<false>(gg[u].y, pp[u].y, mm[u].y, vv[u].y, a.ad_b1, a.ad_b2, step_size, inv_sqrt_bc2, a.ad_eps);
+              sk_adam<false>(gg[u].z, pp[u].z, mm[u].z, vv[u].z, a.ad_b1, a.ad_b2, step_size, inv_sqrt_bc2, a.ad_eps);
+              sk_adam<false>(gg[u].w, pp[u].w, mm[u].w, vv[u].w, a.ad_b1, a.ad_b2, step_size, inv_sqrt_bc2, a.ad_eps);
+            }
           }
 #pragma unroll
           for (int u = 0; u < 4; ++u) {
@@ -565,7 +589,8 @@ static int skinny_gemm_run_impl(int op, const float* in0, const float* in1, cons
     a.idesc = tc05::idesc(tc05::kFmtBF16, 128, 128, 0, 0);
   }
   if (adam) {
-    a.adam = 1; a.ad_m = adam->m; a.ad_v = adam->v; a.ad_step = adam->step; a.ad_shadow = adam->shadow;
+    static const bool ieee = getenv("VAECLUST_FC_ADAM_IEEE") && atoi(getenv("VAECLUST_FC_ADAM_IEEE")) != 0;
+    a.adam = ieee ? 1 : 2; a.ad_m = adam->m; a.ad_v = adam->v; a.ad_step = adam->step; a.ad_shadow = adam->shadow;
     a.ad_lr = adam->lr; a.ad_b1 = adam->b1; a.ad_b2 = adam->b2; a.ad_eps = adam->eps; a.ad_bc1 = adam->bc1; a.ad_bc2 = adam->bc2;
     // the non-transposed epilogue transposes 8 x (32 x 33) floats through the operand ring; the barriers sit behind it
     VC_REQUIRE(ring >= 8 * 32 * 36 * 4, VC_ERR_UNSUPPORTED, "skinny_gemm: operand ring too small for the Adam epilogue");
