@@ -274,7 +274,8 @@ int vc_adam_multi_at(const VcAdamChunk* table, int n_chunks, float lr, float bet
                      const VcAdamDeviceStep* step_state, void* stream);
 /* Weight gradient of a wide nn.Linear (the two 67 M-parameter layers of 12:98-103,129-132) FUSED with its Adam update
  * (12:233,270): dW = dy^T x is formed in tensor memory and applied to W / exp_avg / exp_avg_sq in the epilogue; the
- * gradient is never written to memory.  Arithmetic order as vc_adam_multi.  step_state (device, advanced by vc_adam_tick)
+ * gradient is never written to memory.  Arithmetic order as vc_adam_multi, the quotient with sqrt.approx / div.approx
+ * (this path exists in bf16 mode only; VAECLUST_FC_ADAM_IEEE=1 restores IEEE).  step_state (device, advanced by vc_adam_tick)
  * supplies the bias corrections when non-NULL, else bias_corr1 / bias_corr2 are used.  Single-process training only. */
 int vc_linear_wgrad_adam_supported(int B, int Cin, int Cout);
 size_t vc_linear_wgrad_adam_workspace_bytes(int B, int Cin, int Cout);
